@@ -1,0 +1,382 @@
+"""FedAvg coordinator: round state machine + gRPC service.
+
+Capability parity with ``fl_server.py`` (all of it), re-designed as a single-owner state
+machine (one lock, injectable clock) instead of module globals mutated from ten gRPC
+worker threads with no lock (``fl_server.py:14-20``, quirk Q11).
+
+Message vocabulary and state strings are the reference's:
+
+==========  =========================================  ==================================
+request     reference handler                           reply
+==========  =========================================  ==================================
+ready  'R'  ``ready_client``   fl_server.py:45-81       config{state SW|CTW, model_version,
+                                                        current_round, max_train_round, model_type}
+update 'P'  ``send_parameter`` fl_server.py:23-24       update_rep{type P, buffer_chunk, title "parameters"}
+update 'T'  ack               fl_server.py:162-169      update_rep{type T}
+update 'L'  ``save_chunks_to_file`` :84-89,170-175      update_rep{type L, title}
+update 'D'  ``manage_rounds`` fl_server.py:107-135      update_rep{type D, config{state RESP_ACY|RESP_ARY|FIN,...}}
+version 'P' ``version_check`` fl_server.py:138-149      version_rep{state WAIT|NOT_WAIT|FIN, ...}
+==========  =========================================  ==================================
+
+Deliberate fixes: Q1 per-round mean (updates cleared each round), Q2 the
+broadcast carries the *aggregated* weights, Q7 FIN is a real enum label, Q11 locking,
+Q12 correctly spelt send limit, Q13 directories created, Q14 model_type "unet".
+Extensions: sample-count weighting, FedAdam, quorum + round deadline, server-issued
+unique client ids, chunked payloads above the message cap, resume from checkpoint.
+"""
+from __future__ import annotations
+
+import json
+import os
+import threading
+import time
+from concurrent import futures
+from dataclasses import dataclass, field
+from typing import Callable, Dict, List, Optional, Sequence
+
+import numpy as np
+
+from ..config import Config
+from ..io import checkpoint as ckpt
+from ..io import weights as wio
+from ..parallel.fedavg import FedAdam, FedAvg, make_strategy
+from . import messages as pb
+
+SW, CTW = "SW", "CTW"
+RESP_ACY, RESP_ARY, FIN = "RESP_ACY", "RESP_ARY", "FIN"
+MODEL_TYPE_ALIASES = {"mobilenet_v2": "unet", "unet": "unet"}
+
+
+class HostAggregator:
+    """NumPy aggregation (the reference's place for it: server CPU, ``fl_server.py:92-102``)."""
+
+    kind = "host"
+
+    def __init__(self, strategy):
+        self.strategy = strategy
+
+    def aggregate(self, global_w, updates, num_samples=None):
+        return self.strategy.aggregate(global_w, updates, num_samples)
+
+
+@dataclass
+class FaultInjector:
+    """Test hook: drop / delay / duplicate inbound requests by type tag."""
+
+    drop: Dict[str, int] = field(default_factory=dict)  # tag -> how many to drop
+    delay_s: Dict[str, float] = field(default_factory=dict)
+    duplicate: Dict[str, int] = field(default_factory=dict)
+
+    def on_request(self, tag: str, sleep: Callable[[float], None]) -> str:
+        if self.delay_s.get(tag):
+            sleep(self.delay_s[tag])
+        if self.drop.get(tag, 0) > 0:
+            self.drop[tag] -= 1
+            return "drop"
+        if self.duplicate.get(tag, 0) > 0:
+            self.duplicate[tag] -= 1
+            return "duplicate"
+        return "ok"
+
+
+class FLServer:
+    def __init__(self, cfg: Config, initial_weights: Sequence[np.ndarray], spec=None, aggregator=None,
+                 clock: Callable[[], float] = time.monotonic, sleep: Callable[[float], None] = time.sleep,
+                 fault: Optional[FaultInjector] = None, log: Callable[[str], None] = print):
+        from ..models.spec import REFERENCE_SPEC
+        self.cfg = cfg
+        self.spec = spec or REFERENCE_SPEC
+        self.clock, self.sleep, self.fault, self.log = clock, sleep, fault, log
+        self.lock = threading.RLock()
+        s = cfg.server
+        if aggregator is None:
+            kw = {}
+            if s.strategy == "fedadam":
+                kw = dict(eta=s.fedadam_eta, beta1=s.fedadam_beta1, beta2=s.fedadam_beta2, tau=s.fedadam_tau,
+                          trainable_mask=[t.trainable for t in self.spec.tensors])
+            aggregator = HostAggregator(make_strategy(s.strategy, **kw))
+        self.aggregator = aggregator
+        # ---- state (reference globals, fl_server.py:14-20) ----
+        self.global_weights: List[np.ndarray] = [np.asarray(w, np.float32) for w in initial_weights]
+        self.ready_clients: List[str] = []  # readyClientSids
+        self.round_reporters: List[str] = []  # currentRoundClientUpdates
+        self.round_updates: List[List[np.ndarray]] = []  # received_parameters (cleared every round: fix Q1)
+        self.round_samples: List[float] = []
+        self.round_metrics: List[dict] = []
+        self.current_round = 0  # ALL_CURRENT_ROUND
+        self.model_version = s.initial_model_version  # MODEL_VERSION
+        self.window_deadline: Optional[float] = None  # CHECK_TRAIN_TIMER / CHECK_CLIENT_TRAINING
+        self.round_started_at: Optional[float] = None
+        self.finished = False
+        self.history: List[dict] = []
+        self._payload_cache = {}
+        self._chunks: Dict[str, Dict[int, bytes]] = {}
+        self._next_id = 0
+        if s.resume and ckpt.has_checkpoint(s.weights_dir):
+            self._resume()
+
+    # ------------------------------------------------------------------ helpers
+    def _window_closed(self) -> bool:
+        return self.window_deadline is not None and self.clock() >= self.window_deadline
+
+    def serialized_weights(self) -> bytes:
+        """``send_parameter`` (fl_server.py:23-24); serialised once per model version."""
+        fmt = self.cfg.transport.payload_format
+        key = (self.model_version, fmt)
+        if key not in self._payload_cache:
+            self._payload_cache = {key: wio.dumps(self.global_weights, fmt)}
+        return self._payload_cache[key]
+
+    def _target_count(self) -> int:
+        return len(self.ready_clients)
+
+    # ------------------------------------------------------------------ handlers
+    def ready_client(self, name: str, config: dict) -> dict:
+        s = self.cfg.server
+        with self.lock:
+            if self.window_deadline is None:
+                self.window_deadline = self.clock() + s.admission_window_s
+            if self._window_closed() or self.finished:
+                return {"state": CTW}
+        if s.ready_delay_s > 0:
+            self.sleep(s.ready_delay_s)  # fl_server.py:56 (outside the lock)
+        with self.lock:
+            assigned = name
+            if not name or (name in self.ready_clients and config.get("rejoin", 0) != 1):
+                # reference names are client{randint(1,100000)} and can collide (fl_client.py:26)
+                self._next_id += 1
+                assigned = f"{name or 'client'}#{self._next_id}"
+            if assigned not in self.ready_clients:
+                self.ready_clients.append(assigned)
+            out = {}
+            if int(config.get("current_round", 0) or 0) == 0:
+                self.current_round = 1
+                if self.round_started_at is None:
+                    self.round_started_at = self.clock()
+                out = {"state": SW, "model_version": self.model_version, "current_round": self.current_round,
+                       "max_train_round": s.max_rounds, "model_type": s.model_type, "cname": assigned,
+                       "payload_format": self.cfg.transport.payload_format}
+            return out
+
+    def _aggregate_locked(self) -> str:
+        s = self.cfg.server
+        t0 = time.perf_counter()
+        ns = self.round_samples if all(n > 0 for n in self.round_samples) else None
+        self.global_weights = [np.asarray(w, np.float32) for w in
+                               self.aggregator.aggregate(self.global_weights, self.round_updates, ns)]
+        agg_ms = (time.perf_counter() - t0) * 1e3
+        rec = {"round": self.current_round, "clients": list(self.round_reporters), "num_clients": len(self.round_updates),
+               "samples": list(self.round_samples), "aggregate_ms": agg_ms, "model_version": self.model_version + 1,
+               "aggregator": getattr(self.aggregator, "kind", "?"), "client_metrics": list(self.round_metrics)}
+        self.history.append(rec)
+        finished_round = self.current_round
+        # clients that did not report are no longer waited for in later rounds
+        self.ready_clients = [c for c in self.ready_clients if c in self.round_reporters] or self.ready_clients
+        self.round_reporters, self.round_updates, self.round_samples, self.round_metrics = [], [], [], []
+        self.current_round += 1
+        self.model_version += 1
+        self.round_started_at = self.clock()
+        self._persist(rec)
+        if finished_round >= s.max_rounds:
+            self.finished = True
+            self.log(f"[server] all {s.max_rounds} rounds done -> FIN")
+            return FIN
+        self.log(f"[server] round {finished_round} aggregated ({rec['num_clients']} clients, {agg_ms:.2f} ms) -> RESP_ARY")
+        return RESP_ARY
+
+    def _maybe_timeout_locked(self):
+        s = self.cfg.server
+        if s.round_timeout_s <= 0 or self.finished or not self.round_updates or self.round_started_at is None:
+            return
+        if self.clock() - self.round_started_at >= s.round_timeout_s and \
+                len(self.round_updates) >= max(1, s.min_fit_clients):
+            self.log(f"[server] round {self.current_round} deadline: aggregating {len(self.round_updates)} of "
+                     f"{self._target_count()} clients")
+            self._aggregate_locked()
+
+    def manage_rounds(self, cname: str, client_round: int, weights: List[np.ndarray], num_samples: float = 0.0,
+                      metrics: Optional[dict] = None) -> str:
+        with self.lock:
+            self._maybe_timeout_locked()
+            if self.finished or client_round != self.current_round:
+                return FIN if self.finished else RESP_ACY  # stale update dropped (fl_server.py:134-135)
+            if cname in self.round_reporters:
+                return RESP_ACY  # duplicate report
+            if len(weights) != self.spec.num_tensors:
+                raise ValueError(f"update from {cname} has {len(weights)} tensors, expected {self.spec.num_tensors}")
+            self.round_reporters.append(cname)
+            self.round_updates.append(weights)
+            self.round_samples.append(float(num_samples))
+            if metrics:
+                self.round_metrics.append({"cname": cname, **metrics})
+            target = self._target_count()
+            s = self.cfg.server
+            if s.round_timeout_s <= 0 and s.min_fit_clients > 0:
+                target = min(target, s.min_fit_clients)
+            if len(self.round_updates) >= target:
+                return self._aggregate_locked()
+            return RESP_ACY
+
+    def version_check(self, client_version: int, client_round: int):
+        with self.lock:
+            self._maybe_timeout_locked()
+            if self.model_version == client_version:
+                return pb.State.WAIT, {}
+            cfgd = {"current_round": self.current_round, "model_version": self.model_version}
+            if client_round >= self.cfg.server.max_rounds:
+                return pb.State.FIN, cfgd
+            return pb.State.NOT_WAIT, cfgd
+
+    def save_log_chunk(self, chunk: bytes, title: str, append: bool) -> str:
+        """'L' sink.  Reference strips the 11-char './send_logs' prefix and writes under '.'
+        (fl_server.py:84-89); here the path is confined to ``cfg.server.log_dir``."""
+        rel = title[11:] if title.startswith("./send_logs") else title
+        rel = os.path.normpath("/" + rel.replace("\\", "/")).lstrip("/")
+        root = os.path.abspath(self.cfg.server.log_dir)
+        path = os.path.abspath(os.path.join(root, rel))
+        if not path.startswith(root + os.sep):
+            raise ValueError("log path escapes the log directory")
+        os.makedirs(os.path.dirname(path), exist_ok=True)
+        with open(path, "ab" if append else "wb") as f:
+            f.write(chunk)
+        return path
+
+    # ------------------------------------------------------------------ dispatch
+    def handle(self, req) -> list:
+        """One request -> list of responses (exactly one, except chunked weight replies)."""
+        R = pb.transportResponse
+        if req.ready_req.type == "R":
+            if self._fault("R") == "drop":
+                return []
+            cfgd = self.ready_client(req.ready_req.cname, pb.from_config(req.ready_req.config))
+            return [R(ready_rep=pb.ReadyRep(config=pb.to_config(cfgd)))]
+        u = req.update_req
+        if u.type == "P":
+            return self._weight_replies(lambda chunk, cfgd: R(update_rep=pb.UpdateRep(
+                type="P", buffer_chunk=chunk, title="parameters", config=pb.to_config(cfgd))), {})
+        if u.type == "T":
+            return [R(update_rep=pb.UpdateRep(type="T"))]
+        if u.type == "L":
+            ucfg = pb.from_config(u.config)
+            self.save_log_chunk(u.buffer_chunk, u.title, append=int(ucfg.get("chunk_index", 0) or 0) > 0)
+            return [R(update_rep=pb.UpdateRep(type="L", title=u.title))]
+        if u.type == "D":
+            f = self._fault("D")
+            if f == "drop":
+                return []
+            ucfg = pb.from_config(u.config)
+            payload = self._assemble_chunks(u.cname, u.buffer_chunk, ucfg)
+            if payload is None:
+                return [R(update_rep=pb.UpdateRep(type="D", config=pb.to_config({"state": "CHUNK"})))]
+            weights = wio.loads_auto(payload, allow_pickle=self.cfg.transport.allow_pickle)
+            metrics = {k: ucfg[k] for k in ("loss", "accuracy", "val_loss", "val_accuracy") if k in ucfg}
+            state = self.manage_rounds(u.cname, u.current_round, weights, float(ucfg.get("num_samples", 0) or 0), metrics)
+            if f == "duplicate":
+                self.manage_rounds(u.cname, u.current_round, weights)
+            cfgd = {"model_version": self.model_version, "current_round": self.current_round, "state": state}
+            if state == RESP_ARY:
+                return self._weight_replies(lambda chunk, c: R(update_rep=pb.UpdateRep(
+                    type="D", buffer_chunk=chunk, config=pb.to_config(c))), cfgd)
+            return [R(update_rep=pb.UpdateRep(type="D", config=pb.to_config(cfgd)))]
+        if req.version_req.type == "P":
+            vc = pb.from_config(req.version_req.config)
+            st, cfgd = self.version_check(int(vc.get("model_version", 0) or 0), int(vc.get("current_round", 0) or 0))
+            if st == pb.State.NOT_WAIT:
+                return self._weight_replies(lambda chunk, c: R(version_rep=pb.VersionRep(
+                    state=st, buffer_chunk=chunk, config=pb.to_config(c))), cfgd)
+            return [R(version_rep=pb.VersionRep(state=st, config=pb.to_config(cfgd)))]
+        raise ValueError("unrecognised request")
+
+    def _fault(self, tag: str) -> str:
+        return self.fault.on_request(tag, self.sleep) if self.fault else "ok"
+
+    def _weight_replies(self, make, cfgd: dict) -> list:
+        blob = self.serialized_weights()
+        cap = max(1, self.cfg.transport.max_message_mib - 1) * (1 << 20)
+        if len(blob) <= cap:
+            return [make(blob, cfgd)]
+        n = (len(blob) + cap - 1) // cap
+        return [make(blob[i * cap:(i + 1) * cap], {**cfgd, "chunk_index": i, "chunk_count": n}) for i in range(n)]
+
+    def _assemble_chunks(self, cname: str, chunk: bytes, ucfg: dict) -> Optional[bytes]:
+        n = int(ucfg.get("chunk_count", 0) or 0)
+        if n <= 1:
+            return chunk
+        with self.lock:
+            parts = self._chunks.setdefault(cname, {})
+            parts[int(ucfg.get("chunk_index", 0) or 0)] = chunk
+            if len(parts) < n:
+                return None
+            del self._chunks[cname]
+        return b"".join(parts[i] for i in range(n))
+
+    # gRPC servicer entry point (``TransportService.transport`` fl_server.py:209-212)
+    def transport(self, request_iterator, context=None):
+        for req in request_iterator:
+            for rep in self.handle(req):
+                yield rep
+
+    # ------------------------------------------------------------------ persistence
+    def _persist(self, rec: dict):
+        d = self.cfg.server.weights_dir
+        if not d:
+            return
+        os.makedirs(d, exist_ok=True)
+        wio.save_pickle_file(os.path.join(d, "weights.pickle"), self.global_weights)  # fl_server.py:104-105
+        strat = getattr(self.aggregator, "strategy", None)
+        extra = {}
+        st = strat.state() if strat is not None else {}
+        if st.get("m") is not None:
+            extra = {"fedadam_m": st["m"], "fedadam_v": st["v"]}
+        ckpt.save_checkpoint(d, self.spec, self.global_weights, extra_arenas=extra, meta={
+            "current_round": self.current_round, "model_version": self.model_version, "finished": self.finished,
+            "ready_clients": self.ready_clients, "strategy": self.cfg.server.strategy})
+        with open(os.path.join(d, "rounds.jsonl"), "a") as f:
+            f.write(json.dumps(rec) + "\n")
+
+    def _resume(self):
+        st = ckpt.load_checkpoint(self.cfg.server.weights_dir, self.spec)
+        self.global_weights = st["weights"]
+        m = st["meta"]
+        self.current_round = int(m.get("current_round", 0))
+        self.model_version = int(m.get("model_version", self.model_version))
+        self.finished = bool(m.get("finished", False))
+        self.ready_clients = list(m.get("ready_clients", []))
+        strat = getattr(self.aggregator, "strategy", None)
+        if strat is not None and "fedadam_m" in st["arenas"]:
+            strat.load_state({"m": st["arenas"]["fedadam_m"], "v": st["arenas"]["fedadam_v"]})
+        if self.ready_clients:
+            self.window_deadline = self.clock()  # window already closed for a resumed federation
+        self.log(f"[server] resumed at round {self.current_round}, model_version {self.model_version}")
+
+
+# ---------------------------------------------------------------------- gRPC plumbing
+def grpc_options(cfg: Config):
+    n = cfg.transport.max_message_mib * 1024 * 1024
+    return [("grpc.max_receive_message_length", n), ("grpc.max_send_message_length", n)]
+
+
+def make_grpc_server(server: FLServer, bind: Optional[str] = None):
+    """``serve()`` (fl_server.py:214-226).  Returns ``(grpc_server, bound_port)``; caller starts/stops it."""
+    import grpc
+    cfg = server.cfg
+    gs = grpc.server(futures.ThreadPoolExecutor(max_workers=cfg.transport.workers), options=grpc_options(cfg))
+    handler = grpc.stream_stream_rpc_method_handler(
+        server.transport, request_deserializer=pb.transportRequest.FromString,
+        response_serializer=pb.transportResponse.SerializeToString)
+    gs.add_generic_rpc_handlers((grpc.method_handlers_generic_handler(cfg.transport.service_path, {pb.METHOD: handler}),))
+    port = gs.add_insecure_port(bind or cfg.transport.bind)
+    return gs, port
+
+
+def serve_forever(server: FLServer):
+    gs, port = make_grpc_server(server)
+    gs.start()
+    server.log(f"[server] listening on {server.cfg.transport.bind} (port {port})")
+    try:
+        while not server.finished:
+            time.sleep(0.5)
+        time.sleep(2.0)  # let the last FIN replies drain
+    except KeyboardInterrupt:
+        pass
+    gs.stop(0)

@@ -1,0 +1,233 @@
+"""Protocol state machine + gRPC loopback (BASELINE config 1)."""
+import os
+import re
+import threading
+
+import numpy as np
+import pytest
+
+from crackfl.config import Config, fast_test_config
+from crackfl.io import weights as wio
+from crackfl.models.spec import REFERENCE_SPEC as S
+from crackfl.protocol import messages as pb
+from crackfl.protocol import client as C
+from crackfl.protocol.server import FLServer, FaultInjector, make_grpc_server
+
+
+class FakeClock:
+    def __init__(self):
+        self.t = 0.0
+    def __call__(self):
+        return self.t
+    def sleep(self, s):
+        self.t += s
+
+
+def _server(tmp_path, **kw):
+    cfg = fast_test_config()
+    cfg.server.weights_dir = str(tmp_path / "server_weights")
+    cfg.server.log_dir = str(tmp_path / "logs")
+    for k, v in kw.items():
+        setattr(cfg.server, k, v)
+    clk = FakeClock()
+    srv = FLServer(cfg, S.init_weights(0), S, clock=clk, sleep=clk.sleep, log=lambda s: None)
+    return srv, clk, cfg
+
+
+def _one(srv, req):
+    out = srv.handle(req)
+    assert len(out) == 1
+    return out[0]
+
+
+def _ready(srv, name):
+    return pb.from_config(_one(srv, next(C.request_ready(name))).ready_rep.config)
+
+
+def _done(srv, name, cr, w, extra=None):
+    reqs = list(C.request_traindone(name, cr, wio.dumps_raw(w), extra or {}, 1 << 30))
+    rep = _one(srv, reqs[0]).update_rep
+    return pb.from_config(rep.config), rep.buffer_chunk
+
+
+def test_proto_text_matches_runtime_descriptors():
+    txt = open(os.path.join(os.path.dirname(pb.__file__), "transport.proto")).read()
+    fd = pb.FILE_DESCRIPTOR_PROTO
+    for m in fd.message_type:
+        assert re.search(rf"message {m.name}\s*{{", txt), m.name
+        for f in m.field:
+            assert re.search(rf"\b{f.name}\s*=\s*{f.number};", txt), (m.name, f.name)
+    for v in fd.enum_type[0].value:
+        assert re.search(rf"\b{v.name}\s*=\s*{v.number};", txt)
+    assert "rpc transport(stream transportRequest) returns (stream transportResponse)" in txt
+    assert pb.VersionRep(state="FIN").state == pb.State.FIN  # fl_server.py:145 passes the string
+
+
+def test_admission_window_sw_then_ctw(tmp_path):
+    srv, clk, cfg = _server(tmp_path, admission_window_s=10.0, ready_delay_s=5.0)
+    c = _ready(srv, "a")
+    assert c["state"] == "SW" and c["current_round"] == 1 and c["max_train_round"] == 5 and c["model_version"] == 1
+    assert clk.t == 5.0  # the per-ready delay of fl_server.py:56
+    assert _ready(srv, "b")["state"] == "SW"   # t=5 -> 10: still inside the 10 s window at entry
+    assert _ready(srv, "late")["state"] == "CTW"  # t=10: window closed
+    assert srv.ready_clients == ["a", "b"]
+
+
+def test_name_collision_gets_unique_id(tmp_path):
+    srv, _, _ = _server(tmp_path)
+    a = _ready(srv, "client7"); b = _ready(srv, "client7")
+    assert a["cname"] == "client7" and b["cname"] != "client7" and len(srv.ready_clients) == 2
+
+
+def test_round_flow_acy_ary_fin_and_version_poll(tmp_path):
+    srv, clk, cfg = _server(tmp_path, max_rounds=2)
+    _ready(srv, "a"); _ready(srv, "b")
+    rep = _one(srv, next(C.request_parameter())).update_rep
+    assert rep.type == "P" and rep.title == "parameters"
+    w0 = wio.loads_auto(rep.buffer_chunk)
+    assert _one(srv, next(C.request_training("a"))).update_rep.type == "T"
+    wa = [x + 1 for x in w0]; wb = [x + 3 for x in w0]
+    c, blob = _done(srv, "a", 1, wa)
+    assert c["state"] == "RESP_ACY" and blob == b""
+    v = _one(srv, next(C.request_model_version(1, 1))).version_rep
+    assert v.state == pb.State.WAIT
+    c, blob = _done(srv, "b", 1, wb)
+    assert c["state"] == "RESP_ARY" and c["current_round"] == 2 and c["model_version"] == 2
+    agg = wio.loads_auto(blob)
+    np.testing.assert_allclose(agg[0], w0[0] + 2, rtol=1e-6)  # mean of the two updates
+    v = _one(srv, next(C.request_model_version(1, 1))).version_rep
+    assert v.state == pb.State.NOT_WAIT and pb.from_config(v.config)["current_round"] == 2
+    np.testing.assert_allclose(wio.loads_auto(v.buffer_chunk)[3], agg[3])
+    # stale round is dropped with RESP_ACY (fl_server.py:134-135)
+    c, _ = _done(srv, "a", 1, wa)
+    assert c["state"] == "RESP_ACY" and len(srv.round_updates) == 0
+    # round 2 = last round -> FIN; the straggler learns FIN from the poll (fix Q7)
+    c, _ = _done(srv, "a", 2, wa); assert c["state"] == "RESP_ACY"
+    c, _ = _done(srv, "b", 2, wb); assert c["state"] == "FIN"
+    v = _one(srv, next(C.request_model_version(2, 2))).version_rep
+    assert v.state == pb.State.FIN
+    # per-round mean only (fix Q1): round 2 result is again the mean of exactly two updates
+    np.testing.assert_allclose(srv.global_weights[0], w0[0] + 2, rtol=1e-6)
+    assert os.path.exists(os.path.join(cfg.server.weights_dir, "weights.pickle"))
+    assert len(srv.history) == 2
+
+
+def test_sample_weighted_strategy(tmp_path):
+    srv, _, _ = _server(tmp_path, strategy="fedavg_weighted")
+    _ready(srv, "a"); _ready(srv, "b")
+    w0 = S.init_weights(0)
+    _done(srv, "a", 1, [x * 0 + 1 for x in w0], {"num_samples": 1})
+    c, blob = _done(srv, "b", 1, [x * 0 + 5 for x in w0], {"num_samples": 3})
+    assert c["state"] == "RESP_ARY"
+    np.testing.assert_allclose(wio.loads_auto(blob)[0], 4.0, rtol=1e-6)
+
+
+def test_round_deadline_with_quorum(tmp_path):
+    srv, clk, _ = _server(tmp_path, round_timeout_s=30.0, min_fit_clients=1)
+    _ready(srv, "a"); _ready(srv, "dead")
+    w0 = S.init_weights(0)
+    c, _ = _done(srv, "a", 1, w0)
+    assert c["state"] == "RESP_ACY"
+    clk.t += 31
+    v = _one(srv, next(C.request_model_version(1, 1))).version_rep
+    assert v.state == pb.State.NOT_WAIT and srv.ready_clients == ["a"]
+
+
+def test_fault_injection_drop_and_duplicate(tmp_path):
+    srv, _, _ = _server(tmp_path)
+    srv.fault = FaultInjector(drop={"D": 1}, duplicate={"D": 1})
+    _ready(srv, "a"); _ready(srv, "b")
+    w0 = S.init_weights(0)
+    req = list(C.request_traindone("a", 1, wio.dumps_raw(w0), {}, 1 << 30))[0]
+    assert srv.handle(req) == []            # dropped
+    c = pb.from_config(_one(srv, req).update_rep.config)  # duplicated delivery counts once
+    assert c["state"] == "RESP_ACY" and len(srv.round_updates) == 1
+
+
+def test_log_upload_is_confined(tmp_path):
+    srv, _, cfg = _server(tmp_path)
+    f = tmp_path / "ev.bin"; f.write_bytes(b"x" * 1000)
+    for req in C.get_file_chunks(str(f), 400):
+        req.update_req.title = "./send_logs/logs/r1/ev.bin"
+        assert _one(srv, req).update_rep.type == "L"
+    assert (tmp_path / "logs" / "logs" / "r1" / "ev.bin").read_bytes() == b"x" * 1000
+    p = srv.save_log_chunk(b"z", "../../etc/passwd", False)
+    assert p.startswith(os.path.abspath(cfg.server.log_dir))
+
+
+def test_chunked_weights_both_directions(tmp_path):
+    srv, _, cfg = _server(tmp_path)
+    cfg.transport.max_message_mib = 3  # forces ~8.2 MB payloads into chunks
+    _ready(srv, "a")
+    reps = srv.handle(next(C.request_parameter()))
+    assert len(reps) > 1
+    _, blob = C._collect_weights(reps, "update_rep")
+    w = wio.loads_auto(blob)
+    reqs = list(C.request_traindone("a", 1, wio.dumps_raw(w), {}, 2 << 20))
+    assert len(reqs) > 1
+    states = [pb.from_config(_one(srv, r).update_rep.config)["state"] if i < len(reqs) - 1 else None
+              for i, r in enumerate(reqs[:-1])]
+    assert all(s == "CHUNK" for s in states)
+    last = srv.handle(reqs[-1])
+    assert pb.from_config(last[0].update_rep.config)["state"] == "RESP_ARY"
+
+
+def test_server_resume(tmp_path):
+    srv, _, cfg = _server(tmp_path)
+    _ready(srv, "a")
+    _done(srv, "a", 1, [x + 1 for x in S.init_weights(0)])
+    cfg.server.resume = True
+    srv2 = FLServer(cfg, S.init_weights(5), S, log=lambda s: None)
+    assert srv2.current_round == 2 and srv2.model_version == 2
+    np.testing.assert_allclose(srv2.global_weights[0], srv.global_weights[0])
+
+
+class _StubTrainer:
+    """Stands in for the local fit: adds a client-specific constant to every tensor."""
+    def __init__(self, delta):
+        self.delta, self.calls = delta, []
+    def fit(self, weights, cr):
+        self.calls.append(cr)
+        return [w + self.delta for w in weights], {"loss": 0.5, "accuracy": 0.9, "num_samples": 16}
+
+
+def test_two_clients_over_real_grpc_loopback(tmp_path, monkeypatch):
+    """BASELINE config 1 plumbing: 2 clients, real gRPC on an ephemeral port, 2 rounds."""
+    monkeypatch.chdir(tmp_path)
+    cfg = fast_test_config()
+    cfg.server.max_rounds = 2
+    cfg.server.weights_dir = str(tmp_path / "sw")
+    srv = FLServer(cfg, S.init_weights(0), S, log=lambda s: None)
+    gs, port = make_grpc_server(srv, "127.0.0.1:0")
+    gs.start()
+    try:
+        results = {}
+        def run_client(i, delta):
+            ccfg = fast_test_config()
+            ccfg.client.name = f"c{i}"
+            ccfg.client.weights_path = str(tmp_path / f"saved_weight_{i}" / "weights.pickle")
+            call, ch = C.make_stub(ccfg, f"127.0.0.1:{port}")
+            cl = C.FLClient(ccfg, _StubTrainer(delta), call, log=lambda s: None)
+            results[i] = (cl.run(), cl)
+            ch.close()
+        ts = [threading.Thread(target=run_client, args=(i, d)) for i, d in ((0, 1.0), (1, 3.0))]
+        [t.start() for t in ts]; [t.join(60) for t in ts]
+        assert all(not t.is_alive() for t in ts)
+    finally:
+        gs.stop(0)
+    assert results[0][0]["rounds"] == 2 and results[1][0]["rounds"] == 2
+    w0 = S.init_weights(0)
+    # each round adds mean(1,3)=2 to every tensor
+    np.testing.assert_allclose(srv.global_weights[0], w0[0] + 4, rtol=1e-5)
+    np.testing.assert_allclose(results[0][1].final_weights[0], w0[0] + 4, rtol=1e-5)
+    assert srv.finished and len(srv.history) == 2
+    assert srv.history[0]["client_metrics"][0]["accuracy"] == pytest.approx(0.9)
+    assert os.path.exists(tmp_path / "saved_weight_0" / "weights.pickle")
+
+
+def test_late_client_gets_ctw(tmp_path):
+    srv, clk, cfg = _server(tmp_path)
+    _ready(srv, "a")
+    clk.t += 100
+    cl = C.FLClient(cfg, _StubTrainer(0.0), srv.transport, sleep=clk.sleep, log=lambda s: None)
+    assert cl.run()["state"] == "CTW"
