@@ -1,0 +1,562 @@
+"""B200 U-Net engine: the whole train / eval / predict step as a static schedule of hand-written
+sm_100a kernels over pre-allocated NHWC bf16 buffers, captured in CUDA graphs.
+
+This is the device counterpart of ``change_model_layers`` + ``compile`` + ``fit`` / ``predict``
+(``client_fit_model.py:92-174``).  There is no autograd and no tracing compiler: forward,
+backward and the Keras-form Adam update are an explicit list of launches (``self.train_prog``)
+replayed as one ``cudaGraph`` per step.
+
+Design notes (what differs from the graph as written, with identical results):
+
+* parameters live in ONE flat fp32 arena in Keras ``get_weights()`` order/layout
+  (``models/spec.py``); FedAvg, pickle, h5 and checkpoints are views of it.  A table-driven
+  ``weight_prep`` launch re-lays the GEMM-shaped kernels out as bf16 K-major operands each step;
+* nearest ``UpSampling2D`` commutes with 1x1 convs, BN-apply, add, ReLU and the sigmoid, so the
+  decoder residual conv runs at low resolution and the head (1x1 conv + sigmoid + BCE) runs at
+  H/2 against the 2x2 mask pixels each logit covers: the (B,H,W,32) tensor never exists;
+* BN(train) needs a grid-wide reduction, so each BN is stats -> finalize -> apply fused into
+  its consumer (depthwise load, max-pool tail, decoder combine) instead of a separate pass;
+* a conv bias followed by training-mode BN has an exactly-zero gradient; it is not computed.
+
+GEMM-shaped ops (pointwise / residual 1x1 convs, ConvT-as-3x3-conv, their dgrad and wgrad) go
+to the tcgen05/TMEM/TMA kernels (``csrc/conv_tc.cu``) when ``conv_impl="tc"``, and to the
+CUDA-core cross-check kernels (``csrc/conv_simt.cu``) when ``conv_impl="simt"``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from ..io import weights as wio
+from ..ops import lib as L
+from .spec import REFERENCE_SPEC, UNetSpec
+
+
+def default_conv_impl() -> str:
+    return os.environ.get("CRACKFL_CONV_IMPL", "tc")
+
+
+class UNetEngine:
+    def __init__(self, spec: UNetSpec = REFERENCE_SPEC, batch: int = 16, height: int = 128, width: int = 128,
+                 device: Optional[int] = None, lr: float = 1e-3, beta1: float = 0.9, beta2: float = 0.999,
+                 eps: float = 1e-7, loss: str = "bce", conv_impl: Optional[str] = None, cuda_graph: bool = True,
+                 dice_smooth: float = 1.0):
+        if not torch.cuda.is_available():
+            raise RuntimeError("UNetEngine needs a CUDA device (sm_100a)")
+        spec.check_input(height, width)
+        self.lib = L.get_lib()
+        self.spec, self.B, self.H, self.W = spec, batch, height, width
+        self.dev = torch.device("cuda", torch.cuda.current_device() if device is None else device)
+        self.lr, self.b1, self.b2, self.eps = lr, beta1, beta2, eps
+        self.use_dice = 1 if loss == "bce_dice" else 0
+        self.dice_smooth = dice_smooth
+        self.conv_impl = conv_impl or default_conv_impl()
+        self.cuda_graph = cuda_graph
+        self.launches_per_step = 0
+        self._bufs: Dict[str, torch.Tensor] = {}
+        with torch.cuda.device(self.dev):
+            self._alloc_params()
+            self._build_ops_table()
+            self._alloc_activations()
+            self.train_prog = self._build_train()
+            self.eval_prog = self._build_forward(training=False, with_mask=True, prob=False)
+            self.pred_prog = self._build_forward(training=False, with_mask=False, prob=True)
+        self._graphs: Dict[str, torch.cuda.CUDAGraph] = {}
+        self.launches_per_step = len(self.train_prog) + 1  # + adam tick
+
+    # ------------------------------------------------------------------ allocation
+    def _new(self, name: str, shape, dtype=torch.bfloat16) -> torch.Tensor:
+        t = torch.zeros(tuple(int(s) for s in shape), dtype=dtype, device=self.dev)
+        self._bufs[name] = t
+        return t
+
+    def _alloc_params(self):
+        n = self.spec.arena_numel
+        self.arena = self._new("arena", (n,), torch.float32)
+        self.grads = self._new("grads", (n,), torch.float32)
+        self.m = self._new("adam_m", (n,), torch.float32)
+        self.v = self._new("adam_v", (n,), torch.float32)
+        self.step = self._new("adam_step", (1,), torch.int32)
+        # per-BN scratch: zeroed-every-step region [stats 2C | sums 2C]*, persistent region [bn 4C]*
+        self.bn_layers = [l for l in self.spec.layers if l.op == "bn"]
+        zoff, poff = 0, 0
+        self.bn_z, self.bn_p = {}, {}
+        for l in self.bn_layers:
+            self.bn_z[l.name] = zoff
+            zoff += 4 * l.cout
+            self.bn_p[l.name] = poff
+            poff += 4 * l.cout
+        self.zero_region = self._new("zero_region", (zoff + 16,), torch.float32)
+        self.acc_off = zoff  # 6 floats of loss/metric accumulators for the current step
+        self.bn_params = self._new("bn_params", (poff,), torch.float32)
+        self.metrics_total = self._new("metrics_total", (8,), torch.float32)
+
+    def P(self, tensor_idx: int) -> int:
+        """Device address of weight tensor ``tensor_idx`` inside the arena."""
+        return self.arena.data_ptr() + 4 * self.spec.tensors[tensor_idx].offset
+
+    def G(self, tensor_idx: int) -> int:
+        return self.grads.data_ptr() + 4 * self.spec.tensors[tensor_idx].offset
+
+    def _build_ops_table(self):
+        """bf16 GEMM operands: Wf (forward) and Wd (dgrad) for every GEMM-shaped layer."""
+        descs: List[L.PrepDesc] = []
+        self.ops: Dict[str, Tuple[int, int, int, int]] = {}  # name -> (elem offset, N, T, K)
+        off = 0
+
+        def add(name, src_off, N, T, K, s_n, s_t, s_k):
+            nonlocal off
+            d = L.PrepDesc(src_off=src_off, dst_off=off, N=N, T=T, K=K, pad_=0, s_n=s_n, s_t=s_t, s_k=s_k)
+            descs.append(d)
+            self.ops[name] = (off, N, T, K)
+            off += (N * T * K + 63) // 64 * 64
+
+        for l in self.spec.layers:
+            ts = self.spec.tensors
+            if l.op == "sepconv":
+                pw = ts[l.tensors[1]]  # (1,1,in,out)
+                add(l.name + ".f", pw.offset, l.cout, 1, l.cin, 1, 0, l.cout)
+                add(l.name + ".d", pw.offset, l.cin, 1, l.cout, l.cout, 0, 1)
+            elif l.op == "conv" and l.ksize == 1 and l.cout >= 8:
+                k = ts[l.tensors[0]]
+                add(l.name + ".f", k.offset, l.cout, 1, l.cin, 1, 0, l.cout)
+                add(l.name + ".d", k.offset, l.cin, 1, l.cout, l.cout, 0, 1)
+            elif l.op == "convT":
+                k = ts[l.tensors[0]]  # (3,3,out,in); conv-equivalent Wc[t][i][o] = K[8-t][o][i]
+                oi = l.cout * l.cin
+                add(l.name + ".f", k.offset + 8 * oi, l.cout, 9, l.cin, l.cin, -oi, 1)
+                add(l.name + ".d", k.offset, l.cin, 9, l.cout, 1, oi, l.cin)
+        self.ops_buf = self._new("ops", (off,), torch.bfloat16)
+        arr = (L.PrepDesc * len(descs))(*descs)
+        raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).clone()
+        self.desc_dev = raw.to(self.dev)
+        self._bufs["prep_descs"] = self.desc_dev
+        self.num_desc = len(descs)
+
+    def op_ptr(self, name: str) -> int:
+        return self.ops_buf.data_ptr() + 2 * self.ops[name][0]
+
+    def _alloc_activations(self):
+        s, B, H, W = self.spec, self.B, self.H, self.W
+        self.x_u8 = self._new("x_u8", (B, H, W, 3), torch.uint8)
+        self.mask_u8 = self._new("mask_u8", (B, H, W), torch.uint8)
+        self.prob = self._new("prob", (B, H, W), torch.float32)
+        r, c = H // 2, s.entry
+        rw = W // 2
+        n = self._new
+        n("y0", (B, r, rw, c)); n("x0", (B, r, rw, c)); n("x0e", (B, r // 2, rw // 2, c))
+        n("dz0", (B, r, rw, c)); n("dy0", (B, r, rw, c))
+        cin = c
+        self.enc = []
+        for k, f in enumerate(s.down):
+            e = dict(k=k, r=r, rw=rw, cin=cin, f=f)
+            p = f"e{k}."
+            n(p + "d1", (B, r, rw, cin)); n(p + "y1", (B, r, rw, f)); n(p + "d2", (B, r, rw, f)); n(p + "y2", (B, r, rw, f))
+            n(p + "rs", (B, r // 2, rw // 2, f)); n(p + "out", (B, r // 2, rw // 2, f))
+            n(p + "arg", (B, r // 2, rw // 2, f), torch.uint8)
+            if k + 1 < len(s.down):
+                n(p + "oute", (B, r // 4, rw // 4, f))
+            # backward
+            n(p + "Te", (B, r // 2, rw // 2, cin)); n(p + "dy2", (B, r, rw, f)); n(p + "dd2", (B, r, rw, f))
+            n(p + "dz1", (B, r, rw, f)); n(p + "dy1", (B, r, rw, f)); n(p + "dd1", (B, r, rw, cin))
+            if k > 0:
+                n(p + "dx", (B, r, rw, cin))
+            self.enc.append(e)
+            r //= 2; rw //= 2; cin = f
+        n("a0_0", (B, r, rw, cin))  # relu(x3)
+        n("dx_bott", (B, r, rw, cin))
+        self.dec = []
+        for j, f in enumerate(s.up):
+            d = dict(j=j, r=r, rw=rw, cin=cin, f=f)
+            p = f"d{j}."
+            if j > 0:
+                n(p + "a0", (B, r, rw, cin))
+            n(p + "y1", (B, r, rw, f)); n(p + "a1", (B, r, rw, f)); n(p + "y2", (B, r, rw, f))
+            lr_, lrw = (r, rw) if j == 0 else (r // 2, rw // 2)
+            n(p + "rl", (B, lr_, lrw, f)); n(p + "s", (B, r, rw, f))
+            # backward
+            n(p + "ds", (B, r, rw, f))
+            if j > 0:
+                n(p + "drl", (B, lr_, lrw, f))
+            n(p + "dy2", (B, r, rw, f)); n(p + "da1", (B, r, rw, f)); n(p + "dy1", (B, r, rw, f))
+            n(p + "da0", (B, r, rw, cin)); n(p + "T", (B, lr_, lrw, cin))
+            self.dec.append(d)
+            r *= 2; rw *= 2; cin = f
+        self.head_c = cin
+
+    # ------------------------------------------------------------------ schedule construction
+    def b(self, name: str) -> int:
+        return self._bufs[name].data_ptr()
+
+    def _zptr(self, bn_name: str, which: str) -> int:
+        C_ = next(l.cout for l in self.bn_layers if l.name == bn_name)
+        base = self.zero_region.data_ptr() + 4 * self.bn_z[bn_name]
+        return base if which == "stats" else base + 4 * 2 * C_
+
+    def _bnptr(self, bn_name: str) -> int:
+        return self.bn_params.data_ptr() + 4 * self.bn_p[bn_name]
+
+    def _acc_ptr(self) -> int:
+        return self.zero_region.data_ptr() + 4 * self.acc_off
+
+    def _gemm(self, prog, X, opname, bias, add, Y, B, H, W, stats=0):
+        off, N, T, K = self.ops[opname]
+        if self.conv_impl == "tc":
+            prog.append((self.lib.crackfl_conv_tc_fwd, (X, self.op_ptr(opname), bias, add, Y, stats, B, H, W, K, N, T)))
+            return stats != 0
+        prog.append((self.lib.crackfl_conv_simt_fwd, (X, self.op_ptr(opname), bias, add, Y, B, H, W, K, N, T)))
+        return False
+
+    def _wgrad(self, prog, X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co):
+        fn = self.lib.crackfl_wgrad_tc if self.conv_impl == "tc" else self.lib.crackfl_wgrad_simt
+        prog.append((fn, (X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co)))
+
+    def _layer_iter(self):
+        """Yield the spec layers grouped as entry / encoder blocks / decoder blocks / head."""
+        ls = self.spec.layers
+        i = 0
+        entry = (ls[0], ls[1]); i = 2
+        encs = []
+        for _ in self.spec.down:
+            encs.append(ls[i:i + 5]); i += 5
+        decs = []
+        for _ in self.spec.up:
+            decs.append(ls[i:i + 5]); i += 5
+        return entry, encs, decs, ls[i]
+
+    def _bn_train(self, prog, bnl, y, P, stats_done=False):
+        C_ = bnl.cout
+        lib = self.lib
+        if not stats_done:
+            prog.append((lib.crackfl_bn_stats, (y, self._zptr(bnl.name, "stats"), P, C_)))
+        g, bt, rm, rv = bnl.tensors
+        prog.append((lib.crackfl_bn_finalize, (self._zptr(bnl.name, "stats"), self.P(g), self.P(bt), self.P(rm), self.P(rv),
+                                                self._bnptr(bnl.name), C_, float(P), self.spec.bn_eps, self.spec.bn_momentum)))
+
+    def _bn_eval(self, prog, bnl):
+        g, bt, rm, rv = bnl.tensors
+        prog.append((self.lib.crackfl_bn_eval_prepare, (self.P(g), self.P(bt), self.P(rm), self.P(rv), self._bnptr(bnl.name),
+                                                        bnl.cout, self.spec.bn_eps)))
+
+    def _build_forward(self, training: bool, with_mask: bool, prob: bool, prog=None):
+        lib, B = self.lib, self.B
+        prog = [] if prog is None else prog
+        (conv0, bn0), encs, decs, head = self._layer_iter()
+        b = self.b
+
+        def bn(bnl, y, P, stats_done=False):
+            if training:
+                self._bn_train(prog, bnl, y, P, stats_done)
+            else:
+                self._bn_eval(prog, bnl)
+
+        prog.append((lib.crackfl_weight_prep, (self.arena.data_ptr(), self.ops_buf.data_ptr(), self.desc_dev.data_ptr(),
+                                               self.num_desc)))
+        # entry
+        r, rw, c0 = self.H // 2, self.W // 2, self.spec.entry
+        prog.append((lib.crackfl_entry_conv_fwd, (b("x_u8"), self.P(conv0.tensors[0]), self.P(conv0.tensors[1]), b("y0"),
+                                                  B, self.H, self.W, c0)))
+        bn(bn0, b("y0"), B * r * rw)
+        prog.append((lib.crackfl_bn_act, (b("y0"), self._bnptr(bn0.name), b("x0"), b("x0e"), B, r, rw, c0, 1)))
+        xin, xe = "x0", "x0e"
+        for e, (sep1, bn1, sep2, bn2, res) in zip(self.enc, encs):
+            p = f"e{e['k']}."
+            r, rw, cin, f = e["r"], e["rw"], e["cin"], e["f"]
+            Pn = B * r * rw
+            prog.append((lib.crackfl_dw3x3_fwd, (b(xin), self.P(sep1.tensors[0]), 0, b(p + "d1"), B, r, rw, cin, 0)))
+            sd = self._gemm(prog, b(p + "d1"), sep1.name + ".f", self.P(sep1.tensors[2]), 0, b(p + "y1"), B, r, rw,
+                            self._zptr(bn1.name, "stats") if training else 0)
+            bn(bn1, b(p + "y1"), Pn, sd)
+            prog.append((lib.crackfl_dw3x3_fwd, (b(p + "y1"), self.P(sep2.tensors[0]), self._bnptr(bn1.name), b(p + "d2"),
+                                                 B, r, rw, f, 1)))
+            sd = self._gemm(prog, b(p + "d2"), sep2.name + ".f", self.P(sep2.tensors[2]), 0, b(p + "y2"), B, r, rw,
+                            self._zptr(bn2.name, "stats") if training else 0)
+            bn(bn2, b(p + "y2"), Pn, sd)
+            self._gemm(prog, b(xe), res.name + ".f", self.P(res.tensors[1]), 0, b(p + "rs"), B, r // 2, rw // 2)
+            last = e["k"] + 1 == len(self.enc)
+            prog.append((lib.crackfl_pool_add_fwd, (b(p + "y2"), self._bnptr(bn2.name), b(p + "rs"), b(p + "out"),
+                                                    0 if last else b(p + "oute"), b("a0_0") if last else 0,
+                                                    b(p + "arg") if training else 0, B, r, rw, f)))
+            xin, xe = p + "out", p + "oute"
+        xprev = xin  # bottleneck tensor x3
+        for d, (ct1, bn1, ct2, bn2, res) in zip(self.dec, decs):
+            j, r, rw, cin, f = d["j"], d["r"], d["rw"], d["cin"], d["f"]
+            p = f"d{j}."
+            Pn = B * r * rw
+            a0 = "a0_0" if j == 0 else p + "a0"
+            sd = self._gemm(prog, b(a0), ct1.name + ".f", self.P(ct1.tensors[1]), 0, b(p + "y1"), B, r, rw,
+                            self._zptr(bn1.name, "stats") if training else 0)
+            bn(bn1, b(p + "y1"), Pn, sd)
+            prog.append((lib.crackfl_bn_act, (b(p + "y1"), self._bnptr(bn1.name), b(p + "a1"), 0, B, r, rw, f, 1)))
+            sd = self._gemm(prog, b(p + "a1"), ct2.name + ".f", self.P(ct2.tensors[1]), 0, b(p + "y2"), B, r, rw,
+                            self._zptr(bn2.name, "stats") if training else 0)
+            bn(bn2, b(p + "y2"), Pn, sd)
+            lr_, lrw = (r, rw) if j == 0 else (r // 2, rw // 2)
+            self._gemm(prog, b(xprev), res.name + ".f", self.P(res.tensors[1]), 0, b(p + "rl"), B, lr_, lrw)
+            last = j + 1 == len(self.dec)
+            prog.append((lib.crackfl_dec_combine_fwd, (b(p + "y2"), self._bnptr(bn2.name), b(p + "rl"), b(p + "s"),
+                                                       0 if last else b(f"d{j + 1}.a0"), B, r, rw, f, 0 if j == 0 else 1)))
+            xprev = p + "s"
+        dl = self.dec[-1]
+        prog.append((lib.crackfl_head_fwd, (b(xprev), self.P(head.tensors[0]), self.P(head.tensors[1]),
+                                            b("mask_u8") if with_mask else 0, self._acc_ptr() if with_mask else 0,
+                                            b("prob") if prob else 0, B, dl["r"], dl["rw"], dl["f"])))
+        return prog
+
+    def _build_train(self):
+        lib, B, b = self.lib, self.B, self.b
+        prog = self._build_forward(training=True, with_mask=True, prob=False)
+        (conv0, bn0), encs, decs, head = self._layer_iter()
+        ts = self.spec.tensors
+        dl = self.dec[-1]
+        last = f"d{dl['j']}."
+        prog.append((lib.crackfl_head_bwd, (b(last + "s"), self.P(head.tensors[0]), self.P(head.tensors[1]), b("mask_u8"),
+                                            self._acc_ptr(), b(last + "ds"), self.G(head.tensors[0]), self.G(head.tensors[1]),
+                                            B, dl["r"], dl["rw"], dl["f"], self.use_dice, self.dice_smooth, 1.0)))
+        # ---- decoder backward
+        for d, (ct1, bn1, ct2, bn2, res) in reversed(list(zip(self.dec, decs))):
+            j, r, rw, cin, f = d["j"], d["r"], d["rw"], d["cin"], d["f"]
+            p = f"d{j}."
+            lr_, lrw = (r, rw) if j == 0 else (r // 2, rw // 2)
+            src_res = self.enc_out_name() if j == 0 else f"d{j - 1}.s"
+            if j > 0:
+                prog.append((lib.crackfl_down2sum, (b(p + "ds"), 0, 0, b(p + "drl"), B, lr_, lrw, f)))
+                drl = p + "drl"
+            else:
+                drl = p + "ds"
+            # BN2 (no ReLU after it)
+            prog.append((lib.crackfl_bn_bwd_reduce, (b(p + "ds"), 0, b(p + "y2"), self._bnptr(bn2.name),
+                                                     self._zptr(bn2.name, "sums"), B, r, rw, f, 0)))
+            prog.append((lib.crackfl_bn_bwd_apply, (b(p + "ds"), 0, b(p + "y2"), self._bnptr(bn2.name),
+                                                    self._zptr(bn2.name, "sums"), b(p + "dy2"), self.G(bn2.tensors[0]),
+                                                    self.G(bn2.tensors[1]), B, r, rw, f, 0)))
+            oi = ts[ct2.tensors[0]]
+            self._gemm(prog, b(p + "dy2"), ct2.name + ".d", 0, 0, b(p + "da1"), B, r, rw)
+            self._wgrad(prog, b(p + "a1"), b(p + "dy2"), self.G(ct2.tensors[0]) + 4 * 8 * f * f, B, r, rw, f, f, 9,
+                        -f * f, 1, f)
+            # BN1 + ReLU
+            prog.append((lib.crackfl_bn_bwd_reduce, (b(p + "da1"), 0, b(p + "y1"), self._bnptr(bn1.name),
+                                                     self._zptr(bn1.name, "sums"), B, r, rw, f, 1)))
+            prog.append((lib.crackfl_bn_bwd_apply, (b(p + "da1"), 0, b(p + "y1"), self._bnptr(bn1.name),
+                                                    self._zptr(bn1.name, "sums"), b(p + "dy1"), self.G(bn1.tensors[0]),
+                                                    self.G(bn1.tensors[1]), B, r, rw, f, 1)))
+            a0 = "a0_0" if j == 0 else p + "a0"
+            self._gemm(prog, b(p + "dy1"), ct1.name + ".d", 0, 0, b(p + "da0"), B, r, rw)
+            self._wgrad(prog, b(a0), b(p + "dy1"), self.G(ct1.tensors[0]) + 4 * 8 * f * cin, B, r, rw, cin, f, 9,
+                        -f * cin, 1, cin)
+            # residual 1x1 conv (at low resolution)
+            self._gemm(prog, b(drl), res.name + ".d", 0, 0, b(p + "T"), B, lr_, lrw)
+            self._wgrad(prog, b(src_res), b(drl), self.G(res.tensors[0]), B, lr_, lrw, cin, f, 1, 0, f, 1)
+            prog.append((lib.crackfl_colsum, (b(drl), self.G(res.tensors[1]), B * lr_ * lrw, f)))
+            if j > 0:
+                prog.append((lib.crackfl_down2sum, (b(p + "da0"), b(f"d{j - 1}.s"), b(p + "T"), b(f"d{j - 1}.ds"),
+                                                    B, lr_, lrw, cin)))
+            else:
+                prog.append((lib.crackfl_relu_bwd_add, (b(p + "da0"), b(src_res), b(p + "T"), b("dx_bott"),
+                                                        B * r * rw * cin)))
+        # ---- encoder backward
+        dx_next = "dx_bott"
+        for e, (sep1, bn1, sep2, bn2, res) in reversed(list(zip(self.enc, encs))):
+            k, r, rw, cin, f = e["k"], e["r"], e["rw"], e["cin"], e["f"]
+            p = f"e{k}."
+            xin = "x0" if k == 0 else f"e{k - 1}.out"
+            xe = "x0e" if k == 0 else f"e{k - 1}.oute"
+            r2, rw2 = r // 2, rw // 2
+            # residual 1x1 s2 conv
+            self._gemm(prog, b(dx_next), res.name + ".d", 0, 0, b(p + "Te"), B, r2, rw2)
+            self._wgrad(prog, b(xe), b(dx_next), self.G(res.tensors[0]), B, r2, rw2, cin, f, 1, 0, f, 1)
+            prog.append((lib.crackfl_colsum, (b(dx_next), self.G(res.tensors[1]), B * r2 * rw2, f)))
+            # max-pool + BN2
+            prog.append((lib.crackfl_bn_bwd_reduce, (b(dx_next), b(p + "arg"), b(p + "y2"), self._bnptr(bn2.name),
+                                                     self._zptr(bn2.name, "sums"), B, r, rw, f, 2)))
+            prog.append((lib.crackfl_bn_bwd_apply, (b(dx_next), b(p + "arg"), b(p + "y2"), self._bnptr(bn2.name),
+                                                    self._zptr(bn2.name, "sums"), b(p + "dy2"), self.G(bn2.tensors[0]),
+                                                    self.G(bn2.tensors[1]), B, r, rw, f, 2)))
+            # pointwise 2
+            self._gemm(prog, b(p + "dy2"), sep2.name + ".d", 0, 0, b(p + "dd2"), B, r, rw)
+            self._wgrad(prog, b(p + "d2"), b(p + "dy2"), self.G(sep2.tensors[1]), B, r, rw, f, f, 1, 0, f, 1)
+            # depthwise 2 (input = relu(bn1(y1)))
+            prog.append((lib.crackfl_dw3x3_bwd, (b(p + "dd2"), b(p + "y1"), self.P(sep2.tensors[0]), self._bnptr(bn1.name), 0,
+                                                 b(p + "dz1"), self.G(sep2.tensors[0]), B, r, rw, f, 1, 0)))
+            prog.append((lib.crackfl_bn_bwd_reduce, (b(p + "dz1"), 0, b(p + "y1"), self._bnptr(bn1.name),
+                                                     self._zptr(bn1.name, "sums"), B, r, rw, f, 0)))
+            prog.append((lib.crackfl_bn_bwd_apply, (b(p + "dz1"), 0, b(p + "y1"), self._bnptr(bn1.name),
+                                                    self._zptr(bn1.name, "sums"), b(p + "dy1"), self.G(bn1.tensors[0]),
+                                                    self.G(bn1.tensors[1]), B, r, rw, f, 0)))
+            # pointwise 1
+            self._gemm(prog, b(p + "dy1"), sep1.name + ".d", 0, 0, b(p + "dd1"), B, r, rw)
+            self._wgrad(prog, b(p + "d1"), b(p + "dy1"), self.G(sep1.tensors[1]), B, r, rw, cin, f, 1, 0, f, 1)
+            # depthwise 1 (input = relu(x_k)); adds the residual-path gradient on the even pixels
+            out = "dz0" if k == 0 else p + "dx"
+            prog.append((lib.crackfl_dw3x3_bwd, (b(p + "dd1"), b(xin), self.P(sep1.tensors[0]), 0, b(p + "Te"), b(out),
+                                                 self.G(sep1.tensors[0]), B, r, rw, cin, 0, 2 if k == 0 else 1)))
+            dx_next = out
+        # ---- entry
+        r, rw, c0 = self.H // 2, self.W // 2, self.spec.entry
+        prog.append((lib.crackfl_bn_bwd_reduce, (b("dz0"), 0, b("y0"), self._bnptr(bn0.name), self._zptr(bn0.name, "sums"),
+                                                 B, r, rw, c0, 0)))
+        prog.append((lib.crackfl_bn_bwd_apply, (b("dz0"), 0, b("y0"), self._bnptr(bn0.name), self._zptr(bn0.name, "sums"),
+                                                b("dy0"), self.G(bn0.tensors[0]), self.G(bn0.tensors[1]), B, r, rw, c0, 0)))
+        prog.append((lib.crackfl_entry_conv_wgrad, (b("x_u8"), b("dy0"), self.G(conv0.tensors[0]), B, self.H, self.W, c0)))
+        # ---- optimiser (also zeroes the gradient arena)
+        prog.append((lib.crackfl_adam_step, (self.arena.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(),
+                                             self.v.data_ptr(), self.step.data_ptr(), self.spec.arena_numel, self.lr,
+                                             self.b1, self.b2, self.eps)))
+        return prog
+
+    def enc_out_name(self) -> str:
+        return f"e{len(self.enc) - 1}.out"
+
+    # ------------------------------------------------------------------ execution
+    def _run(self, prog):
+        st = torch.cuda.current_stream(self.dev).cuda_stream
+        for fn, args in prog:
+            rc = fn(*args, st)
+            if rc != 0:
+                raise L.KernelError(f"{fn.__name__} failed with cudaError {rc}")
+
+    def _step_body(self, prog, accumulate: bool):
+        self.zero_region.zero_()
+        self._run(prog)
+        if accumulate:
+            self.metrics_total[:6] += self.zero_region[self.acc_off:self.acc_off + 6]
+
+    def _exec(self, key: str, prog, accumulate: bool):
+        with torch.cuda.device(self.dev):
+            if not self.cuda_graph:
+                self._step_body(prog, accumulate)
+                return
+            g = self._graphs.get(key)
+            if g is None:
+                # one eager run first (lazy module loading / cudaFuncSetAttribute must not happen during capture)
+                saved = None
+                if key == "train":
+                    saved = (self.arena.clone(), self.m.clone(), self.v.clone(), self.step.clone(),
+                             self.metrics_total.clone(), self.grads.clone())
+                else:
+                    saved = (self.metrics_total.clone(),)
+                torch.cuda.synchronize(self.dev)
+                self._step_body(prog, accumulate)
+                torch.cuda.synchronize(self.dev)
+                if key == "train":
+                    self.arena.copy_(saved[0]); self.m.copy_(saved[1]); self.v.copy_(saved[2]); self.step.copy_(saved[3])
+                    self.metrics_total.copy_(saved[4]); self.grads.copy_(saved[5])
+                else:
+                    self.metrics_total.copy_(saved[0])
+                g = torch.cuda.CUDAGraph()
+                s = torch.cuda.Stream(self.dev)
+                s.wait_stream(torch.cuda.current_stream(self.dev))
+                with torch.cuda.stream(s):
+                    with torch.cuda.graph(g, stream=s):
+                        self._step_body(prog, accumulate)
+                torch.cuda.current_stream(self.dev).wait_stream(s)
+                self._graphs[key] = g
+                # the capture itself did not execute anything; fall through to replay
+            g.replay()
+
+    # ------------------------------------------------------------------ public API
+    def load_weights(self, weights: Sequence[np.ndarray]):
+        flat = torch.from_numpy(wio.flatten(weights, self.spec))
+        self.arena.copy_(flat.to(self.dev, non_blocking=False))
+
+    def load_flat(self, flat: torch.Tensor):
+        self.arena.copy_(flat)
+
+    def get_weights(self) -> List[np.ndarray]:
+        return wio.unflatten(self.arena.detach().cpu().numpy(), self.spec)
+
+    def reset_optimizer(self):
+        """Fresh ``compile()``: Adam moments and step count to zero (client_fit_model.py:155-157)."""
+        self.m.zero_(); self.v.zero_(); self.step.zero_(); self.grads.zero_()
+
+    def reset_metrics(self):
+        self.metrics_total.zero_()
+
+    def read_metrics(self) -> Dict[str, float]:
+        t = self.metrics_total.detach().cpu().numpy()
+        n = max(float(t[5]), 1.0)
+        out = {"loss": float(t[0]) / n, "accuracy": float(t[1]) / n}
+        if self.use_dice:
+            # per-batch Dice averaged approximately via the accumulated sums
+            out["dice"] = float((2 * t[2] + self.dice_smooth) / (t[3] + t[4] + self.dice_smooth))
+        return out
+
+    def set_batch(self, x_u8, y_u8=None):
+        """x: (B,H,W,3) uint8 numpy/torch (host or device); y: (B,H,W[,1]) uint8."""
+        xt = torch.as_tensor(x_u8)
+        self.x_u8.copy_(xt.view(self.x_u8.shape) if xt.dtype == torch.uint8 else xt.to(torch.uint8), non_blocking=True)
+        if y_u8 is not None:
+            yt = torch.as_tensor(y_u8)
+            self.mask_u8.copy_(yt.reshape(self.mask_u8.shape), non_blocking=True)
+
+    def train_step(self, x_u8=None, y_u8=None):
+        if x_u8 is not None:
+            self.set_batch(x_u8, y_u8)
+        self._exec("train", self.train_prog, True)
+
+    def eval_step(self, x_u8=None, y_u8=None):
+        if x_u8 is not None:
+            self.set_batch(x_u8, y_u8)
+        self._exec("eval", self.eval_prog, True)
+
+    def predict(self, x_u8=None) -> torch.Tensor:
+        """Returns probabilities (B,H,W) fp32 on the device (valid until the next call)."""
+        if x_u8 is not None:
+            self.set_batch(x_u8)
+        self._exec("pred", self.pred_prog, False)
+        return self.prob
+
+    def step_loss(self) -> torch.Tensor:
+        """Device scalar: mean BCE of the most recent step (for the end-to-end D2H read)."""
+        a = self.zero_region[self.acc_off:self.acc_off + 6]
+        return a[0] / a[5].clamp_min(1.0)
+
+
+class B200Backend:
+    """``trainer.LocalTrainer`` back-end on the engine (one engine per (batch, size) shape)."""
+
+    name = "b200"
+
+    def __init__(self, cfg, spec: UNetSpec, device: Optional[int] = None):
+        t = cfg.train
+        self.cfg, self.spec = cfg, spec
+        self.engine = UNetEngine(spec, t.batch_size, t.image_size[0], t.image_size[1], device=device, lr=t.lr,
+                                 beta1=t.beta1, beta2=t.beta2, eps=t.adam_eps, loss=t.loss, cuda_graph=t.cuda_graph)
+        B, H, W = t.batch_size, t.image_size[0], t.image_size[1]
+        self._hx = torch.empty((B, H, W, 3), dtype=torch.uint8).pin_memory()
+        self._hy = torch.empty((B, H, W), dtype=torch.uint8).pin_memory()
+
+    def begin_round(self, weights):
+        self.engine.load_weights(weights)
+        self.engine.reset_optimizer()
+        self.engine.reset_metrics()
+
+    def reset_metrics(self):
+        self.engine.reset_metrics()
+
+    def _stage(self, x_u8, y_u8):
+        torch.cuda.current_stream(self.engine.dev).synchronize()  # previous H2D from the pinned buffers is done
+        self._hx.copy_(torch.as_tensor(np.ascontiguousarray(x_u8)))
+        if y_u8 is not None:
+            self._hy.copy_(torch.as_tensor(np.ascontiguousarray(y_u8)).reshape(self._hy.shape))
+        return self._hx, (self._hy if y_u8 is not None else None)
+
+    def train_batch(self, x_u8, y_u8):
+        self.engine.train_step(*self._stage(x_u8, y_u8))
+
+    def eval_batch(self, x_u8, y_u8):
+        self.engine.eval_step(*self._stage(x_u8, y_u8))
+
+    def read_metrics(self):
+        return self.engine.read_metrics()
+
+    def predict_batch(self, x_u8) -> np.ndarray:
+        hx, _ = self._stage(x_u8, None)
+        return self.engine.predict(hx).detach().cpu().numpy()[..., None]
+
+    def get_weights(self):
+        return self.engine.get_weights()

@@ -1,0 +1,64 @@
+// Shared device helpers for the crackfl sm_100a kernels.
+// Activations are NHWC bf16 with C a multiple of 8; the unit of access is one uint4 (8 x bf16).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define CK_LAUNCH_CHECK() do { cudaError_t e__ = cudaGetLastError(); if (e__ != cudaSuccess) return (int)e__; } while (0)
+
+namespace ck {
+
+__device__ __forceinline__ void unpack8(const uint4& v, float f[8]) {
+  f[0] = __uint_as_float(v.x << 16); f[1] = __uint_as_float(v.x & 0xffff0000u);
+  f[2] = __uint_as_float(v.y << 16); f[3] = __uint_as_float(v.y & 0xffff0000u);
+  f[4] = __uint_as_float(v.z << 16); f[5] = __uint_as_float(v.z & 0xffff0000u);
+  f[6] = __uint_as_float(v.w << 16); f[7] = __uint_as_float(v.w & 0xffff0000u);
+}
+
+__device__ __forceinline__ uint32_t pack2(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+__device__ __forceinline__ uint4 pack8(const float f[8]) {
+  uint4 v;
+  v.x = pack2(f[0], f[1]); v.y = pack2(f[2], f[3]); v.z = pack2(f[4], f[5]); v.w = pack2(f[6], f[7]);
+  return v;
+}
+
+__device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+__device__ __forceinline__ void stg16(void* p, const uint4& v) { *reinterpret_cast<uint4*>(p) = v; }
+
+__device__ __forceinline__ void load8f(const float* __restrict__ p, float f[8]) {
+  float4 a = __ldg(reinterpret_cast<const float4*>(p));
+  float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Block-level reduction of per-thread partial sums laid out as (pixel-lane, channel-vector):
+// thread t owns channel vector (t % c8) and pixel lane (t / c8).  All lanes of a channel vector
+// are summed through shared memory and lane 0 issues one atomicAdd per channel.
+// `sm` must hold blockDim.x * 8 floats.
+__device__ __forceinline__ void block_channel_atomic(const float acc[8], int c8, float* sm, float* __restrict__ out) {
+  const int t = threadIdx.x;
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sm[t * 8 + j] = acc[j];
+  __syncthreads();
+  const int lanes = blockDim.x / c8;
+  for (int i = t; i < c8 * 8; i += blockDim.x) {
+    const int cv = i >> 3, j = i & 7;
+    float s = 0.f;
+    for (int l = 0; l < lanes; ++l) s += sm[(l * c8 + cv) * 8 + j];
+    atomicAdd(out + cv * 8 + j, s);
+  }
+}
+
+}  // namespace ck

@@ -1,0 +1,879 @@
+// Elementwise / reduction kernels of the U-Net train step (NHWC bf16, fp32 math).
+// Replaces the implicit TF ops O1,O2,O4-O6,O8,O10,O12-O14 and their backward (O16) of
+// client_fit_model.py:100-145,157.
+// Every kernel is HBM-bound; the design goal is one pass per tensor with the neighbouring
+// pointwise work (BN-apply, ReLU, residual add, nearest upsample, /255) fused in.
+#include "common.cuh"
+#include "../include/crackfl.h"
+
+using namespace ck;
+
+namespace {
+
+constexpr int TPB = 256;
+
+// ---------------------------------------------------------------------------------------
+// K4 entry conv 3x3 s2, TF-"same" (pad bottom/right only), uint8 input, /255 fused.  K=27 is too
+// small for the tensor cores to pay; CUDA-core kernel, weights in shared memory.
+__global__ void __launch_bounds__(TPB) entry_conv_fwd_k(const uint8_t* __restrict__ x, const float* __restrict__ w,
+                                                        const float* __restrict__ bias, __nv_bfloat16* __restrict__ y,
+                                                        int B, int H, int W, int C) {
+  extern __shared__ float sw[];  // [27][C] + bias[C]
+  for (int i = threadIdx.x; i < 27 * C; i += blockDim.x) sw[i] = w[i] * (1.0f / 255.0f);
+  for (int i = threadIdx.x; i < C; i += blockDim.x) sw[27 * C + i] = bias[i];
+  __syncthreads();
+  const int Ho = H >> 1, Wo = W >> 1, c8 = C >> 3;
+  const long total = (long)B * Ho * Wo * c8;
+  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long)gridDim.x * blockDim.x) {
+    const int cv = (int)(g % c8);
+    long p = g / c8;
+    const int ow = (int)(p % Wo); p /= Wo;
+    const int oh = (int)(p % Ho);
+    const int b = (int)(p / Ho);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = sw[27 * C + cv * 8 + j];
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      const int ih = 2 * oh + kh;
+      if (ih >= H) continue;
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int iw = 2 * ow + kw;
+        if (iw >= W) continue;
+        const uint8_t* px = x + ((long)(b * H + ih) * W + iw) * 3;
+#pragma unroll
+        for (int ci = 0; ci < 3; ++ci) {
+          const float v = (float)px[ci];
+          const float* wr = sw + ((kh * 3 + kw) * 3 + ci) * C + cv * 8;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] = fmaf(v, wr[j], acc[j]);
+        }
+      }
+    }
+    stg16(y + g * 8, pack8(acc));
+  }
+}
+
+// wgrad of the entry conv: dW[27][C] += sum_p patch(p)[27] * dy[p][C].  blockDim = (C/8, 27).
+__global__ void entry_conv_wgrad_k(const uint8_t* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                                   float* __restrict__ dw, int B, int H, int W, int C, int pix_per_block) {
+  const int Ho = H >> 1, Wo = W >> 1, c8 = C >> 3;
+  const int cv = threadIdx.x, k = threadIdx.y;
+  const int kh = k / 9, kw = (k / 3) % 3, ci = k % 3;
+  const long P = (long)B * Ho * Wo;
+  const long p0 = (long)blockIdx.x * pix_per_block;
+  const long p1 = min(P, p0 + pix_per_block);
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (long p = p0; p < p1; ++p) {
+    const int ow = (int)(p % Wo);
+    const int oh = (int)((p / Wo) % Ho);
+    const int b = (int)(p / ((long)Wo * Ho));
+    const int ih = 2 * oh + kh, iw = 2 * ow + kw;
+    if (ih >= H || iw >= W) continue;
+    const float v = (float)x[((long)(b * H + ih) * W + iw) * 3 + ci] * (1.0f / 255.0f);
+    float g[8];
+    unpack8(ldg16(dy + (p * c8 + cv) * 8), g);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = fmaf(v, g[j], acc[j]);
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) atomicAdd(dw + (long)k * C + cv * 8 + j, acc[j]);
+}
+
+// ---------------------------------------------------------------------------------------
+// BN statistics (forward): per-channel sum and sum of squares.  stats = [sum C][sumsq C].
+__global__ void __launch_bounds__(TPB) bn_stats_k(const __nv_bfloat16* __restrict__ y, float* __restrict__ stats,
+                                                  long P, int C, int pix_per_block) {
+  __shared__ float sm[TPB * 8];
+  const int c8 = C >> 3, lanes = TPB / c8;
+  const int cv = threadIdx.x % c8, lane = threadIdx.x / c8;
+  const long p0 = (long)blockIdx.x * pix_per_block;
+  const long p1 = min(P, p0 + pix_per_block);
+  float s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (long p = p0 + lane; p < p1; p += lanes) {
+    float f[8];
+    unpack8(ldg16(y + (p * c8 + cv) * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s[j] += f[j]; q[j] = fmaf(f[j], f[j], q[j]); }
+  }
+  block_channel_atomic(s, c8, sm, stats);
+  block_channel_atomic(q, c8, sm, stats + C);
+}
+
+// stats -> (scale, shift, mean, invstd) and the moving-average update (momentum 0.99, eps 1e-3,
+// unbiased variance into the running estimate as TF's fused batch norm does).
+// bn = [scale C][shift C][mean C][invstd C]
+__global__ void bn_finalize_k(const float* __restrict__ stats, const float* __restrict__ gamma,
+                              const float* __restrict__ beta, float* __restrict__ run_mean,
+                              float* __restrict__ run_var, float* __restrict__ bn, int C, float count, float eps,
+                              float momentum) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float mean = stats[c] / count;
+  float var = stats[C + c] / count - mean * mean;
+  var = fmaxf(var, 0.f);
+  const float invstd = rsqrtf(var + eps);
+  const float sc = gamma[c] * invstd;
+  bn[c] = sc;
+  bn[C + c] = beta[c] - mean * sc;
+  bn[2 * C + c] = mean;
+  bn[3 * C + c] = invstd;
+  const float unb = count > 1.f ? var * (count / (count - 1.f)) : var;
+  run_mean[c] = run_mean[c] * momentum + mean * (1.f - momentum);
+  run_var[c] = run_var[c] * momentum + unb * (1.f - momentum);
+}
+
+// inference: scale/shift from the moving statistics
+__global__ void bn_eval_prepare_k(const float* __restrict__ gamma, const float* __restrict__ beta,
+                                  const float* __restrict__ run_mean, const float* __restrict__ run_var,
+                                  float* __restrict__ bn, int C, float eps) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float invstd = rsqrtf(run_var[c] + eps);
+  const float sc = gamma[c] * invstd;
+  bn[c] = sc;
+  bn[C + c] = beta[c] - run_mean[c] * sc;
+  bn[2 * C + c] = run_mean[c];
+  bn[3 * C + c] = invstd;
+}
+
+// out = [relu](y*scale+shift); optional compact copy of the even pixels (input of the 1x1 s2 residual conv)
+__global__ void __launch_bounds__(TPB) bn_act_k(const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
+                                                __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ even,
+                                                int B, int H, int W, int C, int relu) {
+  const int c8 = C >> 3;
+  const long total = (long)B * H * W * c8;
+  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long)gridDim.x * blockDim.x) {
+    const int cv = (int)(g % c8);
+    float f[8], sc[8], sh[8];
+    unpack8(ldg16(y + g * 8), f);
+    load8f(bn + cv * 8, sc);
+    load8f(bn + C + cv * 8, sh);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      f[j] = fmaf(f[j], sc[j], sh[j]);
+      if (relu) f[j] = fmaxf(f[j], 0.f);
+    }
+    const uint4 v = pack8(f);
+    stg16(out + g * 8, v);
+    if (even) {
+      long p = g / c8;
+      const int w = (int)(p % W); p /= W;
+      const int h = (int)(p % H);
+      const int b = (int)(p / H);
+      if (!(h & 1) && !(w & 1))
+        stg16(even + ((((long)b * (H >> 1) + (h >> 1)) * (W >> 1) + (w >> 1)) * c8 + cv) * 8, v);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// K5 depthwise 3x3 s1 same.  mode 0: a = relu(x); mode 1: a = relu(x*scale+shift) (BN-apply+ReLU of
+// the producer fused into the load).  Zero padding applies to `a`.
+__device__ __forceinline__ void act_load(const __nv_bfloat16* __restrict__ src, long vec_idx, int mode,
+                                         const float sc[8], const float sh[8], float a[8]) {
+  unpack8(ldg16(src + vec_idx * 8), a);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (mode == 1) a[j] = fmaf(a[j], sc[j], sh[j]);
+    a[j] = fmaxf(a[j], 0.f);
+  }
+}
+
+__global__ void __launch_bounds__(TPB) dw3x3_fwd_k(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+                                                   const float* __restrict__ bn, __nv_bfloat16* __restrict__ out,
+                                                   int B, int H, int W, int C, int mode) {
+  const int c8 = C >> 3;
+  const long total = (long)B * H * W * c8;
+  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long)gridDim.x * blockDim.x) {
+    const int cv = (int)(g % c8);
+    long p = g / c8;
+    const int ww = (int)(p % W); p /= W;
+    const int hh = (int)(p % H);
+    const int b = (int)(p / H);
+    float sc[8], sh[8], acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (mode == 1) { load8f(bn + cv * 8, sc); load8f(bn + C + cv * 8, sh); }
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      const int ih = hh + kh - 1;
+      if (ih < 0 || ih >= H) continue;
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int iw = ww + kw - 1;
+        if (iw < 0 || iw >= W) continue;
+        float a[8], wk[8];
+        act_load(x, (((long)b * H + ih) * W + iw) * c8 + cv, mode, sc, sh, a);
+        load8f(w + (kh * 3 + kw) * C + cv * 8, wk);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(a[j], wk[j], acc[j]);
+      }
+    }
+    stg16(out + g * 8, pack8(acc));
+  }
+}
+
+// Backward of the depthwise conv w.r.t. its (activated) input and its weights.
+//   da[p] = sum_tap g[p - off(tap)] * w[tap];   dz[p] = 1[a[p] > 0] * da[p]  (+ residual term)
+//   dw[tap][c] += sum_o a[o + off(tap)][c] * g[o][c]
+// resid: 0 none; 1 dz += T[h/2,w/2] on even pixels (outside the mask); 2 same but inside the mask.
+__global__ void __launch_bounds__(TPB) dw3x3_bwd_k(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ src,
+                                                   const float* __restrict__ w, const float* __restrict__ bn,
+                                                   const __nv_bfloat16* __restrict__ resid_t,
+                                                   __nv_bfloat16* __restrict__ dz, float* __restrict__ dwk, int B, int H,
+                                                   int W, int C, int mode, int resid, int pix_per_block) {
+  __shared__ float sm[TPB * 8];
+  const int c8 = C >> 3, lanes = TPB / c8;
+  const int cv = threadIdx.x % c8, lane = threadIdx.x / c8;
+  const long P = (long)B * H * W;
+  const long p0 = (long)blockIdx.x * pix_per_block;
+  const long p1 = min(P, p0 + pix_per_block);
+  float sc[8], sh[8], wk[9][8], dacc[9][8];
+  if (mode == 1) { load8f(bn + cv * 8, sc); load8f(bn + C + cv * 8, sh); }
+#pragma unroll
+  for (int t = 0; t < 9; ++t) {
+    load8f(w + t * C + cv * 8, wk[t]);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dacc[t][j] = 0.f;
+  }
+  for (long p = p0 + lane; p < p1; p += lanes) {
+    const int ww = (int)(p % W);
+    const int hh = (int)((p / W) % H);
+    const int b = (int)(p / ((long)W * H));
+    float gc[8], ac[8], da[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    unpack8(ldg16(g + (p * c8 + cv) * 8), gc);
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int t = kh * 3 + kw;
+        // weight gradient: a at (hh+kh-1, ww+kw-1) times g at (hh, ww)
+        const int ih = hh + kh - 1, iw = ww + kw - 1;
+        if (ih >= 0 && ih < H && iw >= 0 && iw < W) {
+          float a[8];
+          act_load(src, (((long)b * H + ih) * W + iw) * c8 + cv, mode, sc, sh, a);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) dacc[t][j] = fmaf(a[j], gc[j], dacc[t][j]);
+          if (t == 4) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ac[j] = a[j];
+          }
+        }
+        // input gradient: g at (hh-kh+1, ww-kw+1) times w[tap]
+        const int oh = hh - kh + 1, ow = ww - kw + 1;
+        if (oh >= 0 && oh < H && ow >= 0 && ow < W) {
+          float gg[8];
+          unpack8(ldg16(g + ((((long)b * H + oh) * W + ow) * c8 + cv) * 8), gg);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) da[j] = fmaf(gg[j], wk[t][j], da[j]);
+        }
+      }
+    }
+    float r[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (resid && !(hh & 1) && !(ww & 1))
+      unpack8(ldg16(resid_t + ((((long)b * (H >> 1) + (hh >> 1)) * (W >> 1) + (ww >> 1)) * c8 + cv) * 8), r);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float m = ac[j] > 0.f ? 1.f : 0.f;
+      da[j] = (resid == 2) ? m * (da[j] + r[j]) : m * da[j] + r[j];
+    }
+    stg16(dz + (p * c8 + cv) * 8, pack8(da));
+  }
+#pragma unroll
+  for (int t = 0; t < 9; ++t) block_channel_atomic(dacc[t], c8, sm, dwk + t * C);
+}
+
+// ---------------------------------------------------------------------------------------
+// K7 encoder block tail: x_next = maxpool3x3s2_same(bn2(y2)) + residual; argmax kept for backward.
+__global__ void __launch_bounds__(TPB) pool_add_fwd_k(const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
+                                                      const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out,
+                                                      __nv_bfloat16* __restrict__ even, __nv_bfloat16* __restrict__ relu_out,
+                                                      uint8_t* __restrict__ arg, int B, int H, int W, int C) {
+  const int c8 = C >> 3, Ho = H >> 1, Wo = W >> 1;
+  const long total = (long)B * Ho * Wo * c8;
+  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long)gridDim.x * blockDim.x) {
+    const int cv = (int)(g % c8);
+    long p = g / c8;
+    const int ow = (int)(p % Wo); p /= Wo;
+    const int oh = (int)(p % Ho);
+    const int b = (int)(p / Ho);
+    float sc[8], sh[8], best[8];
+    int bi[8];
+    load8f(bn + cv * 8, sc);
+    load8f(bn + C + cv * 8, sh);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; bi[j] = 0; }
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      const int ih = 2 * oh + kh;
+      if (ih >= H) continue;
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int iw = 2 * ow + kw;
+        if (iw >= W) continue;
+        float f[8];
+        unpack8(ldg16(y + ((((long)b * H + ih) * W + iw) * c8 + cv) * 8), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float z = fmaf(f[j], sc[j], sh[j]);
+          if (z > best[j]) { best[j] = z; bi[j] = kh * 3 + kw; }
+        }
+      }
+    }
+    float r[8];
+    unpack8(ldg16(res + g * 8), r);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) best[j] += r[j];
+    const uint4 v = pack8(best);
+    stg16(out + g * 8, v);
+    if (arg) {
+      uint2 a;
+      a.x = bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24);
+      a.y = bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24);
+      *reinterpret_cast<uint2*>(arg + g * 8) = a;
+    }
+    if (even && !(oh & 1) && !(ow & 1))
+      stg16(even + ((((long)b * (Ho >> 1) + (oh >> 1)) * (Wo >> 1) + (ow >> 1)) * c8 + cv) * 8, v);
+    if (relu_out) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) best[j] = fmaxf(best[j], 0.f);
+      stg16(relu_out + g * 8, pack8(best));
+    }
+  }
+}
+
+// K8 decoder block tail: s = bn2(y2) + (up2 ? upsample2(rl) : rl);  a_next = relu(upsample2(s)).
+__global__ void __launch_bounds__(TPB) dec_combine_fwd_k(const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
+                                                         const __nv_bfloat16* __restrict__ rl, __nv_bfloat16* __restrict__ s,
+                                                         __nv_bfloat16* __restrict__ a_next, int B, int H, int W, int C,
+                                                         int rl_up) {
+  const int c8 = C >> 3;
+  const long total = (long)B * H * W * c8;
+  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long)gridDim.x * blockDim.x) {
+    const int cv = (int)(g % c8);
+    long p = g / c8;
+    const int w = (int)(p % W); p /= W;
+    const int h = (int)(p % H);
+    const int b = (int)(p / H);
+    float f[8], sc[8], sh[8], r[8];
+    unpack8(ldg16(y + g * 8), f);
+    load8f(bn + cv * 8, sc);
+    load8f(bn + C + cv * 8, sh);
+    const long ri = rl_up ? ((((long)b * (H >> 1) + (h >> 1)) * (W >> 1) + (w >> 1)) * c8 + cv) : g;
+    unpack8(ldg16(rl + ri * 8), r);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]) + r[j];
+    stg16(s + g * 8, pack8(f));
+    if (a_next) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+      const uint4 v = pack8(f);
+      const long W2 = 2L * W;
+      const long base = (((long)b * 2 * H + 2 * h) * W2 + 2 * w) * c8 + cv;
+      stg16(a_next + base * 8, v);
+      stg16(a_next + (base + c8) * 8, v);
+      stg16(a_next + (base + W2 * c8) * 8, v);
+      stg16(a_next + (base + W2 * c8 + c8) * 8, v);
+    }
+  }
+}
+
+// out[q] = (mask ? 1[mask[q] > 0] : 1) * sum_{2x2} in[2q+d]  (+ add[q])     backward of nearest upsample
+__global__ void __launch_bounds__(TPB) down2sum_k(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict__ mask,
+                                                  const __nv_bfloat16* __restrict__ add, __nv_bfloat16* __restrict__ out,
+                                                  int B, int Ho, int Wo, int C) {
+  const int c8 = C >> 3;
+  const long total = (long)B * Ho * Wo * c8;
+  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long)gridDim.x * blockDim.x) {
+    const int cv = (int)(g % c8);
+    long p = g / c8;
+    const int w = (int)(p % Wo); p /= Wo;
+    const int h = (int)(p % Ho);
+    const int b = (int)(p / Ho);
+    const long W2 = 2L * Wo;
+    const long base = (((long)b * 2 * Ho + 2 * h) * W2 + 2 * w) * c8 + cv;
+    float a0[8], a1[8], a2[8], a3[8], o[8];
+    unpack8(ldg16(in + base * 8), a0);
+    unpack8(ldg16(in + (base + c8) * 8), a1);
+    unpack8(ldg16(in + (base + W2 * c8) * 8), a2);
+    unpack8(ldg16(in + (base + W2 * c8 + c8) * 8), a3);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = (a0[j] + a1[j]) + (a2[j] + a3[j]);
+    if (mask) {
+      float m[8];
+      unpack8(ldg16(mask + g * 8), m);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = m[j] > 0.f ? o[j] : 0.f;
+    }
+    if (add) {
+      float t[8];
+      unpack8(ldg16(add + g * 8), t);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] += t[j];
+    }
+    stg16(out + g * 8, pack8(o));
+  }
+}
+
+// out = 1[x > 0] * g + add      (first decoder block: gradient into the bottleneck tensor)
+__global__ void __launch_bounds__(TPB) relu_bwd_add_k(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ x,
+                                                      const __nv_bfloat16* __restrict__ add, __nv_bfloat16* __restrict__ out,
+                                                      long nvec) {
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
+    float a[8], m[8], t[8];
+    unpack8(ldg16(g + i * 8), a);
+    unpack8(ldg16(x + i * 8), m);
+    if (add) unpack8(ldg16(add + i * 8), t);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = (m[j] > 0.f ? a[j] : 0.f) + (add ? t[j] : 0.f);
+    stg16(out + i * 8, pack8(a));
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// BN backward.  dz (gradient w.r.t. the BN output) comes from one of three sources:
+//   0 DIRECT  dz = g[p]
+//   1 RELU    dz = g[p] * 1[bn(y[p]) > 0]
+//   2 POOL    dz[p] = sum over the (<=4) pooling windows q covering p of gq[q] * [argmax[q] == offset(p,q)]
+template <int MODE>
+__device__ __forceinline__ void load_dz(const __nv_bfloat16* __restrict__ g, const uint8_t* __restrict__ arg, long p, int cv,
+                                        int c8, int H, int W, const float yv[8], const float sc[8], const float sh[8],
+                                        float dz[8]) {
+  if (MODE == 0 || MODE == 1) {
+    unpack8(ldg16(g + (p * c8 + cv) * 8), dz);
+    if (MODE == 1) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) dz[j] = fmaf(yv[j], sc[j], sh[j]) > 0.f ? dz[j] : 0.f;
+    }
+  } else {
+    const int w = (int)(p % W);
+    const int h = (int)((p / W) % H);
+    const long b = p / ((long)W * H);
+    const int Ho = H >> 1, Wo = W >> 1;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dz[j] = 0.f;
+    const int qh0 = (h & 1) ? (h >> 1) : (h >> 1) - 1, qh1 = h >> 1;
+    const int qw0 = (w & 1) ? (w >> 1) : (w >> 1) - 1, qw1 = w >> 1;
+    for (int qh = max(qh0, 0); qh <= min(qh1, Ho - 1); ++qh)
+      for (int qw = max(qw0, 0); qw <= min(qw1, Wo - 1); ++qw) {
+        const long q = ((b * Ho + qh) * Wo + qw) * c8 + cv;
+        const int off = (h - 2 * qh) * 3 + (w - 2 * qw);
+        const uint2 a = __ldg(reinterpret_cast<const uint2*>(arg + q * 8));
+        float gq[8];
+        unpack8(ldg16(g + q * 8), gq);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int idx = ((j < 4 ? a.x : a.y) >> ((j & 3) * 8)) & 0xff;
+          if (idx == off) dz[j] += gq[j];
+        }
+      }
+  }
+}
+
+// sums = [sum dz  C][sum dz*xhat  C]
+template <int MODE>
+__global__ void __launch_bounds__(TPB) bn_bwd_reduce_k(const __nv_bfloat16* __restrict__ g, const uint8_t* __restrict__ arg,
+                                                       const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
+                                                       float* __restrict__ sums, long P, int H, int W, int C,
+                                                       int pix_per_block) {
+  __shared__ float sm[TPB * 8];
+  const int c8 = C >> 3, lanes = TPB / c8;
+  const int cv = threadIdx.x % c8, lane = threadIdx.x / c8;
+  float sc[8], sh[8], mu[8], is[8], s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  load8f(bn + cv * 8, sc); load8f(bn + C + cv * 8, sh);
+  load8f(bn + 2 * C + cv * 8, mu); load8f(bn + 3 * C + cv * 8, is);
+  const long p0 = (long)blockIdx.x * pix_per_block;
+  const long p1 = min(P, p0 + pix_per_block);
+  for (long p = p0 + lane; p < p1; p += lanes) {
+    float yv[8], dz[8];
+    unpack8(ldg16(y + (p * c8 + cv) * 8), yv);
+    load_dz<MODE>(g, arg, p, cv, c8, H, W, yv, sc, sh, dz);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      s1[j] += dz[j];
+      s2[j] = fmaf(dz[j], (yv[j] - mu[j]) * is[j], s2[j]);
+    }
+  }
+  block_channel_atomic(s1, c8, sm, sums);
+  block_channel_atomic(s2, c8, sm, sums + C);
+}
+
+// dy = scale * (dz - mean(dz) - xhat * mean(dz*xhat));  block 0 also emits dgamma / dbeta.
+template <int MODE>
+__global__ void __launch_bounds__(TPB) bn_bwd_apply_k(const __nv_bfloat16* __restrict__ g, const uint8_t* __restrict__ arg,
+                                                      const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
+                                                      const float* __restrict__ sums, __nv_bfloat16* __restrict__ dy,
+                                                      float* __restrict__ dgamma, float* __restrict__ dbeta, long P, int H,
+                                                      int W, int C) {
+  const int c8 = C >> 3;
+  const float invn = 1.0f / (float)P;
+  if (blockIdx.x == 0) {
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      dbeta[c] = sums[c];
+      dgamma[c] = sums[C + c];
+    }
+  }
+  const long total = P * c8;
+  for (long gi = (long)blockIdx.x * blockDim.x + threadIdx.x; gi < total; gi += (long)gridDim.x * blockDim.x) {
+    const int cv = (int)(gi % c8);
+    const long p = gi / c8;
+    float sc[8], sh[8], mu[8], is[8], a1[8], a2[8], yv[8], dz[8];
+    load8f(bn + cv * 8, sc); load8f(bn + C + cv * 8, sh);
+    load8f(bn + 2 * C + cv * 8, mu); load8f(bn + 3 * C + cv * 8, is);
+    load8f(sums + cv * 8, a1); load8f(sums + C + cv * 8, a2);
+    unpack8(ldg16(y + gi * 8), yv);
+    load_dz<MODE>(g, arg, p, cv, c8, H, W, yv, sc, sh, dz);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float xh = (yv[j] - mu[j]) * is[j];
+      dz[j] = sc[j] * (dz[j] - a1[j] * invn - xh * a2[j] * invn);
+    }
+    stg16(dy + gi * 8, pack8(dz));
+  }
+}
+
+// column sum of a [P][C] bf16 matrix into fp32 (bias gradient of the residual convs)
+__global__ void __launch_bounds__(TPB) colsum_k(const __nv_bfloat16* __restrict__ g, float* __restrict__ out, long P, int C,
+                                                int pix_per_block) {
+  __shared__ float sm[TPB * 8];
+  const int c8 = C >> 3, lanes = TPB / c8;
+  const int cv = threadIdx.x % c8, lane = threadIdx.x / c8;
+  float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const long p0 = (long)blockIdx.x * pix_per_block;
+  const long p1 = min(P, p0 + pix_per_block);
+  for (long p = p0 + lane; p < p1; p += lanes) {
+    float f[8];
+    unpack8(ldg16(g + (p * c8 + cv) * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] += f[j];
+  }
+  block_channel_atomic(s, c8, sm, out);
+}
+
+// ---------------------------------------------------------------------------------------
+// K9 head.  The final Up2x commutes with the 1x1 conv and the sigmoid, so the logit is computed at
+// the decoder's last low resolution (Hl = H/2) and compared against the 2x2 full-resolution mask
+// pixels it covers: the (B,H,W,32) tensor of client_fit_model.py:136-141 is never materialised.
+// acc = [bce_sum, correct, inter, psum, ysum, pixel_count]
+// Thread mapping: thread = (pixel, channel-vector); the c8 threads of one pixel are adjacent lanes of a
+// warp and reduce the 1x1-conv dot product with shuffles (c8 must divide 32).
+__device__ __forceinline__ float head_logit(const float f[8], const float* sw, int cv, int c8) {
+  float l = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) l = fmaf(f[j], sw[cv * 8 + j], l);
+  for (int o = c8 >> 1; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
+  return l;
+}
+
+__global__ void __launch_bounds__(TPB) head_fwd_k(const __nv_bfloat16* __restrict__ s, const float* __restrict__ w,
+                                                  const float* __restrict__ bias, const uint8_t* __restrict__ mask,
+                                                  float* __restrict__ acc, float* __restrict__ prob, int B, int Hl, int Wl,
+                                                  int C) {
+  extern __shared__ float sw[];
+  for (int i = threadIdx.x; i < C; i += blockDim.x) sw[i] = w[i];
+  __syncthreads();
+  const int c8 = C >> 3;
+  const long P = (long)B * Hl * Wl;
+  const long total = P * c8;
+  const long stride = (long)gridDim.x * blockDim.x;  // multiple of 32 -> whole pixels stay inside a warp
+  const int Wf = 2 * Wl, Hf = 2 * Hl;
+  float a[5] = {0, 0, 0, 0, 0};
+  const long iters = (total + stride - 1) / stride;
+  for (long it = 0; it < iters; ++it) {
+    const long g = it * stride + (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = g < total;
+    const long gg = valid ? g : 0;
+    const int cv = (int)(gg % c8);
+    const long p = gg / c8;
+    float f[8];
+    unpack8(ldg16(s + gg * 8), f);
+    const float logit = head_logit(f, sw, cv, c8) + bias[0];
+    if (!valid || cv != 0) continue;
+    const float pr = 1.f / (1.f + __expf(-logit));
+    const int wl = (int)(p % Wl);
+    const int hl = (int)((p / Wl) % Hl);
+    const long b = p / ((long)Wl * Hl);
+    const long base = (b * Hf + 2 * hl) * Wf + 2 * wl;
+    if (prob) {
+      prob[base] = pr; prob[base + 1] = pr; prob[base + Wf] = pr; prob[base + Wf + 1] = pr;
+    }
+    if (mask) {
+      const float pc = fminf(fmaxf(pr, 1e-7f), 1.f - 1e-7f);
+      const float lp = __logf(pc), lq = __logf(1.f - pc);
+#pragma unroll
+      for (int d = 0; d < 4; ++d) {
+        const float yv = mask[base + (d >> 1) * Wf + (d & 1)] ? 1.f : 0.f;
+        a[0] -= yv * lp + (1.f - yv) * lq;
+        a[1] += ((pr > 0.5f) == (yv > 0.5f)) ? 1.f : 0.f;
+        a[2] += pr * yv;
+        a[3] += pr;
+        a[4] += yv;
+      }
+    }
+  }
+  if (mask) {
+    __shared__ float red[5][TPB / 32];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      const float v = warp_sum(a[k]);
+      if ((threadIdx.x & 31) == 0) red[k][threadIdx.x >> 5] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 5) {
+      float v = 0.f;
+      for (int i = 0; i < TPB / 32; ++i) v += red[threadIdx.x][i];
+      atomicAdd(acc + threadIdx.x, v);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(acc + 5, (float)(P * 4));
+  }
+}
+
+// gradient of mean-BCE (+ optional soft Dice) w.r.t. the low-res logit, then ds = dlogit * w,
+// dw += dlogit * s, db += dlogit.  `sums` = the forward accumulators of THIS batch (needed by Dice).
+__global__ void __launch_bounds__(TPB) head_bwd_k(const __nv_bfloat16* __restrict__ s, const float* __restrict__ w,
+                                                  const float* __restrict__ bias, const uint8_t* __restrict__ mask,
+                                                  const float* __restrict__ sums, __nv_bfloat16* __restrict__ ds,
+                                                  float* __restrict__ dw, float* __restrict__ db, int B, int Hl, int Wl, int C,
+                                                  int use_dice, float dice_smooth, float loss_scale) {
+  extern __shared__ float sh[];  // w[C] | reduction scratch [TPB*8]
+  float* sw = sh;
+  float* sm = sh + C;
+  for (int i = threadIdx.x; i < C; i += blockDim.x) sw[i] = w[i];
+  __syncthreads();
+  const int c8 = C >> 3;
+  const long P = (long)B * Hl * Wl;
+  const long total = P * c8;
+  const long stride = (long)gridDim.x * blockDim.x;
+  const int Wf = 2 * Wl, Hf = 2 * Hl;
+  const float invn = 1.0f / (float)(P * 4);
+  float dnum = 0.f, dden = 1.f;
+  if (use_dice) {
+    dden = sums[3] + sums[4] + dice_smooth;
+    dnum = 2.f * sums[2] + dice_smooth;
+  }
+  float dwacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  float dbl = 0.f;
+  const long iters = (total + stride - 1) / stride;
+  for (long it = 0; it < iters; ++it) {
+    const long g = it * stride + (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = g < total;
+    const long gg = valid ? g : 0;
+    const int cv = (int)(gg % c8);
+    const long p = gg / c8;
+    float f[8], o[8];
+    unpack8(ldg16(s + gg * 8), f);
+    const float logit = head_logit(f, sw, cv, c8) + bias[0];
+    if (!valid) continue;
+    const float pr = 1.f / (1.f + __expf(-logit));
+    const int wl = (int)(p % Wl);
+    const int hl = (int)((p / Wl) % Hl);
+    const long b = p / ((long)Wl * Hl);
+    const long base = (b * Hf + 2 * hl) * Wf + 2 * wl;
+    const bool inside = (pr >= 1e-7f) && (pr <= 1.f - 1e-7f);  // clip_by_value passes no gradient outside
+    float dl = 0.f;
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+      const float yv = mask[base + (d >> 1) * Wf + (d & 1)] ? 1.f : 0.f;
+      if (inside) dl += (pr - yv) * invn;
+      if (use_dice) dl += -(2.f * yv * dden - dnum) / (dden * dden) * pr * (1.f - pr);
+    }
+    dl *= loss_scale;
+    if (cv == 0) dbl += dl;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      o[j] = dl * sw[cv * 8 + j];
+      dwacc[j] = fmaf(dl, f[j], dwacc[j]);
+    }
+    stg16(ds + gg * 8, pack8(o));
+  }
+  // thread t always owns channel vector (t % c8) because stride and blockDim are multiples of c8
+  block_channel_atomic(dwacc, c8, sm, dw);
+  dbl = warp_sum(dbl);
+  if ((threadIdx.x & 31) == 0) atomicAdd(db, dbl);
+}
+
+inline int grid_for(long total, int cap = 148 * 16) {
+  long b = (total + TPB - 1) / TPB;
+  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+inline int ppb_for(long P, int C) {
+  // pixels per block for the reduction kernels: aim at ~2 waves of 148 SMs x 4 blocks, >= one pass of all lanes
+  const int lanes = TPB / (C >> 3);
+  long target = (P + 148 * 8 - 1) / (148 * 8);
+  long ppb = ((target + lanes - 1) / lanes) * lanes;
+  if (ppb < lanes * 4) ppb = lanes * 4;
+  return (int)ppb;
+}
+
+}  // namespace
+
+extern "C" {
+
+int crackfl_entry_conv_fwd(const void* x_u8, const float* w, const float* bias, void* y, int B, int H, int W, int C,
+                           cudaStream_t st) {
+  const long total = (long)B * (H / 2) * (W / 2) * (C / 8);
+  entry_conv_fwd_k<<<grid_for(total), TPB, (27 * C + C) * sizeof(float), st>>>(
+      (const uint8_t*)x_u8, w, bias, (__nv_bfloat16*)y, B, H, W, C);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_entry_conv_wgrad(const void* x_u8, const void* dy, float* dw, int B, int H, int W, int C, cudaStream_t st) {
+  const long P = (long)B * (H / 2) * (W / 2);
+  const int ppb = 512;
+  dim3 blk(C / 8, 27);
+  if (blk.x * blk.y > 1024) return (int)cudaErrorInvalidValue;
+  entry_conv_wgrad_k<<<(int)((P + ppb - 1) / ppb), blk, 0, st>>>((const uint8_t*)x_u8, (const __nv_bfloat16*)dy, dw, B, H, W,
+                                                                C, ppb);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_bn_stats(const void* y, float* stats, long P, int C, cudaStream_t st) {
+  if (C % 8 || TPB % (C / 8)) return (int)cudaErrorInvalidValue;
+  const int ppb = ppb_for(P, C);
+  bn_stats_k<<<(int)((P + ppb - 1) / ppb), TPB, 0, st>>>((const __nv_bfloat16*)y, stats, P, C, ppb);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_bn_finalize(const float* stats, const float* gamma, const float* beta, float* run_mean, float* run_var,
+                        float* bn, int C, float count, float eps, float momentum, cudaStream_t st) {
+  bn_finalize_k<<<(C + 127) / 128, 128, 0, st>>>(stats, gamma, beta, run_mean, run_var, bn, C, count, eps, momentum);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_bn_eval_prepare(const float* gamma, const float* beta, const float* run_mean, const float* run_var, float* bn,
+                            int C, float eps, cudaStream_t st) {
+  bn_eval_prepare_k<<<(C + 127) / 128, 128, 0, st>>>(gamma, beta, run_mean, run_var, bn, C, eps);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_bn_act(const void* y, const float* bn, void* out, void* even, int B, int H, int W, int C, int relu,
+                   cudaStream_t st) {
+  const long total = (long)B * H * W * (C / 8);
+  bn_act_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, bn, (__nv_bfloat16*)out, (__nv_bfloat16*)even, B, H, W,
+                                            C, relu);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_dw3x3_fwd(const void* x, const float* w, const float* bn, void* out, int B, int H, int W, int C, int mode,
+                      cudaStream_t st) {
+  const long total = (long)B * H * W * (C / 8);
+  dw3x3_fwd_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)x, w, bn, (__nv_bfloat16*)out, B, H, W, C, mode);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_dw3x3_bwd(const void* g, const void* src, const float* w, const float* bn, const void* resid_t, void* dz,
+                      float* dwk, int B, int H, int W, int C, int mode, int resid, cudaStream_t st) {
+  if (C % 8 || TPB % (C / 8)) return (int)cudaErrorInvalidValue;
+  const long P = (long)B * H * W;
+  const int ppb = ppb_for(P, C);
+  dw3x3_bwd_k<<<(int)((P + ppb - 1) / ppb), TPB, 0, st>>>((const __nv_bfloat16*)g, (const __nv_bfloat16*)src, w, bn,
+                                                          (const __nv_bfloat16*)resid_t, (__nv_bfloat16*)dz, dwk, B, H, W,
+                                                          C, mode, resid, ppb);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_pool_add_fwd(const void* y, const float* bn, const void* res, void* out, void* even, void* relu_out, void* arg,
+                         int B, int H, int W, int C, cudaStream_t st) {
+  const long total = (long)B * (H / 2) * (W / 2) * (C / 8);
+  pool_add_fwd_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, bn, (const __nv_bfloat16*)res,
+                                                  (__nv_bfloat16*)out, (__nv_bfloat16*)even, (__nv_bfloat16*)relu_out,
+                                                  (uint8_t*)arg, B, H, W, C);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_dec_combine_fwd(const void* y, const float* bn, const void* rl, void* s, void* a_next, int B, int H, int W,
+                            int C, int rl_up, cudaStream_t st) {
+  const long total = (long)B * H * W * (C / 8);
+  dec_combine_fwd_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, bn, (const __nv_bfloat16*)rl,
+                                                     (__nv_bfloat16*)s, (__nv_bfloat16*)a_next, B, H, W, C, rl_up);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_down2sum(const void* in, const void* mask, const void* add, void* out, int B, int Ho, int Wo, int C,
+                     cudaStream_t st) {
+  const long total = (long)B * Ho * Wo * (C / 8);
+  down2sum_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)in, (const __nv_bfloat16*)mask,
+                                              (const __nv_bfloat16*)add, (__nv_bfloat16*)out, B, Ho, Wo, C);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_relu_bwd_add(const void* g, const void* x, const void* add, void* out, long numel, cudaStream_t st) {
+  const long nvec = numel / 8;
+  relu_bwd_add_k<<<grid_for(nvec), TPB, 0, st>>>((const __nv_bfloat16*)g, (const __nv_bfloat16*)x,
+                                                 (const __nv_bfloat16*)add, (__nv_bfloat16*)out, nvec);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_bn_bwd_reduce(const void* g, const void* arg, const void* y, const float* bn, float* sums, int B, int H, int W,
+                          int C, int mode, cudaStream_t st) {
+  if (C % 8 || TPB % (C / 8)) return (int)cudaErrorInvalidValue;
+  const long P = (long)B * H * W;
+  const int ppb = ppb_for(P, C);
+  const int grid = (int)((P + ppb - 1) / ppb);
+  const __nv_bfloat16* gp = (const __nv_bfloat16*)g;
+  const __nv_bfloat16* yp = (const __nv_bfloat16*)y;
+  const uint8_t* ap = (const uint8_t*)arg;
+  if (mode == 0) bn_bwd_reduce_k<0><<<grid, TPB, 0, st>>>(gp, ap, yp, bn, sums, P, H, W, C, ppb);
+  else if (mode == 1) bn_bwd_reduce_k<1><<<grid, TPB, 0, st>>>(gp, ap, yp, bn, sums, P, H, W, C, ppb);
+  else bn_bwd_reduce_k<2><<<grid, TPB, 0, st>>>(gp, ap, yp, bn, sums, P, H, W, C, ppb);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_bn_bwd_apply(const void* g, const void* arg, const void* y, const float* bn, const float* sums, void* dy,
+                         float* dgamma, float* dbeta, int B, int H, int W, int C, int mode, cudaStream_t st) {
+  const long P = (long)B * H * W;
+  const int grid = grid_for(P * (C / 8));
+  const __nv_bfloat16* gp = (const __nv_bfloat16*)g;
+  const __nv_bfloat16* yp = (const __nv_bfloat16*)y;
+  const uint8_t* ap = (const uint8_t*)arg;
+  __nv_bfloat16* dp = (__nv_bfloat16*)dy;
+  if (mode == 0) bn_bwd_apply_k<0><<<grid, TPB, 0, st>>>(gp, ap, yp, bn, sums, dp, dgamma, dbeta, P, H, W, C);
+  else if (mode == 1) bn_bwd_apply_k<1><<<grid, TPB, 0, st>>>(gp, ap, yp, bn, sums, dp, dgamma, dbeta, P, H, W, C);
+  else bn_bwd_apply_k<2><<<grid, TPB, 0, st>>>(gp, ap, yp, bn, sums, dp, dgamma, dbeta, P, H, W, C);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_colsum(const void* g, float* out, long P, int C, cudaStream_t st) {
+  if (C % 8 || TPB % (C / 8)) return (int)cudaErrorInvalidValue;
+  const int ppb = ppb_for(P, C);
+  colsum_k<<<(int)((P + ppb - 1) / ppb), TPB, 0, st>>>((const __nv_bfloat16*)g, out, P, C, ppb);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_head_fwd(const void* s, const float* w, const float* bias, const void* mask_u8, float* acc, float* prob, int B,
+                     int Hl, int Wl, int C, cudaStream_t st) {
+  const long P = (long)B * Hl * Wl;
+  head_fwd_k<<<grid_for(P * (C / 8), 148 * 8), TPB, C * sizeof(float), st>>>((const __nv_bfloat16*)s, w, bias,
+                                                                   (const uint8_t*)mask_u8, acc, prob, B, Hl, Wl, C);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_head_bwd(const void* s, const float* w, const float* bias, const void* mask_u8, const float* sums, void* ds,
+                     float* dw, float* db, int B, int Hl, int Wl, int C, int use_dice, float dice_smooth, float loss_scale,
+                     cudaStream_t st) {
+  const long P = (long)B * Hl * Wl;
+  head_bwd_k<<<grid_for(P * (C / 8), 148 * 8), TPB, (C + TPB * 8) * sizeof(float), st>>>(
+      (const __nv_bfloat16*)s, w, bias, (const uint8_t*)mask_u8, sums, (__nv_bfloat16*)ds, dw, db, B, Hl, Wl, C, use_dice,
+      dice_smooth, loss_scale);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

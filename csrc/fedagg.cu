@@ -1,0 +1,207 @@
+// Fused federated aggregation: ONE kernel that
+//   (1) waits for every rank's update to be published      (signal pads, st.release.sys / ld.acquire.sys)
+//   (2) for its shard of the flat arena pulls every client's update with 128-bit loads
+//       (local HBM or NVLink peer memory: the pointers decide), scales by the per-client coefficient
+//       n_k / sum n, casts bf16->fp32 and accumulates in fp32 registers
+//   (3) applies the server update on the fp32 master shard: FedAvg (w = sum) or FedAdam
+//   (4) stores the new global shard straight into every destination arena (each client's live
+//       parameter arena on every GPU = "broadcast fused with the weight reload"), either as peer
+//       stores or as ONE multimem.st to an NVLS multicast address (the switch replicates)
+//   (5) signals completion to the peers and waits for theirs.
+// It replaces the reference's gather (N gRPC uploads, fl_client.py:61-65 -> fl_server.py:176-179),
+// NumPy reduce (fl_server.py:92-102), N unicast downloads (fl_server.py:190,201) and the 20 s poll
+// barrier (fl_client.py:136-152).  No host round trip, no NCCL call on this path.
+//
+// With world == 1 and K local client buffers the same kernel is the per-GPU pre-reduce (K14) and
+// the single-GPU emulation of a multi-rank round used by the 1-GPU tests.
+#include "common.cuh"
+#include "../include/crackfl.h"
+
+namespace {
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_nc_f4(const float* p) {
+  float4 r;
+  asm volatile("ld.global.relaxed.sys.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint2 ld_nc_u2(const void* p) {
+  uint2 r;
+  asm volatile("ld.global.relaxed.sys.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void multimem_st_f4(float* mc, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+constexpr long long SPIN_TIMEOUT_CYCLES = 4000000000LL;  // ~2 s at 1.9 GHz: a dead rank cannot hang the box
+
+// Cross-GPU barrier over the signal pads.  pad layout per rank: [phase(2)][world] u32, monotonically
+// increasing epoch values (no reset race).  One thread per peer.
+__device__ void pad_barrier(const crackfl_fedagg_params& P, int phase) {
+  const int j = threadIdx.x;
+  if (j < P.world) {
+    st_release_sys(P.pads[j] + phase * CRACKFL_MAX_RANKS + P.rank, P.epoch);
+    const uint32_t* mine = P.pads[P.rank] + phase * CRACKFL_MAX_RANKS + j;
+    const long long t0 = clock64();
+    while (ld_acquire_sys(mine) < P.epoch) {
+      if (clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
+        atomicExch(P.error_flag, 1 + phase);
+        break;
+      }
+    }
+  }
+}
+
+template <bool PAYLOAD_BF16, bool OUT_BF16>
+__global__ void __launch_bounds__(256) fedagg_k(const crackfl_fedagg_params P) {
+  if (P.world > 1) {
+    // (1) enter: block 0 does the cross-GPU handshake and then releases the local grid
+    if (blockIdx.x == 0) {
+      pad_barrier(P, 0);
+      __syncthreads();
+      if (threadIdx.x == 0) st_release_gpu(P.local_sync, P.epoch);
+    } else if (threadIdx.x == 0) {
+      const long long t0 = clock64();
+      while (ld_acquire_gpu(P.local_sync) < P.epoch) {
+        if (clock64() - t0 > 2 * SPIN_TIMEOUT_CYCLES) { atomicExch(P.error_flag, 3); break; }
+      }
+    }
+    __syncthreads();
+  }
+
+  const long n4_begin = P.begin >> 2, n4_end = P.end >> 2;
+  for (long i = n4_begin + (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4_end; i += (long)gridDim.x * blockDim.x) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+    for (int k = 0; k < P.num_clients; ++k) {
+      const float c = P.coef[k];
+      if (PAYLOAD_BF16) {
+        const uint2 u = ld_nc_u2(reinterpret_cast<const uint2*>(P.client[k]) + i);
+        acc.x = fmaf(c, __uint_as_float(u.x << 16), acc.x);
+        acc.y = fmaf(c, __uint_as_float(u.x & 0xffff0000u), acc.y);
+        acc.z = fmaf(c, __uint_as_float(u.y << 16), acc.z);
+        acc.w = fmaf(c, __uint_as_float(u.y & 0xffff0000u), acc.w);
+      } else {
+        const float4 u = ld_nc_f4(reinterpret_cast<const float*>(P.client[k]) + i * 4);
+        acc.x = fmaf(c, u.x, acc.x); acc.y = fmaf(c, u.y, acc.y);
+        acc.z = fmaf(c, u.z, acc.z); acc.w = fmaf(c, u.w, acc.w);
+      }
+    }
+    float4 nw = acc;
+    if (P.master) {
+      float4 w = reinterpret_cast<float4*>(P.master)[i];
+      if (P.delta) { nw.x += w.x; nw.y += w.y; nw.z += w.z; nw.w += w.w; }
+      if (P.server_opt == 1) {
+        float4 m = reinterpret_cast<float4*>(P.m)[i];
+        float4 v = reinterpret_cast<float4*>(P.v)[i];
+        const uchar4 tr = P.trainable ? reinterpret_cast<const uchar4*>(P.trainable)[i] : make_uchar4(1, 1, 1, 1);
+#define CK_FEDADAM1(c)                                                   \
+  if (tr.c) {                                                            \
+    const float d = nw.c - w.c;                                          \
+    m.c = P.beta1 * m.c + (1.f - P.beta1) * d;                           \
+    v.c = P.beta2 * v.c + (1.f - P.beta2) * d * d;                       \
+    nw.c = w.c + P.eta * m.c / (sqrtf(v.c) + P.tau);                     \
+  }
+        CK_FEDADAM1(x) CK_FEDADAM1(y) CK_FEDADAM1(z) CK_FEDADAM1(w)
+#undef CK_FEDADAM1
+        reinterpret_cast<float4*>(P.m)[i] = m;
+        reinterpret_cast<float4*>(P.v)[i] = v;
+      }
+      reinterpret_cast<float4*>(P.master)[i] = nw;
+    }
+    if (P.mc_out) {
+      multimem_st_f4(P.mc_out + i * 4, nw);
+    } else {
+      if (OUT_BF16) {
+        uint2 o;
+        o.x = ck::pack2(nw.x, nw.y);
+        o.y = ck::pack2(nw.z, nw.w);
+        for (int r = 0; r < P.num_out; ++r) reinterpret_cast<uint2*>(P.out[r])[i] = o;
+      } else {
+        for (int r = 0; r < P.num_out; ++r) reinterpret_cast<float4*>(P.out[r])[i] = nw;
+      }
+    }
+  }
+
+  if (P.world > 1) {
+    // (5) exit: every block's stores are fenced system-wide, the last block to arrive handshakes
+    __threadfence_system();
+    __syncthreads();
+    __shared__ int s_last;
+    if (threadIdx.x == 0) {
+      const unsigned prev = atomicAdd(P.local_sync + 1, 1u);
+      s_last = (prev + 1 == gridDim.x * P.epoch);
+    }
+    __syncthreads();
+    if (s_last) pad_barrier(P, 1);
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+int crackfl_fedagg(const crackfl_fedagg_params* p, int grid_blocks, cudaStream_t st) {
+  if (p->num_clients < 1 || p->num_clients > CRACKFL_MAX_CLIENTS || p->num_out > CRACKFL_MAX_OUT ||
+      p->world > CRACKFL_MAX_RANKS || (p->begin & 3) || (p->end & 3) || p->end < p->begin)
+    return (int)cudaErrorInvalidValue;
+  if (p->mc_out && p->out_bf16) return (int)cudaErrorInvalidValue;
+  long n4 = (p->end - p->begin) / 4;
+  long blocks = (n4 + 255) / 256;
+  if (blocks > grid_blocks) blocks = grid_blocks;
+  if (blocks < 1) blocks = 1;
+  if (p->world > 1) blocks = grid_blocks;  // grid size is part of the exit-barrier arithmetic
+  const int g = (int)blocks;
+  if (p->payload_bf16) {
+    if (p->out_bf16) fedagg_k<true, true><<<g, 256, 0, st>>>(*p);
+    else fedagg_k<true, false><<<g, 256, 0, st>>>(*p);
+  } else {
+    if (p->out_bf16) fedagg_k<false, true><<<g, 256, 0, st>>>(*p);
+    else fedagg_k<false, false><<<g, 256, 0, st>>>(*p);
+  }
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+// ---- peer-memory plumbing (legacy CUDA IPC: works between the per-GPU processes of one box) ----
+int crackfl_ipc_export(void* dev_ptr, void* handle_out64) {
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, dev_ptr);
+  if (e != cudaSuccess) return (int)e;
+  memcpy(handle_out64, &h, sizeof(h));
+  return 0;
+}
+
+int crackfl_ipc_open(const void* handle64, void** dev_ptr_out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  cudaError_t e = cudaIpcOpenMemHandle(dev_ptr_out, h, cudaIpcMemLazyEnablePeerAccess);
+  return (int)e;
+}
+
+int crackfl_ipc_close(void* dev_ptr) { return (int)cudaIpcCloseMemHandle(dev_ptr); }
+
+int crackfl_enable_peer_access(int peer_device) {
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return 0; }
+  return (int)e;
+}
+
+}  // extern "C"

@@ -1,0 +1,104 @@
+// Optimiser-side kernels over the flat parameter arena (SURVEY section 8 rows K10 and the weight re-layout).
+//   * Keras-form Adam (client_fit_model.py:157 optimizer="Adam"): theta -= lr_t * m / (sqrt(v) + eps),
+//     lr_t = lr * sqrt(1 - b2^t) / (1 - b1^t), eps = 1e-7 outside the bias correction; zero-grad fused.
+//   * weight_prep: fp32 Keras-layout master weights -> bf16 K-major GEMM operands for conv_tc/conv_simt,
+//     one table-driven launch for every operand of the model.
+#include "common.cuh"
+#include "../include/crackfl.h"
+
+namespace {
+
+__global__ void adam_tick_k(int* __restrict__ step) { *step += 1; }
+
+__global__ void __launch_bounds__(256) adam_k(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
+                                              float* __restrict__ v, const int* __restrict__ step, long n4, float lr,
+                                              float b1, float b2, float eps) {
+  __shared__ float s_lrt;
+  if (threadIdx.x == 0) {
+    const float t = (float)(*step);
+    s_lrt = lr * sqrtf(1.f - powf(b2, t)) / (1.f - powf(b1, t));
+  }
+  __syncthreads();
+  const float lrt = s_lrt;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
+    float4 pv = reinterpret_cast<float4*>(p)[i];
+    const float4 gv = reinterpret_cast<float4*>(g)[i];
+    float4 mv = reinterpret_cast<float4*>(m)[i];
+    float4 vv = reinterpret_cast<float4*>(v)[i];
+#define CK_ADAM1(c)                                  \
+  mv.c = b1 * mv.c + (1.f - b1) * gv.c;              \
+  vv.c = b2 * vv.c + (1.f - b2) * gv.c * gv.c;       \
+  pv.c -= lrt * mv.c / (sqrtf(vv.c) + eps);
+    CK_ADAM1(x) CK_ADAM1(y) CK_ADAM1(z) CK_ADAM1(w)
+#undef CK_ADAM1
+    reinterpret_cast<float4*>(p)[i] = pv;
+    reinterpret_cast<float4*>(m)[i] = mv;
+    reinterpret_cast<float4*>(v)[i] = vv;
+    reinterpret_cast<float4*>(g)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+__global__ void __launch_bounds__(256) weight_prep_k(const float* __restrict__ arena, __nv_bfloat16* __restrict__ ops,
+                                                     const crackfl_prep_desc* __restrict__ descs) {
+  const crackfl_prep_desc d = descs[blockIdx.y];
+  const long total = (long)d.N * d.T * d.K;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int k = (int)(i % d.K);
+    const int t = (int)((i / d.K) % d.T);
+    const long n = i / ((long)d.K * d.T);
+    ops[d.dst_off + i] = __float2bfloat16_rn(arena[d.src_off + n * d.s_n + t * d.s_t + k * d.s_k]);
+  }
+}
+
+__global__ void __launch_bounds__(256) f32_to_bf16_k(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long n) {
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+    out[i] = __float2bfloat16_rn(in[i]);
+}
+
+// K16 staging: client update (fp32, just copied H2D or just trained) -> bf16 delta against the global model
+__global__ void __launch_bounds__(256) publish_delta_k(const float* __restrict__ local, const float* __restrict__ global,
+                                                       __nv_bfloat16* __restrict__ out, long n) {
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+    out[i] = __float2bfloat16_rn(local[i] - global[i]);
+}
+
+}  // namespace
+
+extern "C" {
+
+int crackfl_publish_delta(const float* local, const float* global, void* out_bf16, long n, cudaStream_t st) {
+  long blocks = (n + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  publish_delta_k<<<(int)blocks, 256, 0, st>>>(local, global, (__nv_bfloat16*)out_bf16, n);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_adam_step(float* p, float* g, float* m, float* v, int* step, long n, float lr, float b1, float b2, float eps,
+                      cudaStream_t st) {
+  if (n % 4) return (int)cudaErrorInvalidValue;
+  adam_tick_k<<<1, 1, 0, st>>>(step);
+  const long n4 = n / 4;
+  long blocks = (n4 + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  adam_k<<<(int)blocks, 256, 0, st>>>(p, g, m, v, step, n4, lr, b1, b2, eps);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_weight_prep(const float* arena, void* ops, const crackfl_prep_desc* descs_dev, int num_desc, cudaStream_t st) {
+  dim3 grid(32, num_desc);
+  weight_prep_k<<<grid, 256, 0, st>>>(arena, (__nv_bfloat16*)ops, descs_dev);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_f32_to_bf16(const float* in, void* out, long n, cudaStream_t st) {
+  long blocks = (n + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  f32_to_bf16_k<<<(int)blocks, 256, 0, st>>>(in, (__nv_bfloat16*)out, n);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

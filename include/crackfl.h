@@ -1,0 +1,134 @@
+/* crackfl C ABI: every sm_100a kernel of the framework behind a plain `extern "C"` launcher.
+ *
+ * Conventions
+ *   - activations: NHWC bf16 (`void*`), channel counts multiples of 8;
+ *   - parameters / gradients / optimiser state: fp32 views into the flat arena (Keras layouts);
+ *   - every launcher enqueues on `stream` and returns 0 or a cudaError_t value; nothing synchronises;
+ *   - no launcher allocates: all scratch is passed in by the caller.
+ * The "ref:" notes name the reference site (file:line under the upstream repo) each kernel replaces.
+ */
+#ifndef CRACKFL_H_
+#define CRACKFL_H_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- entry block ------------------------------------------------------------------------- */
+/* ref: client_fit_model.py:100 Conv2D(32,3,strides=2,"same") + :43 x/255.  uint8 NHWC in, bf16 out. */
+int crackfl_entry_conv_fwd(const void* x_u8, const float* w, const float* bias, void* y, int B, int H, int W, int C,
+                           cudaStream_t stream);
+int crackfl_entry_conv_wgrad(const void* x_u8, const void* dy, float* dw, int B, int H, int W, int C, cudaStream_t stream);
+
+/* ---- batch normalisation (ref: client_fit_model.py:101,110,114,130,134; eps 1e-3, momentum .99) ---- */
+/* stats = [sum C][sumsq C]; bn = [scale C][shift C][mean C][invstd C]; sums = [sum dz C][sum dz*xhat C] */
+int crackfl_bn_stats(const void* y, float* stats, long P, int C, cudaStream_t stream);
+int crackfl_bn_finalize(const float* stats, const float* gamma, const float* beta, float* run_mean, float* run_var,
+                        float* bn, int C, float count, float eps, float momentum, cudaStream_t stream);
+int crackfl_bn_eval_prepare(const float* gamma, const float* beta, const float* run_mean, const float* run_var, float* bn,
+                            int C, float eps, cudaStream_t stream);
+int crackfl_bn_act(const void* y, const float* bn, void* out, void* even_or_null, int B, int H, int W, int C, int relu,
+                   cudaStream_t stream);
+/* mode: 0 dz=g, 1 dz=g*1[bn(y)>0], 2 dz=maxpool-backward gather of g through `arg` */
+int crackfl_bn_bwd_reduce(const void* g, const void* arg, const void* y, const float* bn, float* sums, int B, int H, int W,
+                          int C, int mode, cudaStream_t stream);
+int crackfl_bn_bwd_apply(const void* g, const void* arg, const void* y, const float* bn, const float* sums, void* dy,
+                         float* dgamma, float* dbeta, int B, int H, int W, int C, int mode, cudaStream_t stream);
+
+/* ---- depthwise 3x3 (ref: SeparableConv2D, client_fit_model.py:109,113) -------------------- */
+/* mode 0: a = relu(x); mode 1: a = relu(x*scale+shift) */
+int crackfl_dw3x3_fwd(const void* x, const float* w, const float* bn, void* out, int B, int H, int W, int C, int mode,
+                      cudaStream_t stream);
+int crackfl_dw3x3_bwd(const void* g, const void* src, const float* w, const float* bn, const void* resid_t, void* dz,
+                      float* dwk, int B, int H, int W, int C, int mode, int resid, cudaStream_t stream);
+
+/* ---- block tails --------------------------------------------------------------------------- */
+/* ref: client_fit_model.py:116-123 MaxPooling2D(3,2,"same") + add(residual) */
+int crackfl_pool_add_fwd(const void* y, const float* bn, const void* res, void* out, void* even_or_null,
+                         void* relu_out_or_null, void* argmax_u8, int B, int H, int W, int C, cudaStream_t stream);
+/* ref: client_fit_model.py:136-142 UpSampling2D(2) x2 + Conv2D 1x1 + add, evaluated at low resolution */
+int crackfl_dec_combine_fwd(const void* y, const float* bn, const void* rl, void* s, void* a_next_or_null, int B, int H,
+                            int W, int C, int rl_up, cudaStream_t stream);
+int crackfl_down2sum(const void* in, const void* mask_or_null, const void* add_or_null, void* out, int B, int Ho, int Wo,
+                     int C, cudaStream_t stream);
+int crackfl_relu_bwd_add(const void* g, const void* x, const void* add_or_null, void* out, long numel, cudaStream_t stream);
+int crackfl_colsum(const void* g, float* out, long P, int C, cudaStream_t stream);
+
+/* ---- head: Conv2D(1,1x1,sigmoid) + binary_crossentropy (+Dice ext.) + accuracy (ref: :145,157) ---- */
+/* acc = [bce_sum, correct, intersection, prob_sum, mask_sum, pixel_count] (accumulated; caller zeroes) */
+int crackfl_head_fwd(const void* s, const float* w, const float* bias, const void* mask_u8_or_null, float* acc,
+                     float* prob_or_null, int B, int Hl, int Wl, int C, cudaStream_t stream);
+int crackfl_head_bwd(const void* s, const float* w, const float* bias, const void* mask_u8, const float* sums, void* ds,
+                     float* dw, float* db, int B, int Hl, int Wl, int C, int use_dice, float dice_smooth, float loss_scale,
+                     cudaStream_t stream);
+
+/* ---- GEMM-shaped convolutions ---------------------------------------------------------------- */
+/* CUDA-core implicit GEMM (cross-check + odd shapes).  Wk[N][taps*Cin] bf16, taps in {1,9}. */
+int crackfl_conv_simt_fwd(const void* X, const void* Wk, const float* bias_or_null, const void* add_or_null, void* Y, int B,
+                          int H, int W, int Cin, int N, int taps, cudaStream_t stream);
+int crackfl_wgrad_simt(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps, long s_tap,
+                       long s_ci, long s_co, cudaStream_t stream);
+/* tcgen05 / TMEM / TMA implicit GEMM (ref: Conv2DTranspose :129,133, SeparableConv2D pointwise :109,113,
+ * residual Conv2D :119,140 and their dgrad).  stats_or_null: fused BN sum/sumsq epilogue. */
+int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias_or_null, const void* add_or_null, void* Y,
+                        float* stats_or_null, int B, int H, int W, int Cin, int N, int taps, cudaStream_t stream);
+/* tcgen05 weight gradient with MN-major operands, split over pixels, fp32 atomics into the arena. */
+int crackfl_wgrad_tc(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps, long s_tap,
+                     long s_ci, long s_co, cudaStream_t stream);
+int crackfl_tc_selftest_supported(void);
+
+/* ---- optimiser / weight re-layout ------------------------------------------------------------ */
+typedef struct {
+  long src_off; /* element offset into the fp32 arena (already includes any flip base) */
+  long dst_off; /* element offset into the bf16 operand buffer */
+  int N, T, K;  /* out[dst + (n*T + t)*K + k] = arena[src + n*s_n + t*s_t + k*s_k] */
+  int pad_;
+  long s_n, s_t, s_k;
+} crackfl_prep_desc;
+int crackfl_weight_prep(const float* arena, void* ops_bf16, const crackfl_prep_desc* descs_dev, int num_desc,
+                        cudaStream_t stream);
+/* ref: client_fit_model.py:157 optimizer="Adam" (Keras form, eps 1e-7); also zeroes g */
+int crackfl_adam_step(float* p, float* g, float* m, float* v, int* step_dev, long n, float lr, float b1, float b2, float eps,
+                      cudaStream_t stream);
+int crackfl_f32_to_bf16(const float* in, void* out, long n, cudaStream_t stream);
+/* staging of a client update as a bf16 delta against the global model (ref: fl_client.py:61-65 upload) */
+int crackfl_publish_delta(const float* local, const float* global, void* out_bf16, long n, cudaStream_t stream);
+
+/* ---- fused federated aggregation (ref: fl_server.py:92-102 + the gRPC gather/broadcast/poll) ---- */
+#define CRACKFL_MAX_CLIENTS 128
+#define CRACKFL_MAX_OUT 16
+#define CRACKFL_MAX_RANKS 16
+typedef struct {
+  const void* client[CRACKFL_MAX_CLIENTS]; /* update arenas, local or peer-mapped */
+  float coef[CRACKFL_MAX_CLIENTS];         /* n_k / sum n (or 1/K) */
+  void* out[CRACKFL_MAX_OUT];              /* destination arenas for the new global model */
+  int num_clients, num_out;
+  int payload_bf16, out_bf16;
+  int delta;      /* payload is w_k - w_global */
+  int server_opt; /* 0 FedAvg, 1 FedAdam */
+  float eta, beta1, beta2, tau;
+  float* master;            /* fp32 global model (NULL: pure weighted sum, e.g. per-GPU pre-reduce) */
+  float* m;                 /* FedAdam moments */
+  float* v;
+  const uint8_t* trainable; /* per-element mask for FedAdam (BN moving stats are plain-averaged) */
+  float* mc_out;            /* NVLS multicast address of the destination arena (fp32) or NULL */
+  long begin, end;          /* this rank's shard [begin,end), multiples of 4 elements */
+  uint32_t* pads[CRACKFL_MAX_RANKS]; /* signal pads of every rank: [2][CRACKFL_MAX_RANKS] u32 */
+  int rank, world;
+  uint32_t epoch;           /* 1,2,3,... monotonically per call */
+  int* error_flag;          /* set non-zero on spin timeout */
+  uint32_t* local_sync;     /* [2] u32 in local memory, zero-initialised once */
+} crackfl_fedagg_params;
+int crackfl_fedagg(const crackfl_fedagg_params* p, int grid_blocks, cudaStream_t stream);
+int crackfl_ipc_export(void* dev_ptr, void* handle_out64);
+int crackfl_ipc_open(const void* handle64, void** dev_ptr_out);
+int crackfl_ipc_close(void* dev_ptr);
+int crackfl_enable_peer_access(int peer_device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CRACKFL_H_ */

@@ -1,0 +1,196 @@
+"""sm_100a kernels vs plain PyTorch fp32 references (SURVEY §4 'Unit, GPU').  Needs a B200."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _lib():
+    from crackfl.ops import lib as L
+    return L, L.get_lib()
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _conv_ref(x_nhwc, wk, bias, taps, cin):
+    """x (B,H,W,Cin) fp32, wk (N, taps*Cin) with K = tap*Cin + ci, tap t reads pixel p + (t//3-1, t%3-1)."""
+    N = wk.shape[0]
+    k = 3 if taps == 9 else 1
+    w = wk.reshape(N, k, k, cin).permute(0, 3, 1, 2)
+    y = F.conv2d(x_nhwc.permute(0, 3, 1, 2), w, bias, padding=k // 2)
+    return y.permute(0, 2, 3, 1)
+
+
+@pytest.mark.parametrize("impl", ["simt", "tc"])
+@pytest.mark.parametrize("B,H,W,cin,N,taps", [(2, 16, 16, 32, 32, 9), (2, 8, 8, 256, 256, 9), (1, 32, 32, 64, 128, 1),
+                                               (3, 16, 24, 128, 64, 9), (2, 16, 16, 64, 32, 1), (2, 28, 28, 64, 64, 9)])
+def test_conv_fwd(impl, B, H, W, cin, N, taps):
+    L, lib = _lib()
+    torch.manual_seed(0)
+    x = torch.randn(B, H, W, cin, device="cuda").bfloat16()
+    wk = (torch.randn(N, taps * cin, device="cuda") / np.sqrt(taps * cin)).bfloat16()
+    bias = torch.randn(N, device="cuda")
+    y = torch.zeros(B, H, W, N, device="cuda", dtype=torch.bfloat16)
+    if impl == "simt":
+        L.check(lib.crackfl_conv_simt_fwd(x.data_ptr(), wk.data_ptr(), bias.data_ptr(), 0, y.data_ptr(), B, H, W, cin, N,
+                                          taps, _st()))
+    else:
+        L.check(lib.crackfl_conv_tc_fwd(x.data_ptr(), wk.data_ptr(), bias.data_ptr(), 0, y.data_ptr(), 0, B, H, W, cin, N,
+                                        taps, _st()))
+    torch.cuda.synchronize()
+    ref = _conv_ref(x.float(), wk.float(), bias, taps, cin)
+    err = float((y.float() - ref).norm() / ref.norm())
+    assert err < 1e-2, err
+
+
+@pytest.mark.parametrize("impl", ["tc"])
+def test_conv_tc_fused_stats_and_add(impl):
+    L, lib = _lib()
+    torch.manual_seed(1)
+    B, H, W, cin, N, taps = 2, 16, 16, 64, 64, 9
+    x = torch.randn(B, H, W, cin, device="cuda").bfloat16()
+    wk = (torch.randn(N, taps * cin, device="cuda") / np.sqrt(taps * cin)).bfloat16()
+    add = torch.randn(B, H, W, N, device="cuda").bfloat16()
+    y = torch.zeros(B, H, W, N, device="cuda", dtype=torch.bfloat16)
+    stats = torch.zeros(2 * N, device="cuda")
+    L.check(lib.crackfl_conv_tc_fwd(x.data_ptr(), wk.data_ptr(), 0, add.data_ptr(), y.data_ptr(), stats.data_ptr(), B, H, W,
+                                    cin, N, taps, _st()))
+    torch.cuda.synchronize()
+    ref = _conv_ref(x.float(), wk.float(), None, taps, cin) + add.float()
+    assert float((y.float() - ref).norm() / ref.norm()) < 1e-2
+    yf = y.float().reshape(-1, N)
+    assert torch.allclose(stats[:N], yf.sum(0), rtol=2e-2, atol=0.5)
+    assert torch.allclose(stats[N:], (yf * yf).sum(0), rtol=2e-2, atol=0.5)
+
+
+@pytest.mark.parametrize("impl", ["simt", "tc"])
+@pytest.mark.parametrize("B,H,W,cin,cout,taps", [(2, 16, 16, 32, 32, 9), (2, 8, 8, 256, 256, 9), (2, 16, 16, 64, 128, 1),
+                                                  (2, 32, 32, 128, 64, 9), (1, 28, 28, 32, 64, 1)])
+def test_wgrad(impl, B, H, W, cin, cout, taps):
+    L, lib = _lib()
+    torch.manual_seed(0)
+    x = torch.randn(B, H, W, cin, device="cuda").bfloat16()
+    dy = torch.randn(B, H, W, cout, device="cuda").bfloat16()
+    dw = torch.zeros(taps, cin, cout, device="cuda")
+    fn = lib.crackfl_wgrad_simt if impl == "simt" else lib.crackfl_wgrad_tc
+    L.check(fn(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), B, H, W, cin, cout, taps, cin * cout, cout, 1, _st()))
+    torch.cuda.synchronize()
+    k = 3 if taps == 9 else 1
+    w = torch.zeros(cout, cin, k, k, device="cuda", requires_grad=True)
+    yy = F.conv2d(x.float().permute(0, 3, 1, 2), w, padding=k // 2)
+    yy.backward(dy.float().permute(0, 3, 1, 2))
+    ref = w.grad.permute(2, 3, 1, 0).reshape(taps, cin, cout)
+    err = float((dw - ref).norm() / ref.norm())
+    assert err < 1e-2, err
+
+
+def test_dw3x3_fwd_bwd():
+    L, lib = _lib()
+    torch.manual_seed(0)
+    B, H, W, Cc = 2, 12, 20, 64
+    x = torch.randn(B, H, W, Cc, device="cuda").bfloat16()
+    w = torch.randn(9, Cc, device="cuda")
+    out = torch.zeros_like(x)
+    L.check(lib.crackfl_dw3x3_fwd(x.data_ptr(), w.data_ptr(), 0, out.data_ptr(), B, H, W, Cc, 0, _st()))
+    xr = x.float().permute(0, 3, 1, 2).clone().requires_grad_(True)
+    wr = w.reshape(3, 3, Cc).permute(2, 0, 1)[:, None].clone().requires_grad_(True)
+    ref = F.conv2d(F.relu(xr), wr, padding=1, groups=Cc)
+    torch.cuda.synchronize()
+    assert float((out.float().permute(0, 3, 1, 2) - ref).norm() / ref.norm()) < 1e-2
+    g = torch.randn(B, H, W, Cc, device="cuda").bfloat16()
+    ref.backward(g.float().permute(0, 3, 1, 2))
+    dz = torch.zeros_like(x); dwk = torch.zeros(9, Cc, device="cuda")
+    L.check(lib.crackfl_dw3x3_bwd(g.data_ptr(), x.data_ptr(), w.data_ptr(), 0, 0, dz.data_ptr(), dwk.data_ptr(), B, H, W, Cc,
+                                  0, 0, _st()))
+    torch.cuda.synchronize()
+    assert float((dz.float().permute(0, 3, 1, 2) - xr.grad).norm() / xr.grad.norm()) < 1e-2
+    refw = wr.grad[:, 0].permute(1, 2, 0).reshape(9, Cc)
+    assert float((dwk - refw).norm() / refw.norm()) < 1e-2
+
+
+def test_adam_matches_keras_form():
+    L, lib = _lib()
+    from crackfl.models.unet_ref import KerasAdam
+    torch.manual_seed(0)
+    n = 4096
+    p = torch.randn(n, device="cuda"); p0 = p.clone()
+    m = torch.zeros(n, device="cuda"); v = torch.zeros(n, device="cuda"); step = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ref = KerasAdam([p0])
+    for it in range(3):
+        g = torch.randn(n, device="cuda") * 0.1
+        gk = g.clone()
+        L.check(lib.crackfl_adam_step(p.data_ptr(), gk.data_ptr(), m.data_ptr(), v.data_ptr(), step.data_ptr(), n, 1e-3, 0.9,
+                                      0.999, 1e-7, _st()))
+        ref.step([g])
+        torch.cuda.synchronize()
+        assert float(gk.abs().max()) == 0.0  # zero-grad fused
+    assert torch.allclose(p, p0, atol=1e-6, rtol=1e-5) and int(step.item()) == 3
+
+
+@pytest.mark.parametrize("payload_bf16,server_opt", [(0, 0), (1, 0), (0, 1)])
+def test_fedagg_single_gpu_vs_numpy(payload_bf16, server_opt):
+    """K local client arenas reduced by the fused kernel == NumPy weighted mean (fl_server.py:92-102 semantics)."""
+    from crackfl.parallel.device_agg import DeviceAggregator
+    from crackfl.parallel import fedavg as fa
+    from crackfl.models.spec import REFERENCE_SPEC as S
+    rng = np.random.default_rng(0)
+    K = 5
+    g0 = [rng.standard_normal(t.shape).astype(np.float32) for t in S.tensors]
+    ups = [[a + 0.01 * rng.standard_normal(a.shape).astype(np.float32) for a in g0] for _ in range(K)]
+    ns = [10, 20, 30, 40, 50]
+    if server_opt == 0:
+        strat = fa.FedAvg(weighted=True)
+    else:
+        strat = fa.FedAdam(trainable_mask=[t.trainable for t in S.tensors])
+    ref = strat.aggregate(g0, ups, ns)
+    agg = DeviceAggregator(S, strategy="fedavg_weighted" if server_opt == 0 else "fedadam",
+                           payload="bf16_delta" if payload_bf16 else "fp32", max_clients=K)
+    out = agg.aggregate(g0, ups, ns)
+    tol = 2e-3 if payload_bf16 else 1e-5
+    for a, b in zip(out, ref):
+        np.testing.assert_allclose(a, b, rtol=tol, atol=tol)
+
+
+@pytest.mark.parametrize("impl", ["simt", "tc"])
+def test_engine_matches_oracle(impl):
+    from crackfl.utils.check import engine_vs_oracle, format_report, worst
+    rep = engine_vs_oracle(B=4, H=64, W=64, conv_impl=impl)
+    txt = format_report(rep)
+    wf, wc = worst(rep)
+    assert abs(rep["loss"][0] - rep["loss"][1]) < 2e-2 * max(1.0, rep["loss"][1]), txt
+    assert wf < 5e-2, txt
+    assert wc > 0.98, txt
+    for k, v in rep["bn_running"].items():
+        assert v[0] < 2e-2 and v[1] < 2e-2, txt
+
+
+def test_engine_dice_loss_matches_oracle():
+    from crackfl.utils.check import engine_vs_oracle, format_report, worst
+    rep = engine_vs_oracle(B=2, H=32, W=32, conv_impl="simt", loss="bce_dice")
+    assert abs(rep["loss"][0] - rep["loss"][1]) < 2e-2 * max(1.0, rep["loss"][1]), format_report(rep)
+    assert worst(rep)[1] > 0.98, format_report(rep)
+
+
+def test_engine_training_reduces_loss_with_graph():
+    from crackfl.models.unet import UNetEngine
+    from crackfl.models.spec import REFERENCE_SPEC as S
+    from crackfl.data.generator import synth_crack_batch
+    eng = UNetEngine(S, 8, 64, 64, cuda_graph=True)
+    eng.load_weights(S.init_weights(0)); eng.reset_optimizer()
+    x, y = synth_crack_batch(8, 64, 64, 3)
+    losses = []
+    for i in range(30):
+        eng.reset_metrics()
+        eng.train_step(x, y)
+        losses.append(eng.read_metrics()["loss"])
+    assert np.isfinite(losses).all() and losses[-1] < 0.7 * losses[0], losses
+    eng.reset_metrics(); eng.eval_step(x, y)
+    assert np.isfinite(eng.read_metrics()["loss"])
+    p = eng.predict(x)
+    assert p.shape == (8, 64, 64) and float(p.min()) >= 0 and float(p.max()) <= 1
