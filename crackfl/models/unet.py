@@ -66,7 +66,7 @@ class UNetEngine:
             self.eval_prog = self._build_forward(training=False, with_mask=True, prob=False)
             self.pred_prog = self._build_forward(training=False, with_mask=False, prob=True)
         self._graphs: Dict[str, torch.cuda.CUDAGraph] = {}
-        self.launches_per_step = len(self.train_prog) + 1  # + adam tick
+        self.launches_per_step = len(self.train_prog) + 2  # + adam tick + metric accumulation
 
     # ------------------------------------------------------------------ allocation
     def _new(self, name: str, shape, dtype=torch.bfloat16) -> torch.Tensor:
@@ -310,6 +310,7 @@ class UNetEngine:
     def _build_train(self):
         lib, B, b = self.lib, self.B, self.b
         prog = self._build_forward(training=True, with_mask=True, prob=False)
+        self.n_fwd = len(prog)
         (conv0, bn0), encs, decs, head = self._layer_iter()
         ts = self.spec.tensors
         dl = self.dec[-1]
@@ -423,7 +424,8 @@ class UNetEngine:
         self.zero_region.zero_()
         self._run(prog)
         if accumulate:
-            self.metrics_total[:6] += self.zero_region[self.acc_off:self.acc_off + 6]
+            st = torch.cuda.current_stream(self.dev).cuda_stream
+            L.check(self.lib.crackfl_accum_small(self.metrics_total.data_ptr(), self._acc_ptr(), 6, st))
 
     def _exec(self, key: str, prog, accumulate: bool):
         with torch.cuda.device(self.dev):

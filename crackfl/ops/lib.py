@@ -59,12 +59,15 @@ _SIGS = {
     "crackfl_weight_prep": [vp, vp, vp, i32, vp],
     "crackfl_adam_step": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, vp],
     "crackfl_f32_to_bf16": [vp, vp, i64, vp],
+    "crackfl_accum_small": [vp, vp, i32, vp],
     "crackfl_publish_delta": [vp, vp, vp, i64, vp],
     "crackfl_fedagg": [C.POINTER(FedAggParams), i32, vp],
     "crackfl_ipc_export": [vp, vp],
     "crackfl_ipc_open": [vp, C.POINTER(vp)],
     "crackfl_ipc_close": [vp],
     "crackfl_enable_peer_access": [i32],
+    "crackfl_dev_malloc": [C.POINTER(vp), C.c_size_t],
+    "crackfl_dev_free": [vp],
 }
 
 

@@ -1,0 +1,311 @@
+"""On-box federation runtime: one process per GPU, K clients per GPU, fused in-kernel aggregation.
+
+This is the B200-native replacement of the reference's whole server/client exchange for clients that
+live on the same 8-GPU box:
+
+===========================================  =======================================================
+reference                                     here
+===========================================  =======================================================
+N gRPC uploads of pickled weights             each rank publishes ONE partial (weighted sum of its K
+(fl_client.py:61-65 -> fl_server.py:176-179)  local clients, kernel K14) in an IPC-exported arena
+NumPy mean on the server CPU                  shard owner pulls the G partials over NVLink with 128-bit
+(fl_server.py:92-102)                         loads inside ``crackfl_fedagg`` and updates its fp32 master shard
+N unicast downloads (fl_server.py:190,201)    the same kernel stores the new shard into every rank's
+                                              global arena (peer stores / multimem.st)
+count-to-N + 20 s polling (fl_client.py:141)  signal-pad barrier inside the kernel, with a spin timeout
+===========================================  =======================================================
+
+``torch.distributed`` (NCCL or Gloo) is used only to exchange the 64-byte IPC handles at start-up and
+for the max-over-ranks of timings.  On CPU (tests, Gloo) the aggregation falls back to an all_reduce
+of the flat arenas with the same API, so the host-side logic is exercised without a GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from ..io import weights as wio
+from ..models.spec import REFERENCE_SPEC, UNetSpec
+
+
+class RawCudaBuffer:
+    """cudaMalloc'd buffer (own allocation => IPC-exportable base pointer) viewable as a torch tensor."""
+
+    def __init__(self, lib, nbytes: int, ptr: Optional[int] = None, owner: bool = True):
+        self.lib, self.nbytes, self.owner = lib, nbytes, owner
+        if ptr is None:
+            out = C.c_void_p()
+            rc = lib.crackfl_dev_malloc(C.byref(out), nbytes)
+            if rc:
+                raise RuntimeError(f"cudaMalloc({nbytes}) failed: {rc}")
+            ptr = out.value
+        self.ptr = ptr
+
+    def tensor(self, dtype: torch.dtype, numel: int, device) -> torch.Tensor:
+        typestr = {torch.float32: "<f4", torch.bfloat16: "<u2", torch.uint32: "<u4", torch.int32: "<i4",
+                   torch.uint8: "|u1"}[dtype]
+
+        class _View:
+            pass
+        v = _View()
+        v.__cuda_array_interface__ = {"shape": (numel,), "typestr": typestr, "data": (self.ptr, False), "version": 3}
+        t = torch.as_tensor(v, device=device)
+        if dtype == torch.bfloat16:
+            t = t.view(torch.bfloat16)
+        t._crackfl_keepalive = self
+        return t
+
+    def export(self) -> bytes:
+        h = C.create_string_buffer(64)
+        rc = self.lib.crackfl_ipc_export(self.ptr, h)
+        if rc:
+            raise RuntimeError(f"cudaIpcGetMemHandle failed: {rc}")
+        return h.raw
+
+
+class OnBoxFederation:
+    """Per-rank handle of a federation whose clients all live on this box.
+
+    ``payload``: "fp32" (exact reference mean) or "bf16_delta" (partials travel as bf16 deltas against the
+    global model: half the NVLink bytes; the fp32 master keeps the accumulation exact to bf16 rounding
+    of the *update*, not of the weights).
+    """
+
+    def __init__(self, spec: UNetSpec = REFERENCE_SPEC, clients_per_gpu: int = 1, strategy: str = "fedavg",
+                 payload: str = "fp32", eta=1e-2, beta1=0.9, beta2=0.99, tau=1e-3, numel: Optional[int] = None,
+                 grid_blocks: int = 148):
+        self.spec = spec
+        self.n = int(numel if numel is not None else spec.arena_numel)
+        if self.n % 4:
+            raise ValueError("arena length must be a multiple of 4")
+        self.K = clients_per_gpu
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.strategy, self.payload = strategy, payload
+        self.server_opt = 1 if strategy == "fedadam" else 0
+        self.hp = (eta, beta1, beta2, tau)
+        self.cuda = torch.cuda.is_available()
+        self.epoch = 0
+        self.grid_blocks = grid_blocks
+        self.last_agg_ms = 0.0
+        if self.cuda:
+            self._init_cuda()
+        else:
+            self._init_cpu()
+
+    # ------------------------------------------------------------------ set-up
+    def _init_cpu(self):
+        n, K = self.n, self.K
+        self.updates = torch.zeros((K, n), dtype=torch.float32)
+        self.global_arena = torch.zeros(n, dtype=torch.float32)
+        self.master = torch.zeros(n, dtype=torch.float32)
+        self.m = torch.zeros(n, dtype=torch.float32)
+        self.v = torch.zeros(n, dtype=torch.float32)
+        self.trainable = torch.ones(n, dtype=torch.bool)
+        if self.n == self.spec.arena_numel:
+            for t in self.spec.tensors:
+                self.trainable[t.offset:t.offset + t.numel] = t.trainable
+
+    def _init_cuda(self):
+        from ..ops import lib as L
+        self.L, self.lib = L, L.get_lib()
+        n, K, world = self.n, self.K, self.world
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        pbytes = 2 if self.payload == "bf16_delta" else 4
+        self._raw = {"partial": RawCudaBuffer(self.lib, n * pbytes), "global": RawCudaBuffer(self.lib, n * 4),
+                     "pads": RawCudaBuffer(self.lib, 2 * L.MAX_RANKS * 4)}
+        self.partial = self._raw["partial"].tensor(torch.bfloat16 if pbytes == 2 else torch.float32, n, self.dev)
+        self.global_arena = self._raw["global"].tensor(torch.float32, n, self.dev)
+        self.updates = torch.zeros((K, n), dtype=torch.float32, device=self.dev)
+        self.master = torch.zeros(n, dtype=torch.float32, device=self.dev)
+        self.m = torch.zeros(n, dtype=torch.float32, device=self.dev)
+        self.v = torch.zeros(n, dtype=torch.float32, device=self.dev)
+        mask = np.ones(n, np.uint8)
+        if n == self.spec.arena_numel:
+            for t in self.spec.tensors:
+                mask[t.offset:t.offset + t.numel] = 1 if t.trainable else 0
+        self.trainable = torch.from_numpy(mask).to(self.dev)
+        self.local_sync = torch.zeros(2, dtype=torch.int32, device=self.dev)
+        self.error_flag = torch.zeros(1, dtype=torch.int32, device=self.dev)
+        # peer mapping
+        self.peer: Dict[str, List[int]] = {k: [0] * world for k in self._raw}
+        if world > 1:
+            handles = {k: b.export() for k, b in self._raw.items()}
+            gathered: List[Optional[dict]] = [None] * world
+            dist.all_gather_object(gathered, {"dev": torch.cuda.current_device(), "h": handles})
+            for r, info in enumerate(gathered):
+                for k in self._raw:
+                    if r == self.rank:
+                        self.peer[k][r] = self._raw[k].ptr
+                    else:
+                        out = C.c_void_p()
+                        rc = self.lib.crackfl_ipc_open(info["h"][k], C.byref(out))
+                        if rc:
+                            raise RuntimeError(f"cudaIpcOpenMemHandle(rank {r}, {k}) failed: {rc}")
+                        self.peer[k][r] = out.value
+            dist.barrier()
+        else:
+            for k in self._raw:
+                self.peer[k][0] = self._raw[k].ptr
+        # shard of this rank (multiple of 4 elements)
+        n4 = n // 4
+        per = (n4 + world - 1) // world
+        self.begin = min(n4, per * self.rank) * 4
+        self.end = min(n4, per * (self.rank + 1)) * 4
+
+    # ------------------------------------------------------------------ API
+    def set_global(self, flat: torch.Tensor):
+        """Install the initial global model on this rank (same values on every rank)."""
+        self.global_arena.copy_(flat.to(self.global_arena.device))
+        self.master.copy_(self.global_arena)
+
+    def publish(self, k: int, flat: torch.Tensor):
+        """Client k (local index) hands in its trained weights (device-to-device copy of the arena)."""
+        self.updates[k].copy_(flat)
+
+    def aggregate(self, num_samples_local: Sequence[float], weighted: bool = True) -> float:
+        """One FedAvg/FedAdam aggregation + broadcast.  Returns device time in ms (max over ranks)."""
+        ns = torch.tensor([float(x) for x in num_samples_local], dtype=torch.float64)
+        if not weighted:
+            ns = torch.ones_like(ns)
+        tot = ns.sum().clone()
+        if self.world > 1:
+            t = tot.to(self.dev) if self.cuda else tot
+            dist.all_reduce(t)
+            tot = t.cpu()
+        coef = (ns / float(tot)).to(torch.float32)
+        self.epoch += 1
+        if not self.cuda:
+            return self._aggregate_cpu(coef)
+        L, lib = self.L, self.lib
+        st = torch.cuda.current_stream(self.dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        # (K14) local pre-reduce of this GPU's K clients -> partial
+        p = L.FedAggParams()
+        K = self.K
+        for k in range(K):
+            p.client[k] = self.updates[k].data_ptr()
+            p.coef[k] = float(coef[k])
+        nc = K
+        if self.payload == "bf16_delta":
+            p.client[K] = self.global_arena.data_ptr()  # partial = sum c_k (w_k - w_global)
+            p.coef[K] = -float(coef.sum())
+            nc = K + 1
+        p.num_clients, p.num_out = nc, 1
+        p.out[0] = self.partial.data_ptr()
+        p.payload_bf16, p.out_bf16 = 0, 1 if self.payload == "bf16_delta" else 0
+        p.delta = p.server_opt = 0
+        p.master = p.m = p.v = p.trainable = p.mc_out = 0
+        p.begin, p.end = 0, self.n
+        p.rank, p.world, p.epoch = 0, 1, 1
+        p.error_flag = p.local_sync = 0
+        L.check(lib.crackfl_fedagg(C.byref(p), 148 * 4, st.cuda_stream), "fedagg pre-reduce")
+        # (K11-K13) cross-GPU reduce + server update + broadcast, one launch
+        q = L.FedAggParams()
+        for r in range(self.world):
+            q.client[r] = self.peer["partial"][r]
+            q.coef[r] = 1.0
+            q.out[r] = self.peer["global"][r]
+            q.pads[r] = self.peer["pads"][r]
+        q.num_clients = q.num_out = self.world
+        q.payload_bf16 = 1 if self.payload == "bf16_delta" else 0
+        q.out_bf16 = 0
+        q.delta = 1 if self.payload == "bf16_delta" else 0
+        q.server_opt = self.server_opt
+        q.eta, q.beta1, q.beta2, q.tau = self.hp
+        q.master, q.m, q.v = self.master.data_ptr(), self.m.data_ptr(), self.v.data_ptr()
+        q.trainable = self.trainable.data_ptr()
+        q.mc_out = 0
+        q.begin, q.end = self.begin, self.end
+        q.rank, q.world, q.epoch = self.rank, self.world, self.epoch
+        q.error_flag, q.local_sync = self.error_flag.data_ptr(), self.local_sync.data_ptr()
+        L.check(lib.crackfl_fedagg(C.byref(q), self.grid_blocks, st.cuda_stream), "fedagg")
+        e1.record(st)
+        st.synchronize()
+        if int(self.error_flag.item()) != 0:
+            raise RuntimeError(f"rank {self.rank}: aggregation barrier timed out (flag {int(self.error_flag.item())})")
+        ms = torch.tensor([e0.elapsed_time(e1)], device=self.dev)
+        if self.world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        self.last_agg_ms = float(ms.item())
+        return self.last_agg_ms
+
+    def _aggregate_cpu(self, coef: torch.Tensor) -> float:
+        import time
+        t0 = time.perf_counter()
+        acc = (self.updates * coef[:, None]).sum(0)
+        if self.world > 1:
+            dist.all_reduce(acc)
+        if self.server_opt:
+            eta, b1, b2, tau = self.hp
+            d = acc - self.master
+            tr = self.trainable
+            self.m[tr] = b1 * self.m[tr] + (1 - b1) * d[tr]
+            self.v[tr] = b2 * self.v[tr] + (1 - b2) * d[tr] * d[tr]
+            new = acc.clone()
+            new[tr] = self.master[tr] + eta * self.m[tr] / (self.v[tr].sqrt() + tau)
+            acc = new
+        self.master.copy_(acc)
+        self.global_arena.copy_(acc)
+        self.last_agg_ms = (time.perf_counter() - t0) * 1e3
+        return self.last_agg_ms
+
+    def global_weights(self) -> List[np.ndarray]:
+        return wio.unflatten(self.global_arena.detach().cpu().numpy(), self.spec)
+
+
+def init_distributed(backend: Optional[str] = None):
+    """Initialise torch.distributed from the torchrun environment (no-op for a single process)."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world <= 1 or dist.is_initialized():
+        return
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29511")
+    if backend is None:
+        backend = "nccl" if torch.cuda.is_available() else "gloo"
+    if torch.cuda.is_available():
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+    dist.init_process_group(backend=backend)
+
+
+def run_federated_onbox(cfg, rounds: int, clients_per_gpu: int = 1, strategy: str = "fedavg", payload: str = "fp32",
+                        spec: Optional[UNetSpec] = None, steps_per_round: Optional[int] = None, log=print) -> dict:
+    """Full on-box federation: every rank hosts ``clients_per_gpu`` clients that fit locally and aggregate in-kernel.
+
+    Returns {"rounds": [...per-round records...], "weights": final global weights (rank 0)}.
+    """
+    from ..trainer import LocalTrainer, make_backend, spec_from_config
+    from ..data.generator import make_datasets
+    spec = spec or spec_from_config(cfg)
+    fed = OnBoxFederation(spec, clients_per_gpu, strategy, payload, cfg.server.fedadam_eta, cfg.server.fedadam_beta1,
+                          cfg.server.fedadam_beta2, cfg.server.fedadam_tau)
+    backend = make_backend(cfg, spec)
+    init = torch.from_numpy(wio.flatten(spec.init_weights(cfg.server.seed), spec))
+    fed.set_global(init)
+    trainers = []
+    for k in range(clients_per_gpu):
+        cid = fed.rank * clients_per_gpu + k
+        tr, va = make_datasets(cfg, cid)
+        trainers.append(LocalTrainer(cfg, tr, va, spec=spec, backend=backend, client_index=cid, log=lambda s: None))
+    records = []
+    for rnd in range(1, rounds + 1):
+        ns, metrics = [], []
+        for k, t in enumerate(trainers):
+            w = fed.global_weights()
+            w2, m = t.fit(w, rnd)
+            fed.publish(k, torch.from_numpy(wio.flatten(w2, spec)).to(fed.updates.device))
+            ns.append(m["num_samples"]); metrics.append(m)
+        ms = fed.aggregate(ns, weighted=(strategy != "fedavg"))
+        rec = {"round": rnd, "aggregate_ms": ms, "loss": float(np.mean([m["loss"] for m in metrics])),
+               "accuracy": float(np.mean([m["accuracy"] for m in metrics])),
+               "images_per_sec_per_client": float(np.mean([m["images_per_sec"] for m in metrics]))}
+        records.append(rec)
+        if fed.rank == 0:
+            log(f"[onbox] round {rnd}: loss {rec['loss']:.4f} acc {rec['accuracy']:.4f} aggregate {ms:.3f} ms")
+    return {"rounds": records, "weights": fed.global_weights() if fed.rank == 0 else None}

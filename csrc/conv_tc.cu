@@ -1,0 +1,592 @@
+// tcgen05 / TMEM / TMA implicit-GEMM convolution kernels for sm_100a  (SURVEY section 8 rows K1-K3).
+//
+//   conv_tc_fwd : Y[p][n] = sum_{t,c} X[p + off(t)][c] * Wk[n][t*Cin + c]  (+bias, +add, BN sum/sumsq epilogue)
+//                 3x3 stride-1 "same" conv == Keras Conv2DTranspose(3, stride 1, same) with flipped taps
+//                 (client_fit_model.py:129,133), every 1x1 conv (pointwise of SeparableConv2D :109,113 and
+//                 the residual projections :119,140) and, with the transposed operand, all their dgrads.
+//   wgrad_tc    : dW[t][ci][co] += sum_p X[p + off(t)][ci] * dY[p][co]      (fp32 atomics into the Keras-layout arena)
+//
+// Structure (one CTA = one 128-pixel x BN-channel output tile, 192 threads):
+//   warp 0   : TMA producer.  The 128 pixels are a TB x TH x TW box of the NHWC tensor; for tap t the box is
+//              simply shifted by (dh,dw) and TMA's out-of-bounds zero fill IS the "same" padding, so the
+//              im2col matrix is never built.  A and B tiles land in shared memory in the 128B/64B-swizzled
+//              K-major layout that tcgen05 reads directly.  Multi-stage ring, mbarrier full/empty pairs.
+//   warp 1   : allocates TMEM, then one elected lane issues tcgen05.mma (M=128, N=BN, K=16) per 32 bytes of K,
+//              accumulating in TMEM; tcgen05.commit releases smem stages and finally signals the epilogue.
+//   warps 2-5: epilogue.  tcgen05.ld 32 lanes x 32 columns per warp, +bias, +residual, bf16 pack, 64-byte
+//              contiguous stores per thread, and (optionally) the BatchNorm per-channel sum / sum-of-squares of
+//              the *stored* values via a 31-shuffle recursive-halving transpose-reduce + one atomic per column.
+// wgrad uses the same TMA boxes but feeds them as MN-major operands (the pixel axis is K), pairs/quadruples
+// (tap, channel-chunk) blocks to fill M=128 and splits the pixel axis over CTAs.
+#include <cuda.h>
+#include <cstring>
+#include <mutex>
+#include <unordered_map>
+#include <string>
+
+#include "common.cuh"
+#include "../include/crackfl.h"
+
+namespace {
+
+// ----------------------------------------------------------------------------------------------------------
+// PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  const long long t0 = clock64();
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) break;
+    if (clock64() - t0 > 4000000000LL) __trap();  // a broken pipeline must not hang the GPU
+  }
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tm)) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t v[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
+//   [0,14) start>>4 | [16,30) LBO>>4 | [32,46) SBO>>4 | [46,48) version=1 | [49,52) base_offset | [61,64) layout
+// layout: 2 = SWIZZLE_128B, 4 = SWIZZLE_64B.
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)layout << 61;
+  return d;
+}
+
+// Instruction descriptor for kind::f16, bf16 x bf16 -> fp32 (cute::UMMA::InstrDescriptor bit layout)
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, int b_mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+struct TileGeom {
+  int TW, TH, TB;           // pixel box, TW*TH*TB == 128
+  int tiles_w, tiles_h, tiles_b;
+};
+
+struct ConvArgs {
+  const float* bias;
+  const __nv_bfloat16* add;
+  __nv_bfloat16* Y;
+  float* stats;
+  int B, H, W, Cin, N, taps;
+  int BN, kc, stages;
+  uint32_t layout, sbo;     // swizzle mode of A/B tiles (2: 128B, 4: 64B) and its 8-row group stride
+  TileGeom g;
+};
+
+// Column sums of a 32(lanes) x 32(columns) register tile via recursive halving: after the 5 exchange steps
+// lane L holds the total of column L.  31 shuffles instead of 160.
+__device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    const bool up = (lane & o) != 0;
+#pragma unroll
+    for (int j = 0; j < o; ++j) {
+      const float send = up ? v[j] : v[j + o];
+      const float keep = up ? v[j + o] : v[j];
+      v[j] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+    }
+  }
+  return v[0];
+}
+
+__global__ void __launch_bounds__(192) conv_tc_fwd_k(const __grid_constant__ CUtensorMap tmA,
+                                                     const __grid_constant__ CUtensorMap tmB, const ConvArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t a_bytes = 128u * a.kc * 2u, b_bytes = (uint32_t)a.BN * a.kc * 2u;
+  const uint32_t stage_bytes = a_bytes + b_bytes;
+  const uint32_t bar_base = base + a.stages * stage_bytes;  // full[s], empty[s], tmem_full, tmem_ptr
+  const uint32_t full0 = bar_base, empty0 = bar_base + 8u * a.stages, tfull = bar_base + 16u * a.stages;
+  const uint32_t tptr = tfull + 8u;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // tile coordinates
+  int tile = blockIdx.x;
+  const int tw_i = tile % a.g.tiles_w; tile /= a.g.tiles_w;
+  const int th_i = tile % a.g.tiles_h; tile /= a.g.tiles_h;
+  const int tb_i = tile;
+  const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tb_i * a.g.TB;
+  const int n0 = blockIdx.y * a.BN;
+  const int kchunks = a.Cin / a.kc;
+  const int iters = a.taps * kchunks;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < a.stages; ++s) {
+      mbar_init(full0 + 8u * s, 1);
+      mbar_init(empty0 + 8u * s, 1);
+    }
+    mbar_init(tfull, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) tmem_alloc(tptr, (uint32_t)(a.BN < 32 ? 32 : a.BN));
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tptr));
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int it = 0; it < iters; ++it) {
+        const int s = it % a.stages;
+        const uint32_t ph = (uint32_t)(it / a.stages) & 1u;
+        mbar_wait(empty0 + 8u * s, ph ^ 1u);
+        const int t = it / kchunks, c = it % kchunks;
+        const int dh = a.taps == 9 ? t / 3 - 1 : 0, dw = a.taps == 9 ? t % 3 - 1 : 0;
+        const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
+        mbar_expect_tx(full0 + 8u * s, stage_bytes);
+        tma_load_4d(sa, &tmA, full0 + 8u * s, c * a.kc, w0 + dw, h0 + dh, b0);
+        tma_load_2d(sb, &tmB, full0 + 8u * s, t * a.Cin + c * a.kc, n0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(128, a.BN, 0, 0);
+      for (int it = 0; it < iters; ++it) {
+        const int s = it % a.stages;
+        const uint32_t ph = (uint32_t)(it / a.stages) & 1u;
+        mbar_wait(full0 + 8u * s, ph);
+        tc_fence_after();
+        const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
+        const uint64_t ad = make_desc(sa, 16, a.sbo, a.layout);
+        const uint64_t bd = make_desc(sb, 16, a.sbo, a.layout);
+        for (int k = 0; k < a.kc / 16; ++k)  // +32 bytes of K per MMA: start-address field += 2
+          umma_f16(tmem_base, ad + 2u * k, bd + 2u * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+        umma_commit(empty0 + 8u * s);
+      }
+      umma_commit(tfull);
+    }
+  } else {
+    // ---- epilogue warps: TMEM lane quarter = warp % 4
+    const int q = warp & 3;
+    const int r = q * 32 + lane;  // accumulator row == pixel index inside the box (tw fastest)
+    const int tw = r % a.g.TW, th = (r / a.g.TW) % a.g.TH, tb = r / (a.g.TW * a.g.TH);
+    const int pw = w0 + tw, ph_ = h0 + th, pb = b0 + tb;
+    const bool valid = pw < a.W && ph_ < a.H && pb < a.B;
+    const long pix = ((long)pb * a.H + ph_) * a.W + pw;
+    mbar_wait(tfull, 0);
+    tc_fence_after();
+    for (int c0 = 0; c0 < a.BN; c0 += 32) {
+      uint32_t raw[32];
+      tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, raw);
+      float v[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
+      if (a.bias) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const float4 bb = __ldg(reinterpret_cast<const float4*>(a.bias + n0 + c0 + j));
+          v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
+        }
+      }
+      if (a.add && valid) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+          float t8[8];
+          ck::unpack8(ck::ldg16(a.add + pix * a.N + n0 + c0 + j), t8);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) v[j + e] += t8[e];
+        }
+      }
+      if (valid) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) ck::stg16(a.Y + pix * a.N + n0 + c0 + j, ck::pack8(&v[j]));
+      }
+      if (a.stats) {
+        float s1[32], s2[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          // statistics of the value as stored (bf16-rounded), zero for masked pixels
+          const float x = valid ? __bfloat162float(__float2bfloat16_rn(v[j])) : 0.f;
+          s1[j] = x;
+          s2[j] = x * x;
+        }
+        const float t1 = warp_colsum32(s1, lane);
+        const float t2 = warp_colsum32(s2, lane);
+        atomicAdd(a.stats + n0 + c0 + lane, t1);
+        atomicAdd(a.stats + a.N + n0 + c0 + lane, t2);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, (uint32_t)(a.BN < 32 ? 32 : a.BN));
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------------
+struct WgradArgs {
+  float* dW;
+  long s_tap, s_ci, s_co;
+  int B, H, W, Cin, Cout, taps;
+  int cw, nw, BN, mblk, nblk;     // channel width of one A box / one B box; boxes per operand
+  int total_blocks, ntiles, tiles_per_split, stages;
+  uint32_t layoutA, sboA, layoutB, sboB;
+  TileGeom g;
+};
+
+__global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtensorMap tmX,
+                                                  const __grid_constant__ CUtensorMap tmDY, const WgradArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t ablk_bytes = 128u * a.cw * 2u, bblk_bytes = 128u * a.nw * 2u;
+  const uint32_t a_bytes = ablk_bytes * a.mblk, b_bytes = bblk_bytes * a.nblk;
+  const uint32_t stage_bytes = a_bytes + b_bytes;
+  const uint32_t bar_base = base + a.stages * stage_bytes;
+  const uint32_t full0 = bar_base, empty0 = bar_base + 8u * a.stages, tfull = bar_base + 16u * a.stages;
+  const uint32_t tptr = tfull + 8u;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int group = blockIdx.x;
+  const int n0 = blockIdx.y * a.BN;
+  const int tile_begin = blockIdx.z * a.tiles_per_split;
+  const int tile_end = min(a.ntiles, tile_begin + a.tiles_per_split);
+  const int iters = tile_end - tile_begin;
+  const int cchunks = a.Cin / a.cw;
+  const uint32_t ncols = (uint32_t)(a.BN < 32 ? 32 : a.BN);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < a.stages; ++s) {
+      mbar_init(full0 + 8u * s, 1);
+      mbar_init(empty0 + 8u * s, 1);
+    }
+    mbar_init(tfull, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    tma_prefetch_desc(&tmX);
+    tma_prefetch_desc(&tmDY);
+  }
+  if (warp == 1) tmem_alloc(tptr, ncols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tptr));
+
+  if (iters > 0) {
+    if (warp == 0) {
+      if (lane == 0) {
+        for (int it = 0; it < iters; ++it) {
+          const int s = it % a.stages;
+          const uint32_t ph = (uint32_t)(it / a.stages) & 1u;
+          mbar_wait(empty0 + 8u * s, ph ^ 1u);
+          int tile = tile_begin + it;
+          const int tw_i = tile % a.g.tiles_w; tile /= a.g.tiles_w;
+          const int th_i = tile % a.g.tiles_h; tile /= a.g.tiles_h;
+          const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tile * a.g.TB;
+          const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
+          mbar_expect_tx(full0 + 8u * s, stage_bytes);
+          for (int m = 0; m < a.mblk; ++m) {
+            const int blk = min(group * a.mblk + m, a.total_blocks - 1);
+            const int t = blk / cchunks, c = blk % cchunks;
+            const int dh = a.taps == 9 ? t / 3 - 1 : 0, dw = a.taps == 9 ? t % 3 - 1 : 0;
+            tma_load_4d(sa + m * ablk_bytes, &tmX, full0 + 8u * s, c * a.cw, w0 + dw, h0 + dh, b0);
+          }
+          for (int nb = 0; nb < a.nblk; ++nb)
+            tma_load_4d(sb + nb * bblk_bytes, &tmDY, full0 + 8u * s, n0 + nb * a.nw, w0, h0, b0);
+        }
+      }
+    } else if (warp == 1) {
+      if (lane == 0) {
+        const uint32_t idesc = make_idesc(128, a.BN, 1, 1);
+        for (int it = 0; it < iters; ++it) {
+          const int s = it % a.stages;
+          const uint32_t ph = (uint32_t)(it / a.stages) & 1u;
+          mbar_wait(full0 + 8u * s, ph);
+          tc_fence_after();
+          const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
+          for (int k = 0; k < 8; ++k) {  // 16 pixels (K) per MMA = 16 smem rows
+            const uint64_t ad = make_desc(sa + k * 16u * a.cw * 2u, ablk_bytes, a.sboA, a.layoutA);
+            const uint64_t bd = make_desc(sb + k * 16u * a.nw * 2u, bblk_bytes, a.sboB, a.layoutB);
+            umma_f16(tmem_base, ad, bd, idesc, (it > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(empty0 + 8u * s);
+        }
+        umma_commit(tfull);
+      }
+    } else {
+      const int q = warp & 3;
+      const int r = q * 32 + lane;  // accumulator row = (block m, channel within block)
+      const int m = r / a.cw;
+      const int blk = group * a.mblk + m;
+      const bool valid = blk < a.total_blocks;
+      const int bc = valid ? blk : 0;
+      const int t = bc / cchunks, ci = (bc % cchunks) * a.cw + (r % a.cw);
+      float* dst = a.dW + (long)t * a.s_tap + (long)ci * a.s_ci;
+      mbar_wait(tfull, 0);
+      tc_fence_after();
+      for (int c0 = 0; c0 < a.BN; c0 += 32) {
+        uint32_t raw[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, raw);
+        if (valid) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) atomicAdd(dst + (long)(n0 + c0 + j) * a.s_co, __uint_as_float(raw[j]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, ncols);
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------------
+// host side: tensor-map cache + geometry
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (PFN_encodeTiled)p;
+  });
+  return fn;
+}
+
+struct MapKey {
+  const void* ptr;
+  int d[4];
+  int box[4];
+  int swz;
+  bool operator==(const MapKey& o) const { return memcmp(this, &o, sizeof(MapKey)) == 0; }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    std::string s(reinterpret_cast<const char*>(&k), sizeof(MapKey));
+    return std::hash<std::string>()(s);
+  }
+};
+std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
+std::mutex g_maps_mu;
+
+// bf16 tensor with `rank` dims (innermost first) tightly packed; box per dim; swizzle 128B or 64B.
+int get_map(const void* ptr, int rank, const int* dims, const int* box, int swz_bytes, CUtensorMap* out) {
+  MapKey k;
+  memset(&k, 0, sizeof(k));
+  k.ptr = ptr;
+  for (int i = 0; i < rank; ++i) { k.d[i] = dims[i]; k.box[i] = box[i]; }
+  k.swz = swz_bytes * 8 + rank;
+  std::lock_guard<std::mutex> lk(g_maps_mu);
+  auto it = g_maps.find(k);
+  if (it != g_maps.end()) { *out = it->second; return 0; }
+  PFN_encodeTiled enc = get_encode();
+  if (!enc) return (int)cudaErrorNotSupported;
+  cuuint64_t gdim[4], gstr[3];
+  cuuint32_t bx[4], es[4];
+  cuuint64_t stride = 2;
+  for (int i = 0; i < rank; ++i) {
+    gdim[i] = (cuuint64_t)dims[i];
+    bx[i] = (cuuint32_t)box[i];
+    es[i] = 1;
+    stride *= (cuuint64_t)dims[i];
+    if (i < rank - 1) gstr[i] = stride;
+  }
+  CUtensorMap tm;
+  CUresult r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), gdim, gstr, bx, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swz_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return 10000 + (int)r;
+  g_maps[k] = tm;
+  *out = tm;
+  return 0;
+}
+
+int pick(int extent, int maxv) {  // power of two in {4..maxv} minimising padded waste, larger wins ties
+  int best = 4;
+  long bestw = -1;
+  for (int v = maxv; v >= 4; v >>= 1) {
+    const long padded = (long)((extent + v - 1) / v) * v;
+    if (bestw < 0 || padded < bestw) { bestw = padded; best = v; }
+  }
+  return best;
+}
+
+TileGeom make_geom(int B, int H, int W) {
+  TileGeom g;
+  g.TW = pick(W, 16);
+  int rest = 128 / g.TW;
+  g.TH = 1;
+  if (H >= 2) {
+    int v = pick(H, rest < 4 ? 4 : rest);
+    if (v > rest) v = rest;
+    g.TH = v;
+  }
+  g.TB = 128 / (g.TW * g.TH);
+  g.tiles_w = (W + g.TW - 1) / g.TW;
+  g.tiles_h = (H + g.TH - 1) / g.TH;
+  g.tiles_b = (B + g.TB - 1) / g.TB;
+  return g;
+}
+
+}  // namespace
+
+extern "C" {
+
+int crackfl_tc_selftest_supported(void) { return get_encode() ? 1 : 0; }
+
+int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const void* add, void* Y, float* stats, int B, int H,
+                        int W, int Cin, int N, int taps, cudaStream_t st) {
+  if (Cin % 32 || N % 32 || (taps != 1 && taps != 9)) return (int)cudaErrorInvalidValue;
+  ConvArgs a;
+  a.bias = bias; a.add = (const __nv_bfloat16*)add; a.Y = (__nv_bfloat16*)Y; a.stats = stats;
+  a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.N = N; a.taps = taps;
+  a.BN = N > 128 ? 128 : N;
+  if (N % a.BN) return (int)cudaErrorInvalidValue;
+  a.kc = (Cin % 64 == 0) ? 64 : 32;
+  a.layout = a.kc == 64 ? 2u : 4u;
+  a.sbo = a.kc == 64 ? 1024u : 512u;
+  a.g = make_geom(B, H, W);
+  const int iters = taps * (Cin / a.kc);
+  const uint32_t stage_bytes = 128u * a.kc * 2u + (uint32_t)a.BN * a.kc * 2u;
+  int stages = (int)(98304u / stage_bytes);
+  if (stages > 6) stages = 6;
+  if (stages > iters) stages = iters;
+  if (stages < 1) stages = 1;
+  a.stages = stages;
+  const size_t smem = (size_t)stages * stage_bytes + 1024 + 256;
+  CUtensorMap tmA, tmB;
+  const int dA[4] = {Cin, W, H, B}, bA[4] = {a.kc, a.g.TW, a.g.TH, a.g.TB};
+  int rc = get_map(X, 4, dA, bA, a.kc * 2, &tmA);
+  if (rc) return rc;
+  const int dB[2] = {taps * Cin, N}, bB[2] = {a.kc, a.BN};
+  rc = get_map(Wk, 2, dB, bB, a.kc * 2, &tmB);
+  if (rc) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_fwd_k, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return (int)e;
+    attr_set = true;
+  }
+  dim3 grid(a.g.tiles_w * a.g.tiles_h * a.g.tiles_b, N / a.BN);
+  conv_tc_fwd_k<<<grid, 192, smem, st>>>(tmA, tmB, a);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_wgrad_tc(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps, long s_tap,
+                     long s_ci, long s_co, cudaStream_t st) {
+  if (Cin % 32 || Cout % 32 || (taps != 1 && taps != 9)) return (int)cudaErrorInvalidValue;
+  WgradArgs a;
+  a.dW = dW; a.s_tap = s_tap; a.s_ci = s_ci; a.s_co = s_co;
+  a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.Cout = Cout; a.taps = taps;
+  a.cw = (Cin % 64 == 0) ? 64 : 32;
+  a.nw = (Cout % 64 == 0) ? 64 : 32;
+  a.BN = Cout > 128 ? 128 : Cout;
+  if (Cout % a.BN) return (int)cudaErrorInvalidValue;
+  a.mblk = 128 / a.cw;
+  a.nblk = a.BN / a.nw;
+  a.layoutA = a.cw == 64 ? 2u : 4u; a.sboA = a.cw == 64 ? 1024u : 512u;
+  a.layoutB = a.nw == 64 ? 2u : 4u; a.sboB = a.nw == 64 ? 1024u : 512u;
+  a.g = make_geom(B, H, W);
+  a.total_blocks = taps * (Cin / a.cw);
+  const int groups = (a.total_blocks + a.mblk - 1) / a.mblk;
+  const int ntn = Cout / a.BN;
+  a.ntiles = a.g.tiles_w * a.g.tiles_h * a.g.tiles_b;
+  int splits = (148 * 3 + groups * ntn - 1) / (groups * ntn);
+  if (splits > a.ntiles) splits = a.ntiles;
+  if (splits < 1) splits = 1;
+  a.tiles_per_split = (a.ntiles + splits - 1) / splits;
+  splits = (a.ntiles + a.tiles_per_split - 1) / a.tiles_per_split;
+  const uint32_t stage_bytes = 128u * 128u * 2u + 128u * (uint32_t)a.BN * 2u;
+  int stages = (int)(196608u / stage_bytes);
+  if (stages > 4) stages = 4;
+  if (stages > a.tiles_per_split) stages = a.tiles_per_split;
+  if (stages < 1) stages = 1;
+  a.stages = stages;
+  const size_t smem = (size_t)stages * stage_bytes + 1024 + 256;
+  CUtensorMap tmX, tmDY;
+  const int dX[4] = {Cin, W, H, B}, bX[4] = {a.cw, a.g.TW, a.g.TH, a.g.TB};
+  int rc = get_map(X, 4, dX, bX, a.cw * 2, &tmX);
+  if (rc) return rc;
+  const int dD[4] = {Cout, W, H, B}, bD[4] = {a.nw, a.g.TW, a.g.TH, a.g.TB};
+  rc = get_map(dY, 4, dD, bD, a.nw * 2, &tmDY);
+  if (rc) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(wgrad_tc_k, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return (int)e;
+    attr_set = true;
+  }
+  dim3 grid(groups, ntn, splits);
+  wgrad_tc_k<<<grid, 192, smem, st>>>(tmX, tmDY, a);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

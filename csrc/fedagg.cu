@@ -198,6 +198,14 @@ int crackfl_ipc_open(const void* handle64, void** dev_ptr_out) {
 
 int crackfl_ipc_close(void* dev_ptr) { return (int)cudaIpcCloseMemHandle(dev_ptr); }
 
+int crackfl_dev_malloc(void** out, size_t bytes) {
+  cudaError_t e = cudaMalloc(out, bytes);
+  if (e == cudaSuccess) e = cudaMemset(*out, 0, bytes);
+  return (int)e;
+}
+
+int crackfl_dev_free(void* p) { return (int)cudaFree(p); }
+
 int crackfl_enable_peer_access(int peer_device) {
   cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
   if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return 0; }

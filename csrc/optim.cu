@@ -62,9 +62,20 @@ __global__ void __launch_bounds__(256) publish_delta_k(const float* __restrict__
     out[i] = __float2bfloat16_rn(local[i] - global[i]);
 }
 
+__global__ void accum_k(float* __restrict__ total, const float* __restrict__ step, int n) {
+  if (threadIdx.x < n) total[threadIdx.x] += step[threadIdx.x];
+}
+
 }  // namespace
 
 extern "C" {
+
+int crackfl_accum_small(float* total, const float* step, int n, cudaStream_t st) {
+  if (n > 32) return (int)cudaErrorInvalidValue;
+  accum_k<<<1, 32, 0, st>>>(total, step, n);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
 
 int crackfl_publish_delta(const float* local, const float* global, void* out_bf16, long n, cudaStream_t st) {
   long blocks = (n + 255) / 256;

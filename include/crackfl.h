@@ -94,6 +94,8 @@ int crackfl_weight_prep(const float* arena, void* ops_bf16, const crackfl_prep_d
 int crackfl_adam_step(float* p, float* g, float* m, float* v, int* step_dev, long n, float lr, float b1, float b2, float eps,
                       cudaStream_t stream);
 int crackfl_f32_to_bf16(const float* in, void* out, long n, cudaStream_t stream);
+/* total[i] += step[i], i < n <= 32 (per-epoch metric accumulation of the per-step loss/accuracy sums) */
+int crackfl_accum_small(float* total, const float* step, int n, cudaStream_t stream);
 /* staging of a client update as a bf16 delta against the global model (ref: fl_client.py:61-65 upload) */
 int crackfl_publish_delta(const float* local, const float* global, void* out_bf16, long n, cudaStream_t stream);
 
@@ -127,6 +129,9 @@ int crackfl_ipc_export(void* dev_ptr, void* handle_out64);
 int crackfl_ipc_open(const void* handle64, void** dev_ptr_out);
 int crackfl_ipc_close(void* dev_ptr);
 int crackfl_enable_peer_access(int peer_device);
+/* whole-allocation device buffers (zero-filled) whose base address can be exported with crackfl_ipc_export */
+int crackfl_dev_malloc(void** out, size_t bytes);
+int crackfl_dev_free(void* p);
 
 #ifdef __cplusplus
 }

@@ -17,3 +17,17 @@ for impl in impls:
         print(hdr); print(txt)
         with open(f"gpurun_out/check_engine_{impl}.txt", "a") as f:
             f.write(hdr + "\n" + txt + "\n")
+
+from crackfl.utils.check import directional_fd_check, bf16_oracle_noise
+try:
+    fd = directional_fd_check(conv_impl=impls[0])
+    noise = bf16_oracle_noise()
+    txt = "-- directional finite differences (engine loss along engine gradient)\n" + "\n".join(
+        f"  {k:44s} |g| {v['engine_|g|']:.4e}  fd {v['fd_slope']:.4e}  oracle d.g {v['oracle_d.g']:.4e}" for k, v in fd.items())
+    txt += "\n-- plain-PyTorch bf16 vs fp32 gradient cosine (noise floor of the comparison)\n" + "\n".join(
+        f"  {k:44s} {v:.5f}" for k, v in noise.items())
+except Exception:
+    txt = traceback.format_exc()
+print(txt)
+with open(f"gpurun_out/check_engine_{impls[0]}.txt", "a") as f:
+    f.write(txt + "\n")
