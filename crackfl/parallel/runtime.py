@@ -81,6 +81,7 @@ class OnBoxFederation:
                  grid_blocks: int = 148):
         self.spec = spec
         self.n = int(numel if numel is not None else spec.arena_numel)
+        self.mask_from_spec = numel is None  # synthetic sizes (bandwidth sweeps) treat every element as trainable
         if self.n % 4:
             raise ValueError("arena length must be a multiple of 4")
         self.K = clients_per_gpu
@@ -107,7 +108,7 @@ class OnBoxFederation:
         self.m = torch.zeros(n, dtype=torch.float32)
         self.v = torch.zeros(n, dtype=torch.float32)
         self.trainable = torch.ones(n, dtype=torch.bool)
-        if self.n == self.spec.arena_numel:
+        if self.mask_from_spec:
             for t in self.spec.tensors:
                 self.trainable[t.offset:t.offset + t.numel] = t.trainable
 
@@ -126,7 +127,7 @@ class OnBoxFederation:
         self.m = torch.zeros(n, dtype=torch.float32, device=self.dev)
         self.v = torch.zeros(n, dtype=torch.float32, device=self.dev)
         mask = np.ones(n, np.uint8)
-        if n == self.spec.arena_numel:
+        if self.mask_from_spec:
             for t in self.spec.tensors:
                 mask[t.offset:t.offset + t.numel] = 1 if t.trainable else 0
         self.trainable = torch.from_numpy(mask).to(self.dev)
