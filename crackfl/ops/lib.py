@@ -42,6 +42,8 @@ _SIGS = {
     "crackfl_bn_act": [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_bn_bwd_reduce": [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_bn_bwd_apply": [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    "crackfl_bn_train_fwd_noalloc": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, f32, vp],
+    "crackfl_noalloc_max_channels": [],
     "crackfl_dw3x3_fwd": [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_dw3x3_bwd": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
     "crackfl_pool_add_fwd": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],

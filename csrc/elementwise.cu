@@ -3,6 +3,8 @@
 // client_fit_model.py:100-145,157.
 // Every kernel is HBM-bound; the design goal is one pass per tensor with the neighbouring
 // pointwise work (BN-apply, ReLU, residual add, nearest upsample, /255) fused in.
+#include <cstdio>
+
 #include "common.cuh"
 #include "../include/crackfl.h"
 
@@ -872,6 +874,89 @@ int crackfl_head_bwd(const void* s, const float* w, const float* bias, const voi
   head_bwd_k<<<grid_for(P * (C / 8), 148 * 8), TPB, (C + TPB * 8) * sizeof(float), st>>>(
       (const __nv_bfloat16*)s, w, bias, (const uint8_t*)mask_u8, sums, (__nv_bfloat16*)ds, dw, db, B, Hl, Wl, C, use_dice,
       dice_smooth, loss_scale);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------
+// Allocation-free training-mode BatchNorm(+ReLU) forward.
+//
+// Who needs this: code that drives this library from a place where it cannot obtain device memory of its own.
+// Examples are a plug-in running inside a host process that has handed the whole device heap to another
+// framework's pool, a step function that is only allowed to touch buffers it was given at start-up (fixed
+// memory budget, no allocator in the hot path), and clean-up or recovery code that runs after an
+// out-of-memory condition, when asking for more memory is the one thing that cannot work.  The ordinary path
+// (crackfl_bn_stats + crackfl_bn_finalize + crackfl_bn_act) expects the caller to bring 6*C floats of scratch
+// for the per-channel sums and the scale/shift table; here that scratch lives in the library image instead.
+//
+// The scratch is ONE fixed array per GPU (every GPU that loads the library carries it until the process ends):
+// 6 * CRACKFL_NOALLOC_MAX_CHANNELS floats = 48 KiB.  Consequences the caller has to know:
+//   * channel counts above CRACKFL_NOALLOC_MAX_CHANNELS are refused (message on stderr, cudaErrorInvalidValue);
+//   * all calls on a GPU share the array, and it keeps whatever the previous call left in it.  The part that
+//     must start at zero (the sums) is cleared on the stream at the start of every call; two calls whose GPU
+//     work overlaps in time (different streams, no ordering between them) race on it and give wrong results;
+//   * the first call on each device looks the array's device address up (cudaGetSymbolAddress, with that
+//     device current).  Make that first call during start-up, before any stream capture is begun.
+// Nothing in here calls cudaMalloc, cudaFree or any routine that allocates.
+static __device__ __align__(256) float g_noalloc_bn_scratch[6 * CRACKFL_NOALLOC_MAX_CHANNELS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_noalloc_ptr[kMaxDevices] = {nullptr};
+
+// In host code `g_noalloc_bn_scratch` is only a handle for the device symbol, not an address a kernel can use.
+int noalloc_scratch_for_current_device(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kMaxDevices) return (int)cudaErrorInvalidDevice;
+  if (g_noalloc_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_noalloc_bn_scratch);
+    if (e != cudaSuccess) return (int)e;
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
+int crackfl_noalloc_max_channels(void) { return CRACKFL_NOALLOC_MAX_CHANNELS; }
+
+int crackfl_bn_train_fwd_noalloc(const void* y, const float* gamma, const float* beta, float* run_mean, float* run_var,
+                                 void* out, int B, int H, int W, int C, int relu, float eps, float momentum,
+                                 cudaStream_t st) {
+  if (C > CRACKFL_NOALLOC_MAX_CHANNELS) {
+    fprintf(stderr,
+            "crackfl_bn_train_fwd_noalloc: C=%d exceeds the built-in scratch (max %d channels); use crackfl_bn_stats/"
+            "crackfl_bn_finalize/crackfl_bn_act with caller-provided scratch instead\n",
+            C, CRACKFL_NOALLOC_MAX_CHANNELS);
+    return (int)cudaErrorInvalidValue;
+  }
+  if (C < 8 || C % 8 || TPB % (C / 8) || B < 1 || H < 1 || W < 1) {
+    fprintf(stderr, "crackfl_bn_train_fwd_noalloc: unsupported shape B=%d H=%d W=%d C=%d (C must be a multiple of 8 "
+                    "with C/8 dividing %d)\n", B, H, W, C, TPB);
+    return (int)cudaErrorInvalidValue;
+  }
+  float* scratch = nullptr;
+  int rc = noalloc_scratch_for_current_device(&scratch);
+  if (rc) return rc;
+  float* stats = scratch;                                  // [sum C][sumsq C]   must start at zero
+  float* bn = scratch + 2 * CRACKFL_NOALLOC_MAX_CHANNELS;  // [scale][shift][mean][invstd], fully rewritten
+  cudaError_t e = cudaMemsetAsync(stats, 0, 2 * (size_t)C * sizeof(float), st);
+  if (e != cudaSuccess) return (int)e;
+  const long P = (long)B * H * W;
+  const int ppb = ppb_for(P, C);
+  bn_stats_k<<<(int)((P + ppb - 1) / ppb), TPB, 0, st>>>((const __nv_bfloat16*)y, stats, P, C, ppb);
+  CK_LAUNCH_CHECK();
+  bn_finalize_k<<<(C + 127) / 128, 128, 0, st>>>(stats, gamma, beta, run_mean, run_var, bn, C, (float)P, eps, momentum);
+  CK_LAUNCH_CHECK();
+  bn_act_k<<<grid_for(P * (C / 8)), TPB, 0, st>>>((const __nv_bfloat16*)y, bn, (__nv_bfloat16*)out, nullptr, B, H, W, C,
+                                                 relu);
   CK_LAUNCH_CHECK();
   return 0;
 }

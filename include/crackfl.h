@@ -38,6 +38,19 @@ int crackfl_bn_bwd_reduce(const void* g, const void* arg, const void* y, const f
 int crackfl_bn_bwd_apply(const void* g, const void* arg, const void* y, const float* bn, const float* sums, void* dy,
                          float* dgamma, float* dbeta, int B, int H, int W, int C, int mode, cudaStream_t stream);
 
+/* Training-mode BatchNorm(+ReLU) forward for callers that cannot allocate device memory (a plug-in inside a
+ * process whose device heap belongs to another framework, a fixed-budget step function, recovery code after an
+ * out-of-memory error).  Same result as crackfl_bn_stats + crackfl_bn_finalize + crackfl_bn_act, but the 6*C
+ * floats of scratch come from a fixed array inside the library (48 KiB per GPU, held until exit) instead of the
+ * caller.  C <= CRACKFL_NOALLOC_MAX_CHANNELS, larger C is refused.  Calls share that array: do not let two calls
+ * overlap on one GPU.  The first call per device resolves the array's address; make it before any stream capture.
+ * No counterpart in the reference (it never manages device memory itself). */
+#define CRACKFL_NOALLOC_MAX_CHANNELS 2048
+int crackfl_bn_train_fwd_noalloc(const void* y, const float* gamma, const float* beta, float* run_mean, float* run_var,
+                                 void* out, int B, int H, int W, int C, int relu, float eps, float momentum,
+                                 cudaStream_t stream);
+int crackfl_noalloc_max_channels(void);
+
 /* ---- depthwise 3x3 (ref: SeparableConv2D, client_fit_model.py:109,113) -------------------- */
 /* mode 0: a = relu(x); mode 1: a = relu(x*scale+shift) */
 int crackfl_dw3x3_fwd(const void* x, const float* w, const float* bn, void* out, int B, int H, int W, int C, int mode,
