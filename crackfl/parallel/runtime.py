@@ -78,7 +78,7 @@ class OnBoxFederation:
 
     def __init__(self, spec: UNetSpec = REFERENCE_SPEC, clients_per_gpu: int = 1, strategy: str = "fedavg",
                  payload: str = "fp32", eta=1e-2, beta1=0.9, beta2=0.99, tau=1e-3, numel: Optional[int] = None,
-                 grid_blocks: int = 148):
+                 grid_blocks: int = 148 * 8):
         self.spec = spec
         self.n = int(numel if numel is not None else spec.arena_numel)
         self.mask_from_spec = numel is None  # synthetic sizes (bandwidth sweeps) treat every element as trainable
@@ -167,19 +167,40 @@ class OnBoxFederation:
 
     def publish(self, k: int, flat: torch.Tensor):
         """Client k (local index) hands in its trained weights (device-to-device copy of the arena)."""
-        self.updates[k].copy_(flat)
+        if self.cuda and self.K == 1 and self.payload == "fp32":
+            self.partial.copy_(flat)  # exported arena: peers pull it directly, no pre-reduce pass
+        else:
+            self.updates[k].copy_(flat)
 
-    def aggregate(self, num_samples_local: Sequence[float], weighted: bool = True) -> float:
-        """One FedAvg/FedAdam aggregation + broadcast.  Returns device time in ms (max over ranks)."""
-        ns = torch.tensor([float(x) for x in num_samples_local], dtype=torch.float64)
-        if not weighted:
-            ns = torch.ones_like(ns)
-        tot = ns.sum().clone()
+    def configure(self, num_samples_local: Sequence[float], weighted: bool = True):
+        """Control plane, once per federation (or whenever sample counts change): exchange the per-client sample
+        counts and derive every client's coefficient n_k / sum n.  This is the only collective call; ``aggregate``
+        itself makes none."""
+        ns = [float(x) if weighted else 1.0 for x in num_samples_local]
+        if len(ns) != self.K:
+            raise ValueError(f"need {self.K} sample counts, got {len(ns)}")
+        allns: List[Optional[list]] = [None] * self.world
         if self.world > 1:
-            t = tot.to(self.dev) if self.cuda else tot
-            dist.all_reduce(t)
-            tot = t.cpu()
-        coef = (ns / float(tot)).to(torch.float32)
+            dist.all_gather_object(allns, ns)
+        else:
+            allns = [ns]
+        tot = float(sum(sum(r) for r in allns))
+        if tot <= 0:
+            raise ValueError("total sample count must be positive")
+        self.coef_all = [[x / tot for x in r] for r in allns]
+        self._configured = (tuple(ns), weighted)
+
+    def aggregate(self, num_samples_local: Optional[Sequence[float]] = None, weighted: bool = True,
+                  reduce_timing: bool = True) -> float:
+        """One FedAvg/FedAdam aggregation + broadcast.  Returns device time in ms (max over ranks when
+        ``reduce_timing``; that all_reduce happens after the timed region and is for reporting only)."""
+        if num_samples_local is not None:
+            key = (tuple(float(x) if weighted else 1.0 for x in num_samples_local), weighted)
+            if getattr(self, "_configured", None) != key:
+                self.configure(num_samples_local, weighted)
+        if getattr(self, "coef_all", None) is None:
+            raise RuntimeError("call configure(num_samples) first")
+        coef = torch.tensor(self.coef_all[self.rank], dtype=torch.float32)
         self.epoch += 1
         if not self.cuda:
             return self._aggregate_cpu(coef)
@@ -187,31 +208,33 @@ class OnBoxFederation:
         st = torch.cuda.current_stream(self.dev)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(st)
-        # (K14) local pre-reduce of this GPU's K clients -> partial
-        p = L.FedAggParams()
         K = self.K
-        for k in range(K):
-            p.client[k] = self.updates[k].data_ptr()
-            p.coef[k] = float(coef[k])
-        nc = K
-        if self.payload == "bf16_delta":
-            p.client[K] = self.global_arena.data_ptr()  # partial = sum c_k (w_k - w_global)
-            p.coef[K] = -float(coef.sum())
-            nc = K + 1
-        p.num_clients, p.num_out = nc, 1
-        p.out[0] = self.partial.data_ptr()
-        p.payload_bf16, p.out_bf16 = 0, 1 if self.payload == "bf16_delta" else 0
-        p.delta = p.server_opt = 0
-        p.master = p.m = p.v = p.trainable = p.mc_out = 0
-        p.begin, p.end = 0, self.n
-        p.rank, p.world, p.epoch = 0, 1, 1
-        p.error_flag = p.local_sync = 0
-        L.check(lib.crackfl_fedagg(C.byref(p), 148 * 4, st.cuda_stream), "fedagg pre-reduce")
+        direct = (K == 1 and self.payload == "fp32")  # the single local update IS the partial: no pre-reduce pass
+        if not direct:
+            # (K14) local pre-reduce of this GPU's K clients -> partial
+            p = L.FedAggParams()
+            for k in range(K):
+                p.client[k] = self.updates[k].data_ptr()
+                p.coef[k] = float(coef[k])
+            nc = K
+            if self.payload == "bf16_delta":
+                p.client[K] = self.global_arena.data_ptr()  # partial = sum c_k (w_k - w_global)
+                p.coef[K] = -float(coef.sum())
+                nc = K + 1
+            p.num_clients, p.num_out = nc, 1
+            p.out[0] = self.partial.data_ptr()
+            p.payload_bf16, p.out_bf16 = 0, 1 if self.payload == "bf16_delta" else 0
+            p.delta = p.server_opt = 0
+            p.master = p.m = p.v = p.trainable = p.mc_out = 0
+            p.begin, p.end = 0, self.n
+            p.rank, p.world, p.epoch = 0, 1, 1
+            p.error_flag = p.local_sync = 0
+            L.check(lib.crackfl_fedagg(C.byref(p), 148 * 8, st.cuda_stream), "fedagg pre-reduce")
         # (K11-K13) cross-GPU reduce + server update + broadcast, one launch
         q = L.FedAggParams()
         for r in range(self.world):
             q.client[r] = self.peer["partial"][r]
-            q.coef[r] = 1.0
+            q.coef[r] = float(self.coef_all[r][0]) if direct else 1.0
             q.out[r] = self.peer["global"][r]
             q.pads[r] = self.peer["pads"][r]
         q.num_clients = q.num_out = self.world
@@ -232,7 +255,7 @@ class OnBoxFederation:
         if int(self.error_flag.item()) != 0:
             raise RuntimeError(f"rank {self.rank}: aggregation barrier timed out (flag {int(self.error_flag.item())})")
         ms = torch.tensor([e0.elapsed_time(e1)], device=self.dev)
-        if self.world > 1:
+        if self.world > 1 and reduce_timing:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         self.last_agg_ms = float(ms.item())
         return self.last_agg_ms

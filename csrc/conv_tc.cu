@@ -19,6 +19,7 @@
 // wgrad uses the same TMA boxes but feeds them as MN-major operands (the pixel axis is K), pairs/quadruples
 // (tap, channel-chunk) blocks to fill M=128 and splits the pixel axis over CTAs.
 #include <cuda.h>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <unordered_map>
@@ -284,6 +285,216 @@ __global__ void __launch_bounds__(192) conv_tc_fwd_k(const __grid_constant__ CUt
 }
 
 // ----------------------------------------------------------------------------------------------------------
+// v2: persistent CTAs, double-buffered TMEM accumulators, TMA-store epilogue.
+// The v1 kernel above pays its prologue (barrier init, descriptor fetch, TMEM alloc) and an un-overlapped epilogue
+// once per 128-pixel tile; for the thin 1x1 / small-K layers of this network that is most of the tile's life.
+// Here a CTA loops over tiles (m fastest, so consecutive tiles reuse the weight tile in L2), the producer runs
+// ahead across tile boundaries, the MMA warp alternates between two TMEM accumulator stages, and the epilogue
+// warps drain stage s (tcgen05.ld -> bias/add/stats -> bf16 -> swizzled smem -> one TMA bulk store, which also
+// clips out-of-bounds pixels) while the tensor core already fills stage s^1.
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* tm, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tm)), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+struct ConvArgs2 {
+  const float* bias;
+  const __nv_bfloat16* add;
+  float* stats;
+  int B, H, W, Cin, N, taps;
+  int BN, kc, stages;
+  int sub_w;                 // channels per output sub-tile (64 with 128B swizzle, 32 with 64B swizzle)
+  int n_tiles_m, n_tiles_n;  // tile counts
+  uint32_t layout, sbo;
+  TileGeom g;
+};
+
+__global__ void __launch_bounds__(192) conv_tc_fwd_v2_k(const __grid_constant__ CUtensorMap tmA,
+                                                        const __grid_constant__ CUtensorMap tmB,
+                                                        const __grid_constant__ CUtensorMap tmY, const ConvArgs2 a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t a_bytes = 128u * a.kc * 2u, b_bytes = (uint32_t)a.BN * a.kc * 2u;
+  const uint32_t stage_bytes = a_bytes + b_bytes;
+  const uint32_t out_bytes = 128u * (uint32_t)a.BN * 2u;               // one staging buffer
+  const uint32_t out0 = base + a.stages * stage_bytes;                  // 2 staging buffers
+  const uint32_t bar_base = out0 + 2u * out_bytes;
+  const uint32_t full0 = bar_base, empty0 = bar_base + 8u * a.stages;
+  const uint32_t tfull0 = bar_base + 16u * a.stages, tempty0 = tfull0 + 16u;
+  const uint32_t tptr = tempty0 + 16u;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kchunks = a.Cin / a.kc;
+  const int iters = a.taps * kchunks;
+  const int total_tiles = a.n_tiles_m * a.n_tiles_n;
+  const uint32_t ncols = (uint32_t)(2 * a.BN < 32 ? 32 : 2 * a.BN);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < a.stages; ++s) {
+      mbar_init(full0 + 8u * s, 1);
+      mbar_init(empty0 + 8u * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull0 + 8u * s, 1);
+      mbar_init(tempty0 + 8u * s, 4);  // one arrival per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmY);
+  }
+  if (warp == 1) tmem_alloc(tptr, ncols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tptr));
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it_g = 0;  // global k-iteration counter across tiles (ring position)
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int tm_ = tile % a.n_tiles_m;
+        const int n0 = (tile / a.n_tiles_m) * a.BN;
+        const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
+        const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
+        const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
+        for (int it = 0; it < iters; ++it, ++it_g) {
+          const uint32_t s = it_g % a.stages, ph = (it_g / a.stages) & 1u;
+          mbar_wait(empty0 + 8u * s, ph ^ 1u);
+          const int t = it / kchunks, c = it % kchunks;
+          const int dh = a.taps == 9 ? t / 3 - 1 : 0, dw = a.taps == 9 ? t % 3 - 1 : 0;
+          const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
+          mbar_expect_tx(full0 + 8u * s, stage_bytes);
+          tma_load_4d(sa, &tmA, full0 + 8u * s, c * a.kc, w0 + dw, h0 + dh, b0);
+          tma_load_2d(sb, &tmB, full0 + 8u * s, t * a.Cin + c * a.kc, n0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(128, a.BN, 0, 0);
+      uint32_t it_g = 0, tcount = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+        const uint32_t as = tcount & 1u, aph = (tcount >> 1) & 1u;
+        mbar_wait(tempty0 + 8u * as, aph ^ 1u);  // epilogue has drained this accumulator stage
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + as * (uint32_t)a.BN;
+        for (int it = 0; it < iters; ++it, ++it_g) {
+          const uint32_t s = it_g % a.stages, ph = (it_g / a.stages) & 1u;
+          mbar_wait(full0 + 8u * s, ph);
+          tc_fence_after();
+          const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
+          const uint64_t ad = make_desc(sa, 16, a.sbo, a.layout);
+          const uint64_t bd = make_desc(sb, 16, a.sbo, a.layout);
+          for (int k = 0; k < a.kc / 16; ++k)
+            umma_f16(tacc, ad + 2u * k, bd + 2u * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+          umma_commit(empty0 + 8u * s);
+        }
+        umma_commit(tfull0 + 8u * as);
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const int tw = r % a.g.TW, th = (r / a.g.TW) % a.g.TH, tb = r / (a.g.TW * a.g.TH);
+    const int et = threadIdx.x - 64;  // 0..127 among the epilogue threads
+    const int nsub = a.BN / a.sub_w;
+    const uint32_t sub_bytes = 128u * (uint32_t)a.sub_w * 2u;
+    const uint32_t row_bytes = (uint32_t)a.sub_w * 2u;
+    uint32_t tcount = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+      int tm_ = tile % a.n_tiles_m;
+      const int n0 = (tile / a.n_tiles_m) * a.BN;
+      const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
+      const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
+      const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
+      const int pw = w0 + tw, ph_ = h0 + th, pb = b0 + tb;
+      const bool valid = pw < a.W && ph_ < a.H && pb < a.B;
+      const long pix = ((long)pb * a.H + ph_) * a.W + pw;
+      const uint32_t as = tcount & 1u, aph = (tcount >> 1) & 1u;
+      const uint32_t obuf = out0 + as * out_bytes;
+      // the TMA store that last read this staging buffer (two tiles ago) must have finished reading it
+      if (et == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+      epi_bar_sync();
+      mbar_wait(tfull0 + 8u * as, aph);
+      tc_fence_after();
+      for (int c0 = 0; c0 < a.BN; c0 += 32) {
+        uint32_t raw[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * (uint32_t)a.BN + (uint32_t)c0, raw);
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
+        if (a.bias) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 bb = __ldg(reinterpret_cast<const float4*>(a.bias + n0 + c0 + j));
+            v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
+          }
+        }
+        if (a.add && valid) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            float t8[8];
+            ck::unpack8(ck::ldg16(a.add + pix * a.N + n0 + c0 + j), t8);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[j + e] += t8[e];
+          }
+        }
+        // bf16 pack + swizzled staging store (row r of sub-tile c0 / sub_w)
+        const int sub = c0 / a.sub_w, cin_sub = c0 % a.sub_w;
+        const uint32_t rowaddr = obuf + sub * sub_bytes + (uint32_t)r * row_bytes;
+        const uint32_t xorv = (a.sub_w == 64) ? (uint32_t)(r & 7) : (uint32_t)((r >> 1) & 3);
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+          const uint4 pk = ck::pack8(&v[j]);
+          const uint32_t chunk = (uint32_t)((cin_sub + j) >> 3);
+          const uint32_t dst = rowaddr + ((chunk ^ xorv) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(pk.x), "r"(pk.y), "r"(pk.z), "r"(pk.w)
+                       : "memory");
+        }
+        if (a.stats) {
+          float s1[32], s2[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float x = valid ? __bfloat162float(__float2bfloat16_rn(v[j])) : 0.f;
+            s1[j] = x;
+            s2[j] = x * x;
+          }
+          const float t1 = warp_colsum32(s1, lane);
+          const float t2 = warp_colsum32(s2, lane);
+          atomicAdd(a.stats + n0 + c0 + lane, t1);
+          atomicAdd(a.stats + a.N + n0 + c0 + lane, t2);
+        }
+      }
+      // accumulator stage fully read: hand it back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty0 + 8u * as);
+      // make the staging writes visible to the async proxy, then one thread stores the tile
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      epi_bar_sync();
+      if (et == 0) {
+        for (int sub = 0; sub < nsub; ++sub)
+          tma_store_4d(&tmY, obuf + sub * sub_bytes, n0 + sub * a.sub_w, w0, h0, b0);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    }
+    if (et == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, ncols);
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------------
 struct WgradArgs {
   float* dW;
   long s_tap, s_ci, s_co;
@@ -500,8 +711,8 @@ extern "C" {
 
 int crackfl_tc_selftest_supported(void) { return get_encode() ? 1 : 0; }
 
-int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const void* add, void* Y, float* stats, int B, int H,
-                        int W, int Cin, int N, int taps, cudaStream_t st) {
+static int conv_tc_fwd_v1(const void* X, const void* Wk, const float* bias, const void* add, void* Y, float* stats, int B, int H,
+                          int W, int Cin, int N, int taps, cudaStream_t st) {
   if (Cin % 32 || N % 32 || (taps != 1 && taps != 9)) return (int)cudaErrorInvalidValue;
   ConvArgs a;
   a.bias = bias; a.add = (const __nv_bfloat16*)add; a.Y = (__nv_bfloat16*)Y; a.stats = stats;
@@ -535,6 +746,66 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
   }
   dim3 grid(a.g.tiles_w * a.g.tiles_h * a.g.tiles_b, N / a.BN);
   conv_tc_fwd_k<<<grid, 192, smem, st>>>(tmA, tmB, a);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+static int g_num_sms = 0;
+
+int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const void* add, void* Y, float* stats, int B, int H,
+                        int W, int Cin, int N, int taps, cudaStream_t st) {
+  static int use_v1 = -1;
+  if (use_v1 < 0) {
+    const char* e = getenv("CRACKFL_TC_V1");
+    use_v1 = (e && e[0] == '1') ? 1 : 0;
+  }
+  if (use_v1) return conv_tc_fwd_v1(X, Wk, bias, add, Y, stats, B, H, W, Cin, N, taps, st);
+  if (Cin % 32 || N % 32 || (taps != 1 && taps != 9)) return (int)cudaErrorInvalidValue;
+  ConvArgs2 a;
+  a.bias = bias; a.add = (const __nv_bfloat16*)add; a.stats = stats;
+  a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.N = N; a.taps = taps;
+  a.BN = N > 128 ? 128 : N;
+  if (N % a.BN) return (int)cudaErrorInvalidValue;
+  a.kc = (Cin % 64 == 0) ? 64 : 32;
+  a.layout = a.kc == 64 ? 2u : 4u;
+  a.sbo = a.kc == 64 ? 1024u : 512u;
+  a.sub_w = (a.BN % 64 == 0) ? 64 : 32;
+  a.g = make_geom(B, H, W);
+  a.n_tiles_m = a.g.tiles_w * a.g.tiles_h * a.g.tiles_b;
+  a.n_tiles_n = N / a.BN;
+  const int iters = taps * (Cin / a.kc);
+  const uint32_t stage_bytes = 128u * a.kc * 2u + (uint32_t)a.BN * a.kc * 2u;
+  const uint32_t out_bytes = 2u * 128u * (uint32_t)a.BN * 2u;
+  int stages = (int)((106496u - out_bytes) / stage_bytes);  // ~104 KB per CTA -> two CTAs per SM
+  if (stages > 8) stages = 8;
+  if (stages < 2) stages = 2;
+  a.stages = stages;
+  (void)iters;
+  const size_t smem = (size_t)stages * stage_bytes + out_bytes + 1024 + 256;
+  CUtensorMap tmA, tmB, tmY;
+  const int dA[4] = {Cin, W, H, B}, bA[4] = {a.kc, a.g.TW, a.g.TH, a.g.TB};
+  int rc = get_map(X, 4, dA, bA, a.kc * 2, &tmA);
+  if (rc) return rc;
+  const int dB[2] = {taps * Cin, N}, bB[2] = {a.kc, a.BN};
+  rc = get_map(Wk, 2, dB, bB, a.kc * 2, &tmB);
+  if (rc) return rc;
+  const int dY[4] = {N, W, H, B}, bY[4] = {a.sub_w, a.g.TW, a.g.TH, a.g.TB};
+  rc = get_map(Y, 4, dY, bY, a.sub_w * 2, &tmY);
+  if (rc) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_fwd_v2_k, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return (int)e;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+    attr_set = true;
+  }
+  const int total = a.n_tiles_m * a.n_tiles_n;
+  int grid = 2 * g_num_sms;
+  if (grid > total) grid = total;
+  conv_tc_fwd_v2_k<<<grid, 192, smem, st>>>(tmA, tmB, tmY, a);
   CK_LAUNCH_CHECK();
   return 0;
 }

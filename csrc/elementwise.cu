@@ -694,6 +694,232 @@ __global__ void __launch_bounds__(TPB) head_bwd_k(const __nv_bfloat16* __restric
   if ((threadIdx.x & 31) == 0) atomicAdd(db, dbl);
 }
 
+
+// ---------------------------------------------------------------------------------------
+// v2 depthwise kernels: the naive versions above issue 9 (fwd) / 18 (bwd) 16-byte L1 loads per output vector and
+// are L1-bandwidth bound (128 B/clk/SM).  Here a thread owns a strip of S=4 consecutive pixels of one row for one
+// channel vector and slides a 3 x (S+2) register window over it: 4.5 loads (and BN+ReLU evaluations) per output.
+constexpr int DWS = 4;
+
+template <bool ACT>
+__device__ __forceinline__ void load_row_window(const __nv_bfloat16* __restrict__ src, long row_base_vec, int w0, int W,
+                                                int c8, int cv, int mode, const float sc[8], const float sh[8],
+                                                float win[DWS + 2][8]) {
+#pragma unroll
+  for (int i = 0; i < DWS + 2; ++i) {
+    const int iw = w0 - 1 + i;
+    if (iw >= 0 && iw < W) {
+      if (ACT) act_load(src, row_base_vec + (long)iw * c8 + cv, mode, sc, sh, win[i]);
+      else unpack8(ldg16(src + (row_base_vec + (long)iw * c8 + cv) * 8), win[i]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) win[i][j] = 0.f;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(TPB, 2) dw3x3_fwd_v2_k(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+                                                         const float* __restrict__ bn, __nv_bfloat16* __restrict__ out,
+                                                         int B, int H, int W, int C, int mode) {
+  const int c8 = C >> 3, WS = W / DWS;
+  const long total = (long)B * H * WS * c8;
+  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long)gridDim.x * blockDim.x) {
+    const int cv = (int)(g % c8);
+    long s = g / c8;
+    const int ws = (int)(s % WS); s /= WS;
+    const int hh = (int)(s % H);
+    const long b = s / H;
+    const int w0 = ws * DWS;
+    float sc[8], sh[8], acc[DWS][8];
+    if (mode == 1) { load8f(bn + cv * 8, sc); load8f(bn + C + cv * 8, sh); }
+#pragma unroll
+    for (int i = 0; i < DWS; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int ih = hh + r - 1;
+      if (ih < 0 || ih >= H) continue;
+      float win[DWS + 2][8], wk[3][8];
+      load_row_window<true>(x, (b * H + ih) * (long)W * c8, w0, W, c8, cv, mode, sc, sh, win);
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) load8f(w + (r * 3 + kw) * C + cv * 8, wk[kw]);
+#pragma unroll
+      for (int i = 0; i < DWS; ++i)
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(win[i + kw][j], wk[kw][j], acc[i][j]);
+    }
+    const long obase = ((b * H + hh) * (long)W + w0) * c8 + cv;
+#pragma unroll
+    for (int i = 0; i < DWS; ++i) stg16(out + (obase + (long)i * c8) * 8, pack8(acc[i]));
+  }
+}
+
+// input gradient: da[p] = sum_tap g[p - off(tap)] * w[tap]; dz = mask * da (+ residual), see dw3x3_bwd_k
+__global__ void __launch_bounds__(TPB, 2) dw3x3_dgrad_v2_k(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ src,
+                                                           const float* __restrict__ w, const float* __restrict__ bn,
+                                                           const __nv_bfloat16* __restrict__ resid_t,
+                                                           __nv_bfloat16* __restrict__ dz, int B, int H, int W, int C, int mode,
+                                                           int resid) {
+  const int c8 = C >> 3, WS = W / DWS;
+  const long total = (long)B * H * WS * c8;
+  for (long gi = (long)blockIdx.x * blockDim.x + threadIdx.x; gi < total; gi += (long)gridDim.x * blockDim.x) {
+    const int cv = (int)(gi % c8);
+    long s = gi / c8;
+    const int ws = (int)(s % WS); s /= WS;
+    const int hh = (int)(s % H);
+    const long b = s / H;
+    const int w0 = ws * DWS;
+    float sc[8], sh[8], acc[DWS][8];
+    if (mode == 1) { load8f(bn + cv * 8, sc); load8f(bn + C + cv * 8, sh); }
+#pragma unroll
+    for (int i = 0; i < DWS; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int oh = hh + r - 1;  // row of g; it used tap kh = 2 - r to reach row hh
+      if (oh < 0 || oh >= H) continue;
+      float win[DWS + 2][8], wk[3][8];
+      load_row_window<false>(g, (b * H + oh) * (long)W * c8, w0, W, c8, cv, 0, sc, sh, win);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) load8f(w + ((2 - r) * 3 + (2 - c)) * C + cv * 8, wk[c]);
+#pragma unroll
+      for (int i = 0; i < DWS; ++i)
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(win[i + c][j], wk[c][j], acc[i][j]);
+    }
+    const long obase = ((b * H + hh) * (long)W + w0) * c8 + cv;
+#pragma unroll
+    for (int i = 0; i < DWS; ++i) {
+      float a[8], r8[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      act_load(src, obase + (long)i * c8, mode, sc, sh, a);
+      const int ww = w0 + i;
+      if (resid && !(hh & 1) && !(ww & 1))
+        unpack8(ldg16(resid_t + (((b * (H >> 1) + (hh >> 1)) * (long)(W >> 1) + (ww >> 1)) * c8 + cv) * 8), r8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float m = a[j] > 0.f ? 1.f : 0.f;
+        acc[i][j] = (resid == 2) ? m * (acc[i][j] + r8[j]) : m * acc[i][j] + r8[j];
+      }
+      stg16(dz + (obase + (long)i * c8) * 8, pack8(acc[i]));
+    }
+  }
+}
+
+// weight gradient: dw[tap][c] += sum_o a[o + off(tap)][c] * g[o][c]
+__global__ void __launch_bounds__(TPB, 1) dw3x3_wgrad_v2_k(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ src,
+                                                           const float* __restrict__ bn, float* __restrict__ dwk, int B, int H,
+                                                           int W, int C, int mode, int strips_per_block) {
+  __shared__ float sm[TPB * 8];
+  const int c8 = C >> 3, WS = W / DWS, lanes = TPB / c8;
+  const int cv = threadIdx.x % c8, lane = threadIdx.x / c8;
+  const long S = (long)B * H * WS;
+  const long s0 = (long)blockIdx.x * strips_per_block;
+  const long s1 = min(S, s0 + strips_per_block);
+  float sc[8], sh[8], dacc[9][8];
+  if (mode == 1) { load8f(bn + cv * 8, sc); load8f(bn + C + cv * 8, sh); }
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dacc[t][j] = 0.f;
+  for (long s = s0 + lane; s < s1; s += lanes) {
+    const int ws = (int)(s % WS);
+    const int hh = (int)((s / WS) % H);
+    const long b = s / ((long)WS * H);
+    const int w0 = ws * DWS;
+    float gc[DWS][8];
+    const long obase = ((b * H + hh) * (long)W + w0) * c8 + cv;
+#pragma unroll
+    for (int i = 0; i < DWS; ++i) unpack8(ldg16(g + (obase + (long)i * c8) * 8), gc[i]);
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int ih = hh + r - 1;
+      if (ih < 0 || ih >= H) continue;
+      float win[DWS + 2][8];
+      load_row_window<true>(src, (b * H + ih) * (long)W * c8, w0, W, c8, cv, mode, sc, sh, win);
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw)
+#pragma unroll
+        for (int i = 0; i < DWS; ++i)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) dacc[r * 3 + kw][j] = fmaf(win[i + kw][j], gc[i][j], dacc[r * 3 + kw][j]);
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < 9; ++t) block_channel_atomic(dacc[t], c8, sm, dwk + t * C);
+}
+
+// v2 entry-conv weight gradient: block = 256 threads = (C channels) x (256/C k-groups); 128-pixel chunks staged in smem.
+__global__ void __launch_bounds__(TPB) entry_conv_wgrad_v2_k(const uint8_t* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                                                             float* __restrict__ dw, int B, int H, int W, int C,
+                                                             int pix_per_block) {
+  extern __shared__ float smw[];  // patch[128][28] | dy[128][C]
+  float* sp = smw;
+  float* sd = smw + 128 * 28;
+  const int Ho = H >> 1, Wo = W >> 1, c8 = C >> 3;
+  const long P = (long)B * Ho * Wo;
+  const long p0 = (long)blockIdx.x * pix_per_block;
+  const long p1 = min(P, p0 + pix_per_block);
+  const int G = TPB / C;                 // k-groups
+  const int c = threadIdx.x % C, kg = threadIdx.x / C;
+  float acc[7] = {0, 0, 0, 0, 0, 0, 0};  // k = kg + i*G, i < ceil(27/G) <= 7 (C <= 64)
+  for (long pc = p0; pc < p1; pc += 128) {
+    const int np = (int)min((long)128, p1 - pc);
+    __syncthreads();
+    if (threadIdx.x < 128) {
+      const int i = threadIdx.x;
+      float* row = sp + i * 28;
+      if (i < np) {
+        const long p = pc + i;
+        const int ow = (int)(p % Wo);
+        const int oh = (int)((p / Wo) % Ho);
+        const long b = p / ((long)Wo * Ho);
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
+          const int ih = 2 * oh + kh;
+#pragma unroll
+          for (int kw = 0; kw < 3; ++kw) {
+            const int iw = 2 * ow + kw;
+            const bool ok = ih < H && iw < W;
+            const uint8_t* px = x + ((b * H + ih) * (long)W + iw) * 3;
+#pragma unroll
+            for (int ci = 0; ci < 3; ++ci) row[(kh * 3 + kw) * 3 + ci] = ok ? (float)px[ci] * (1.0f / 255.0f) : 0.f;
+          }
+        }
+      } else {
+        for (int k = 0; k < 27; ++k) row[k] = 0.f;
+      }
+    }
+    for (int v = threadIdx.x; v < 128 * c8; v += TPB) {
+      const int i = v / c8, cvv = v % c8;
+      float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      if (i < np) unpack8(ldg16(dy + ((pc + i) * c8 + cvv) * 8), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sd[i * C + cvv * 8 + j] = f[j];
+    }
+    __syncthreads();
+    for (int i = 0; i < 128; ++i) {
+      const float d = sd[i * C + c];
+      const float* row = sp + i * 28;
+#pragma unroll
+      for (int q = 0; q < 7; ++q) {
+        const int k = kg + q * G;
+        if (k < 27) acc[q] = fmaf(row[k], d, acc[q]);
+      }
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < 7; ++q) {
+    const int k = kg + q * G;
+    if (k < 27) atomicAdd(dw + (long)k * C + c, acc[q]);
+  }
+}
+
 inline int grid_for(long total, int cap = 148 * 16) {
   long b = (total + TPB - 1) / TPB;
   return (int)(b < 1 ? 1 : (b > cap ? cap : b));
@@ -723,6 +949,13 @@ int crackfl_entry_conv_fwd(const void* x_u8, const float* w, const float* bias, 
 
 int crackfl_entry_conv_wgrad(const void* x_u8, const void* dy, float* dw, int B, int H, int W, int C, cudaStream_t st) {
   const long P = (long)B * (H / 2) * (W / 2);
+  if (C <= 64 && TPB % C == 0) {
+    const int ppb2 = 512;
+    entry_conv_wgrad_v2_k<<<(int)((P + ppb2 - 1) / ppb2), TPB, (128 * 28 + 128 * C) * sizeof(float), st>>>(
+        (const uint8_t*)x_u8, (const __nv_bfloat16*)dy, dw, B, H, W, C, ppb2);
+    CK_LAUNCH_CHECK();
+    return 0;
+  }
   const int ppb = 512;
   dim3 blk(C / 8, 27);
   if (blk.x * blk.y > 1024) return (int)cudaErrorInvalidValue;
@@ -766,6 +999,12 @@ int crackfl_bn_act(const void* y, const float* bn, void* out, void* even, int B,
 int crackfl_dw3x3_fwd(const void* x, const float* w, const float* bn, void* out, int B, int H, int W, int C, int mode,
                       cudaStream_t st) {
   const long total = (long)B * H * W * (C / 8);
+  if (W % DWS == 0) {
+    dw3x3_fwd_v2_k<<<grid_for(total / DWS, 148 * 8), TPB, 0, st>>>((const __nv_bfloat16*)x, w, bn, (__nv_bfloat16*)out, B, H, W,
+                                                                  C, mode);
+    CK_LAUNCH_CHECK();
+    return 0;
+  }
   dw3x3_fwd_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)x, w, bn, (__nv_bfloat16*)out, B, H, W, C, mode);
   CK_LAUNCH_CHECK();
   return 0;
@@ -775,6 +1014,21 @@ int crackfl_dw3x3_bwd(const void* g, const void* src, const float* w, const floa
                       float* dwk, int B, int H, int W, int C, int mode, int resid, cudaStream_t st) {
   if (C % 8 || TPB % (C / 8)) return (int)cudaErrorInvalidValue;
   const long P = (long)B * H * W;
+  if (W % DWS == 0) {
+    const long strips = P / DWS;
+    dw3x3_dgrad_v2_k<<<grid_for(strips * (C / 8), 148 * 8), TPB, 0, st>>>(
+        (const __nv_bfloat16*)g, (const __nv_bfloat16*)src, w, bn, (const __nv_bfloat16*)resid_t, (__nv_bfloat16*)dz, B, H, W, C,
+        mode, resid);
+    CK_LAUNCH_CHECK();
+    const int lanes = TPB / (C / 8);
+    long spb = (strips + 148 * 4 - 1) / (148 * 4);
+    spb = ((spb + lanes - 1) / lanes) * lanes;
+    if (spb < lanes) spb = lanes;
+    dw3x3_wgrad_v2_k<<<(int)((strips + spb - 1) / spb), TPB, 0, st>>>((const __nv_bfloat16*)g, (const __nv_bfloat16*)src, bn,
+                                                                      dwk, B, H, W, C, mode, (int)spb);
+    CK_LAUNCH_CHECK();
+    return 0;
+  }
   const int ppb = ppb_for(P, C);
   dw3x3_bwd_k<<<(int)((P + ppb - 1) / ppb), TPB, 0, st>>>((const __nv_bfloat16*)g, (const __nv_bfloat16*)src, w, bn,
                                                           (const __nv_bfloat16*)resid_t, (__nv_bfloat16*)dz, dwk, B, H, W,

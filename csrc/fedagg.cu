@@ -87,31 +87,54 @@ __global__ void __launch_bounds__(256) fedagg_k(const crackfl_fedagg_params P) {
   }
 
   const long n4_begin = P.begin >> 2, n4_end = P.end >> 2;
-  for (long i = n4_begin + (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4_end; i += (long)gridDim.x * blockDim.x) {
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 4
+  constexpr int U = 4;  // independent 16-byte loads per client per thread: NVLink latency is ~2 us, keep bytes in flight
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i0 = n4_begin + (long)blockIdx.x * blockDim.x + threadIdx.x; i0 < n4_end; i0 += stride * U) {
+    float4 acc[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int k = 0; k < P.num_clients; ++k) {
       const float c = P.coef[k];
       if (PAYLOAD_BF16) {
-        const uint2 u = ld_nc_u2(reinterpret_cast<const uint2*>(P.client[k]) + i);
-        acc.x = fmaf(c, __uint_as_float(u.x << 16), acc.x);
-        acc.y = fmaf(c, __uint_as_float(u.x & 0xffff0000u), acc.y);
-        acc.z = fmaf(c, __uint_as_float(u.y << 16), acc.z);
-        acc.w = fmaf(c, __uint_as_float(u.y & 0xffff0000u), acc.w);
+        uint2 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const long i = i0 + u * stride;
+          v[u] = i < n4_end ? ld_nc_u2(reinterpret_cast<const uint2*>(P.client[k]) + i) : make_uint2(0u, 0u);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          acc[u].x = fmaf(c, __uint_as_float(v[u].x << 16), acc[u].x);
+          acc[u].y = fmaf(c, __uint_as_float(v[u].x & 0xffff0000u), acc[u].y);
+          acc[u].z = fmaf(c, __uint_as_float(v[u].y << 16), acc[u].z);
+          acc[u].w = fmaf(c, __uint_as_float(v[u].y & 0xffff0000u), acc[u].w);
+        }
       } else {
-        const float4 u = ld_nc_f4(reinterpret_cast<const float*>(P.client[k]) + i * 4);
-        acc.x = fmaf(c, u.x, acc.x); acc.y = fmaf(c, u.y, acc.y);
-        acc.z = fmaf(c, u.z, acc.z); acc.w = fmaf(c, u.w, acc.w);
+        float4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const long i = i0 + u * stride;
+          v[u] = i < n4_end ? ld_nc_f4(reinterpret_cast<const float*>(P.client[k]) + i * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          acc[u].x = fmaf(c, v[u].x, acc[u].x); acc[u].y = fmaf(c, v[u].y, acc[u].y);
+          acc[u].z = fmaf(c, v[u].z, acc[u].z); acc[u].w = fmaf(c, v[u].w, acc[u].w);
+        }
       }
     }
-    float4 nw = acc;
-    if (P.master) {
-      float4 w = reinterpret_cast<float4*>(P.master)[i];
-      if (P.delta) { nw.x += w.x; nw.y += w.y; nw.z += w.z; nw.w += w.w; }
-      if (P.server_opt == 1) {
-        float4 m = reinterpret_cast<float4*>(P.m)[i];
-        float4 v = reinterpret_cast<float4*>(P.v)[i];
-        const uchar4 tr = P.trainable ? reinterpret_cast<const uchar4*>(P.trainable)[i] : make_uchar4(1, 1, 1, 1);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long i = i0 + u * stride;
+      if (i >= n4_end) break;
+      float4 nw = acc[u];
+      if (P.master) {
+        float4 w = reinterpret_cast<float4*>(P.master)[i];
+        if (P.delta) { nw.x += w.x; nw.y += w.y; nw.z += w.z; nw.w += w.w; }
+        if (P.server_opt == 1) {
+          float4 m = reinterpret_cast<float4*>(P.m)[i];
+          float4 v = reinterpret_cast<float4*>(P.v)[i];
+          const uchar4 tr = P.trainable ? reinterpret_cast<const uchar4*>(P.trainable)[i] : make_uchar4(1, 1, 1, 1);
 #define CK_FEDADAM1(c)                                                   \
   if (tr.c) {                                                            \
     const float d = nw.c - w.c;                                          \
@@ -119,17 +142,16 @@ __global__ void __launch_bounds__(256) fedagg_k(const crackfl_fedagg_params P) {
     v.c = P.beta2 * v.c + (1.f - P.beta2) * d * d;                       \
     nw.c = w.c + P.eta * m.c / (sqrtf(v.c) + P.tau);                     \
   }
-        CK_FEDADAM1(x) CK_FEDADAM1(y) CK_FEDADAM1(z) CK_FEDADAM1(w)
+          CK_FEDADAM1(x) CK_FEDADAM1(y) CK_FEDADAM1(z) CK_FEDADAM1(w)
 #undef CK_FEDADAM1
-        reinterpret_cast<float4*>(P.m)[i] = m;
-        reinterpret_cast<float4*>(P.v)[i] = v;
+          reinterpret_cast<float4*>(P.m)[i] = m;
+          reinterpret_cast<float4*>(P.v)[i] = v;
+        }
+        reinterpret_cast<float4*>(P.master)[i] = nw;
       }
-      reinterpret_cast<float4*>(P.master)[i] = nw;
-    }
-    if (P.mc_out) {
-      multimem_st_f4(P.mc_out + i * 4, nw);
-    } else {
-      if (OUT_BF16) {
+      if (P.mc_out) {
+        multimem_st_f4(P.mc_out + i * 4, nw);
+      } else if (OUT_BF16) {
         uint2 o;
         o.x = ck::pack2(nw.x, nw.y);
         o.y = ck::pack2(nw.z, nw.w);
@@ -164,7 +186,7 @@ int crackfl_fedagg(const crackfl_fedagg_params* p, int grid_blocks, cudaStream_t
     return (int)cudaErrorInvalidValue;
   if (p->mc_out && p->out_bf16) return (int)cudaErrorInvalidValue;
   long n4 = (p->end - p->begin) / 4;
-  long blocks = (n4 + 255) / 256;
+  long blocks = (n4 + 256 * 4 - 1) / (256 * 4);
   if (blocks > grid_blocks) blocks = grid_blocks;
   if (blocks < 1) blocks = 1;
   if (p->world > 1) blocks = grid_blocks;  // grid size is part of the exit-barrier arithmetic
