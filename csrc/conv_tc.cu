@@ -327,6 +327,7 @@ __global__ void __launch_bounds__(192) conv_tc_fwd_v2_k(const __grid_constant__ 
   const uint32_t full0 = bar_base, empty0 = bar_base + 8u * a.stages;
   const uint32_t tfull0 = bar_base + 16u * a.stages, tempty0 = tfull0 + 16u;
   const uint32_t tptr = tempty0 + 16u;
+  const uint32_t stat_smem = tptr + 16u;  // 4 warps x 2 x 128 floats
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kchunks = a.Cin / a.kc;
   const int iters = a.taps * kchunks;
@@ -406,10 +407,36 @@ __global__ void __launch_bounds__(192) conv_tc_fwd_v2_k(const __grid_constant__ 
     const int nsub = a.BN / a.sub_w;
     const uint32_t sub_bytes = 128u * (uint32_t)a.sub_w * 2u;
     const uint32_t row_bytes = (uint32_t)a.sub_w * 2u;
+    // BN statistics are accumulated per CTA across all its tiles of one n-tile (registers: lane <-> column) and
+    // flushed with 2*BN atomics per CTA instead of 8*BN per tile: the per-tile version serialised thousands of
+    // same-address atomics in L2 and doubled the kernel time.
+    float st1[4] = {0.f, 0.f, 0.f, 0.f}, st2[4] = {0.f, 0.f, 0.f, 0.f};
+    int cur_n0 = -1;
+    auto flush_stats = [&](int n0f) {
+      // per-warp partials -> smem -> one atomic per column
+      float* red = reinterpret_cast<float*>(smem_raw + (stat_smem - smem_u32(smem_raw)));
+      epi_bar_sync();
+      for (int c = 0; c < a.BN / 32; ++c) {
+        red[(q * 2 + 0) * 128 + c * 32 + lane] = st1[c];
+        red[(q * 2 + 1) * 128 + c * 32 + lane] = st2[c];
+        st1[c] = 0.f; st2[c] = 0.f;
+      }
+      epi_bar_sync();
+      for (int i = et; i < 2 * a.BN; i += 128) {
+        const int which = i / a.BN, col = i % a.BN;
+        const float v = red[(0 * 2 + which) * 128 + col] + red[(1 * 2 + which) * 128 + col] +
+                        red[(2 * 2 + which) * 128 + col] + red[(3 * 2 + which) * 128 + col];
+        atomicAdd(a.stats + which * a.N + n0f + col, v);
+      }
+    };
     uint32_t tcount = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
       int tm_ = tile % a.n_tiles_m;
       const int n0 = (tile / a.n_tiles_m) * a.BN;
+      if (a.stats && n0 != cur_n0) {
+        if (cur_n0 >= 0) flush_stats(cur_n0);
+        cur_n0 = n0;
+      }
       const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
       const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
       const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
@@ -465,10 +492,8 @@ __global__ void __launch_bounds__(192) conv_tc_fwd_v2_k(const __grid_constant__ 
             s1[j] = x;
             s2[j] = x * x;
           }
-          const float t1 = warp_colsum32(s1, lane);
-          const float t2 = warp_colsum32(s2, lane);
-          atomicAdd(a.stats + n0 + c0 + lane, t1);
-          atomicAdd(a.stats + a.N + n0 + c0 + lane, t2);
+          st1[c0 >> 5] += warp_colsum32(s1, lane);
+          st2[c0 >> 5] += warp_colsum32(s2, lane);
         }
       }
       // accumulator stage fully read: hand it back to the MMA warp
@@ -484,6 +509,7 @@ __global__ void __launch_bounds__(192) conv_tc_fwd_v2_k(const __grid_constant__ 
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       }
     }
+    if (a.stats && cur_n0 >= 0) flush_stats(cur_n0);
     if (et == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   tc_fence_before();
@@ -523,6 +549,11 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
   const int iters = tile_end - tile_begin;
   const int cchunks = a.Cin / a.cw;
   const uint32_t ncols = (uint32_t)(a.BN < 32 ? 32 : a.BN);
+  // a group with a single real (tap, chunk) block does not load padding copies: the descriptor's block stride
+  // (LBO) is set to 0 so that every M-block of the MMA aliases block 0; the duplicate rows are discarded.
+  const int nvalid = min(a.mblk, a.total_blocks - group * a.mblk);
+  const int nload = nvalid == 1 ? 1 : a.mblk;
+  const uint32_t lboA = nvalid == 1 ? 0u : ablk_bytes;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < a.stages; ++s) {
@@ -553,8 +584,8 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
           const int th_i = tile % a.g.tiles_h; tile /= a.g.tiles_h;
           const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tile * a.g.TB;
           const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
-          mbar_expect_tx(full0 + 8u * s, stage_bytes);
-          for (int m = 0; m < a.mblk; ++m) {
+          mbar_expect_tx(full0 + 8u * s, (uint32_t)nload * ablk_bytes + b_bytes);
+          for (int m = 0; m < nload; ++m) {
             const int blk = min(group * a.mblk + m, a.total_blocks - 1);
             const int t = blk / cchunks, c = blk % cchunks;
             const int dh = a.taps == 9 ? t / 3 - 1 : 0, dw = a.taps == 9 ? t % 3 - 1 : 0;
@@ -574,7 +605,7 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
           tc_fence_after();
           const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
           for (int k = 0; k < 8; ++k) {  // 16 pixels (K) per MMA = 16 smem rows
-            const uint64_t ad = make_desc(sa + k * 16u * a.cw * 2u, ablk_bytes, a.sboA, a.layoutA);
+            const uint64_t ad = make_desc(sa + k * 16u * a.cw * 2u, lboA, a.sboA, a.layoutA);
             const uint64_t bd = make_desc(sb + k * 16u * a.nw * 2u, bblk_bytes, a.sboB, a.layoutB);
             umma_f16(tmem_base, ad, bd, idesc, (it > 0 || k > 0) ? 1u : 0u);
           }
@@ -781,7 +812,7 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
   if (stages < 2) stages = 2;
   a.stages = stages;
   (void)iters;
-  const size_t smem = (size_t)stages * stage_bytes + out_bytes + 1024 + 256;
+  const size_t smem = (size_t)stages * stage_bytes + out_bytes + 1024 + 256 + 4096;
   CUtensorMap tmA, tmB, tmY;
   const int dA[4] = {Cin, W, H, B}, bA[4] = {a.kc, a.g.TW, a.g.TH, a.g.TB};
   int rc = get_map(X, 4, dA, bA, a.kc * 2, &tmA);
@@ -829,14 +860,18 @@ int crackfl_wgrad_tc(const void* X, const void* dY, float* dW, int B, int H, int
   const int groups = (a.total_blocks + a.mblk - 1) / a.mblk;
   const int ntn = Cout / a.BN;
   a.ntiles = a.g.tiles_w * a.g.tiles_h * a.g.tiles_b;
-  int splits = (148 * 3 + groups * ntn - 1) / (groups * ntn);
+  // one wave of CTAs: two per SM when two pipelines of >= 2 stages fit in shared memory, else one per SM with
+  // up to 3 stages; few, long-running CTAs keep the fp32 atomics of the epilogue (one per output element per
+  // CTA) from serialising in L2
+  const uint32_t stage_bytes = 128u * 128u * 2u + 128u * (uint32_t)a.BN * 2u;
+  int per_sm = (2u * stage_bytes <= 106496u) ? 2 : 1;
+  int stages = per_sm == 2 ? (int)(106496u / stage_bytes) : (int)(200704u / stage_bytes);
+  if (stages > 4) stages = 4;
+  int splits = (148 * per_sm) / (groups * ntn);
   if (splits > a.ntiles) splits = a.ntiles;
   if (splits < 1) splits = 1;
   a.tiles_per_split = (a.ntiles + splits - 1) / splits;
   splits = (a.ntiles + a.tiles_per_split - 1) / a.tiles_per_split;
-  const uint32_t stage_bytes = 128u * 128u * 2u + 128u * (uint32_t)a.BN * 2u;
-  int stages = (int)(196608u / stage_bytes);
-  if (stages > 4) stages = 4;
   if (stages > a.tiles_per_split) stages = a.tiles_per_split;
   if (stages < 1) stages = 1;
   a.stages = stages;
