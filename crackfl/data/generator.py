@@ -175,5 +175,16 @@ def make_datasets(cfg, client_index: int = 0):
     if d.train_image_dir and d.train_mask_dir and not d.synthetic:
         return gen_train_val_data(d.train_image_dir, d.train_mask_dir, t.batch_size, t.image_size, d.split_count,
                                   d.split_seed, d.split_mode, d.workers)
+    backend = t.backend
+    if backend == "auto":
+        try:
+            import torch
+            backend = "b200" if torch.cuda.is_available() else "torch_ref"
+        except Exception:
+            backend = "torch_ref"
+    if backend == "b200":  # generate on the device (csrc/synth.cu): no host rasterisation, no H2D copies
+        from .synthetic_device import DeviceSyntheticDataset
+        return (DeviceSyntheticDataset(d.synthetic_train, t.batch_size, t.image_size, seed=1000 + client_index),
+                DeviceSyntheticDataset(d.synthetic_val, t.batch_size, t.image_size, seed=5000 + client_index))
     return (SyntheticCrackDataset(d.synthetic_train, t.batch_size, t.image_size, seed=1000 + client_index),
             SyntheticCrackDataset(d.synthetic_val, t.batch_size, t.image_size, seed=5000 + client_index))

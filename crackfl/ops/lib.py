@@ -63,6 +63,8 @@ _SIGS = {
     "crackfl_f32_to_bf16": [vp, vp, i64, vp],
     "crackfl_accum_small": [vp, vp, i32, vp],
     "crackfl_publish_delta": [vp, vp, vp, i64, vp],
+    "crackfl_synth_cracks": [vp, vp, i32, i32, i32, C.c_uint, vp],
+    "crackfl_measure_masks": [vp, vp, i32, i32, i32, i32, vp],
     "crackfl_fedagg": [C.POINTER(FedAggParams), i32, vp],
     "crackfl_ipc_export": [vp, vp],
     "crackfl_ipc_open": [vp, C.POINTER(vp)],

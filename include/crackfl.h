@@ -112,6 +112,13 @@ int crackfl_accum_small(float* total, const float* step, int n, cudaStream_t str
 /* staging of a client update as a bf16 delta against the global model (ref: fl_client.py:61-65 upload) */
 int crackfl_publish_delta(const float* local, const float* global, void* out_bf16, long n, cudaStream_t stream);
 
+/* ---- synthetic data + measurement --------------------------------------------------------------- */
+/* ref: dataset of client_fit_model.py:58-59 is not shipped; crack-like uint8 images (B,H,W,3) + masks (B,H,W) */
+int crackfl_synth_cracks(void* img_u8, void* mask_u8, int B, int H, int W, unsigned seed, cudaStream_t stream);
+/* ref: Predict/contour, client_fit_model.py:209-221 + test/Segmentation2.py:118-124 (device half):
+ * out4[b] = {foreground area, boundary pixels, component seeds, sum of probabilities} at threshold (127) */
+int crackfl_measure_masks(const float* prob, float* out4, int B, int H, int W, int threshold, cudaStream_t stream);
+
 /* ---- fused federated aggregation (ref: fl_server.py:92-102 + the gRPC gather/broadcast/poll) ---- */
 #define CRACKFL_MAX_CLIENTS 128
 #define CRACKFL_MAX_OUT 16

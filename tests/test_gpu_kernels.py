@@ -220,3 +220,53 @@ def test_engine_training_reduces_loss_with_graph():
     assert np.isfinite(eng.read_metrics()["loss"])
     p = eng.predict(x)
     assert p.shape == (8, 64, 64) and float(p.min()) >= 0 and float(p.max()) <= 1
+
+
+def test_device_synth_and_measure():
+    from crackfl.data.synthetic_device import synth_crack_batch_device
+    from crackfl.postproc.device_measure import measure_masks_device, measure_masks_reference
+    img, mask = synth_crack_batch_device(8, 128, 128, 7)
+    assert img.shape == (8, 128, 128, 3) and mask.shape == (8, 128, 128)
+    frac = float(mask.float().mean())
+    assert 0.002 < frac < 0.25, frac                      # thin cracks, not empty, not flooded
+    crack = img.float().mean(-1)[mask.bool()].mean(); rest = img.float().mean(-1)[~mask.bool()].mean()
+    assert float(crack) < 0.6 * float(rest)               # cracks are darker than the concrete
+    img2, mask2 = synth_crack_batch_device(8, 128, 128, 7)
+    assert torch.equal(img, img2) and torch.equal(mask, mask2)   # deterministic in the seed
+    prob = (mask.float() * 0.9 + 0.02).contiguous()
+    got = measure_masks_device(prob).cpu().numpy()
+    ref = measure_masks_reference(prob.cpu().numpy())
+    np.testing.assert_allclose(got[:, :3], ref[:, :3], rtol=0, atol=0.5)
+    np.testing.assert_allclose(got[:, 3], ref[:, 3], rtol=1e-4)
+
+
+def test_wide_unet_and_odd_resolution():
+    """North-star extensions: 2x-wide U-Net and a 448-style resolution whose levels are not multiples of 16 px."""
+    from crackfl.models.spec import wide_spec
+    from crackfl.utils.check import engine_vs_oracle, format_report, worst
+    rep = engine_vs_oracle(spec=wide_spec(2), B=2, H=64, W=64, conv_impl="tc", randomize_bn=False)
+    assert abs(rep["loss"][0] - rep["loss"][1]) < 3e-2 * max(1.0, rep["loss"][1]), format_report(rep)
+    rep = engine_vs_oracle(B=2, H=112, W=112, conv_impl="tc", randomize_bn=False)   # 448/4: levels 56,28,14,7
+    assert abs(rep["loss"][0] - rep["loss"][1]) < 3e-2 * max(1.0, rep["loss"][1]), format_report(rep)
+    assert worst(rep)[0] < 8e-2, format_report(rep)
+
+
+def test_server_with_device_aggregator(tmp_path):
+    """Off-box path: gRPC-level server state machine whose aggregation runs in the fused kernel (K16 + K11)."""
+    from crackfl.config import fast_test_config
+    from crackfl.io import weights as wio
+    from crackfl.models.spec import REFERENCE_SPEC as S
+    from crackfl.parallel.device_agg import DeviceAggregator
+    from crackfl.protocol import client as Cl, messages as pb
+    from crackfl.protocol.server import FLServer
+    cfg = fast_test_config()
+    cfg.server.weights_dir = str(tmp_path / "sw"); cfg.server.strategy = "fedavg_weighted"
+    srv = FLServer(cfg, S.init_weights(0), S, aggregator=DeviceAggregator(S, "fedavg_weighted", max_clients=4), log=lambda s: None)
+    for n in ("a", "b"):
+        srv.handle(next(Cl.request_ready(n)))
+    w0 = S.init_weights(0)
+    srv.handle(list(Cl.request_traindone("a", 1, wio.dumps_raw([x + 1 for x in w0]), {"num_samples": 1}, 1 << 30))[0])
+    rep = srv.handle(list(Cl.request_traindone("b", 1, wio.dumps_raw([x + 5 for x in w0]), {"num_samples": 3}, 1 << 30))[0])[0]
+    assert pb.from_config(rep.update_rep.config)["state"] == "RESP_ARY"
+    np.testing.assert_allclose(wio.loads_auto(rep.update_rep.buffer_chunk)[0], w0[0] + 4.0, rtol=1e-5, atol=1e-5)
+    assert srv.history[0]["aggregator"] == "device"
