@@ -36,11 +36,13 @@ SHIMS = {
     "transport_pb2.py": '''
 import os, time as _time
 from crackfl.protocol.messages import *  # noqa: F401,F403  (Scalar, transportRequest, ..., State)
-_scale = float(os.environ.get("REF_SLEEP_SCALE", "1"))
-if _scale != 1.0:
+_mode = os.environ.get("REF_SLEEP_MODE", "shipped")
+if _mode == "nopoll":
+    # keep the registration sleeps (5 s per 'R', 10 s window: they are what makes every client register before the
+    # first one reports, fl_server.py:42,56) but turn the client's 20 s version poll (fl_client.py:141) into a busy poll
     _orig = _time.sleep
     def _sleep(s):
-        _orig(s if s >= 3600 else max(s * _scale, 0.002))
+        _orig(0.002 if s == 20 else s)
     _time.sleep = _sleep
 ''',
     "transport_pb2_grpc.py": '''
@@ -104,7 +106,7 @@ class learning_fit(object):
 RUNNER = "import runpy,sys; sys.argv=[sys.argv[1]]; runpy.run_path(sys.argv[0], run_name='__main__')"
 
 
-def run_once(num_clients: int, payload_mb: float, sleep_scale: float, timeout_s: float) -> dict:
+def run_once(num_clients: int, payload_mb: float, sleep_mode: str, timeout_s: float) -> dict:
     work = tempfile.mkdtemp(prefix="refcomm_")
     shim = os.path.join(work, "shim")
     os.makedirs(shim)
@@ -112,13 +114,13 @@ def run_once(num_clients: int, payload_mb: float, sleep_scale: float, timeout_s:
         with open(os.path.join(shim, fn), "w") as f:
             f.write(src)
     env = dict(os.environ, PYTHONPATH=os.pathsep.join([shim, REPO]), REF_PAYLOAD_MB=str(payload_mb),
-               REF_SLEEP_SCALE=str(sleep_scale), PYTHONUNBUFFERED="1")
+               REF_SLEEP_MODE=sleep_mode, PYTHONUNBUFFERED="1")
     sdir = os.path.join(work, "server")
     os.makedirs(os.path.join(sdir, "server_weights"))
     slog = open(os.path.join(work, "server.log"), "w")
     server = subprocess.Popen([sys.executable, "-c", RUNNER, os.path.join(REF, "fl_server.py")], cwd=sdir, env=env,
                               stdout=slog, stderr=subprocess.STDOUT)
-    time.sleep(1.5 if sleep_scale >= 1 else 1.0)
+    time.sleep(1.5)
     t0 = time.perf_counter()
     clients, logs = [], []
     for i in range(num_clients):
@@ -147,8 +149,10 @@ def run_once(num_clients: int, payload_mb: float, sleep_scale: float, timeout_s:
     for lg in logs + [slog]:
         lg.close()
     stxt = open(os.path.join(work, "server.log")).read()
-    rec = {"clients": num_clients, "payload_mb": payload_mb, "sleep_scale": sleep_scale, "rounds": 5,
-           "t_first_round_s": first_round_t, "t_all_rounds_s": fin_t, "server_errors": stxt.count("Traceback"),
+    per_round = (fin_t - first_round_t) / 4.0 if (fin_t and first_round_t) else None
+    rec = {"clients": num_clients, "payload_mb": payload_mb, "sleep_mode": sleep_mode, "rounds": 5,
+           "t_first_round_s": first_round_t, "t_all_rounds_s": fin_t, "per_round_s_rounds_2_to_5": per_round,
+           "server_errors": stxt.count("Traceback"),
            "clients_exited_cleanly": finished, "label": "reference gRPC + pickle + NumPy path (reference code; proto and "
            "missing modules reconstructed; local fit stubbed out)"}
     if fin_t is None:
@@ -161,12 +165,13 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--clients", default="2")
     ap.add_argument("--payload-mb", default="8.233")
-    ap.add_argument("--sleep-scales", default="0,1", help="1 = as shipped (5/10/20 s), 0 = sleeps removed")
+    ap.add_argument("--sleep-modes", default="nopoll,shipped",
+                    help="shipped = 5/10/20 s sleeps as in the reference; nopoll = 20 s version poll turned into a busy poll")
     ap.add_argument("--timeout", type=float, default=400)
     ap.add_argument("--out", default="baseline/ref_comm_results.json")
     a = ap.parse_args()
     out = []
-    for sc in [float(x) for x in a.sleep_scales.split(",")]:
+    for sc in a.sleep_modes.split(","):
         for n in [int(x) for x in a.clients.split(",")]:
             for mb in [float(x) for x in a.payload_mb.split(",")]:
                 rec = run_once(n, mb, sc, a.timeout)

@@ -42,37 +42,37 @@ def main():
                     continue
                 n = int(mb * 1e6 / 4) // 1024 * 1024
                 fed = OnBoxFederation(clients_per_gpu=K, strategy=strategy, payload=payload, numel=n)
-                g = torch.Generator().manual_seed(1234)
-                glob = torch.randn(n, generator=g)
+                dev = fed.global_arena.device
+                idx = torch.arange(n, device=dev, dtype=torch.float32)
+                glob = torch.sin(idx * 0.37) * 0.5                      # cheap deterministic data, built on the device
                 fed.set_global(glob)
                 ns_all = [[1 + ((r * K + k) % 5) for k in range(K)] for r in range(world)]
-                ups_all = []
-                for r in range(world):
-                    for k in range(K):
-                        gg = torch.Generator().manual_seed(100 + r * K + k)
-                        ups_all.append(glob + 0.01 * torch.randn(n, generator=gg))
+
+                def update_of(cid):
+                    return glob + 0.01 * torch.cos(idx * (0.11 + 0.013 * cid))
                 for k in range(K):
-                    fed.publish(k, ups_all[rank * K + k].to(fed.updates.device))
+                    fed.publish(k, update_of(rank * K + k))
                 ms = fed.aggregate(ns_all[rank], weighted=True)
-                # oracle
+                # oracle (same arithmetic as fl_server.py:92-102 with sample-count weights), evaluated on `dev`
                 flat_ns = np.array([x for row in ns_all for x in row], np.float64)
                 coef = (flat_ns / flat_ns.sum()).astype(np.float32)
-                avg = torch.zeros(n)
-                for c, u in zip(coef, ups_all):
-                    avg += float(c) * u
+                avg = torch.zeros(n, device=dev)
+                for cid, c in enumerate(coef):
+                    avg += float(c) * update_of(cid)
                 if strategy == "fedadam":
                     d = avg - glob
                     m = 0.1 * d; v = 0.01 * d * d
                     want = glob + 1e-2 * m / (v.sqrt() + 1e-3)
                 else:
                     want = avg
-                got = fed.global_arena.detach().cpu()
+                got = fed.global_arena.detach()
                 tol = 3e-4 if payload == "bf16_delta" else 2e-6
                 err = float((got - want).abs().max())
                 ok = err < tol * (10 if strategy == "fedadam" else 1) + 1e-6
+                del avg, want
                 # all ranks bit-identical
                 if world > 1:
-                    chk = got[:4096].clone().to(fed.global_arena.device)
+                    chk = got[:4096].clone()
                     ref = chk.clone()
                     dist.broadcast(ref, 0)
                     same = bool(torch.equal(chk, ref))

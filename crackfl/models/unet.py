@@ -56,6 +56,7 @@ class UNetEngine:
         self.dice_smooth = dice_smooth
         self.conv_impl = conv_impl or default_conv_impl()
         self.cuda_graph = cuda_graph
+        self.side_streams = os.environ.get("CRACKFL_SIDE_STREAM", "1") != "0"
         self.launches_per_step = 0
         self._bufs: Dict[str, torch.Tensor] = {}
         with torch.cuda.device(self.dev):
@@ -66,7 +67,8 @@ class UNetEngine:
             self.eval_prog = self._build_forward(training=False, with_mask=True, prob=False)
             self.pred_prog = self._build_forward(training=False, with_mask=False, prob=True)
         self._graphs: Dict[str, torch.cuda.CUDAGraph] = {}
-        self.launches_per_step = len(self.train_prog) + 2  # + adam tick + metric accumulation
+        self._side_stream = torch.cuda.Stream(self.dev)
+        self.launches_per_step = sum(1 for e in self.train_prog if e[0] is not None) + 2  # + adam tick + metric accumulation
 
     # ------------------------------------------------------------------ allocation
     def _new(self, name: str, shape, dtype=torch.bfloat16) -> torch.Tensor:
@@ -213,7 +215,15 @@ class UNetEngine:
 
     def _wgrad(self, prog, X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co):
         fn = self.lib.crackfl_wgrad_tc if self.conv_impl == "tc" else self.lib.crackfl_wgrad_simt
-        prog.append((fn, (X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co)))
+        prog.append((fn, (X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co), "side"))
+
+    def _dw_bwd(self, prog, g, src, w, bn, resid_t, dz, dwk, B, H, W, C, mode, resid):
+        """Depthwise backward: input gradient on the main stream, weight gradient on the side stream."""
+        if W % 4 == 0 and 128 % (C // 8) == 0:
+            prog.append((self.lib.crackfl_dw3x3_dgrad, (g, src, w, bn, resid_t, dz, B, H, W, C, mode, resid)))
+            prog.append((self.lib.crackfl_dw3x3_wgrad, (g, src, bn, dwk, B, H, W, C, mode), "side"))
+        else:
+            prog.append((self.lib.crackfl_dw3x3_bwd, (g, src, w, bn, resid_t, dz, dwk, B, H, W, C, mode, resid)))
 
     def _layer_iter(self):
         """Yield the spec layers grouped as entry / encoder blocks / decoder blocks / head."""
@@ -352,7 +362,7 @@ class UNetEngine:
             # residual 1x1 conv (at low resolution)
             self._gemm(prog, b(drl), res.name + ".d", 0, 0, b(p + "T"), B, lr_, lrw)
             self._wgrad(prog, b(src_res), b(drl), self.G(res.tensors[0]), B, lr_, lrw, cin, f, 1, 0, f, 1)
-            prog.append((lib.crackfl_colsum, (b(drl), self.G(res.tensors[1]), B * lr_ * lrw, f)))
+            prog.append((lib.crackfl_colsum, (b(drl), self.G(res.tensors[1]), B * lr_ * lrw, f), "side"))
             if j > 0:
                 prog.append((lib.crackfl_down2sum, (b(p + "da0"), b(f"d{j - 1}.s"), b(p + "T"), b(f"d{j - 1}.ds"),
                                                     B, lr_, lrw, cin)))
@@ -370,7 +380,7 @@ class UNetEngine:
             # residual 1x1 s2 conv
             self._gemm(prog, b(dx_next), res.name + ".d", 0, 0, b(p + "Te"), B, r2, rw2)
             self._wgrad(prog, b(xe), b(dx_next), self.G(res.tensors[0]), B, r2, rw2, cin, f, 1, 0, f, 1)
-            prog.append((lib.crackfl_colsum, (b(dx_next), self.G(res.tensors[1]), B * r2 * rw2, f)))
+            prog.append((lib.crackfl_colsum, (b(dx_next), self.G(res.tensors[1]), B * r2 * rw2, f), "side"))
             # max-pool + BN2
             prog.append((lib.crackfl_bn_bwd_reduce, (b(dx_next), b(p + "arg"), b(p + "y2"), self._bnptr(bn2.name),
                                                      self._zptr(bn2.name, "sums"), B, r, rw, f, 2)))
@@ -381,8 +391,8 @@ class UNetEngine:
             self._gemm(prog, b(p + "dy2"), sep2.name + ".d", 0, 0, b(p + "dd2"), B, r, rw)
             self._wgrad(prog, b(p + "d2"), b(p + "dy2"), self.G(sep2.tensors[1]), B, r, rw, f, f, 1, 0, f, 1)
             # depthwise 2 (input = relu(bn1(y1)))
-            prog.append((lib.crackfl_dw3x3_bwd, (b(p + "dd2"), b(p + "y1"), self.P(sep2.tensors[0]), self._bnptr(bn1.name), 0,
-                                                 b(p + "dz1"), self.G(sep2.tensors[0]), B, r, rw, f, 1, 0)))
+            self._dw_bwd(prog, b(p + "dd2"), b(p + "y1"), self.P(sep2.tensors[0]), self._bnptr(bn1.name), 0,
+                         b(p + "dz1"), self.G(sep2.tensors[0]), B, r, rw, f, 1, 0)
             prog.append((lib.crackfl_bn_bwd_reduce, (b(p + "dz1"), 0, b(p + "y1"), self._bnptr(bn1.name),
                                                      self._zptr(bn1.name, "sums"), B, r, rw, f, 0)))
             prog.append((lib.crackfl_bn_bwd_apply, (b(p + "dz1"), 0, b(p + "y1"), self._bnptr(bn1.name),
@@ -393,8 +403,8 @@ class UNetEngine:
             self._wgrad(prog, b(p + "d1"), b(p + "dy1"), self.G(sep1.tensors[1]), B, r, rw, cin, f, 1, 0, f, 1)
             # depthwise 1 (input = relu(x_k)); adds the residual-path gradient on the even pixels
             out = "dz0" if k == 0 else p + "dx"
-            prog.append((lib.crackfl_dw3x3_bwd, (b(p + "dd1"), b(xin), self.P(sep1.tensors[0]), 0, b(p + "Te"), b(out),
-                                                 self.G(sep1.tensors[0]), B, r, rw, cin, 0, 2 if k == 0 else 1)))
+            self._dw_bwd(prog, b(p + "dd1"), b(xin), self.P(sep1.tensors[0]), 0, b(p + "Te"), b(out),
+                         self.G(sep1.tensors[0]), B, r, rw, cin, 0, 2 if k == 0 else 1)
             dx_next = out
         # ---- entry
         r, rw, c0 = self.H // 2, self.W // 2, self.spec.entry
@@ -402,7 +412,9 @@ class UNetEngine:
                                                  B, r, rw, c0, 0)))
         prog.append((lib.crackfl_bn_bwd_apply, (b("dz0"), 0, b("y0"), self._bnptr(bn0.name), self._zptr(bn0.name, "sums"),
                                                 b("dy0"), self.G(bn0.tensors[0]), self.G(bn0.tensors[1]), B, r, rw, c0, 0)))
-        prog.append((lib.crackfl_entry_conv_wgrad, (b("x_u8"), b("dy0"), self.G(conv0.tensors[0]), B, self.H, self.W, c0)))
+        prog.append((lib.crackfl_entry_conv_wgrad, (b("x_u8"), b("dy0"), self.G(conv0.tensors[0]), B, self.H, self.W, c0),
+                     "side"))
+        prog.append((None, None, "join"))
         # ---- optimiser (also zeroes the gradient arena)
         prog.append((lib.crackfl_adam_step, (self.arena.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(),
                                              self.v.data_ptr(), self.step.data_ptr(), self.spec.arena_numel, self.lr,
@@ -414,11 +426,39 @@ class UNetEngine:
 
     # ------------------------------------------------------------------ execution
     def _run(self, prog):
-        st = torch.cuda.current_stream(self.dev).cuda_stream
-        for fn, args in prog:
-            rc = fn(*args, st)
+        """Execute a schedule.  Entries tagged "side" (weight / bias gradients: nothing downstream but Adam reads
+        them) are forked onto a second stream after the main-stream work issued so far, so they overlap with the
+        dgrad chain; "join" makes the main stream wait for all of them.  Works eagerly and under graph capture."""
+        main = torch.cuda.current_stream(self.dev)
+        st = main.cuda_stream
+        side = None
+        forked = False
+        for entry in prog:
+            fn, args = entry[0], entry[1]
+            tag = entry[2] if len(entry) > 2 else None
+            if tag == "join":
+                if forked:
+                    ev = torch.cuda.Event()
+                    ev.record(side)
+                    main.wait_event(ev)
+                    forked = False
+                continue
+            if tag == "side" and self.side_streams:
+                if side is None:
+                    side = self._side_stream
+                ev = torch.cuda.Event()
+                ev.record(main)
+                side.wait_event(ev)
+                rc = fn(*args, side.cuda_stream)
+                forked = True
+            else:
+                rc = fn(*args, st)
             if rc != 0:
                 raise L.KernelError(f"{fn.__name__} failed with cudaError {rc}")
+        if forked:
+            ev = torch.cuda.Event()
+            ev.record(side)
+            main.wait_event(ev)
 
     def _step_body(self, prog, accumulate: bool):
         self.zero_region.zero_()

@@ -39,8 +39,8 @@ def _digest() -> str:
     for fn in sources() + [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cuh", ".h"))] + \
             [os.path.join(ROOT, "include", "crackfl.h")]:
         with open(fn, "rb") as f:
-            h.update(fn.encode() + f.read())
-    h.update(" ".join(ARCH_FLAGS + NVCC_FLAGS).encode())
+            h.update(os.path.relpath(fn, ROOT).encode() + f.read())  # relative: the repo is snapshotted to other paths
+    h.update(" ".join(ARCH_FLAGS + [f for f in NVCC_FLAGS if not f.startswith(ROOT)]).encode())
     return h.hexdigest()
 
 
@@ -50,9 +50,23 @@ def is_current() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile + link under an exclusive file lock; the .so is replaced atomically, so concurrent ranks of a
+    torchrun job can never observe a half-written library."""
     if not force and is_current():
         return LIBPATH
     os.makedirs(LIBDIR, exist_ok=True)
+    import fcntl
+    with open(os.path.join(LIBDIR, ".build.lock"), "w") as lk:
+        fcntl.flock(lk, fcntl.LOCK_EX)
+        try:
+            if not force and is_current():  # another process built it while we waited
+                return LIBPATH
+            return _build_locked(verbose)
+        finally:
+            fcntl.flock(lk, fcntl.LOCK_UN)
+
+
+def _build_locked(verbose: bool) -> str:
     nvcc = nvcc_path()
     objs, logs = [], {}
 
@@ -70,10 +84,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
     with open(os.path.join(LIBDIR, "ptxas.log"), "w") as f:
         for s, l in logs.items():
             f.write(f"==== {os.path.basename(s)}\n{l}\n")
-    cmd = [nvcc, *ARCH_FLAGS, "-shared", "-o", LIBPATH, *objs, "-lcudart"]
+    tmp = LIBPATH + f".tmp.{os.getpid()}"
+    cmd = [nvcc, *ARCH_FLAGS, "-shared", "-o", tmp, *objs, "-lcudart"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    os.replace(tmp, LIBPATH)
     with open(os.path.join(LIBDIR, "build.stamp"), "w") as f:
         f.write(_digest())
     if verbose:

@@ -46,6 +46,8 @@ _SIGS = {
     "crackfl_noalloc_max_channels": [],
     "crackfl_dw3x3_fwd": [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_dw3x3_bwd": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
+    "crackfl_dw3x3_dgrad": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
+    "crackfl_dw3x3_wgrad": [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_pool_add_fwd": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],
     "crackfl_dec_combine_fwd": [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_down2sum": [vp, vp, vp, vp, i32, i32, i32, i32, vp],
@@ -88,7 +90,10 @@ def get_lib(build_if_needed: bool = True) -> C.CDLL:
     if _lib is not None:
         return _lib
     path = _build.LIBPATH
-    if build_if_needed and not _build.is_current():
+    # Rebuild only when the library is missing, or when it is stale AND we are a single process (developer loop).
+    # Ranks of a multi-process job never race to rebuild a library that is already there.
+    multi = int(os.environ.get("WORLD_SIZE", "1")) > 1
+    if build_if_needed and (not os.path.exists(path) or (not multi and not _build.is_current())):
         try:
             _build.build()
         except Exception as e:

@@ -854,6 +854,60 @@ __global__ void __launch_bounds__(TPB, 1) dw3x3_wgrad_v2_k(const __nv_bfloat16* 
   for (int t = 0; t < 9; ++t) block_channel_atomic(dacc[t], c8, sm, dwk + t * C);
 }
 
+
+// v3 depthwise weight gradient: the three tap rows are split over threadIdx.y, so a thread keeps 3x8 accumulators
+// instead of 9x8 (the v2 kernel needed 212 registers and ran one 8-warp block per SM).  blockDim = (128, 3).
+__global__ void __launch_bounds__(384, 1) dw3x3_wgrad_v3_k(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ src,
+                                                           const float* __restrict__ bn, float* __restrict__ dwk, int B, int H,
+                                                           int W, int C, int mode, int strips_per_block) {
+  __shared__ float sm[384 * 8];
+  const int c8 = C >> 3, WS = W / DWS, lanes = 128 / c8;
+  const int tx = threadIdx.x, r = threadIdx.y;
+  const int cv = tx % c8, lane = tx / c8;
+  const long S = (long)B * H * WS;
+  const long s0 = (long)blockIdx.x * strips_per_block;
+  const long s1 = min(S, s0 + strips_per_block);
+  float sc[8], sh[8], dacc[3][8];
+  if (mode == 1) { load8f(bn + cv * 8, sc); load8f(bn + C + cv * 8, sh); }
+#pragma unroll
+  for (int t = 0; t < 3; ++t)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dacc[t][j] = 0.f;
+  for (long s = s0 + lane; s < s1; s += lanes) {
+    const int ws = (int)(s % WS);
+    const int hh = (int)((s / WS) % H);
+    const long b = s / ((long)WS * H);
+    const int w0 = ws * DWS;
+    const int ih = hh + r - 1;
+    if (ih < 0 || ih >= H) continue;
+    float gc[DWS][8], win[DWS + 2][8];
+    const long obase = ((b * H + hh) * (long)W + w0) * c8 + cv;
+#pragma unroll
+    for (int i = 0; i < DWS; ++i) unpack8(ldg16(g + (obase + (long)i * c8) * 8), gc[i]);
+    load_row_window<true>(src, (b * H + ih) * (long)W * c8, w0, W, c8, cv, mode, sc, sh, win);
+#pragma unroll
+    for (int kw = 0; kw < 3; ++kw)
+#pragma unroll
+      for (int i = 0; i < DWS; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dacc[kw][j] = fmaf(win[i + kw][j], gc[i][j], dacc[kw][j]);
+  }
+  const int tid = r * 128 + tx;
+  for (int kw = 0; kw < 3; ++kw) {
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sm[tid * 8 + j] = dacc[kw][j];
+    __syncthreads();
+    for (int i = tid; i < 3 * c8 * 8; i += 384) {
+      const int plane = i / (c8 * 8), rem = i % (c8 * 8);
+      const int cvv = rem >> 3, j = rem & 7;
+      float v = 0.f;
+      for (int l = 0; l < lanes; ++l) v += sm[((plane * 128) + l * c8 + cvv) * 8 + j];
+      atomicAdd(dwk + (long)(plane * 3 + kw) * C + cvv * 8 + j, v);
+    }
+  }
+}
+
 // v2 entry-conv weight gradient: block = 256 threads = (C channels) x (256/C k-groups); 128-pixel chunks staged in smem.
 __global__ void __launch_bounds__(TPB) entry_conv_wgrad_v2_k(const uint8_t* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                                                              float* __restrict__ dw, int B, int H, int W, int C,
@@ -1128,6 +1182,36 @@ int crackfl_head_bwd(const void* s, const float* w, const float* bias, const voi
   head_bwd_k<<<grid_for(P * (C / 8), 148 * 8), TPB, (C + TPB * 8) * sizeof(float), st>>>(
       (const __nv_bfloat16*)s, w, bias, (const uint8_t*)mask_u8, sums, (__nv_bfloat16*)ds, dw, db, B, Hl, Wl, C, use_dice,
       dice_smooth, loss_scale);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+// split backward of the depthwise conv so that the weight gradient can run on a side stream
+int crackfl_dw3x3_dgrad(const void* g, const void* src, const float* w, const float* bn, const void* resid_t, void* dz, int B,
+                        int H, int W, int C, int mode, int resid, cudaStream_t st) {
+  if (W % DWS) return (int)cudaErrorInvalidValue;
+  const long strips = (long)B * H * W / DWS;
+  dw3x3_dgrad_v2_k<<<grid_for(strips * (C / 8), 148 * 8), TPB, 0, st>>>(
+      (const __nv_bfloat16*)g, (const __nv_bfloat16*)src, w, bn, (const __nv_bfloat16*)resid_t, (__nv_bfloat16*)dz, B, H, W, C, mode,
+      resid);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_dw3x3_wgrad(const void* g, const void* src, const float* bn, float* dwk, int B, int H, int W, int C, int mode,
+                        cudaStream_t st) {
+  if (W % DWS || C % 8 || 128 % (C / 8)) return (int)cudaErrorInvalidValue;
+  const long strips = (long)B * H * W / DWS;
+  const int lanes = 128 / (C / 8);
+  long spb = (strips + 148 * 2 - 1) / (148 * 2);
+  spb = ((spb + lanes - 1) / lanes) * lanes;
+  if (spb < lanes) spb = lanes;
+  dw3x3_wgrad_v3_k<<<(int)((strips + spb - 1) / spb), dim3(128, 3), 0, st>>>((const __nv_bfloat16*)g, (const __nv_bfloat16*)src,
+                                                                             bn, dwk, B, H, W, C, mode, (int)spb);
   CK_LAUNCH_CHECK();
   return 0;
 }

@@ -58,6 +58,12 @@ int crackfl_dw3x3_fwd(const void* x, const float* w, const float* bn, void* out,
 int crackfl_dw3x3_bwd(const void* g, const void* src, const float* w, const float* bn, const void* resid_t, void* dz,
                       float* dwk, int B, int H, int W, int C, int mode, int resid, cudaStream_t stream);
 
+/* the same backward split in two launches (input gradient / weight gradient) for concurrent streams; W % 4 == 0 */
+int crackfl_dw3x3_dgrad(const void* g, const void* src, const float* w, const float* bn, const void* resid_t, void* dz, int B,
+                        int H, int W, int C, int mode, int resid, cudaStream_t stream);
+int crackfl_dw3x3_wgrad(const void* g, const void* src, const float* bn, float* dwk, int B, int H, int W, int C, int mode,
+                        cudaStream_t stream);
+
 /* ---- block tails --------------------------------------------------------------------------- */
 /* ref: client_fit_model.py:116-123 MaxPooling2D(3,2,"same") + add(residual) */
 int crackfl_pool_add_fwd(const void* y, const float* bn, const void* res, void* out, void* even_or_null,
