@@ -4,8 +4,10 @@
 Launch: python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 bench/agg_sweep.py [--sizes-mb 1,8,64,...]
 Every rank publishes K client updates with known values; after the fused kernel every rank's global arena must equal
 the NumPy weighted mean (fl_server.py:92-102 semantics), bit-identical on all ranks.  Timing: CUDA events around the
-two launches, max over ranks.  Roofline per GPU: (G-1)/G of the payload in over NVLink + the same out for the
-broadcast; reported against the measured 770 GB/s per direction (B200_PROFILING.md) and, for G=1, against HBM.
+launch(es), ranks released together by a barrier, max over ranks.  Roofline per GPU and direction: the G-1 shards of
+its partial that the other owners pull PLUS its updated shard pushed to G-1 peers = (partial_bytes + 4n)(G-1)/G,
+over the measured 770 GB/s per direction (B200_PROFILING.md; bench/p2p_probe.py measures 750-780 GB/s read and
+~710 GB/s write with this very kernel); for G=1 the bound is HBM traffic over the measured copy bandwidth.
 Works on CPU/Gloo too (host fallback path) so the logic is testable without GPUs.
 """
 import argparse
@@ -85,16 +87,22 @@ def main():
                 # timing
                 times = []
                 for _ in range(a.iters):
+                    if cuda:
+                        torch.cuda.synchronize()
+                    if world > 1:
+                        dist.barrier()   # start every rank together: the max-over-ranks time is then the kernel, not rank skew
                     times.append(fed.aggregate(ns_all[rank], weighted=True))
                 times.sort()
                 best, med = times[0], times[len(times) // 2]
                 pbytes = n * (2 if payload == "bf16_delta" else 4)
                 if world > 1:
-                    link_bytes = pbytes * (world - 1) / world          # inbound partials for my shard
-                    link_bytes_out = n * 4 * (world - 1) / world       # outbound broadcast of my shard
-                    roof_ms = max(link_bytes, link_bytes_out) / 770e9 * 1e3
+                    # bytes that must cross NVLink per GPU per direction for pull-reduce + push-broadcast:
+                    # outbound = my partial's shards served to the G-1 other owners + my updated shard pushed to G-1 peers
+                    # (inbound is the mirror image); NVLink is full duplex, so the bound is one direction's bytes.
+                    link_bytes = (pbytes + n * 4) * (world - 1) / world
+                    roof_ms = link_bytes / 770e9 * 1e3
                 else:
-                    hbm = K * n * 4 + pbytes + pbytes + n * 4 * 3
+                    hbm = K * n * 4 + pbytes + pbytes + n * 4 * 2
                     roof_ms = hbm / 6454.6e9 * 1e3
                 rec = {"payload": payload, "strategy": strategy, "mb": mb, "numel": n, "world": world, "clients_per_gpu": K,
                        "ms_best": best, "ms_median": med, "roofline_ms": roof_ms, "roofline_frac": roof_ms / best if best > 0 else None,

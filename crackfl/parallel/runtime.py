@@ -92,7 +92,7 @@ class OnBoxFederation:
         self.hp = (eta, beta1, beta2, tau)
         self.cuda = torch.cuda.is_available()
         self.epoch = 0
-        self.grid_blocks = grid_blocks
+        self.grid_blocks = int(os.environ.get("CRACKFL_AGG_GRID", grid_blocks))
         self.last_agg_ms = 0.0
         if self.cuda:
             self._init_cuda()
@@ -229,6 +229,7 @@ class OnBoxFederation:
             p.begin, p.end = 0, self.n
             p.rank, p.world, p.epoch = 0, 1, 1
             p.error_flag = p.local_sync = 0
+            p.load_mode = 1
             L.check(lib.crackfl_fedagg(C.byref(p), 148 * 8, st.cuda_stream), "fedagg pre-reduce")
         # (K11-K13) cross-GPU reduce + server update + broadcast, one launch
         q = L.FedAggParams()
@@ -249,6 +250,8 @@ class OnBoxFederation:
         q.begin, q.end = self.begin, self.end
         q.rank, q.world, q.epoch = self.rank, self.world, self.epoch
         q.error_flag, q.local_sync = self.error_flag.data_ptr(), self.local_sync.data_ptr()
+        q.load_mode = int(os.environ.get("CRACKFL_AGG_LOAD_MODE", "0"))
+        q.unroll = int(os.environ.get("CRACKFL_AGG_UNROLL", "4"))
         L.check(lib.crackfl_fedagg(C.byref(q), self.grid_blocks, st.cuda_stream), "fedagg")
         e1.record(st)
         st.synchronize()

@@ -45,6 +45,16 @@ __device__ __forceinline__ uint2 ld_nc_u2(const void* p) {
   asm volatile("ld.global.relaxed.sys.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
   return r;
 }
+__device__ __forceinline__ float4 ld_stream_f4(const float* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint2 ld_stream_u2(const void* p) {
+  uint2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+  return r;
+}
 __device__ __forceinline__ void multimem_st_f4(float* mc, const float4& v) {
   asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
                : "memory");
@@ -69,7 +79,7 @@ __device__ void pad_barrier(const crackfl_fedagg_params& P, int phase) {
   }
 }
 
-template <bool PAYLOAD_BF16, bool OUT_BF16>
+template <bool PAYLOAD_BF16, bool OUT_BF16, int U>
 __global__ void __launch_bounds__(256) fedagg_k(const crackfl_fedagg_params P) {
   if (P.world > 1) {
     // (1) enter: block 0 does the cross-GPU handshake and then releases the local grid
@@ -87,7 +97,7 @@ __global__ void __launch_bounds__(256) fedagg_k(const crackfl_fedagg_params P) {
   }
 
   const long n4_begin = P.begin >> 2, n4_end = P.end >> 2;
-  constexpr int U = 4;  // independent 16-byte loads per client per thread: NVLink latency is ~2 us, keep bytes in flight
+  // U independent 16-byte loads per client per thread: NVLink latency is ~2 us, keep bytes in flight
   const long stride = (long)gridDim.x * blockDim.x;
   for (long i0 = n4_begin + (long)blockIdx.x * blockDim.x + threadIdx.x; i0 < n4_end; i0 += stride * U) {
     float4 acc[U];
@@ -100,7 +110,9 @@ __global__ void __launch_bounds__(256) fedagg_k(const crackfl_fedagg_params P) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const long i = i0 + u * stride;
-          v[u] = i < n4_end ? ld_nc_u2(reinterpret_cast<const uint2*>(P.client[k]) + i) : make_uint2(0u, 0u);
+          v[u] = i < n4_end ? (P.load_mode ? ld_stream_u2(reinterpret_cast<const uint2*>(P.client[k]) + i)
+                                           : ld_nc_u2(reinterpret_cast<const uint2*>(P.client[k]) + i))
+                             : make_uint2(0u, 0u);
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -114,7 +126,9 @@ __global__ void __launch_bounds__(256) fedagg_k(const crackfl_fedagg_params P) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const long i = i0 + u * stride;
-          v[u] = i < n4_end ? ld_nc_f4(reinterpret_cast<const float*>(P.client[k]) + i * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+          v[u] = i < n4_end ? (P.load_mode ? ld_stream_f4(reinterpret_cast<const float*>(P.client[k]) + i * 4)
+                                           : ld_nc_f4(reinterpret_cast<const float*>(P.client[k]) + i * 4))
+                             : make_float4(0.f, 0.f, 0.f, 0.f);
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -129,7 +143,8 @@ __global__ void __launch_bounds__(256) fedagg_k(const crackfl_fedagg_params P) {
       if (i >= n4_end) break;
       float4 nw = acc[u];
       if (P.master) {
-        float4 w = reinterpret_cast<float4*>(P.master)[i];
+        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (P.delta || P.server_opt == 1) w = reinterpret_cast<float4*>(P.master)[i];  // plain FedAvg overwrites it
         if (P.delta) { nw.x += w.x; nw.y += w.y; nw.z += w.z; nw.w += w.w; }
         if (P.server_opt == 1) {
           float4 m = reinterpret_cast<float4*>(P.m)[i];
@@ -187,16 +202,18 @@ int crackfl_fedagg(const crackfl_fedagg_params* p, int grid_blocks, cudaStream_t
   if (p->mc_out && p->out_bf16) return (int)cudaErrorInvalidValue;
   long n4 = (p->end - p->begin) / 4;
   long blocks = (n4 + 256 * 4 - 1) / (256 * 4);
+  if (p->unroll == 8) blocks = (n4 + 256 * 8 - 1) / (256 * 8);
   if (blocks > grid_blocks) blocks = grid_blocks;
   if (blocks < 1) blocks = 1;
   if (p->world > 1) blocks = grid_blocks;  // grid size is part of the exit-barrier arithmetic
   const int g = (int)blocks;
+  const bool u8 = p->unroll == 8;
   if (p->payload_bf16) {
-    if (p->out_bf16) fedagg_k<true, true><<<g, 256, 0, st>>>(*p);
-    else fedagg_k<true, false><<<g, 256, 0, st>>>(*p);
+    if (p->out_bf16) { if (u8) fedagg_k<true, true, 8><<<g, 256, 0, st>>>(*p); else fedagg_k<true, true, 4><<<g, 256, 0, st>>>(*p); }
+    else { if (u8) fedagg_k<true, false, 8><<<g, 256, 0, st>>>(*p); else fedagg_k<true, false, 4><<<g, 256, 0, st>>>(*p); }
   } else {
-    if (p->out_bf16) fedagg_k<false, true><<<g, 256, 0, st>>>(*p);
-    else fedagg_k<false, false><<<g, 256, 0, st>>>(*p);
+    if (p->out_bf16) { if (u8) fedagg_k<false, true, 8><<<g, 256, 0, st>>>(*p); else fedagg_k<false, true, 4><<<g, 256, 0, st>>>(*p); }
+    else { if (u8) fedagg_k<false, false, 8><<<g, 256, 0, st>>>(*p); else fedagg_k<false, false, 4><<<g, 256, 0, st>>>(*p); }
   }
   CK_LAUNCH_CHECK();
   return 0;

@@ -149,6 +149,8 @@ typedef struct {
   uint32_t epoch;           /* 1,2,3,... monotonically per call */
   int* error_flag;          /* set non-zero on spin timeout */
   uint32_t* local_sync;     /* [2] u32 in local memory, zero-initialised once */
+  int unroll;               /* independent 16-byte loads per client per thread: 4 (default when 0) or 8 */
+  int load_mode;            /* 0: ld.relaxed.sys (default), 1: ld.global.nc.L1::no_allocate (updates are immutable during the launch) */
 } crackfl_fedagg_params;
 int crackfl_fedagg(const crackfl_fedagg_params* p, int grid_blocks, cudaStream_t stream);
 int crackfl_ipc_export(void* dev_ptr, void* handle_out64);
