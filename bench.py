@@ -159,9 +159,14 @@ def main():
             eng.mask_u8.copy_(dy[i % NB], non_blocking=True)
             eng.train_step()
 
+        eng.prefetch(hx[0], hy[0])
+
         def step_e2e(i):
-            eng.train_step(hx[i % NB], hy[i % NB])       # public API: pinned H2D + graph replay
-            return float(eng.step_loss().item())          # D2H read of the step's loss
+            # public API: batch i was handed to prefetch() (pinned H2D on the copy stream); start the copy of batch
+            # i+1 so that it overlaps this step's compute, train on batch i, read its loss back (D2H, synchronises)
+            eng.train_step_prefetched()
+            eng.prefetch(hx[(i + 1) % NB], hy[(i + 1) % NB])
+            return float(eng.step_loss().item())
 
         def round_end():
             # FedAvg round boundary: publish the local fit, fused aggregate+broadcast kernel, reload, fresh Adam

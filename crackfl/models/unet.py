@@ -500,6 +500,32 @@ class UNetEngine:
                 # the capture itself did not execute anything; fall through to replay
             g.replay()
 
+    def profile_step(self, repeats: int = 3):
+        """In-situ per-kernel timing: the train schedule run eagerly on ONE stream with a CUDA event after every
+        launch (warm L2, real producer/consumer adjacency - unlike ncu's serialised cold-cache replay).
+        Returns [(kernel name, ms)] averaged over ``repeats`` steps."""
+        names = [e[0].__name__ for e in self.train_prog if e[0] is not None]
+        acc = [0.0] * len(names)
+        st = torch.cuda.current_stream(self.dev)
+        for rep in range(repeats + 1):
+            self.zero_region.zero_()
+            evs = [torch.cuda.Event(enable_timing=True) for _ in range(len(names) + 1)]
+            evs[0].record(st)
+            i = 0
+            for e in self.train_prog:
+                if e[0] is None:
+                    continue
+                rc = e[0](*e[1], st.cuda_stream)
+                if rc:
+                    raise L.KernelError(f"{e[0].__name__}: {rc}")
+                i += 1
+                evs[i].record(st)
+            st.synchronize()
+            if rep > 0:
+                for k in range(len(names)):
+                    acc[k] += evs[k].elapsed_time(evs[k + 1]) / repeats
+        return list(zip(names, acc))
+
     # ------------------------------------------------------------------ public API
     def load_weights(self, weights: Sequence[np.ndarray]):
         flat = torch.from_numpy(wio.flatten(weights, self.spec))
@@ -538,6 +564,39 @@ class UNetEngine:
     def train_step(self, x_u8=None, y_u8=None):
         if x_u8 is not None:
             self.set_batch(x_u8, y_u8)
+        self._exec("train", self.train_prog, True)
+
+    # -- input prefetch: the H2D copy of batch i+1 runs on a copy stream while batch i trains -----------------
+    def prefetch(self, x_u8, y_u8):
+        """Start the host->device copy of the NEXT batch (pinned host tensors) on the copy stream."""
+        if not hasattr(self, "_copy_stream"):
+            self._copy_stream = torch.cuda.Stream(self.dev)
+            self._stage = [(torch.empty_like(self.x_u8), torch.empty_like(self.mask_u8)) for _ in range(2)]
+            self._stage_ev = [torch.cuda.Event(), torch.cuda.Event()]
+            self._stage_free = [torch.cuda.Event(), torch.cuda.Event()]
+            self._stage_i = 0
+            self._stage_pending = None
+        i = self._stage_i
+        sx, sy = self._stage[i]
+        with torch.cuda.stream(self._copy_stream):
+            self._copy_stream.wait_event(self._stage_free[i])  # the step that consumed this slot has read it
+            sx.copy_(torch.as_tensor(x_u8).view(sx.shape), non_blocking=True)
+            sy.copy_(torch.as_tensor(y_u8).reshape(sy.shape), non_blocking=True)
+            self._stage_ev[i].record(self._copy_stream)
+        self._stage_pending = i
+        self._stage_i ^= 1
+
+    def train_step_prefetched(self):
+        """Train on the batch handed to the last ``prefetch`` call (device-to-device move of 4 MB, then the graph)."""
+        i = self._stage_pending
+        if i is None:
+            raise RuntimeError("prefetch() a batch first")
+        main = torch.cuda.current_stream(self.dev)
+        main.wait_event(self._stage_ev[i])
+        self.x_u8.copy_(self._stage[i][0], non_blocking=True)
+        self.mask_u8.copy_(self._stage[i][1], non_blocking=True)
+        self._stage_free[i].record(main)
+        self._stage_pending = None
         self._exec("train", self.train_prog, True)
 
     def eval_step(self, x_u8=None, y_u8=None):

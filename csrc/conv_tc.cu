@@ -300,7 +300,11 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* tm, uint32_t src
                ::"l"(reinterpret_cast<uint64_t>(tm)), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
                : "memory");
 }
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+// 8 epilogue warps: thin-K layers (1x1 convs, K = 32..64) are epilogue-bound, so two warps share each TMEM lane
+// quarter and split the accumulator columns between them.
+constexpr int EPI_WARPS = 8;
+constexpr int EPI_THREADS = EPI_WARPS * 32;
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 struct ConvArgs2 {
   const float* bias;
@@ -314,7 +318,7 @@ struct ConvArgs2 {
   TileGeom g;
 };
 
-__global__ void __launch_bounds__(192) conv_tc_fwd_v2_k(const __grid_constant__ CUtensorMap tmA,
+__global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __grid_constant__ CUtensorMap tmA,
                                                         const __grid_constant__ CUtensorMap tmB,
                                                         const __grid_constant__ CUtensorMap tmY, const ConvArgs2 a) {
   extern __shared__ uint8_t smem_raw[];
@@ -327,7 +331,7 @@ __global__ void __launch_bounds__(192) conv_tc_fwd_v2_k(const __grid_constant__ 
   const uint32_t full0 = bar_base, empty0 = bar_base + 8u * a.stages;
   const uint32_t tfull0 = bar_base + 16u * a.stages, tempty0 = tfull0 + 16u;
   const uint32_t tptr = tempty0 + 16u;
-  const uint32_t stat_smem = tptr + 16u;  // 4 warps x 2 x 128 floats
+  const uint32_t stat_smem = tptr + 16u;  // EPI_WARPS x 2 x 128 floats
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kchunks = a.Cin / a.kc;
   const int iters = a.taps * kchunks;
@@ -341,7 +345,7 @@ __global__ void __launch_bounds__(192) conv_tc_fwd_v2_k(const __grid_constant__ 
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull0 + 8u * s, 1);
-      mbar_init(tempty0 + 8u * s, 4);  // one arrival per epilogue warp
+      mbar_init(tempty0 + 8u * s, EPI_WARPS);  // one arrival per epilogue warp
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     tma_prefetch_desc(&tmA);
@@ -400,10 +404,12 @@ __global__ void __launch_bounds__(192) conv_tc_fwd_v2_k(const __grid_constant__ 
       }
     }
   } else {
-    const int q = warp & 3;
+    const int q = warp & 3;          // TMEM lane quarter this warp may read
+    const int eg = (warp - 2) >> 2;  // column group: chunks eg, eg+2, ...
+    const int ew = eg * 4 + q;       // 0..7
     const int r = q * 32 + lane;
     const int tw = r % a.g.TW, th = (r / a.g.TW) % a.g.TH, tb = r / (a.g.TW * a.g.TH);
-    const int et = threadIdx.x - 64;  // 0..127 among the epilogue threads
+    const int et = threadIdx.x - 64;  // 0..255 among the epilogue threads
     const int nsub = a.BN / a.sub_w;
     const uint32_t sub_bytes = 128u * (uint32_t)a.sub_w * 2u;
     const uint32_t row_bytes = (uint32_t)a.sub_w * 2u;
@@ -417,15 +423,16 @@ __global__ void __launch_bounds__(192) conv_tc_fwd_v2_k(const __grid_constant__ 
       float* red = reinterpret_cast<float*>(smem_raw + (stat_smem - smem_u32(smem_raw)));
       epi_bar_sync();
       for (int c = 0; c < a.BN / 32; ++c) {
-        red[(q * 2 + 0) * 128 + c * 32 + lane] = st1[c];
-        red[(q * 2 + 1) * 128 + c * 32 + lane] = st2[c];
+        red[(ew * 2 + 0) * 128 + c * 32 + lane] = st1[c];
+        red[(ew * 2 + 1) * 128 + c * 32 + lane] = st2[c];
         st1[c] = 0.f; st2[c] = 0.f;
       }
       epi_bar_sync();
-      for (int i = et; i < 2 * a.BN; i += 128) {
+      for (int i = et; i < 2 * a.BN; i += EPI_THREADS) {
         const int which = i / a.BN, col = i % a.BN;
-        const float v = red[(0 * 2 + which) * 128 + col] + red[(1 * 2 + which) * 128 + col] +
-                        red[(2 * 2 + which) * 128 + col] + red[(3 * 2 + which) * 128 + col];
+        float v = 0.f;
+#pragma unroll
+        for (int w8 = 0; w8 < EPI_WARPS; ++w8) v += red[(w8 * 2 + which) * 128 + col];
         atomicAdd(a.stats + which * a.N + n0f + col, v);
       }
     };
@@ -450,7 +457,7 @@ __global__ void __launch_bounds__(192) conv_tc_fwd_v2_k(const __grid_constant__ 
       epi_bar_sync();
       mbar_wait(tfull0 + 8u * as, aph);
       tc_fence_after();
-      for (int c0 = 0; c0 < a.BN; c0 += 32) {
+      for (int c0 = eg * 32; c0 < a.BN; c0 += 64) {
         uint32_t raw[32];
         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * (uint32_t)a.BN + (uint32_t)c0, raw);
         float v[32];
@@ -807,12 +814,12 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
   const int iters = taps * (Cin / a.kc);
   const uint32_t stage_bytes = 128u * a.kc * 2u + (uint32_t)a.BN * a.kc * 2u;
   const uint32_t out_bytes = 2u * 128u * (uint32_t)a.BN * 2u;
-  int stages = (int)((106496u - out_bytes) / stage_bytes);  // ~104 KB per CTA -> two CTAs per SM
+  int stages = (int)((102400u - out_bytes) / stage_bytes);  // ~104 KB per CTA -> two CTAs per SM
   if (stages > 8) stages = 8;
   if (stages < 2) stages = 2;
   a.stages = stages;
   (void)iters;
-  const size_t smem = (size_t)stages * stage_bytes + out_bytes + 1024 + 256 + 4096;
+  const size_t smem = (size_t)stages * stage_bytes + out_bytes + 1024 + 256 + 8192;
   CUtensorMap tmA, tmB, tmY;
   const int dA[4] = {Cin, W, H, B}, bA[4] = {a.kc, a.g.TW, a.g.TH, a.g.TB};
   int rc = get_map(X, 4, dA, bA, a.kc * 2, &tmA);
@@ -836,7 +843,7 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
   const int total = a.n_tiles_m * a.n_tiles_n;
   int grid = 2 * g_num_sms;
   if (grid > total) grid = total;
-  conv_tc_fwd_v2_k<<<grid, 192, smem, st>>>(tmA, tmB, tmY, a);
+  conv_tc_fwd_v2_k<<<grid, 64 + EPI_THREADS, smem, st>>>(tmA, tmB, tmY, a);
   CK_LAUNCH_CHECK();
   return 0;
 }

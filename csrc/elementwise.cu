@@ -141,31 +141,42 @@ __global__ void bn_eval_prepare_k(const float* __restrict__ gamma, const float* 
 }
 
 // out = [relu](y*scale+shift); optional compact copy of the even pixels (input of the 1x1 s2 residual conv)
-__global__ void __launch_bounds__(TPB) bn_act_k(const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
-                                                __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ even,
-                                                int B, int H, int W, int C, int relu) {
+__global__ void __launch_bounds__(TPB, 4) bn_act_k(const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
+                                                   __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ even,
+                                                   int B, int H, int W, int C, int relu) {
   const int c8 = C >> 3;
   const long total = (long)B * H * W * c8;
-  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long)gridDim.x * blockDim.x) {
-    const int cv = (int)(g % c8);
-    float f[8], sc[8], sh[8];
-    unpack8(ldg16(y + g * 8), f);
-    load8f(bn + cv * 8, sc);
-    load8f(bn + C + cv * 8, sh);
+  const long stride = (long)gridDim.x * blockDim.x;  // multiple of c8: a thread keeps its channel vector
+  const long g0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int cv = (int)(g0 % c8);
+  float sc[8], sh[8];
+  load8f(bn + cv * 8, sc);
+  load8f(bn + C + cv * 8, sh);
+  for (long g = g0; g < total; g += 2 * stride) {
+    const long g2 = g + stride;
+    const bool has2 = g2 < total;
+    float f[2][8];
+    unpack8(ldg16(y + g * 8), f[0]);
+    if (has2) unpack8(ldg16(y + g2 * 8), f[1]);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      f[j] = fmaf(f[j], sc[j], sh[j]);
-      if (relu) f[j] = fmaxf(f[j], 0.f);
-    }
-    const uint4 v = pack8(f);
-    stg16(out + g * 8, v);
-    if (even) {
-      long p = g / c8;
-      const int w = (int)(p % W); p /= W;
-      const int h = (int)(p % H);
-      const int b = (int)(p / H);
-      if (!(h & 1) && !(w & 1))
-        stg16(even + ((((long)b * (H >> 1) + (h >> 1)) * (W >> 1) + (w >> 1)) * c8 + cv) * 8, v);
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !has2) break;
+      const long gi = u ? g2 : g;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        f[u][j] = fmaf(f[u][j], sc[j], sh[j]);
+        if (relu) f[u][j] = fmaxf(f[u][j], 0.f);
+      }
+      const uint4 v = pack8(f[u]);
+      stg16(out + gi * 8, v);
+      if (even) {
+        long p = gi / c8;
+        const int w = (int)(p % W); p /= W;
+        const int h = (int)(p % H);
+        const int b = (int)(p / H);
+        if (!(h & 1) && !(w & 1))
+          stg16(even + ((((long)b * (H >> 1) + (h >> 1)) * (W >> 1) + (w >> 1)) * c8 + cv) * 8, v);
+      }
     }
   }
 }
@@ -472,37 +483,46 @@ __device__ __forceinline__ void load_dz(const __nv_bfloat16* __restrict__ g, con
   }
 }
 
-// sums = [sum dz  C][sum dz*xhat  C]
+// sums = [sum dz  C][sum dz*(y-mean)  C]   (centred moment: no cancellation; apply multiplies by invstd)
 template <int MODE>
-__global__ void __launch_bounds__(TPB) bn_bwd_reduce_k(const __nv_bfloat16* __restrict__ g, const uint8_t* __restrict__ arg,
+__global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : 3) bn_bwd_reduce_k(const __nv_bfloat16* __restrict__ g, const uint8_t* __restrict__ arg,
                                                        const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
                                                        float* __restrict__ sums, long P, int H, int W, int C,
                                                        int pix_per_block) {
   __shared__ float sm[TPB * 8];
   const int c8 = C >> 3, lanes = TPB / c8;
   const int cv = threadIdx.x % c8, lane = threadIdx.x / c8;
-  float sc[8], sh[8], mu[8], is[8], s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  load8f(bn + cv * 8, sc); load8f(bn + C + cv * 8, sh);
-  load8f(bn + 2 * C + cv * 8, mu); load8f(bn + 3 * C + cv * 8, is);
+  float sc[8], sh[8], mu[8], s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (MODE == 1) { load8f(bn + cv * 8, sc); load8f(bn + C + cv * 8, sh); }
+  load8f(bn + 2 * C + cv * 8, mu);
   const long p0 = (long)blockIdx.x * pix_per_block;
   const long p1 = min(P, p0 + pix_per_block);
-  for (long p = p0 + lane; p < p1; p += lanes) {
-    float yv[8], dz[8];
-    unpack8(ldg16(y + (p * c8 + cv) * 8), yv);
-    load_dz<MODE>(g, arg, p, cv, c8, H, W, yv, sc, sh, dz);
+  for (long p = p0 + lane; p < p1; p += 2 * lanes) {
+    const long q = p + lanes;
+    const bool has2 = q < p1;
+    float yv[2][8], dz[2][8];
+    unpack8(ldg16(y + (p * c8 + cv) * 8), yv[0]);
+    if (has2) unpack8(ldg16(y + (q * c8 + cv) * 8), yv[1]);
+    load_dz<MODE>(g, arg, p, cv, c8, H, W, yv[0], sc, sh, dz[0]);
+    if (has2) load_dz<MODE>(g, arg, q, cv, c8, H, W, yv[1], sc, sh, dz[1]);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      s1[j] += dz[j];
-      s2[j] = fmaf(dz[j], (yv[j] - mu[j]) * is[j], s2[j]);
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !has2) break;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s1[j] += dz[u][j];
+        s2[j] = fmaf(dz[u][j], yv[u][j] - mu[j], s2[j]);
+      }
     }
   }
   block_channel_atomic(s1, c8, sm, sums);
   block_channel_atomic(s2, c8, sm, sums + C);
 }
 
-// dy = scale * (dz - mean(dz) - xhat * mean(dz*xhat));  block 0 also emits dgamma / dbeta.
+// dy = scale * (dz - mean(dz) - xhat * mean(dz*xhat)), folded into dy = A*dz + Bc*y + Cc per channel;
+// block 0 also emits dgamma = sum dz*xhat and dbeta = sum dz.
 template <int MODE>
-__global__ void __launch_bounds__(TPB) bn_bwd_apply_k(const __nv_bfloat16* __restrict__ g, const uint8_t* __restrict__ arg,
+__global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : 3) bn_bwd_apply_k(const __nv_bfloat16* __restrict__ g, const uint8_t* __restrict__ arg,
                                                       const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
                                                       const float* __restrict__ sums, __nv_bfloat16* __restrict__ dy,
                                                       float* __restrict__ dgamma, float* __restrict__ dbeta, long P, int H,
@@ -512,25 +532,43 @@ __global__ void __launch_bounds__(TPB) bn_bwd_apply_k(const __nv_bfloat16* __res
   if (blockIdx.x == 0) {
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
       dbeta[c] = sums[c];
-      dgamma[c] = sums[C + c];
+      dgamma[c] = bn[3 * C + c] * sums[C + c];
     }
   }
   const long total = P * c8;
-  for (long gi = (long)blockIdx.x * blockDim.x + threadIdx.x; gi < total; gi += (long)gridDim.x * blockDim.x) {
-    const int cv = (int)(gi % c8);
-    const long p = gi / c8;
-    float sc[8], sh[8], mu[8], is[8], a1[8], a2[8], yv[8], dz[8];
+  const long stride = (long)gridDim.x * blockDim.x;  // multiple of c8: a thread keeps its channel vector
+  const long g0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int cv = (int)(g0 % c8);
+  float sc[8], sh[8], A[8], Bc[8], Cc[8];
+  {
+    float mu[8], is[8], a1[8], a2[8];
     load8f(bn + cv * 8, sc); load8f(bn + C + cv * 8, sh);
     load8f(bn + 2 * C + cv * 8, mu); load8f(bn + 3 * C + cv * 8, is);
     load8f(sums + cv * 8, a1); load8f(sums + C + cv * 8, a2);
-    unpack8(ldg16(y + gi * 8), yv);
-    load_dz<MODE>(g, arg, p, cv, c8, H, W, yv, sc, sh, dz);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float xh = (yv[j] - mu[j]) * is[j];
-      dz[j] = sc[j] * (dz[j] - a1[j] * invn - xh * a2[j] * invn);
+      const float m1 = a1[j] * invn;                               // mean(dz)
+      const float m2 = is[j] * a2[j] * invn;                       // mean(dz * xhat)
+      A[j] = sc[j];
+      Bc[j] = -sc[j] * is[j] * m2;
+      Cc[j] = -sc[j] * m1 - Bc[j] * mu[j];
     }
-    stg16(dy + gi * 8, pack8(dz));
+  }
+  for (long gi = g0; gi < total; gi += 2 * stride) {
+    const long gj = gi + stride;
+    const bool has2 = gj < total;
+    float yv[2][8], dz[2][8];
+    unpack8(ldg16(y + gi * 8), yv[0]);
+    if (has2) unpack8(ldg16(y + gj * 8), yv[1]);
+    load_dz<MODE>(g, arg, gi / c8, cv, c8, H, W, yv[0], sc, sh, dz[0]);
+    if (has2) load_dz<MODE>(g, arg, gj / c8, cv, c8, H, W, yv[1], sc, sh, dz[1]);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !has2) break;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) dz[u][j] = fmaf(A[j], dz[u][j], fmaf(Bc[j], yv[u][j], Cc[j]));
+      stg16(dy + (u ? gj : gi) * 8, pack8(dz[u]));
+    }
   }
 }
 

@@ -24,7 +24,7 @@ int crackfl_entry_conv_fwd(const void* x_u8, const float* w, const float* bias, 
 int crackfl_entry_conv_wgrad(const void* x_u8, const void* dy, float* dw, int B, int H, int W, int C, cudaStream_t stream);
 
 /* ---- batch normalisation (ref: client_fit_model.py:101,110,114,130,134; eps 1e-3, momentum .99) ---- */
-/* stats = [sum C][sumsq C]; bn = [scale C][shift C][mean C][invstd C]; sums = [sum dz C][sum dz*xhat C] */
+/* stats = [sum C][sumsq C]; bn = [scale C][shift C][mean C][invstd C]; sums = [sum dz C][sum dz*(y-mean) C] */
 int crackfl_bn_stats(const void* y, float* stats, long P, int C, cudaStream_t stream);
 int crackfl_bn_finalize(const float* stats, const float* gamma, const float* beta, float* run_mean, float* run_var,
                         float* bn, int C, float count, float eps, float momentum, cudaStream_t stream);
