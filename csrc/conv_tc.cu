@@ -528,6 +528,252 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
 }
 
 // ----------------------------------------------------------------------------------------------------------
+// v3 ("halo"): 3x3 convs with Cin % 64 == 0.  v1/v2 reload the shifted 128-pixel box for each of the 9 taps, so the
+// L2 -> shared-memory traffic of the activations is 9x the tensor; ncu showed the kernel bound by exactly that.  Here
+// ONE (16+2) x (8+2)-pixel halo tile per 64-channel chunk is loaded and the nine taps are nine shared-memory matrix
+// descriptors into it (start address shifted by (kh*10 + kw) pixels, 8-row group stride = one halo row), i.e. a real
+// implicit GEMM: activation traffic drops from 9x to 1.4x.  Weight tiles stream through their own ring.
+struct ConvArgs3 {
+  const float* bias;
+  const __nv_bfloat16* add;
+  float* stats;
+  int B, H, W, Cin, N, taps;
+  int BN, kc, stages;
+  int sub_w;
+  int n_tiles_m, n_tiles_n;
+  uint32_t layout, sbo;
+  int base_off;              // set the descriptor's base_offset field from the start address
+  TileGeom g;
+};
+
+__global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __grid_constant__ CUtensorMap tmA,
+                                                        const __grid_constant__ CUtensorMap tmB,
+                                                        const __grid_constant__ CUtensorMap tmY, const ConvArgs3 a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  // A ring: 2 halo tiles of (TH+2) x (TW+2) = 18 x 10 pixels x 64 channels (23040 B, padded to 23552);
+  // B ring: a.stages weight tiles [BN][64] (one per (chunk, tap)); then 2 output staging buffers.
+  constexpr uint32_t HALO_W = 10u, HALO_ROWS = 180u, A_STAGE = 23552u, A_BYTES = HALO_ROWS * 128u;
+  const uint32_t b_bytes = (uint32_t)a.BN * 64u * 2u;
+  const uint32_t bring = base + 2u * A_STAGE;
+  const uint32_t out_bytes = 128u * (uint32_t)a.BN * 2u;
+  const uint32_t out0 = bring + a.stages * b_bytes;
+  const uint32_t bar_base = out0 + 2u * out_bytes;
+  const uint32_t fullA0 = bar_base, emptyA0 = bar_base + 16u;
+  const uint32_t full0 = bar_base + 32u, empty0 = full0 + 8u * a.stages;
+  const uint32_t tfull0 = empty0 + 8u * a.stages, tempty0 = tfull0 + 16u;
+  const uint32_t tptr = tempty0 + 16u;
+  const uint32_t stat_smem = tptr + 16u;  // EPI_WARPS x 2 x 128 floats
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kchunks = a.Cin / 64;
+  const int total_tiles = a.n_tiles_m * a.n_tiles_n;
+  const uint32_t ncols = (uint32_t)(2 * a.BN < 32 ? 32 : 2 * a.BN);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < a.stages; ++s) {
+      mbar_init(full0 + 8u * s, 1);
+      mbar_init(empty0 + 8u * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(fullA0 + 8u * s, 1);
+      mbar_init(emptyA0 + 8u * s, 1);
+      mbar_init(tfull0 + 8u * s, 1);
+      mbar_init(tempty0 + 8u * s, EPI_WARPS);  // one arrival per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmY);
+  }
+  if (warp == 1) tmem_alloc(tptr, ncols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tptr));
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t ia = 0, ib = 0;  // ring positions: halo tiles / weight tiles
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int tm_ = tile % a.n_tiles_m;
+        const int n0 = (tile / a.n_tiles_m) * a.BN;
+        const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
+        const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
+        const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
+        for (int c = 0; c < kchunks; ++c, ++ia) {
+          const uint32_t sa = ia & 1u, pha = (ia >> 1) & 1u;
+          mbar_wait(emptyA0 + 8u * sa, pha ^ 1u);
+          mbar_expect_tx(fullA0 + 8u * sa, A_BYTES);
+          tma_load_4d(base + sa * A_STAGE, &tmA, fullA0 + 8u * sa, c * 64, w0 - 1, h0 - 1, b0);  // halo: zero fill = padding
+          for (int t = 0; t < 9; ++t, ++ib) {
+            const uint32_t s = ib % a.stages, ph = (ib / a.stages) & 1u;
+            mbar_wait(empty0 + 8u * s, ph ^ 1u);
+            mbar_expect_tx(full0 + 8u * s, b_bytes);
+            tma_load_2d(bring + s * b_bytes, &tmB, full0 + 8u * s, t * a.Cin + c * 64, n0);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(128, a.BN, 0, 0);
+      uint32_t ia = 0, ib = 0, tcount = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+        const uint32_t as = tcount & 1u, aph = (tcount >> 1) & 1u;
+        mbar_wait(tempty0 + 8u * as, aph ^ 1u);
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + as * (uint32_t)a.BN;
+        for (int c = 0; c < kchunks; ++c, ++ia) {
+          const uint32_t sa = ia & 1u, pha = (ia >> 1) & 1u;
+          mbar_wait(fullA0 + 8u * sa, pha);
+          tc_fence_after();
+          const uint32_t halo = base + sa * A_STAGE;
+          for (int t = 0; t < 9; ++t, ++ib) {
+            const uint32_t s = ib % a.stages, ph = (ib / a.stages) & 1u;
+            mbar_wait(full0 + 8u * s, ph);
+            tc_fence_after();
+            // tap (kh,kw): output pixel (th,tw) reads halo pixel (th+kh, tw+kw).  One 8-row swizzle group = the 8
+            // pixels of one tile row, groups HALO_W*128 bytes apart: the shifted window is still a canonical
+            // K-major SW128 operand, it just starts (kh*HALO_W + kw) rows into the halo tile.
+            const uint32_t astart = halo + (uint32_t)((t / 3) * HALO_W + (t % 3)) * 128u;
+            uint64_t ad = make_desc(astart, 16, HALO_W * 128u, 2u);
+            if (a.base_off) ad |= (uint64_t)((astart >> 7) & 7u) << 49;
+            const uint64_t bd = make_desc(bring + s * b_bytes, 16, 1024u, 2u);
+            for (int k = 0; k < 4; ++k)
+              umma_f16(tacc, ad + 2u * k, bd + 2u * k, idesc, (c > 0 || t > 0 || k > 0) ? 1u : 0u);
+            umma_commit(empty0 + 8u * s);
+          }
+          umma_commit(emptyA0 + 8u * sa);
+        }
+        umma_commit(tfull0 + 8u * as);
+      }
+    }
+  } else {
+    const int q = warp & 3;          // TMEM lane quarter this warp may read
+    const int eg = (warp - 2) >> 2;  // column group: chunks eg, eg+2, ...
+    const int ew = eg * 4 + q;       // 0..7
+    const int r = q * 32 + lane;
+    const int tw = r % a.g.TW, th = (r / a.g.TW) % a.g.TH, tb = r / (a.g.TW * a.g.TH);
+    const int et = threadIdx.x - 64;  // 0..255 among the epilogue threads
+    const int nsub = a.BN / a.sub_w;
+    const uint32_t sub_bytes = 128u * (uint32_t)a.sub_w * 2u;
+    const uint32_t row_bytes = (uint32_t)a.sub_w * 2u;
+    // BN statistics are accumulated per CTA across all its tiles of one n-tile (registers: lane <-> column) and
+    // flushed with 2*BN atomics per CTA instead of 8*BN per tile: the per-tile version serialised thousands of
+    // same-address atomics in L2 and doubled the kernel time.
+    float st1[4] = {0.f, 0.f, 0.f, 0.f}, st2[4] = {0.f, 0.f, 0.f, 0.f};
+    int cur_n0 = -1;
+    auto flush_stats = [&](int n0f) {
+      // per-warp partials -> smem -> one atomic per column
+      float* red = reinterpret_cast<float*>(smem_raw + (stat_smem - smem_u32(smem_raw)));
+      epi_bar_sync();
+      for (int c = 0; c < a.BN / 32; ++c) {
+        red[(ew * 2 + 0) * 128 + c * 32 + lane] = st1[c];
+        red[(ew * 2 + 1) * 128 + c * 32 + lane] = st2[c];
+        st1[c] = 0.f; st2[c] = 0.f;
+      }
+      epi_bar_sync();
+      for (int i = et; i < 2 * a.BN; i += EPI_THREADS) {
+        const int which = i / a.BN, col = i % a.BN;
+        float v = 0.f;
+#pragma unroll
+        for (int w8 = 0; w8 < EPI_WARPS; ++w8) v += red[(w8 * 2 + which) * 128 + col];
+        atomicAdd(a.stats + which * a.N + n0f + col, v);
+      }
+    };
+    uint32_t tcount = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+      int tm_ = tile % a.n_tiles_m;
+      const int n0 = (tile / a.n_tiles_m) * a.BN;
+      if (a.stats && n0 != cur_n0) {
+        if (cur_n0 >= 0) flush_stats(cur_n0);
+        cur_n0 = n0;
+      }
+      const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
+      const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
+      const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
+      const int pw = w0 + tw, ph_ = h0 + th, pb = b0 + tb;
+      const bool valid = pw < a.W && ph_ < a.H && pb < a.B;
+      const long pix = ((long)pb * a.H + ph_) * a.W + pw;
+      const uint32_t as = tcount & 1u, aph = (tcount >> 1) & 1u;
+      const uint32_t obuf = out0 + as * out_bytes;
+      // the TMA store that last read this staging buffer (two tiles ago) must have finished reading it
+      if (et == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+      epi_bar_sync();
+      mbar_wait(tfull0 + 8u * as, aph);
+      tc_fence_after();
+      for (int c0 = eg * 32; c0 < a.BN; c0 += 64) {
+        uint32_t raw[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * (uint32_t)a.BN + (uint32_t)c0, raw);
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
+        if (a.bias) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 bb = __ldg(reinterpret_cast<const float4*>(a.bias + n0 + c0 + j));
+            v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
+          }
+        }
+        if (a.add && valid) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            float t8[8];
+            ck::unpack8(ck::ldg16(a.add + pix * a.N + n0 + c0 + j), t8);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[j + e] += t8[e];
+          }
+        }
+        // bf16 pack + swizzled staging store (row r of sub-tile c0 / sub_w)
+        const int sub = c0 / a.sub_w, cin_sub = c0 % a.sub_w;
+        const uint32_t rowaddr = obuf + sub * sub_bytes + (uint32_t)r * row_bytes;
+        const uint32_t xorv = (a.sub_w == 64) ? (uint32_t)(r & 7) : (uint32_t)((r >> 1) & 3);
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+          const uint4 pk = ck::pack8(&v[j]);
+          const uint32_t chunk = (uint32_t)((cin_sub + j) >> 3);
+          const uint32_t dst = rowaddr + ((chunk ^ xorv) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(pk.x), "r"(pk.y), "r"(pk.z), "r"(pk.w)
+                       : "memory");
+        }
+        if (a.stats) {
+          float s1[32], s2[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float x = valid ? __bfloat162float(__float2bfloat16_rn(v[j])) : 0.f;
+            s1[j] = x;
+            s2[j] = x * x;
+          }
+          st1[c0 >> 5] += warp_colsum32(s1, lane);
+          st2[c0 >> 5] += warp_colsum32(s2, lane);
+        }
+      }
+      // accumulator stage fully read: hand it back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty0 + 8u * as);
+      // make the staging writes visible to the async proxy, then one thread stores the tile
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      epi_bar_sync();
+      if (et == 0) {
+        for (int sub = 0; sub < nsub; ++sub)
+          tma_store_4d(&tmY, obuf + sub * sub_bytes, n0 + sub * a.sub_w, w0, h0, b0);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    }
+    if (a.stats && cur_n0 >= 0) flush_stats(cur_n0);
+    if (et == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, ncols);
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------------
 struct WgradArgs {
   float* dW;
   long s_tap, s_ci, s_co;
@@ -799,6 +1045,69 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
   }
   if (use_v1) return conv_tc_fwd_v1(X, Wk, bias, add, Y, stats, B, H, W, Cin, N, taps, st);
   if (Cin % 32 || N % 32 || (taps != 1 && taps != 9)) return (int)cudaErrorInvalidValue;
+  static int use_halo = -1, halo_base_off = 0;  // measured: tcgen05 applies the swizzle XOR on absolute smem address bits, so a window that starts
+  // mid-atom needs base_offset = 0 (setting it from the start address gives wrong results)
+  if (use_halo < 0) {
+    const char* e = getenv("CRACKFL_TC_HALO");
+    use_halo = (e && e[0] == '0') ? 0 : 1;
+    const char* e2 = getenv("CRACKFL_HALO_BASEOFF");
+    if (e2) halo_base_off = atoi(e2);
+  }
+  if (use_halo && taps == 9 && Cin % 64 == 0 && H >= 16 && W >= 8) {
+    ConvArgs3 a;
+    a.bias = bias; a.add = (const __nv_bfloat16*)add; a.stats = stats;
+    a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.N = N; a.taps = taps;
+    a.BN = N > 128 ? 128 : N;
+    if (N % a.BN) return (int)cudaErrorInvalidValue;
+    a.kc = 64; a.layout = 2u; a.sbo = 1024u;
+    a.sub_w = (a.BN % 64 == 0) ? 64 : 32;
+    a.base_off = halo_base_off;
+    a.g.TW = 8; a.g.TH = 16; a.g.TB = 1;
+    a.g.tiles_w = (W + 7) / 8; a.g.tiles_h = (H + 15) / 16; a.g.tiles_b = B;
+    a.n_tiles_m = a.g.tiles_w * a.g.tiles_h * a.g.tiles_b;
+    a.n_tiles_n = N / a.BN;
+    const uint32_t b_bytes = (uint32_t)a.BN * 128u;
+    const uint32_t out_bytes = 2u * 128u * (uint32_t)a.BN * 2u;
+    // two CTAs per SM when >= 3 weight stages still fit in ~104 KB (small BN), else one CTA with a deep ring
+    int per_sm = 1;
+    int stages = 0;
+    if (2u * 23552u + out_bytes + 3u * b_bytes + 10240u <= 106496u) {
+      per_sm = 2;
+      stages = (int)((106496u - 10240u - 2u * 23552u - out_bytes) / b_bytes);
+    } else {
+      stages = (int)((200704u - 2u * 23552u - out_bytes) / b_bytes);
+    }
+    if (stages > 9) stages = 9;
+    if (stages < 2) stages = 2;
+    a.stages = stages;
+    const size_t smem = 2 * 23552 + (size_t)stages * b_bytes + out_bytes + 1024 + 512 + 8192;
+    CUtensorMap tmA, tmB, tmY;
+    const int dA[4] = {Cin, W, H, B}, bA[4] = {64, 10, 18, 1};
+    int rc = get_map(X, 4, dA, bA, 128, &tmA);
+    if (rc) return rc;
+    const int dB[2] = {taps * Cin, N}, bB[2] = {64, a.BN};
+    rc = get_map(Wk, 2, dB, bB, 128, &tmB);
+    if (rc) return rc;
+    const int dY[4] = {N, W, H, B}, bY[4] = {a.sub_w, 8, 16, 1};
+    rc = get_map(Y, 4, dY, bY, a.sub_w * 2, &tmY);
+    if (rc) return rc;
+    static bool attr3 = false;
+    if (!attr3) {
+      cudaError_t e = cudaFuncSetAttribute(conv_tc_fwd_v3_k, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+      if (e != cudaSuccess) return (int)e;
+      int dev = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+      if (g_num_sms <= 0) g_num_sms = 148;
+      attr3 = true;
+    }
+    const int total = a.n_tiles_m * a.n_tiles_n;
+    int grid = per_sm * g_num_sms;
+    if (grid > total) grid = total;
+    conv_tc_fwd_v3_k<<<grid, 64 + EPI_THREADS, smem, st>>>(tmA, tmB, tmY, a);
+    CK_LAUNCH_CHECK();
+    return 0;
+  }
   ConvArgs2 a;
   a.bias = bias; a.add = (const __nv_bfloat16*)add; a.stats = stats;
   a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.N = N; a.taps = taps;
