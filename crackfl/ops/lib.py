@@ -30,7 +30,7 @@ class FedAggParams(C.Structure):
                 ("delta", i32), ("server_opt", i32), ("eta", f32), ("beta1", f32), ("beta2", f32), ("tau", f32),
                 ("master", vp), ("m", vp), ("v", vp), ("trainable", vp), ("mc_out", vp),
                 ("begin", i64), ("end", i64), ("pads", vp * MAX_RANKS), ("rank", i32), ("world", i32),
-                ("epoch", C.c_uint32), ("error_flag", vp), ("local_sync", vp), ("unroll", i32), ("load_mode", i32)]
+                ("epoch", C.c_uint32), ("error_flag", vp), ("local_sync", vp), ("mc_in", vp), ("unroll", i32), ("load_mode", i32)]
 
 
 _SIGS = {

@@ -78,7 +78,7 @@ class OnBoxFederation:
 
     def __init__(self, spec: UNetSpec = REFERENCE_SPEC, clients_per_gpu: int = 1, strategy: str = "fedavg",
                  payload: str = "fp32", eta=1e-2, beta1=0.9, beta2=0.99, tau=1e-3, numel: Optional[int] = None,
-                 grid_blocks: int = 148 * 8):
+                 grid_blocks: int = 148 * 8, nvls: Optional[bool] = None):
         self.spec = spec
         self.n = int(numel if numel is not None else spec.arena_numel)
         self.mask_from_spec = numel is None  # synthetic sizes (bandwidth sweeps) treat every element as trainable
@@ -92,6 +92,8 @@ class OnBoxFederation:
         self.hp = (eta, beta1, beta2, tau)
         self.cuda = torch.cuda.is_available()
         self.epoch = 0
+        self.nvls = bool(int(os.environ.get("CRACKFL_NVLS", "0"))) if nvls is None else nvls
+        self.mc = {}
         self.grid_blocks = int(os.environ.get("CRACKFL_AGG_GRID", grid_blocks))
         self.last_agg_ms = 0.0
         if self.cuda:
@@ -118,10 +120,27 @@ class OnBoxFederation:
         n, K, world = self.n, self.K, self.world
         self.dev = torch.device("cuda", torch.cuda.current_device())
         pbytes = 2 if self.payload == "bf16_delta" else 4
-        self._raw = {"partial": RawCudaBuffer(self.lib, n * pbytes), "global": RawCudaBuffer(self.lib, n * 4),
-                     "pads": RawCudaBuffer(self.lib, 2 * L.MAX_RANKS * 4)}
-        self.partial = self._raw["partial"].tensor(torch.bfloat16 if pbytes == 2 else torch.float32, n, self.dev)
-        self.global_arena = self._raw["global"].tensor(torch.float32, n, self.dev)
+        self.nvls = self.nvls and world > 1
+        self._raw = {"pads": RawCudaBuffer(self.lib, 2 * L.MAX_RANKS * 4)}
+        self._symm = {}
+        if self.nvls:
+            # NVLS: arenas come from torch's symmetric-memory allocator, which also maps them on an NVSwitch
+            # multicast address (multimem.ld_reduce for the pull, multimem.st for the broadcast)
+            import torch.distributed._symmetric_memory as symm
+            self.partial = symm.empty(n, dtype=torch.bfloat16 if pbytes == 2 else torch.float32, device=self.dev)
+            self.global_arena = symm.empty(n, dtype=torch.float32, device=self.dev)
+            self.partial.zero_(); self.global_arena.zero_()
+            for name, t in (("partial", self.partial), ("global", self.global_arena)):
+                h = symm.rendezvous(t, group=dist.group.WORLD)
+                if not getattr(h, "multicast_ptr", 0):
+                    raise RuntimeError("symmetric memory has no multicast mapping on this system (NVLS unavailable)")
+                self._symm[name] = h
+                self.mc[name] = int(h.multicast_ptr)
+        else:
+            self._raw["partial"] = RawCudaBuffer(self.lib, n * pbytes)
+            self._raw["global"] = RawCudaBuffer(self.lib, n * 4)
+            self.partial = self._raw["partial"].tensor(torch.bfloat16 if pbytes == 2 else torch.float32, n, self.dev)
+            self.global_arena = self._raw["global"].tensor(torch.float32, n, self.dev)
         self.updates = torch.zeros((K, n), dtype=torch.float32, device=self.dev)
         self.master = torch.zeros(n, dtype=torch.float32, device=self.dev)
         self.m = torch.zeros(n, dtype=torch.float32, device=self.dev)
@@ -134,7 +153,9 @@ class OnBoxFederation:
         self.local_sync = torch.zeros(2, dtype=torch.int32, device=self.dev)
         self.error_flag = torch.zeros(1, dtype=torch.int32, device=self.dev)
         # peer mapping
-        self.peer: Dict[str, List[int]] = {k: [0] * world for k in self._raw}
+        self.peer: Dict[str, List[int]] = {k: [0] * world for k in ("partial", "global", "pads")}
+        for name, h in self._symm.items():
+            self.peer[name] = [int(p) for p in h.buffer_ptrs]
         if world > 1:
             handles = {k: b.export() for k, b in self._raw.items()}
             gathered: List[Optional[dict]] = [None] * world
@@ -167,7 +188,7 @@ class OnBoxFederation:
 
     def publish(self, k: int, flat: torch.Tensor):
         """Client k (local index) hands in its trained weights (device-to-device copy of the arena)."""
-        if self.cuda and self.K == 1 and self.payload == "fp32":
+        if self.cuda and self.K == 1 and self.payload == "fp32" and not self.nvls:
             self.partial.copy_(flat)  # exported arena: peers pull it directly, no pre-reduce pass
         else:
             self.updates[k].copy_(flat)
@@ -209,7 +230,9 @@ class OnBoxFederation:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(st)
         K = self.K
-        direct = (K == 1 and self.payload == "fp32")  # the single local update IS the partial: no pre-reduce pass
+        # the single local update IS the partial (no pre-reduce pass) - except with NVLS, where the switch can only
+        # add, so every partial must already carry its coefficient
+        direct = (K == 1 and self.payload == "fp32" and not self.nvls)
         if not direct:
             # (K14) local pre-reduce of this GPU's K clients -> partial
             p = L.FedAggParams()
@@ -246,7 +269,8 @@ class OnBoxFederation:
         q.eta, q.beta1, q.beta2, q.tau = self.hp
         q.master, q.m, q.v = self.master.data_ptr(), self.m.data_ptr(), self.v.data_ptr()
         q.trainable = self.trainable.data_ptr()
-        q.mc_out = 0
+        q.mc_out = self.mc.get("global", 0)
+        q.mc_in = self.mc.get("partial", 0)
         q.begin, q.end = self.begin, self.end
         q.rank, q.world, q.epoch = self.rank, self.world, self.epoch
         q.error_flag, q.local_sync = self.error_flag.data_ptr(), self.local_sync.data_ptr()

@@ -1049,11 +1049,15 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
   // mid-atom needs base_offset = 0 (setting it from the start address gives wrong results)
   if (use_halo < 0) {
     const char* e = getenv("CRACKFL_TC_HALO");
-    use_halo = (e && e[0] == '0') ? 0 : 1;
+    use_halo = e ? atoi(e) : 1;
     const char* e2 = getenv("CRACKFL_HALO_BASEOFF");
     if (e2) halo_base_off = atoi(e2);
   }
-  if (use_halo && taps == 9 && Cin % 64 == 0 && H >= 16 && W >= 8) {
+  // measured (profiles/conv_bench_r1.json): the halo kernel wins when the N tile is 128 wide (d0/d1 and the 64->128
+  // dgrads); with narrower N tiles the per-tap barrier round trips of its single producer/issuer threads dominate and
+  // the two-CTA-per-SM v2 kernel is faster.  CRACKFL_TC_HALO=2 forces it for every eligible layer.
+  const bool halo_ok = taps == 9 && Cin % 64 == 0 && H >= 16 && W >= 8;
+  if (halo_ok && (use_halo == 2 || (use_halo == 1 && N >= 128))) {
     ConvArgs3 a;
     a.bias = bias; a.add = (const __nv_bfloat16*)add; a.stats = stats;
     a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.N = N; a.taps = taps;

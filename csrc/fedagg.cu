@@ -60,6 +60,21 @@ __device__ __forceinline__ void multimem_st_f4(float* mc, const float4& v) {
                : "memory");
 }
 
+// NVLS: one load that the NVSwitch turns into a reduction over every GPU's replica of the address
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* mc) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(mc) : "memory");
+  return r;
+}
+// 4 bf16 per load, accumulated in fp32 inside the switch
+__device__ __forceinline__ uint2 multimem_ld_reduce_bf16x4(const void* mc) {
+  uint2 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v2.bf16x2 {%0,%1}, [%2];"
+               : "=r"(r.x), "=r"(r.y) : "l"(mc) : "memory");
+  return r;
+}
+
 constexpr long long SPIN_TIMEOUT_CYCLES = 4000000000LL;  // ~2 s at 1.9 GHz: a dead rank cannot hang the box
 
 // Cross-GPU barrier over the signal pads.  pad layout per rank: [phase(2)][world] u32, monotonically
@@ -103,6 +118,22 @@ __global__ void __launch_bounds__(256) fedagg_k(const crackfl_fedagg_params P) {
     float4 acc[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (P.mc_in) {
+      // NVLS pull: the partials were pre-scaled by their coefficients, the switch adds the G replicas
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long i = i0 + u * stride;
+        if (i >= n4_end) continue;
+        if (PAYLOAD_BF16) {
+          const uint2 w4 = multimem_ld_reduce_bf16x4(reinterpret_cast<const uint2*>(P.mc_in) + i);
+          const uint32_t lo = w4.x, hi = w4.y;
+          acc[u].x = __uint_as_float(lo << 16); acc[u].y = __uint_as_float(lo & 0xffff0000u);
+          acc[u].z = __uint_as_float(hi << 16); acc[u].w = __uint_as_float(hi & 0xffff0000u);
+        } else {
+          acc[u] = multimem_ld_reduce_f4(reinterpret_cast<const float*>(P.mc_in) + i * 4);
+        }
+      }
+    } else
     for (int k = 0; k < P.num_clients; ++k) {
       const float c = P.coef[k];
       if (PAYLOAD_BF16) {
@@ -196,7 +227,7 @@ __global__ void __launch_bounds__(256) fedagg_k(const crackfl_fedagg_params P) {
 extern "C" {
 
 int crackfl_fedagg(const crackfl_fedagg_params* p, int grid_blocks, cudaStream_t st) {
-  if (p->num_clients < 1 || p->num_clients > CRACKFL_MAX_CLIENTS || p->num_out > CRACKFL_MAX_OUT ||
+  if ((p->num_clients < 1 && !p->mc_in) || p->num_clients > CRACKFL_MAX_CLIENTS || p->num_out > CRACKFL_MAX_OUT ||
       p->world > CRACKFL_MAX_RANKS || (p->begin & 3) || (p->end & 3) || p->end < p->begin)
     return (int)cudaErrorInvalidValue;
   if (p->mc_out && p->out_bf16) return (int)cudaErrorInvalidValue;

@@ -149,6 +149,7 @@ typedef struct {
   uint32_t epoch;           /* 1,2,3,... monotonically per call */
   int* error_flag;          /* set non-zero on spin timeout */
   uint32_t* local_sync;     /* [2] u32 in local memory, zero-initialised once */
+  const void* mc_in;        /* NVLS multicast address of the (pre-scaled) partial arena: multimem.ld_reduce pull, or NULL */
   int unroll;               /* independent 16-byte loads per client per thread: 4 (default when 0) or 8 */
   int load_mode;            /* 0: ld.relaxed.sys (default), 1: ld.global.nc.L1::no_allocate (updates are immutable during the launch) */
 } crackfl_fedagg_params;
