@@ -46,20 +46,7 @@ if _mode == "nopoll":
     _time.sleep = _sleep
 ''',
     "transport_pb2_grpc.py": '''
-import grpc
-from crackfl.protocol import messages as pb
-_PATH = "/transport.TransportService/transport"
-class TransportServiceServicer(object):
-    def transport(self, request_iterator, context):
-        raise NotImplementedError
-def add_TransportServiceServicer_to_server(servicer, server):
-    h = grpc.stream_stream_rpc_method_handler(servicer.transport, request_deserializer=pb.transportRequest.FromString,
-                                              response_serializer=pb.transportResponse.SerializeToString)
-    server.add_generic_rpc_handlers((grpc.method_handlers_generic_handler("transport.TransportService", {"transport": h}),))
-class TransportServiceStub(object):
-    def __init__(self, channel):
-        self.transport = channel.stream_stream(_PATH, request_serializer=pb.transportRequest.SerializeToString,
-                                               response_deserializer=pb.transportResponse.FromString)
+from crackfl.compat.transport_pb2_grpc import *  # noqa: F401,F403
 ''',
     "model_evaluate.py": '''
 import os, pickle, numpy as np

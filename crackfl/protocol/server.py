@@ -82,11 +82,15 @@ class FaultInjector:
 class FLServer:
     def __init__(self, cfg: Config, initial_weights: Sequence[np.ndarray], spec=None, aggregator=None,
                  clock: Callable[[], float] = time.monotonic, sleep: Callable[[float], None] = time.sleep,
-                 fault: Optional[FaultInjector] = None, log: Callable[[str], None] = print):
+                 fault: Optional[FaultInjector] = None, log: Callable[[str], None] = print,
+                 eval_fn: Optional[Callable[[List[np.ndarray]], dict]] = None):
         from ..models.spec import REFERENCE_SPEC
         self.cfg = cfg
         self.spec = spec or REFERENCE_SPEC
         self.clock, self.sleep, self.fault, self.log = clock, sleep, fault, log
+        # optional server-side evaluation of every new global model: the reference's dead ``trainNextRound`` hook
+        # (fl_server.py:27-37, call site commented out at :65); returns e.g. {'loss':..., 'accuracy':...}
+        self.eval_fn = eval_fn
         self.lock = threading.RLock()
         s = cfg.server
         if aggregator is None:
@@ -168,6 +172,12 @@ class FLServer:
         rec = {"round": self.current_round, "clients": list(self.round_reporters), "num_clients": len(self.round_updates),
                "samples": list(self.round_samples), "aggregate_ms": agg_ms, "model_version": self.model_version + 1,
                "aggregator": getattr(self.aggregator, "kind", "?"), "client_metrics": list(self.round_metrics)}
+        if self.eval_fn is not None:
+            try:
+                rec["global_eval"] = self.eval_fn(self.global_weights)
+                self.log(f"[server] round {self.current_round} global model: {rec['global_eval']}")
+            except Exception as e:  # evaluation must never stall a round
+                rec["global_eval_error"] = repr(e)
         self.history.append(rec)
         finished_round = self.current_round
         # clients that did not report are no longer waited for in later rounds
