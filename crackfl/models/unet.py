@@ -59,6 +59,8 @@ class UNetEngine:
         self.side_streams = os.environ.get("CRACKFL_SIDE_STREAM", "1") != "0"
         self.launches_per_step = 0
         self._bufs: Dict[str, torch.Tensor] = {}
+        self._fins: list = []
+        self.fuse_finalize = os.environ.get("CRACKFL_FUSE_FINALIZE", "1") != "0"
         with torch.cuda.device(self.dev):
             self._alloc_params()
             self._build_ops_table()
@@ -247,6 +249,15 @@ class UNetEngine:
         prog.append((lib.crackfl_bn_finalize, (self._zptr(bnl.name, "stats"), self.P(g), self.P(bt), self.P(rm), self.P(rv),
                                                 self._bnptr(bnl.name), C_, float(P), self.spec.bn_eps, self.spec.bn_momentum)))
 
+    def _fin(self, bnl, P) -> "C.POINTER":
+        """ctypes crackfl_bn_fin for BN layer ``bnl`` (kept alive on the engine)."""
+        g, bt, rm, rv = bnl.tensors
+        f = L.BnFin(stats=self._zptr(bnl.name, "stats"), gamma=self.P(g), beta=self.P(bt), run_mean=self.P(rm),
+                    run_var=self.P(rv), bn_out=self._bnptr(bnl.name), count=float(P), eps=self.spec.bn_eps,
+                    momentum=self.spec.bn_momentum)
+        self._fins.append(f)
+        return C.byref(f)
+
     def _bn_eval(self, prog, bnl):
         g, bt, rm, rv = bnl.tensors
         prog.append((self.lib.crackfl_bn_eval_prepare, (self.P(g), self.P(bt), self.P(rm), self.P(rv), self._bnptr(bnl.name),
@@ -258,9 +269,16 @@ class UNetEngine:
         (conv0, bn0), encs, decs, head = self._layer_iter()
         b = self.b
 
-        def bn(bnl, y, P, stats_done=False):
+        fuse = training and self.fuse_finalize
+
+        def bn(bnl, y, P, stats_done=False, consumer_finalizes=False):
+            """stats (+ finalize unless the consumer kernel folds it in) in training, moving statistics in eval."""
             if training:
-                self._bn_train(prog, bnl, y, P, stats_done)
+                if consumer_finalizes:
+                    if not stats_done:
+                        prog.append((lib.crackfl_bn_stats, (y, self._zptr(bnl.name, "stats"), P, bnl.cout)))
+                else:
+                    self._bn_train(prog, bnl, y, P, stats_done)
             else:
                 self._bn_eval(prog, bnl)
 
@@ -270,8 +288,11 @@ class UNetEngine:
         r, rw, c0 = self.H // 2, self.W // 2, self.spec.entry
         prog.append((lib.crackfl_entry_conv_fwd, (b("x_u8"), self.P(conv0.tensors[0]), self.P(conv0.tensors[1]), b("y0"),
                                                   B, self.H, self.W, c0)))
-        bn(bn0, b("y0"), B * r * rw)
-        prog.append((lib.crackfl_bn_act, (b("y0"), self._bnptr(bn0.name), b("x0"), b("x0e"), B, r, rw, c0, 1)))
+        bn(bn0, b("y0"), B * r * rw, consumer_finalizes=fuse)
+        if fuse:
+            prog.append((lib.crackfl_bn_act_fin, (b("y0"), self._fin(bn0, B * r * rw), b("x0"), b("x0e"), B, r, rw, c0, 1)))
+        else:
+            prog.append((lib.crackfl_bn_act, (b("y0"), self._bnptr(bn0.name), b("x0"), b("x0e"), B, r, rw, c0, 1)))
         xin, xe = "x0", "x0e"
         for e, (sep1, bn1, sep2, bn2, res) in zip(self.enc, encs):
             p = f"e{e['k']}."
@@ -280,17 +301,27 @@ class UNetEngine:
             prog.append((lib.crackfl_dw3x3_fwd, (b(xin), self.P(sep1.tensors[0]), 0, b(p + "d1"), B, r, rw, cin, 0)))
             sd = self._gemm(prog, b(p + "d1"), sep1.name + ".f", self.P(sep1.tensors[2]), 0, b(p + "y1"), B, r, rw,
                             self._zptr(bn1.name, "stats") if training else 0)
-            bn(bn1, b(p + "y1"), Pn, sd)
-            prog.append((lib.crackfl_dw3x3_fwd, (b(p + "y1"), self.P(sep2.tensors[0]), self._bnptr(bn1.name), b(p + "d2"),
-                                                 B, r, rw, f, 1)))
+            fuse_dw = fuse and rw % 4 == 0
+            bn(bn1, b(p + "y1"), Pn, sd, consumer_finalizes=fuse_dw)
+            if fuse_dw:
+                prog.append((lib.crackfl_dw3x3_fwd_fin, (b(p + "y1"), self.P(sep2.tensors[0]), self._fin(bn1, Pn), b(p + "d2"),
+                                                         B, r, rw, f)))
+            else:
+                prog.append((lib.crackfl_dw3x3_fwd, (b(p + "y1"), self.P(sep2.tensors[0]), self._bnptr(bn1.name),
+                                                     b(p + "d2"), B, r, rw, f, 1)))
             sd = self._gemm(prog, b(p + "d2"), sep2.name + ".f", self.P(sep2.tensors[2]), 0, b(p + "y2"), B, r, rw,
                             self._zptr(bn2.name, "stats") if training else 0)
-            bn(bn2, b(p + "y2"), Pn, sd)
+            bn(bn2, b(p + "y2"), Pn, sd, consumer_finalizes=fuse)
             self._gemm(prog, b(xe), res.name + ".f", self.P(res.tensors[1]), 0, b(p + "rs"), B, r // 2, rw // 2)
             last = e["k"] + 1 == len(self.enc)
-            prog.append((lib.crackfl_pool_add_fwd, (b(p + "y2"), self._bnptr(bn2.name), b(p + "rs"), b(p + "out"),
-                                                    0 if last else b(p + "oute"), b("a0_0") if last else 0,
-                                                    b(p + "arg") if training else 0, B, r, rw, f)))
+            if fuse:
+                prog.append((lib.crackfl_pool_add_fwd_fin, (b(p + "y2"), self._fin(bn2, Pn), b(p + "rs"), b(p + "out"),
+                                                            0 if last else b(p + "oute"), b("a0_0") if last else 0,
+                                                            b(p + "arg"), B, r, rw, f)))
+            else:
+                prog.append((lib.crackfl_pool_add_fwd, (b(p + "y2"), self._bnptr(bn2.name), b(p + "rs"), b(p + "out"),
+                                                        0 if last else b(p + "oute"), b("a0_0") if last else 0,
+                                                        b(p + "arg") if training else 0, B, r, rw, f)))
             xin, xe = p + "out", p + "oute"
         xprev = xin  # bottleneck tensor x3
         for d, (ct1, bn1, ct2, bn2, res) in zip(self.dec, decs):
@@ -300,16 +331,25 @@ class UNetEngine:
             a0 = "a0_0" if j == 0 else p + "a0"
             sd = self._gemm(prog, b(a0), ct1.name + ".f", self.P(ct1.tensors[1]), 0, b(p + "y1"), B, r, rw,
                             self._zptr(bn1.name, "stats") if training else 0)
-            bn(bn1, b(p + "y1"), Pn, sd)
-            prog.append((lib.crackfl_bn_act, (b(p + "y1"), self._bnptr(bn1.name), b(p + "a1"), 0, B, r, rw, f, 1)))
+            bn(bn1, b(p + "y1"), Pn, sd, consumer_finalizes=fuse)
+            if fuse:
+                prog.append((lib.crackfl_bn_act_fin, (b(p + "y1"), self._fin(bn1, Pn), b(p + "a1"), 0, B, r, rw, f, 1)))
+            else:
+                prog.append((lib.crackfl_bn_act, (b(p + "y1"), self._bnptr(bn1.name), b(p + "a1"), 0, B, r, rw, f, 1)))
             sd = self._gemm(prog, b(p + "a1"), ct2.name + ".f", self.P(ct2.tensors[1]), 0, b(p + "y2"), B, r, rw,
                             self._zptr(bn2.name, "stats") if training else 0)
-            bn(bn2, b(p + "y2"), Pn, sd)
+            bn(bn2, b(p + "y2"), Pn, sd, consumer_finalizes=fuse)
             lr_, lrw = (r, rw) if j == 0 else (r // 2, rw // 2)
             self._gemm(prog, b(xprev), res.name + ".f", self.P(res.tensors[1]), 0, b(p + "rl"), B, lr_, lrw)
             last = j + 1 == len(self.dec)
-            prog.append((lib.crackfl_dec_combine_fwd, (b(p + "y2"), self._bnptr(bn2.name), b(p + "rl"), b(p + "s"),
-                                                       0 if last else b(f"d{j + 1}.a0"), B, r, rw, f, 0 if j == 0 else 1)))
+            if fuse:
+                prog.append((lib.crackfl_dec_combine_fwd_fin, (b(p + "y2"), self._fin(bn2, Pn), b(p + "rl"), b(p + "s"),
+                                                               0 if last else b(f"d{j + 1}.a0"), B, r, rw, f,
+                                                               0 if j == 0 else 1)))
+            else:
+                prog.append((lib.crackfl_dec_combine_fwd, (b(p + "y2"), self._bnptr(bn2.name), b(p + "rl"), b(p + "s"),
+                                                           0 if last else b(f"d{j + 1}.a0"), B, r, rw, f,
+                                                           0 if j == 0 else 1)))
             xprev = p + "s"
         dl = self.dec[-1]
         prog.append((lib.crackfl_head_fwd, (b(xprev), self.P(head.tensors[0]), self.P(head.tensors[1]),

@@ -24,6 +24,11 @@ class PrepDesc(C.Structure):
                 ("s_n", i64), ("s_t", i64), ("s_k", i64)]
 
 
+class BnFin(C.Structure):
+    _fields_ = [("stats", vp), ("gamma", vp), ("beta", vp), ("run_mean", vp), ("run_var", vp), ("bn_out", vp),
+                ("count", f32), ("eps", f32), ("momentum", f32)]
+
+
 class FedAggParams(C.Structure):
     _fields_ = [("client", vp * MAX_CLIENTS), ("coef", f32 * MAX_CLIENTS), ("out", vp * MAX_OUT),
                 ("num_clients", i32), ("num_out", i32), ("payload_bf16", i32), ("out_bf16", i32),
@@ -46,6 +51,10 @@ _SIGS = {
     "crackfl_noalloc_max_channels": [],
     "crackfl_dw3x3_fwd": [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_dw3x3_bwd": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
+    "crackfl_bn_act_fin": [vp, C.POINTER(BnFin), vp, vp, i32, i32, i32, i32, i32, vp],
+    "crackfl_dw3x3_fwd_fin": [vp, vp, C.POINTER(BnFin), vp, i32, i32, i32, i32, vp],
+    "crackfl_pool_add_fwd_fin": [vp, C.POINTER(BnFin), vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],
+    "crackfl_dec_combine_fwd_fin": [vp, C.POINTER(BnFin), vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_dw3x3_dgrad": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
     "crackfl_dw3x3_wgrad": [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_pool_add_fwd": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],

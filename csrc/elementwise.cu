@@ -14,6 +14,50 @@ namespace {
 
 constexpr int TPB = 256;
 
+// BatchNorm "finalize" folded into the consumer of the normalised tensor: the consumer derives scale/shift for its
+// own channel vector straight from the sum / sum-of-squares accumulators (a handful of flops, once per thread) and
+// block 0 publishes [scale, shift, mean, invstd] for the backward pass and updates the moving statistics.  This
+// removes one tiny launch (and its dependency bubble) per BN layer from the critical path of the step.
+typedef crackfl_bn_fin BnFin;
+
+__device__ __forceinline__ void bn_coeffs(const BnFin& f, const float* __restrict__ bn, int C, int cv, float sc[8],
+                                          float sh[8]) {
+  if (f.stats == nullptr) {
+    load8f(bn + cv * 8, sc);
+    load8f(bn + C + cv * 8, sh);
+    return;
+  }
+  float s1[8], s2[8], g[8], b[8];
+  load8f(f.stats + cv * 8, s1); load8f(f.stats + C + cv * 8, s2);
+  load8f(f.gamma + cv * 8, g); load8f(f.beta + cv * 8, b);
+  const float inv = 1.0f / f.count;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float mean = s1[j] * inv;
+    const float var = fmaxf(s2[j] * inv - mean * mean, 0.f);
+    const float invstd = rsqrtf(var + f.eps);
+    sc[j] = g[j] * invstd;
+    sh[j] = b[j] - mean * sc[j];
+  }
+}
+
+__device__ __forceinline__ void bn_publish(const BnFin& f, int C) {
+  if (f.stats == nullptr || blockIdx.x != 0) return;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float mean = f.stats[c] / f.count;
+    const float var = fmaxf(f.stats[C + c] / f.count - mean * mean, 0.f);
+    const float invstd = rsqrtf(var + f.eps);
+    const float scl = f.gamma[c] * invstd;
+    f.bn_out[c] = scl;
+    f.bn_out[C + c] = f.beta[c] - mean * scl;
+    f.bn_out[2 * C + c] = mean;
+    f.bn_out[3 * C + c] = invstd;
+    const float unb = f.count > 1.f ? var * (f.count / (f.count - 1.f)) : var;
+    f.run_mean[c] = f.run_mean[c] * f.momentum + mean * (1.f - f.momentum);
+    f.run_var[c] = f.run_var[c] * f.momentum + unb * (1.f - f.momentum);
+  }
+}
+
 // ---------------------------------------------------------------------------------------
 // K4 entry conv 3x3 s2, TF-"same" (pad bottom/right only), uint8 input, /255 fused.  K=27 is too
 // small for the tensor cores to pay; CUDA-core kernel, weights in shared memory.
@@ -143,15 +187,15 @@ __global__ void bn_eval_prepare_k(const float* __restrict__ gamma, const float* 
 // out = [relu](y*scale+shift); optional compact copy of the even pixels (input of the 1x1 s2 residual conv)
 __global__ void __launch_bounds__(TPB, 4) bn_act_k(const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
                                                    __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ even,
-                                                   int B, int H, int W, int C, int relu) {
+                                                   int B, int H, int W, int C, int relu, const BnFin fin) {
   const int c8 = C >> 3;
   const long total = (long)B * H * W * c8;
   const long stride = (long)gridDim.x * blockDim.x;  // multiple of c8: a thread keeps its channel vector
   const long g0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
   const int cv = (int)(g0 % c8);
   float sc[8], sh[8];
-  load8f(bn + cv * 8, sc);
-  load8f(bn + C + cv * 8, sh);
+  bn_coeffs(fin, bn, C, cv, sc, sh);
+  bn_publish(fin, C);
   for (long g = g0; g < total; g += 2 * stride) {
     const long g2 = g + stride;
     const bool has2 = g2 < total;
@@ -301,19 +345,21 @@ __global__ void __launch_bounds__(TPB) dw3x3_bwd_k(const __nv_bfloat16* __restri
 __global__ void __launch_bounds__(TPB) pool_add_fwd_k(const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
                                                       const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out,
                                                       __nv_bfloat16* __restrict__ even, __nv_bfloat16* __restrict__ relu_out,
-                                                      uint8_t* __restrict__ arg, int B, int H, int W, int C) {
+                                                      uint8_t* __restrict__ arg, int B, int H, int W, int C, const BnFin fin) {
   const int c8 = C >> 3, Ho = H >> 1, Wo = W >> 1;
   const long total = (long)B * Ho * Wo * c8;
-  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long)gridDim.x * blockDim.x) {
-    const int cv = (int)(g % c8);
+  const long g0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int cv = (int)(g0 % c8);
+  float sc[8], sh[8];
+  bn_coeffs(fin, bn, C, cv, sc, sh);
+  bn_publish(fin, C);
+  for (long g = g0; g < total; g += (long)gridDim.x * blockDim.x) {
     long p = g / c8;
     const int ow = (int)(p % Wo); p /= Wo;
     const int oh = (int)(p % Ho);
     const int b = (int)(p / Ho);
-    float sc[8], sh[8], best[8];
+    float best[8];
     int bi[8];
-    load8f(bn + cv * 8, sc);
-    load8f(bn + C + cv * 8, sh);
 #pragma unroll
     for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; bi[j] = 0; }
 #pragma unroll
@@ -359,19 +405,21 @@ __global__ void __launch_bounds__(TPB) pool_add_fwd_k(const __nv_bfloat16* __res
 __global__ void __launch_bounds__(TPB) dec_combine_fwd_k(const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
                                                          const __nv_bfloat16* __restrict__ rl, __nv_bfloat16* __restrict__ s,
                                                          __nv_bfloat16* __restrict__ a_next, int B, int H, int W, int C,
-                                                         int rl_up) {
+                                                         int rl_up, const BnFin fin) {
   const int c8 = C >> 3;
   const long total = (long)B * H * W * c8;
-  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long)gridDim.x * blockDim.x) {
-    const int cv = (int)(g % c8);
+  const long g0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int cv = (int)(g0 % c8);
+  float sc[8], sh[8];
+  bn_coeffs(fin, bn, C, cv, sc, sh);
+  bn_publish(fin, C);
+  for (long g = g0; g < total; g += (long)gridDim.x * blockDim.x) {
     long p = g / c8;
     const int w = (int)(p % W); p /= W;
     const int h = (int)(p % H);
     const int b = (int)(p / H);
-    float f[8], sc[8], sh[8], r[8];
+    float f[8], r[8];
     unpack8(ldg16(y + g * 8), f);
-    load8f(bn + cv * 8, sc);
-    load8f(bn + C + cv * 8, sh);
     const long ri = rl_up ? ((((long)b * (H >> 1) + (h >> 1)) * (W >> 1) + (w >> 1)) * c8 + cv) : g;
     unpack8(ldg16(rl + ri * 8), r);
 #pragma unroll
@@ -758,18 +806,21 @@ __device__ __forceinline__ void load_row_window(const __nv_bfloat16* __restrict_
 
 __global__ void __launch_bounds__(TPB, 2) dw3x3_fwd_v2_k(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
                                                          const float* __restrict__ bn, __nv_bfloat16* __restrict__ out,
-                                                         int B, int H, int W, int C, int mode) {
+                                                         int B, int H, int W, int C, int mode, const BnFin fin) {
   const int c8 = C >> 3, WS = W / DWS;
   const long total = (long)B * H * WS * c8;
-  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long)gridDim.x * blockDim.x) {
-    const int cv = (int)(g % c8);
+  const long g0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int cv = (int)(g0 % c8);  // grid stride is a multiple of c8: the channel vector is loop invariant
+  float sc[8], sh[8];
+  if (mode == 1) bn_coeffs(fin, bn, C, cv, sc, sh);
+  bn_publish(fin, C);
+  for (long g = g0; g < total; g += (long)gridDim.x * blockDim.x) {
     long s = g / c8;
     const int ws = (int)(s % WS); s /= WS;
     const int hh = (int)(s % H);
     const long b = s / H;
     const int w0 = ws * DWS;
-    float sc[8], sh[8], acc[DWS][8];
-    if (mode == 1) { load8f(bn + cv * 8, sc); load8f(bn + C + cv * 8, sh); }
+    float acc[DWS][8];
 #pragma unroll
     for (int i = 0; i < DWS; ++i)
 #pragma unroll
@@ -1083,7 +1134,7 @@ int crackfl_bn_act(const void* y, const float* bn, void* out, void* even, int B,
                    cudaStream_t st) {
   const long total = (long)B * H * W * (C / 8);
   bn_act_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, bn, (__nv_bfloat16*)out, (__nv_bfloat16*)even, B, H, W,
-                                            C, relu);
+                                            C, relu, BnFin{});
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -1093,7 +1144,7 @@ int crackfl_dw3x3_fwd(const void* x, const float* w, const float* bn, void* out,
   const long total = (long)B * H * W * (C / 8);
   if (W % DWS == 0) {
     dw3x3_fwd_v2_k<<<grid_for(total / DWS, 148 * 8), TPB, 0, st>>>((const __nv_bfloat16*)x, w, bn, (__nv_bfloat16*)out, B, H, W,
-                                                                  C, mode);
+                                                                  C, mode, BnFin{});
     CK_LAUNCH_CHECK();
     return 0;
   }
@@ -1134,7 +1185,7 @@ int crackfl_pool_add_fwd(const void* y, const float* bn, const void* res, void* 
   const long total = (long)B * (H / 2) * (W / 2) * (C / 8);
   pool_add_fwd_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, bn, (const __nv_bfloat16*)res,
                                                   (__nv_bfloat16*)out, (__nv_bfloat16*)even, (__nv_bfloat16*)relu_out,
-                                                  (uint8_t*)arg, B, H, W, C);
+                                                  (uint8_t*)arg, B, H, W, C, BnFin{});
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -1143,7 +1194,7 @@ int crackfl_dec_combine_fwd(const void* y, const float* bn, const void* rl, void
                             int C, int rl_up, cudaStream_t st) {
   const long total = (long)B * H * W * (C / 8);
   dec_combine_fwd_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, bn, (const __nv_bfloat16*)rl,
-                                                     (__nv_bfloat16*)s, (__nv_bfloat16*)a_next, B, H, W, C, rl_up);
+                                                     (__nv_bfloat16*)s, (__nv_bfloat16*)a_next, B, H, W, C, rl_up, BnFin{});
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -1256,6 +1307,48 @@ int crackfl_dw3x3_wgrad(const void* g, const void* src, const float* bn, float* 
 
 }  // extern "C"
 
+extern "C" {
+
+int crackfl_bn_act_fin(const void* y, const crackfl_bn_fin* fin, void* out, void* even, int B, int H, int W, int C, int relu,
+                       cudaStream_t st) {
+  const long total = (long)B * H * W * (C / 8);
+  bn_act_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, nullptr, (__nv_bfloat16*)out, (__nv_bfloat16*)even, B, H, W,
+                                            C, relu, *fin);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_dw3x3_fwd_fin(const void* x, const float* w, const crackfl_bn_fin* fin, void* out, int B, int H, int W, int C,
+                          cudaStream_t st) {
+  if (W % DWS) return (int)cudaErrorInvalidValue;
+  const long total = (long)B * H * W * (C / 8);
+  dw3x3_fwd_v2_k<<<grid_for(total / DWS, 148 * 8), TPB, 0, st>>>((const __nv_bfloat16*)x, w, nullptr, (__nv_bfloat16*)out, B, H,
+                                                                W, C, 1, *fin);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_pool_add_fwd_fin(const void* y, const crackfl_bn_fin* fin, const void* res, void* out, void* even, void* relu_out,
+                             void* arg, int B, int H, int W, int C, cudaStream_t st) {
+  const long total = (long)B * (H / 2) * (W / 2) * (C / 8);
+  pool_add_fwd_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, nullptr, (const __nv_bfloat16*)res,
+                                                  (__nv_bfloat16*)out, (__nv_bfloat16*)even, (__nv_bfloat16*)relu_out,
+                                                  (uint8_t*)arg, B, H, W, C, *fin);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_dec_combine_fwd_fin(const void* y, const crackfl_bn_fin* fin, const void* rl, void* s, void* a_next, int B, int H,
+                                int W, int C, int rl_up, cudaStream_t st) {
+  const long total = (long)B * H * W * (C / 8);
+  dec_combine_fwd_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, nullptr, (const __nv_bfloat16*)rl,
+                                                     (__nv_bfloat16*)s, (__nv_bfloat16*)a_next, B, H, W, C, rl_up, *fin);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"
+
 // ---------------------------------------------------------------------------------------------------------
 // Allocation-free training-mode BatchNorm(+ReLU) forward.
 //
@@ -1332,7 +1425,7 @@ int crackfl_bn_train_fwd_noalloc(const void* y, const float* gamma, const float*
   bn_finalize_k<<<(C + 127) / 128, 128, 0, st>>>(stats, gamma, beta, run_mean, run_var, bn, C, (float)P, eps, momentum);
   CK_LAUNCH_CHECK();
   bn_act_k<<<grid_for(P * (C / 8)), TPB, 0, st>>>((const __nv_bfloat16*)y, bn, (__nv_bfloat16*)out, nullptr, B, H, W, C,
-                                                 relu);
+                                                 relu, BnFin{});
   CK_LAUNCH_CHECK();
   return 0;
 }

@@ -38,15 +38,39 @@ __global__ void __launch_bounds__(256) adam_k(float* __restrict__ p, float* __re
   }
 }
 
+// out[dst + (n*T + t)*K + k] = bf16(arena[src + n*s_n + t*s_t + k*s_k]).  Exactly one of s_n / s_k is 1 for every
+// operand of the model; when it is s_n (the source is contiguous along n but the operand wants k contiguous) the
+// 32x32 tile goes through shared memory so that both the fp32 reads and the bf16 writes are coalesced.
 __global__ void __launch_bounds__(256) weight_prep_k(const float* __restrict__ arena, __nv_bfloat16* __restrict__ ops,
                                                      const crackfl_prep_desc* __restrict__ descs) {
+  __shared__ float tile[32][33];
   const crackfl_prep_desc d = descs[blockIdx.y];
-  const long total = (long)d.N * d.T * d.K;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const int k = (int)(i % d.K);
-    const int t = (int)((i / d.K) % d.T);
-    const long n = i / ((long)d.K * d.T);
-    ops[d.dst_off + i] = __float2bfloat16_rn(arena[d.src_off + n * d.s_n + t * d.s_t + k * d.s_k]);
+  const int tn = (d.N + 31) / 32, tk = (d.K + 31) / 32;
+  const int tiles = tn * tk * d.T;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  for (int tl = blockIdx.x; tl < tiles; tl += gridDim.x) {
+    const int kt = tl % tk, nt = (tl / tk) % tn, t = tl / (tk * tn);
+    const int n0 = nt * 32, k0 = kt * 32;
+    if (d.s_n == 1 && d.s_k != 1) {
+      // read with n fastest, write with k fastest
+      for (int r = ty; r < 32; r += 8) {
+        const int n = n0 + tx, k = k0 + r;
+        tile[r][tx] = (n < d.N && k < d.K) ? arena[d.src_off + (long)n * d.s_n + (long)t * d.s_t + (long)k * d.s_k] : 0.f;
+      }
+      __syncthreads();
+      for (int r = ty; r < 32; r += 8) {
+        const int n = n0 + r, k = k0 + tx;
+        if (n < d.N && k < d.K) ops[d.dst_off + ((long)n * d.T + t) * d.K + k] = __float2bfloat16_rn(tile[tx][r]);
+      }
+      __syncthreads();
+    } else {
+      for (int r = ty; r < 32; r += 8) {
+        const int n = n0 + r, k = k0 + tx;
+        if (n < d.N && k < d.K)
+          ops[d.dst_off + ((long)n * d.T + t) * d.K + k] =
+              __float2bfloat16_rn(arena[d.src_off + (long)n * d.s_n + (long)t * d.s_t + (long)k * d.s_k]);
+      }
+    }
   }
 }
 
@@ -98,7 +122,7 @@ int crackfl_adam_step(float* p, float* g, float* m, float* v, int* step, long n,
 }
 
 int crackfl_weight_prep(const float* arena, void* ops, const crackfl_prep_desc* descs_dev, int num_desc, cudaStream_t st) {
-  dim3 grid(32, num_desc);
+  dim3 grid(48, num_desc);
   weight_prep_k<<<grid, 256, 0, st>>>(arena, (__nv_bfloat16*)ops, descs_dev);
   CK_LAUNCH_CHECK();
   return 0;

@@ -17,6 +17,19 @@
 extern "C" {
 #endif
 
+/* BatchNorm finalize folded into the consumer kernel (the *_fin launchers): scale/shift are derived from the
+ * sum / sum-of-squares accumulators on the fly; block 0 publishes bn_out = [scale|shift|mean|invstd] and updates
+ * the moving statistics.  Saves one launch per BN layer on the critical path. */
+typedef struct {
+  const float* stats;  /* [sum C][sumsq C] */
+  const float* gamma;
+  const float* beta;
+  float* run_mean;
+  float* run_var;
+  float* bn_out;       /* [4C] */
+  float count, eps, momentum;
+} crackfl_bn_fin;
+
 /* ---- entry block ------------------------------------------------------------------------- */
 /* ref: client_fit_model.py:100 Conv2D(32,3,strides=2,"same") + :43 x/255.  uint8 NHWC in, bf16 out. */
 int crackfl_entry_conv_fwd(const void* x_u8, const float* w, const float* bias, void* y, int B, int H, int W, int C,
@@ -51,6 +64,9 @@ int crackfl_bn_train_fwd_noalloc(const void* y, const float* gamma, const float*
                                  cudaStream_t stream);
 int crackfl_noalloc_max_channels(void);
 
+int crackfl_bn_act_fin(const void* y, const crackfl_bn_fin* fin, void* out, void* even_or_null, int B, int H, int W, int C,
+                       int relu, cudaStream_t stream);
+
 /* ---- depthwise 3x3 (ref: SeparableConv2D, client_fit_model.py:109,113) -------------------- */
 /* mode 0: a = relu(x); mode 1: a = relu(x*scale+shift) */
 int crackfl_dw3x3_fwd(const void* x, const float* w, const float* bn, void* out, int B, int H, int W, int C, int mode,
@@ -64,6 +80,9 @@ int crackfl_dw3x3_dgrad(const void* g, const void* src, const float* w, const fl
 int crackfl_dw3x3_wgrad(const void* g, const void* src, const float* bn, float* dwk, int B, int H, int W, int C, int mode,
                         cudaStream_t stream);
 
+int crackfl_dw3x3_fwd_fin(const void* x, const float* w, const crackfl_bn_fin* fin, void* out, int B, int H, int W, int C,
+                          cudaStream_t stream); /* a = relu(bn(x)), W % 4 == 0 */
+
 /* ---- block tails --------------------------------------------------------------------------- */
 /* ref: client_fit_model.py:116-123 MaxPooling2D(3,2,"same") + add(residual) */
 int crackfl_pool_add_fwd(const void* y, const float* bn, const void* res, void* out, void* even_or_null,
@@ -71,6 +90,10 @@ int crackfl_pool_add_fwd(const void* y, const float* bn, const void* res, void* 
 /* ref: client_fit_model.py:136-142 UpSampling2D(2) x2 + Conv2D 1x1 + add, evaluated at low resolution */
 int crackfl_dec_combine_fwd(const void* y, const float* bn, const void* rl, void* s, void* a_next_or_null, int B, int H,
                             int W, int C, int rl_up, cudaStream_t stream);
+int crackfl_pool_add_fwd_fin(const void* y, const crackfl_bn_fin* fin, const void* res, void* out, void* even_or_null,
+                             void* relu_out_or_null, void* argmax_u8, int B, int H, int W, int C, cudaStream_t stream);
+int crackfl_dec_combine_fwd_fin(const void* y, const crackfl_bn_fin* fin, const void* rl, void* s, void* a_next_or_null, int B,
+                                int H, int W, int C, int rl_up, cudaStream_t stream);
 int crackfl_down2sum(const void* in, const void* mask_or_null, const void* add_or_null, void* out, int B, int Ho, int Wo,
                      int C, cudaStream_t stream);
 int crackfl_relu_bwd_add(const void* g, const void* x, const void* add_or_null, void* out, long numel, cudaStream_t stream);
