@@ -61,6 +61,7 @@ class UNetEngine:
         self._bufs: Dict[str, torch.Tensor] = {}
         self._fins: list = []
         self.fuse_finalize = os.environ.get("CRACKFL_FUSE_FINALIZE", "1") != "0"
+        self.dw_tma = os.environ.get("CRACKFL_DW_TMA", "1") != "0"
         with torch.cuda.device(self.dev):
             self._alloc_params()
             self._build_ops_table()
@@ -221,7 +222,10 @@ class UNetEngine:
 
     def _dw_bwd(self, prog, g, src, w, bn, resid_t, dz, dwk, B, H, W, C, mode, resid):
         """Depthwise backward: input gradient on the main stream, weight gradient on the side stream."""
-        if W % 4 == 0 and 128 % (C // 8) == 0:
+        if self.dw_tma:
+            prog.append((self.lib.crackfl_dw3x3_tma, (g, w, 0, None, dz, src, bn, resid_t, B, H, W, C, 2, 1, mode, resid)))
+            prog.append((self.lib.crackfl_dw3x3_wgrad_tma, (g, src, bn, dwk, B, H, W, C, mode), "side"))
+        elif W % 4 == 0 and 128 % (C // 8) == 0:
             prog.append((self.lib.crackfl_dw3x3_dgrad, (g, src, w, bn, resid_t, dz, B, H, W, C, mode, resid)))
             prog.append((self.lib.crackfl_dw3x3_wgrad, (g, src, bn, dwk, B, H, W, C, mode), "side"))
         else:
@@ -298,12 +302,20 @@ class UNetEngine:
             p = f"e{e['k']}."
             r, rw, cin, f = e["r"], e["rw"], e["cin"], e["f"]
             Pn = B * r * rw
-            prog.append((lib.crackfl_dw3x3_fwd, (b(xin), self.P(sep1.tensors[0]), 0, b(p + "d1"), B, r, rw, cin, 0)))
+            if self.dw_tma:
+                prog.append((lib.crackfl_dw3x3_tma, (b(xin), self.P(sep1.tensors[0]), 0, None, b(p + "d1"), 0, 0, 0,
+                                                     B, r, rw, cin, 0, 0, 0, 0)))
+            else:
+                prog.append((lib.crackfl_dw3x3_fwd, (b(xin), self.P(sep1.tensors[0]), 0, b(p + "d1"), B, r, rw, cin, 0)))
             sd = self._gemm(prog, b(p + "d1"), sep1.name + ".f", self.P(sep1.tensors[2]), 0, b(p + "y1"), B, r, rw,
                             self._zptr(bn1.name, "stats") if training else 0)
-            fuse_dw = fuse and rw % 4 == 0
+            fuse_dw = fuse and (rw % 4 == 0 or self.dw_tma)
             bn(bn1, b(p + "y1"), Pn, sd, consumer_finalizes=fuse_dw)
-            if fuse_dw:
+            if self.dw_tma:
+                prog.append((lib.crackfl_dw3x3_tma, (b(p + "y1"), self.P(sep2.tensors[0]), self._bnptr(bn1.name),
+                                                     self._fin(bn1, Pn) if fuse_dw else None, b(p + "d2"), 0, 0, 0,
+                                                     B, r, rw, f, 1, 0, 0, 0)))
+            elif fuse_dw:
                 prog.append((lib.crackfl_dw3x3_fwd_fin, (b(p + "y1"), self.P(sep2.tensors[0]), self._fin(bn1, Pn), b(p + "d2"),
                                                          B, r, rw, f)))
             else:

@@ -55,6 +55,8 @@ _SIGS = {
     "crackfl_dw3x3_fwd_fin": [vp, vp, C.POINTER(BnFin), vp, i32, i32, i32, i32, vp],
     "crackfl_pool_add_fwd_fin": [vp, C.POINTER(BnFin), vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],
     "crackfl_dec_combine_fwd_fin": [vp, C.POINTER(BnFin), vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    "crackfl_dw3x3_tma": [vp, vp, vp, C.POINTER(BnFin), vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+    "crackfl_dw3x3_wgrad_tma": [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_dw3x3_dgrad": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
     "crackfl_dw3x3_wgrad": [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_pool_add_fwd": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],

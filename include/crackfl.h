@@ -83,6 +83,15 @@ int crackfl_dw3x3_wgrad(const void* g, const void* src, const float* bn, float* 
 int crackfl_dw3x3_fwd_fin(const void* x, const float* w, const crackfl_bn_fin* fin, void* out, int B, int H, int W, int C,
                           cudaStream_t stream); /* a = relu(bn(x)), W % 4 == 0 */
 
+/* second generation: TMA-staged halo tiles (csrc/dw_tma.cu).  Forward: src = NULL, flip = 0, act_mode 0 relu(x) /
+ * 1 relu(bn(x)) (bn pointer or fused-finalize struct).  Input gradient: x = g, act_mode = 2, flip = 1, src = forward
+ * input (src_mode 0: mask = src > 0, 1: mask = bn(src) > 0), resid as crackfl_dw3x3_bwd.  C in {32, 64, 128, ...}. */
+int crackfl_dw3x3_tma(const void* x, const float* w, const float* bn, const crackfl_bn_fin* fin_or_null, void* out,
+                      const void* src_or_null, const float* src_bn, const void* resid_t, int B, int H, int W, int C,
+                      int act_mode, int flip, int src_mode, int resid, cudaStream_t stream);
+int crackfl_dw3x3_wgrad_tma(const void* g, const void* src, const float* bn, float* dwk, int B, int H, int W, int C, int mode,
+                            cudaStream_t stream);
+
 /* ---- block tails --------------------------------------------------------------------------- */
 /* ref: client_fit_model.py:116-123 MaxPooling2D(3,2,"same") + add(residual) */
 int crackfl_pool_add_fwd(const void* y, const float* bn, const void* res, void* out, void* even_or_null,

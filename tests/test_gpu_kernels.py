@@ -270,3 +270,36 @@ def test_server_with_device_aggregator(tmp_path):
     assert pb.from_config(rep.update_rep.config)["state"] == "RESP_ARY"
     np.testing.assert_allclose(wio.loads_auto(rep.update_rep.buffer_chunk)[0], w0[0] + 4.0, rtol=1e-5, atol=1e-5)
     assert srv.history[0]["aggregator"] == "device"
+
+
+@pytest.mark.parametrize("B,H,W,Cc,mode", [(2, 32, 32, 64, 0), (2, 20, 24, 32, 1), (1, 16, 16, 128, 1), (2, 14, 14, 64, 0)])
+def test_dw3x3_tma_fwd_dgrad_wgrad(B, H, W, Cc, mode):
+    """TMA-staged depthwise kernels vs autograd of relu[(bn)] -> depthwise conv."""
+    L, lib = _lib()
+    torch.manual_seed(0)
+    x = torch.randn(B, H, W, Cc, device="cuda").bfloat16()
+    w = torch.randn(9, Cc, device="cuda") * 0.3
+    bn = torch.cat([torch.rand(Cc, device="cuda") + 0.5, torch.randn(Cc, device="cuda") * 0.2,
+                    torch.zeros(2 * Cc, device="cuda")])
+    out = torch.zeros_like(x)
+    L.check(lib.crackfl_dw3x3_tma(x.data_ptr(), w.data_ptr(), bn.data_ptr(), None, out.data_ptr(), 0, 0, 0, B, H, W, Cc,
+                                  mode, 0, 0, 0, _st()))
+    xr = x.float().permute(0, 3, 1, 2).clone().requires_grad_(True)
+    wr = w.reshape(3, 3, Cc).permute(2, 0, 1)[:, None].clone().requires_grad_(True)
+    pre = xr * bn[:Cc][None, :, None, None] + bn[Cc:2 * Cc][None, :, None, None] if mode == 1 else xr
+    ref = F.conv2d(F.relu(pre), wr, padding=1, groups=Cc)
+    torch.cuda.synchronize()
+    assert float((out.float().permute(0, 3, 1, 2) - ref.detach()).norm() / ref.detach().norm()) < 1e-2
+    g = torch.randn(B, H, W, Cc, device="cuda").bfloat16()
+    ref.backward(g.float().permute(0, 3, 1, 2))
+    # input gradient w.r.t. the pre-activation tensor: mask * dw^T(g)   (the BN scale is applied by the caller)
+    dz = torch.zeros_like(x)
+    L.check(lib.crackfl_dw3x3_tma(g.data_ptr(), w.data_ptr(), 0, None, dz.data_ptr(), x.data_ptr(), bn.data_ptr(), 0, B, H, W,
+                                  Cc, 2, 1, mode, 0, _st()))
+    dwk = torch.zeros(9, Cc, device="cuda")
+    L.check(lib.crackfl_dw3x3_wgrad_tma(g.data_ptr(), x.data_ptr(), bn.data_ptr(), dwk.data_ptr(), B, H, W, Cc, mode, _st()))
+    torch.cuda.synchronize()
+    want = xr.grad / (bn[:Cc][None, :, None, None] if mode == 1 else 1.0)
+    assert float((dz.float().permute(0, 3, 1, 2) - want).norm() / want.norm()) < 1.5e-2
+    refw = wr.grad[:, 0].permute(1, 2, 0).reshape(9, Cc)
+    assert float((dwk - refw).norm() / refw.norm()) < 1e-2
