@@ -434,11 +434,13 @@ class UNetEngine:
             self._wgrad(prog, b(xe), b(dx_next), self.G(res.tensors[0]), B, r2, rw2, cin, f, 1, 0, f, 1)
             prog.append((lib.crackfl_colsum, (b(dx_next), self.G(res.tensors[1]), B * r2 * rw2, f), "side"))
             # max-pool + BN2
-            prog.append((lib.crackfl_bn_bwd_reduce, (b(dx_next), b(p + "arg"), b(p + "y2"), self._bnptr(bn2.name),
-                                                     self._zptr(bn2.name, "sums"), B, r, rw, f, 2)))
-            prog.append((lib.crackfl_bn_bwd_apply, (b(dx_next), b(p + "arg"), b(p + "y2"), self._bnptr(bn2.name),
+            # max-pool backward once into dd2 (reused below as the pointwise dgrad output), then DIRECT-mode BN backward
+            prog.append((lib.crackfl_pool_bwd, (b(dx_next), b(p + "arg"), b(p + "dd2"), B, r, rw, f)))
+            prog.append((lib.crackfl_bn_bwd_reduce, (b(p + "dd2"), 0, b(p + "y2"), self._bnptr(bn2.name),
+                                                     self._zptr(bn2.name, "sums"), B, r, rw, f, 0)))
+            prog.append((lib.crackfl_bn_bwd_apply, (b(p + "dd2"), 0, b(p + "y2"), self._bnptr(bn2.name),
                                                     self._zptr(bn2.name, "sums"), b(p + "dy2"), self.G(bn2.tensors[0]),
-                                                    self.G(bn2.tensors[1]), B, r, rw, f, 2)))
+                                                    self.G(bn2.tensors[1]), B, r, rw, f, 0)))
             # pointwise 2
             self._gemm(prog, b(p + "dy2"), sep2.name + ".d", 0, 0, b(p + "dd2"), B, r, rw)
             self._wgrad(prog, b(p + "d2"), b(p + "dy2"), self.G(sep2.tensors[1]), B, r, rw, f, f, 1, 0, f, 1)

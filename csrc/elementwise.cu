@@ -620,6 +620,20 @@ __global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : 3) bn_bwd_apply_k(const _
   }
 }
 
+// max-pool backward materialised once: dz[p] = sum over the windows covering p of g[q] * [argmax[q] == offset(p,q)].
+// The BN2 reduce + apply kernels then run in their cheap DIRECT mode instead of decoding the arg-max twice.
+__global__ void __launch_bounds__(TPB, 3) pool_bwd_k(const __nv_bfloat16* __restrict__ g, const uint8_t* __restrict__ arg,
+                                                     __nv_bfloat16* __restrict__ dz, long P, int H, int W, int C) {
+  const int c8 = C >> 3;
+  const long total = P * c8;
+  float unused[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (long gi = (long)blockIdx.x * blockDim.x + threadIdx.x; gi < total; gi += (long)gridDim.x * blockDim.x) {
+    float v[8];
+    load_dz<2>(g, arg, gi / c8, (int)(gi % c8), c8, H, W, unused, unused, unused, v);
+    stg16(dz + gi * 8, pack8(v));
+  }
+}
+
 // column sum of a [P][C] bf16 matrix into fp32 (bias gradient of the residual convs)
 __global__ void __launch_bounds__(TPB) colsum_k(const __nv_bfloat16* __restrict__ g, float* __restrict__ out, long P, int C,
                                                 int pix_per_block) {
@@ -1343,6 +1357,17 @@ int crackfl_dec_combine_fwd_fin(const void* y, const crackfl_bn_fin* fin, const 
   const long total = (long)B * H * W * (C / 8);
   dec_combine_fwd_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, nullptr, (const __nv_bfloat16*)rl,
                                                      (__nv_bfloat16*)s, (__nv_bfloat16*)a_next, B, H, W, C, rl_up, *fin);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+int crackfl_pool_bwd(const void* g, const void* arg, void* dz, int B, int H, int W, int C, cudaStream_t st) {
+  const long P = (long)B * H * W;
+  pool_bwd_k<<<grid_for(P * (C / 8)), TPB, 0, st>>>((const __nv_bfloat16*)g, (const uint8_t*)arg, (__nv_bfloat16*)dz, P, H, W, C);
   CK_LAUNCH_CHECK();
   return 0;
 }

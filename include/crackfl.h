@@ -103,6 +103,8 @@ int crackfl_pool_add_fwd_fin(const void* y, const crackfl_bn_fin* fin, const voi
                              void* relu_out_or_null, void* argmax_u8, int B, int H, int W, int C, cudaStream_t stream);
 int crackfl_dec_combine_fwd_fin(const void* y, const crackfl_bn_fin* fin, const void* rl, void* s, void* a_next_or_null, int B,
                                 int H, int W, int C, int rl_up, cudaStream_t stream);
+/* max-pool backward: scatter-free gather of g [B,H/2,W/2,C] through the arg-max map into dz [B,H,W,C] */
+int crackfl_pool_bwd(const void* g, const void* argmax_u8, void* dz, int B, int H, int W, int C, cudaStream_t stream);
 int crackfl_down2sum(const void* in, const void* mask_or_null, const void* add_or_null, void* out, int B, int Ho, int Wo,
                      int C, cudaStream_t stream);
 int crackfl_relu_bwd_add(const void* g, const void* x, const void* add_or_null, void* out, long numel, cudaStream_t stream);
