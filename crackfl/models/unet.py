@@ -69,6 +69,9 @@ class UNetEngine:
             self.train_prog = self._build_train()
             self.eval_prog = self._build_forward(training=False, with_mask=True, prob=False)
             self.pred_prog = self._build_forward(training=False, with_mask=False, prob=True)
+        skip = [k for k in os.environ.get("CRACKFL_SKIP_KERNELS", "").split(",") if k]
+        if skip:  # profiling aid only ("what if this kernel were free"): the step no longer trains correctly
+            self.train_prog = [e for e in self.train_prog if e[0] is None or not any(k in e[0].__name__ for k in skip)]
         self._graphs: Dict[str, torch.cuda.CUDAGraph] = {}
         self._side_stream = torch.cuda.Stream(self.dev)
         self.launches_per_step = sum(1 for e in self.train_prog if e[0] is not None) + 2  # + adam tick + metric accumulation
@@ -217,8 +220,14 @@ class UNetEngine:
         return False
 
     def _wgrad(self, prog, X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co):
-        fn = self.lib.crackfl_wgrad_tc if self.conv_impl == "tc" else self.lib.crackfl_wgrad_simt
-        prog.append((fn, (X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co), "side"))
+        if self.conv_impl == "tc":
+            if "wgrad_ws" not in self._bufs:  # split-reduction workspace shared by all (stream-ordered) wgrad launches
+                self._new("wgrad_ws", (8 << 20,), torch.float32)
+            ws = self._bufs["wgrad_ws"]
+            prog.append((self.lib.crackfl_wgrad_tc_ws, (X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co,
+                                                        ws.data_ptr(), ws.numel()), "side"))
+        else:
+            prog.append((self.lib.crackfl_wgrad_simt, (X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co), "side"))
 
     def _dw_bwd(self, prog, g, src, w, bn, resid_t, dz, dwk, B, H, W, C, mode, resid):
         """Depthwise backward: input gradient on the main stream, weight gradient on the side stream."""

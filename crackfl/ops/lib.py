@@ -71,6 +71,7 @@ _SIGS = {
     "crackfl_wgrad_simt": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, vp],
     "crackfl_conv_tc_fwd": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
     "crackfl_wgrad_tc": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, vp],
+    "crackfl_wgrad_tc_ws": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, vp, i64, vp],
     "crackfl_tc_selftest_supported": [],
     "crackfl_weight_prep": [vp, vp, vp, i32, vp],
     "crackfl_adam_step": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, vp],

@@ -707,6 +707,8 @@ struct WgradArgs {
   int B, H, W, Cin, Cout, taps;
   int cw, nw, BN, mblk, nblk;     // channel width of one A box / one B box; boxes per operand
   int total_blocks, ntiles, tiles_per_split, stages;
+  int dbg_noatomic;  // profiling aid: skip the epilogue atomics
+  float* ws;         // per-CTA partial tiles [grid][128][BN] (NULL: fp32 atomics straight into dW)
   uint32_t layoutA, sboA, layoutB, sboB;
   TileGeom g;
 };
@@ -752,6 +754,11 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tptr));
 
+  if (iters <= 0 && a.ws && warp >= 2) {
+    const long cta = ((long)blockIdx.x * gridDim.y + blockIdx.y) * gridDim.z + blockIdx.z;
+    const int r = (warp & 3) * 32 + lane;
+    for (int c = 0; c < a.BN; ++c) a.ws[(cta * 128 + r) * a.BN + c] = 0.f;
+  }
   if (iters > 0) {
     if (warp == 0) {
       if (lane == 0) {
@@ -807,7 +814,15 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
       for (int c0 = 0; c0 < a.BN; c0 += 32) {
         uint32_t raw[32];
         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, raw);
-        if (valid) {
+        if (a.ws) {
+          // contention-free: this CTA's partial tile goes to its own slab, wgrad_reduce_k sums the slabs
+          const long cta = ((long)blockIdx.x * gridDim.y + blockIdx.y) * gridDim.z + blockIdx.z;
+          float4* wp = reinterpret_cast<float4*>(a.ws + (cta * 128 + r) * a.BN + c0);
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            wp[j >> 2] = make_float4(__uint_as_float(raw[j]), __uint_as_float(raw[j + 1]), __uint_as_float(raw[j + 2]),
+                                     __uint_as_float(raw[j + 3]));
+        } else if (valid && !a.dbg_noatomic) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) atomicAdd(dst + (long)(n0 + c0 + j) * a.s_co, __uint_as_float(raw[j]));
         }
@@ -819,6 +834,28 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, ncols);
+  }
+}
+
+// Sum the per-CTA partial tiles of wgrad_tc_k over the pixel splits and add the result into the Keras-layout
+// gradient arena (one writer per element, no atomics).
+__global__ void __launch_bounds__(256) wgrad_reduce_k(const float* __restrict__ ws, float* __restrict__ dW, int groups, int ntn,
+                                                      int splits, int BN, int cw, int mblk, int total_blocks, int cchunks,
+                                                      long s_tap, long s_ci, long s_co) {
+  const long per_tile = 128L * BN;
+  const long total = (long)groups * ntn * per_tile;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % BN);
+    const int r = (int)((i / BN) % 128);
+    const long gt = i / per_tile;  // g * ntn + nt
+    const int nt = (int)(gt % ntn), g = (int)(gt / ntn);
+    const int blk = g * mblk + r / cw;
+    if (blk >= total_blocks) continue;
+    const float* p = ws + (gt * splits) * per_tile + (long)r * BN + c;
+    float acc = 0.f;
+    for (int z = 0; z < splits; ++z) acc += p[z * per_tile];
+    const int t = blk / cchunks, ci = (blk % cchunks) * cw + (r % cw);
+    dW[(long)t * s_tap + (long)ci * s_ci + (long)(nt * BN + c) * s_co] += acc;
   }
 }
 
@@ -1096,8 +1133,8 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
   return 0;
 }
 
-int crackfl_wgrad_tc(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps, long s_tap,
-                     long s_ci, long s_co, cudaStream_t st) {
+int crackfl_wgrad_tc_ws(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps,
+                        long s_tap, long s_ci, long s_co, float* workspace, long workspace_floats, cudaStream_t st) {
   if (Cin % 32 || Cout % 32 || (taps != 1 && taps != 9)) return (int)cudaErrorInvalidValue;
   WgradArgs a;
   a.dW = dW; a.s_tap = s_tap; a.s_ci = s_ci; a.s_co = s_co;
@@ -1120,6 +1157,13 @@ int crackfl_wgrad_tc(const void* X, const void* dY, float* dW, int B, int H, int
   // CTA) from serialising in L2
   const uint32_t stage_bytes = 128u * 128u * 2u + 128u * (uint32_t)a.BN * 2u;
   int per_sm = (2u * stage_bytes <= 106496u) ? 2 : 1;
+  {
+    static int dbg_persm = -1, dbg_noat = -1;
+    if (dbg_persm < 0) { const char* e = getenv("CRACKFL_WGRAD_PERSM"); dbg_persm = e ? atoi(e) : 0; }
+    if (dbg_noat < 0) { const char* e = getenv("CRACKFL_WGRAD_NOATOMIC"); dbg_noat = e ? atoi(e) : 0; }
+    if (dbg_persm == 1) per_sm = 1;
+    a.dbg_noatomic = dbg_noat;
+  }
   int stages = per_sm == 2 ? (int)(106496u / stage_bytes) : (int)(200704u / stage_bytes);
   if (stages > 4) stages = 4;
   int splits = (148 * per_sm) / (groups * ntn);
@@ -1145,9 +1189,24 @@ int crackfl_wgrad_tc(const void* X, const void* dY, float* dW, int B, int H, int
     attr_set = true;
   }
   dim3 grid(groups, ntn, splits);
+  const long need = (long)groups * ntn * splits * 128L * a.BN;
+  a.ws = (workspace && workspace_floats >= need) ? workspace : nullptr;
   wgrad_tc_k<<<grid, 192, smem, st>>>(tmX, tmDY, a);
   CK_LAUNCH_CHECK();
+  if (a.ws) {
+    const long total = (long)groups * ntn * 128L * a.BN;
+    long blocks = (total + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    wgrad_reduce_k<<<(int)blocks, 256, 0, st>>>(a.ws, dW, groups, ntn, splits, a.BN, a.cw, a.mblk, a.total_blocks, Cin / a.cw,
+                                               s_tap, s_ci, s_co);
+    CK_LAUNCH_CHECK();
+  }
   return 0;
+}
+
+int crackfl_wgrad_tc(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps, long s_tap,
+                     long s_ci, long s_co, cudaStream_t st) {
+  return crackfl_wgrad_tc_ws(X, dY, dW, B, H, W, Cin, Cout, taps, s_tap, s_ci, s_co, nullptr, 0, st);
 }
 
 }  // extern "C"

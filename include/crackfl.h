@@ -131,6 +131,10 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias_or_null
 /* tcgen05 weight gradient with MN-major operands, split over pixels, fp32 atomics into the arena. */
 int crackfl_wgrad_tc(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps, long s_tap,
                      long s_ci, long s_co, cudaStream_t stream);
+/* same with a caller-provided workspace (>= groups*ntiles*splits*128*BN floats, 32 MB covers every layer of the
+ * model): per-CTA partial tiles + a reduction pass instead of contended fp32 atomics (about 2x faster). */
+int crackfl_wgrad_tc_ws(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps,
+                        long s_tap, long s_ci, long s_co, float* workspace, long workspace_floats, cudaStream_t stream);
 int crackfl_tc_selftest_supported(void);
 
 /* ---- optimiser / weight re-layout ------------------------------------------------------------ */

@@ -69,7 +69,7 @@ def test_conv_tc_fused_stats_and_add(impl):
     assert torch.allclose(stats[N:], (yf * yf).sum(0), rtol=2e-2, atol=0.5)
 
 
-@pytest.mark.parametrize("impl", ["simt", "tc"])
+@pytest.mark.parametrize("impl", ["simt", "tc", "tc_ws"])
 @pytest.mark.parametrize("B,H,W,cin,cout,taps", [(2, 16, 16, 32, 32, 9), (2, 8, 8, 256, 256, 9), (2, 16, 16, 64, 128, 1),
                                                   (2, 32, 32, 128, 64, 9), (1, 28, 28, 32, 64, 1)])
 def test_wgrad(impl, B, H, W, cin, cout, taps):
@@ -78,8 +78,15 @@ def test_wgrad(impl, B, H, W, cin, cout, taps):
     x = torch.randn(B, H, W, cin, device="cuda").bfloat16()
     dy = torch.randn(B, H, W, cout, device="cuda").bfloat16()
     dw = torch.zeros(taps, cin, cout, device="cuda")
-    fn = lib.crackfl_wgrad_simt if impl == "simt" else lib.crackfl_wgrad_tc
-    L.check(fn(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), B, H, W, cin, cout, taps, cin * cout, cout, 1, _st()))
+    if impl == "tc_ws":  # split partials in a workspace + reduction pass (no atomics); run twice: accumulates
+        ws = torch.empty(8 << 20, device="cuda")
+        for _ in range(2):
+            L.check(lib.crackfl_wgrad_tc_ws(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), B, H, W, cin, cout, taps, cin * cout,
+                                            cout, 1, ws.data_ptr(), ws.numel(), _st()))
+        dw = dw / 2
+    else:
+        fn = lib.crackfl_wgrad_simt if impl == "simt" else lib.crackfl_wgrad_tc
+        L.check(fn(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), B, H, W, cin, cout, taps, cin * cout, cout, 1, _st()))
     torch.cuda.synchronize()
     k = 3 if taps == 9 else 1
     w = torch.zeros(cout, cin, k, k, device="cuda", requires_grad=True)
