@@ -4,6 +4,7 @@
 // Every kernel is HBM-bound; the design goal is one pass per tensor with the neighbouring
 // pointwise work (BN-apply, ReLU, residual add, nearest upsample, /255) fused in.
 #include <cstdio>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "../include/crackfl.h"
@@ -1083,9 +1084,11 @@ inline int grid_for(long total, int cap = 148 * 16) {
 }
 
 inline int ppb_for(long P, int C) {
-  // pixels per block for the reduction kernels: aim at ~2 waves of 148 SMs x 4 blocks, >= one pass of all lanes
+  // pixels per block for the reduction kernels: 2 blocks per SM measured best (fewer contended atomics per channel), >= one pass of all lanes
   const int lanes = TPB / (C >> 3);
-  long target = (P + 148 * 8 - 1) / (148 * 8);
+  static int waves = -1;
+  if (waves < 0) { const char* e = getenv("CRACKFL_REDUCE_BLOCKS_PER_SM"); waves = e ? atoi(e) : 2; if (waves < 1) waves = 1; }
+  long target = (P + 148L * waves - 1) / (148L * waves);
   long ppb = ((target + lanes - 1) / lanes) * lanes;
   if (ppb < lanes * 4) ppb = lanes * 4;
   return (int)ppb;
