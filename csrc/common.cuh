@@ -4,10 +4,40 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #define CK_LAUNCH_CHECK() do { cudaError_t e__ = cudaGetLastError(); if (e__ != cudaSuccess) return (int)e__; } while (0)
 
 namespace ck {
+
+// ---- programmatic dependent launch (PDL) ------------------------------------------------------------------------------
+// Every kernel of the training step is launched with programmaticStreamSerialization and starts with
+// pdl_wait(); pdl_trigger();  The wait blocks until the preceding kernel in the stream has completed and flushed, so no
+// global memory is touched early; what overlaps with the predecessor's tail is the launch latency, CTA scheduling and the
+// per-CTA set-up before the wait (barrier init, TMEM allocation, descriptor prefetch).  The trigger lets the NEXT kernel be
+// scheduled as soon as all CTAs of this one are resident.  Because every kernel waits before it exits, completion order
+// stays transitive (kernel n+2 cannot pass its wait before kernel n has finished).  CRACKFL_PDL=0 turns the attribute off;
+// the two instructions are then no-ops.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() { pdl_wait(); pdl_trigger(); }
+
+inline int pdl_enabled() {
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("CRACKFL_PDL"); on = e ? (atoi(e) != 0) : 1; }
+  return on;
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = pdl_enabled();
+  cfg.attrs = at; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
 
 __device__ __forceinline__ void unpack8(const uint4& v, float f[8]) {
   f[0] = __uint_as_float(v.x << 16); f[1] = __uint_as_float(v.x & 0xffff0000u);

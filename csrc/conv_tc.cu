@@ -117,6 +117,7 @@ __global__ void __launch_bounds__(192) conv_tc_fwd_k(const __grid_constant__ CUt
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  ck::pdl_enter();  // set-up above overlapped the previous kernel's tail; global memory is touched only from here on
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tptr));
 
@@ -283,6 +284,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  ck::pdl_enter();  // set-up above overlapped the previous kernel's tail; global memory is touched only from here on
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tptr));
 
@@ -516,6 +518,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  ck::pdl_enter();  // set-up above overlapped the previous kernel's tail; global memory is touched only from here on
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tptr));
 
@@ -751,6 +754,7 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  ck::pdl_enter();  // set-up above overlapped the previous kernel's tail; global memory is touched only from here on
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tptr));
 
@@ -842,6 +846,7 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
 __global__ void __launch_bounds__(256) wgrad_reduce_k(const float* __restrict__ ws, float* __restrict__ dW, int groups, int ntn,
                                                       int splits, int BN, int cw, int mblk, int total_blocks, int cchunks,
                                                       long s_tap, long s_ci, long s_co) {
+  ck::pdl_enter();
   const long per_tile = 128L * BN;
   const long total = (long)groups * ntn * per_tile;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -1001,7 +1006,7 @@ static int conv_tc_fwd_v1(const void* X, const void* Wk, const float* bias, cons
     attr_set = true;
   }
   dim3 grid(a.g.tiles_w * a.g.tiles_h * a.g.tiles_b, N / a.BN);
-  conv_tc_fwd_k<<<grid, 192, smem, st>>>(tmA, tmB, a);
+  ck::launch(conv_tc_fwd_k, grid, 192, smem, st, tmA, tmB, a);
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -1080,7 +1085,7 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
     const int total = a.n_tiles_m * a.n_tiles_n;
     int grid = per_sm * g_num_sms;
     if (grid > total) grid = total;
-    conv_tc_fwd_v3_k<<<grid, 64 + EPI_THREADS, smem, st>>>(tmA, tmB, tmY, a);
+    ck::launch(conv_tc_fwd_v3_k, grid, 64 + EPI_THREADS, smem, st, tmA, tmB, tmY, a);
     CK_LAUNCH_CHECK();
     return 0;
   }
@@ -1128,7 +1133,7 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
   const int total = a.n_tiles_m * a.n_tiles_n;
   int grid = 2 * g_num_sms;
   if (grid > total) grid = total;
-  conv_tc_fwd_v2_k<<<grid, 64 + EPI_THREADS, smem, st>>>(tmA, tmB, tmY, a);
+  ck::launch(conv_tc_fwd_v2_k, grid, 64 + EPI_THREADS, smem, st, tmA, tmB, tmY, a);
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -1191,13 +1196,13 @@ int crackfl_wgrad_tc_ws(const void* X, const void* dY, float* dW, int B, int H, 
   dim3 grid(groups, ntn, splits);
   const long need = (long)groups * ntn * splits * 128L * a.BN;
   a.ws = (workspace && workspace_floats >= need) ? workspace : nullptr;
-  wgrad_tc_k<<<grid, 192, smem, st>>>(tmX, tmDY, a);
+  ck::launch(wgrad_tc_k, grid, 192, smem, st, tmX, tmDY, a);
   CK_LAUNCH_CHECK();
   if (a.ws) {
     const long total = (long)groups * ntn * 128L * a.BN;
     long blocks = (total + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
-    wgrad_reduce_k<<<(int)blocks, 256, 0, st>>>(a.ws, dW, groups, ntn, splits, a.BN, a.cw, a.mblk, a.total_blocks, Cin / a.cw,
+    ck::launch(wgrad_reduce_k, (int)blocks, 256, 0, st, a.ws, dW, groups, ntn, splits, a.BN, a.cw, a.mblk, a.total_blocks, Cin / a.cw,
                                                s_tap, s_ci, s_co);
     CK_LAUNCH_CHECK();
   }

@@ -96,6 +96,7 @@ __global__ void __launch_bounds__(256, 2) dw_stencil_k(const __grid_constant__ C
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     tma_prefetch_desc(&tmX);
   }
+  pdl_enter();  // barrier init / descriptor prefetch above overlap the previous kernel's tail
   fin_publish(a.fin, a.C);
   __syncthreads();
 
@@ -225,6 +226,7 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
     tma_prefetch_desc(&tmG);
   }
   __syncthreads();
+  pdl_enter();
 
   auto issue = [&](int tile, int stage) {
     const int cblk = tile / spatial;
@@ -363,8 +365,8 @@ int crackfl_dw3x3_tma(const void* x, const float* w, const float* bn, const crac
   }
   int grid = 2 * num_sms();
   if (grid > a.total_tiles) grid = a.total_tiles;
-  if (a.CB == 64) dw_stencil_k<TY, 1><<<grid, 256, smem, st>>>(tm, a);
-  else dw_stencil_k<TY, 2><<<grid, 256, smem, st>>>(tm, a);
+  if (a.CB == 64) ck::launch(dw_stencil_k<TY, 1>, grid, 256, smem, st, tm, a);
+  else ck::launch(dw_stencil_k<TY, 2>, grid, 256, smem, st, tm, a);
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -396,8 +398,8 @@ int crackfl_dw3x3_wgrad_tma(const void* g, const void* src, const float* bn, flo
   }
   int grid = 2 * num_sms();
   if (grid > a.total_tiles) grid = a.total_tiles;
-  if (a.CB == 64) dw_wgrad_k<TY, 1><<<grid, 256, smem, st>>>(tmA, tmG, a);
-  else dw_wgrad_k<TY, 2><<<grid, 256, smem, st>>>(tmA, tmG, a);
+  if (a.CB == 64) ck::launch(dw_wgrad_k<TY, 1>, grid, 256, smem, st, tmA, tmG, a);
+  else ck::launch(dw_wgrad_k<TY, 2>, grid, 256, smem, st, tmA, tmG, a);
   CK_LAUNCH_CHECK();
   return 0;
 }

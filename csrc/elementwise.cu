@@ -65,6 +65,7 @@ __device__ __forceinline__ void bn_publish(const BnFin& f, int C) {
 __global__ void __launch_bounds__(TPB) entry_conv_fwd_k(const uint8_t* __restrict__ x, const float* __restrict__ w,
                                                         const float* __restrict__ bias, __nv_bfloat16* __restrict__ y,
                                                         int B, int H, int W, int C) {
+  ck::pdl_enter();
   extern __shared__ float sw[];  // [27][C] + bias[C]
   for (int i = threadIdx.x; i < 27 * C; i += blockDim.x) sw[i] = w[i] * (1.0f / 255.0f);
   for (int i = threadIdx.x; i < C; i += blockDim.x) sw[27 * C + i] = bias[i];
@@ -105,6 +106,7 @@ __global__ void __launch_bounds__(TPB) entry_conv_fwd_k(const uint8_t* __restric
 // wgrad of the entry conv: dW[27][C] += sum_p patch(p)[27] * dy[p][C].  blockDim = (C/8, 27).
 __global__ void entry_conv_wgrad_k(const uint8_t* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                                    float* __restrict__ dw, int B, int H, int W, int C, int pix_per_block) {
+  ck::pdl_enter();
   const int Ho = H >> 1, Wo = W >> 1, c8 = C >> 3;
   const int cv = threadIdx.x, k = threadIdx.y;
   const int kh = k / 9, kw = (k / 3) % 3, ci = k % 3;
@@ -132,6 +134,7 @@ __global__ void entry_conv_wgrad_k(const uint8_t* __restrict__ x, const __nv_bfl
 // BN statistics (forward): per-channel sum and sum of squares.  stats = [sum C][sumsq C].
 __global__ void __launch_bounds__(TPB) bn_stats_k(const __nv_bfloat16* __restrict__ y, float* __restrict__ stats,
                                                   long P, int C, int pix_per_block) {
+  ck::pdl_enter();
   __shared__ float sm[TPB * 8];
   const int c8 = C >> 3, lanes = TPB / c8;
   const int cv = threadIdx.x % c8, lane = threadIdx.x / c8;
@@ -155,6 +158,7 @@ __global__ void bn_finalize_k(const float* __restrict__ stats, const float* __re
                               const float* __restrict__ beta, float* __restrict__ run_mean,
                               float* __restrict__ run_var, float* __restrict__ bn, int C, float count, float eps,
                               float momentum) {
+  ck::pdl_enter();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const float mean = stats[c] / count;
@@ -175,6 +179,7 @@ __global__ void bn_finalize_k(const float* __restrict__ stats, const float* __re
 __global__ void bn_eval_prepare_k(const float* __restrict__ gamma, const float* __restrict__ beta,
                                   const float* __restrict__ run_mean, const float* __restrict__ run_var,
                                   float* __restrict__ bn, int C, float eps) {
+  ck::pdl_enter();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const float invstd = rsqrtf(run_var[c] + eps);
@@ -189,6 +194,7 @@ __global__ void bn_eval_prepare_k(const float* __restrict__ gamma, const float* 
 __global__ void __launch_bounds__(TPB, 4) bn_act_k(const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
                                                    __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ even,
                                                    int B, int H, int W, int C, int relu, const BnFin fin) {
+  ck::pdl_enter();
   const int c8 = C >> 3;
   const long total = (long)B * H * W * c8;
   const long stride = (long)gridDim.x * blockDim.x;  // multiple of c8: a thread keeps its channel vector
@@ -242,6 +248,7 @@ __device__ __forceinline__ void act_load(const __nv_bfloat16* __restrict__ src, 
 __global__ void __launch_bounds__(TPB) dw3x3_fwd_k(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
                                                    const float* __restrict__ bn, __nv_bfloat16* __restrict__ out,
                                                    int B, int H, int W, int C, int mode) {
+  ck::pdl_enter();
   const int c8 = C >> 3;
   const long total = (long)B * H * W * c8;
   for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long)gridDim.x * blockDim.x) {
@@ -280,6 +287,7 @@ __global__ void __launch_bounds__(TPB) dw3x3_bwd_k(const __nv_bfloat16* __restri
                                                    const __nv_bfloat16* __restrict__ resid_t,
                                                    __nv_bfloat16* __restrict__ dz, float* __restrict__ dwk, int B, int H,
                                                    int W, int C, int mode, int resid, int pix_per_block) {
+  ck::pdl_enter();
   __shared__ float sm[TPB * 8];
   const int c8 = C >> 3, lanes = TPB / c8;
   const int cv = threadIdx.x % c8, lane = threadIdx.x / c8;
@@ -347,6 +355,7 @@ __global__ void __launch_bounds__(TPB) pool_add_fwd_k(const __nv_bfloat16* __res
                                                       const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ out,
                                                       __nv_bfloat16* __restrict__ even, __nv_bfloat16* __restrict__ relu_out,
                                                       uint8_t* __restrict__ arg, int B, int H, int W, int C, const BnFin fin) {
+  ck::pdl_enter();
   const int c8 = C >> 3, Ho = H >> 1, Wo = W >> 1;
   const long total = (long)B * Ho * Wo * c8;
   const long g0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -407,6 +416,7 @@ __global__ void __launch_bounds__(TPB) dec_combine_fwd_k(const __nv_bfloat16* __
                                                          const __nv_bfloat16* __restrict__ rl, __nv_bfloat16* __restrict__ s,
                                                          __nv_bfloat16* __restrict__ a_next, int B, int H, int W, int C,
                                                          int rl_up, const BnFin fin) {
+  ck::pdl_enter();
   const int c8 = C >> 3;
   const long total = (long)B * H * W * c8;
   const long g0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -444,6 +454,7 @@ __global__ void __launch_bounds__(TPB) dec_combine_fwd_k(const __nv_bfloat16* __
 __global__ void __launch_bounds__(TPB) down2sum_k(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict__ mask,
                                                   const __nv_bfloat16* __restrict__ add, __nv_bfloat16* __restrict__ out,
                                                   int B, int Ho, int Wo, int C) {
+  ck::pdl_enter();
   const int c8 = C >> 3;
   const long total = (long)B * Ho * Wo * c8;
   for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long)gridDim.x * blockDim.x) {
@@ -481,6 +492,7 @@ __global__ void __launch_bounds__(TPB) down2sum_k(const __nv_bfloat16* __restric
 __global__ void __launch_bounds__(TPB) relu_bwd_add_k(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ x,
                                                       const __nv_bfloat16* __restrict__ add, __nv_bfloat16* __restrict__ out,
                                                       long nvec) {
+  ck::pdl_enter();
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
     float a[8], m[8], t[8];
     unpack8(ldg16(g + i * 8), a);
@@ -538,6 +550,7 @@ __global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : 3) bn_bwd_reduce_k(const 
                                                        const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
                                                        float* __restrict__ sums, long P, int H, int W, int C,
                                                        int pix_per_block) {
+  ck::pdl_enter();
   __shared__ float sm[TPB * 8];
   const int c8 = C >> 3, lanes = TPB / c8;
   const int cv = threadIdx.x % c8, lane = threadIdx.x / c8;
@@ -576,6 +589,7 @@ __global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : 3) bn_bwd_apply_k(const _
                                                       const float* __restrict__ sums, __nv_bfloat16* __restrict__ dy,
                                                       float* __restrict__ dgamma, float* __restrict__ dbeta, long P, int H,
                                                       int W, int C) {
+  ck::pdl_enter();
   const int c8 = C >> 3;
   const float invn = 1.0f / (float)P;
   if (blockIdx.x == 0) {
@@ -625,6 +639,7 @@ __global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : 3) bn_bwd_apply_k(const _
 // The BN2 reduce + apply kernels then run in their cheap DIRECT mode instead of decoding the arg-max twice.
 __global__ void __launch_bounds__(TPB, 3) pool_bwd_k(const __nv_bfloat16* __restrict__ g, const uint8_t* __restrict__ arg,
                                                      __nv_bfloat16* __restrict__ dz, long P, int H, int W, int C) {
+  ck::pdl_enter();
   const int c8 = C >> 3;
   const long total = P * c8;
   float unused[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -638,6 +653,7 @@ __global__ void __launch_bounds__(TPB, 3) pool_bwd_k(const __nv_bfloat16* __rest
 // column sum of a [P][C] bf16 matrix into fp32 (bias gradient of the residual convs)
 __global__ void __launch_bounds__(TPB) colsum_k(const __nv_bfloat16* __restrict__ g, float* __restrict__ out, long P, int C,
                                                 int pix_per_block) {
+  ck::pdl_enter();
   __shared__ float sm[TPB * 8];
   const int c8 = C >> 3, lanes = TPB / c8;
   const int cv = threadIdx.x % c8, lane = threadIdx.x / c8;
@@ -672,6 +688,7 @@ __global__ void __launch_bounds__(TPB) head_fwd_k(const __nv_bfloat16* __restric
                                                   const float* __restrict__ bias, const uint8_t* __restrict__ mask,
                                                   float* __restrict__ acc, float* __restrict__ prob, int B, int Hl, int Wl,
                                                   int C) {
+  ck::pdl_enter();
   extern __shared__ float sw[];
   for (int i = threadIdx.x; i < C; i += blockDim.x) sw[i] = w[i];
   __syncthreads();
@@ -738,6 +755,7 @@ __global__ void __launch_bounds__(TPB) head_bwd_k(const __nv_bfloat16* __restric
                                                   const float* __restrict__ sums, __nv_bfloat16* __restrict__ ds,
                                                   float* __restrict__ dw, float* __restrict__ db, int B, int Hl, int Wl, int C,
                                                   int use_dice, float dice_smooth, float loss_scale) {
+  ck::pdl_enter();
   extern __shared__ float sh[];  // w[C] | reduction scratch [TPB*8]
   float* sw = sh;
   float* sm = sh + C;
@@ -822,6 +840,7 @@ __device__ __forceinline__ void load_row_window(const __nv_bfloat16* __restrict_
 __global__ void __launch_bounds__(TPB, 2) dw3x3_fwd_v2_k(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
                                                          const float* __restrict__ bn, __nv_bfloat16* __restrict__ out,
                                                          int B, int H, int W, int C, int mode, const BnFin fin) {
+  ck::pdl_enter();
   const int c8 = C >> 3, WS = W / DWS;
   const long total = (long)B * H * WS * c8;
   const long g0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -867,6 +886,7 @@ __global__ void __launch_bounds__(TPB, 2) dw3x3_dgrad_v2_k(const __nv_bfloat16* 
                                                            const __nv_bfloat16* __restrict__ resid_t,
                                                            __nv_bfloat16* __restrict__ dz, int B, int H, int W, int C, int mode,
                                                            int resid) {
+  ck::pdl_enter();
   const int c8 = C >> 3, WS = W / DWS;
   const long total = (long)B * H * WS * c8;
   for (long gi = (long)blockIdx.x * blockDim.x + threadIdx.x; gi < total; gi += (long)gridDim.x * blockDim.x) {
@@ -919,6 +939,7 @@ __global__ void __launch_bounds__(TPB, 2) dw3x3_dgrad_v2_k(const __nv_bfloat16* 
 __global__ void __launch_bounds__(TPB, 1) dw3x3_wgrad_v2_k(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ src,
                                                            const float* __restrict__ bn, float* __restrict__ dwk, int B, int H,
                                                            int W, int C, int mode, int strips_per_block) {
+  ck::pdl_enter();
   __shared__ float sm[TPB * 8];
   const int c8 = C >> 3, WS = W / DWS, lanes = TPB / c8;
   const int cv = threadIdx.x % c8, lane = threadIdx.x / c8;
@@ -964,6 +985,7 @@ __global__ void __launch_bounds__(TPB, 1) dw3x3_wgrad_v2_k(const __nv_bfloat16* 
 __global__ void __launch_bounds__(384, 1) dw3x3_wgrad_v3_k(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ src,
                                                            const float* __restrict__ bn, float* __restrict__ dwk, int B, int H,
                                                            int W, int C, int mode, int strips_per_block) {
+  ck::pdl_enter();
   __shared__ float sm[384 * 8];
   const int c8 = C >> 3, WS = W / DWS, lanes = 128 / c8;
   const int tx = threadIdx.x, r = threadIdx.y;
@@ -1016,6 +1038,7 @@ __global__ void __launch_bounds__(384, 1) dw3x3_wgrad_v3_k(const __nv_bfloat16* 
 __global__ void __launch_bounds__(TPB) entry_conv_wgrad_v2_k(const uint8_t* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                                                              float* __restrict__ dw, int B, int H, int W, int C,
                                                              int pix_per_block) {
+  ck::pdl_enter();
   extern __shared__ float smw[];  // patch[128][28] | dy[128][C]
   float* sp = smw;
   float* sd = smw + 128 * 28;
@@ -1101,7 +1124,7 @@ extern "C" {
 int crackfl_entry_conv_fwd(const void* x_u8, const float* w, const float* bias, void* y, int B, int H, int W, int C,
                            cudaStream_t st) {
   const long total = (long)B * (H / 2) * (W / 2) * (C / 8);
-  entry_conv_fwd_k<<<grid_for(total), TPB, (27 * C + C) * sizeof(float), st>>>(
+  ck::launch(entry_conv_fwd_k, grid_for(total), TPB, (27 * C + C) * sizeof(float), st, 
       (const uint8_t*)x_u8, w, bias, (__nv_bfloat16*)y, B, H, W, C);
   CK_LAUNCH_CHECK();
   return 0;
@@ -1111,7 +1134,7 @@ int crackfl_entry_conv_wgrad(const void* x_u8, const void* dy, float* dw, int B,
   const long P = (long)B * (H / 2) * (W / 2);
   if (C <= 64 && TPB % C == 0) {
     const int ppb2 = 512;
-    entry_conv_wgrad_v2_k<<<(int)((P + ppb2 - 1) / ppb2), TPB, (128 * 28 + 128 * C) * sizeof(float), st>>>(
+    ck::launch(entry_conv_wgrad_v2_k, (int)((P + ppb2 - 1) / ppb2), TPB, (128 * 28 + 128 * C) * sizeof(float), st, 
         (const uint8_t*)x_u8, (const __nv_bfloat16*)dy, dw, B, H, W, C, ppb2);
     CK_LAUNCH_CHECK();
     return 0;
@@ -1119,7 +1142,7 @@ int crackfl_entry_conv_wgrad(const void* x_u8, const void* dy, float* dw, int B,
   const int ppb = 512;
   dim3 blk(C / 8, 27);
   if (blk.x * blk.y > 1024) return (int)cudaErrorInvalidValue;
-  entry_conv_wgrad_k<<<(int)((P + ppb - 1) / ppb), blk, 0, st>>>((const uint8_t*)x_u8, (const __nv_bfloat16*)dy, dw, B, H, W,
+  ck::launch(entry_conv_wgrad_k, (int)((P + ppb - 1) / ppb), blk, 0, st, (const uint8_t*)x_u8, (const __nv_bfloat16*)dy, dw, B, H, W,
                                                                 C, ppb);
   CK_LAUNCH_CHECK();
   return 0;
@@ -1128,21 +1151,21 @@ int crackfl_entry_conv_wgrad(const void* x_u8, const void* dy, float* dw, int B,
 int crackfl_bn_stats(const void* y, float* stats, long P, int C, cudaStream_t st) {
   if (C % 8 || TPB % (C / 8)) return (int)cudaErrorInvalidValue;
   const int ppb = ppb_for(P, C);
-  bn_stats_k<<<(int)((P + ppb - 1) / ppb), TPB, 0, st>>>((const __nv_bfloat16*)y, stats, P, C, ppb);
+  ck::launch(bn_stats_k, (int)((P + ppb - 1) / ppb), TPB, 0, st, (const __nv_bfloat16*)y, stats, P, C, ppb);
   CK_LAUNCH_CHECK();
   return 0;
 }
 
 int crackfl_bn_finalize(const float* stats, const float* gamma, const float* beta, float* run_mean, float* run_var,
                         float* bn, int C, float count, float eps, float momentum, cudaStream_t st) {
-  bn_finalize_k<<<(C + 127) / 128, 128, 0, st>>>(stats, gamma, beta, run_mean, run_var, bn, C, count, eps, momentum);
+  ck::launch(bn_finalize_k, (C + 127) / 128, 128, 0, st, stats, gamma, beta, run_mean, run_var, bn, C, count, eps, momentum);
   CK_LAUNCH_CHECK();
   return 0;
 }
 
 int crackfl_bn_eval_prepare(const float* gamma, const float* beta, const float* run_mean, const float* run_var, float* bn,
                             int C, float eps, cudaStream_t st) {
-  bn_eval_prepare_k<<<(C + 127) / 128, 128, 0, st>>>(gamma, beta, run_mean, run_var, bn, C, eps);
+  ck::launch(bn_eval_prepare_k, (C + 127) / 128, 128, 0, st, gamma, beta, run_mean, run_var, bn, C, eps);
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -1150,7 +1173,7 @@ int crackfl_bn_eval_prepare(const float* gamma, const float* beta, const float* 
 int crackfl_bn_act(const void* y, const float* bn, void* out, void* even, int B, int H, int W, int C, int relu,
                    cudaStream_t st) {
   const long total = (long)B * H * W * (C / 8);
-  bn_act_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, bn, (__nv_bfloat16*)out, (__nv_bfloat16*)even, B, H, W,
+  ck::launch(bn_act_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)y, bn, (__nv_bfloat16*)out, (__nv_bfloat16*)even, B, H, W,
                                             C, relu, BnFin{});
   CK_LAUNCH_CHECK();
   return 0;
@@ -1160,12 +1183,12 @@ int crackfl_dw3x3_fwd(const void* x, const float* w, const float* bn, void* out,
                       cudaStream_t st) {
   const long total = (long)B * H * W * (C / 8);
   if (W % DWS == 0) {
-    dw3x3_fwd_v2_k<<<grid_for(total / DWS, 148 * 8), TPB, 0, st>>>((const __nv_bfloat16*)x, w, bn, (__nv_bfloat16*)out, B, H, W,
+    ck::launch(dw3x3_fwd_v2_k, grid_for(total / DWS, 148 * 8), TPB, 0, st, (const __nv_bfloat16*)x, w, bn, (__nv_bfloat16*)out, B, H, W,
                                                                   C, mode, BnFin{});
     CK_LAUNCH_CHECK();
     return 0;
   }
-  dw3x3_fwd_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)x, w, bn, (__nv_bfloat16*)out, B, H, W, C, mode);
+  ck::launch(dw3x3_fwd_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)x, w, bn, (__nv_bfloat16*)out, B, H, W, C, mode);
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -1176,7 +1199,7 @@ int crackfl_dw3x3_bwd(const void* g, const void* src, const float* w, const floa
   const long P = (long)B * H * W;
   if (W % DWS == 0) {
     const long strips = P / DWS;
-    dw3x3_dgrad_v2_k<<<grid_for(strips * (C / 8), 148 * 8), TPB, 0, st>>>(
+    ck::launch(dw3x3_dgrad_v2_k, grid_for(strips * (C / 8), 148 * 8), TPB, 0, st, 
         (const __nv_bfloat16*)g, (const __nv_bfloat16*)src, w, bn, (const __nv_bfloat16*)resid_t, (__nv_bfloat16*)dz, B, H, W, C,
         mode, resid);
     CK_LAUNCH_CHECK();
@@ -1184,13 +1207,13 @@ int crackfl_dw3x3_bwd(const void* g, const void* src, const float* w, const floa
     long spb = (strips + 148 * 4 - 1) / (148 * 4);
     spb = ((spb + lanes - 1) / lanes) * lanes;
     if (spb < lanes) spb = lanes;
-    dw3x3_wgrad_v2_k<<<(int)((strips + spb - 1) / spb), TPB, 0, st>>>((const __nv_bfloat16*)g, (const __nv_bfloat16*)src, bn,
+    ck::launch(dw3x3_wgrad_v2_k, (int)((strips + spb - 1) / spb), TPB, 0, st, (const __nv_bfloat16*)g, (const __nv_bfloat16*)src, bn,
                                                                       dwk, B, H, W, C, mode, (int)spb);
     CK_LAUNCH_CHECK();
     return 0;
   }
   const int ppb = ppb_for(P, C);
-  dw3x3_bwd_k<<<(int)((P + ppb - 1) / ppb), TPB, 0, st>>>((const __nv_bfloat16*)g, (const __nv_bfloat16*)src, w, bn,
+  ck::launch(dw3x3_bwd_k, (int)((P + ppb - 1) / ppb), TPB, 0, st, (const __nv_bfloat16*)g, (const __nv_bfloat16*)src, w, bn,
                                                           (const __nv_bfloat16*)resid_t, (__nv_bfloat16*)dz, dwk, B, H, W,
                                                           C, mode, resid, ppb);
   CK_LAUNCH_CHECK();
@@ -1200,7 +1223,7 @@ int crackfl_dw3x3_bwd(const void* g, const void* src, const float* w, const floa
 int crackfl_pool_add_fwd(const void* y, const float* bn, const void* res, void* out, void* even, void* relu_out, void* arg,
                          int B, int H, int W, int C, cudaStream_t st) {
   const long total = (long)B * (H / 2) * (W / 2) * (C / 8);
-  pool_add_fwd_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, bn, (const __nv_bfloat16*)res,
+  ck::launch(pool_add_fwd_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)y, bn, (const __nv_bfloat16*)res,
                                                   (__nv_bfloat16*)out, (__nv_bfloat16*)even, (__nv_bfloat16*)relu_out,
                                                   (uint8_t*)arg, B, H, W, C, BnFin{});
   CK_LAUNCH_CHECK();
@@ -1210,7 +1233,7 @@ int crackfl_pool_add_fwd(const void* y, const float* bn, const void* res, void* 
 int crackfl_dec_combine_fwd(const void* y, const float* bn, const void* rl, void* s, void* a_next, int B, int H, int W,
                             int C, int rl_up, cudaStream_t st) {
   const long total = (long)B * H * W * (C / 8);
-  dec_combine_fwd_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, bn, (const __nv_bfloat16*)rl,
+  ck::launch(dec_combine_fwd_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)y, bn, (const __nv_bfloat16*)rl,
                                                      (__nv_bfloat16*)s, (__nv_bfloat16*)a_next, B, H, W, C, rl_up, BnFin{});
   CK_LAUNCH_CHECK();
   return 0;
@@ -1219,7 +1242,7 @@ int crackfl_dec_combine_fwd(const void* y, const float* bn, const void* rl, void
 int crackfl_down2sum(const void* in, const void* mask, const void* add, void* out, int B, int Ho, int Wo, int C,
                      cudaStream_t st) {
   const long total = (long)B * Ho * Wo * (C / 8);
-  down2sum_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)in, (const __nv_bfloat16*)mask,
+  ck::launch(down2sum_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)in, (const __nv_bfloat16*)mask,
                                               (const __nv_bfloat16*)add, (__nv_bfloat16*)out, B, Ho, Wo, C);
   CK_LAUNCH_CHECK();
   return 0;
@@ -1227,7 +1250,7 @@ int crackfl_down2sum(const void* in, const void* mask, const void* add, void* ou
 
 int crackfl_relu_bwd_add(const void* g, const void* x, const void* add, void* out, long numel, cudaStream_t st) {
   const long nvec = numel / 8;
-  relu_bwd_add_k<<<grid_for(nvec), TPB, 0, st>>>((const __nv_bfloat16*)g, (const __nv_bfloat16*)x,
+  ck::launch(relu_bwd_add_k, grid_for(nvec), TPB, 0, st, (const __nv_bfloat16*)g, (const __nv_bfloat16*)x,
                                                  (const __nv_bfloat16*)add, (__nv_bfloat16*)out, nvec);
   CK_LAUNCH_CHECK();
   return 0;
@@ -1242,9 +1265,9 @@ int crackfl_bn_bwd_reduce(const void* g, const void* arg, const void* y, const f
   const __nv_bfloat16* gp = (const __nv_bfloat16*)g;
   const __nv_bfloat16* yp = (const __nv_bfloat16*)y;
   const uint8_t* ap = (const uint8_t*)arg;
-  if (mode == 0) bn_bwd_reduce_k<0><<<grid, TPB, 0, st>>>(gp, ap, yp, bn, sums, P, H, W, C, ppb);
-  else if (mode == 1) bn_bwd_reduce_k<1><<<grid, TPB, 0, st>>>(gp, ap, yp, bn, sums, P, H, W, C, ppb);
-  else bn_bwd_reduce_k<2><<<grid, TPB, 0, st>>>(gp, ap, yp, bn, sums, P, H, W, C, ppb);
+  if (mode == 0) ck::launch(bn_bwd_reduce_k<0>, grid, TPB, 0, st, gp, ap, yp, bn, sums, P, H, W, C, ppb);
+  else if (mode == 1) ck::launch(bn_bwd_reduce_k<1>, grid, TPB, 0, st, gp, ap, yp, bn, sums, P, H, W, C, ppb);
+  else ck::launch(bn_bwd_reduce_k<2>, grid, TPB, 0, st, gp, ap, yp, bn, sums, P, H, W, C, ppb);
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -1257,9 +1280,9 @@ int crackfl_bn_bwd_apply(const void* g, const void* arg, const void* y, const fl
   const __nv_bfloat16* yp = (const __nv_bfloat16*)y;
   const uint8_t* ap = (const uint8_t*)arg;
   __nv_bfloat16* dp = (__nv_bfloat16*)dy;
-  if (mode == 0) bn_bwd_apply_k<0><<<grid, TPB, 0, st>>>(gp, ap, yp, bn, sums, dp, dgamma, dbeta, P, H, W, C);
-  else if (mode == 1) bn_bwd_apply_k<1><<<grid, TPB, 0, st>>>(gp, ap, yp, bn, sums, dp, dgamma, dbeta, P, H, W, C);
-  else bn_bwd_apply_k<2><<<grid, TPB, 0, st>>>(gp, ap, yp, bn, sums, dp, dgamma, dbeta, P, H, W, C);
+  if (mode == 0) ck::launch(bn_bwd_apply_k<0>, grid, TPB, 0, st, gp, ap, yp, bn, sums, dp, dgamma, dbeta, P, H, W, C);
+  else if (mode == 1) ck::launch(bn_bwd_apply_k<1>, grid, TPB, 0, st, gp, ap, yp, bn, sums, dp, dgamma, dbeta, P, H, W, C);
+  else ck::launch(bn_bwd_apply_k<2>, grid, TPB, 0, st, gp, ap, yp, bn, sums, dp, dgamma, dbeta, P, H, W, C);
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -1267,7 +1290,7 @@ int crackfl_bn_bwd_apply(const void* g, const void* arg, const void* y, const fl
 int crackfl_colsum(const void* g, float* out, long P, int C, cudaStream_t st) {
   if (C % 8 || TPB % (C / 8)) return (int)cudaErrorInvalidValue;
   const int ppb = ppb_for(P, C);
-  colsum_k<<<(int)((P + ppb - 1) / ppb), TPB, 0, st>>>((const __nv_bfloat16*)g, out, P, C, ppb);
+  ck::launch(colsum_k, (int)((P + ppb - 1) / ppb), TPB, 0, st, (const __nv_bfloat16*)g, out, P, C, ppb);
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -1275,7 +1298,7 @@ int crackfl_colsum(const void* g, float* out, long P, int C, cudaStream_t st) {
 int crackfl_head_fwd(const void* s, const float* w, const float* bias, const void* mask_u8, float* acc, float* prob, int B,
                      int Hl, int Wl, int C, cudaStream_t st) {
   const long P = (long)B * Hl * Wl;
-  head_fwd_k<<<grid_for(P * (C / 8), 148 * 8), TPB, C * sizeof(float), st>>>((const __nv_bfloat16*)s, w, bias,
+  ck::launch(head_fwd_k, grid_for(P * (C / 8), 148 * 8), TPB, C * sizeof(float), st, (const __nv_bfloat16*)s, w, bias,
                                                                    (const uint8_t*)mask_u8, acc, prob, B, Hl, Wl, C);
   CK_LAUNCH_CHECK();
   return 0;
@@ -1285,7 +1308,7 @@ int crackfl_head_bwd(const void* s, const float* w, const float* bias, const voi
                      float* dw, float* db, int B, int Hl, int Wl, int C, int use_dice, float dice_smooth, float loss_scale,
                      cudaStream_t st) {
   const long P = (long)B * Hl * Wl;
-  head_bwd_k<<<grid_for(P * (C / 8), 148 * 8), TPB, (C + TPB * 8) * sizeof(float), st>>>(
+  ck::launch(head_bwd_k, grid_for(P * (C / 8), 148 * 8), TPB, (C + TPB * 8) * sizeof(float), st, 
       (const __nv_bfloat16*)s, w, bias, (const uint8_t*)mask_u8, sums, (__nv_bfloat16*)ds, dw, db, B, Hl, Wl, C, use_dice,
       dice_smooth, loss_scale);
   CK_LAUNCH_CHECK();
@@ -1301,7 +1324,7 @@ int crackfl_dw3x3_dgrad(const void* g, const void* src, const float* w, const fl
                         int H, int W, int C, int mode, int resid, cudaStream_t st) {
   if (W % DWS) return (int)cudaErrorInvalidValue;
   const long strips = (long)B * H * W / DWS;
-  dw3x3_dgrad_v2_k<<<grid_for(strips * (C / 8), 148 * 8), TPB, 0, st>>>(
+  ck::launch(dw3x3_dgrad_v2_k, grid_for(strips * (C / 8), 148 * 8), TPB, 0, st, 
       (const __nv_bfloat16*)g, (const __nv_bfloat16*)src, w, bn, (const __nv_bfloat16*)resid_t, (__nv_bfloat16*)dz, B, H, W, C, mode,
       resid);
   CK_LAUNCH_CHECK();
@@ -1316,7 +1339,7 @@ int crackfl_dw3x3_wgrad(const void* g, const void* src, const float* bn, float* 
   long spb = (strips + 148 * 2 - 1) / (148 * 2);
   spb = ((spb + lanes - 1) / lanes) * lanes;
   if (spb < lanes) spb = lanes;
-  dw3x3_wgrad_v3_k<<<(int)((strips + spb - 1) / spb), dim3(128, 3), 0, st>>>((const __nv_bfloat16*)g, (const __nv_bfloat16*)src,
+  ck::launch(dw3x3_wgrad_v3_k, (int)((strips + spb - 1) / spb), dim3(128, 3), 0, st, (const __nv_bfloat16*)g, (const __nv_bfloat16*)src,
                                                                              bn, dwk, B, H, W, C, mode, (int)spb);
   CK_LAUNCH_CHECK();
   return 0;
@@ -1329,7 +1352,7 @@ extern "C" {
 int crackfl_bn_act_fin(const void* y, const crackfl_bn_fin* fin, void* out, void* even, int B, int H, int W, int C, int relu,
                        cudaStream_t st) {
   const long total = (long)B * H * W * (C / 8);
-  bn_act_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, nullptr, (__nv_bfloat16*)out, (__nv_bfloat16*)even, B, H, W,
+  ck::launch(bn_act_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)y, nullptr, (__nv_bfloat16*)out, (__nv_bfloat16*)even, B, H, W,
                                             C, relu, *fin);
   CK_LAUNCH_CHECK();
   return 0;
@@ -1339,7 +1362,7 @@ int crackfl_dw3x3_fwd_fin(const void* x, const float* w, const crackfl_bn_fin* f
                           cudaStream_t st) {
   if (W % DWS) return (int)cudaErrorInvalidValue;
   const long total = (long)B * H * W * (C / 8);
-  dw3x3_fwd_v2_k<<<grid_for(total / DWS, 148 * 8), TPB, 0, st>>>((const __nv_bfloat16*)x, w, nullptr, (__nv_bfloat16*)out, B, H,
+  ck::launch(dw3x3_fwd_v2_k, grid_for(total / DWS, 148 * 8), TPB, 0, st, (const __nv_bfloat16*)x, w, nullptr, (__nv_bfloat16*)out, B, H,
                                                                 W, C, 1, *fin);
   CK_LAUNCH_CHECK();
   return 0;
@@ -1348,7 +1371,7 @@ int crackfl_dw3x3_fwd_fin(const void* x, const float* w, const crackfl_bn_fin* f
 int crackfl_pool_add_fwd_fin(const void* y, const crackfl_bn_fin* fin, const void* res, void* out, void* even, void* relu_out,
                              void* arg, int B, int H, int W, int C, cudaStream_t st) {
   const long total = (long)B * (H / 2) * (W / 2) * (C / 8);
-  pool_add_fwd_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, nullptr, (const __nv_bfloat16*)res,
+  ck::launch(pool_add_fwd_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)y, nullptr, (const __nv_bfloat16*)res,
                                                   (__nv_bfloat16*)out, (__nv_bfloat16*)even, (__nv_bfloat16*)relu_out,
                                                   (uint8_t*)arg, B, H, W, C, *fin);
   CK_LAUNCH_CHECK();
@@ -1358,7 +1381,7 @@ int crackfl_pool_add_fwd_fin(const void* y, const crackfl_bn_fin* fin, const voi
 int crackfl_dec_combine_fwd_fin(const void* y, const crackfl_bn_fin* fin, const void* rl, void* s, void* a_next, int B, int H,
                                 int W, int C, int rl_up, cudaStream_t st) {
   const long total = (long)B * H * W * (C / 8);
-  dec_combine_fwd_k<<<grid_for(total), TPB, 0, st>>>((const __nv_bfloat16*)y, nullptr, (const __nv_bfloat16*)rl,
+  ck::launch(dec_combine_fwd_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)y, nullptr, (const __nv_bfloat16*)rl,
                                                      (__nv_bfloat16*)s, (__nv_bfloat16*)a_next, B, H, W, C, rl_up, *fin);
   CK_LAUNCH_CHECK();
   return 0;
@@ -1370,7 +1393,7 @@ extern "C" {
 
 int crackfl_pool_bwd(const void* g, const void* arg, void* dz, int B, int H, int W, int C, cudaStream_t st) {
   const long P = (long)B * H * W;
-  pool_bwd_k<<<grid_for(P * (C / 8)), TPB, 0, st>>>((const __nv_bfloat16*)g, (const uint8_t*)arg, (__nv_bfloat16*)dz, P, H, W, C);
+  ck::launch(pool_bwd_k, grid_for(P * (C / 8)), TPB, 0, st, (const __nv_bfloat16*)g, (const uint8_t*)arg, (__nv_bfloat16*)dz, P, H, W, C);
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -1448,11 +1471,11 @@ int crackfl_bn_train_fwd_noalloc(const void* y, const float* gamma, const float*
   if (e != cudaSuccess) return (int)e;
   const long P = (long)B * H * W;
   const int ppb = ppb_for(P, C);
-  bn_stats_k<<<(int)((P + ppb - 1) / ppb), TPB, 0, st>>>((const __nv_bfloat16*)y, stats, P, C, ppb);
+  ck::launch(bn_stats_k, (int)((P + ppb - 1) / ppb), TPB, 0, st, (const __nv_bfloat16*)y, stats, P, C, ppb);
   CK_LAUNCH_CHECK();
-  bn_finalize_k<<<(C + 127) / 128, 128, 0, st>>>(stats, gamma, beta, run_mean, run_var, bn, C, (float)P, eps, momentum);
+  ck::launch(bn_finalize_k, (C + 127) / 128, 128, 0, st, stats, gamma, beta, run_mean, run_var, bn, C, (float)P, eps, momentum);
   CK_LAUNCH_CHECK();
-  bn_act_k<<<grid_for(P * (C / 8)), TPB, 0, st>>>((const __nv_bfloat16*)y, bn, (__nv_bfloat16*)out, nullptr, B, H, W, C,
+  ck::launch(bn_act_k, grid_for(P * (C / 8)), TPB, 0, st, (const __nv_bfloat16*)y, bn, (__nv_bfloat16*)out, nullptr, B, H, W, C,
                                                  relu, BnFin{});
   CK_LAUNCH_CHECK();
   return 0;

@@ -8,11 +8,13 @@
 
 namespace {
 
-__global__ void adam_tick_k(int* __restrict__ step) { *step += 1; }
+__global__ void adam_tick_k(int* __restrict__ step) {
+  ck::pdl_enter(); *step += 1; }
 
 __global__ void __launch_bounds__(256) adam_k(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
                                               float* __restrict__ v, const int* __restrict__ step, long n4, float lr,
                                               float b1, float b2, float eps) {
+  ck::pdl_enter();
   __shared__ float s_lrt;
   if (threadIdx.x == 0) {
     const float t = (float)(*step);
@@ -43,6 +45,7 @@ __global__ void __launch_bounds__(256) adam_k(float* __restrict__ p, float* __re
 // 32x32 tile goes through shared memory so that both the fp32 reads and the bf16 writes are coalesced.
 __global__ void __launch_bounds__(256) weight_prep_k(const float* __restrict__ arena, __nv_bfloat16* __restrict__ ops,
                                                      const crackfl_prep_desc* __restrict__ descs) {
+  ck::pdl_enter();
   __shared__ float tile[32][33];
   const crackfl_prep_desc d = descs[blockIdx.y];
   const int tn = (d.N + 31) / 32, tk = (d.K + 31) / 32;
@@ -75,6 +78,7 @@ __global__ void __launch_bounds__(256) weight_prep_k(const float* __restrict__ a
 }
 
 __global__ void __launch_bounds__(256) f32_to_bf16_k(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long n) {
+  ck::pdl_enter();
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
     out[i] = __float2bfloat16_rn(in[i]);
 }
@@ -82,11 +86,13 @@ __global__ void __launch_bounds__(256) f32_to_bf16_k(const float* __restrict__ i
 // K16 staging: client update (fp32, just copied H2D or just trained) -> bf16 delta against the global model
 __global__ void __launch_bounds__(256) publish_delta_k(const float* __restrict__ local, const float* __restrict__ global,
                                                        __nv_bfloat16* __restrict__ out, long n) {
+  ck::pdl_enter();
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
     out[i] = __float2bfloat16_rn(local[i] - global[i]);
 }
 
 __global__ void accum_k(float* __restrict__ total, const float* __restrict__ step, int n) {
+  ck::pdl_enter();
   if (threadIdx.x < n) total[threadIdx.x] += step[threadIdx.x];
 }
 
@@ -96,7 +102,7 @@ extern "C" {
 
 int crackfl_accum_small(float* total, const float* step, int n, cudaStream_t st) {
   if (n > 32) return (int)cudaErrorInvalidValue;
-  accum_k<<<1, 32, 0, st>>>(total, step, n);
+  ck::launch(accum_k, 1, 32, 0, st, total, step, n);
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -104,7 +110,7 @@ int crackfl_accum_small(float* total, const float* step, int n, cudaStream_t st)
 int crackfl_publish_delta(const float* local, const float* global, void* out_bf16, long n, cudaStream_t st) {
   long blocks = (n + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  publish_delta_k<<<(int)blocks, 256, 0, st>>>(local, global, (__nv_bfloat16*)out_bf16, n);
+  ck::launch(publish_delta_k, (int)blocks, 256, 0, st, local, global, (__nv_bfloat16*)out_bf16, n);
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -112,18 +118,18 @@ int crackfl_publish_delta(const float* local, const float* global, void* out_bf1
 int crackfl_adam_step(float* p, float* g, float* m, float* v, int* step, long n, float lr, float b1, float b2, float eps,
                       cudaStream_t st) {
   if (n % 4) return (int)cudaErrorInvalidValue;
-  adam_tick_k<<<1, 1, 0, st>>>(step);
+  ck::launch(adam_tick_k, 1, 1, 0, st, step);
   const long n4 = n / 4;
   long blocks = (n4 + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  adam_k<<<(int)blocks, 256, 0, st>>>(p, g, m, v, step, n4, lr, b1, b2, eps);
+  ck::launch(adam_k, (int)blocks, 256, 0, st, p, g, m, v, step, n4, lr, b1, b2, eps);
   CK_LAUNCH_CHECK();
   return 0;
 }
 
 int crackfl_weight_prep(const float* arena, void* ops, const crackfl_prep_desc* descs_dev, int num_desc, cudaStream_t st) {
   dim3 grid(48, num_desc);
-  weight_prep_k<<<grid, 256, 0, st>>>(arena, (__nv_bfloat16*)ops, descs_dev);
+  ck::launch(weight_prep_k, grid, 256, 0, st, arena, (__nv_bfloat16*)ops, descs_dev);
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -131,7 +137,7 @@ int crackfl_weight_prep(const float* arena, void* ops, const crackfl_prep_desc* 
 int crackfl_f32_to_bf16(const float* in, void* out, long n, cudaStream_t st) {
   long blocks = (n + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  f32_to_bf16_k<<<(int)blocks, 256, 0, st>>>(in, (__nv_bfloat16*)out, n);
+  ck::launch(f32_to_bf16_k, (int)blocks, 256, 0, st, in, (__nv_bfloat16*)out, n);
   CK_LAUNCH_CHECK();
   return 0;
 }
