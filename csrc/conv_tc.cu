@@ -842,25 +842,58 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
 }
 
 // Sum the per-CTA partial tiles of wgrad_tc_k over the pixel splits and add the result into the Keras-layout
-// gradient arena (one writer per element, no atomics).
+// gradient arena (one writer per element, no atomics).  A block is (256 / zl) float4 columns x zl split lanes: every
+// lane strides over the splits with four loads in flight, the lanes meet in shared memory, lane 0 writes.  (The first
+// version walked all splits serially per thread: 16-64 blocks x up to 293 dependent-latency loads, 13-29 us a launch.)
 __global__ void __launch_bounds__(256) wgrad_reduce_k(const float* __restrict__ ws, float* __restrict__ dW, int groups, int ntn,
                                                       int splits, int BN, int cw, int mblk, int total_blocks, int cchunks,
-                                                      long s_tap, long s_ci, long s_co) {
+                                                      long s_tap, long s_ci, long s_co, int zl) {
   ck::pdl_enter();
+  __shared__ float4 sm[256];
   const long per_tile = 128L * BN;
-  const long total = (long)groups * ntn * per_tile;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const int c = (int)(i % BN);
-    const int r = (int)((i / BN) % 128);
-    const long gt = i / per_tile;  // g * ntn + nt
+  const long total4 = (long)groups * ntn * per_tile / 4;
+  const int vpb = 256 / zl;
+  const int v = threadIdx.x % vpb, lane = threadIdx.x / vpb;
+  for (long base = (long)blockIdx.x * vpb; base < total4; base += (long)gridDim.x * vpb) {
+    const long i = (base + v) * 4;
+    const bool live = base + v < total4;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const long gt = live ? i / per_tile : 0;  // g * ntn + nt
+    const long in_tile = i - gt * per_tile;
+    if (live) {
+      const float4* p = reinterpret_cast<const float4*>(ws + (gt * splits) * per_tile + in_tile);
+      const long stride4 = per_tile / 4;
+      int z = lane;
+      for (; z + 3 * zl < splits; z += 4 * zl) {
+        const float4 a0 = __ldg(p + (long)z * stride4), a1 = __ldg(p + (long)(z + zl) * stride4);
+        const float4 a2 = __ldg(p + (long)(z + 2 * zl) * stride4), a3 = __ldg(p + (long)(z + 3 * zl) * stride4);
+        acc.x += (a0.x + a1.x) + (a2.x + a3.x); acc.y += (a0.y + a1.y) + (a2.y + a3.y);
+        acc.z += (a0.z + a1.z) + (a2.z + a3.z); acc.w += (a0.w + a1.w) + (a2.w + a3.w);
+      }
+      for (; z < splits; z += zl) {
+        const float4 a0 = __ldg(p + (long)z * stride4);
+        acc.x += a0.x; acc.y += a0.y; acc.z += a0.z; acc.w += a0.w;
+      }
+    }
+    if (zl > 1) {
+      __syncthreads();
+      sm[threadIdx.x] = acc;
+      __syncthreads();
+      if (lane == 0)
+        for (int l = 1; l < zl; ++l) {
+          const float4 o = sm[l * vpb + v];
+          acc.x += o.x; acc.y += o.y; acc.z += o.z; acc.w += o.w;
+        }
+    }
+    if (!live || lane != 0) continue;
+    const int c = (int)(in_tile % BN);
+    const int r = (int)(in_tile / BN);
     const int nt = (int)(gt % ntn), g = (int)(gt / ntn);
     const int blk = g * mblk + r / cw;
     if (blk >= total_blocks) continue;
-    const float* p = ws + (gt * splits) * per_tile + (long)r * BN + c;
-    float acc = 0.f;
-    for (int z = 0; z < splits; ++z) acc += p[z * per_tile];
     const int t = blk / cchunks, ci = (blk % cchunks) * cw + (r % cw);
-    dW[(long)t * s_tap + (long)ci * s_ci + (long)(nt * BN + c) * s_co] += acc;
+    float* d = dW + (long)t * s_tap + (long)ci * s_ci + (long)(nt * BN + c) * s_co;
+    d[0] += acc.x; d[s_co] += acc.y; d[2 * s_co] += acc.z; d[3 * s_co] += acc.w;
   }
 }
 
@@ -1199,11 +1232,13 @@ int crackfl_wgrad_tc_ws(const void* X, const void* dY, float* dW, int B, int H, 
   ck::launch(wgrad_tc_k, grid, 192, smem, st, tmX, tmDY, a);
   CK_LAUNCH_CHECK();
   if (a.ws) {
-    const long total = (long)groups * ntn * 128L * a.BN;
-    long blocks = (total + 255) / 256;
+    const long total4 = (long)groups * ntn * 128L * a.BN / 4;
+    int zl = 1;
+    while (zl * 2 <= splits && zl < 32 && total4 * (zl * 2) / 256 <= 148 * 8) zl *= 2;  // split lanes per block
+    long blocks = (total4 * zl + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
     ck::launch(wgrad_reduce_k, (int)blocks, 256, 0, st, a.ws, dW, groups, ntn, splits, a.BN, a.cw, a.mblk, a.total_blocks, Cin / a.cw,
-                                               s_tap, s_ci, s_co);
+               s_tap, s_ci, s_co, zl);
     CK_LAUNCH_CHECK();
   }
   return 0;
