@@ -116,13 +116,21 @@ class UNetEngine:
         self.ops: Dict[str, Tuple[int, int, int, int]] = {}  # name -> (elem offset, N, T, K)
         off = 0
 
-        def add(name, src_off, N, T, K, s_n, s_t, s_k):
+        def add(name, src_off, N, T, K, s_n, s_t, s_k, kpad=0):
             nonlocal off
-            d = L.PrepDesc(src_off=src_off, dst_off=off, N=N, T=T, K=K, pad_=0, s_n=s_n, s_t=s_t, s_k=s_k)
+            d = L.PrepDesc(src_off=src_off, dst_off=off, N=N, T=T, K=K, pad_=kpad, s_n=s_n, s_t=s_t, s_k=s_k)
             descs.append(d)
-            self.ops[name] = (off, N, T, K)
-            off += (N * T * K + 63) // 64 * 64
+            Kd = kpad or K
+            self.ops[name] = (off, N, T, Kd)
+            off += (N * T * Kd + 63) // 64 * 64
 
+        # entry conv as a K=32 GEMM over the im2col matrix (27 real rows of the (3,3,3,c0) kernel, 5 zero columns)
+        self.entry_tc = (self.conv_impl == "tc" and self.spec.entry % 32 == 0
+                         and os.environ.get("CRACKFL_ENTRY_TC", "1") != "0")
+        if self.entry_tc:
+            c0 = self.spec.entry
+            k0 = self.spec.tensors[self.spec.layers[0].tensors[0]]
+            add("conv0.f", k0.offset, c0, 1, 27, 1, 0, c0, kpad=32)
         for l in self.spec.layers:
             ts = self.spec.tensors
             if l.op == "sepconv":
@@ -158,6 +166,8 @@ class UNetEngine:
         n = self._new
         n("y0", (B, r, rw, c)); n("x0", (B, r, rw, c)); n("x0e", (B, r // 2, rw // 2, c))
         n("dz0", (B, r, rw, c)); n("dy0", (B, r, rw, c))
+        if self.entry_tc:
+            n("x0col", (B, r, rw, 32))  # im2col of the uint8 image: operand of the entry conv and of its weight gradient
         cin = c
         self.enc = []
         for k, f in enumerate(s.down):
@@ -299,9 +309,15 @@ class UNetEngine:
                                                self.num_desc)))
         # entry
         r, rw, c0 = self.H // 2, self.W // 2, self.spec.entry
-        prog.append((lib.crackfl_entry_conv_fwd, (b("x_u8"), self.P(conv0.tensors[0]), self.P(conv0.tensors[1]), b("y0"),
-                                                  B, self.H, self.W, c0)))
-        bn(bn0, b("y0"), B * r * rw, consumer_finalizes=fuse)
+        if self.entry_tc:
+            prog.append((lib.crackfl_entry_im2col, (b("x_u8"), b("x0col"), B, self.H, self.W)))
+            sd = self._gemm(prog, b("x0col"), "conv0.f", self.P(conv0.tensors[1]), 0, b("y0"), B, r, rw,
+                            self._zptr(bn0.name, "stats") if training else 0)
+        else:
+            prog.append((lib.crackfl_entry_conv_fwd, (b("x_u8"), self.P(conv0.tensors[0]), self.P(conv0.tensors[1]), b("y0"),
+                                                      B, self.H, self.W, c0)))
+            sd = False
+        bn(bn0, b("y0"), B * r * rw, sd, consumer_finalizes=fuse)
         if fuse:
             prog.append((lib.crackfl_bn_act_fin, (b("y0"), self._fin(bn0, B * r * rw), b("x0"), b("x0e"), B, r, rw, c0, 1)))
         else:
@@ -475,8 +491,13 @@ class UNetEngine:
                                                  B, r, rw, c0, 0)))
         prog.append((lib.crackfl_bn_bwd_apply, (b("dz0"), 0, b("y0"), self._bnptr(bn0.name), self._zptr(bn0.name, "sums"),
                                                 b("dy0"), self.G(bn0.tensors[0]), self.G(bn0.tensors[1]), B, r, rw, c0, 0)))
-        prog.append((lib.crackfl_entry_conv_wgrad, (b("x_u8"), b("dy0"), self.G(conv0.tensors[0]), B, self.H, self.W, c0),
-                     "side"))
+        if self.entry_tc:
+            ws = self._bufs["wgrad_ws"]
+            prog.append((lib.crackfl_wgrad_tc_ws_cv, (b("x0col"), b("dy0"), self.G(conv0.tensors[0]), B, r, rw, 32, c0, 1,
+                                                      0, c0, 1, ws.data_ptr(), ws.numel(), 27), "side"))
+        else:
+            prog.append((lib.crackfl_entry_conv_wgrad, (b("x_u8"), b("dy0"), self.G(conv0.tensors[0]), B, self.H, self.W, c0),
+                         "side"))
         prog.append((None, None, "join"))
         # ---- optimiser (also zeroes the gradient arena)
         prog.append((lib.crackfl_adam_step, (self.arena.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(),

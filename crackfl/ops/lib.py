@@ -41,6 +41,7 @@ class FedAggParams(C.Structure):
 _SIGS = {
     "crackfl_entry_conv_fwd": [vp, vp, vp, vp, i32, i32, i32, i32, vp],
     "crackfl_entry_conv_wgrad": [vp, vp, vp, i32, i32, i32, i32, vp],
+    "crackfl_entry_im2col": [vp, vp, i32, i32, i32, vp],
     "crackfl_bn_stats": [vp, vp, i64, i32, vp],
     "crackfl_bn_finalize": [vp, vp, vp, vp, vp, vp, i32, f32, f32, f32, vp],
     "crackfl_bn_eval_prepare": [vp, vp, vp, vp, vp, i32, f32, vp],
@@ -72,6 +73,7 @@ _SIGS = {
     "crackfl_conv_tc_fwd": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
     "crackfl_wgrad_tc": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, vp],
     "crackfl_wgrad_tc_ws": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, vp, i64, vp],
+    "crackfl_wgrad_tc_ws_cv": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, vp, i64, i32, vp],
     "crackfl_tc_selftest_supported": [],
     "crackfl_weight_prep": [vp, vp, vp, i32, vp],
     "crackfl_adam_step": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, vp],

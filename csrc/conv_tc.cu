@@ -847,7 +847,7 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
 // version walked all splits serially per thread: 16-64 blocks x up to 293 dependent-latency loads, 13-29 us a launch.)
 __global__ void __launch_bounds__(256) wgrad_reduce_k(const float* __restrict__ ws, float* __restrict__ dW, int groups, int ntn,
                                                       int splits, int BN, int cw, int mblk, int total_blocks, int cchunks,
-                                                      long s_tap, long s_ci, long s_co, int zl) {
+                                                      long s_tap, long s_ci, long s_co, int zl, int cin_valid) {
   ck::pdl_enter();
   __shared__ float4 sm[256];
   const long per_tile = 128L * BN;
@@ -892,6 +892,7 @@ __global__ void __launch_bounds__(256) wgrad_reduce_k(const float* __restrict__ 
     const int blk = g * mblk + r / cw;
     if (blk >= total_blocks) continue;
     const int t = blk / cchunks, ci = (blk % cchunks) * cw + (r % cw);
+    if (ci >= cin_valid) continue;  // zero-padded input channels (entry conv: 27 of 32)
     float* d = dW + (long)t * s_tap + (long)ci * s_ci + (long)(nt * BN + c) * s_co;
     d[0] += acc.x; d[s_co] += acc.y; d[2 * s_co] += acc.z; d[3 * s_co] += acc.w;
   }
@@ -1171,8 +1172,11 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
   return 0;
 }
 
-int crackfl_wgrad_tc_ws(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps,
-                        long s_tap, long s_ci, long s_co, float* workspace, long workspace_floats, cudaStream_t st) {
+// cin_valid < Cin: the last Cin - cin_valid input channels are zero padding; their gradient rows are not written
+// (workspace path only)
+int crackfl_wgrad_tc_ws_cv(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps,
+                           long s_tap, long s_ci, long s_co, float* workspace, long workspace_floats, int cin_valid,
+                           cudaStream_t st) {
   if (Cin % 32 || Cout % 32 || (taps != 1 && taps != 9)) return (int)cudaErrorInvalidValue;
   WgradArgs a;
   a.dW = dW; a.s_tap = s_tap; a.s_ci = s_ci; a.s_co = s_co;
@@ -1229,6 +1233,7 @@ int crackfl_wgrad_tc_ws(const void* X, const void* dY, float* dW, int B, int H, 
   dim3 grid(groups, ntn, splits);
   const long need = (long)groups * ntn * splits * 128L * a.BN;
   a.ws = (workspace && workspace_floats >= need) ? workspace : nullptr;
+  if (!a.ws && cin_valid > 0 && cin_valid < Cin) return (int)cudaErrorInvalidValue;
   ck::launch(wgrad_tc_k, grid, 192, smem, st, tmX, tmDY, a);
   CK_LAUNCH_CHECK();
   if (a.ws) {
@@ -1238,10 +1243,15 @@ int crackfl_wgrad_tc_ws(const void* X, const void* dY, float* dW, int B, int H, 
     long blocks = (total4 * zl + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
     ck::launch(wgrad_reduce_k, (int)blocks, 256, 0, st, a.ws, dW, groups, ntn, splits, a.BN, a.cw, a.mblk, a.total_blocks, Cin / a.cw,
-               s_tap, s_ci, s_co, zl);
+               s_tap, s_ci, s_co, zl, cin_valid > 0 ? cin_valid : Cin);
     CK_LAUNCH_CHECK();
   }
   return 0;
+}
+
+int crackfl_wgrad_tc_ws(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps,
+                        long s_tap, long s_ci, long s_co, float* workspace, long workspace_floats, cudaStream_t st) {
+  return crackfl_wgrad_tc_ws_cv(X, dY, dW, B, H, W, Cin, Cout, taps, s_tap, s_ci, s_co, workspace, workspace_floats, 0, st);
 }
 
 int crackfl_wgrad_tc(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps, long s_tap,

@@ -1101,6 +1101,36 @@ __global__ void __launch_bounds__(TPB) entry_conv_wgrad_v2_k(const uint8_t* __re
   }
 }
 
+// Entry conv as a tensor-core GEMM (second generation of K4): the 3x3 stride-2 patches of the uint8 image are written out
+// once as a bf16 matrix col[pixel][32] (k = (kh*3+kw)*3+ci for k < 27, zeros for k = 27..31, /255 applied; TF "same"
+// padding = bottom/right zeros), and both the forward conv and its weight gradient become K=32 / Cin=32 tcgen05 GEMMs
+// over that matrix (the CUDA-core kernels above spend 37 us / 103 us on what is 5 + 10 us of memory traffic).
+// ref: client_fit_model.py:100 Conv2D(32,3,strides=2,"same"), :43 x/255
+__global__ void __launch_bounds__(TPB) entry_im2col_k(const uint8_t* __restrict__ x, __nv_bfloat16* __restrict__ col, int B, int H,
+                                                      int W) {
+  ck::pdl_enter();
+  const int Ho = H >> 1, Wo = W >> 1;
+  const long total = (long)B * Ho * Wo * 4;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int q = (int)(i & 3);
+    const long p = i >> 2;
+    const int ow = (int)(p % Wo);
+    const int oh = (int)((p / Wo) % Ho);
+    const long b = p / ((long)Wo * Ho);
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = q * 8 + j;
+      const int tap = k / 3, ci = k - tap * 3;
+      const int kh = tap / 3, kw = tap - kh * 3;
+      const int ih = 2 * oh + kh, iw = 2 * ow + kw;
+      const bool ok = k < 27 && ih < H && iw < W;
+      f[j] = ok ? (float)__ldg(x + ((b * H + ih) * (long)W + iw) * 3 + ci) * (1.0f / 255.0f) : 0.f;
+    }
+    stg16(col + p * 32 + q * 8, pack8(f));
+  }
+}
+
 inline int grid_for(long total, int cap = 148 * 16) {
   long b = (total + TPB - 1) / TPB;
   return (int)(b < 1 ? 1 : (b > cap ? cap : b));
@@ -1126,6 +1156,13 @@ int crackfl_entry_conv_fwd(const void* x_u8, const float* w, const float* bias, 
   const long total = (long)B * (H / 2) * (W / 2) * (C / 8);
   ck::launch(entry_conv_fwd_k, grid_for(total), TPB, (27 * C + C) * sizeof(float), st, 
       (const uint8_t*)x_u8, w, bias, (__nv_bfloat16*)y, B, H, W, C);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_entry_im2col(const void* x_u8, void* col, int B, int H, int W, cudaStream_t st) {
+  const long total = (long)B * (H / 2) * (W / 2) * 4;
+  ck::launch(entry_im2col_k, grid_for(total), TPB, 0, st, (const uint8_t*)x_u8, (__nv_bfloat16*)col, B, H, W);
   CK_LAUNCH_CHECK();
   return 0;
 }

@@ -40,7 +40,7 @@ __global__ void __launch_bounds__(256) adam_k(float* __restrict__ p, float* __re
   }
 }
 
-// out[dst + (n*T + t)*K + k] = bf16(arena[src + n*s_n + t*s_t + k*s_k]).  Exactly one of s_n / s_k is 1 for every
+// out[dst + (n*T + t)*Kd + k] = bf16(arena[src + n*s_n + t*s_t + k*s_k]), Kd = pad_ ? pad_ : K.  Exactly one of s_n / s_k is 1 for every
 // operand of the model; when it is s_n (the source is contiguous along n but the operand wants k contiguous) the
 // 32x32 tile goes through shared memory so that both the fp32 reads and the bf16 writes are coalesced.
 __global__ void __launch_bounds__(256) weight_prep_k(const float* __restrict__ arena, __nv_bfloat16* __restrict__ ops,
@@ -49,6 +49,7 @@ __global__ void __launch_bounds__(256) weight_prep_k(const float* __restrict__ a
   __shared__ float tile[32][33];
   const crackfl_prep_desc d = descs[blockIdx.y];
   const int tn = (d.N + 31) / 32, tk = (d.K + 31) / 32;
+  const int Kd = d.pad_ ? d.pad_ : d.K;  // row stride of the operand (K padded up, the pad columns stay zero)
   const int tiles = tn * tk * d.T;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
   for (int tl = blockIdx.x; tl < tiles; tl += gridDim.x) {
@@ -63,14 +64,14 @@ __global__ void __launch_bounds__(256) weight_prep_k(const float* __restrict__ a
       __syncthreads();
       for (int r = ty; r < 32; r += 8) {
         const int n = n0 + r, k = k0 + tx;
-        if (n < d.N && k < d.K) ops[d.dst_off + ((long)n * d.T + t) * d.K + k] = __float2bfloat16_rn(tile[tx][r]);
+        if (n < d.N && k < d.K) ops[d.dst_off + ((long)n * d.T + t) * Kd + k] = __float2bfloat16_rn(tile[tx][r]);
       }
       __syncthreads();
     } else {
       for (int r = ty; r < 32; r += 8) {
         const int n = n0 + r, k = k0 + tx;
         if (n < d.N && k < d.K)
-          ops[d.dst_off + ((long)n * d.T + t) * d.K + k] =
+          ops[d.dst_off + ((long)n * d.T + t) * Kd + k] =
               __float2bfloat16_rn(arena[d.src_off + (long)n * d.s_n + (long)t * d.s_t + (long)k * d.s_k]);
       }
     }
@@ -128,7 +129,7 @@ int crackfl_adam_step(float* p, float* g, float* m, float* v, int* step, long n,
 }
 
 int crackfl_weight_prep(const float* arena, void* ops, const crackfl_prep_desc* descs_dev, int num_desc, cudaStream_t st) {
-  dim3 grid(48, num_desc);
+  dim3 grid(192, num_desc);  // <= 3 tiles of 32x32 per block for the largest operand (256 x 9 x 256)
   ck::launch(weight_prep_k, grid, 256, 0, st, arena, (__nv_bfloat16*)ops, descs_dev);
   CK_LAUNCH_CHECK();
   return 0;

@@ -35,6 +35,10 @@ typedef struct {
 int crackfl_entry_conv_fwd(const void* x_u8, const float* w, const float* bias, void* y, int B, int H, int W, int C,
                            cudaStream_t stream);
 int crackfl_entry_conv_wgrad(const void* x_u8, const void* dy, float* dw, int B, int H, int W, int C, cudaStream_t stream);
+/* second generation: col[B*H/2*W/2][32] bf16 = the /255-normalised 3x3 stride-2 patches (k = (kh*3+kw)*3+ci, k >= 27 zero);
+ * the entry conv and its weight gradient then run as tcgen05 GEMMs over col (crackfl_conv_tc_fwd with K = 32,
+ * crackfl_wgrad_tc_ws_cv with Cin = 32, cin_valid = 27). */
+int crackfl_entry_im2col(const void* x_u8, void* col, int B, int H, int W, cudaStream_t stream);
 
 /* ---- batch normalisation (ref: client_fit_model.py:101,110,114,130,134; eps 1e-3, momentum .99) ---- */
 /* stats = [sum C][sumsq C]; bn = [scale C][shift C][mean C][invstd C]; sums = [sum dz C][sum dz*(y-mean) C] */
@@ -135,6 +139,10 @@ int crackfl_wgrad_tc(const void* X, const void* dY, float* dW, int B, int H, int
  * model): per-CTA partial tiles + a reduction pass instead of contended fp32 atomics (about 2x faster). */
 int crackfl_wgrad_tc_ws(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps,
                         long s_tap, long s_ci, long s_co, float* workspace, long workspace_floats, cudaStream_t stream);
+/* as crackfl_wgrad_tc_ws; gradient rows of the zero-padded input channels ci >= cin_valid are not written */
+int crackfl_wgrad_tc_ws_cv(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps,
+                           long s_tap, long s_ci, long s_co, float* workspace, long workspace_floats, int cin_valid,
+                           cudaStream_t stream);
 int crackfl_tc_selftest_supported(void);
 
 /* ---- optimiser / weight re-layout ------------------------------------------------------------ */
@@ -142,7 +150,7 @@ typedef struct {
   long src_off; /* element offset into the fp32 arena (already includes any flip base) */
   long dst_off; /* element offset into the bf16 operand buffer */
   int N, T, K;  /* out[dst + (n*T + t)*K + k] = arena[src + n*s_n + t*s_t + k*s_k] */
-  int pad_;
+  int pad_; /* row stride of the operand when K is padded up (0: = K); pad columns are never written */
   long s_n, s_t, s_k;
 } crackfl_prep_desc;
 int crackfl_weight_prep(const float* arena, void* ops_bf16, const crackfl_prep_desc* descs_dev, int num_desc,

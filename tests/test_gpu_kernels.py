@@ -204,8 +204,10 @@ def test_engine_dice_loss_vs_oracle():
 def test_backward_matches_finite_differences():
     from crackfl.utils.check import directional_fd_check
     fd = directional_fd_check(conv_impl="tc", rel_step=0.004,
-                              tensors=("batch_normalization/gamma", "conv2d_2/kernel", "separable_conv2d_3/pointwise_kernel",
-                                       "conv2d_transpose_6/kernel"))
+                              tensors=("conv2d_2/kernel", "separable_conv2d_3/pointwise_kernel", "conv2d_transpose_6/kernel"))
+    # the first BN sits under the whole bf16 network: its finite difference needs a longer step to rise above the
+    # forward's rounding noise (measured: 15 % scatter at 0.004, 5 % at 0.01)
+    fd.update(directional_fd_check(conv_impl="tc", rel_step=0.01, tensors=("batch_normalization/gamma",)))
     for k, v in fd.items():
         assert abs(v["fd_slope"] - v["engine_|g|"]) < 0.15 * v["engine_|g|"], (k, v)
 
@@ -310,3 +312,45 @@ def test_dw3x3_tma_fwd_dgrad_wgrad(B, H, W, Cc, mode):
     assert float((dz.float().permute(0, 3, 1, 2) - want).norm() / want.norm()) < 1.5e-2
     refw = wr.grad[:, 0].permute(1, 2, 0).reshape(9, Cc)
     assert float((dwk - refw).norm() / refw.norm()) < 1e-2
+
+
+@pytest.mark.parametrize("B,H,W,c0", [(2, 32, 32, 32), (3, 48, 80, 64), (1, 30, 34, 32)])
+def test_entry_conv_tensor_core_path(B, H, W, c0):
+    """im2col + tcgen05 GEMMs (forward and weight gradient) vs an fp32 PyTorch conv with TF 'same' stride-2 padding
+    (ref: client_fit_model.py:100, :43)."""
+    L, lib = _lib()
+    torch.manual_seed(3)
+    x = torch.randint(0, 256, (B, H, W, 3), device="cuda", dtype=torch.uint8)
+    k = torch.randn(3, 3, 3, c0, device="cuda") * 0.3  # Keras (kh, kw, ci, co)
+    bias = torch.randn(c0, device="cuda")
+    Ho, Wo = H // 2, W // 2
+    col = torch.zeros(B, Ho, Wo, 32, device="cuda", dtype=torch.bfloat16)
+    L.check(lib.crackfl_entry_im2col(x.data_ptr(), col.data_ptr(), B, H, W, _st()))
+    # operand [N][32] through weight_prep (pad_ = 32: columns 27..31 stay zero)
+    desc = L.PrepDesc(src_off=0, dst_off=0, N=c0, T=1, K=27, pad_=32, s_n=1, s_t=0, s_k=c0)
+    ddev = torch.frombuffer(bytearray(bytes(desc)), dtype=torch.uint8).clone().cuda()
+    ops = torch.zeros(c0 * 32, device="cuda", dtype=torch.bfloat16)
+    L.check(lib.crackfl_weight_prep(k.data_ptr(), ops.data_ptr(), ddev.data_ptr(), 1, _st()))
+    y = torch.zeros(B, Ho, Wo, c0, device="cuda", dtype=torch.bfloat16)
+    stats = torch.zeros(2 * c0, device="cuda")
+    L.check(lib.crackfl_conv_tc_fwd(col.data_ptr(), ops.data_ptr(), bias.data_ptr(), 0, y.data_ptr(), stats.data_ptr(),
+                                    B, Ho, Wo, 32, c0, 1, _st()))
+    xf = (x.float() / 255).permute(0, 3, 1, 2)
+    xp = F.pad(xf, (0, 1, 0, 1))  # TF "same" with stride 2 and even input: one row / column at the bottom / right
+    w = k.permute(3, 2, 0, 1).contiguous().requires_grad_(True)
+    ref = F.conv2d(xp, w, bias, stride=2).permute(0, 2, 3, 1)
+    torch.cuda.synchronize()
+    assert float((y.float() - ref).norm() / ref.norm()) < 1e-2
+    assert float((stats[:c0] - y.float().sum((0, 1, 2))).abs().max() / (y.float().sum((0, 1, 2)).abs().max() + 1)) < 1e-2
+    # weight gradient
+    dy = torch.randn(B, Ho, Wo, c0, device="cuda").bfloat16()
+    ref.backward(dy.float())
+    gref = w.grad.permute(2, 3, 1, 0)  # -> (kh, kw, ci, co)
+    dw = torch.zeros(27 * c0 + 64, device="cuda")
+    ws = torch.zeros(4 << 20, device="cuda")
+    L.check(lib.crackfl_wgrad_tc_ws_cv(col.data_ptr(), dy.data_ptr(), dw.data_ptr(), B, Ho, Wo, 32, c0, 1, 0, c0, 1,
+                                       ws.data_ptr(), ws.numel(), 27, _st()))
+    torch.cuda.synchronize()
+    got = dw[:27 * c0].reshape(3, 3, 3, c0)
+    assert float((got - gref).norm() / gref.norm()) < 1e-2
+    assert float(dw[27 * c0:].abs().max()) == 0.0  # the padded rows are not written
