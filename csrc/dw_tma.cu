@@ -76,15 +76,65 @@ __device__ __forceinline__ void fin_publish(const BnFin& f, int C) {
   }
 }
 
+// ---- packed fp32 helpers: Blackwell issues two fp32 FMAs per FFMA2 (fma.rn.f32x2 on a 64-bit register pair) ----------
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t ffma2(f2_t a_, f2_t b_, f2_t c_) {
+  f2_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a_), "l"(b_), "l"(c_));
+  return d;
+}
+__device__ __forceinline__ f2_t fmul2(f2_t a_, f2_t b_) {
+  f2_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a_), "l"(b_));
+  return d;
+}
+__device__ __forceinline__ f2_t pk2(float lo, float hi) {
+  f2_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void upk2(f2_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+// one 32-bit word of two bf16 -> packed (lo, hi) fp32
+__device__ __forceinline__ f2_t bf2_to_f2(uint32_t v) {
+  f2_t r;
+  const uint32_t lo = v << 16, hi = v & 0xffff0000u;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+// packed (lo, hi) fp32 -> relu -> one word of two bf16
+__device__ __forceinline__ uint32_t f2_to_bf2_relu(f2_t v) {
+  float lo, hi;
+  upk2(v, lo, hi);
+  uint32_t r;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ uint32_t relu_bf2(uint32_t v) {
+  uint32_t r;
+  asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(0u));
+  return r;
+}
+
+// Second generation of the stencil kernel.  ncu on the first one (profiles/ncu_dw_stencil.md): 2344 warp instructions per
+// 16x16x64 tile, issue-bound at 52 % with `no_instruction` the top stall (an 18-row fully unrolled body with the
+// activation inlined three times per element outgrew the 32 KB instruction cache).  Here
+//   * the activation (relu / relu(bn)) is applied ONCE per element, in place in the shared-memory halo tile, before the
+//     stencil (cvt.rn.relu.bf16x2 packs and clamps in one instruction);
+//   * the stencil accumulates channel pairs with FFMA2 (18 instead of 36 FMAs per output quad);
+//   * the input-gradient variant gets the forward input (relu mask) as a second TMA tile instead of a dependent global
+//     load per output row, and prefetches the residual-path gradient before it waits for the tile.
 // TY = tile rows; threads: (c4 = CB/4) x 16 columns x RG row groups = 256 (RG = 1 for CB = 64, 2 for CB = 32)
-template <int TY, int RG>
-__global__ void __launch_bounds__(256, 2) dw_stencil_k(const __grid_constant__ CUtensorMap tmX, const DwArgs a) {
+template <int TY, int RG, bool DGRAD>
+__global__ void __launch_bounds__(256, 2) dw_stencil_k(const __grid_constant__ CUtensorMap tmX,
+                                                       const __grid_constant__ CUtensorMap tmS, const DwArgs a) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 127u) & ~127u;
   uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
   const int CB = a.CB, rowb = CB * 2;
-  const uint32_t stage_bytes = (uint32_t)((TY + 2) * HW * rowb);
+  const uint32_t halo_bytes = (uint32_t)((TY + 2) * HW * rowb);
+  const uint32_t stage_bytes = halo_bytes + (DGRAD ? (uint32_t)(TY * TX * rowb) : 0u);
   const uint32_t bar0 = base + 2u * stage_bytes;
+  float* coef = reinterpret_cast<float*>(gbase + 2u * stage_bytes + 64);  // [scale CB][shift CB] of the current channel block
   const int nc4 = CB >> 2;
   constexpr int rows = TY / RG;
   const int c4 = threadIdx.x % nc4, col = (threadIdx.x / nc4) % TX, rg = threadIdx.x / (nc4 * TX);
@@ -95,6 +145,7 @@ __global__ void __launch_bounds__(256, 2) dw_stencil_k(const __grid_constant__ C
     mbar_init(bar0 + 8u, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     tma_prefetch_desc(&tmX);
+    if (DGRAD) tma_prefetch_desc(&tmS);
   }
   pdl_enter();  // barrier init / descriptor prefetch above overlap the previous kernel's tail
   fin_publish(a.fin, a.C);
@@ -108,11 +159,13 @@ __global__ void __launch_bounds__(256, 2) dw_stencil_k(const __grid_constant__ C
     const int b = sp / a.tiles_y;
     mbar_expect_tx(bar0 + 8u * stage, stage_bytes);
     tma_load_4d(base + stage * stage_bytes, &tmX, bar0 + 8u * stage, cblk * CB, tx_i * TX - 1, ty_i * TY - 1, b);
+    if (DGRAD) tma_load_4d(base + stage * stage_bytes + halo_bytes, &tmS, bar0 + 8u * stage, cblk * CB, tx_i * TX, ty_i * TY, b);
   };
   if (threadIdx.x == 0 && (int)blockIdx.x < a.total_tiles) issue(blockIdx.x, 0);
 
   int cur_cblk = -1;
-  float wk[9][4], sc[4], sh[4], msc[4], msh[4];
+  f2_t wk[9][2], msc[2], msh[2];
+  msc[0] = msc[1] = msh[0] = msh[1] = 0ull;
   int it = 0;
   for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
     const int stage = it & 1;
@@ -124,80 +177,141 @@ __global__ void __launch_bounds__(256, 2) dw_stencil_k(const __grid_constant__ C
     const int ty_i = sp % a.tiles_y;
     const int b = sp / a.tiles_y;
     const int cg = cblk * CB + c4 * 4;  // first global channel of this thread
-    if (cblk != cur_cblk) {
+    if (cblk != cur_cblk) {             // uniform over the CTA
       cur_cblk = cblk;
 #pragma unroll
       for (int t = 0; t < 9; ++t) {
         const float4 v = __ldg(reinterpret_cast<const float4*>(a.w + (a.flip ? 8 - t : t) * a.C + cg));
-        wk[t][0] = v.x; wk[t][1] = v.y; wk[t][2] = v.z; wk[t][3] = v.w;
+        wk[t][0] = pk2(v.x, v.y); wk[t][1] = pk2(v.z, v.w);
       }
-      if (a.act_mode == 1) coeffs4(a.fin, a.bn, a.C, cg, sc, sh);
-      if (a.src && a.src_mode == 1) {
+      if (!DGRAD && a.act_mode == 1) {
+        if (threadIdx.x < nc4) {
+          float sc[4], sh[4];
+          coeffs4(a.fin, a.bn, a.C, cblk * CB + threadIdx.x * 4, sc, sh);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { msc[j] = a.src_bn[cg + j]; msh[j] = a.src_bn[a.C + cg + j]; }
+          for (int j = 0; j < 4; ++j) { coef[threadIdx.x * 4 + j] = sc[j]; coef[CB + threadIdx.x * 4 + j] = sh[j]; }
+        }
+        __syncthreads();
+      }
+      if (DGRAD && a.src_mode == 1) {
+        const float4 s4 = __ldg(reinterpret_cast<const float4*>(a.src_bn + cg));
+        const float4 h4 = __ldg(reinterpret_cast<const float4*>(a.src_bn + a.C + cg));
+        msc[0] = pk2(s4.x, s4.y); msc[1] = pk2(s4.z, s4.w);
+        msh[0] = pk2(h4.x, h4.y); msh[1] = pk2(h4.z, h4.w);
+      }
+    }
+    const int w0 = tx_i * TX, ty0 = ty_i * TY, h0 = ty0 + rg * rows;
+    const int gw = w0 + col;
+    // residual-path gradient (half resolution, even pixels only): in flight while we wait for the tile
+    uint2 rres[(rows + 1) / 2];
+    if (DGRAD) {
+#pragma unroll
+      for (int i = 0; i < (rows + 1) / 2; ++i) {
+        rres[i] = make_uint2(0u, 0u);
+        const int oh = h0 + 2 * i;  // h0 is even
+        if (a.resid && !(col & 1) && oh < a.H && gw < a.W)
+          rres[i] = __ldg(reinterpret_cast<const uint2*>(
+              a.resid_t + (((long)b * (a.H >> 1) + (oh >> 1)) * (a.W >> 1) + (gw >> 1)) * a.C + cg));
       }
     }
     mbar_wait(bar0 + 8u * stage, (uint32_t)(it >> 1) & 1u);
-    const uint8_t* tile_s = gbase + stage * stage_bytes;
-    const int w0 = tx_i * TX, h0 = ty_i * TY + rg * rows;
-    const int gw = w0 + col;
-    float win[3][3][4];
-#pragma unroll
-    for (int r = 0; r < rows + 2; ++r) {
-      const int gh = h0 - 1 + r;
-      const uint8_t* rowp = tile_s + (size_t)((rg * rows + r) * HW) * rowb + c4 * 8;
-      // slide: row r goes into slot r % 3
-#pragma unroll
-      for (int kx = 0; kx < 3; ++kx) {
-        float v[4];
-        load4(rowp, (col + kx) * rowb, v);
-        const bool inside = gh >= 0 && gh < a.H && (gw - 1 + kx) >= 0 && (gw - 1 + kx) < a.W;
+    uint8_t* tile_s = gbase + stage * stage_bytes;
+
+    if (!DGRAD && a.act_mode != 2) {
+      // activation pre-pass, in place; out-of-image pixels (TMA zero fill) must stay zero under relu(bn(.))
+      const int c8n = CB >> 3;
+      const int nchunk = (TY + 2) * HW * c8n;
+      const bool interior = w0 >= 1 && w0 + TX < a.W && ty0 >= 1 && ty0 + TY < a.H;
+      if (a.act_mode == 0) {
+        for (int idx = threadIdx.x; idx < nchunk; idx += 256) {
+          uint4* q = reinterpret_cast<uint4*>(tile_s) + idx;
+          uint4 v = *q;
+          v.x = relu_bf2(v.x); v.y = relu_bf2(v.y); v.z = relu_bf2(v.z); v.w = relu_bf2(v.w);
+          *q = v;
+        }
+      } else {
+        const int c8 = threadIdx.x % c8n;  // 256 % c8n == 0: the same channel octet on every trip
+        f2_t scp[4], shp[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          float x = v[j];
-          if (a.act_mode == 1) x = fmaf(x, sc[j], sh[j]);
-          if (a.act_mode != 2) x = fmaxf(x, 0.f);
-          win[r % 3][kx][j] = inside ? x : 0.f;
+          scp[j] = *reinterpret_cast<const f2_t*>(coef + c8 * 8 + 2 * j);
+          shp[j] = *reinterpret_cast<const f2_t*>(coef + CB + c8 * 8 + 2 * j);
         }
+        for (int idx = threadIdx.x; idx < nchunk; idx += 256) {
+          uint4* q = reinterpret_cast<uint4*>(tile_s) + idx;
+          uint4 v = *q;
+          v.x = f2_to_bf2_relu(ffma2(bf2_to_f2(v.x), scp[0], shp[0]));
+          v.y = f2_to_bf2_relu(ffma2(bf2_to_f2(v.y), scp[1], shp[1]));
+          v.z = f2_to_bf2_relu(ffma2(bf2_to_f2(v.z), scp[2], shp[2]));
+          v.w = f2_to_bf2_relu(ffma2(bf2_to_f2(v.w), scp[3], shp[3]));
+          if (!interior) {
+            const int pi = idx / c8n;
+            const int hr = pi / HW, hc = pi - hr * HW;
+            const int gh = ty0 - 1 + hr, gx = w0 - 1 + hc;
+            if (gh < 0 || gh >= a.H || gx < 0 || gx >= a.W) v = make_uint4(0u, 0u, 0u, 0u);
+          }
+          *q = v;
+        }
+      }
+      __syncthreads();
+    }
+
+    f2_t win[3][3][2];
+    const long out_rs = (long)a.W * a.C;  // elements per image row
+    __nv_bfloat16* const out_p = a.out + (((long)b * a.H + h0) * a.W + gw) * a.C + cg;
+    const uint8_t* const row0 = tile_s + (size_t)(((rg * rows) * HW + col) * rowb + c4 * 8);
+    const uint8_t* const src0 = tile_s + halo_bytes + (size_t)(((rg * rows) * TX + col) * rowb + c4 * 8);
+#pragma unroll
+    for (int r = 0; r < rows + 2; ++r) {
+      const uint8_t* rowp = row0 + r * (HW * rowb);
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        const uint2 v = *reinterpret_cast<const uint2*>(rowp + kx * rowb);
+        win[r % 3][kx][0] = bf2_to_f2(v.x);
+        win[r % 3][kx][1] = bf2_to_f2(v.y);
       }
       if (r >= 2) {
         const int oh = h0 + r - 2;
-        if (oh < a.H && gw < a.W) {
-          float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        f2_t acc0 = fmul2(win[(r - 2) % 3][0][0], wk[0][0]), acc1 = fmul2(win[(r - 2) % 3][0][1], wk[0][1]);
 #pragma unroll
-          for (int kh = 0; kh < 3; ++kh)
-#pragma unroll
-            for (int kx = 0; kx < 3; ++kx)
-#pragma unroll
-              for (int j = 0; j < 4; ++j) acc[j] = fmaf(win[(r - 2 + kh) % 3][kx][j], wk[kh * 3 + kx][j], acc[j]);
-          const long o = (((long)b * a.H + oh) * a.W + gw) * a.C + cg;
-          if (a.src) {
-            // input-gradient epilogue: relu mask of the forward input, residual-path gradient on even pixels
-            const uint2 sv = __ldg(reinterpret_cast<const uint2*>(a.src + o));
-            float s4[4] = {__uint_as_float(sv.x << 16), __uint_as_float(sv.x & 0xffff0000u), __uint_as_float(sv.y << 16),
-                           __uint_as_float(sv.y & 0xffff0000u)};
-            float r4[4] = {0.f, 0.f, 0.f, 0.f};
-            if (a.resid && !(oh & 1) && !(gw & 1)) {
-              const uint2 rv = __ldg(reinterpret_cast<const uint2*>(
-                  a.resid_t + (((long)b * (a.H >> 1) + (oh >> 1)) * (a.W >> 1) + (gw >> 1)) * a.C + cg));
-              r4[0] = __uint_as_float(rv.x << 16); r4[1] = __uint_as_float(rv.x & 0xffff0000u);
-              r4[2] = __uint_as_float(rv.y << 16); r4[3] = __uint_as_float(rv.y & 0xffff0000u);
-            }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const float pre = a.src_mode == 1 ? fmaf(s4[j], msc[j], msh[j]) : s4[j];
-              const float m = pre > 0.f ? 1.f : 0.f;
-              acc[j] = (a.resid == 2) ? m * (acc[j] + r4[j]) : m * acc[j] + r4[j];
-            }
+        for (int t = 1; t < 9; ++t) {
+          acc0 = ffma2(win[(r - 2 + t / 3) % 3][t % 3][0], wk[t][0], acc0);
+          acc1 = ffma2(win[(r - 2 + t / 3) % 3][t % 3][1], wk[t][1], acc1);
+        }
+        float o4[4];
+        upk2(acc0, o4[0], o4[1]);
+        upk2(acc1, o4[2], o4[3]);
+        if (DGRAD) {
+          // input-gradient epilogue: relu mask of the forward input, residual-path gradient on even pixels
+          const uint2 sv = *reinterpret_cast<const uint2*>(src0 + (r - 2) * (TX * rowb));
+          f2_t p0 = bf2_to_f2(sv.x), p1 = bf2_to_f2(sv.y);
+          if (a.src_mode == 1) { p0 = ffma2(p0, msc[0], msh[0]); p1 = ffma2(p1, msc[1], msh[1]); }
+          float pre[4];
+          upk2(p0, pre[0], pre[1]);
+          upk2(p1, pre[2], pre[3]);
+          float r4[4] = {0.f, 0.f, 0.f, 0.f};
+          if (((r - 2) & 1) == 0) {
+            const uint2 rv = rres[(r - 2) / 2];
+            r4[0] = __uint_as_float(rv.x << 16); r4[1] = __uint_as_float(rv.x & 0xffff0000u);
+            r4[2] = __uint_as_float(rv.y << 16); r4[3] = __uint_as_float(rv.y & 0xffff0000u);
           }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const bool m = pre[j] > 0.f;
+            o4[j] = (a.resid == 2) ? (m ? o4[j] + r4[j] : 0.f) : ((m ? o4[j] : 0.f) + r4[j]);
+          }
+        }
+        if (oh < a.H && gw < a.W) {
           uint2 pk;
-          pk.x = pack2(acc[0], acc[1]);
-          pk.y = pack2(acc[2], acc[3]);
-          *reinterpret_cast<uint2*>(a.out + o) = pk;
+          pk.x = pack2(o4[0], o4[1]);
+          pk.y = pack2(o4[2], o4[3]);
+          *reinterpret_cast<uint2*>(out_p + (r - 2) * out_rs) = pk;
         }
       }
     }
-    __syncthreads();  // every thread is done with this stage before it is refilled two iterations from now
+    // generic-proxy writes (pre-pass) are ordered before the TMA refill of this stage two iterations from now
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();  // every thread is done with this stage before it is refilled
   }
 }
 
@@ -333,42 +447,54 @@ int num_sms() {
 
 bool shape_ok(int C) { return C % 32 == 0 && (C <= 64 || C % 64 == 0); }
 
+// forward (src == NULL) or input gradient (src != NULL, flip = 1, act_mode = 2)
+template <int TY, bool DGRAD>
+static int launch_stencil(const void* x, DwArgs& a, cudaStream_t st) {
+  a.tiles_x = (a.W + TX - 1) / TX; a.tiles_y = (a.H + TY - 1) / TY;
+  a.total_tiles = a.tiles_x * a.tiles_y * a.B * (a.C / a.CB);
+  CUtensorMap tm, tmS;
+  const int d[4] = {a.C, a.W, a.H, a.B}, bx[4] = {a.CB, HW, TY + 2, 1}, bs[4] = {a.CB, TX, TY, 1};
+  int rc = ck::get_tensor_map(x, 4, d, bx, 0, &tm);
+  if (rc) return rc;
+  rc = ck::get_tensor_map(DGRAD ? (const void*)a.src : x, 4, d, DGRAD ? bs : bx, 0, &tmS);
+  if (rc) return rc;
+  const size_t stage = (size_t)(TY + 2) * HW * a.CB * 2 + (DGRAD ? (size_t)TY * TX * a.CB * 2 : 0);
+  const size_t smem = 2 * stage + 64 + 2 * a.CB * sizeof(float) + 128;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(dw_stencil_k<TY, 1, DGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(dw_stencil_k<TY, 2, DGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    if (e != cudaSuccess) return (int)e;
+    attr = true;
+  }
+  int grid = 2 * num_sms();
+  if (grid > a.total_tiles) grid = a.total_tiles;
+  if (a.CB == 64) ck::launch(dw_stencil_k<TY, 1, DGRAD>, grid, 256, smem, st, tm, tmS, a);
+  else ck::launch(dw_stencil_k<TY, 2, DGRAD>, grid, 256, smem, st, tm, tmS, a);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
 }  // namespace
 
 extern "C" {
 
-// forward (src == NULL) or input gradient (src != NULL, flip = 1, act_mode = 2)
 int crackfl_dw3x3_tma(const void* x, const float* w, const float* bn, const crackfl_bn_fin* fin, void* out, const void* src,
                       const float* src_bn, const void* resid_t, int B, int H, int W, int C, int act_mode, int flip,
                       int src_mode, int resid, cudaStream_t st) {
   if (!shape_ok(C)) return (int)cudaErrorInvalidValue;
-  constexpr int TY = 16;
   DwArgs a;
   memset(&a, 0, sizeof(a));
   a.w = w; a.bn = bn; if (fin) a.fin = *fin;
   a.out = (__nv_bfloat16*)out; a.src = (const __nv_bfloat16*)src; a.src_bn = src_bn; a.resid_t = (const __nv_bfloat16*)resid_t;
   a.B = B; a.H = H; a.W = W; a.C = C; a.CB = C >= 64 ? 64 : 32;
   a.act_mode = act_mode; a.flip = flip; a.src_mode = src_mode; a.resid = resid;
-  a.tiles_x = (W + TX - 1) / TX; a.tiles_y = (H + TY - 1) / TY;
-  a.total_tiles = a.tiles_x * a.tiles_y * B * (C / a.CB);
-  CUtensorMap tm;
-  const int d[4] = {C, W, H, B}, bx[4] = {a.CB, HW, TY + 2, 1};
-  int rc = ck::get_tensor_map(x, 4, d, bx, 0, &tm);
-  if (rc) return rc;
-  const size_t smem = 2 * (size_t)(TY + 2) * HW * a.CB * 2 + 128 + 64;
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(dw_stencil_k<TY, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_stencil_k<TY, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-    if (e != cudaSuccess) return (int)e;
-    attr = true;
+  if (src) {
+    if (act_mode != 2) return (int)cudaErrorInvalidValue;  // the gradient variant takes g as is
+    return launch_stencil<8, true>(x, a, st);
   }
-  int grid = 2 * num_sms();
-  if (grid > a.total_tiles) grid = a.total_tiles;
-  if (a.CB == 64) ck::launch(dw_stencil_k<TY, 1>, grid, 256, smem, st, tm, a);
-  else ck::launch(dw_stencil_k<TY, 2>, grid, 256, smem, st, tm, a);
-  CK_LAUNCH_CHECK();
-  return 0;
+  return launch_stencil<16, false>(x, a, st);
 }
 
 int crackfl_dw3x3_wgrad_tma(const void* g, const void* src, const float* bn, float* dwk, int B, int H, int W, int C, int mode,
