@@ -424,8 +424,9 @@ class UNetEngine:
                                                     self.G(bn2.tensors[1]), B, r, rw, f, 0)))
             oi = ts[ct2.tensors[0]]
             self._gemm(prog, b(p + "dy2"), ct2.name + ".d", 0, 0, b(p + "da1"), B, r, rw)
-            self._wgrad(prog, b(p + "a1"), b(p + "dy2"), self.G(ct2.tensors[0]) + 4 * 8 * f * f, B, r, rw, f, f, 9,
-                        -f * f, 1, f)
+            # Keras (kh,kw,out,in) kernel: with the operands swapped (A = dY, B = X) the tile columns run along "in", the
+            # contiguous axis of the arena, so the split reduction writes coalesced; the tap flip then cancels out
+            self._wgrad(prog, b(p + "dy2"), b(p + "a1"), self.G(ct2.tensors[0]), B, r, rw, f, f, 9, f * f, f, 1)
             # BN1 + ReLU
             prog.append((lib.crackfl_bn_bwd_reduce, (b(p + "da1"), 0, b(p + "y1"), self._bnptr(bn1.name),
                                                      self._zptr(bn1.name, "sums"), B, r, rw, f, 1)))
@@ -434,8 +435,7 @@ class UNetEngine:
                                                     self.G(bn1.tensors[1]), B, r, rw, f, 1)))
             a0 = "a0_0" if j == 0 else p + "a0"
             self._gemm(prog, b(p + "dy1"), ct1.name + ".d", 0, 0, b(p + "da0"), B, r, rw)
-            self._wgrad(prog, b(a0), b(p + "dy1"), self.G(ct1.tensors[0]) + 4 * 8 * f * cin, B, r, rw, cin, f, 9,
-                        -f * cin, 1, cin)
+            self._wgrad(prog, b(p + "dy1"), b(a0), self.G(ct1.tensors[0]), B, r, rw, f, cin, 9, f * cin, cin, 1)
             # residual 1x1 conv (at low resolution)
             self._gemm(prog, b(drl), res.name + ".d", 0, 0, b(p + "T"), B, lr_, lrw)
             self._wgrad(prog, b(src_res), b(drl), self.G(res.tensors[0]), B, lr_, lrw, cin, f, 1, 0, f, 1)

@@ -196,15 +196,15 @@ __global__ void __launch_bounds__(TPB, 4) bn_act_k(const __nv_bfloat16* __restri
                                                    int B, int H, int W, int C, int relu, const BnFin fin) {
   ck::pdl_enter();
   const int c8 = C >> 3;
-  const long total = (long)B * H * W * c8;
-  const long stride = (long)gridDim.x * blockDim.x;  // multiple of c8: a thread keeps its channel vector
-  const long g0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int total = (int)B * H * W * c8;
+  const int stride = (int)gridDim.x * blockDim.x;  // multiple of c8: a thread keeps its channel vector
+  const int g0 = (int)blockIdx.x * blockDim.x + threadIdx.x;
   const int cv = (int)(g0 % c8);
   float sc[8], sh[8];
   bn_coeffs(fin, bn, C, cv, sc, sh);
   bn_publish(fin, C);
-  for (long g = g0; g < total; g += 2 * stride) {
-    const long g2 = g + stride;
+  for (int g = g0; g < total; g += 2 * stride) {
+    const int g2 = g + stride;
     const bool has2 = g2 < total;
     float f[2][8];
     unpack8(ldg16(y + g * 8), f[0]);
@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(TPB, 4) bn_act_k(const __nv_bfloat16* __restri
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
       if (u == 1 && !has2) break;
-      const long gi = u ? g2 : g;
+      const int gi = u ? g2 : g;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         f[u][j] = fmaf(f[u][j], sc[j], sh[j]);
@@ -221,12 +221,12 @@ __global__ void __launch_bounds__(TPB, 4) bn_act_k(const __nv_bfloat16* __restri
       const uint4 v = pack8(f[u]);
       stg16(out + gi * 8, v);
       if (even) {
-        long p = gi / c8;
+        int p = gi / c8;
         const int w = (int)(p % W); p /= W;
         const int h = (int)(p % H);
         const int b = (int)(p / H);
         if (!(h & 1) && !(w & 1))
-          stg16(even + ((((long)b * (H >> 1) + (h >> 1)) * (W >> 1) + (w >> 1)) * c8 + cv) * 8, v);
+          stg16(even + ((((int)b * (H >> 1) + (h >> 1)) * (W >> 1) + (w >> 1)) * c8 + cv) * 8, v);
       }
     }
   }
@@ -357,14 +357,14 @@ __global__ void __launch_bounds__(TPB) pool_add_fwd_k(const __nv_bfloat16* __res
                                                       uint8_t* __restrict__ arg, int B, int H, int W, int C, const BnFin fin) {
   ck::pdl_enter();
   const int c8 = C >> 3, Ho = H >> 1, Wo = W >> 1;
-  const long total = (long)B * Ho * Wo * c8;
-  const long g0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int total = (int)B * Ho * Wo * c8;
+  const int g0 = (int)blockIdx.x * blockDim.x + threadIdx.x;
   const int cv = (int)(g0 % c8);
   float sc[8], sh[8];
   bn_coeffs(fin, bn, C, cv, sc, sh);
   bn_publish(fin, C);
-  for (long g = g0; g < total; g += (long)gridDim.x * blockDim.x) {
-    long p = g / c8;
+  for (int g = g0; g < total; g += (int)gridDim.x * blockDim.x) {
+    int p = g / c8;
     const int ow = (int)(p % Wo); p /= Wo;
     const int oh = (int)(p % Ho);
     const int b = (int)(p / Ho);
@@ -381,7 +381,7 @@ __global__ void __launch_bounds__(TPB) pool_add_fwd_k(const __nv_bfloat16* __res
         const int iw = 2 * ow + kw;
         if (iw >= W) continue;
         float f[8];
-        unpack8(ldg16(y + ((((long)b * H + ih) * W + iw) * c8 + cv) * 8), f);
+        unpack8(ldg16(y + ((((int)b * H + ih) * W + iw) * c8 + cv) * 8), f);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const float z = fmaf(f[j], sc[j], sh[j]);
@@ -402,7 +402,7 @@ __global__ void __launch_bounds__(TPB) pool_add_fwd_k(const __nv_bfloat16* __res
       *reinterpret_cast<uint2*>(arg + g * 8) = a;
     }
     if (even && !(oh & 1) && !(ow & 1))
-      stg16(even + ((((long)b * (Ho >> 1) + (oh >> 1)) * (Wo >> 1) + (ow >> 1)) * c8 + cv) * 8, v);
+      stg16(even + ((((int)b * (Ho >> 1) + (oh >> 1)) * (Wo >> 1) + (ow >> 1)) * c8 + cv) * 8, v);
     if (relu_out) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) best[j] = fmaxf(best[j], 0.f);
@@ -418,20 +418,20 @@ __global__ void __launch_bounds__(TPB) dec_combine_fwd_k(const __nv_bfloat16* __
                                                          int rl_up, const BnFin fin) {
   ck::pdl_enter();
   const int c8 = C >> 3;
-  const long total = (long)B * H * W * c8;
-  const long g0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int total = (int)B * H * W * c8;
+  const int g0 = (int)blockIdx.x * blockDim.x + threadIdx.x;
   const int cv = (int)(g0 % c8);
   float sc[8], sh[8];
   bn_coeffs(fin, bn, C, cv, sc, sh);
   bn_publish(fin, C);
-  for (long g = g0; g < total; g += (long)gridDim.x * blockDim.x) {
-    long p = g / c8;
+  for (int g = g0; g < total; g += (int)gridDim.x * blockDim.x) {
+    int p = g / c8;
     const int w = (int)(p % W); p /= W;
     const int h = (int)(p % H);
     const int b = (int)(p / H);
     float f[8], r[8];
     unpack8(ldg16(y + g * 8), f);
-    const long ri = rl_up ? ((((long)b * (H >> 1) + (h >> 1)) * (W >> 1) + (w >> 1)) * c8 + cv) : g;
+    const int ri = rl_up ? ((((int)b * (H >> 1) + (h >> 1)) * (W >> 1) + (w >> 1)) * c8 + cv) : g;
     unpack8(ldg16(rl + ri * 8), r);
 #pragma unroll
     for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]) + r[j];
@@ -440,8 +440,8 @@ __global__ void __launch_bounds__(TPB) dec_combine_fwd_k(const __nv_bfloat16* __
 #pragma unroll
       for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
       const uint4 v = pack8(f);
-      const long W2 = 2L * W;
-      const long base = (((long)b * 2 * H + 2 * h) * W2 + 2 * w) * c8 + cv;
+      const int W2 = 2 * W;
+      const int base = (((int)b * 2 * H + 2 * h) * W2 + 2 * w) * c8 + cv;
       stg16(a_next + base * 8, v);
       stg16(a_next + (base + c8) * 8, v);
       stg16(a_next + (base + W2 * c8) * 8, v);
@@ -456,15 +456,15 @@ __global__ void __launch_bounds__(TPB) down2sum_k(const __nv_bfloat16* __restric
                                                   int B, int Ho, int Wo, int C) {
   ck::pdl_enter();
   const int c8 = C >> 3;
-  const long total = (long)B * Ho * Wo * c8;
-  for (long g = (long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long)gridDim.x * blockDim.x) {
+  const int total = (int)B * Ho * Wo * c8;
+  for (int g = (int)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (int)gridDim.x * blockDim.x) {
     const int cv = (int)(g % c8);
-    long p = g / c8;
+    int p = g / c8;
     const int w = (int)(p % Wo); p /= Wo;
     const int h = (int)(p % Ho);
     const int b = (int)(p / Ho);
-    const long W2 = 2L * Wo;
-    const long base = (((long)b * 2 * Ho + 2 * h) * W2 + 2 * w) * c8 + cv;
+    const int W2 = 2 * Wo;
+    const int base = (((int)b * 2 * Ho + 2 * h) * W2 + 2 * w) * c8 + cv;
     float a0[8], a1[8], a2[8], a3[8], o[8];
     unpack8(ldg16(in + base * 8), a0);
     unpack8(ldg16(in + (base + c8) * 8), a1);
@@ -493,7 +493,7 @@ __global__ void __launch_bounds__(TPB) relu_bwd_add_k(const __nv_bfloat16* __res
                                                       const __nv_bfloat16* __restrict__ add, __nv_bfloat16* __restrict__ out,
                                                       long nvec) {
   ck::pdl_enter();
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
+  for (int i = (int)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int)gridDim.x * blockDim.x) {
     float a[8], m[8], t[8];
     unpack8(ldg16(g + i * 8), a);
     unpack8(ldg16(x + i * 8), m);
@@ -522,7 +522,7 @@ __device__ __forceinline__ void load_dz(const __nv_bfloat16* __restrict__ g, con
   } else {
     const int w = (int)(p % W);
     const int h = (int)((p / W) % H);
-    const long b = p / ((long)W * H);
+    const int b = p / ((int)W * H);
     const int Ho = H >> 1, Wo = W >> 1;
 #pragma unroll
     for (int j = 0; j < 8; ++j) dz[j] = 0.f;
@@ -530,7 +530,7 @@ __device__ __forceinline__ void load_dz(const __nv_bfloat16* __restrict__ g, con
     const int qw0 = (w & 1) ? (w >> 1) : (w >> 1) - 1, qw1 = w >> 1;
     for (int qh = max(qh0, 0); qh <= min(qh1, Ho - 1); ++qh)
       for (int qw = max(qw0, 0); qw <= min(qw1, Wo - 1); ++qw) {
-        const long q = ((b * Ho + qh) * Wo + qw) * c8 + cv;
+        const int q = ((b * Ho + qh) * Wo + qw) * c8 + cv;
         const int off = (h - 2 * qh) * 3 + (w - 2 * qw);
         const uint2 a = __ldg(reinterpret_cast<const uint2*>(arg + q * 8));
         float gq[8];
@@ -557,10 +557,10 @@ __global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : 3) bn_bwd_reduce_k(const 
   float sc[8], sh[8], mu[8], s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (MODE == 1) { load8f(bn + cv * 8, sc); load8f(bn + C + cv * 8, sh); }
   load8f(bn + 2 * C + cv * 8, mu);
-  const long p0 = (long)blockIdx.x * pix_per_block;
-  const long p1 = min(P, p0 + pix_per_block);
-  for (long p = p0 + lane; p < p1; p += 2 * lanes) {
-    const long q = p + lanes;
+  const int p0 = (int)blockIdx.x * pix_per_block;
+  const int p1 = min((int)P, p0 + pix_per_block);
+  for (int p = p0 + lane; p < p1; p += 2 * lanes) {
+    const int q = p + lanes;
     const bool has2 = q < p1;
     float yv[2][8], dz[2][8];
     unpack8(ldg16(y + (p * c8 + cv) * 8), yv[0]);
@@ -598,9 +598,9 @@ __global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : 3) bn_bwd_apply_k(const _
       dgamma[c] = bn[3 * C + c] * sums[C + c];
     }
   }
-  const long total = P * c8;
-  const long stride = (long)gridDim.x * blockDim.x;  // multiple of c8: a thread keeps its channel vector
-  const long g0 = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int total = P * c8;
+  const int stride = (int)gridDim.x * blockDim.x;  // multiple of c8: a thread keeps its channel vector
+  const int g0 = (int)blockIdx.x * blockDim.x + threadIdx.x;
   const int cv = (int)(g0 % c8);
   float sc[8], sh[8], A[8], Bc[8], Cc[8];
   {
@@ -617,8 +617,8 @@ __global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : 3) bn_bwd_apply_k(const _
       Cc[j] = -sc[j] * m1 - Bc[j] * mu[j];
     }
   }
-  for (long gi = g0; gi < total; gi += 2 * stride) {
-    const long gj = gi + stride;
+  for (int gi = g0; gi < total; gi += 2 * stride) {
+    const int gj = gi + stride;
     const bool has2 = gj < total;
     float yv[2][8], dz[2][8];
     unpack8(ldg16(y + gi * 8), yv[0]);
@@ -641,9 +641,9 @@ __global__ void __launch_bounds__(TPB, 3) pool_bwd_k(const __nv_bfloat16* __rest
                                                      __nv_bfloat16* __restrict__ dz, long P, int H, int W, int C) {
   ck::pdl_enter();
   const int c8 = C >> 3;
-  const long total = P * c8;
+  const int total = P * c8;
   float unused[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  for (long gi = (long)blockIdx.x * blockDim.x + threadIdx.x; gi < total; gi += (long)gridDim.x * blockDim.x) {
+  for (int gi = (int)blockIdx.x * blockDim.x + threadIdx.x; gi < total; gi += (int)gridDim.x * blockDim.x) {
     float v[8];
     load_dz<2>(g, arg, gi / c8, (int)(gi % c8), c8, H, W, unused, unused, unused, v);
     stg16(dz + gi * 8, pack8(v));
@@ -658,9 +658,9 @@ __global__ void __launch_bounds__(TPB) colsum_k(const __nv_bfloat16* __restrict_
   const int c8 = C >> 3, lanes = TPB / c8;
   const int cv = threadIdx.x % c8, lane = threadIdx.x / c8;
   float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  const long p0 = (long)blockIdx.x * pix_per_block;
-  const long p1 = min(P, p0 + pix_per_block);
-  for (long p = p0 + lane; p < p1; p += lanes) {
+  const int p0 = (int)blockIdx.x * pix_per_block;
+  const int p1 = min((int)P, p0 + pix_per_block);
+  for (int p = p0 + lane; p < p1; p += lanes) {
     float f[8];
     unpack8(ldg16(g + (p * c8 + cv) * 8), f);
 #pragma unroll
@@ -1110,13 +1110,13 @@ __global__ void __launch_bounds__(TPB) entry_im2col_k(const uint8_t* __restrict_
                                                       int W) {
   ck::pdl_enter();
   const int Ho = H >> 1, Wo = W >> 1;
-  const long total = (long)B * Ho * Wo * 4;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+  const int total = (int)B * Ho * Wo * 4;
+  for (int i = (int)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int)gridDim.x * blockDim.x) {
     const int q = (int)(i & 3);
-    const long p = i >> 2;
+    const int p = i >> 2;
     const int ow = (int)(p % Wo);
     const int oh = (int)((p / Wo) % Ho);
-    const long b = p / ((long)Wo * Ho);
+    const int b = p / ((int)Wo * Ho);
     float f[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -1125,7 +1125,7 @@ __global__ void __launch_bounds__(TPB) entry_im2col_k(const uint8_t* __restrict_
       const int kh = tap / 3, kw = tap - kh * 3;
       const int ih = 2 * oh + kh, iw = 2 * ow + kw;
       const bool ok = k < 27 && ih < H && iw < W;
-      f[j] = ok ? (float)__ldg(x + ((b * H + ih) * (long)W + iw) * 3 + ci) * (1.0f / 255.0f) : 0.f;
+      f[j] = ok ? (float)__ldg(x + ((b * H + ih) * (int)W + iw) * 3 + ci) * (1.0f / 255.0f) : 0.f;
     }
     stg16(col + p * 32 + q * 8, pack8(f));
   }
@@ -1149,6 +1149,9 @@ inline int ppb_for(long P, int C) {
 
 }  // namespace
 
+// the streaming kernels index with 32-bit integers (64-bit div/mod per element cost more than the memory traffic)
+#define CK_FITS32(elems) do { if ((long)(elems) >= (1L << 31)) return (int)cudaErrorInvalidValue; } while (0)
+
 extern "C" {
 
 int crackfl_entry_conv_fwd(const void* x_u8, const float* w, const float* bias, void* y, int B, int H, int W, int C,
@@ -1161,6 +1164,7 @@ int crackfl_entry_conv_fwd(const void* x_u8, const float* w, const float* bias, 
 }
 
 int crackfl_entry_im2col(const void* x_u8, void* col, int B, int H, int W, cudaStream_t st) {
+  CK_FITS32((long)B * H * W * 16);
   const long total = (long)B * (H / 2) * (W / 2) * 4;
   ck::launch(entry_im2col_k, grid_for(total), TPB, 0, st, (const uint8_t*)x_u8, (__nv_bfloat16*)col, B, H, W);
   CK_LAUNCH_CHECK();
@@ -1209,6 +1213,7 @@ int crackfl_bn_eval_prepare(const float* gamma, const float* beta, const float* 
 
 int crackfl_bn_act(const void* y, const float* bn, void* out, void* even, int B, int H, int W, int C, int relu,
                    cudaStream_t st) {
+  CK_FITS32((long)B * H * W * C);
   const long total = (long)B * H * W * (C / 8);
   ck::launch(bn_act_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)y, bn, (__nv_bfloat16*)out, (__nv_bfloat16*)even, B, H, W,
                                             C, relu, BnFin{});
@@ -1259,6 +1264,7 @@ int crackfl_dw3x3_bwd(const void* g, const void* src, const float* w, const floa
 
 int crackfl_pool_add_fwd(const void* y, const float* bn, const void* res, void* out, void* even, void* relu_out, void* arg,
                          int B, int H, int W, int C, cudaStream_t st) {
+  CK_FITS32((long)B * H * W * C);
   const long total = (long)B * (H / 2) * (W / 2) * (C / 8);
   ck::launch(pool_add_fwd_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)y, bn, (const __nv_bfloat16*)res,
                                                   (__nv_bfloat16*)out, (__nv_bfloat16*)even, (__nv_bfloat16*)relu_out,
@@ -1269,6 +1275,7 @@ int crackfl_pool_add_fwd(const void* y, const float* bn, const void* res, void* 
 
 int crackfl_dec_combine_fwd(const void* y, const float* bn, const void* rl, void* s, void* a_next, int B, int H, int W,
                             int C, int rl_up, cudaStream_t st) {
+  CK_FITS32((long)B * H * W * C * 4);
   const long total = (long)B * H * W * (C / 8);
   ck::launch(dec_combine_fwd_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)y, bn, (const __nv_bfloat16*)rl,
                                                      (__nv_bfloat16*)s, (__nv_bfloat16*)a_next, B, H, W, C, rl_up, BnFin{});
@@ -1278,6 +1285,7 @@ int crackfl_dec_combine_fwd(const void* y, const float* bn, const void* rl, void
 
 int crackfl_down2sum(const void* in, const void* mask, const void* add, void* out, int B, int Ho, int Wo, int C,
                      cudaStream_t st) {
+  CK_FITS32((long)B * Ho * Wo * C * 4);
   const long total = (long)B * Ho * Wo * (C / 8);
   ck::launch(down2sum_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)in, (const __nv_bfloat16*)mask,
                                               (const __nv_bfloat16*)add, (__nv_bfloat16*)out, B, Ho, Wo, C);
@@ -1286,6 +1294,7 @@ int crackfl_down2sum(const void* in, const void* mask, const void* add, void* ou
 }
 
 int crackfl_relu_bwd_add(const void* g, const void* x, const void* add, void* out, long numel, cudaStream_t st) {
+  CK_FITS32(numel);
   const long nvec = numel / 8;
   ck::launch(relu_bwd_add_k, grid_for(nvec), TPB, 0, st, (const __nv_bfloat16*)g, (const __nv_bfloat16*)x,
                                                  (const __nv_bfloat16*)add, (__nv_bfloat16*)out, nvec);
@@ -1295,6 +1304,7 @@ int crackfl_relu_bwd_add(const void* g, const void* x, const void* add, void* ou
 
 int crackfl_bn_bwd_reduce(const void* g, const void* arg, const void* y, const float* bn, float* sums, int B, int H, int W,
                           int C, int mode, cudaStream_t st) {
+  CK_FITS32((long)B * H * W * C);
   if (C % 8 || TPB % (C / 8)) return (int)cudaErrorInvalidValue;
   const long P = (long)B * H * W;
   const int ppb = ppb_for(P, C);
@@ -1311,6 +1321,7 @@ int crackfl_bn_bwd_reduce(const void* g, const void* arg, const void* y, const f
 
 int crackfl_bn_bwd_apply(const void* g, const void* arg, const void* y, const float* bn, const float* sums, void* dy,
                          float* dgamma, float* dbeta, int B, int H, int W, int C, int mode, cudaStream_t st) {
+  CK_FITS32((long)B * H * W * C);
   const long P = (long)B * H * W;
   const int grid = grid_for(P * (C / 8));
   const __nv_bfloat16* gp = (const __nv_bfloat16*)g;
@@ -1325,6 +1336,7 @@ int crackfl_bn_bwd_apply(const void* g, const void* arg, const void* y, const fl
 }
 
 int crackfl_colsum(const void* g, float* out, long P, int C, cudaStream_t st) {
+  CK_FITS32(P * C);
   if (C % 8 || TPB % (C / 8)) return (int)cudaErrorInvalidValue;
   const int ppb = ppb_for(P, C);
   ck::launch(colsum_k, (int)((P + ppb - 1) / ppb), TPB, 0, st, (const __nv_bfloat16*)g, out, P, C, ppb);
@@ -1388,6 +1400,7 @@ extern "C" {
 
 int crackfl_bn_act_fin(const void* y, const crackfl_bn_fin* fin, void* out, void* even, int B, int H, int W, int C, int relu,
                        cudaStream_t st) {
+  CK_FITS32((long)B * H * W * C);
   const long total = (long)B * H * W * (C / 8);
   ck::launch(bn_act_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)y, nullptr, (__nv_bfloat16*)out, (__nv_bfloat16*)even, B, H, W,
                                             C, relu, *fin);
@@ -1407,6 +1420,7 @@ int crackfl_dw3x3_fwd_fin(const void* x, const float* w, const crackfl_bn_fin* f
 
 int crackfl_pool_add_fwd_fin(const void* y, const crackfl_bn_fin* fin, const void* res, void* out, void* even, void* relu_out,
                              void* arg, int B, int H, int W, int C, cudaStream_t st) {
+  CK_FITS32((long)B * H * W * C);
   const long total = (long)B * (H / 2) * (W / 2) * (C / 8);
   ck::launch(pool_add_fwd_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)y, nullptr, (const __nv_bfloat16*)res,
                                                   (__nv_bfloat16*)out, (__nv_bfloat16*)even, (__nv_bfloat16*)relu_out,
@@ -1417,6 +1431,7 @@ int crackfl_pool_add_fwd_fin(const void* y, const crackfl_bn_fin* fin, const voi
 
 int crackfl_dec_combine_fwd_fin(const void* y, const crackfl_bn_fin* fin, const void* rl, void* s, void* a_next, int B, int H,
                                 int W, int C, int rl_up, cudaStream_t st) {
+  CK_FITS32((long)B * H * W * C * 4);
   const long total = (long)B * H * W * (C / 8);
   ck::launch(dec_combine_fwd_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)y, nullptr, (const __nv_bfloat16*)rl,
                                                      (__nv_bfloat16*)s, (__nv_bfloat16*)a_next, B, H, W, C, rl_up, *fin);
@@ -1429,6 +1444,7 @@ int crackfl_dec_combine_fwd_fin(const void* y, const crackfl_bn_fin* fin, const 
 extern "C" {
 
 int crackfl_pool_bwd(const void* g, const void* arg, void* dz, int B, int H, int W, int C, cudaStream_t st) {
+  CK_FITS32((long)B * H * W * C);
   const long P = (long)B * H * W;
   ck::launch(pool_bwd_k, grid_for(P * (C / 8)), TPB, 0, st, (const __nv_bfloat16*)g, (const uint8_t*)arg, (__nv_bfloat16*)dz, P, H, W, C);
   CK_LAUNCH_CHECK();
