@@ -74,6 +74,7 @@ class UNetEngine:
             self.train_prog = [e for e in self.train_prog if e[0] is None or not any(k in e[0].__name__ for k in skip)]
         self._graphs: Dict[str, torch.cuda.CUDAGraph] = {}
         self._side_stream = torch.cuda.Stream(self.dev)
+        self._aux_stream = torch.cuda.Stream(self.dev)
         self.launches_per_step = sum(1 for e in self.train_prog if e[0] is not None) + 2  # + adam tick + metric accumulation
 
     # ------------------------------------------------------------------ allocation
@@ -221,12 +222,13 @@ class UNetEngine:
     def _acc_ptr(self) -> int:
         return self.zero_region.data_ptr() + 4 * self.acc_off
 
-    def _gemm(self, prog, X, opname, bias, add, Y, B, H, W, stats=0):
+    def _gemm(self, prog, X, opname, bias, add, Y, B, H, W, stats=0, tag=None):
         off, N, T, K = self.ops[opname]
+        extra = (tag,) if tag else ()
         if self.conv_impl == "tc":
-            prog.append((self.lib.crackfl_conv_tc_fwd, (X, self.op_ptr(opname), bias, add, Y, stats, B, H, W, K, N, T)))
+            prog.append((self.lib.crackfl_conv_tc_fwd, (X, self.op_ptr(opname), bias, add, Y, stats, B, H, W, K, N, T)) + extra)
             return stats != 0
-        prog.append((self.lib.crackfl_conv_simt_fwd, (X, self.op_ptr(opname), bias, add, Y, B, H, W, K, N, T)))
+        prog.append((self.lib.crackfl_conv_simt_fwd, (X, self.op_ptr(opname), bias, add, Y, B, H, W, K, N, T)) + extra)
         return False
 
     def _wgrad(self, prog, X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co):
@@ -327,6 +329,9 @@ class UNetEngine:
             p = f"e{e['k']}."
             r, rw, cin, f = e["r"], e["rw"], e["cin"], e["f"]
             Pn = B * r * rw
+            # residual 1x1 stride-2 conv: a small GEMM that only depends on the block input; it runs on the auxiliary
+            # stream next to the separable-conv chain and is joined before the block tail
+            self._gemm(prog, b(xe), res.name + ".f", self.P(res.tensors[1]), 0, b(p + "rs"), B, r // 2, rw // 2, tag="aux")
             if self.dw_tma:
                 prog.append((lib.crackfl_dw3x3_tma, (b(xin), self.P(sep1.tensors[0]), 0, None, b(p + "d1"), 0, 0, 0,
                                                      B, r, rw, cin, 0, 0, 0, 0)))
@@ -349,7 +354,7 @@ class UNetEngine:
             sd = self._gemm(prog, b(p + "d2"), sep2.name + ".f", self.P(sep2.tensors[2]), 0, b(p + "y2"), B, r, rw,
                             self._zptr(bn2.name, "stats") if training else 0)
             bn(bn2, b(p + "y2"), Pn, sd, consumer_finalizes=fuse)
-            self._gemm(prog, b(xe), res.name + ".f", self.P(res.tensors[1]), 0, b(p + "rs"), B, r // 2, rw // 2)
+            prog.append((None, None, "join_aux"))
             last = e["k"] + 1 == len(self.enc)
             if fuse:
                 prog.append((lib.crackfl_pool_add_fwd_fin, (b(p + "y2"), self._fin(bn2, Pn), b(p + "rs"), b(p + "out"),
@@ -366,6 +371,8 @@ class UNetEngine:
             p = f"d{j}."
             Pn = B * r * rw
             a0 = "a0_0" if j == 0 else p + "a0"
+            lr_, lrw = (r, rw) if j == 0 else (r // 2, rw // 2)
+            self._gemm(prog, b(xprev), res.name + ".f", self.P(res.tensors[1]), 0, b(p + "rl"), B, lr_, lrw, tag="aux")
             sd = self._gemm(prog, b(a0), ct1.name + ".f", self.P(ct1.tensors[1]), 0, b(p + "y1"), B, r, rw,
                             self._zptr(bn1.name, "stats") if training else 0)
             bn(bn1, b(p + "y1"), Pn, sd, consumer_finalizes=fuse)
@@ -376,8 +383,7 @@ class UNetEngine:
             sd = self._gemm(prog, b(p + "a1"), ct2.name + ".f", self.P(ct2.tensors[1]), 0, b(p + "y2"), B, r, rw,
                             self._zptr(bn2.name, "stats") if training else 0)
             bn(bn2, b(p + "y2"), Pn, sd, consumer_finalizes=fuse)
-            lr_, lrw = (r, rw) if j == 0 else (r // 2, rw // 2)
-            self._gemm(prog, b(xprev), res.name + ".f", self.P(res.tensors[1]), 0, b(p + "rl"), B, lr_, lrw)
+            prog.append((None, None, "join_aux"))
             last = j + 1 == len(self.dec)
             if fuse:
                 prog.append((lib.crackfl_dec_combine_fwd_fin, (b(p + "y2"), self._fin(bn2, Pn), b(p + "rl"), b(p + "s"),
@@ -416,6 +422,8 @@ class UNetEngine:
                 drl = p + "drl"
             else:
                 drl = p + "ds"
+            # residual 1x1 conv (at low resolution): input gradient on the auxiliary stream, joined before the block tail
+            self._gemm(prog, b(drl), res.name + ".d", 0, 0, b(p + "T"), B, lr_, lrw, tag="aux")
             # BN2 (no ReLU after it)
             prog.append((lib.crackfl_bn_bwd_reduce, (b(p + "ds"), 0, b(p + "y2"), self._bnptr(bn2.name),
                                                      self._zptr(bn2.name, "sums"), B, r, rw, f, 0)))
@@ -436,10 +444,9 @@ class UNetEngine:
             a0 = "a0_0" if j == 0 else p + "a0"
             self._gemm(prog, b(p + "dy1"), ct1.name + ".d", 0, 0, b(p + "da0"), B, r, rw)
             self._wgrad(prog, b(p + "dy1"), b(a0), self.G(ct1.tensors[0]), B, r, rw, f, cin, 9, f * cin, cin, 1)
-            # residual 1x1 conv (at low resolution)
-            self._gemm(prog, b(drl), res.name + ".d", 0, 0, b(p + "T"), B, lr_, lrw)
             self._wgrad(prog, b(src_res), b(drl), self.G(res.tensors[0]), B, lr_, lrw, cin, f, 1, 0, f, 1)
             prog.append((lib.crackfl_colsum, (b(drl), self.G(res.tensors[1]), B * lr_ * lrw, f), "side"))
+            prog.append((None, None, "join_aux"))
             if j > 0:
                 prog.append((lib.crackfl_down2sum, (b(p + "da0"), b(f"d{j - 1}.s"), b(p + "T"), b(f"d{j - 1}.ds"),
                                                     B, lr_, lrw, cin)))
@@ -455,7 +462,7 @@ class UNetEngine:
             xe = "x0e" if k == 0 else f"e{k - 1}.oute"
             r2, rw2 = r // 2, rw // 2
             # residual 1x1 s2 conv
-            self._gemm(prog, b(dx_next), res.name + ".d", 0, 0, b(p + "Te"), B, r2, rw2)
+            self._gemm(prog, b(dx_next), res.name + ".d", 0, 0, b(p + "Te"), B, r2, rw2, tag="aux")
             self._wgrad(prog, b(xe), b(dx_next), self.G(res.tensors[0]), B, r2, rw2, cin, f, 1, 0, f, 1)
             prog.append((lib.crackfl_colsum, (b(dx_next), self.G(res.tensors[1]), B * r2 * rw2, f), "side"))
             # max-pool + BN2
@@ -482,6 +489,7 @@ class UNetEngine:
             self._wgrad(prog, b(p + "d1"), b(p + "dy1"), self.G(sep1.tensors[1]), B, r, rw, cin, f, 1, 0, f, 1)
             # depthwise 1 (input = relu(x_k)); adds the residual-path gradient on the even pixels
             out = "dz0" if k == 0 else p + "dx"
+            prog.append((None, None, "join_aux"))
             self._dw_bwd(prog, b(p + "dd1"), b(xin), self.P(sep1.tensors[0]), 0, b(p + "Te"), b(out),
                          self.G(sep1.tensors[0]), B, r, rw, cin, 0, 2 if k == 0 else 1)
             dx_next = out
@@ -512,37 +520,42 @@ class UNetEngine:
     def _run(self, prog):
         """Execute a schedule.  Entries tagged "side" (weight / bias gradients: nothing downstream but Adam reads
         them) are forked onto a second stream after the main-stream work issued so far, so they overlap with the
-        dgrad chain; "join" makes the main stream wait for all of them.  Works eagerly and under graph capture."""
+        dgrad chain; "join" makes the main stream wait for all of them.  Entries tagged "aux" (the small residual-path
+        GEMMs) fork onto a third stream the same way and are joined by the next "join_aux" marker, placed before their
+        consumer.  Works eagerly and under graph capture."""
         main = torch.cuda.current_stream(self.dev)
         st = main.cuda_stream
-        side = None
-        forked = False
+        streams = {"side": self._side_stream, "aux": self._aux_stream}
+        forked = {"side": False, "aux": False}
+
+        def join(name):
+            if forked[name]:
+                ev = torch.cuda.Event()
+                ev.record(streams[name])
+                main.wait_event(ev)
+                forked[name] = False
+
         for entry in prog:
             fn, args = entry[0], entry[1]
             tag = entry[2] if len(entry) > 2 else None
             if tag == "join":
-                if forked:
-                    ev = torch.cuda.Event()
-                    ev.record(side)
-                    main.wait_event(ev)
-                    forked = False
+                join("side")
                 continue
-            if tag == "side" and self.side_streams:
-                if side is None:
-                    side = self._side_stream
+            if tag == "join_aux":
+                join("aux")
+                continue
+            if tag in streams and self.side_streams:
                 ev = torch.cuda.Event()
                 ev.record(main)
-                side.wait_event(ev)
-                rc = fn(*args, side.cuda_stream)
-                forked = True
+                streams[tag].wait_event(ev)
+                rc = fn(*args, streams[tag].cuda_stream)
+                forked[tag] = True
             else:
                 rc = fn(*args, st)
             if rc != 0:
                 raise L.KernelError(f"{fn.__name__} failed with cudaError {rc}")
-        if forked:
-            ev = torch.cuda.Event()
-            ev.record(side)
-            main.wait_event(ev)
+        join("side")
+        join("aux")
 
     def _step_body(self, prog, accumulate: bool):
         self.zero_region.zero_()
