@@ -307,17 +307,20 @@ class UNetEngine:
             else:
                 self._bn_eval(prog, bnl)
 
+        # bf16 GEMM operands of this step's weights: next to the im2col / entry kernels on the auxiliary stream
         prog.append((lib.crackfl_weight_prep, (self.arena.data_ptr(), self.ops_buf.data_ptr(), self.desc_dev.data_ptr(),
-                                               self.num_desc)))
+                                               self.num_desc), "aux"))
         # entry
         r, rw, c0 = self.H // 2, self.W // 2, self.spec.entry
         if self.entry_tc:
             prog.append((lib.crackfl_entry_im2col, (b("x_u8"), b("x0col"), B, self.H, self.W)))
+            prog.append((None, None, "join_aux"))
             sd = self._gemm(prog, b("x0col"), "conv0.f", self.P(conv0.tensors[1]), 0, b("y0"), B, r, rw,
                             self._zptr(bn0.name, "stats") if training else 0)
         else:
             prog.append((lib.crackfl_entry_conv_fwd, (b("x_u8"), self.P(conv0.tensors[0]), self.P(conv0.tensors[1]), b("y0"),
                                                       B, self.H, self.W, c0)))
+            prog.append((None, None, "join_aux"))
             sd = False
         bn(bn0, b("y0"), B * r * rw, sd, consumer_finalizes=fuse)
         if fuse:

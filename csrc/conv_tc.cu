@@ -472,9 +472,16 @@ struct ConvArgs3 {
   int n_tiles_m, n_tiles_n;
   uint32_t layout, sbo;
   int base_off;              // set the descriptor's base_offset field from the start address
+  int astages;               // halo-tile ring depth (2..4)
+  int resident;              // all 9 * Cin/kc weight tiles stay in shared memory for the CTA's lifetime (stages == that count)
+  uint32_t a_stage, a_bytes; // halo stage pitch (1024-aligned) / payload bytes (180 rows of kc channels)
   TileGeom g;
 };
 
+// "resident" mode (small layers: 9 * Cin * N * 2 bytes <= ~80 KB, one n-tile): the weight tiles are loaded ONCE per CTA
+// onto a single barrier; per tile the producer only streams halo tiles and the issuing thread fires its 9 * kc/16 MMAs
+// back to back (no per-tap barrier round trip, no re-streaming of the weights from L2 for every 128-pixel tile, which
+// for N = 32 was more traffic than the activations).  kc = 32 (Cin = 32) uses the SWIZZLE_64B flavour of the same trick.
 __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __grid_constant__ CUtensorMap tmA,
                                                         const __grid_constant__ CUtensorMap tmB,
                                                         const __grid_constant__ CUtensorMap tmY, const ConvArgs3 a) {
@@ -482,19 +489,20 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   // A ring: 2 halo tiles of (TH+2) x (TW+2) = 18 x 10 pixels x 64 channels (23040 B, padded to 23552);
   // B ring: a.stages weight tiles [BN][64] (one per (chunk, tap)); then 2 output staging buffers.
-  constexpr uint32_t HALO_W = 10u, HALO_ROWS = 180u, A_STAGE = 23552u, A_BYTES = HALO_ROWS * 128u;
-  const uint32_t b_bytes = (uint32_t)a.BN * 64u * 2u;
-  const uint32_t bring = base + 2u * A_STAGE;
+  constexpr uint32_t HALO_W = 10u;
+  const uint32_t A_STAGE = a.a_stage, A_BYTES = a.a_bytes, row_b = (uint32_t)a.kc * 2u;
+  const uint32_t b_bytes = (uint32_t)a.BN * row_b;
+  const uint32_t bring = base + (uint32_t)a.astages * A_STAGE;
   const uint32_t out_bytes = 128u * (uint32_t)a.BN * 2u;
   const uint32_t out0 = bring + a.stages * b_bytes;
   const uint32_t bar_base = out0 + 2u * out_bytes;
-  const uint32_t fullA0 = bar_base, emptyA0 = bar_base + 16u;
-  const uint32_t full0 = bar_base + 32u, empty0 = full0 + 8u * a.stages;
+  const uint32_t fullA0 = bar_base, emptyA0 = bar_base + 32u;
+  const uint32_t full0 = bar_base + 64u, empty0 = full0 + 8u * a.stages;
   const uint32_t tfull0 = empty0 + 8u * a.stages, tempty0 = tfull0 + 16u;
   const uint32_t tptr = tempty0 + 16u;
   const uint32_t stat_smem = tptr + 16u;  // EPI_WARPS x 2 x 128 floats
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int kchunks = a.Cin / 64;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
+  const int kchunks = a.Cin / a.kc;
   const int total_tiles = a.n_tiles_m * a.n_tiles_n;
   const uint32_t ncols = (uint32_t)(2 * a.BN < 32 ? 32 : 2 * a.BN);
 
@@ -503,9 +511,11 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
       mbar_init(full0 + 8u * s, 1);
       mbar_init(empty0 + 8u * s, 1);
     }
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < a.astages; ++s) {
       mbar_init(fullA0 + 8u * s, 1);
       mbar_init(emptyA0 + 8u * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
       mbar_init(tfull0 + 8u * s, 1);
       mbar_init(tempty0 + 8u * s, EPI_WARPS);  // one arrival per epilogue warp
     }
@@ -523,61 +533,92 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tptr));
 
   if (warp == 0) {
-    if (lane == 0) {
-      uint32_t ia = 0, ib = 0;  // ring positions: halo tiles / weight tiles
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        int tm_ = tile % a.n_tiles_m;
-        const int n0 = (tile / a.n_tiles_m) * a.BN;
-        const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
-        const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
-        const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
-        for (int c = 0; c < kchunks; ++c, ++ia) {
-          const uint32_t sa = ia & 1u, pha = (ia >> 1) & 1u;
-          mbar_wait(emptyA0 + 8u * sa, pha ^ 1u);
+    // ---- producer: all lanes walk the schedule (uniform control flow), one elected lane issues
+    uint32_t ia = 0, ib = 0;  // ring positions: halo tiles / weight tiles
+    if (a.resident && (int)blockIdx.x < total_tiles) {
+      if (elect_one()) {
+        mbar_expect_tx(full0, (uint32_t)a.stages * b_bytes);
+        for (int c = 0; c < kchunks; ++c)
+          for (int t = 0; t < 9; ++t)
+            tma_load_2d(bring + (uint32_t)(c * 9 + t) * b_bytes, &tmB, full0, t * a.Cin + c * a.kc, 0);
+      }
+      __syncwarp();
+    }
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      int tm_ = tile % a.n_tiles_m;
+      const int n0 = (tile / a.n_tiles_m) * a.BN;
+      const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
+      const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
+      const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
+      for (int c = 0; c < kchunks; ++c, ++ia) {
+        const uint32_t sa = ia % (uint32_t)a.astages, pha = (ia / (uint32_t)a.astages) & 1u;
+        mbar_wait(emptyA0 + 8u * sa, pha ^ 1u);
+        if (elect_one()) {
           mbar_expect_tx(fullA0 + 8u * sa, A_BYTES);
-          tma_load_4d(base + sa * A_STAGE, &tmA, fullA0 + 8u * sa, c * 64, w0 - 1, h0 - 1, b0);  // halo: zero fill = padding
-          for (int t = 0; t < 9; ++t, ++ib) {
-            const uint32_t s = ib % a.stages, ph = (ib / a.stages) & 1u;
-            mbar_wait(empty0 + 8u * s, ph ^ 1u);
+          tma_load_4d(base + sa * A_STAGE, &tmA, fullA0 + 8u * sa, c * a.kc, w0 - 1, h0 - 1, b0);  // halo: zero fill = padding
+        }
+        __syncwarp();
+        if (a.resident) continue;
+        for (int t = 0; t < 9; ++t, ++ib) {
+          const uint32_t s = ib % a.stages, ph = (ib / a.stages) & 1u;
+          mbar_wait(empty0 + 8u * s, ph ^ 1u);
+          if (elect_one()) {
             mbar_expect_tx(full0 + 8u * s, b_bytes);
-            tma_load_2d(bring + s * b_bytes, &tmB, full0 + 8u * s, t * a.Cin + c * 64, n0);
+            tma_load_2d(bring + s * b_bytes, &tmB, full0 + 8u * s, t * a.Cin + c * a.kc, n0);
           }
+          __syncwarp();
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc(128, a.BN, 0, 0);
-      uint32_t ia = 0, ib = 0, tcount = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
-        const uint32_t as = tcount & 1u, aph = (tcount >> 1) & 1u;
-        mbar_wait(tempty0 + 8u * as, aph ^ 1u);
+    // ---- MMA issue: uniform control flow, descriptors in {lo, hi} words, one elected lane fires the instructions
+    const uint32_t idesc = make_idesc(128, a.BN, 0, 0);
+    const uint32_t ahi = desc_hi(HALO_W * row_b, a.layout), bhi = desc_hi(a.sbo, a.layout);
+    const bool k64 = a.kc == 64;
+    uint32_t ia = 0, ib = 0, tcount = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+      const uint32_t as = tcount & 1u, aph = (tcount >> 1) & 1u;
+      mbar_wait(tempty0 + 8u * as, aph ^ 1u);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + as * (uint32_t)a.BN;
+      if (a.resident && tcount == 0) {
+        mbar_wait(full0, 0u);  // the resident weight tiles have landed
         tc_fence_after();
-        const uint32_t tacc = tmem_base + as * (uint32_t)a.BN;
-        for (int c = 0; c < kchunks; ++c, ++ia) {
-          const uint32_t sa = ia & 1u, pha = (ia >> 1) & 1u;
-          mbar_wait(fullA0 + 8u * sa, pha);
-          tc_fence_after();
-          const uint32_t halo = base + sa * A_STAGE;
-          for (int t = 0; t < 9; ++t, ++ib) {
-            const uint32_t s = ib % a.stages, ph = (ib / a.stages) & 1u;
+      }
+      for (int c = 0; c < kchunks; ++c, ++ia) {
+        const uint32_t sa = ia % (uint32_t)a.astages, pha = (ia / (uint32_t)a.astages) & 1u;
+        mbar_wait(fullA0 + 8u * sa, pha);
+        tc_fence_after();
+        const uint32_t halo = base + sa * A_STAGE;
+#pragma unroll
+        for (int t = 0; t < 9; ++t, ++ib) {
+          const uint32_t s = a.resident ? (uint32_t)(c * 9 + t) : ib % a.stages, ph = (ib / a.stages) & 1u;
+          if (!a.resident) {
             mbar_wait(full0 + 8u * s, ph);
             tc_fence_after();
-            // tap (kh,kw): output pixel (th,tw) reads halo pixel (th+kh, tw+kw).  One 8-row swizzle group = the 8
-            // pixels of one tile row, groups HALO_W*128 bytes apart: the shifted window is still a canonical
-            // K-major SW128 operand, it just starts (kh*HALO_W + kw) rows into the halo tile.
-            const uint32_t astart = halo + (uint32_t)((t / 3) * HALO_W + (t % 3)) * 128u;
-            uint64_t ad = make_desc(astart, 16, HALO_W * 128u, 2u);
-            if (a.base_off) ad |= (uint64_t)((astart >> 7) & 7u) << 49;
-            const uint64_t bd = make_desc(bring + s * b_bytes, 16, 1024u, 2u);
-            for (int k = 0; k < 4; ++k)
-              umma_f16(tacc, ad + 2u * k, bd + 2u * k, idesc, (c > 0 || t > 0 || k > 0) ? 1u : 0u);
-            umma_commit(empty0 + 8u * s);
           }
-          umma_commit(emptyA0 + 8u * sa);
+          // tap (kh,kw): output pixel (th,tw) reads halo pixel (th+kh, tw+kw).  One 8-row swizzle group = the 8
+          // pixels of one tile row, groups HALO_W * row_b bytes apart: the shifted window is still a canonical
+          // K-major swizzled operand, it just starts (kh*HALO_W + kw) rows into the halo tile.
+          const uint32_t alo = desc_lo(halo + (uint32_t)((t / 3) * HALO_W + (t % 3)) * row_b, 16);
+          const uint32_t blo = desc_lo(bring + s * b_bytes, 16);
+          const uint32_t first = (c > 0 || t > 0) ? 1u : 0u;
+          if (elect_one()) {
+            umma_f16_w(tacc, alo, ahi, blo, bhi, idesc, first);
+            umma_f16_w(tacc, alo + 2u, ahi, blo + 2u, bhi, idesc, 1u);
+            if (k64) {
+              umma_f16_w(tacc, alo + 4u, ahi, blo + 4u, bhi, idesc, 1u);
+              umma_f16_w(tacc, alo + 6u, ahi, blo + 6u, bhi, idesc, 1u);
+            }
+            if (!a.resident) umma_commit(empty0 + 8u * s);
+          }
+          __syncwarp();
         }
-        umma_commit(tfull0 + 8u * as);
+        if (elect_one()) umma_commit(emptyA0 + 8u * sa);
+        __syncwarp();
       }
+      if (elect_one()) umma_commit(tfull0 + 8u * as);
+      __syncwarp();
     }
   } else {
     const int q = warp & 3;          // TMEM lane quarter this warp may read
@@ -1067,41 +1108,79 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
   // measured (profiles/conv_bench_r1.json): the halo kernel wins when the N tile is 128 wide (d0/d1 and the 64->128
   // dgrads); with narrower N tiles the per-tap barrier round trips of its single producer/issuer threads dominate and
   // the two-CTA-per-SM v2 kernel is faster.  CRACKFL_TC_HALO=2 forces it for every eligible layer.
-  const bool halo_ok = taps == 9 && Cin % 64 == 0 && H >= 16 && W >= 8;
-  if (halo_ok && (use_halo == 2 || (use_halo == 1 && N >= 128))) {
+  const int kc3 = (Cin % 64 == 0) ? 64 : 32;
+  const int BN3 = N > 128 ? 128 : N;
+  const bool halo_ok = taps == 9 && Cin % kc3 == 0 && H >= 16 && W >= 8;
+  // resident-weight mode: every (chunk, tap) weight tile of the layer fits next to the halo ring
+  const uint32_t wbytes = 9u * (uint32_t)Cin * (uint32_t)BN3 * 2u;
+  static int use_res = -1;
+  if (use_res < 0) { const char* e = getenv("CRACKFL_TC_RESIDENT"); use_res = e ? atoi(e) : 1; }
+  const bool resident = halo_ok && use_res && N == BN3 && wbytes <= 81920u;
+  if (halo_ok && (use_halo == 2 || (use_halo == 1 && (N >= 128 || resident)))) {
+    if (kc3 == 32 && !resident) goto v2_path;  // the streaming variant is only set up for 64-channel chunks
     ConvArgs3 a;
     a.bias = bias; a.add = (const __nv_bfloat16*)add; a.stats = stats;
     a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.N = N; a.taps = taps;
-    a.BN = N > 128 ? 128 : N;
+    a.BN = BN3;
     if (N % a.BN) return (int)cudaErrorInvalidValue;
-    a.kc = 64; a.layout = 2u; a.sbo = 1024u;
+    a.kc = kc3; a.layout = kc3 == 64 ? 2u : 4u; a.sbo = kc3 == 64 ? 1024u : 512u;
     a.sub_w = (a.BN % 64 == 0) ? 64 : 32;
     a.base_off = halo_base_off;
+    a.resident = resident ? 1 : 0;
+    a.a_bytes = 180u * (uint32_t)kc3 * 2u;
+    a.a_stage = (a.a_bytes + 1023u) & ~1023u;
     a.g.TW = 8; a.g.TH = 16; a.g.TB = 1;
     a.g.tiles_w = (W + 7) / 8; a.g.tiles_h = (H + 15) / 16; a.g.tiles_b = B;
     a.n_tiles_m = a.g.tiles_w * a.g.tiles_h * a.g.tiles_b;
     a.n_tiles_n = N / a.BN;
-    const uint32_t b_bytes = (uint32_t)a.BN * 128u;
+    const uint32_t b_bytes = (uint32_t)a.BN * (uint32_t)kc3 * 2u;
     const uint32_t out_bytes = 2u * 128u * (uint32_t)a.BN * 2u;
-    // two CTAs per SM when >= 3 weight stages still fit in ~104 KB (small BN), else one CTA with a deep ring
+    const uint32_t fixed = out_bytes + 10240u;  // staging + barriers + statistics scratch + alignment slack
     int per_sm = 1;
     int stages = 0;
-    if (2u * 23552u + out_bytes + 3u * b_bytes + 10240u <= 106496u) {
-      per_sm = 2;
-      stages = (int)((106496u - 10240u - 2u * 23552u - out_bytes) / b_bytes);
+    if (resident) {
+      stages = 9 * (Cin / kc3);
+      // two CTAs per SM (<= 113 KB each) when the weights plus >= 2 halo stages fit, else one CTA with a deeper ring
+      const uint32_t lim2 = 114688u, lim1 = 220u * 1024u;
+      if (wbytes + fixed + 2u * a.a_stage <= lim2) {
+        per_sm = 2;
+        a.astages = (int)((lim2 - wbytes - fixed) / a.a_stage);
+      } else {
+        a.astages = (int)((lim1 - wbytes - fixed) / a.a_stage);
+      }
+      if (a.astages > 4) a.astages = 4;
+      {
+        static int dbg_persm = -1, dbg_ast = -1;  // tuning knobs
+        if (dbg_persm < 0) { const char* e = getenv("CRACKFL_V3_PERSM"); dbg_persm = e ? atoi(e) : 0; }
+        if (dbg_ast < 0) { const char* e = getenv("CRACKFL_V3_ASTAGES"); dbg_ast = e ? atoi(e) : 0; }
+        if (dbg_persm == 1 && per_sm == 2) {
+          per_sm = 1;
+          a.astages = (int)((lim1 - wbytes - fixed) / a.a_stage);
+          if (a.astages > 4) a.astages = 4;
+        }
+        if (dbg_ast >= 2 && dbg_ast <= a.astages) a.astages = dbg_ast;
+      }
+      if (a.astages < 2) return (int)cudaErrorInvalidValue;
     } else {
-      stages = (int)((200704u - 2u * 23552u - out_bytes) / b_bytes);
+      a.astages = 2;
+      // two CTAs per SM when >= 3 weight stages still fit in ~104 KB (small BN), else one CTA with a deep ring
+      if (2u * a.a_stage + out_bytes + 3u * b_bytes + 10240u <= 106496u) {
+        per_sm = 2;
+        stages = (int)((106496u - 10240u - 2u * a.a_stage - out_bytes) / b_bytes);
+      } else {
+        stages = (int)((200704u - 2u * a.a_stage - out_bytes) / b_bytes);
+      }
+      if (stages > 9) stages = 9;
+      if (stages < 2) stages = 2;
     }
-    if (stages > 9) stages = 9;
-    if (stages < 2) stages = 2;
     a.stages = stages;
-    const size_t smem = 2 * 23552 + (size_t)stages * b_bytes + out_bytes + 1024 + 512 + 8192;
+    const size_t smem = (size_t)a.astages * a.a_stage + (size_t)stages * b_bytes + out_bytes + 1024 + 512 + 8192;
     CUtensorMap tmA, tmB, tmY;
-    const int dA[4] = {Cin, W, H, B}, bA[4] = {64, 10, 18, 1};
-    int rc = get_map(X, 4, dA, bA, 128, &tmA);
+    const int dA[4] = {Cin, W, H, B}, bA[4] = {kc3, 10, 18, 1};
+    int rc = get_map(X, 4, dA, bA, kc3 * 2, &tmA);
     if (rc) return rc;
-    const int dB[2] = {taps * Cin, N}, bB[2] = {64, a.BN};
-    rc = get_map(Wk, 2, dB, bB, 128, &tmB);
+    const int dB[2] = {taps * Cin, N}, bB[2] = {kc3, a.BN};
+    rc = get_map(Wk, 2, dB, bB, kc3 * 2, &tmB);
     if (rc) return rc;
     const int dY[4] = {N, W, H, B}, bY[4] = {a.sub_w, 8, 16, 1};
     rc = get_map(Y, 4, dY, bY, a.sub_w * 2, &tmY);
@@ -1123,6 +1202,7 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
     CK_LAUNCH_CHECK();
     return 0;
   }
+v2_path:
   ConvArgs2 a;
   a.bias = bias; a.add = (const __nv_bfloat16*)add; a.stats = stats;
   a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.N = N; a.taps = taps;
