@@ -260,7 +260,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
   const uint32_t tfull0 = bar_base + 16u * a.stages, tempty0 = tfull0 + 16u;
   const uint32_t tptr = tempty0 + 16u;
   const uint32_t stat_smem = tptr + 16u;  // EPI_WARPS x 2 x 128 floats
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   const int kchunks = a.Cin / a.kc;
   const int iters = a.taps * kchunks;
   const int total_tiles = a.n_tiles_m * a.n_tiles_n;
@@ -289,48 +289,60 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tptr));
 
   if (warp == 0) {
-    if (lane == 0) {
-      uint32_t it_g = 0;  // global k-iteration counter across tiles (ring position)
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        int tm_ = tile % a.n_tiles_m;
-        const int n0 = (tile / a.n_tiles_m) * a.BN;
-        const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
-        const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
-        const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
-        for (int it = 0; it < iters; ++it, ++it_g) {
-          const uint32_t s = it_g % a.stages, ph = (it_g / a.stages) & 1u;
-          mbar_wait(empty0 + 8u * s, ph ^ 1u);
-          const int t = it / kchunks, c = it % kchunks;
-          const int dh = a.taps == 9 ? t / 3 - 1 : 0, dw = a.taps == 9 ? t % 3 - 1 : 0;
-          const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
+    // ---- producer: uniform control flow, one elected lane issues (see tc_common.cuh)
+    uint32_t it_g = 0;  // global k-iteration counter across tiles (ring position)
+    uint32_t s = 0, ph = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      int tm_ = tile % a.n_tiles_m;
+      const int n0 = (tile / a.n_tiles_m) * a.BN;
+      const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
+      const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
+      const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
+      int t = 0, c = 0;
+      for (int it = 0; it < iters; ++it, ++it_g) {
+        mbar_wait(empty0 + 8u * s, ph ^ 1u);
+        const int dh = a.taps == 9 ? t / 3 - 1 : 0, dw = a.taps == 9 ? t % 3 - 1 : 0;
+        const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
+        if (elect_one()) {
           mbar_expect_tx(full0 + 8u * s, stage_bytes);
           tma_load_4d(sa, &tmA, full0 + 8u * s, c * a.kc, w0 + dw, h0 + dh, b0);
           tma_load_2d(sb, &tmB, full0 + 8u * s, t * a.Cin + c * a.kc, n0);
         }
+        __syncwarp();
+        if (++c == kchunks) { c = 0; ++t; }
+        if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1u; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc(128, a.BN, 0, 0);
-      uint32_t it_g = 0, tcount = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
-        const uint32_t as = tcount & 1u, aph = (tcount >> 1) & 1u;
-        mbar_wait(tempty0 + 8u * as, aph ^ 1u);  // epilogue has drained this accumulator stage
+    // ---- MMA issue: uniform control flow, {lo, hi} descriptor words, one elected lane fires the instructions
+    const uint32_t idesc = make_idesc(128, a.BN, 0, 0);
+    const uint32_t dhi = desc_hi(a.sbo, a.layout);
+    const bool k64 = a.kc == 64;
+    uint32_t tcount = 0, s = 0, ph = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+      const uint32_t as = tcount & 1u, aph = (tcount >> 1) & 1u;
+      mbar_wait(tempty0 + 8u * as, aph ^ 1u);  // epilogue has drained this accumulator stage
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + as * (uint32_t)a.BN;
+      for (int it = 0; it < iters; ++it) {
+        mbar_wait(full0 + 8u * s, ph);
         tc_fence_after();
-        const uint32_t tacc = tmem_base + as * (uint32_t)a.BN;
-        for (int it = 0; it < iters; ++it, ++it_g) {
-          const uint32_t s = it_g % a.stages, ph = (it_g / a.stages) & 1u;
-          mbar_wait(full0 + 8u * s, ph);
-          tc_fence_after();
-          const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
-          const uint64_t ad = make_desc(sa, 16, a.sbo, a.layout);
-          const uint64_t bd = make_desc(sb, 16, a.sbo, a.layout);
-          for (int k = 0; k < a.kc / 16; ++k)
-            umma_f16(tacc, ad + 2u * k, bd + 2u * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+        const uint32_t sa = base + s * stage_bytes;
+        const uint32_t alo = desc_lo(sa, 16), blo = desc_lo(sa + a_bytes, 16);
+        if (elect_one()) {
+          umma_f16_w(tacc, alo, dhi, blo, dhi, idesc, it > 0 ? 1u : 0u);
+          umma_f16_w(tacc, alo + 2u, dhi, blo + 2u, dhi, idesc, 1u);
+          if (k64) {
+            umma_f16_w(tacc, alo + 4u, dhi, blo + 4u, dhi, idesc, 1u);
+            umma_f16_w(tacc, alo + 6u, dhi, blo + 6u, dhi, idesc, 1u);
+          }
           umma_commit(empty0 + 8u * s);
         }
-        umma_commit(tfull0 + 8u * as);
+        __syncwarp();
+        if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1u; }
       }
+      if (elect_one()) umma_commit(tfull0 + 8u * as);
+      __syncwarp();
     }
   } else {
     const int q = warp & 3;          // TMEM lane quarter this warp may read
@@ -767,7 +779,7 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
   const uint32_t bar_base = base + a.stages * stage_bytes;
   const uint32_t full0 = bar_base, empty0 = bar_base + 8u * a.stages, tfull = bar_base + 16u * a.stages;
   const uint32_t tptr = tfull + 8u;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   const int group = blockIdx.x;
   const int n0 = blockIdx.y * a.BN;
   const int tile_begin = blockIdx.z * a.tiles_per_split;
@@ -806,16 +818,16 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
   }
   if (iters > 0) {
     if (warp == 0) {
-      if (lane == 0) {
-        for (int it = 0; it < iters; ++it) {
-          const int s = it % a.stages;
-          const uint32_t ph = (uint32_t)(it / a.stages) & 1u;
-          mbar_wait(empty0 + 8u * s, ph ^ 1u);
-          int tile = tile_begin + it;
-          const int tw_i = tile % a.g.tiles_w; tile /= a.g.tiles_w;
-          const int th_i = tile % a.g.tiles_h; tile /= a.g.tiles_h;
-          const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tile * a.g.TB;
-          const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
+      // ---- producer: uniform control flow, one elected lane issues (see tc_common.cuh)
+      uint32_t s = 0, ph = 0;
+      for (int it = 0; it < iters; ++it) {
+        mbar_wait(empty0 + 8u * s, ph ^ 1u);
+        int tile = tile_begin + it;
+        const int tw_i = tile % a.g.tiles_w; tile /= a.g.tiles_w;
+        const int th_i = tile % a.g.tiles_h; tile /= a.g.tiles_h;
+        const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tile * a.g.TB;
+        const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
+        if (elect_one()) {
           mbar_expect_tx(full0 + 8u * s, (uint32_t)nload * ablk_bytes + b_bytes);
           for (int m = 0; m < nload; ++m) {
             const int blk = min(group * a.mblk + m, a.total_blocks - 1);
@@ -826,25 +838,31 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
           for (int nb = 0; nb < a.nblk; ++nb)
             tma_load_4d(sb + nb * bblk_bytes, &tmDY, full0 + 8u * s, n0 + nb * a.nw, w0, h0, b0);
         }
+        __syncwarp();
+        if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1u; }
       }
     } else if (warp == 1) {
-      if (lane == 0) {
-        const uint32_t idesc = make_idesc(128, a.BN, 1, 1);
-        for (int it = 0; it < iters; ++it) {
-          const int s = it % a.stages;
-          const uint32_t ph = (uint32_t)(it / a.stages) & 1u;
-          mbar_wait(full0 + 8u * s, ph);
-          tc_fence_after();
-          const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
-          for (int k = 0; k < 8; ++k) {  // 16 pixels (K) per MMA = 16 smem rows
-            const uint64_t ad = make_desc(sa + k * 16u * a.cw * 2u, lboA, a.sboA, a.layoutA);
-            const uint64_t bd = make_desc(sb + k * 16u * a.nw * 2u, bblk_bytes, a.sboB, a.layoutB);
-            umma_f16(tmem_base, ad, bd, idesc, (it > 0 || k > 0) ? 1u : 0u);
-          }
+      // ---- MMA issue: uniform control flow, {lo, hi} descriptor words, one elected lane fires the instructions
+      const uint32_t idesc = make_idesc(128, a.BN, 1, 1);
+      const uint32_t ahi = desc_hi(a.sboA, a.layoutA), bhi = desc_hi(a.sboB, a.layoutB);
+      const uint32_t astep = (uint32_t)(16 * a.cw * 2) >> 4, bstep = (uint32_t)(16 * a.nw * 2) >> 4;  // 16 pixels (K) per MMA
+      uint32_t s = 0, ph = 0;
+      for (int it = 0; it < iters; ++it) {
+        mbar_wait(full0 + 8u * s, ph);
+        tc_fence_after();
+        const uint32_t sa = base + s * stage_bytes;
+        const uint32_t alo = desc_lo(sa, lboA), blo = desc_lo(sa + a_bytes, bblk_bytes);
+        if (elect_one()) {
+          umma_f16_w(tmem_base, alo, ahi, blo, bhi, idesc, it > 0 ? 1u : 0u);
+#pragma unroll
+          for (uint32_t k = 1; k < 8; ++k) umma_f16_w(tmem_base, alo + k * astep, ahi, blo + k * bstep, bhi, idesc, 1u);
           umma_commit(empty0 + 8u * s);
         }
-        umma_commit(tfull);
+        __syncwarp();
+        if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1u; }
       }
+      if (elect_one()) umma_commit(tfull);
+      __syncwarp();
     } else {
       const int q = warp & 3;
       const int r = q * 32 + lane;  // accumulator row = (block m, channel within block)
@@ -1109,7 +1127,14 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
   // dgrads); with narrower N tiles the per-tap barrier round trips of its single producer/issuer threads dominate and
   // the two-CTA-per-SM v2 kernel is faster.  CRACKFL_TC_HALO=2 forces it for every eligible layer.
   const int kc3 = (Cin % 64 == 0) ? 64 : 32;
-  const int BN3 = N > 128 ? 128 : N;
+  int BN3 = N > 128 ? 128 : N;
+  {
+    // tuning knob.  Measured: 64-wide n-tiles for the small-M layers (fewer tiles than SMs at 128) do not help (d0 23 ->
+    // 22 us) or hurt (d1 24 -> 33 us): those layers are bound by the L2 -> shared-memory weight stream, not by the MMA chain
+    static int dbg_bn = -1;
+    if (dbg_bn < 0) { const char* e = getenv("CRACKFL_V3_BN"); dbg_bn = e ? atoi(e) : 0; }
+    if (dbg_bn > 0 && N % dbg_bn == 0 && dbg_bn <= BN3) BN3 = dbg_bn;
+  }
   const bool halo_ok = taps == 9 && Cin % kc3 == 0 && H >= 16 && W >= 8;
   // resident-weight mode: every (chunk, tap) weight tile of the layer fits next to the halo ring
   const uint32_t wbytes = 9u * (uint32_t)Cin * (uint32_t)BN3 * 2u;
