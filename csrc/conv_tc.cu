@@ -357,23 +357,28 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
     // BN statistics are accumulated per CTA across all its tiles of one n-tile (registers: lane <-> column) and
     // flushed with 2*BN atomics per CTA instead of 8*BN per tile: the per-tile version serialised thousands of
     // same-address atomics in L2 and doubled the kernel time.
-    float st1[4] = {0.f, 0.f, 0.f, 0.f}, st2[4] = {0.f, 0.f, 0.f, 0.f};
+    // Column sums come from the staged bf16 tile in shared memory (second version; the first transposed 2 x 32 registers
+    // through 62 warp shuffles per chunk and cost 8-11 us on the 128x128-pixel layers): thread = one bf16x2 word column x
+    // one group of rows, packed fp32 accumulators that live across all tiles of the CTA's current n-tile.
+    f2_t cs1 = 0ull, cs2 = 0ull;
+    const int wpr = a.BN >> 1;                 // bf16x2 words per tile row
+    const int s_wcol = et % wpr, s_rgrp = et / wpr, s_groups = EPI_THREADS / wpr, s_rows = 128 / s_groups;
     int cur_n0 = -1;
     auto flush_stats = [&](int n0f) {
-      // per-warp partials -> smem -> one atomic per column
+      // per-thread partials -> smem -> one atomic per column
       float* red = reinterpret_cast<float*>(smem_raw + (stat_smem - smem_u32(smem_raw)));
       epi_bar_sync();
-      for (int c = 0; c < a.BN / 32; ++c) {
-        red[(ew * 2 + 0) * 128 + c * 32 + lane] = st1[c];
-        red[(ew * 2 + 1) * 128 + c * 32 + lane] = st2[c];
-        st1[c] = 0.f; st2[c] = 0.f;
-      }
+      float x0, x1, q0, q1;
+      upk2(cs1, x0, x1);
+      upk2(cs2, q0, q1);
+      red[(s_rgrp * 2 + 0) * a.BN + 2 * s_wcol] = x0; red[(s_rgrp * 2 + 0) * a.BN + 2 * s_wcol + 1] = x1;
+      red[(s_rgrp * 2 + 1) * a.BN + 2 * s_wcol] = q0; red[(s_rgrp * 2 + 1) * a.BN + 2 * s_wcol + 1] = q1;
+      cs1 = 0ull; cs2 = 0ull;
       epi_bar_sync();
       for (int i = et; i < 2 * a.BN; i += EPI_THREADS) {
         const int which = i / a.BN, col = i % a.BN;
         float v = 0.f;
-#pragma unroll
-        for (int w8 = 0; w8 < EPI_WARPS; ++w8) v += red[(w8 * 2 + which) * 128 + col];
+        for (int g = 0; g < s_groups; ++g) v += red[(g * 2 + which) * a.BN + col];
         atomicAdd(a.stats + which * a.N + n0f + col, v);
       }
     };
@@ -420,6 +425,10 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
             for (int e = 0; e < 8; ++e) v[j + e] += t8[e];
           }
         }
+        if (a.stats && !valid) {  // out-of-image rows are clipped by the TMA store but must not enter the statistics
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0.f;
+        }
         // bf16 pack + swizzled staging store (row r of sub-tile c0 / sub_w)
         const int sub = c0 / a.sub_w, cin_sub = c0 % a.sub_w;
         const uint32_t rowaddr = obuf + sub * sub_bytes + (uint32_t)r * row_bytes;
@@ -431,17 +440,6 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
           const uint32_t dst = rowaddr + ((chunk ^ xorv) << 4);
           asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(pk.x), "r"(pk.y), "r"(pk.z), "r"(pk.w)
                        : "memory");
-        }
-        if (a.stats) {
-          float s1[32], s2[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float x = valid ? __bfloat162float(__float2bfloat16_rn(v[j])) : 0.f;
-            s1[j] = x;
-            s2[j] = x * x;
-          }
-          st1[c0 >> 5] += warp_colsum32(s1, lane);
-          st2[c0 >> 5] += warp_colsum32(s2, lane);
         }
       }
       // accumulator stage fully read: hand it back to the MMA warp
@@ -455,6 +453,24 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
         for (int sub = 0; sub < nsub; ++sub)
           tma_store_4d(&tmY, obuf + sub * sub_bytes, n0 + sub * a.sub_w, w0, h0, b0);
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+      if (a.stats) {
+        // the staged tile is complete (barrier above) and stays untouched until two tiles from now
+        const int col = 2 * s_wcol;
+        const int sub = col / a.sub_w, cin_sub = col % a.sub_w;
+        const uint32_t chunk = (uint32_t)(cin_sub >> 3), within = (uint32_t)(cin_sub & 7) * 2u;
+        const uint32_t colbase = obuf + sub * sub_bytes + within;
+        const int r0 = s_rgrp * s_rows;
+#pragma unroll 4
+        for (int rr = 0; rr < s_rows; ++rr) {
+          const int rw_ = r0 + rr;
+          const uint32_t xv = (a.sub_w == 64) ? (uint32_t)(rw_ & 7) : (uint32_t)((rw_ >> 1) & 3);
+          uint32_t w;
+          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(colbase + (uint32_t)rw_ * row_bytes + ((chunk ^ xv) << 4)));
+          const f2_t x = bf2_to_f2(w);
+          cs1 = fadd2(cs1, x);
+          cs2 = ffma2(x, x, cs2);
+        }
       }
     }
     if (a.stats && cur_n0 >= 0) flush_stats(cur_n0);
@@ -645,23 +661,28 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
     // BN statistics are accumulated per CTA across all its tiles of one n-tile (registers: lane <-> column) and
     // flushed with 2*BN atomics per CTA instead of 8*BN per tile: the per-tile version serialised thousands of
     // same-address atomics in L2 and doubled the kernel time.
-    float st1[4] = {0.f, 0.f, 0.f, 0.f}, st2[4] = {0.f, 0.f, 0.f, 0.f};
+    // Column sums come from the staged bf16 tile in shared memory (second version; the first transposed 2 x 32 registers
+    // through 62 warp shuffles per chunk and cost 8-11 us on the 128x128-pixel layers): thread = one bf16x2 word column x
+    // one group of rows, packed fp32 accumulators that live across all tiles of the CTA's current n-tile.
+    f2_t cs1 = 0ull, cs2 = 0ull;
+    const int wpr = a.BN >> 1;                 // bf16x2 words per tile row
+    const int s_wcol = et % wpr, s_rgrp = et / wpr, s_groups = EPI_THREADS / wpr, s_rows = 128 / s_groups;
     int cur_n0 = -1;
     auto flush_stats = [&](int n0f) {
-      // per-warp partials -> smem -> one atomic per column
+      // per-thread partials -> smem -> one atomic per column
       float* red = reinterpret_cast<float*>(smem_raw + (stat_smem - smem_u32(smem_raw)));
       epi_bar_sync();
-      for (int c = 0; c < a.BN / 32; ++c) {
-        red[(ew * 2 + 0) * 128 + c * 32 + lane] = st1[c];
-        red[(ew * 2 + 1) * 128 + c * 32 + lane] = st2[c];
-        st1[c] = 0.f; st2[c] = 0.f;
-      }
+      float x0, x1, q0, q1;
+      upk2(cs1, x0, x1);
+      upk2(cs2, q0, q1);
+      red[(s_rgrp * 2 + 0) * a.BN + 2 * s_wcol] = x0; red[(s_rgrp * 2 + 0) * a.BN + 2 * s_wcol + 1] = x1;
+      red[(s_rgrp * 2 + 1) * a.BN + 2 * s_wcol] = q0; red[(s_rgrp * 2 + 1) * a.BN + 2 * s_wcol + 1] = q1;
+      cs1 = 0ull; cs2 = 0ull;
       epi_bar_sync();
       for (int i = et; i < 2 * a.BN; i += EPI_THREADS) {
         const int which = i / a.BN, col = i % a.BN;
         float v = 0.f;
-#pragma unroll
-        for (int w8 = 0; w8 < EPI_WARPS; ++w8) v += red[(w8 * 2 + which) * 128 + col];
+        for (int g = 0; g < s_groups; ++g) v += red[(g * 2 + which) * a.BN + col];
         atomicAdd(a.stats + which * a.N + n0f + col, v);
       }
     };
@@ -708,6 +729,10 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
             for (int e = 0; e < 8; ++e) v[j + e] += t8[e];
           }
         }
+        if (a.stats && !valid) {  // out-of-image rows are clipped by the TMA store but must not enter the statistics
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0.f;
+        }
         // bf16 pack + swizzled staging store (row r of sub-tile c0 / sub_w)
         const int sub = c0 / a.sub_w, cin_sub = c0 % a.sub_w;
         const uint32_t rowaddr = obuf + sub * sub_bytes + (uint32_t)r * row_bytes;
@@ -719,17 +744,6 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
           const uint32_t dst = rowaddr + ((chunk ^ xorv) << 4);
           asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(pk.x), "r"(pk.y), "r"(pk.z), "r"(pk.w)
                        : "memory");
-        }
-        if (a.stats) {
-          float s1[32], s2[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float x = valid ? __bfloat162float(__float2bfloat16_rn(v[j])) : 0.f;
-            s1[j] = x;
-            s2[j] = x * x;
-          }
-          st1[c0 >> 5] += warp_colsum32(s1, lane);
-          st2[c0 >> 5] += warp_colsum32(s2, lane);
         }
       }
       // accumulator stage fully read: hand it back to the MMA warp
@@ -743,6 +757,24 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
         for (int sub = 0; sub < nsub; ++sub)
           tma_store_4d(&tmY, obuf + sub * sub_bytes, n0 + sub * a.sub_w, w0, h0, b0);
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+      if (a.stats) {
+        // the staged tile is complete (barrier above) and stays untouched until two tiles from now
+        const int col = 2 * s_wcol;
+        const int sub = col / a.sub_w, cin_sub = col % a.sub_w;
+        const uint32_t chunk = (uint32_t)(cin_sub >> 3), within = (uint32_t)(cin_sub & 7) * 2u;
+        const uint32_t colbase = obuf + sub * sub_bytes + within;
+        const int r0 = s_rgrp * s_rows;
+#pragma unroll 4
+        for (int rr = 0; rr < s_rows; ++rr) {
+          const int rw_ = r0 + rr;
+          const uint32_t xv = (a.sub_w == 64) ? (uint32_t)(rw_ & 7) : (uint32_t)((rw_ >> 1) & 3);
+          uint32_t w;
+          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(colbase + (uint32_t)rw_ * row_bytes + ((chunk ^ xv) << 4)));
+          const f2_t x = bf2_to_f2(w);
+          cs1 = fadd2(cs1, x);
+          cs2 = ffma2(x, x, cs2);
+        }
       }
     }
     if (a.stats && cur_n0 >= 0) flush_stats(cur_n0);

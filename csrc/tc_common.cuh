@@ -114,4 +114,49 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t v[32]) {
 }
 
 
+// ---- packed fp32 helpers: Blackwell issues two fp32 FMAs per FFMA2 (fma.rn.f32x2 on a 64-bit register pair) ----------
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t ffma2(f2_t a_, f2_t b_, f2_t c_) {
+  f2_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a_), "l"(b_), "l"(c_));
+  return d;
+}
+__device__ __forceinline__ f2_t fadd2(f2_t a_, f2_t b_) {
+  f2_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a_), "l"(b_));
+  return d;
+}
+__device__ __forceinline__ f2_t fmul2(f2_t a_, f2_t b_) {
+  f2_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a_), "l"(b_));
+  return d;
+}
+__device__ __forceinline__ f2_t pk2(float lo, float hi) {
+  f2_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void upk2(f2_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+// one 32-bit word of two bf16 -> packed (lo, hi) fp32
+__device__ __forceinline__ f2_t bf2_to_f2(uint32_t v) {
+  f2_t r;
+  const uint32_t lo = v << 16, hi = v & 0xffff0000u;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+// packed (lo, hi) fp32 -> relu -> one word of two bf16
+__device__ __forceinline__ uint32_t f2_to_bf2_relu(f2_t v) {
+  float lo, hi;
+  upk2(v, lo, hi);
+  uint32_t r;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ uint32_t relu_bf2(uint32_t v) {
+  uint32_t r;
+  asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(0u));
+  return r;
+}
+
+
 }  // namespace
