@@ -382,6 +382,11 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
         atomicAdd(a.stats + which * a.N + n0f + col, v);
       }
     };
+    // bias vector into shared memory once (ordered by the first epi_bar_sync below): no global-memory latency between
+    // the accumulator becoming ready and the tile being stored
+    float* sbias = reinterpret_cast<float*>(smem_raw + (stat_smem + 4096u - smem_u32(smem_raw)));
+    if (a.bias)
+      for (int i = et; i < a.N; i += EPI_THREADS) sbias[i] = __ldg(a.bias + i);
     uint32_t tcount = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
       int tm_ = tile % a.n_tiles_m;
@@ -412,7 +417,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
         if (a.bias) {
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
-            const float4 bb = __ldg(reinterpret_cast<const float4*>(a.bias + n0 + c0 + j));
+            const float4 bb = *reinterpret_cast<const float4*>(sbias + n0 + c0 + j);
             v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
           }
         }
@@ -474,7 +479,9 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
       }
     }
     if (a.stats && cur_n0 >= 0) flush_stats(cur_n0);
-    if (et == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    // only the shared-memory reads of the last stores must finish before the CTA retires; the global writes are
+    // complete at grid end like any other store
+    if (et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
@@ -686,6 +693,11 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
         atomicAdd(a.stats + which * a.N + n0f + col, v);
       }
     };
+    // bias vector into shared memory once (ordered by the first epi_bar_sync below): no global-memory latency between
+    // the accumulator becoming ready and the tile being stored
+    float* sbias = reinterpret_cast<float*>(smem_raw + (stat_smem + 4096u - smem_u32(smem_raw)));
+    if (a.bias)
+      for (int i = et; i < a.N; i += EPI_THREADS) sbias[i] = __ldg(a.bias + i);
     uint32_t tcount = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
       int tm_ = tile % a.n_tiles_m;
@@ -716,7 +728,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
         if (a.bias) {
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
-            const float4 bb = __ldg(reinterpret_cast<const float4*>(a.bias + n0 + c0 + j));
+            const float4 bb = *reinterpret_cast<const float4*>(sbias + n0 + c0 + j);
             v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
           }
         }
@@ -778,7 +790,9 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
       }
     }
     if (a.stats && cur_n0 >= 0) flush_stats(cur_n0);
-    if (et == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    // only the shared-memory reads of the last stores must finish before the CTA retires; the global writes are
+    // complete at grid end like any other store
+    if (et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
