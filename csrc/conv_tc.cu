@@ -820,7 +820,8 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t ablk_bytes = 128u * a.cw * 2u, bblk_bytes = 128u * a.nw * 2u;
-  const uint32_t a_bytes = ablk_bytes * a.mblk, b_bytes = bblk_bytes * a.nblk;
+  // a layer with a single (tap, chunk) block only stages that block (the other M-blocks alias it, see lboA below)
+  const uint32_t a_bytes = ablk_bytes * (a.total_blocks == 1 ? 1u : (uint32_t)a.mblk), b_bytes = bblk_bytes * a.nblk;
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const uint32_t bar_base = base + a.stages * stage_bytes;
   const uint32_t full0 = bar_base, empty0 = bar_base + 8u * a.stages, tfull = bar_base + 16u * a.stages;
@@ -1348,7 +1349,7 @@ int crackfl_wgrad_tc_ws_cv(const void* X, const void* dY, float* dW, int B, int 
   // one wave of CTAs: two per SM when two pipelines of >= 2 stages fit in shared memory, else one per SM with
   // up to 3 stages; few, long-running CTAs keep the fp32 atomics of the epilogue (one per output element per
   // CTA) from serialising in L2
-  const uint32_t stage_bytes = 128u * 128u * 2u + 128u * (uint32_t)a.BN * 2u;
+  const uint32_t stage_bytes = (a.total_blocks == 1 ? 128u * (uint32_t)a.cw * 2u : 128u * 128u * 2u) + 128u * (uint32_t)a.BN * 2u;
   int per_sm = (2u * stage_bytes <= 106496u) ? 2 : 1;
   {
     static int dbg_persm = -1, dbg_noat = -1;
@@ -1358,7 +1359,7 @@ int crackfl_wgrad_tc_ws_cv(const void* X, const void* dY, float* dW, int B, int 
     a.dbg_noatomic = dbg_noat;
   }
   int stages = per_sm == 2 ? (int)(106496u / stage_bytes) : (int)(200704u / stage_bytes);
-  if (stages > 4) stages = 4;
+  if (stages > 6) stages = 6;
   int splits = (148 * per_sm) / (groups * ntn);
   if (splits > a.ntiles) splits = a.ntiles;
   if (splits < 1) splits = 1;

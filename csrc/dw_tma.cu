@@ -276,7 +276,8 @@ __global__ void __launch_bounds__(256, 2) dw_stencil_k(const __grid_constant__ C
   }
 }
 
-// weight gradient: a-halo tile + g tile per stage
+// weight gradient: a-halo tile + g tile per stage; same structure as the stencil kernel (in-place activation pre-pass,
+// FFMA2 channel pairs): dW[t][c] accumulates in 18 packed registers per thread over all tiles of a channel block.
 template <int TY, int RG>
 __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUtensorMap tmA,
                                                      const __grid_constant__ CUtensorMap tmG, const DwArgs a) {
@@ -288,6 +289,7 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
   const uint32_t stage_bytes = a_bytes + g_bytes;
   const uint32_t bar0 = base + 2u * stage_bytes;
   float* red = reinterpret_cast<float*>(gbase + 2u * stage_bytes + 64);  // [256][4] floats
+  float* coef = red + 256 * 4;                                            // [scale CB][shift CB]
   const int nc4 = CB >> 2;
   constexpr int rows = TY / RG;
   const int c4 = threadIdx.x % nc4, col = (threadIdx.x / nc4) % TX, rg = threadIdx.x / (nc4 * TX);
@@ -315,11 +317,9 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
   };
   if (threadIdx.x == 0 && (int)blockIdx.x < a.total_tiles) issue(blockIdx.x, 0);
 
-  float acc[9][4], sc[4], sh[4];
+  f2_t acc[9][2];
 #pragma unroll
-  for (int t = 0; t < 9; ++t)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) acc[t][j] = 0.f;
+  for (int t = 0; t < 9; ++t) { acc[t][0] = 0ull; acc[t][1] = 0ull; }
   int cur_cblk = -1;
 
   auto flush = [&](int cblk) {
@@ -327,8 +327,10 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
 #pragma unroll
     for (int t = 0; t < 9; ++t) {
       __syncthreads();
-#pragma unroll
-      for (int j = 0; j < 4; ++j) red[threadIdx.x * 4 + j] = acc[t][j];
+      float f0, f1, f2, f3;
+      upk2(acc[t][0], f0, f1);
+      upk2(acc[t][1], f2, f3);
+      *reinterpret_cast<float4*>(red + threadIdx.x * 4) = make_float4(f0, f1, f2, f3);
       __syncthreads();
       if (threadIdx.x < nc4 * 4) {
         const int cc = threadIdx.x >> 2, j = threadIdx.x & 3;
@@ -336,8 +338,7 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
         for (int q = 0; q < 256 / nc4; ++q) v += red[(q * nc4 + cc) * 4 + j];
         atomicAdd(a.dwk + (long)t * a.C + cblk * CB + cc * 4 + j, v);
       }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) acc[t][j] = 0.f;
+      acc[t][0] = 0ull; acc[t][1] = 0ull;
     }
   };
 
@@ -350,46 +351,87 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
     int sp = tile % spatial;
     const int tx_i = sp % a.tiles_x; sp /= a.tiles_x;
     const int ty_i = sp % a.tiles_y;
-    const int cg = cblk * CB + c4 * 4;
-    if (cblk != cur_cblk) {
+    if (cblk != cur_cblk) {  // uniform over the CTA
       if (cur_cblk >= 0) flush(cur_cblk);
       cur_cblk = cblk;
-      if (a.act_mode == 1) coeffs4(a.fin, a.bn, a.C, cg, sc, sh);
+      if (a.act_mode == 1) {
+        __syncthreads();  // the previous tile's pre-pass readers of coef are done
+        if (threadIdx.x < nc4) {
+          float sc[4], sh[4];
+          coeffs4(a.fin, a.bn, a.C, cblk * CB + threadIdx.x * 4, sc, sh);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { coef[threadIdx.x * 4 + j] = sc[j]; coef[CB + threadIdx.x * 4 + j] = sh[j]; }
+        }
+        __syncthreads();
+      }
     }
     mbar_wait(bar0 + 8u * stage, (uint32_t)(it >> 1) & 1u);
-    const uint8_t* tile_a = gbase + stage * stage_bytes;
+    uint8_t* tile_a = gbase + stage * stage_bytes;
     const uint8_t* tile_g = tile_a + a_bytes;
-    const int w0 = tx_i * TX, h0 = ty_i * TY + rg * rows;
-    const int gw = w0 + col;
-    float win[3][3][4];
-#pragma unroll
-    for (int r = 0; r < rows + 2; ++r) {
-      const int gh = h0 - 1 + r;
-      const uint8_t* rowp = tile_a + (size_t)((rg * rows + r) * HW) * rowb + c4 * 8;
-#pragma unroll
-      for (int kx = 0; kx < 3; ++kx) {
-        float v[4];
-        load4(rowp, (col + kx) * rowb, v);
-        const bool inside = gh >= 0 && gh < a.H && (gw - 1 + kx) >= 0 && (gw - 1 + kx) < a.W;
+    const int w0 = tx_i * TX, ty0 = ty_i * TY;
+
+    {  // activation pre-pass, in place (relu / relu(bn)); out-of-image pixels stay zero
+      const int c8n = CB >> 3;
+      const int nchunk = (TY + 2) * HW * c8n;
+      if (a.act_mode == 0) {
+        for (int idx = threadIdx.x; idx < nchunk; idx += 256) {
+          uint4* q = reinterpret_cast<uint4*>(tile_a) + idx;
+          uint4 v = *q;
+          v.x = relu_bf2(v.x); v.y = relu_bf2(v.y); v.z = relu_bf2(v.z); v.w = relu_bf2(v.w);
+          *q = v;
+        }
+      } else {
+        const bool interior = w0 >= 1 && w0 + TX < a.W && ty0 >= 1 && ty0 + TY < a.H;
+        const int c8 = threadIdx.x % c8n;
+        f2_t scp[4], shp[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          float x = v[j];
-          if (a.act_mode == 1) x = fmaf(x, sc[j], sh[j]);
-          x = fmaxf(x, 0.f);
-          win[r % 3][kx][j] = inside ? x : 0.f;
+          scp[j] = *reinterpret_cast<const f2_t*>(coef + c8 * 8 + 2 * j);
+          shp[j] = *reinterpret_cast<const f2_t*>(coef + CB + c8 * 8 + 2 * j);
+        }
+        for (int idx = threadIdx.x; idx < nchunk; idx += 256) {
+          uint4* q = reinterpret_cast<uint4*>(tile_a) + idx;
+          uint4 v = *q;
+          v.x = f2_to_bf2_relu(ffma2(bf2_to_f2(v.x), scp[0], shp[0]));
+          v.y = f2_to_bf2_relu(ffma2(bf2_to_f2(v.y), scp[1], shp[1]));
+          v.z = f2_to_bf2_relu(ffma2(bf2_to_f2(v.z), scp[2], shp[2]));
+          v.w = f2_to_bf2_relu(ffma2(bf2_to_f2(v.w), scp[3], shp[3]));
+          if (!interior) {
+            const int pi = idx / c8n;
+            const int hr = pi / HW, hc = pi - hr * HW;
+            const int gh = ty0 - 1 + hr, gx = w0 - 1 + hc;
+            if (gh < 0 || gh >= a.H || gx < 0 || gx >= a.W) v = make_uint4(0u, 0u, 0u, 0u);
+          }
+          *q = v;
         }
       }
+      __syncthreads();
+    }
+
+    f2_t win[3][3][2];
+    const uint8_t* const row0 = tile_a + (size_t)(((rg * rows) * HW + col) * rowb + c4 * 8);
+    const uint8_t* const g0 = tile_g + (size_t)(((rg * rows) * TX + col) * rowb + c4 * 8);
+#pragma unroll
+    for (int r = 0; r < rows + 2; ++r) {
+      const uint8_t* rowp = row0 + r * (HW * rowb);
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        const uint2 v = *reinterpret_cast<const uint2*>(rowp + kx * rowb);
+        win[r % 3][kx][0] = bf2_to_f2(v.x);
+        win[r % 3][kx][1] = bf2_to_f2(v.y);
+      }
       if (r >= 2) {
-        float g4[4];  // out-of-image g pixels are TMA zero fill: they contribute nothing
-        load4(tile_g + (size_t)((rg * rows + r - 2) * TX + col) * rowb + c4 * 8, 0, g4);
+        // out-of-image g pixels are TMA zero fill: they contribute nothing
+        const uint2 gv = *reinterpret_cast<const uint2*>(g0 + (r - 2) * (TX * rowb));
+        const f2_t ga = bf2_to_f2(gv.x), gb = bf2_to_f2(gv.y);
 #pragma unroll
-        for (int kh = 0; kh < 3; ++kh)
-#pragma unroll
-          for (int kx = 0; kx < 3; ++kx)
-#pragma unroll
-            for (int j = 0; j < 4; ++j) acc[kh * 3 + kx][j] = fmaf(win[(r - 2 + kh) % 3][kx][j], g4[j], acc[kh * 3 + kx][j]);
+        for (int t = 0; t < 9; ++t) {
+          acc[t][0] = ffma2(win[(r - 2 + t / 3) % 3][t % 3][0], ga, acc[t][0]);
+          acc[t][1] = ffma2(win[(r - 2 + t / 3) % 3][t % 3][1], gb, acc[t][1]);
+        }
       }
     }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
   }
   if (cur_cblk >= 0) flush(cur_cblk);
@@ -475,7 +517,7 @@ int crackfl_dw3x3_wgrad_tma(const void* g, const void* src, const float* bn, flo
   if (rc) return rc;
   rc = ck::get_tensor_map(g, 4, d, bg, 0, &tmG);
   if (rc) return rc;
-  const size_t smem = 2 * ((size_t)(TY + 2) * HW + TY * TX) * a.CB * 2 + 128 + 64 + 256 * 4 * sizeof(float);
+  const size_t smem = 2 * ((size_t)(TY + 2) * HW + TY * TX) * a.CB * 2 + 128 + 64 + 256 * 4 * sizeof(float) + 2 * 64 * sizeof(float);
   static bool attr = false;
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(dw_wgrad_k<TY, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
