@@ -36,6 +36,7 @@ struct DwArgs {
   int flip;                     // use w[8 - t] (input gradient)
   int src_mode, resid;          // dgrad epilogue (see dw3x3_bwd_k in elementwise.cu)
   int tiles_x, tiles_y, total_tiles;
+  int nstage;                   // depth of the TMA ring (2..4)
 };
 
 __device__ __forceinline__ void load4(const uint8_t* smem_row, int off_bytes, float f[4]) {
@@ -94,16 +95,18 @@ __global__ void __launch_bounds__(256, 2) dw_stencil_k(const __grid_constant__ C
   const int CB = a.CB, rowb = CB * 2;
   const uint32_t halo_bytes = (uint32_t)((TY + 2) * HW * rowb);
   const uint32_t stage_bytes = halo_bytes + (DGRAD ? (uint32_t)(TY * TX * rowb) : 0u);
-  const uint32_t bar0 = base + 2u * stage_bytes;
-  float* coef = reinterpret_cast<float*>(gbase + 2u * stage_bytes + 64);  // [scale CB][shift CB] of the current channel block
+  // ring of NS stages: measured, with the original 2 stages (one tile in flight while one is processed) these kernels
+  // sat at 25-30 % of the HBM rate however few instructions they executed - latency-bound on the bulk copies
+  const int NS = a.nstage;
+  const uint32_t bar0 = base + (uint32_t)NS * stage_bytes;
+  float* coef = reinterpret_cast<float*>(gbase + (uint32_t)NS * stage_bytes + 64);  // [scale CB][shift CB] of the current channel block
   const int nc4 = CB >> 2;
   constexpr int rows = TY / RG;
   const int c4 = threadIdx.x % nc4, col = (threadIdx.x / nc4) % TX, rg = threadIdx.x / (nc4 * TX);
   const int spatial = a.tiles_x * a.tiles_y * a.B;
 
   if (threadIdx.x == 0) {
-    mbar_init(bar0, 1);
-    mbar_init(bar0 + 8u, 1);
+    for (int i = 0; i < NS; ++i) mbar_init(bar0 + 8u * i, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     tma_prefetch_desc(&tmX);
     if (DGRAD) tma_prefetch_desc(&tmS);
@@ -122,16 +125,22 @@ __global__ void __launch_bounds__(256, 2) dw_stencil_k(const __grid_constant__ C
     tma_load_4d(base + stage * stage_bytes, &tmX, bar0 + 8u * stage, cblk * CB, tx_i * TX - 1, ty_i * TY - 1, b);
     if (DGRAD) tma_load_4d(base + stage * stage_bytes + halo_bytes, &tmS, bar0 + 8u * stage, cblk * CB, tx_i * TX, ty_i * TY, b);
   };
-  if (threadIdx.x == 0 && (int)blockIdx.x < a.total_tiles) issue(blockIdx.x, 0);
+  if (threadIdx.x == 0)
+    for (int i = 0; i < NS - 1; ++i)
+      if ((int)(blockIdx.x + i * gridDim.x) < a.total_tiles) issue(blockIdx.x + i * gridDim.x, i);
 
   int cur_cblk = -1;
   f2_t wk[9][2], msc[2], msh[2];
   msc[0] = msc[1] = msh[0] = msh[1] = 0ull;
-  int it = 0;
+  int it = 0, stage = 0;
+  uint32_t par = 0;
   for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
-    const int stage = it & 1;
-    const int nxt = tile + gridDim.x;
-    if (threadIdx.x == 0 && nxt < a.total_tiles) issue(nxt, stage ^ 1);  // its last readers passed the barrier below
+    {
+      // refill the stage consumed in the previous iteration (its last readers passed the barrier at the loop tail)
+      const int nxt = tile + (NS - 1) * gridDim.x;
+      const int ns = stage == 0 ? NS - 1 : stage - 1;
+      if (threadIdx.x == 0 && nxt < a.total_tiles) issue(nxt, ns);
+    }
     const int cblk = tile / spatial;
     int sp = tile % spatial;
     const int tx_i = sp % a.tiles_x; sp /= a.tiles_x;
@@ -175,7 +184,7 @@ __global__ void __launch_bounds__(256, 2) dw_stencil_k(const __grid_constant__ C
               a.resid_t + (((long)b * (a.H >> 1) + (oh >> 1)) * (a.W >> 1) + (gw >> 1)) * a.C + cg));
       }
     }
-    mbar_wait(bar0 + 8u * stage, (uint32_t)(it >> 1) & 1u);
+    mbar_wait(bar0 + 8u * stage, par);
     uint8_t* tile_s = gbase + stage * stage_bytes;
 
     if (!DGRAD && a.act_mode != 2) {
@@ -273,6 +282,7 @@ __global__ void __launch_bounds__(256, 2) dw_stencil_k(const __grid_constant__ C
     // generic-proxy writes (pre-pass) are ordered before the TMA refill of this stage two iterations from now
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();  // every thread is done with this stage before it is refilled
+    if (++stage == NS) { stage = 0; par ^= 1u; }
   }
 }
 
@@ -287,8 +297,9 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
   const int CB = a.CB, rowb = CB * 2;
   const uint32_t a_bytes = (uint32_t)((TY + 2) * HW * rowb), g_bytes = (uint32_t)(TY * TX * rowb);
   const uint32_t stage_bytes = a_bytes + g_bytes;
-  const uint32_t bar0 = base + 2u * stage_bytes;
-  float* red = reinterpret_cast<float*>(gbase + 2u * stage_bytes + 64);  // [256][4] floats
+  const int NS = a.nstage;
+  const uint32_t bar0 = base + (uint32_t)NS * stage_bytes;
+  float* red = reinterpret_cast<float*>(gbase + (uint32_t)NS * stage_bytes + 64);  // [256][4] floats
   float* coef = red + 256 * 4;                                            // [scale CB][shift CB]
   const int nc4 = CB >> 2;
   constexpr int rows = TY / RG;
@@ -296,8 +307,7 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
   const int spatial = a.tiles_x * a.tiles_y * a.B;
 
   if (threadIdx.x == 0) {
-    mbar_init(bar0, 1);
-    mbar_init(bar0 + 8u, 1);
+    for (int i = 0; i < NS; ++i) mbar_init(bar0 + 8u * i, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmG);
@@ -315,7 +325,9 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
     tma_load_4d(base + stage * stage_bytes, &tmA, bar0 + 8u * stage, cblk * CB, tx_i * TX - 1, ty_i * TY - 1, b);
     tma_load_4d(base + stage * stage_bytes + a_bytes, &tmG, bar0 + 8u * stage, cblk * CB, tx_i * TX, ty_i * TY, b);
   };
-  if (threadIdx.x == 0 && (int)blockIdx.x < a.total_tiles) issue(blockIdx.x, 0);
+  if (threadIdx.x == 0)
+    for (int i = 0; i < NS - 1; ++i)
+      if ((int)(blockIdx.x + i * gridDim.x) < a.total_tiles) issue(blockIdx.x + i * gridDim.x, i);
 
   f2_t acc[9][2];
 #pragma unroll
@@ -342,11 +354,14 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
     }
   };
 
-  int it = 0;
+  int it = 0, stage = 0;
+  uint32_t par = 0;
   for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
-    const int stage = it & 1;
-    const int nxt = tile + gridDim.x;
-    if (threadIdx.x == 0 && nxt < a.total_tiles) issue(nxt, stage ^ 1);
+    {
+      const int nxt = tile + (NS - 1) * gridDim.x;
+      const int ns = stage == 0 ? NS - 1 : stage - 1;
+      if (threadIdx.x == 0 && nxt < a.total_tiles) issue(nxt, ns);
+    }
     const int cblk = tile / spatial;
     int sp = tile % spatial;
     const int tx_i = sp % a.tiles_x; sp /= a.tiles_x;
@@ -365,7 +380,7 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
         __syncthreads();
       }
     }
-    mbar_wait(bar0 + 8u * stage, (uint32_t)(it >> 1) & 1u);
+    mbar_wait(bar0 + 8u * stage, par);
     uint8_t* tile_a = gbase + stage * stage_bytes;
     const uint8_t* tile_g = tile_a + a_bytes;
     const int w0 = tx_i * TX, ty0 = ty_i * TY;
@@ -433,6 +448,7 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
+    if (++stage == NS) { stage = 0; par ^= 1u; }
   }
   if (cur_cblk >= 0) flush(cur_cblk);
 }
@@ -450,9 +466,27 @@ int num_sms() {
 
 bool shape_ok(int C) { return C % 32 == 0 && (C <= 64 || C % 64 == 0); }
 
+// channel block and ring depth: as many stages (<= 4) as fit twice per SM (2 x <= 112 KB); CRACKFL_DW_CB /
+// CRACKFL_DW_STAGES override for tuning.  Measured (bench/dw_bench.py, 128x128x64): ring depth 2, 3 or 4 makes no
+// difference (the kernels are bound by the shared FMA/ALU pipe, ncu math_pipe_throttle, not by copy latency) and
+// 32-channel blocks are 10-25 % slower than 64 (twice the per-tile overhead), so 64-channel blocks x 2 stages stay.
+void pick_ring(DwArgs& a, size_t stage_bytes_per_channel, size_t extra) {
+  static int env_cb = -1, env_ns = -1;
+  if (env_cb < 0) { const char* e = getenv("CRACKFL_DW_CB"); env_cb = e ? atoi(e) : 0; }
+  if (env_ns < 0) { const char* e = getenv("CRACKFL_DW_STAGES"); env_ns = e ? atoi(e) : 0; }
+  a.CB = (a.C >= 64 && env_cb != 32) ? 64 : 32;
+  int ns = (int)((112 * 1024 - extra) / (stage_bytes_per_channel * a.CB));
+  if (ns > 4) ns = 4;
+  if (env_ns >= 2 && env_ns <= ns) ns = env_ns;
+  if (ns < 2) ns = 2;
+  a.nstage = ns;
+}
+
 // forward (src == NULL) or input gradient (src != NULL, flip = 1, act_mode = 2)
 template <int TY, bool DGRAD>
 static int launch_stencil(const void* x, DwArgs& a, cudaStream_t st) {
+  const size_t extra = 64 + 2 * 64 * sizeof(float) + 128;
+  pick_ring(a, ((size_t)(TY + 2) * HW + (DGRAD ? (size_t)TY * TX : 0)) * 2, extra);
   a.tiles_x = (a.W + TX - 1) / TX; a.tiles_y = (a.H + TY - 1) / TY;
   a.total_tiles = a.tiles_x * a.tiles_y * a.B * (a.C / a.CB);
   CUtensorMap tm, tmS;
@@ -462,12 +496,12 @@ static int launch_stencil(const void* x, DwArgs& a, cudaStream_t st) {
   rc = ck::get_tensor_map(DGRAD ? (const void*)a.src : x, 4, d, DGRAD ? bs : bx, 0, &tmS);
   if (rc) return rc;
   const size_t stage = (size_t)(TY + 2) * HW * a.CB * 2 + (DGRAD ? (size_t)TY * TX * a.CB * 2 : 0);
-  const size_t smem = 2 * stage + 64 + 2 * a.CB * sizeof(float) + 128;
+  const size_t smem = (size_t)a.nstage * stage + extra;
   static bool attr = false;
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(dw_stencil_k<TY, 1, DGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(dw_stencil_k<TY, 1, DGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
     if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(dw_stencil_k<TY, 2, DGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+      e = cudaFuncSetAttribute(dw_stencil_k<TY, 2, DGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
     if (e != cudaSuccess) return (int)e;
     attr = true;
   }
@@ -507,8 +541,10 @@ int crackfl_dw3x3_wgrad_tma(const void* g, const void* src, const float* bn, flo
   DwArgs a;
   memset(&a, 0, sizeof(a));
   a.bn = bn; a.dwk = dwk;
-  a.B = B; a.H = H; a.W = W; a.C = C; a.CB = C >= 64 ? 64 : 32;
+  a.B = B; a.H = H; a.W = W; a.C = C;
   a.act_mode = mode;
+  const size_t extra = 64 + 256 * 4 * sizeof(float) + 2 * 64 * sizeof(float) + 128;
+  pick_ring(a, ((size_t)(TY + 2) * HW + (size_t)TY * TX) * 2, extra);
   a.tiles_x = (W + TX - 1) / TX; a.tiles_y = (H + TY - 1) / TY;
   a.total_tiles = a.tiles_x * a.tiles_y * B * (C / a.CB);
   CUtensorMap tmA, tmG;
@@ -517,11 +553,11 @@ int crackfl_dw3x3_wgrad_tma(const void* g, const void* src, const float* bn, flo
   if (rc) return rc;
   rc = ck::get_tensor_map(g, 4, d, bg, 0, &tmG);
   if (rc) return rc;
-  const size_t smem = 2 * ((size_t)(TY + 2) * HW + TY * TX) * a.CB * 2 + 128 + 64 + 256 * 4 * sizeof(float) + 2 * 64 * sizeof(float);
+  const size_t smem = (size_t)a.nstage * ((size_t)(TY + 2) * HW + TY * TX) * a.CB * 2 + extra;
   static bool attr = false;
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(dw_wgrad_k<TY, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_wgrad_k<TY, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(dw_wgrad_k<TY, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_wgrad_k<TY, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
     if (e != cudaSuccess) return (int)e;
     attr = true;
   }
