@@ -39,7 +39,12 @@ def ncu_raw(rep, tag, title):
     want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
             "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
             "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.pct_of_peak_sustained_active",
-            "launch__registers_per_thread", "launch__grid_size", "lts__t_sectors_srcunit_tex_op_read.sum"]
+            "launch__registers_per_thread", "launch__grid_size", "lts__t_sectors_srcunit_tex_op_read.sum",
+            "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+            "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio",
+            "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
+            "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+            "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio"]
     try:
         txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     except FileNotFoundError:
@@ -102,11 +107,15 @@ if __name__ == "__main__":
     for fn in sorted(glob.glob(os.path.join(GO, "launches*.csv"))):
         launches(fn, os.path.basename(fn)[:-4].replace("launches", "v") or "v")
     for rep, t, title in (("prof_conv.ncu-rep", "conv3x3_d3ct1", "tcgen05 conv fwd/dgrad + wgrad, 3x3 64->32 @128^2 B=16"),
-                          ("prof_pw.ncu-rep", "pointwise_e0pw2", "tcgen05 conv fwd/dgrad + wgrad, 1x1 64->64 @128^2 B=16")):
+                          ("prof_pw.ncu-rep", "pointwise_e0pw2", "tcgen05 conv fwd/dgrad + wgrad, 1x1 64->64 @128^2 B=16"),
+                          ("prof_dw.ncu-rep", "dw_stencil_gen1", "depthwise 3x3 (first TMA version: fully unrolled, activation inlined), 64 ch @128^2 B=16"),
+                          ("prof_dw2.ncu-rep", "dw_gen2", "depthwise 3x3 fwd / dgrad / wgrad (pre-pass + FFMA2 version), 64 ch @128^2 B=16"),
+                          ("prof_d3.ncu-rep", "conv3x3_d3ct1_halo_lane0", "halo conv 3x3 64->32 @128^2 before the warp-uniform issue path (MMA thread under if(lane==0))"),
+                          ("prof_small.ncu-rep", "small_gemm_d1res", "1x1 256->128 @16^2 B=16: fixed cost of a small tcgen05 GEMM launch")):
         p = os.path.join(GO, rep)
         if os.path.exists(p):
             ncu_raw(p, t, title)
     sass()
-    for pat in ("agg_sweep_*.json", "conv_bench*.json", "bench_*.json"):
+    for pat in ("agg_sweep_*.json", "conv_bench*.json", "bench_*.json", "dw_bench*.json"):
         copy_json(pat, None)
     print(sorted(os.listdir(OUT)))
