@@ -62,6 +62,8 @@ class UNetEngine:
         self._fins: list = []
         self.fuse_finalize = os.environ.get("CRACKFL_FUSE_FINALIZE", "1") != "0"
         self.dw_tma = os.environ.get("CRACKFL_DW_TMA", "1") != "0"
+        self.gemm_stats = os.environ.get("CRACKFL_GEMM_STATS", "1") != "0"
+        self.dw_merged = os.environ.get("CRACKFL_DW_MERGED", "1") != "0"
         with torch.cuda.device(self.dev):
             self._alloc_params()
             self._build_ops_table()
@@ -225,6 +227,8 @@ class UNetEngine:
     def _gemm(self, prog, X, opname, bias, add, Y, B, H, W, stats=0, tag=None):
         off, N, T, K = self.ops[opname]
         extra = (tag,) if tag else ()
+        if not self.gemm_stats:
+            stats = 0  # tuning knob: BN statistics by a separate pass over the GEMM output instead of the fused epilogue
         if self.conv_impl == "tc":
             prog.append((self.lib.crackfl_conv_tc_fwd, (X, self.op_ptr(opname), bias, add, Y, stats, B, H, W, K, N, T)) + extra)
             return stats != 0
@@ -243,7 +247,10 @@ class UNetEngine:
 
     def _dw_bwd(self, prog, g, src, w, bn, resid_t, dz, dwk, B, H, W, C, mode, resid):
         """Depthwise backward: input gradient on the main stream, weight gradient on the side stream."""
-        if self.dw_tma:
+        if self.dw_tma and self.dw_merged:
+            # one pass over g and src: warps 0-7 the input gradient, warps 8-15 the weight gradient
+            prog.append((self.lib.crackfl_dw3x3_bwd_tma, (g, src, w, bn, resid_t, dz, dwk, B, H, W, C, mode, resid)))
+        elif self.dw_tma:
             prog.append((self.lib.crackfl_dw3x3_tma, (g, w, 0, None, dz, src, bn, resid_t, B, H, W, C, 2, 1, mode, resid)))
             prog.append((self.lib.crackfl_dw3x3_wgrad_tma, (g, src, bn, dwk, B, H, W, C, mode), "side"))
         elif W % 4 == 0 and 128 % (C // 8) == 0:

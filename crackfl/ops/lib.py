@@ -58,6 +58,7 @@ _SIGS = {
     "crackfl_dec_combine_fwd_fin": [vp, C.POINTER(BnFin), vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_dw3x3_tma": [vp, vp, vp, C.POINTER(BnFin), vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
     "crackfl_dw3x3_wgrad_tma": [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    "crackfl_dw3x3_bwd_tma": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
     "crackfl_dw3x3_dgrad": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
     "crackfl_dw3x3_wgrad": [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_pool_add_fwd": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],

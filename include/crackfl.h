@@ -95,6 +95,9 @@ int crackfl_dw3x3_tma(const void* x, const float* w, const float* bn, const crac
                       int act_mode, int flip, int src_mode, int resid, cudaStream_t stream);
 int crackfl_dw3x3_wgrad_tma(const void* g, const void* src, const float* bn, float* dwk, int B, int H, int W, int C, int mode,
                             cudaStream_t stream);
+/* third generation: input gradient and weight gradient in one pass over g and src (warps 0-7 / 8-15 of a 512-thread CTA) */
+int crackfl_dw3x3_bwd_tma(const void* g, const void* src, const float* w, const float* src_bn, const void* resid_t, void* dz,
+                          float* dwk, int B, int H, int W, int C, int src_mode, int resid, cudaStream_t stream);
 
 /* ---- block tails --------------------------------------------------------------------------- */
 /* ref: client_fit_model.py:116-123 MaxPooling2D(3,2,"same") + add(residual) */

@@ -312,6 +312,34 @@ def test_dw3x3_tma_fwd_dgrad_wgrad(B, H, W, Cc, mode):
     assert float((dz.float().permute(0, 3, 1, 2) - want).norm() / want.norm()) < 1.5e-2
     refw = wr.grad[:, 0].permute(1, 2, 0).reshape(9, Cc)
     assert float((dwk - refw).norm() / refw.norm()) < 1e-2
+    # one-pass variant (input gradient + weight gradient from the same staged tiles), with a residual-path gradient
+    resid = torch.randn(B, H // 2, W // 2, Cc, device="cuda").bfloat16()
+    for rmode in (0, 1, 2):
+        dz2 = torch.zeros_like(x)
+        dwk2 = torch.zeros(9, Cc, device="cuda")
+        L.check(lib.crackfl_dw3x3_bwd_tma(g.data_ptr(), x.data_ptr(), w.data_ptr(), bn.data_ptr(), resid.data_ptr() if rmode else 0,
+                                          dz2.data_ptr(), dwk2.data_ptr(), B, H, W, Cc, mode, rmode, _st()))
+        torch.cuda.synchronize()
+        up = torch.zeros(B, Cc, H, W, device="cuda")
+        up[:, :, ::2, ::2] = resid.float().permute(0, 3, 1, 2)
+        mask = (pre.detach() > 0).float()
+        want2 = want if rmode == 0 else (want + up if rmode == 1 else want + mask * up)
+        assert float((dz2.float().permute(0, 3, 1, 2) - want2).norm() / want2.norm()) < 1.5e-2, rmode
+        assert float((dwk2 - refw).norm() / refw.norm()) < 1e-2, rmode
+    # one-pass variant (input gradient + weight gradient from the same staged tiles), with a residual-path gradient
+    resid = torch.randn(B, H // 2, W // 2, Cc, device="cuda").bfloat16()
+    for rmode in (0, 1, 2):
+        dz2 = torch.zeros_like(x)
+        dwk2 = torch.zeros(9, Cc, device="cuda")
+        L.check(lib.crackfl_dw3x3_bwd_tma(g.data_ptr(), x.data_ptr(), w.data_ptr(), bn.data_ptr(), resid.data_ptr() if rmode else 0,
+                                          dz2.data_ptr(), dwk2.data_ptr(), B, H, W, Cc, mode, rmode, _st()))
+        torch.cuda.synchronize()
+        up = torch.zeros(B, Cc, H, W, device="cuda")
+        up[:, :, ::2, ::2] = resid.float().permute(0, 3, 1, 2)
+        mask = (pre.detach() > 0).float()
+        want2 = want if rmode == 0 else (want + up if rmode == 1 else want + mask * up)
+        assert float((dz2.float().permute(0, 3, 1, 2) - want2).norm() / want2.norm()) < 1.5e-2, rmode
+        assert float((dwk2 - refw).norm() / refw.norm()) < 1e-2, rmode
 
 
 @pytest.mark.parametrize("B,H,W,c0", [(2, 32, 32, 32), (3, 48, 80, 64), (1, 30, 34, 32)])
