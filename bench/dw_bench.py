@@ -59,6 +59,7 @@ for r, c in ((S // 2, 32), (S // 2, 64), (S // 4, 64), (S // 4, 128), (S // 8, 1
         ("dw_fwd_bn", lambda: lib.crackfl_dw3x3_tma(x.data_ptr(), w.data_ptr(), bn.data_ptr(), None, out.data_ptr(), 0, 0, 0, B, r, r, c, 1, 0, 0, 0, st), 2 * n),
         ("dw_dgrad_bn", lambda: lib.crackfl_dw3x3_tma(g.data_ptr(), w.data_ptr(), 0, None, out.data_ptr(), x.data_ptr(), bn.data_ptr(), 0, B, r, r, c, 2, 1, 1, 0, st), 3 * n),
         ("dw_wgrad_bn", lambda: lib.crackfl_dw3x3_wgrad_tma(g.data_ptr(), x.data_ptr(), bn.data_ptr(), dwk.data_ptr(), B, r, r, c, 1, st), 2 * n),
+        ("dw_bwd_merged", lambda: lib.crackfl_dw3x3_bwd_tma(g.data_ptr(), x.data_ptr(), w.data_ptr(), bn.data_ptr(), 0, out.data_ptr(), dwk.data_ptr(), B, r, r, c, 1, 0, st), 3 * n),
         ("bn_bwd_reduce", lambda: lib.crackfl_bn_bwd_reduce(g.data_ptr(), 0, x.data_ptr(), bnfull.data_ptr(), sums.data_ptr(), B, r, r, c, 0, st), 2 * n),
         ("bn_bwd_apply", lambda: lib.crackfl_bn_bwd_apply(g.data_ptr(), 0, x.data_ptr(), bnfull.data_ptr(), sums.data_ptr(), out.data_ptr(), dg.data_ptr(), db.data_ptr(), B, r, r, c, 0, st), 3 * n),
     )

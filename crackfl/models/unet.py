@@ -64,6 +64,10 @@ class UNetEngine:
         self.dw_tma = os.environ.get("CRACKFL_DW_TMA", "1") != "0"
         self.gemm_stats = os.environ.get("CRACKFL_GEMM_STATS", "1") != "0"
         self.dw_merged = os.environ.get("CRACKFL_DW_MERGED", "1") != "0"
+        # measured: batching the split reductions per block (7 launches instead of 22) is 35-45 us SLOWER - the partial
+        # tiles fall out of L2 before they are reduced - so the per-layer reduction right behind each GEMM stays the default
+        self.wgrad_deferred = os.environ.get("CRACKFL_WGRAD_DEFERRED", "0") != "0"
+        self._wg_descs, self._wg_off, self._wg_max, self._wg_flushed = [], 0, 0, 0
         with torch.cuda.device(self.dev):
             self._alloc_params()
             self._build_ops_table()
@@ -235,15 +239,55 @@ class UNetEngine:
         prog.append((self.lib.crackfl_conv_simt_fwd, (X, self.op_ptr(opname), bias, add, Y, B, H, W, K, N, T)) + extra)
         return False
 
-    def _wgrad(self, prog, X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co):
-        if self.conv_impl == "tc":
+    def _wgrad(self, prog, X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co, cin_valid=0):
+        if self.conv_impl == "tc" and self.wgrad_deferred:
+            # split-K partial tiles now, ONE reduction launch per block later (_wgrad_flush); the workspace slice is
+            # assigned here, the pointers are patched in once the workspace size is known (_wgrad_resolve)
+            d = L.WgradRedDesc()
+            L.check(self.lib.crackfl_wgrad_plan(B, H, W, cin, cout, taps, s_tap, s_ci, s_co, cin_valid, C.byref(d)),
+                    "crackfl_wgrad_plan")
+            d.ws_off = self._wg_off
+            d.dw_off = (dW - self.grads.data_ptr()) // 4
+            self._wg_off += (d.need + 255) // 256 * 256
+            self._wg_max = max(self._wg_max, self._wg_off)
+            self._wg_descs.append(d)
+            prog.append(("WGRAD", (X, dY, B, H, W, cin, cout, taps, d.ws_off, d.need), "side"))
+        elif self.conv_impl == "tc":
             if "wgrad_ws" not in self._bufs:  # split-reduction workspace shared by all (stream-ordered) wgrad launches
                 self._new("wgrad_ws", (8 << 20,), torch.float32)
             ws = self._bufs["wgrad_ws"]
-            prog.append((self.lib.crackfl_wgrad_tc_ws, (X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co,
-                                                        ws.data_ptr(), ws.numel()), "side"))
+            prog.append((self.lib.crackfl_wgrad_tc_ws_cv, (X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co,
+                                                           ws.data_ptr(), ws.numel(), cin_valid), "side"))
         else:
             prog.append((self.lib.crackfl_wgrad_simt, (X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co), "side"))
+
+    def _wgrad_flush(self, prog):
+        """One reduction launch for the wgrad GEMMs recorded since the previous flush; their workspace is reused after it."""
+        n = len(self._wg_descs) - self._wg_flushed
+        if n > 0:
+            prog.append(("WREDUCE", (self._wg_flushed, n), "side"))
+            self._wg_flushed = len(self._wg_descs)
+            self._wg_off = 0
+
+    def _wgrad_resolve(self, prog):
+        if not self._wg_descs:
+            return prog
+        ws = self._new("wgrad_ws", (max(self._wg_max, 1024),), torch.float32)
+        arr = (L.WgradRedDesc * len(self._wg_descs))(*self._wg_descs)
+        self._bufs["wgrad_descs"] = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).clone().to(self.dev)
+        dptr, dsz = self._bufs["wgrad_descs"].data_ptr(), C.sizeof(L.WgradRedDesc)
+        out = []
+        for e in prog:
+            if e[0] == "WGRAD":
+                X, dY, B, H, W, cin, cout, taps, off, need = e[1]
+                out.append((self.lib.crackfl_wgrad_tc_deferred, (X, dY, B, H, W, cin, cout, taps, ws.data_ptr() + 4 * off, need),
+                            "side"))
+            elif e[0] == "WREDUCE":
+                i0, n = e[1]
+                out.append((self.lib.crackfl_wgrad_reduce_all, (dptr + i0 * dsz, n, ws.data_ptr(), self.grads.data_ptr()), "side"))
+            else:
+                out.append(e)
+        return out
 
     def _dw_bwd(self, prog, g, src, w, bn, resid_t, dz, dwk, B, H, W, C, mode, resid):
         """Depthwise backward: input gradient on the main stream, weight gradient on the side stream."""
@@ -457,6 +501,7 @@ class UNetEngine:
             self._wgrad(prog, b(src_res), b(drl), self.G(res.tensors[0]), B, lr_, lrw, cin, f, 1, 0, f, 1)
             prog.append((lib.crackfl_colsum, (b(drl), self.G(res.tensors[1]), B * lr_ * lrw, f), "side"))
             prog.append((None, None, "join_aux"))
+            self._wgrad_flush(prog)
             if j > 0:
                 prog.append((lib.crackfl_down2sum, (b(p + "da0"), b(f"d{j - 1}.s"), b(p + "T"), b(f"d{j - 1}.ds"),
                                                     B, lr_, lrw, cin)))
@@ -499,6 +544,8 @@ class UNetEngine:
             self._wgrad(prog, b(p + "d1"), b(p + "dy1"), self.G(sep1.tensors[1]), B, r, rw, cin, f, 1, 0, f, 1)
             # depthwise 1 (input = relu(x_k)); adds the residual-path gradient on the even pixels
             out = "dz0" if k == 0 else p + "dx"
+            if k > 0:
+                self._wgrad_flush(prog)  # (the first block's batch also takes the entry conv, flushed before Adam)
             prog.append((None, None, "join_aux"))
             self._dw_bwd(prog, b(p + "dd1"), b(xin), self.P(sep1.tensors[0]), 0, b(p + "Te"), b(out),
                          self.G(sep1.tensors[0]), B, r, rw, cin, 0, 2 if k == 0 else 1)
@@ -510,18 +557,17 @@ class UNetEngine:
         prog.append((lib.crackfl_bn_bwd_apply, (b("dz0"), 0, b("y0"), self._bnptr(bn0.name), self._zptr(bn0.name, "sums"),
                                                 b("dy0"), self.G(bn0.tensors[0]), self.G(bn0.tensors[1]), B, r, rw, c0, 0)))
         if self.entry_tc:
-            ws = self._bufs["wgrad_ws"]
-            prog.append((lib.crackfl_wgrad_tc_ws_cv, (b("x0col"), b("dy0"), self.G(conv0.tensors[0]), B, r, rw, 32, c0, 1,
-                                                      0, c0, 1, ws.data_ptr(), ws.numel(), 27), "side"))
+            self._wgrad(prog, b("x0col"), b("dy0"), self.G(conv0.tensors[0]), B, r, rw, 32, c0, 1, 0, c0, 1, cin_valid=27)
         else:
             prog.append((lib.crackfl_entry_conv_wgrad, (b("x_u8"), b("dy0"), self.G(conv0.tensors[0]), B, self.H, self.W, c0),
                          "side"))
+        self._wgrad_flush(prog)
         prog.append((None, None, "join"))
         # ---- optimiser (also zeroes the gradient arena)
         prog.append((lib.crackfl_adam_step, (self.arena.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(),
                                              self.v.data_ptr(), self.step.data_ptr(), self.spec.arena_numel, self.lr,
                                              self.b1, self.b2, self.eps)))
-        return prog
+        return self._wgrad_resolve(prog)
 
     def enc_out_name(self) -> str:
         return f"e{len(self.enc) - 1}.out"

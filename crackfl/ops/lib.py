@@ -29,6 +29,12 @@ class BnFin(C.Structure):
                 ("count", f32), ("eps", f32), ("momentum", f32)]
 
 
+class WgradRedDesc(C.Structure):
+    _fields_ = [("ws_off", i64), ("dw_off", i64), ("s_tap", i64), ("s_ci", i64), ("s_co", i64), ("need", i64),
+                ("groups", i32), ("ntn", i32), ("splits", i32), ("BN", i32), ("cw", i32), ("mblk", i32),
+                ("total_blocks", i32), ("cchunks", i32), ("cin_valid", i32), ("zl", i32)]
+
+
 class FedAggParams(C.Structure):
     _fields_ = [("client", vp * MAX_CLIENTS), ("coef", f32 * MAX_CLIENTS), ("out", vp * MAX_OUT),
                 ("num_clients", i32), ("num_out", i32), ("payload_bf16", i32), ("out_bf16", i32),
@@ -75,6 +81,9 @@ _SIGS = {
     "crackfl_wgrad_tc": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, vp],
     "crackfl_wgrad_tc_ws": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, vp, i64, vp],
     "crackfl_wgrad_tc_ws_cv": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, vp, i64, i32, vp],
+    "crackfl_wgrad_plan": [i32, i32, i32, i32, i32, i32, i64, i64, i64, i32, C.POINTER(WgradRedDesc)],
+    "crackfl_wgrad_tc_deferred": [vp, vp, i32, i32, i32, i32, i32, i32, vp, i64, vp],
+    "crackfl_wgrad_reduce_all": [vp, i32, vp, vp, vp],
     "crackfl_tc_selftest_supported": [],
     "crackfl_weight_prep": [vp, vp, vp, i32, vp],
     "crackfl_adam_step": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, vp],

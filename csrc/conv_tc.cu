@@ -928,6 +928,7 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
           // contention-free: this CTA's partial tile goes to its own slab, wgrad_reduce_k sums the slabs
           const long cta = ((long)blockIdx.x * gridDim.y + blockIdx.y) * gridDim.z + blockIdx.z;
           float4* wp = reinterpret_cast<float4*>(a.ws + (cta * 128 + r) * a.BN + c0);
+          if (valid)  // padding blocks are never read back
 #pragma unroll
           for (int j = 0; j < 32; j += 4)
             wp[j >> 2] = make_float4(__uint_as_float(raw[j]), __uint_as_float(raw[j + 1]), __uint_as_float(raw[j + 2]),
@@ -951,21 +952,27 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
 // gradient arena (one writer per element, no atomics).  A block is (256 / zl) float4 columns x zl split lanes: every
 // lane strides over the splits with four loads in flight, the lanes meet in shared memory, lane 0 writes.  (The first
 // version walked all splits serially per thread: 16-64 blocks x up to 293 dependent-latency loads, 13-29 us a launch.)
-__global__ void __launch_bounds__(256) wgrad_reduce_k(const float* __restrict__ ws, float* __restrict__ dW, int groups, int ntn,
-                                                      int splits, int BN, int cw, int mblk, int total_blocks, int cchunks,
-                                                      long s_tap, long s_ci, long s_co, int zl, int cin_valid) {
-  ck::pdl_enter();
-  __shared__ float4 sm[256];
+__device__ __forceinline__ void wgrad_reduce_body(const float* __restrict__ ws, float* __restrict__ dW, int groups, int ntn,
+                                                  int splits, int BN, int cw, int mblk, int total_blocks, int cchunks,
+                                                  long s_tap, long s_ci, long s_co, int zl, int cin_valid, int bid, int nblk,
+                                                  float4* sm) {
   const long per_tile = 128L * BN;
   const long total4 = (long)groups * ntn * per_tile / 4;
   const int vpb = 256 / zl;
   const int v = threadIdx.x % vpb, lane = threadIdx.x / vpb;
-  for (long base = (long)blockIdx.x * vpb; base < total4; base += (long)gridDim.x * vpb) {
+  for (long base = (long)bid * vpb; base < total4; base += (long)nblk * vpb) {
     const long i = (base + v) * 4;
-    const bool live = base + v < total4;
+    bool live = base + v < total4;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     const long gt = live ? i / per_tile : 0;  // g * ntn + nt
     const long in_tile = i - gt * per_tile;
+    {
+      // rows of padding blocks / padded input channels are neither read nor written (a 32-channel 1x1 layer fills only a
+      // quarter of the 128-row tile)
+      const int r_ = (int)(in_tile / BN);
+      const int blk_ = (int)(gt / ntn) * mblk + r_ / cw;
+      live = live && blk_ < total_blocks && (blk_ % cchunks) * cw + (r_ % cw) < cin_valid;
+    }
     if (live) {
       const float4* p = reinterpret_cast<const float4*>(ws + (gt * splits) * per_tile + in_tile);
       const long stride4 = per_tile / 4;
@@ -1002,6 +1009,26 @@ __global__ void __launch_bounds__(256) wgrad_reduce_k(const float* __restrict__ 
     float* d = dW + (long)t * s_tap + (long)ci * s_ci + (long)(nt * BN + c) * s_co;
     d[0] += acc.x; d[s_co] += acc.y; d[2 * s_co] += acc.z; d[3 * s_co] += acc.w;
   }
+}
+
+__global__ void __launch_bounds__(256) wgrad_reduce_k(const float* __restrict__ ws, float* __restrict__ dW, int groups, int ntn,
+                                                      int splits, int BN, int cw, int mblk, int total_blocks, int cchunks,
+                                                      long s_tap, long s_ci, long s_co, int zl, int cin_valid) {
+  ck::pdl_enter();
+  __shared__ float4 sm[256];
+  wgrad_reduce_body(ws, dW, groups, ntn, splits, BN, cw, mblk, total_blocks, cchunks, s_tap, s_ci, s_co, zl, cin_valid,
+                    blockIdx.x, gridDim.x, sm);
+}
+
+// every layer's split reduction in ONE launch at the end of the backward pass (blockIdx.y = layer): the per-layer
+// reduction launches were 22 x 5-12 us of mostly fixed cost
+__global__ void __launch_bounds__(256) wgrad_reduce_all_k(const crackfl_wgrad_red_desc* __restrict__ descs,
+                                                          const float* __restrict__ ws_base, float* __restrict__ dw_base) {
+  ck::pdl_enter();
+  __shared__ float4 sm[256];
+  const crackfl_wgrad_red_desc d = descs[blockIdx.y];
+  wgrad_reduce_body(ws_base + d.ws_off, dw_base + d.dw_off, d.groups, d.ntn, d.splits, d.BN, d.cw, d.mblk, d.total_blocks,
+                    d.cchunks, d.s_tap, d.s_ci, d.s_co, d.zl, d.cin_valid, blockIdx.x, gridDim.x, sm);
 }
 
 // ----------------------------------------------------------------------------------------------------------
@@ -1326,9 +1353,10 @@ v2_path:
 
 // cin_valid < Cin: the last Cin - cin_valid input channels are zero padding; their gradient rows are not written
 // (workspace path only)
-int crackfl_wgrad_tc_ws_cv(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps,
-                           long s_tap, long s_ci, long s_co, float* workspace, long workspace_floats, int cin_valid,
-                           cudaStream_t st) {
+// mode 0: launch + per-layer reduction; 1: launch only, fill *desc for crackfl_wgrad_reduce_all; 2: plan only (no launch)
+static int wgrad_impl(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps,
+                      long s_tap, long s_ci, long s_co, float* workspace, long workspace_floats, int cin_valid,
+                      int mode, crackfl_wgrad_red_desc* desc, cudaStream_t st) {
   if (Cin % 32 || Cout % 32 || (taps != 1 && taps != 9)) return (int)cudaErrorInvalidValue;
   WgradArgs a;
   a.dW = dW; a.s_tap = s_tap; a.s_ci = s_ci; a.s_co = s_co;
@@ -1369,6 +1397,19 @@ int crackfl_wgrad_tc_ws_cv(const void* X, const void* dY, float* dW, int B, int 
   if (stages < 1) stages = 1;
   a.stages = stages;
   const size_t smem = (size_t)stages * stage_bytes + 1024 + 256;
+  const long need = (long)groups * ntn * splits * 128L * a.BN;
+  int zl = 1;
+  {
+    const long total4 = (long)groups * ntn * 128L * a.BN / 4;
+    while (zl * 2 <= splits && zl < 32 && total4 * (zl * 2) / 256 <= 148 * 8) zl *= 2;  // split lanes per block
+  }
+  if (desc) {
+    desc->s_tap = s_tap; desc->s_ci = s_ci; desc->s_co = s_co; desc->need = need;
+    desc->groups = groups; desc->ntn = ntn; desc->splits = splits; desc->BN = a.BN; desc->cw = a.cw; desc->mblk = a.mblk;
+    desc->total_blocks = a.total_blocks; desc->cchunks = Cin / a.cw; desc->cin_valid = cin_valid > 0 ? cin_valid : Cin;
+    desc->zl = zl;
+  }
+  if (mode == 2) return 0;
   CUtensorMap tmX, tmDY;
   const int dX[4] = {Cin, W, H, B}, bX[4] = {a.cw, a.g.TW, a.g.TH, a.g.TB};
   int rc = get_map(X, 4, dX, bX, a.cw * 2, &tmX);
@@ -1383,21 +1424,45 @@ int crackfl_wgrad_tc_ws_cv(const void* X, const void* dY, float* dW, int B, int 
     attr_set = true;
   }
   dim3 grid(groups, ntn, splits);
-  const long need = (long)groups * ntn * splits * 128L * a.BN;
   a.ws = (workspace && workspace_floats >= need) ? workspace : nullptr;
-  if (!a.ws && cin_valid > 0 && cin_valid < Cin) return (int)cudaErrorInvalidValue;
+  if (!a.ws && ((cin_valid > 0 && cin_valid < Cin) || mode == 1)) return (int)cudaErrorInvalidValue;
   ck::launch(wgrad_tc_k, grid, 192, smem, st, tmX, tmDY, a);
   CK_LAUNCH_CHECK();
-  if (a.ws) {
+  if (a.ws && mode == 0) {
     const long total4 = (long)groups * ntn * 128L * a.BN / 4;
-    int zl = 1;
-    while (zl * 2 <= splits && zl < 32 && total4 * (zl * 2) / 256 <= 148 * 8) zl *= 2;  // split lanes per block
     long blocks = (total4 * zl + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
     ck::launch(wgrad_reduce_k, (int)blocks, 256, 0, st, a.ws, dW, groups, ntn, splits, a.BN, a.cw, a.mblk, a.total_blocks, Cin / a.cw,
                s_tap, s_ci, s_co, zl, cin_valid > 0 ? cin_valid : Cin);
     CK_LAUNCH_CHECK();
   }
+  return 0;
+}
+
+int crackfl_wgrad_tc_ws_cv(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps,
+                           long s_tap, long s_ci, long s_co, float* workspace, long workspace_floats, int cin_valid,
+                           cudaStream_t st) {
+  return wgrad_impl(X, dY, dW, B, H, W, Cin, Cout, taps, s_tap, s_ci, s_co, workspace, workspace_floats, cin_valid, 0, nullptr, st);
+}
+
+int crackfl_wgrad_plan(int B, int H, int W, int Cin, int Cout, int taps, long s_tap, long s_ci, long s_co, int cin_valid,
+                       crackfl_wgrad_red_desc* desc) {
+  return wgrad_impl(nullptr, nullptr, nullptr, B, H, W, Cin, Cout, taps, s_tap, s_ci, s_co, nullptr, 0, cin_valid, 2, desc, 0);
+}
+
+int crackfl_wgrad_tc_deferred(const void* X, const void* dY, int B, int H, int W, int Cin, int Cout, int taps, float* ws_layer,
+                              long ws_floats, cudaStream_t st) {
+  return wgrad_impl(X, dY, nullptr, B, H, W, Cin, Cout, taps, 0, 0, 0, ws_layer, ws_floats, 0, 1, nullptr, st);
+}
+
+int crackfl_wgrad_reduce_all(const crackfl_wgrad_red_desc* descs_dev, int n, const float* ws_base, float* dw_base,
+                             cudaStream_t st) {
+  if (n <= 0) return 0;
+  static int gx = -1;
+  if (gx < 0) { const char* e = getenv("CRACKFL_WRED_GRID"); gx = e ? atoi(e) : 592; }
+  dim3 grid(gx, n);
+  ck::launch(wgrad_reduce_all_k, grid, 256, 0, st, descs_dev, ws_base, dw_base);
+  CK_LAUNCH_CHECK();
   return 0;
 }
 

@@ -146,6 +146,21 @@ int crackfl_wgrad_tc_ws(const void* X, const void* dY, float* dW, int B, int H, 
 int crackfl_wgrad_tc_ws_cv(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps,
                            long s_tap, long s_ci, long s_co, float* workspace, long workspace_floats, int cin_valid,
                            cudaStream_t stream);
+/* deferred split reduction: every wgrad GEMM of the step writes its per-CTA partial tiles into its own slice of one
+ * workspace and ONE launch at the end of the backward pass reduces them all into the gradient arena. */
+typedef struct {
+  long ws_off;  /* float offset of the layer's partial tiles in the workspace (caller fills) */
+  long dw_off;  /* float offset of the gradient tensor (incl. any tap base) in the gradient arena (caller fills) */
+  long s_tap, s_ci, s_co;
+  long need;    /* workspace floats the layer uses */
+  int groups, ntn, splits, BN, cw, mblk, total_blocks, cchunks, cin_valid, zl;
+} crackfl_wgrad_red_desc;
+int crackfl_wgrad_plan(int B, int H, int W, int Cin, int Cout, int taps, long s_tap, long s_ci, long s_co, int cin_valid,
+                       crackfl_wgrad_red_desc* desc_host);
+int crackfl_wgrad_tc_deferred(const void* X, const void* dY, int B, int H, int W, int Cin, int Cout, int taps, float* ws_layer,
+                              long ws_floats, cudaStream_t stream);
+int crackfl_wgrad_reduce_all(const crackfl_wgrad_red_desc* descs_dev, int n, const float* ws_base, float* dw_base,
+                             cudaStream_t stream);
 int crackfl_tc_selftest_supported(void);
 
 /* ---- optimiser / weight re-layout ------------------------------------------------------------ */
