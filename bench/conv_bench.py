@@ -62,6 +62,7 @@ for name, r, cin, n, taps in shapes:
     flops = 2.0 * M * cin * n * taps
     for kind, fn, byt in (
         ("fwd", lambda: L.check(lib.crackfl_conv_tc_fwd(x.data_ptr(), w.data_ptr(), 0, 0, y.data_ptr(), stats.data_ptr(), B, r, r, cin, n, taps, st)), (M * cin + M * n) * 2),
+        ("fwd_nostat", lambda: L.check(lib.crackfl_conv_tc_fwd(x.data_ptr(), w.data_ptr(), 0, 0, y.data_ptr(), 0, B, r, r, cin, n, taps, st)), (M * cin + M * n) * 2),
         ("dgrad", lambda: L.check(lib.crackfl_conv_tc_fwd(dy.data_ptr(), wd.data_ptr(), 0, 0, dx.data_ptr(), 0, B, r, r, n, cin, taps, st)), (M * cin + M * n) * 2),
         ("wgrad", lambda: L.check(lib.crackfl_wgrad_tc(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), B, r, r, cin, n, taps, cin * n, n, 1, st)), (M * cin + M * n) * 2),
     ):
