@@ -64,6 +64,7 @@ class UNetEngine:
         self.dw_tma = os.environ.get("CRACKFL_DW_TMA", "1") != "0"
         self.gemm_stats = os.environ.get("CRACKFL_GEMM_STATS", "1") != "0"
         self.dw_merged = os.environ.get("CRACKFL_DW_MERGED", "1") != "0"
+        self.pool_bwd_fused = os.environ.get("CRACKFL_POOL_BWD_FUSED", "1") != "0"
         # measured: batching the split reductions per block (7 launches instead of 22) is 35-45 us SLOWER - the partial
         # tiles fall out of L2 before they are reduced - so the per-layer reduction right behind each GEMM stays the default
         self.wgrad_deferred = os.environ.get("CRACKFL_WGRAD_DEFERRED", "0") != "0"
@@ -522,9 +523,13 @@ class UNetEngine:
             prog.append((lib.crackfl_colsum, (b(dx_next), self.G(res.tensors[1]), B * r2 * rw2, f), "side"))
             # max-pool + BN2
             # max-pool backward once into dd2 (reused below as the pointwise dgrad output), then DIRECT-mode BN backward
-            prog.append((lib.crackfl_pool_bwd, (b(dx_next), b(p + "arg"), b(p + "dd2"), B, r, rw, f)))
-            prog.append((lib.crackfl_bn_bwd_reduce, (b(p + "dd2"), 0, b(p + "y2"), self._bnptr(bn2.name),
-                                                     self._zptr(bn2.name, "sums"), B, r, rw, f, 0)))
+            if self.pool_bwd_fused:
+                prog.append((lib.crackfl_pool_bwd_bn, (b(dx_next), b(p + "arg"), b(p + "y2"), self._bnptr(bn2.name), b(p + "dd2"),
+                                                       self._zptr(bn2.name, "sums"), B, r, rw, f)))
+            else:
+                prog.append((lib.crackfl_pool_bwd, (b(dx_next), b(p + "arg"), b(p + "dd2"), B, r, rw, f)))
+                prog.append((lib.crackfl_bn_bwd_reduce, (b(p + "dd2"), 0, b(p + "y2"), self._bnptr(bn2.name),
+                                                         self._zptr(bn2.name, "sums"), B, r, rw, f, 0)))
             prog.append((lib.crackfl_bn_bwd_apply, (b(p + "dd2"), 0, b(p + "y2"), self._bnptr(bn2.name),
                                                     self._zptr(bn2.name, "sums"), b(p + "dy2"), self.G(bn2.tensors[0]),
                                                     self.G(bn2.tensors[1]), B, r, rw, f, 0)))

@@ -70,6 +70,7 @@ _SIGS = {
     "crackfl_pool_add_fwd": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],
     "crackfl_dec_combine_fwd": [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_pool_bwd": [vp, vp, vp, i32, i32, i32, i32, vp],
+    "crackfl_pool_bwd_bn": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],
     "crackfl_down2sum": [vp, vp, vp, vp, i32, i32, i32, i32, vp],
     "crackfl_relu_bwd_add": [vp, vp, vp, vp, i64, vp],
     "crackfl_colsum": [vp, vp, i64, i32, vp],

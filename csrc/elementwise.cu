@@ -650,6 +650,75 @@ __global__ void __launch_bounds__(TPB, 3) pool_bwd_k(const __nv_bfloat16* __rest
   }
 }
 
+// max-pool backward + the BN-backward reductions of the layer below it, in one pass (second version of the pair
+// pool_bwd_k + bn_bwd_reduce_k<0>): a thread owns one 2x2 block of input pixels x 8 channels, reads the (<= 4) pooling
+// windows that cover it once (the per-pixel version read 9 windows per 2x2 block), writes the four dz vectors and
+// accumulates sum dz and sum dz * (y - mean) on the way.
+__global__ void __launch_bounds__(TPB, 2) pool_bwd_bn_k(const __nv_bfloat16* __restrict__ g, const uint8_t* __restrict__ arg,
+                                                        const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
+                                                        __nv_bfloat16* __restrict__ dz, float* __restrict__ sums, int B, int H,
+                                                        int W, int C, int items_per_block) {
+  ck::pdl_enter();
+  __shared__ float sm[TPB * 8];
+  const int c8 = C >> 3, Ho = H >> 1, Wo = W >> 1, lanes = TPB / c8;
+  const int cv = threadIdx.x % c8, lane = threadIdx.x / c8;
+  float mu[8], s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  load8f(bn + 2 * C + cv * 8, mu);
+  const int P2 = B * Ho * Wo;
+  const int p0 = blockIdx.x * items_per_block;
+  const int p1 = min(P2, p0 + items_per_block);
+  for (int p = p0 + lane; p < p1; p += lanes) {
+    const int j = p % Wo, i = (p / Wo) % Ho, b = p / (Wo * Ho);
+    float d[4][8];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) d[q][e] = 0.f;
+    // window (i + di, j + dj), di, dj in {0, -1}; pixel (r, c) of the 2x2 block sits at offset (r - 2di)*3 + (c - 2dj)
+#pragma unroll
+    for (int wi = 0; wi < 4; ++wi) {
+      const int di = -(wi >> 1), dj = -(wi & 1);
+      const int qi = i + di, qj = j + dj;
+      if (qi < 0 || qj < 0) continue;
+      const int qv = ((b * Ho + qi) * Wo + qj) * c8 + cv;
+      const uint2 a = __ldg(reinterpret_cast<const uint2*>(arg + (size_t)qv * 8));
+      float gq[8];
+      unpack8(ldg16(g + (size_t)qv * 8), gq);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int r = q >> 1, c = q & 1;
+        const int rr = r - 2 * di, cc = c - 2 * dj;  // position inside the 3x3 window
+        if (rr > 2 || cc > 2) continue;             // compile-time: this window does not cover that pixel
+        const int off = rr * 3 + cc;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int idx = ((e < 4 ? a.x : a.y) >> ((e & 3) * 8)) & 0xff;
+          if (idx == off) d[q][e] += gq[e];
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int h = 2 * i + (q >> 1), w = 2 * j + (q & 1);
+      const size_t v = ((size_t)(b * H + h) * W + w) * c8 + cv;
+      float yv[8];
+      unpack8(ldg16(y + v * 8), yv);
+      // the reductions see the bf16-rounded dz, exactly what the apply pass will read back
+      const uint4 pk = pack8(d[q]);
+      float dr[8];
+      unpack8(pk, dr);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        s1[e] += dr[e];
+        s2[e] = fmaf(dr[e], yv[e] - mu[e], s2[e]);
+      }
+      stg16(dz + v * 8, pk);
+    }
+  }
+  block_channel_atomic(s1, c8, sm, sums);
+  block_channel_atomic(s2, c8, sm, sums + C);
+}
+
 // column sum of a [P][C] bf16 matrix into fp32 (bias gradient of the residual convs)
 __global__ void __launch_bounds__(TPB) colsum_k(const __nv_bfloat16* __restrict__ g, float* __restrict__ out, long P, int C,
                                                 int pix_per_block) {
@@ -1442,6 +1511,19 @@ int crackfl_dec_combine_fwd_fin(const void* y, const crackfl_bn_fin* fin, const 
 }  // extern "C"
 
 extern "C" {
+
+int crackfl_pool_bwd_bn(const void* g, const void* arg, const void* y, const float* bn, void* dz, float* sums, int B, int H,
+                        int W, int C, cudaStream_t st) {
+  CK_FITS32((long)B * H * W * C);
+  if ((H | W) & 1 || TPB % (C >> 3)) return (int)cudaErrorInvalidValue;
+  const int P2 = B * (H / 2) * (W / 2), lanes = TPB / (C >> 3);
+  int ipb = (P2 + 148 * 2 - 1) / (148 * 2);
+  ipb = (ipb + lanes - 1) / lanes * lanes;
+  ck::launch(pool_bwd_bn_k, (P2 + ipb - 1) / ipb, TPB, 0, st, (const __nv_bfloat16*)g, (const uint8_t*)arg,
+             (const __nv_bfloat16*)y, bn, (__nv_bfloat16*)dz, sums, B, H, W, C, ipb);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
 
 int crackfl_pool_bwd(const void* g, const void* arg, void* dz, int B, int H, int W, int C, cudaStream_t st) {
   CK_FITS32((long)B * H * W * C);

@@ -112,6 +112,9 @@ int crackfl_dec_combine_fwd_fin(const void* y, const crackfl_bn_fin* fin, const 
                                 int H, int W, int C, int rl_up, cudaStream_t stream);
 /* max-pool backward: scatter-free gather of g [B,H/2,W/2,C] through the arg-max map into dz [B,H,W,C] */
 int crackfl_pool_bwd(const void* g, const void* argmax_u8, void* dz, int B, int H, int W, int C, cudaStream_t stream);
+/* the same plus the BN-backward reductions of the layer below (sums = [sum dz C][sum dz*(y-mean) C], pre-zeroed), one pass */
+int crackfl_pool_bwd_bn(const void* g, const void* argmax_u8, const void* y, const float* bn, void* dz, float* sums, int B,
+                        int H, int W, int C, cudaStream_t stream);
 int crackfl_down2sum(const void* in, const void* mask_or_null, const void* add_or_null, void* out, int B, int Ho, int Wo,
                      int C, cudaStream_t stream);
 int crackfl_relu_bwd_add(const void* g, const void* x, const void* add_or_null, void* out, long numel, cudaStream_t stream);

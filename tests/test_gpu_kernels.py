@@ -382,3 +382,35 @@ def test_entry_conv_tensor_core_path(B, H, W, c0):
     got = dw[:27 * c0].reshape(3, 3, 3, c0)
     assert float((got - gref).norm() / gref.norm()) < 1e-2
     assert float(dw[27 * c0:].abs().max()) == 0.0  # the padded rows are not written
+
+
+@pytest.mark.parametrize("B,H,W,Cc", [(2, 16, 16, 64), (3, 8, 12, 128), (1, 32, 32, 256)])
+def test_pool_bwd_bn_fused_matches_two_pass(B, H, W, Cc):
+    """max-pool backward + BN-backward reductions in one pass vs crackfl_pool_bwd followed by crackfl_bn_bwd_reduce."""
+    L, lib = _lib()
+    torch.manual_seed(5)
+    Ho, Wo = H // 2, W // 2
+    g = torch.randn(B, Ho, Wo, Cc, device="cuda").bfloat16()
+    rr = torch.randint(0, 3, (B, Ho, Wo, Cc), device="cuda")
+    cc = torch.randint(0, 3, (B, Ho, Wo, Cc), device="cuda")
+    rr[:, Ho - 1] = rr[:, Ho - 1].clamp(max=1)  # the bottom / right windows only cover two rows / columns
+    cc[:, :, Wo - 1] = cc[:, :, Wo - 1].clamp(max=1)
+    arg = (rr * 3 + cc).to(torch.uint8)
+    y = torch.randn(B, H, W, Cc, device="cuda").bfloat16()
+    bn = torch.cat([torch.ones(Cc, device="cuda"), torch.zeros(Cc, device="cuda"), torch.randn(Cc, device="cuda") * 0.1,
+                    torch.ones(Cc, device="cuda")])
+    dz_a, dz_b = torch.zeros_like(y), torch.zeros_like(y)
+    s_a, s_b = torch.zeros(2 * Cc, device="cuda"), torch.zeros(2 * Cc, device="cuda")
+    L.check(lib.crackfl_pool_bwd(g.data_ptr(), arg.data_ptr(), dz_a.data_ptr(), B, H, W, Cc, _st()))
+    L.check(lib.crackfl_bn_bwd_reduce(dz_a.data_ptr(), 0, y.data_ptr(), bn.data_ptr(), s_a.data_ptr(), B, H, W, Cc, 0, _st()))
+    L.check(lib.crackfl_pool_bwd_bn(g.data_ptr(), arg.data_ptr(), y.data_ptr(), bn.data_ptr(), dz_b.data_ptr(), s_b.data_ptr(),
+                                    B, H, W, Cc, _st()))
+    torch.cuda.synchronize()
+    assert torch.equal(dz_a, dz_b)
+    assert float((s_a - s_b).abs().max() / (s_a.abs().max() + 1e-6)) < 1e-4
+    # and against a direct scatter
+    ref = torch.zeros(B, H, W, Cc, device="cuda")
+    bi, qi, qj, ci = torch.meshgrid(torch.arange(B, device="cuda"), torch.arange(Ho, device="cuda"),
+                                    torch.arange(Wo, device="cuda"), torch.arange(Cc, device="cuda"), indexing="ij")
+    ref.index_put_((bi, 2 * qi + rr, 2 * qj + cc, ci), g.float(), accumulate=True)
+    assert float((dz_b.float() - ref).abs().max()) < 0.05
