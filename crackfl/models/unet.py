@@ -458,14 +458,23 @@ class UNetEngine:
     def _build_train(self):
         lib, B, b = self.lib, self.B, self.b
         prog = self._build_forward(training=True, with_mask=True, prob=False)
+        self.fwd_prog = list(prog)  # training-mode forward incl. the loss head (cross-checks, finite differences)
         self.n_fwd = len(prog)
         (conv0, bn0), encs, decs, head = self._layer_iter()
         ts = self.spec.tensors
         dl = self.dec[-1]
         last = f"d{dl['j']}."
-        prog.append((lib.crackfl_head_bwd, (b(last + "s"), self.P(head.tensors[0]), self.P(head.tensors[1]), b("mask_u8"),
-                                            self._acc_ptr(), b(last + "ds"), self.G(head.tensors[0]), self.G(head.tensors[1]),
-                                            B, dl["r"], dl["rw"], dl["f"], self.use_dice, self.dice_smooth, 1.0)))
+        if not self.use_dice and os.environ.get("CRACKFL_HEAD_FUSED", "1") != "0":
+            # plain BCE: the loss head's forward metrics and its backward in one pass (head_fwd is not launched)
+            prog.pop()
+            self.n_fwd = len(prog)
+            prog.append((lib.crackfl_head_fwd_bwd, (b(last + "s"), self.P(head.tensors[0]), self.P(head.tensors[1]), b("mask_u8"),
+                                                    self._acc_ptr(), b(last + "ds"), self.G(head.tensors[0]),
+                                                    self.G(head.tensors[1]), B, dl["r"], dl["rw"], dl["f"], 1.0)))
+        else:
+            prog.append((lib.crackfl_head_bwd, (b(last + "s"), self.P(head.tensors[0]), self.P(head.tensors[1]), b("mask_u8"),
+                                                self._acc_ptr(), b(last + "ds"), self.G(head.tensors[0]), self.G(head.tensors[1]),
+                                                B, dl["r"], dl["rw"], dl["f"], self.use_dice, self.dice_smooth, 1.0)))
         # ---- decoder backward
         for d, (ct1, bn1, ct2, bn2, res) in reversed(list(zip(self.dec, decs))):
             j, r, rw, cin, f = d["j"], d["r"], d["rw"], d["cin"], d["f"]

@@ -151,7 +151,7 @@ def directional_fd_check(spec: UNetSpec = REFERENCE_SPEC, B=8, H=64, W=64, seed=
     def loss_at(flat):
         eng.arena.copy_(flat)
         eng.zero_region.zero_()
-        eng._run(eng.train_prog[:eng.n_fwd])
+        eng._run(eng.fwd_prog)
         a = eng.zero_region[eng.acc_off:eng.acc_off + 6].cpu().numpy()
         return float(a[0]) / float(a[5])
 

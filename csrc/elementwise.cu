@@ -823,7 +823,8 @@ __global__ void __launch_bounds__(TPB) head_bwd_k(const __nv_bfloat16* __restric
                                                   const float* __restrict__ bias, const uint8_t* __restrict__ mask,
                                                   const float* __restrict__ sums, __nv_bfloat16* __restrict__ ds,
                                                   float* __restrict__ dw, float* __restrict__ db, int B, int Hl, int Wl, int C,
-                                                  int use_dice, float dice_smooth, float loss_scale) {
+                                                  int use_dice, float dice_smooth, float loss_scale,
+                                                  float* __restrict__ acc_out) {
   ck::pdl_enter();
   extern __shared__ float sh[];  // w[C] | reduction scratch [TPB*8]
   float* sw = sh;
@@ -843,6 +844,7 @@ __global__ void __launch_bounds__(TPB) head_bwd_k(const __nv_bfloat16* __restric
   }
   float dwacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   float dbl = 0.f;
+  float am[5] = {0, 0, 0, 0, 0};  // acc_out != NULL (plain BCE): the forward's loss / metric sums, so head_fwd_k is not launched
   const long iters = (total + stride - 1) / stride;
   for (long it = 0; it < iters; ++it) {
     const long g = it * stride + (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -861,11 +863,24 @@ __global__ void __launch_bounds__(TPB) head_bwd_k(const __nv_bfloat16* __restric
     const long base = (b * Hf + 2 * hl) * Wf + 2 * wl;
     const bool inside = (pr >= 1e-7f) && (pr <= 1.f - 1e-7f);  // clip_by_value passes no gradient outside
     float dl = 0.f;
+    const bool metrics = acc_out != nullptr && cv == 0;
+    float lp = 0.f, lq = 0.f;
+    if (metrics) {
+      const float pc = fminf(fmaxf(pr, 1e-7f), 1.f - 1e-7f);
+      lp = __logf(pc); lq = __logf(1.f - pc);
+    }
 #pragma unroll
     for (int d = 0; d < 4; ++d) {
       const float yv = mask[base + (d >> 1) * Wf + (d & 1)] ? 1.f : 0.f;
       if (inside) dl += (pr - yv) * invn;
       if (use_dice) dl += -(2.f * yv * dden - dnum) / (dden * dden) * pr * (1.f - pr);
+      if (metrics) {
+        am[0] -= yv * lp + (1.f - yv) * lq;
+        am[1] += ((pr > 0.5f) == (yv > 0.5f)) ? 1.f : 0.f;
+        am[2] += pr * yv;
+        am[3] += pr;
+        am[4] += yv;
+      }
     }
     dl *= loss_scale;
     if (cv == 0) dbl += dl;
@@ -880,6 +895,21 @@ __global__ void __launch_bounds__(TPB) head_bwd_k(const __nv_bfloat16* __restric
   block_channel_atomic(dwacc, c8, sm, dw);
   dbl = warp_sum(dbl);
   if ((threadIdx.x & 31) == 0) atomicAdd(db, dbl);
+  if (acc_out) {
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      const float v = warp_sum(am[k]);
+      if ((threadIdx.x & 31) == 0) sm[k * (TPB / 32) + (threadIdx.x >> 5)] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 5) {
+      float v = 0.f;
+      for (int i = 0; i < TPB / 32; ++i) v += sm[threadIdx.x * (TPB / 32) + i];
+      atomicAdd(acc_out + threadIdx.x, v);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(acc_out + 5, (float)(P * 4));
+  }
 }
 
 
@@ -1428,7 +1458,19 @@ int crackfl_head_bwd(const void* s, const float* w, const float* bias, const voi
   const long P = (long)B * Hl * Wl;
   ck::launch(head_bwd_k, grid_for(P * (C / 8), 148 * 8), TPB, (C + TPB * 8) * sizeof(float), st, 
       (const __nv_bfloat16*)s, w, bias, (const uint8_t*)mask_u8, sums, (__nv_bfloat16*)ds, dw, db, B, Hl, Wl, C, use_dice,
-      dice_smooth, loss_scale);
+      dice_smooth, loss_scale, (float*)nullptr);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+// plain-BCE training: forward metrics (loss / accuracy / dice sums into acc_out[6]) and the backward in ONE pass over s
+// (the BCE gradient needs nothing global but 1/N); with Dice the two-kernel sequence head_fwd -> head_bwd is required
+int crackfl_head_fwd_bwd(const void* s, const float* w, const float* bias, const void* mask_u8, float* acc_out, void* ds,
+                         float* dw, float* db, int B, int Hl, int Wl, int C, float loss_scale, cudaStream_t st) {
+  const long P = (long)B * Hl * Wl;
+  ck::launch(head_bwd_k, grid_for(P * (C / 8), 148 * 8), TPB, (C + TPB * 8) * sizeof(float), st,
+      (const __nv_bfloat16*)s, w, bias, (const uint8_t*)mask_u8, (const float*)nullptr, (__nv_bfloat16*)ds, dw, db, B, Hl, Wl, C,
+      0, 1.0f, loss_scale, acc_out);
   CK_LAUNCH_CHECK();
   return 0;
 }

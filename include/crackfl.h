@@ -127,6 +127,9 @@ int crackfl_head_fwd(const void* s, const float* w, const float* bias, const voi
 int crackfl_head_bwd(const void* s, const float* w, const float* bias, const void* mask_u8, const float* sums, void* ds,
                      float* dw, float* db, int B, int Hl, int Wl, int C, int use_dice, float dice_smooth, float loss_scale,
                      cudaStream_t stream);
+/* plain-BCE training step: forward metrics (acc_out[6], pre-zeroed) + backward in one pass over s */
+int crackfl_head_fwd_bwd(const void* s, const float* w, const float* bias, const void* mask_u8, float* acc_out, void* ds,
+                         float* dw, float* db, int B, int Hl, int Wl, int C, float loss_scale, cudaStream_t stream);
 
 /* ---- GEMM-shaped convolutions ---------------------------------------------------------------- */
 /* CUDA-core implicit GEMM (cross-check + odd shapes).  Wk[N][taps*Cin] bf16, taps in {1,9}. */
