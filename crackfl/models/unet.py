@@ -82,7 +82,7 @@ class UNetEngine:
         self._graphs: Dict[str, torch.cuda.CUDAGraph] = {}
         self._side_stream = torch.cuda.Stream(self.dev)
         self._aux_stream = torch.cuda.Stream(self.dev)
-        self.launches_per_step = sum(1 for e in self.train_prog if e[0] is not None) + 2  # + adam tick + metric accumulation
+        self.launches_per_step = sum(1 for e in self.train_prog if e[0] is not None)
 
     # ------------------------------------------------------------------ allocation
     def _new(self, name: str, shape, dtype=torch.bfloat16) -> torch.Tensor:
@@ -578,9 +578,11 @@ class UNetEngine:
         self._wgrad_flush(prog)
         prog.append((None, None, "join"))
         # ---- optimiser (also zeroes the gradient arena)
-        prog.append((lib.crackfl_adam_step, (self.arena.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(),
-                                             self.v.data_ptr(), self.step.data_ptr(), self.spec.arena_numel, self.lr,
-                                             self.b1, self.b2, self.eps)))
+        # Adam, its step tick and the metric accumulation in one launch (counter slot acc_off + 8 of the zeroed region)
+        prog.append((lib.crackfl_adam_step_tail, (self.arena.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(),
+                                                  self.v.data_ptr(), self.step.data_ptr(), self.spec.arena_numel, self.lr,
+                                                  self.b1, self.b2, self.eps, self._acc_ptr() + 4 * 8,
+                                                  self.metrics_total.data_ptr(), self._acc_ptr(), 6)))
         return self._wgrad_resolve(prog)
 
     def enc_out_name(self) -> str:
@@ -630,7 +632,7 @@ class UNetEngine:
     def _step_body(self, prog, accumulate: bool):
         self.zero_region.zero_()
         self._run(prog)
-        if accumulate:
+        if accumulate and prog is not self.train_prog:  # the train schedule accumulates inside its Adam launch
             st = torch.cuda.current_stream(self.dev).cuda_stream
             L.check(self.lib.crackfl_accum_small(self.metrics_total.data_ptr(), self._acc_ptr(), 6, st))
 

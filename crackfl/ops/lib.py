@@ -90,6 +90,7 @@ _SIGS = {
     "crackfl_weight_prep": [vp, vp, vp, i32, vp],
     "crackfl_adam_step": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, vp],
     "crackfl_f32_to_bf16": [vp, vp, i64, vp],
+    "crackfl_adam_step_tail": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, vp, vp, vp, i32, vp],
     "crackfl_accum_small": [vp, vp, i32, vp],
     "crackfl_publish_delta": [vp, vp, vp, i64, vp],
     "crackfl_synth_cracks": [vp, vp, i32, i32, i32, C.c_uint, vp],

@@ -11,16 +11,23 @@ namespace {
 __global__ void adam_tick_k(int* __restrict__ step) {
   ck::pdl_enter(); *step += 1; }
 
+// tail != NULL: the step counter tick and the metric accumulation ride along (two tiny launches less per step): every
+// block uses t = *step + 1, block 0 adds the step's metric sums to the running totals, and the LAST block to finish
+// (counter tail[0], zeroed with the step's scratch region) publishes the new step count.
 __global__ void __launch_bounds__(256) adam_k(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
-                                              float* __restrict__ v, const int* __restrict__ step, long n4, float lr,
-                                              float b1, float b2, float eps) {
+                                              float* __restrict__ v, int* __restrict__ step, long n4, float lr,
+                                              float b1, float b2, float eps, unsigned* __restrict__ tail,
+                                              float* __restrict__ total, const float* __restrict__ acc, int nacc) {
   ck::pdl_enter();
   __shared__ float s_lrt;
+  __shared__ int s_t;
   if (threadIdx.x == 0) {
-    const float t = (float)(*step);
+    s_t = *step + (tail ? 1 : 0);
+    const float t = (float)s_t;
     s_lrt = lr * sqrtf(1.f - powf(b2, t)) / (1.f - powf(b1, t));
   }
   __syncthreads();
+  if (tail && blockIdx.x == 0 && (int)threadIdx.x < nacc) total[threadIdx.x] += acc[threadIdx.x];
   const float lrt = s_lrt;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
     float4 pv = reinterpret_cast<float4*>(p)[i];
@@ -37,6 +44,13 @@ __global__ void __launch_bounds__(256) adam_k(float* __restrict__ p, float* __re
     reinterpret_cast<float4*>(m)[i] = mv;
     reinterpret_cast<float4*>(v)[i] = vv;
     reinterpret_cast<float4*>(g)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  if (tail) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(tail, 1u) == gridDim.x - 1) *step = s_t;  // every block has read the old count by now
+    }
   }
 }
 
@@ -123,7 +137,21 @@ int crackfl_adam_step(float* p, float* g, float* m, float* v, int* step, long n,
   const long n4 = n / 4;
   long blocks = (n4 + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  ck::launch(adam_k, (int)blocks, 256, 0, st, p, g, m, v, step, n4, lr, b1, b2, eps);
+  ck::launch(adam_k, (int)blocks, 256, 0, st, p, g, m, v, step, n4, lr, b1, b2, eps, (unsigned*)nullptr, (float*)nullptr,
+             (const float*)nullptr, 0);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+// Adam + step tick + metric accumulation in one launch; tail_counter must be zero on entry (it lives in the per-step
+// scratch region the caller zeroes anyway)
+int crackfl_adam_step_tail(float* p, float* g, float* m, float* v, int* step, long n, float lr, float b1, float b2, float eps,
+                           unsigned* tail_counter, float* metrics_total, const float* step_acc, int nacc, cudaStream_t st) {
+  if (n % 4 || nacc > 32 || !tail_counter) return (int)cudaErrorInvalidValue;
+  const long n4 = n / 4;
+  long blocks = (n4 + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  ck::launch(adam_k, (int)blocks, 256, 0, st, p, g, m, v, step, n4, lr, b1, b2, eps, tail_counter, metrics_total, step_acc, nacc);
   CK_LAUNCH_CHECK();
   return 0;
 }

@@ -184,6 +184,9 @@ int crackfl_adam_step(float* p, float* g, float* m, float* v, int* step_dev, lon
                       cudaStream_t stream);
 int crackfl_f32_to_bf16(const float* in, void* out, long n, cudaStream_t stream);
 /* total[i] += step[i], i < n <= 32 (per-epoch metric accumulation of the per-step loss/accuracy sums) */
+/* Adam + step-count tick + metric accumulation (metrics_total[i] += step_acc[i]) in one launch; *tail_counter == 0 on entry */
+int crackfl_adam_step_tail(float* p, float* g, float* m, float* v, int* step_dev, long n, float lr, float b1, float b2, float eps,
+                           unsigned* tail_counter, float* metrics_total, const float* step_acc, int nacc, cudaStream_t stream);
 int crackfl_accum_small(float* total, const float* step, int n, cudaStream_t stream);
 /* staging of a client update as a bf16 delta against the global model (ref: fl_client.py:61-65 upload) */
 int crackfl_publish_delta(const float* local, const float* global, void* out_bf16, long n, cudaStream_t stream);
