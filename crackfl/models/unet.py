@@ -65,6 +65,7 @@ class UNetEngine:
         self.gemm_stats = os.environ.get("CRACKFL_GEMM_STATS", "1") != "0"
         self.dw_merged = os.environ.get("CRACKFL_DW_MERGED", "1") != "0"
         self.pool_bwd_fused = os.environ.get("CRACKFL_POOL_BWD_FUSED", "1") != "0"
+        self.dw_bn_fused = os.environ.get("CRACKFL_DW_BN_FUSED", "1") != "0"
         # measured: batching the split reductions per block (7 launches instead of 22) is 35-45 us SLOWER - the partial
         # tiles fall out of L2 before they are reduced - so the per-layer reduction right behind each GEMM stays the default
         self.wgrad_deferred = os.environ.get("CRACKFL_WGRAD_DEFERRED", "0") != "0"
@@ -290,10 +291,15 @@ class UNetEngine:
                 out.append(e)
         return out
 
-    def _dw_bwd(self, prog, g, src, w, bn, resid_t, dz, dwk, B, H, W, C, mode, resid):
-        """Depthwise backward: input gradient on the main stream, weight gradient on the side stream."""
+    def _dw_bwd(self, prog, g, src, w, bn, resid_t, dz, dwk, B, H, W, C, mode, resid, red_bn=0, red_sums=0):
+        """Depthwise backward: input gradient on the main stream, weight gradient on the side stream.  Returns True when
+        the BN-backward reductions (red_bn / red_sums) were folded into the launch."""
         if self.dw_tma and self.dw_merged:
-            # one pass over g and src: warps 0-7 the input gradient, warps 8-15 the weight gradient
+            # one pass over g and src: warps 0-7 the input gradient (+ BN reductions), warps 8-15 the weight gradient
+            if red_bn and self.dw_bn_fused:
+                prog.append((self.lib.crackfl_dw3x3_bwd_tma_bn, (g, src, w, bn, resid_t, dz, dwk, B, H, W, C, mode, resid,
+                                                                 red_bn, red_sums)))
+                return True
             prog.append((self.lib.crackfl_dw3x3_bwd_tma, (g, src, w, bn, resid_t, dz, dwk, B, H, W, C, mode, resid)))
         elif self.dw_tma:
             prog.append((self.lib.crackfl_dw3x3_tma, (g, w, 0, None, dz, src, bn, resid_t, B, H, W, C, 2, 1, mode, resid)))
@@ -546,10 +552,12 @@ class UNetEngine:
             self._gemm(prog, b(p + "dy2"), sep2.name + ".d", 0, 0, b(p + "dd2"), B, r, rw)
             self._wgrad(prog, b(p + "d2"), b(p + "dy2"), self.G(sep2.tensors[1]), B, r, rw, f, f, 1, 0, f, 1)
             # depthwise 2 (input = relu(bn1(y1)))
-            self._dw_bwd(prog, b(p + "dd2"), b(p + "y1"), self.P(sep2.tensors[0]), self._bnptr(bn1.name), 0,
-                         b(p + "dz1"), self.G(sep2.tensors[0]), B, r, rw, f, 1, 0)
-            prog.append((lib.crackfl_bn_bwd_reduce, (b(p + "dz1"), 0, b(p + "y1"), self._bnptr(bn1.name),
-                                                     self._zptr(bn1.name, "sums"), B, r, rw, f, 0)))
+            folded = self._dw_bwd(prog, b(p + "dd2"), b(p + "y1"), self.P(sep2.tensors[0]), self._bnptr(bn1.name), 0,
+                                  b(p + "dz1"), self.G(sep2.tensors[0]), B, r, rw, f, 1, 0,
+                                  red_bn=self._bnptr(bn1.name), red_sums=self._zptr(bn1.name, "sums"))
+            if not folded:
+                prog.append((lib.crackfl_bn_bwd_reduce, (b(p + "dz1"), 0, b(p + "y1"), self._bnptr(bn1.name),
+                                                         self._zptr(bn1.name, "sums"), B, r, rw, f, 0)))
             prog.append((lib.crackfl_bn_bwd_apply, (b(p + "dz1"), 0, b(p + "y1"), self._bnptr(bn1.name),
                                                     self._zptr(bn1.name, "sums"), b(p + "dy1"), self.G(bn1.tensors[0]),
                                                     self.G(bn1.tensors[1]), B, r, rw, f, 0)))
@@ -561,13 +569,16 @@ class UNetEngine:
             if k > 0:
                 self._wgrad_flush(prog)  # (the first block's batch also takes the entry conv, flushed before Adam)
             prog.append((None, None, "join_aux"))
-            self._dw_bwd(prog, b(p + "dd1"), b(xin), self.P(sep1.tensors[0]), 0, b(p + "Te"), b(out),
-                         self.G(sep1.tensors[0]), B, r, rw, cin, 0, 2 if k == 0 else 1)
+            folded0 = self._dw_bwd(prog, b(p + "dd1"), b(xin), self.P(sep1.tensors[0]), 0, b(p + "Te"), b(out),
+                                   self.G(sep1.tensors[0]), B, r, rw, cin, 0, 2 if k == 0 else 1,
+                                   red_bn=self._bnptr(bn0.name) if k == 0 else 0,
+                                   red_sums=self._zptr(bn0.name, "sums") if k == 0 else 0)
             dx_next = out
         # ---- entry
         r, rw, c0 = self.H // 2, self.W // 2, self.spec.entry
-        prog.append((lib.crackfl_bn_bwd_reduce, (b("dz0"), 0, b("y0"), self._bnptr(bn0.name), self._zptr(bn0.name, "sums"),
-                                                 B, r, rw, c0, 0)))
+        if not folded0:  # (folded0 is from the k == 0 block, the last one of the reversed loop)
+            prog.append((lib.crackfl_bn_bwd_reduce, (b("dz0"), 0, b("y0"), self._bnptr(bn0.name), self._zptr(bn0.name, "sums"),
+                                                     B, r, rw, c0, 0)))
         prog.append((lib.crackfl_bn_bwd_apply, (b("dz0"), 0, b("y0"), self._bnptr(bn0.name), self._zptr(bn0.name, "sums"),
                                                 b("dy0"), self.G(bn0.tensors[0]), self.G(bn0.tensors[1]), B, r, rw, c0, 0)))
         if self.entry_tc:

@@ -65,6 +65,7 @@ _SIGS = {
     "crackfl_dw3x3_tma": [vp, vp, vp, C.POINTER(BnFin), vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp],
     "crackfl_dw3x3_wgrad_tma": [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_dw3x3_bwd_tma": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
+    "crackfl_dw3x3_bwd_tma_bn": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp, vp],
     "crackfl_dw3x3_dgrad": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
     "crackfl_dw3x3_wgrad": [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_pool_add_fwd": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],

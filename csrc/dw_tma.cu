@@ -37,6 +37,8 @@ struct DwArgs {
   int src_mode, resid;          // dgrad epilogue (see dw3x3_bwd_k in elementwise.cu)
   int tiles_x, tiles_y, total_tiles;
   int nstage;                   // depth of the TMA ring (2..4)
+  const float* rbn;             // dw_bwd_k: BN ([scale][shift][mean][invstd]) whose backward reductions ride along
+  float* rsums;                 //           [sum dz C][sum dz*(y-mean) C], pre-zeroed (NULL: off)
 };
 
 __device__ __forceinline__ void load4(const uint8_t* smem_row, int off_bytes, float f[4]) {
@@ -472,6 +474,7 @@ __global__ void __launch_bounds__(512, 1) dw_bwd_k(const __grid_constant__ CUten
   const uint32_t bar0 = base + 2u * stage_bytes;
   float* red = reinterpret_cast<float*>(gbase + 2u * stage_bytes + 64);  // [256][4] floats
   float* coef = red + 256 * 4;                                            // [scale CB][shift CB]
+  float* red0 = coef + 2 * 64;                                            // [256][4] floats, role 0 (BN reductions)
   const int nc4 = CB >> 2;
   constexpr int rows = TY / RG;
   const int role = threadIdx.x >> 8, tl = threadIdx.x & 255;
@@ -525,6 +528,37 @@ __global__ void __launch_bounds__(512, 1) dw_bwd_k(const __grid_constant__ CUten
     }
   };
 
+  // BN-backward reductions of the layer below (role 0): sum dz and sum dz * a, a = the activated tile.  Where the
+  // mask is on, a = scale * y + shift, so  sum dz * (y - mean) = (sum dz * a - beta * sum dz) / scale,  beta = shift + mean * scale.
+  f2_t bs1[2] = {0ull, 0ull}, bs2[2] = {0ull, 0ull};
+  auto flush_bn = [&](int cblk) {  // role 0 only (named barrier 2, 256 threads)
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      float f0, f1, f2, f3;
+      upk2(which ? bs2[0] : bs1[0], f0, f1);
+      upk2(which ? bs2[1] : bs1[1], f2, f3);
+      *reinterpret_cast<float4*>(red0 + tl * 4) = make_float4(f0, f1, f2, f3);
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      if (tl < nc4 * 4) {
+        const int cc = tl >> 2, j = tl & 3;
+        float v = 0.f;
+        for (int q = 0; q < 256 / nc4; ++q) v += red0[(q * nc4 + cc) * 4 + j];
+        red0[1024 + which * 64 + tl] = v;  // [which][CB] staging behind the partials
+      }
+    }
+    asm volatile("bar.sync 2, 256;" ::: "memory");
+    if (tl < nc4 * 4) {
+      const int c = cblk * CB + tl;
+      const float S1 = red0[1024 + tl], S2 = red0[1024 + 64 + tl];
+      const float sc = a.rbn[c], sh = a.rbn[a.C + c], mu = a.rbn[2 * a.C + c];
+      const float beta = sh + mu * sc;
+      atomicAdd(a.rsums + c, S1);
+      atomicAdd(a.rsums + a.C + c, sc != 0.f ? (S2 - beta * S1) / sc : 0.f);
+    }
+    bs1[0] = bs1[1] = bs2[0] = bs2[1] = 0ull;
+  };
+
   int it = 0;
   for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
     const int stage = it & 1;
@@ -538,6 +572,7 @@ __global__ void __launch_bounds__(512, 1) dw_bwd_k(const __grid_constant__ CUten
     const int cg = cblk * CB + c4 * 4;
     if (cblk != cur_cblk) {  // uniform over the CTA
       if (role == 1 && cur_cblk >= 0) flush(cur_cblk);
+      if (role == 0 && cur_cblk >= 0 && a.rsums) flush_bn(cur_cblk);
       cur_cblk = cblk;
       if (role == 0) {
 #pragma unroll
@@ -654,12 +689,15 @@ __global__ void __launch_bounds__(512, 1) dw_bwd_k(const __grid_constant__ CUten
 #pragma unroll
           for (int j = 0; j < 4; ++j)
             o4[j] = (a.resid == 2) ? (mm[j] ? o4[j] + r4[j] : 0.f) : ((mm[j] ? o4[j] : 0.f) + r4[j]);
-          if (oh < a.H && gw < a.W) {
-            uint2 pk;
-            pk.x = pack2(o4[0], o4[1]);
-            pk.y = pack2(o4[2], o4[3]);
-            *reinterpret_cast<uint2*>(out_p + (r - 2) * out_rs) = pk;
+          uint2 pk;
+          pk.x = pack2(o4[0], o4[1]);
+          pk.y = pack2(o4[2], o4[3]);
+          if (a.rsums) {  // sums over the bf16-rounded dz, exactly what the apply pass reads back
+            const f2_t d0 = bf2_to_f2(pk.x), d1 = bf2_to_f2(pk.y);
+            bs1[0] = fadd2(bs1[0], d0); bs1[1] = fadd2(bs1[1], d1);
+            bs2[0] = ffma2(d0, bf2_to_f2(sv.x), bs2[0]); bs2[1] = ffma2(d1, bf2_to_f2(sv.y), bs2[1]);
           }
+          if (oh < a.H && gw < a.W) *reinterpret_cast<uint2*>(out_p + (r - 2) * out_rs) = pk;
         }
       }
     } else {
@@ -690,6 +728,7 @@ __global__ void __launch_bounds__(512, 1) dw_bwd_k(const __grid_constant__ CUten
     __syncthreads();  // every thread is done with this stage before it is refilled
   }
   if (role == 1 && cur_cblk >= 0) flush(cur_cblk);
+  if (role == 0 && cur_cblk >= 0 && a.rsums) flush_bn(cur_cblk);
 }
 
 int g_sms = 0;
@@ -810,8 +849,20 @@ int crackfl_dw3x3_wgrad_tma(const void* g, const void* src, const float* bn, flo
 
 // dz (input gradient) and dW (weight gradient) of the depthwise 3x3 in one pass; arguments as crackfl_dw3x3_tma (gradient
 // variant) + crackfl_dw3x3_wgrad_tma
+int crackfl_dw3x3_bwd_tma_bn(const void* g, const void* src, const float* w, const float* src_bn, const void* resid_t, void* dz,
+                             float* dwk, int B, int H, int W, int C, int src_mode, int resid, const float* red_bn,
+                             float* red_sums, cudaStream_t st);
+
 int crackfl_dw3x3_bwd_tma(const void* g, const void* src, const float* w, const float* src_bn, const void* resid_t, void* dz,
                           float* dwk, int B, int H, int W, int C, int src_mode, int resid, cudaStream_t st) {
+  return crackfl_dw3x3_bwd_tma_bn(g, src, w, src_bn, resid_t, dz, dwk, B, H, W, C, src_mode, resid, nullptr, nullptr, st);
+}
+
+// + the BN-backward reductions of the BN that produced src's activation (red_bn = its [scale][shift][mean][invstd],
+// red_sums = [sum dz C][sum dz*(y-mean) C], pre-zeroed): saves the separate crackfl_bn_bwd_reduce pass over dz and y
+int crackfl_dw3x3_bwd_tma_bn(const void* g, const void* src, const float* w, const float* src_bn, const void* resid_t, void* dz,
+                             float* dwk, int B, int H, int W, int C, int src_mode, int resid, const float* red_bn,
+                             float* red_sums, cudaStream_t st) {
   if (!shape_ok(C)) return (int)cudaErrorInvalidValue;
   constexpr int TY = 8;
   DwArgs a;
@@ -820,6 +871,7 @@ int crackfl_dw3x3_bwd_tma(const void* g, const void* src, const float* w, const 
   a.resid_t = (const __nv_bfloat16*)resid_t; a.dwk = dwk;
   a.B = B; a.H = H; a.W = W; a.C = C; a.CB = C >= 64 ? 64 : 32;
   a.act_mode = 2; a.flip = 1; a.src_mode = src_mode; a.resid = resid; a.nstage = 2;
+  a.rbn = red_bn; a.rsums = red_bn ? red_sums : nullptr;
   a.tiles_x = (W + TX - 1) / TX; a.tiles_y = (H + TY - 1) / TY;
   a.total_tiles = a.tiles_x * a.tiles_y * B * (C / a.CB);
   CUtensorMap tmG, tmS;
@@ -828,7 +880,8 @@ int crackfl_dw3x3_bwd_tma(const void* g, const void* src, const float* w, const 
   if (rc) return rc;
   rc = ck::get_tensor_map(src, 4, d, bx, 0, &tmS);
   if (rc) return rc;
-  const size_t smem = 2 * 2 * (size_t)(TY + 2) * HW * a.CB * 2 + 64 + 256 * 4 * sizeof(float) + 2 * 64 * sizeof(float) + 128;
+  const size_t smem = 2 * 2 * (size_t)(TY + 2) * HW * a.CB * 2 + 64 + 256 * 4 * sizeof(float) + 2 * 64 * sizeof(float) +
+                      (256 * 4 + 2 * 64) * sizeof(float) + 128;
   static bool attr = false;
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(dw_bwd_k<TY, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);

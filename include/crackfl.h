@@ -98,6 +98,10 @@ int crackfl_dw3x3_wgrad_tma(const void* g, const void* src, const float* bn, flo
 /* third generation: input gradient and weight gradient in one pass over g and src (warps 0-7 / 8-15 of a 512-thread CTA) */
 int crackfl_dw3x3_bwd_tma(const void* g, const void* src, const float* w, const float* src_bn, const void* resid_t, void* dz,
                           float* dwk, int B, int H, int W, int C, int src_mode, int resid, cudaStream_t stream);
+/* the same + the BN-backward reductions of the BN behind src (red_bn = [scale][shift][mean][invstd], red_sums pre-zeroed) */
+int crackfl_dw3x3_bwd_tma_bn(const void* g, const void* src, const float* w, const float* src_bn, const void* resid_t, void* dz,
+                             float* dwk, int B, int H, int W, int C, int src_mode, int resid, const float* red_bn,
+                             float* red_sums, cudaStream_t stream);
 
 /* ---- block tails --------------------------------------------------------------------------- */
 /* ref: client_fit_model.py:116-123 MaxPooling2D(3,2,"same") + add(residual) */

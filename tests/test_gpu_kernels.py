@@ -326,20 +326,17 @@ def test_dw3x3_tma_fwd_dgrad_wgrad(B, H, W, Cc, mode):
         want2 = want if rmode == 0 else (want + up if rmode == 1 else want + mask * up)
         assert float((dz2.float().permute(0, 3, 1, 2) - want2).norm() / want2.norm()) < 1.5e-2, rmode
         assert float((dwk2 - refw).norm() / refw.norm()) < 1e-2, rmode
-    # one-pass variant (input gradient + weight gradient from the same staged tiles), with a residual-path gradient
-    resid = torch.randn(B, H // 2, W // 2, Cc, device="cuda").bfloat16()
-    for rmode in (0, 1, 2):
-        dz2 = torch.zeros_like(x)
-        dwk2 = torch.zeros(9, Cc, device="cuda")
-        L.check(lib.crackfl_dw3x3_bwd_tma(g.data_ptr(), x.data_ptr(), w.data_ptr(), bn.data_ptr(), resid.data_ptr() if rmode else 0,
-                                          dz2.data_ptr(), dwk2.data_ptr(), B, H, W, Cc, mode, rmode, _st()))
-        torch.cuda.synchronize()
-        up = torch.zeros(B, Cc, H, W, device="cuda")
-        up[:, :, ::2, ::2] = resid.float().permute(0, 3, 1, 2)
-        mask = (pre.detach() > 0).float()
-        want2 = want if rmode == 0 else (want + up if rmode == 1 else want + mask * up)
-        assert float((dz2.float().permute(0, 3, 1, 2) - want2).norm() / want2.norm()) < 1.5e-2, rmode
-        assert float((dwk2 - refw).norm() / refw.norm()) < 1e-2, rmode
+    # ... and with the BN-backward reductions folded in: sums == crackfl_bn_bwd_reduce(dz, y = x)
+    rbn = bn.clone() if mode == 1 else torch.cat([torch.ones(Cc, device="cuda"), torch.zeros(3 * Cc, device="cuda")])
+    rbn[2 * Cc:3 * Cc] = torch.randn(Cc, device="cuda") * 0.1  # a non-trivial mean (scale / shift unchanged)
+    dz3, dwk3 = torch.zeros_like(x), torch.zeros(9, Cc, device="cuda")
+    s_f, s_r = torch.zeros(2 * Cc, device="cuda"), torch.zeros(2 * Cc, device="cuda")
+    L.check(lib.crackfl_dw3x3_bwd_tma_bn(g.data_ptr(), x.data_ptr(), w.data_ptr(), rbn.data_ptr(), 0, dz3.data_ptr(),
+                                         dwk3.data_ptr(), B, H, W, Cc, mode, 0, rbn.data_ptr(), s_f.data_ptr(), _st()))
+    L.check(lib.crackfl_bn_bwd_reduce(dz3.data_ptr(), 0, x.data_ptr(), rbn.data_ptr(), s_r.data_ptr(), B, H, W, Cc, 0, _st()))
+    torch.cuda.synchronize()
+    assert float((s_f[:Cc] - s_r[:Cc]).abs().max() / (s_r[:Cc].abs().max() + 1e-6)) < 2e-3
+    assert float((s_f[Cc:] - s_r[Cc:]).norm() / (s_r[Cc:].norm() + 1e-6)) < 1e-2
 
 
 @pytest.mark.parametrize("B,H,W,c0", [(2, 32, 32, 32), (3, 48, 80, 64), (1, 30, 34, 32)])
