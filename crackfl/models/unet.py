@@ -69,6 +69,7 @@ class UNetEngine:
         # measured: batching the split reductions per block (7 launches instead of 22) is 35-45 us SLOWER - the partial
         # tiles fall out of L2 before they are reduced - so the per-layer reduction right behind each GEMM stays the default
         self.wgrad_deferred = os.environ.get("CRACKFL_WGRAD_DEFERRED", "0") != "0"
+        self.wgrad_split = os.environ.get("CRACKFL_WGRAD_SPLIT", "1") != "0"  # measured: -20 us per step
         self._wg_descs, self._wg_off, self._wg_max, self._wg_flushed = [], 0, 0, 0
         with torch.cuda.device(self.dev):
             self._alloc_params()
@@ -83,6 +84,7 @@ class UNetEngine:
         self._graphs: Dict[str, torch.cuda.CUDAGraph] = {}
         self._side_stream = torch.cuda.Stream(self.dev)
         self._aux_stream = torch.cuda.Stream(self.dev)
+        self._side2_stream = torch.cuda.Stream(self.dev)
         self.launches_per_step = sum(1 for e in self.train_prog if e[0] is not None)
 
     # ------------------------------------------------------------------ allocation
@@ -242,7 +244,24 @@ class UNetEngine:
         return False
 
     def _wgrad(self, prog, X, dY, dW, B, H, W, cin, cout, taps, s_tap, s_ci, s_co, cin_valid=0):
-        if self.conv_impl == "tc" and self.wgrad_deferred:
+        if self.conv_impl == "tc" and self.wgrad_split:
+            # partial tiles on the side stream, their reduction on a THIRD stream behind it, two workspace slots in
+            # turn: reduction n overlaps GEMM n+1 (GEMM n+2 waits for reduction n before it reuses the slot)
+            d = L.WgradRedDesc()
+            L.check(self.lib.crackfl_wgrad_plan(B, H, W, cin, cout, taps, s_tap, s_ci, s_co, cin_valid, C.byref(d)),
+                    "crackfl_wgrad_plan")
+            n = len(self._wg_descs)
+            d.dw_off = (dW - self.grads.data_ptr()) // 4
+            self._wg_max = max(self._wg_max, (d.need + 255) // 256 * 256)
+            self._wg_descs.append(d)
+            if n >= 2:
+                prog.append((None, None, ("wait", "side", f"r{n - 2}")))
+            prog.append(("WGRAD", (X, dY, B, H, W, cin, cout, taps, n % 2, d.need), "side"))
+            prog.append((None, None, ("rec", "side", f"w{n}")))
+            prog.append((None, None, ("wait", "side2", f"w{n}")))
+            prog.append(("WREDUCE", (n, 1), "side2"))
+            prog.append((None, None, ("rec", "side2", f"r{n}")))
+        elif self.conv_impl == "tc" and self.wgrad_deferred:
             # split-K partial tiles now, ONE reduction launch per block later (_wgrad_flush); the workspace slice is
             # assigned here, the pointers are patched in once the workspace size is known (_wgrad_resolve)
             d = L.WgradRedDesc()
@@ -266,7 +285,7 @@ class UNetEngine:
     def _wgrad_flush(self, prog):
         """One reduction launch for the wgrad GEMMs recorded since the previous flush; their workspace is reused after it."""
         n = len(self._wg_descs) - self._wg_flushed
-        if n > 0:
+        if n > 0 and not self.wgrad_split:
             prog.append(("WREDUCE", (self._wg_flushed, n), "side"))
             self._wg_flushed = len(self._wg_descs)
             self._wg_off = 0
@@ -274,7 +293,11 @@ class UNetEngine:
     def _wgrad_resolve(self, prog):
         if not self._wg_descs:
             return prog
-        ws = self._new("wgrad_ws", (max(self._wg_max, 1024),), torch.float32)
+        slot = max(self._wg_max, 1024)
+        ws = self._new("wgrad_ws", (slot * (2 if self.wgrad_split else 1),), torch.float32)
+        if self.wgrad_split:
+            for n, d in enumerate(self._wg_descs):
+                d.ws_off = (n % 2) * slot
         arr = (L.WgradRedDesc * len(self._wg_descs))(*self._wg_descs)
         self._bufs["wgrad_descs"] = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).clone().to(self.dev)
         dptr, dsz = self._bufs["wgrad_descs"].data_ptr(), C.sizeof(L.WgradRedDesc)
@@ -282,11 +305,13 @@ class UNetEngine:
         for e in prog:
             if e[0] == "WGRAD":
                 X, dY, B, H, W, cin, cout, taps, off, need = e[1]
+                if self.wgrad_split:
+                    off *= slot
                 out.append((self.lib.crackfl_wgrad_tc_deferred, (X, dY, B, H, W, cin, cout, taps, ws.data_ptr() + 4 * off, need),
                             "side"))
             elif e[0] == "WREDUCE":
                 i0, n = e[1]
-                out.append((self.lib.crackfl_wgrad_reduce_all, (dptr + i0 * dsz, n, ws.data_ptr(), self.grads.data_ptr()), "side"))
+                out.append((self.lib.crackfl_wgrad_reduce_all, (dptr + i0 * dsz, n, ws.data_ptr(), self.grads.data_ptr()), e[2]))
             else:
                 out.append(e)
         return out
@@ -608,8 +633,9 @@ class UNetEngine:
         consumer.  Works eagerly and under graph capture."""
         main = torch.cuda.current_stream(self.dev)
         st = main.cuda_stream
-        streams = {"side": self._side_stream, "aux": self._aux_stream}
-        forked = {"side": False, "aux": False}
+        streams = {"side": self._side_stream, "aux": self._aux_stream, "side2": self._side2_stream}
+        forked = {"side": False, "aux": False, "side2": False}
+        events = {}
 
         def join(name):
             if forked[name]:
@@ -621,16 +647,26 @@ class UNetEngine:
         for entry in prog:
             fn, args = entry[0], entry[1]
             tag = entry[2] if len(entry) > 2 else None
+            if isinstance(tag, tuple):  # ("rec" | "wait", stream, key): explicit event edges between the extra streams
+                if self.side_streams:
+                    if tag[0] == "rec":
+                        events[tag[2]] = torch.cuda.Event()
+                        events[tag[2]].record(streams[tag[1]])
+                    else:
+                        streams[tag[1]].wait_event(events[tag[2]])
+                continue
             if tag == "join":
                 join("side")
+                join("side2")
                 continue
             if tag == "join_aux":
                 join("aux")
                 continue
             if tag in streams and self.side_streams:
-                ev = torch.cuda.Event()
-                ev.record(main)
-                streams[tag].wait_event(ev)
+                if tag != "side2":  # side2 work is ordered by explicit events only
+                    ev = torch.cuda.Event()
+                    ev.record(main)
+                    streams[tag].wait_event(ev)
                 rc = fn(*args, streams[tag].cuda_stream)
                 forked[tag] = True
             else:
@@ -638,6 +674,7 @@ class UNetEngine:
             if rc != 0:
                 raise L.KernelError(f"{fn.__name__} failed with cudaError {rc}")
         join("side")
+        join("side2")
         join("aux")
 
     def _step_body(self, prog, accumulate: bool):
