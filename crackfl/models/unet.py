@@ -85,6 +85,7 @@ class UNetEngine:
         self._side_stream = torch.cuda.Stream(self.dev)
         self._aux_stream = torch.cuda.Stream(self.dev)
         self._side2_stream = torch.cuda.Stream(self.dev)
+        self._side3_stream = torch.cuda.Stream(self.dev)  # bias-gradient column sums
         self.launches_per_step = sum(1 for e in self.train_prog if e[0] is not None)
 
     # ------------------------------------------------------------------ allocation
@@ -540,7 +541,7 @@ class UNetEngine:
             self._gemm(prog, b(p + "dy1"), ct1.name + ".d", 0, 0, b(p + "da0"), B, r, rw)
             self._wgrad(prog, b(p + "dy1"), b(a0), self.G(ct1.tensors[0]), B, r, rw, f, cin, 9, f * cin, cin, 1)
             self._wgrad(prog, b(src_res), b(drl), self.G(res.tensors[0]), B, lr_, lrw, cin, f, 1, 0, f, 1)
-            prog.append((lib.crackfl_colsum, (b(drl), self.G(res.tensors[1]), B * lr_ * lrw, f), "side"))
+            prog.append((lib.crackfl_colsum, (b(drl), self.G(res.tensors[1]), B * lr_ * lrw, f), os.environ.get("CRACKFL_COLSUM_STREAM", "side3")))
             prog.append((None, None, "join_aux"))
             self._wgrad_flush(prog)
             if j > 0:
@@ -560,7 +561,7 @@ class UNetEngine:
             # residual 1x1 s2 conv
             self._gemm(prog, b(dx_next), res.name + ".d", 0, 0, b(p + "Te"), B, r2, rw2, tag="aux")
             self._wgrad(prog, b(xe), b(dx_next), self.G(res.tensors[0]), B, r2, rw2, cin, f, 1, 0, f, 1)
-            prog.append((lib.crackfl_colsum, (b(dx_next), self.G(res.tensors[1]), B * r2 * rw2, f), "side"))
+            prog.append((lib.crackfl_colsum, (b(dx_next), self.G(res.tensors[1]), B * r2 * rw2, f), os.environ.get("CRACKFL_COLSUM_STREAM", "side3")))
             # max-pool + BN2
             # max-pool backward once into dd2 (reused below as the pointwise dgrad output), then DIRECT-mode BN backward
             if self.pool_bwd_fused:
@@ -633,8 +634,9 @@ class UNetEngine:
         consumer.  Works eagerly and under graph capture."""
         main = torch.cuda.current_stream(self.dev)
         st = main.cuda_stream
-        streams = {"side": self._side_stream, "aux": self._aux_stream, "side2": self._side2_stream}
-        forked = {"side": False, "aux": False, "side2": False}
+        streams = {"side": self._side_stream, "aux": self._aux_stream, "side2": self._side2_stream,
+                   "side3": self._side3_stream}
+        forked = {"side": False, "aux": False, "side2": False, "side3": False}
         events = {}
 
         def join(name):
@@ -658,6 +660,7 @@ class UNetEngine:
             if tag == "join":
                 join("side")
                 join("side2")
+                join("side3")
                 continue
             if tag == "join_aux":
                 join("aux")
@@ -675,6 +678,7 @@ class UNetEngine:
                 raise L.KernelError(f"{fn.__name__} failed with cudaError {rc}")
         join("side")
         join("side2")
+        join("side3")
         join("aux")
 
     def _step_body(self, prog, accumulate: bool):
