@@ -243,6 +243,7 @@ struct ConvArgs2 {
   int sub_w;                 // channels per output sub-tile (64 with 128B swizzle, 32 with 64B swizzle)
   int n_tiles_m, n_tiles_n;  // tile counts
   uint32_t layout, sbo;
+  int dbg_noflush;           // profiling aid (CRACKFL_DBG_NOFLUSH=1): skip the statistics atomics
   TileGeom g;
 };
 
@@ -379,7 +380,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
         const int which = i / a.BN, col = i % a.BN;
         float v = 0.f;
         for (int g = 0; g < s_groups; ++g) v += red[(g * 2 + which) * a.BN + col];
-        atomicAdd(a.stats + which * a.N + n0f + col, v);
+        if (!a.dbg_noflush) atomicAdd(a.stats + which * a.N + n0f + col, v);
       }
     };
     // bias vector into shared memory once (ordered by the first epi_bar_sync below): no global-memory latency between
@@ -507,6 +508,7 @@ struct ConvArgs3 {
   int n_tiles_m, n_tiles_n;
   uint32_t layout, sbo;
   int base_off;              // set the descriptor's base_offset field from the start address
+  int dbg_noflush;
   int astages;               // halo-tile ring depth (2..4)
   int resident;              // all 9 * Cin/kc weight tiles stay in shared memory for the CTA's lifetime (stages == that count)
   uint32_t a_stage, a_bytes; // halo stage pitch (1024-aligned) / payload bytes (180 rows of kc channels)
@@ -690,7 +692,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
         const int which = i / a.BN, col = i % a.BN;
         float v = 0.f;
         for (int g = 0; g < s_groups; ++g) v += red[(g * 2 + which) * a.BN + col];
-        atomicAdd(a.stats + which * a.N + n0f + col, v);
+        if (!a.dbg_noflush) atomicAdd(a.stats + which * a.N + n0f + col, v);
       }
     };
     // bias vector into shared memory once (ordered by the first epi_bar_sync below): no global-memory latency between
@@ -1241,6 +1243,11 @@ static int conv_tc_fwd_v1(const void* X, const void* Wk, const float* bias, cons
 }
 
 static int g_num_sms = 0;
+static int dbg_noflush() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("CRACKFL_DBG_NOFLUSH"); v = e ? atoi(e) : 0; }
+  return v;
+}
 
 int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const void* add, void* Y, float* stats, int B, int H,
                         int W, int Cin, int N, int taps, cudaStream_t st) {
@@ -1287,6 +1294,7 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
     a.kc = kc3; a.layout = kc3 == 64 ? 2u : 4u; a.sbo = kc3 == 64 ? 1024u : 512u;
     a.sub_w = (a.BN % 64 == 0) ? 64 : 32;
     a.base_off = halo_base_off;
+    a.dbg_noflush = dbg_noflush();
     a.resident = resident ? 1 : 0;
     a.a_bytes = 180u * (uint32_t)kc3 * 2u;
     a.a_stage = (a.a_bytes + 1023u) & ~1023u;
@@ -1365,6 +1373,7 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
   }
 v2_path:
   ConvArgs2 a;
+  a.dbg_noflush = dbg_noflush();
   a.bias = bias; a.add = (const __nv_bfloat16*)add; a.stats = stats;
   a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.N = N; a.taps = taps;
   a.BN = N > 128 ? 128 : N;
