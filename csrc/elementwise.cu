@@ -1230,7 +1230,13 @@ __global__ void __launch_bounds__(TPB) entry_im2col_k(const uint8_t* __restrict_
   }
 }
 
-inline int grid_for(long total, int cap = 148 * 16) {
+inline int grid_for(long total, int cap = 0) {
+  // blocks per SM of the grid-stride streaming kernels.  Measured on the full step (ms): 2: 1.354, 3: 1.325, 4: 1.311,
+  // 6: 1.315, 8: 1.315, 12: 1.336, 16: 1.347, 24: 1.375, 48: 1.404 - about one resident wave is best (no tail of
+  // partially filled waves, and room on the SMs for the kernels of the side streams).
+  static int env_cap = -1;
+  if (env_cap < 0) { const char* e = getenv("CRACKFL_EW_BLOCKS_PER_SM"); env_cap = e ? atoi(e) : 4; if (env_cap < 1) env_cap = 4; }
+  if (cap == 0) cap = 148 * env_cap;
   long b = (total + TPB - 1) / TPB;
   return (int)(b < 1 ? 1 : (b > cap ? cap : b));
 }
@@ -1446,7 +1452,7 @@ int crackfl_colsum(const void* g, float* out, long P, int C, cudaStream_t st) {
 int crackfl_head_fwd(const void* s, const float* w, const float* bias, const void* mask_u8, float* acc, float* prob, int B,
                      int Hl, int Wl, int C, cudaStream_t st) {
   const long P = (long)B * Hl * Wl;
-  ck::launch(head_fwd_k, grid_for(P * (C / 8), 148 * 8), TPB, C * sizeof(float), st, (const __nv_bfloat16*)s, w, bias,
+  ck::launch(head_fwd_k, grid_for(P * (C / 8), 148 * 4), TPB, C * sizeof(float), st, (const __nv_bfloat16*)s, w, bias,
                                                                    (const uint8_t*)mask_u8, acc, prob, B, Hl, Wl, C);
   CK_LAUNCH_CHECK();
   return 0;
@@ -1456,7 +1462,7 @@ int crackfl_head_bwd(const void* s, const float* w, const float* bias, const voi
                      float* dw, float* db, int B, int Hl, int Wl, int C, int use_dice, float dice_smooth, float loss_scale,
                      cudaStream_t st) {
   const long P = (long)B * Hl * Wl;
-  ck::launch(head_bwd_k, grid_for(P * (C / 8), 148 * 8), TPB, (C + TPB * 8) * sizeof(float), st, 
+  ck::launch(head_bwd_k, grid_for(P * (C / 8), 148 * 4), TPB, (C + TPB * 8) * sizeof(float), st, 
       (const __nv_bfloat16*)s, w, bias, (const uint8_t*)mask_u8, sums, (__nv_bfloat16*)ds, dw, db, B, Hl, Wl, C, use_dice,
       dice_smooth, loss_scale, (float*)nullptr);
   CK_LAUNCH_CHECK();
@@ -1468,7 +1474,7 @@ int crackfl_head_bwd(const void* s, const float* w, const float* bias, const voi
 int crackfl_head_fwd_bwd(const void* s, const float* w, const float* bias, const void* mask_u8, float* acc_out, void* ds,
                          float* dw, float* db, int B, int Hl, int Wl, int C, float loss_scale, cudaStream_t st) {
   const long P = (long)B * Hl * Wl;
-  ck::launch(head_bwd_k, grid_for(P * (C / 8), 148 * 8), TPB, (C + TPB * 8) * sizeof(float), st,
+  ck::launch(head_bwd_k, grid_for(P * (C / 8), 148 * 4), TPB, (C + TPB * 8) * sizeof(float), st,
       (const __nv_bfloat16*)s, w, bias, (const uint8_t*)mask_u8, (const float*)nullptr, (__nv_bfloat16*)ds, dw, db, B, Hl, Wl, C,
       0, 1.0f, loss_scale, acc_out);
   CK_LAUNCH_CHECK();
