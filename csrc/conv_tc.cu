@@ -1243,6 +1243,13 @@ static int conv_tc_fwd_v1(const void* X, const void* Wk, const float* bias, cons
 }
 
 static int g_num_sms = 0;
+static int wred_cap() {  // blocks per SM of the split-reduction kernel (tuning knob)
+  static int v = -1;
+  // measured on the full step (ms): 1: 1.283, 2: 1.287, 3: 1.289, 4: 1.297, 8: 1.312, 16: 1.347 - the reduction runs next
+  // to the following GEMM on its own stream, a small footprint disturbs it least
+  if (v < 0) { const char* e = getenv("CRACKFL_WRED_BLOCKS_PER_SM"); v = e ? atoi(e) : 1; if (v < 1) v = 1; }
+  return v;
+}
 static int dbg_noflush() {
   static int v = -1;
   if (v < 0) { const char* e = getenv("CRACKFL_DBG_NOFLUSH"); v = e ? atoi(e) : 0; }
@@ -1494,7 +1501,7 @@ static int wgrad_impl(const void* X, const void* dY, float* dW, int B, int H, in
   int zl = 1;
   {
     const long total4 = (long)groups * ntn * 128L * a.BN / 4;
-    while (zl * 2 <= splits && zl < 32 && total4 * (zl * 2) / 256 <= 148 * 8) zl *= 2;  // split lanes per block
+    while (zl * 2 <= splits && zl < 32 && total4 * (zl * 2) / 256 <= 148 * wred_cap()) zl *= 2;  // split lanes per block
   }
   if (desc) {
     desc->s_tap = s_tap; desc->s_ci = s_ci; desc->s_co = s_co; desc->need = need;
@@ -1531,7 +1538,7 @@ static int wgrad_impl(const void* X, const void* dY, float* dW, int B, int H, in
   if (a.ws && mode == 0) {
     const long total4 = (long)groups * ntn * 128L * a.BN / 4;
     long blocks = (total4 * zl + 255) / 256;
-    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks > 148 * wred_cap()) blocks = 148 * wred_cap();
     ck::launch(wgrad_reduce_k, (int)blocks, 256, 0, st, a.ws, dW, groups, ntn, splits, a.BN, a.cw, a.mblk, a.total_blocks, Cin / a.cw,
                s_tap, s_ci, s_co, zl, cin_valid > 0 ? cin_valid : Cin);
     CK_LAUNCH_CHECK();

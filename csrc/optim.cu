@@ -113,6 +113,12 @@ __global__ void accum_k(float* __restrict__ total, const float* __restrict__ ste
 
 }  // namespace
 
+static int opt_cap() {  // blocks per SM of the flat-arena kernels (tuning knob)
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("CRACKFL_OPT_BLOCKS_PER_SM"); v = e ? atoi(e) : 8; if (v < 1) v = 8; }
+  return v;
+}
+
 extern "C" {
 
 int crackfl_accum_small(float* total, const float* step, int n, cudaStream_t st) {
@@ -124,7 +130,7 @@ int crackfl_accum_small(float* total, const float* step, int n, cudaStream_t st)
 
 int crackfl_publish_delta(const float* local, const float* global, void* out_bf16, long n, cudaStream_t st) {
   long blocks = (n + 255) / 256;
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks > 148 * opt_cap()) blocks = 148 * opt_cap();
   ck::launch(publish_delta_k, (int)blocks, 256, 0, st, local, global, (__nv_bfloat16*)out_bf16, n);
   CK_LAUNCH_CHECK();
   return 0;
@@ -136,7 +142,7 @@ int crackfl_adam_step(float* p, float* g, float* m, float* v, int* step, long n,
   ck::launch(adam_tick_k, 1, 1, 0, st, step);
   const long n4 = n / 4;
   long blocks = (n4 + 255) / 256;
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks > 148 * opt_cap()) blocks = 148 * opt_cap();
   ck::launch(adam_k, (int)blocks, 256, 0, st, p, g, m, v, step, n4, lr, b1, b2, eps, (unsigned*)nullptr, (float*)nullptr,
              (const float*)nullptr, 0);
   CK_LAUNCH_CHECK();
@@ -150,7 +156,7 @@ int crackfl_adam_step_tail(float* p, float* g, float* m, float* v, int* step, lo
   if (n % 4 || nacc > 32 || !tail_counter) return (int)cudaErrorInvalidValue;
   const long n4 = n / 4;
   long blocks = (n4 + 255) / 256;
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks > 148 * opt_cap()) blocks = 148 * opt_cap();
   ck::launch(adam_k, (int)blocks, 256, 0, st, p, g, m, v, step, n4, lr, b1, b2, eps, tail_counter, metrics_total, step_acc, nacc);
   CK_LAUNCH_CHECK();
   return 0;
@@ -165,7 +171,7 @@ int crackfl_weight_prep(const float* arena, void* ops, const crackfl_prep_desc* 
 
 int crackfl_f32_to_bf16(const float* in, void* out, long n, cudaStream_t st) {
   long blocks = (n + 255) / 256;
-  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks > 148 * opt_cap()) blocks = 148 * opt_cap();
   ck::launch(f32_to_bf16_k, (int)blocks, 256, 0, st, in, (__nv_bfloat16*)out, n);
   CK_LAUNCH_CHECK();
   return 0;
