@@ -742,6 +742,12 @@ int num_sms() {
   return g_sms;
 }
 
+int dw_per_sm() {  // CTAs per SM of the persistent depthwise kernels (tuning knob; 2 = what fits)
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("CRACKFL_DW_CTAS_PER_SM"); v = e ? atoi(e) : 2; if (v < 1 || v > 2) v = 2; }
+  return v;
+}
+
 bool shape_ok(int C) { return C % 32 == 0 && (C <= 64 || C % 64 == 0); }
 
 // channel block and ring depth: as many stages (<= 4) as fit twice per SM (2 x <= 112 KB); CRACKFL_DW_CB /
@@ -783,7 +789,7 @@ static int launch_stencil(const void* x, DwArgs& a, cudaStream_t st) {
     if (e != cudaSuccess) return (int)e;
     attr = true;
   }
-  int grid = 2 * num_sms();
+  int grid = dw_per_sm() * num_sms();
   if (grid > a.total_tiles) grid = a.total_tiles;
   if (a.CB == 64) ck::launch(dw_stencil_k<TY, 1, DGRAD>, grid, 256, smem, st, tm, tmS, a);
   else ck::launch(dw_stencil_k<TY, 2, DGRAD>, grid, 256, smem, st, tm, tmS, a);
@@ -839,7 +845,7 @@ int crackfl_dw3x3_wgrad_tma(const void* g, const void* src, const float* bn, flo
     if (e != cudaSuccess) return (int)e;
     attr = true;
   }
-  int grid = 2 * num_sms();
+  int grid = dw_per_sm() * num_sms();
   if (grid > a.total_tiles) grid = a.total_tiles;
   if (a.CB == 64) ck::launch(dw_wgrad_k<TY, 1>, grid, 256, smem, st, tmA, tmG, a);
   else ck::launch(dw_wgrad_k<TY, 2>, grid, 256, smem, st, tmA, tmG, a);

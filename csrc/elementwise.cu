@@ -1565,7 +1565,9 @@ int crackfl_pool_bwd_bn(const void* g, const void* arg, const void* y, const flo
   CK_FITS32((long)B * H * W * C);
   if ((H | W) & 1 || TPB % (C >> 3)) return (int)cudaErrorInvalidValue;
   const int P2 = B * (H / 2) * (W / 2), lanes = TPB / (C >> 3);
-  int ipb = (P2 + 148 * 2 - 1) / (148 * 2);
+  static int per_sm = -1;  // tuning knob
+  if (per_sm < 0) { const char* e = getenv("CRACKFL_POOLBWD_BLOCKS_PER_SM"); per_sm = e ? atoi(e) : 2; if (per_sm < 1) per_sm = 2; }
+  int ipb = (P2 + 148 * per_sm - 1) / (148 * per_sm);
   ipb = (ipb + lanes - 1) / lanes * lanes;
   ck::launch(pool_bwd_bn_k, (P2 + ipb - 1) / ipb, TPB, 0, st, (const __nv_bfloat16*)g, (const uint8_t*)arg,
              (const __nv_bfloat16*)y, bn, (__nv_bfloat16*)dz, sums, B, H, W, C, ipb);
