@@ -1245,8 +1245,9 @@ static int conv_tc_fwd_v1(const void* X, const void* Wk, const float* bias, cons
 static int g_num_sms = 0;
 static int wred_cap() {  // blocks per SM of the split-reduction kernel (tuning knob)
   static int v = -1;
-  // measured on the full step (ms): 1: 1.283, 2: 1.287, 3: 1.289, 4: 1.297, 8: 1.312, 16: 1.347 - the reduction runs next
-  // to the following GEMM on its own stream, a small footprint disturbs it least
+  // measured on the full step (ms): 1: 1.283, 2: 1.287, 3: 1.289, 4: 1.297, 8: 1.312, 16: 1.347.  With the engine's
+  // one-descriptor reduction launches (fixed grid) the knob acts through the number of split lanes per block it allows:
+  // few lanes with long load chains beat many lanes + a shared-memory tree next to the following GEMM
   if (v < 0) { const char* e = getenv("CRACKFL_WRED_BLOCKS_PER_SM"); v = e ? atoi(e) : 1; if (v < 1) v = 1; }
   return v;
 }
