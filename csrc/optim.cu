@@ -163,7 +163,9 @@ int crackfl_adam_step_tail(float* p, float* g, float* m, float* v, int* step, lo
 }
 
 int crackfl_weight_prep(const float* arena, void* ops, const crackfl_prep_desc* descs_dev, int num_desc, cudaStream_t st) {
-  dim3 grid(192, num_desc);  // <= 3 tiles of 32x32 per block for the largest operand (256 x 9 x 256)
+  static int gx = -1;  // tuning knob; 192: <= 3 tiles of 32x32 per block for the largest operand (256 x 9 x 256)
+  if (gx < 0) { const char* e = getenv("CRACKFL_PREP_GRID_X"); gx = e ? atoi(e) : 48; if (gx < 1) gx = 48; }  // measured: 48: 1.279, 96: 1.282, 192: 1.286 ms/step (it overlaps the entry kernels on the auxiliary stream)
+  dim3 grid(gx, num_desc);
   ck::launch(weight_prep_k, grid, 256, 0, st, arena, (__nv_bfloat16*)ops, descs_dev);
   CK_LAUNCH_CHECK();
   return 0;
