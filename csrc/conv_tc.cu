@@ -1467,7 +1467,9 @@ static int wgrad_impl(const void* X, const void* dY, float* dW, int B, int H, in
   }
   int stages = per_sm == 2 ? (int)(106496u / stage_bytes) : (int)(200704u / stage_bytes);
   if (stages > 6) stages = 6;
-  int splits = (148 * per_sm) / (groups * ntn);
+  static int fill = -1;  // tuning knob: percentage of the 148 * per_sm CTA slots the split count may fill
+  if (fill < 0) { const char* e = getenv("CRACKFL_WGRAD_FILL"); fill = e ? atoi(e) : 100; if (fill < 10 || fill > 100) fill = 100; }
+  int splits = (148 * per_sm * fill / 100) / (groups * ntn);
   if (splits > a.ntiles) splits = a.ntiles;
   if (splits < 1) splits = 1;
   a.tiles_per_split = (a.ntiles + splits - 1) / splits;
