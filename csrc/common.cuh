@@ -17,7 +17,8 @@ namespace ck {
 // per-CTA set-up before the wait (barrier init, TMEM allocation, descriptor prefetch).  The trigger lets the NEXT kernel be
 // scheduled as soon as all CTAs of this one are resident.  Because every kernel waits before it exits, completion order
 // stays transitive (kernel n+2 cannot pass its wait before kernel n has finished).  CRACKFL_PDL=0 turns the attribute off;
-// the two instructions are then no-ops.
+// the two instructions are then no-ops.  Measured on the full step: wait-then-trigger 1.28 ms, trigger-then-wait 1.30 ms,
+// wait without an explicit trigger (dependents launch only when the grid drains) 1.34 ms.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_enter() { pdl_wait(); pdl_trigger(); }
