@@ -1347,7 +1347,11 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
       } else {
         stages = (int)((200704u - 2u * a.a_stage - out_bytes) / b_bytes);
       }
-      if (stages > 9) stages = 9;
+      {
+        static int cap = -1;  // tuning knob: depth of the streamed weight ring
+        if (cap < 0) { const char* e = getenv("CRACKFL_V3_BSTAGES"); cap = e ? atoi(e) : 9; if (cap < 2 || cap > 24) cap = 9; }
+        if (stages > cap) stages = cap;
+      }
       if (stages < 2) stages = 2;
     }
     a.stages = stages;
