@@ -411,3 +411,30 @@ def test_pool_bwd_bn_fused_matches_two_pass(B, H, W, Cc):
                                     torch.arange(Wo, device="cuda"), torch.arange(Cc, device="cuda"), indexing="ij")
     ref.index_put_((bi, 2 * qi + rr, 2 * qj + cc, ci), g.float(), accumulate=True)
     assert float((dz_b.float() - ref).abs().max()) < 0.05
+
+
+def test_adam_step_tail_matches_adam_step():
+    """Adam + step tick + metric accumulation in one launch == crackfl_adam_step followed by crackfl_accum_small."""
+    L, lib = _lib()
+    torch.manual_seed(1)
+    n = 1 << 16
+    pa = torch.randn(n, device="cuda"); pb = pa.clone()
+    ma, va = torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    mb, vb = torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    sa = torch.zeros(1, dtype=torch.int32, device="cuda"); sb = sa.clone()
+    tot_a, tot_b = torch.zeros(6, device="cuda"), torch.zeros(6, device="cuda")
+    for it in range(3):
+        g = torch.randn(n, device="cuda") * 0.1
+        acc = torch.rand(6, device="cuda")
+        ga, gb = g.clone(), g.clone()
+        L.check(lib.crackfl_adam_step(pa.data_ptr(), ga.data_ptr(), ma.data_ptr(), va.data_ptr(), sa.data_ptr(), n, 1e-3, 0.9,
+                                      0.999, 1e-7, _st()))
+        L.check(lib.crackfl_accum_small(tot_a.data_ptr(), acc.data_ptr(), 6, _st()))
+        counter = torch.zeros(1, dtype=torch.int32, device="cuda")
+        L.check(lib.crackfl_adam_step_tail(pb.data_ptr(), gb.data_ptr(), mb.data_ptr(), vb.data_ptr(), sb.data_ptr(), n, 1e-3,
+                                           0.9, 0.999, 1e-7, counter.data_ptr(), tot_b.data_ptr(), acc.data_ptr(), 6, _st()))
+        torch.cuda.synchronize()
+        assert float(gb.abs().max()) == 0.0
+    assert torch.equal(pa, pb) and torch.equal(ma, mb) and torch.equal(va, vb)
+    assert int(sa.item()) == int(sb.item()) == 3
+    assert torch.allclose(tot_a, tot_b)
