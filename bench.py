@@ -166,7 +166,7 @@ def main():
             # i+1 so that it overlaps this step's compute, train on batch i, read its loss back (D2H, synchronises)
             eng.train_step_prefetched()
             eng.prefetch(hx[(i + 1) % NB], hy[(i + 1) % NB])
-            return float(eng.step_loss().item())
+            return eng.step_loss_host()
 
         def round_end():
             # FedAvg round boundary: publish the local fit, fused aggregate+broadcast kernel, reload, fresh Adam
@@ -221,7 +221,7 @@ def main():
             dist.all_reduce(ems, op=dist.ReduceOp.MAX)
         ems = float(ems.item())
         e2e = {"value": world * B * a.steps / (ems / 1e3), "unit": "images/s", "ms_per_step": ems / a.steps,
-               "h2d_bytes_per_step": B * S * S * 3 + B * S * S, "d2h_bytes_per_step": 4,
+               "h2d_bytes_per_step": B * S * S * 3 + B * S * S, "d2h_bytes_per_step": 24 if a.impl == "ours" else 4,
                "wall_ms_rank0": wall_ms, "last_loss": last}
 
     if rank == 0:

@@ -838,6 +838,17 @@ class UNetEngine:
         return a[0] / a[5].clamp_min(1.0)
 
 
+    def step_loss_host(self) -> float:
+        """Mean BCE of the most recent step read back to the host: ONE 24-byte D2H copy of the step's accumulators into
+        pinned memory + a stream synchronise (no device-side arithmetic kernels), the division is done on the host."""
+        if getattr(self, "_acc_host", None) is None:
+            self._acc_host = torch.empty(6, dtype=torch.float32, pin_memory=True)
+        self._acc_host.copy_(self.zero_region[self.acc_off:self.acc_off + 6], non_blocking=True)
+        torch.cuda.current_stream(self.dev).synchronize()
+        a = self._acc_host
+        return float(a[0]) / max(float(a[5]), 1.0)
+
+
 class B200Backend:
     """``trainer.LocalTrainer`` back-end on the engine (one engine per (batch, size) shape)."""
 
