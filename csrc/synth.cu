@@ -80,14 +80,17 @@ __global__ void __launch_bounds__(256) synth_cracks_k(uint8_t* __restrict__ img,
 // out[b] = {foreground area, boundary pixels, component seeds, sum of probabilities}
 __global__ void __launch_bounds__(256) measure_masks_k(const float* __restrict__ prob, float* __restrict__ out, int H, int W,
                                                        int threshold) {
+  // grid (B, slices): each block reduces a band of rows and adds its four partial sums to the (pre-zeroed) output
   const int b = blockIdx.x;
   const float* p = prob + (long)b * H * W;
+  const int rows = (H + gridDim.y - 1) / gridDim.y;
+  const int y0 = blockIdx.y * rows, y1 = min(H, y0 + rows);
   auto fg = [&](int y, int x) -> bool {
     if (y < 0 || y >= H || x < 0 || x >= W) return false;
     return (int)(p[y * W + x] * 255.f) > threshold;   // (pred*255).astype(uint8) then threshold(127, 255, BINARY)
   };
   float a[4] = {0, 0, 0, 0};
-  for (int i = threadIdx.x; i < H * W; i += blockDim.x) {
+  for (int i = y0 * W + threadIdx.x; i < y1 * W; i += blockDim.x) {
     const int y = i / W, x = i % W;
     a[3] += p[i];
     if (!fg(y, x)) continue;
@@ -104,7 +107,7 @@ __global__ void __launch_bounds__(256) measure_masks_k(const float* __restrict__
   if (threadIdx.x < 4) {
     float v = 0.f;
     for (int i = 0; i < 8; ++i) v += red[threadIdx.x][i];
-    out[b * 4 + threadIdx.x] = v;
+    atomicAdd(out + b * 4 + threadIdx.x, v);
   }
 }
 
@@ -119,7 +122,12 @@ int crackfl_synth_cracks(void* img_u8, void* mask_u8, int B, int H, int W, unsig
 }
 
 int crackfl_measure_masks(const float* prob, float* out4, int B, int H, int W, int threshold, cudaStream_t st) {
-  measure_masks_k<<<B, 256, 0, st>>>(prob, out4, H, W, threshold);
+  cudaError_t e = cudaMemsetAsync(out4, 0, (size_t)B * 4 * sizeof(float), st);
+  if (e != cudaSuccess) return (int)e;
+  int slices = (148 * 4 + B - 1) / B;  // about four blocks per SM over the whole batch (one block per image used 16 SMs)
+  if (slices > H) slices = H;
+  if (slices < 1) slices = 1;
+  measure_masks_k<<<dim3(B, slices), 256, 0, st>>>(prob, out4, H, W, threshold);
   CK_LAUNCH_CHECK();
   return 0;
 }
