@@ -138,6 +138,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    e2e_drain = None
     if a.impl == "standin":
         from baseline.torch_standin import StandinTrainer
         tr = StandinTrainer(spec, dev)
@@ -161,12 +162,25 @@ def main():
 
         eng.prefetch(hx[0], hy[0])
 
+        pending = [None, None]  # [ticket of the step whose loss has not been read yet, last loss]
+
         def step_e2e(i):
-            # public API: batch i was handed to prefetch() (pinned H2D on the copy stream); start the copy of batch
-            # i+1 so that it overlaps this step's compute, train on batch i, read its loss back (D2H, synchronises)
+            # public API: batch i was handed to prefetch() (pinned H2D on the copy stream); train on it, enqueue the D2H
+            # read of its loss, start the copy of batch i+1, and only then block on the loss of step i-1: every step's
+            # loss is read on the host inside the timed region, one step behind the launches (e2e_drain reads the last)
             eng.train_step_prefetched()
+            ticket = eng.enqueue_loss_read()
             eng.prefetch(hx[(i + 1) % NB], hy[(i + 1) % NB])
-            return eng.step_loss_host()
+            if pending[0] is not None:
+                pending[1] = eng.wait_loss(pending[0])
+            pending[0] = ticket
+            return pending[1]
+
+        def e2e_drain():
+            if pending[0] is not None:
+                pending[1] = eng.wait_loss(pending[0])
+                pending[0] = None
+            return pending[1]
 
         def round_end():
             # FedAvg round boundary: publish the local fit, fused aggregate+broadcast kernel, reload, fresh Adam
@@ -212,6 +226,8 @@ def main():
         last = None
         for i in range(a.steps):
             last = step_e2e(i)
+        if e2e_drain is not None:
+            last = e2e_drain()
         round_end()
         t1.record()
         barrier()

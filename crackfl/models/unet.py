@@ -849,6 +849,26 @@ class UNetEngine:
         return float(a[0]) / max(float(a[5]), 1.0)
 
 
+    def enqueue_loss_read(self) -> int:
+        """Asynchronous form of ``step_loss_host``: enqueue the 24-byte D2H copy of the step that was just launched (stream
+        ordered before the next step clears the accumulators) and return a ticket for ``wait_loss``.  Lets the caller
+        launch step i+1 before it blocks on the loss of step i, so the GPU never idles on the host's launch latency."""
+        if getattr(self, "_lr_host", None) is None:
+            self._lr_host = [torch.empty(6, dtype=torch.float32, pin_memory=True) for _ in range(2)]
+            self._lr_ev = [torch.cuda.Event(), torch.cuda.Event()]
+            self._lr_i = 0
+        i = self._lr_i
+        self._lr_i ^= 1
+        self._lr_host[i].copy_(self.zero_region[self.acc_off:self.acc_off + 6], non_blocking=True)
+        self._lr_ev[i].record(torch.cuda.current_stream(self.dev))
+        return i
+
+    def wait_loss(self, ticket: int) -> float:
+        self._lr_ev[ticket].synchronize()
+        a = self._lr_host[ticket]
+        return float(a[0]) / max(float(a[5]), 1.0)
+
+
 class B200Backend:
     """``trainer.LocalTrainer`` back-end on the engine (one engine per (batch, size) shape)."""
 
