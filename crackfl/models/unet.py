@@ -901,7 +901,27 @@ class B200Backend:
         return self._hx, (self._hy if y_u8 is not None else None)
 
     def train_batch(self, x_u8, y_u8):
-        self.engine.train_step(*self._stage(x_u8, y_u8))
+        """Host batches go through two pinned buffers in turn and the engine's copy stream, so preparing batch i+1 on the
+        host (and its H2D copy) overlaps training on batch i; only the copy that last READ a pinned buffer is waited for,
+        never the training stream."""
+        if torch.is_tensor(x_u8) and x_u8.is_cuda:
+            self.engine.train_step(x_u8, y_u8)
+            return
+        eng = self.engine
+        if not hasattr(self, "_pin"):
+            self._pin = [(torch.empty_like(self._hx).pin_memory(), torch.empty_like(self._hy).pin_memory()) for _ in range(2)]
+            self._pin_ev = [None, None]
+            self._pi = 0
+        i = self._pi
+        self._pi ^= 1
+        if self._pin_ev[i] is not None:
+            self._pin_ev[i].synchronize()  # the H2D copy that read this pinned buffer two batches ago is done
+        hx, hy = self._pin[i]
+        hx.copy_(torch.as_tensor(np.ascontiguousarray(x_u8)).reshape(hx.shape))
+        hy.copy_(torch.as_tensor(np.ascontiguousarray(y_u8)).reshape(hy.shape))
+        eng.prefetch(hx, hy)
+        self._pin_ev[i] = eng._stage_ev[eng._stage_pending]
+        eng.train_step_prefetched()
 
     def eval_batch(self, x_u8, y_u8):
         self.engine.eval_step(*self._stage(x_u8, y_u8))
