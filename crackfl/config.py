@@ -43,6 +43,8 @@ class ServerConfig:
     log_dir: str = "."  # 'L' uploads land in '.' + title[11:] (fl_server.py:84-89)
     resume: bool = False  # extension: reload round/version/weights/optimizer state
     aggregator: str = "auto"  # auto | host | device
+    check_finite: bool = True  # extension: reject updates holding NaN/Inf before they are queued
+    fin_grace_s: float = 0.0  # serve_forever: how long to keep answering after the last round; 0 = client.poll_interval_s + 5
     seed: int = 0
 
 

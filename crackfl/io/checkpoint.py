@@ -5,7 +5,12 @@ never read back) and no round counter, so a restarted server starts again from r
 with a fresh model.  This format lets the server resume: the manifest carries round,
 model_version, the client registry and the server-optimiser (FedAdam m/v) state; each
 arena is one little-endian float32 file that can be mapped straight into the device
-arena.  Writes are atomic (tmp + rename).
+arena.  Every file is written tmp + rename, and the checkpoint AS A WHOLE commits at one
+point: arenas are written under names that carry a save id (``global.<id>.f32``), the
+manifest that names them is renamed into place last, and only then are the previous
+save's arena files deleted.  A crash at any moment leaves either the old manifest with
+its old arenas or the new manifest with its new arenas, never new weights under the old
+round number.
 """
 from __future__ import annotations
 
@@ -36,10 +41,18 @@ def save_checkpoint(dirpath: str, spec, weights: Sequence[np.ndarray], meta: Opt
     arenas = {"global": weights}
     arenas.update(extra_arenas or {})
     files = {}
+    old_files = []
+    try:
+        with open(os.path.join(dirpath, "manifest.json")) as f:
+            old_files = list(json.load(f).get("arenas", {}).values())
+    except (OSError, ValueError):
+        pass
+    mv = (meta or {}).get("model_version")
+    save_id = f"{mv if mv is not None else 'x'}-{time.time_ns():x}"
     for name, wl in arenas.items():
         if wl is None:
             continue
-        fn = f"{name}.f32"
+        fn = f"{name}.{save_id}.f32"
         _atomic_write(os.path.join(dirpath, fn), flatten(wl, spec).astype("<f4").tobytes())
         files[name] = fn
     manifest = {
@@ -52,7 +65,13 @@ def save_checkpoint(dirpath: str, spec, weights: Sequence[np.ndarray], meta: Opt
         "arenas": files,
         "meta": meta or {},
     }
-    _atomic_write(os.path.join(dirpath, "manifest.json"), json.dumps(manifest, indent=1).encode())
+    _atomic_write(os.path.join(dirpath, "manifest.json"), json.dumps(manifest, indent=1).encode())  # the commit point
+    for fn in old_files:
+        if fn not in files.values():
+            try:
+                os.remove(os.path.join(dirpath, fn))
+            except OSError:
+                pass
     return os.path.join(dirpath, "manifest.json")
 
 

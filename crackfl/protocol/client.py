@@ -61,9 +61,11 @@ def request_traindone(name: str, cr: int, payload: bytes, extra: dict, cap: int)
             current_round=cr, config=pb.to_config(cfgd)))
 
 
-def request_model_version(mv: int, cr: int):
-    yield pb.transportRequest(version_req=pb.VersionReq(type="P", config=pb.to_config(
-        {"model_version": mv, "current_round": cr})))
+def request_model_version(mv: int, cr: int, name: str = ""):
+    cfgd = {"model_version": mv, "current_round": cr}
+    if name:
+        cfgd["cname"] = name  # extension: lets the server tick this client off when it answers FIN
+    yield pb.transportRequest(version_req=pb.VersionReq(type="P", config=pb.to_config(cfgd)))
 
 
 def get_file_chunks(filename: str, chunk_bytes: int):
@@ -79,6 +81,14 @@ def get_file_chunks(filename: str, chunk_bytes: int):
             i += 1
             if len(piece) < chunk_bytes:
                 return
+
+
+def _is_unavailable(e: Exception) -> bool:
+    try:
+        import grpc
+        return isinstance(e, grpc.RpcError) and e.code() in (grpc.StatusCode.UNAVAILABLE, grpc.StatusCode.CANCELLED)
+    except Exception:
+        return False
 
 
 def _collect_weights(responses: Iterable, field: str):
@@ -163,14 +173,22 @@ class FLClient:
                 new = None
                 while new is None:
                     self.sleep(cfg.client.poll_interval_s)  # fl_client.py:141
-                    vrep, vblob = _collect_weights(
-                        self.transport(request_model_version(info["mv"], info["cr"])), "version_rep")
+                    try:
+                        vrep, vblob = _collect_weights(
+                            self.transport(request_model_version(info["mv"], info["cr"], self.name)), "version_rep")
+                    except Exception as e:
+                        # a server that has shut down after the last round is the same news as FIN
+                        if info["cr"] >= info["mtr"] and _is_unavailable(e):
+                            self.log(f"[{self.name}] server gone after the last round: treated as FIN")
+                            state, vrep = "FIN", None
+                            break
+                        raise
                     if vrep.state == pb.State.NOT_WAIT:
                         new = vblob
                     elif vrep.state == pb.State.FIN:
                         state = "FIN"
                         break
-                vc = pb.from_config(vrep.config)
+                vc = pb.from_config(vrep.config) if vrep is not None else {}
                 info["cr"], info["mv"] = vc.get("current_round", info["cr"] + 1), vc.get("model_version", info["mv"])
                 if state == "FIN":
                     break

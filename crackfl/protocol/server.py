@@ -116,6 +116,9 @@ class FLServer:
         self._payload_cache = {}
         self._chunks: Dict[str, Dict[int, bytes]] = {}
         self._next_id = 0
+        self.final_clients: List[str] = []  # reporters of the last round: each must be told FIN before the server stops
+        self.fin_answered: set = set()
+        self.finished_at: Optional[float] = None
         if s.resume and ckpt.has_checkpoint(s.weights_dir):
             self._resume()
 
@@ -150,11 +153,19 @@ class FLServer:
                 # reference names are client{randint(1,100000)} and can collide (fl_client.py:26)
                 self._next_id += 1
                 assigned = f"{name or 'client'}#{self._next_id}"
+            cap = getattr(self.aggregator, "max_clients", 0) or 0
+            if cap and assigned not in self.ready_clients and len(self.ready_clients) >= cap:
+                return {"state": CTW}  # the device aggregator has a fixed number of staging slots
             if assigned not in self.ready_clients:
                 self.ready_clients.append(assigned)
             out = {}
             if int(config.get("current_round", 0) or 0) == 0:
-                self.current_round = 1
+                # the reference does ``ALL_CURRENT_ROUND = 1`` on every such request (fl_server.py:61-63); with rounds
+                # that last seconds a client can be admitted AFTER the first aggregation, and resetting the counter then
+                # would strand everybody (stale-drop + WAIT forever).  Only the very first ready starts round 1; a later
+                # joiner is handed the live round and model version.
+                if self.current_round == 0:
+                    self.current_round = 1
                 if self.round_started_at is None:
                     self.round_started_at = self.clock()
                 out = {"state": SW, "model_version": self.model_version, "current_round": self.current_round,
@@ -189,6 +200,8 @@ class FLServer:
         self._persist(rec)
         if finished_round >= s.max_rounds:
             self.finished = True
+            self.final_clients = list(rec["clients"])
+            self.finished_at = self.clock()
             self.log(f"[server] all {s.max_rounds} rounds done -> FIN")
             return FIN
         self.log(f"[server] round {finished_round} aggregated ({rec['num_clients']} clients, {agg_ms:.2f} ms) -> RESP_ARY")
@@ -202,7 +215,7 @@ class FLServer:
                 len(self.round_updates) >= max(1, s.min_fit_clients):
             self.log(f"[server] round {self.current_round} deadline: aggregating {len(self.round_updates)} of "
                      f"{self._target_count()} clients")
-            self._aggregate_locked()
+            self._aggregate_guarded(self.round_reporters[-1])
 
     def manage_rounds(self, cname: str, client_round: int, weights: List[np.ndarray], num_samples: float = 0.0,
                       metrics: Optional[dict] = None) -> str:
@@ -212,8 +225,7 @@ class FLServer:
                 return FIN if self.finished else RESP_ACY  # stale update dropped (fl_server.py:134-135)
             if cname in self.round_reporters:
                 return RESP_ACY  # duplicate report
-            if len(weights) != self.spec.num_tensors:
-                raise ValueError(f"update from {cname} has {len(weights)} tensors, expected {self.spec.num_tensors}")
+            weights = self._validated(cname, weights)
             self.round_reporters.append(cname)
             self.round_updates.append(weights)
             self.round_samples.append(float(num_samples))
@@ -224,8 +236,49 @@ class FLServer:
             if s.round_timeout_s <= 0 and s.min_fit_clients > 0:
                 target = min(target, s.min_fit_clients)
             if len(self.round_updates) >= target:
-                return self._aggregate_locked()
+                return self._aggregate_guarded(cname)
             return RESP_ACY
+
+    def _validated(self, cname: str, weights) -> List[np.ndarray]:
+        """Reject an update BEFORE it is queued: tensor count, exact shapes (NumPy broadcasting would silently accept
+        ``(1,)`` or ``()``), float dtype, finite values.  Raises ValueError; nothing is stored."""
+        if len(weights) != self.spec.num_tensors:
+            raise ValueError(f"update from {cname} has {len(weights)} tensors, expected {self.spec.num_tensors}")
+        out = []
+        for t, w in zip(self.spec.tensors, weights):
+            a = np.asarray(w)
+            if tuple(a.shape) != tuple(t.shape):
+                raise ValueError(f"update from {cname}: tensor {t.name} has shape {tuple(a.shape)}, expected {tuple(t.shape)}")
+            if a.dtype.kind != "f":
+                raise ValueError(f"update from {cname}: tensor {t.name} has dtype {a.dtype}, expected a float type")
+            if self.cfg.server.check_finite and not np.isfinite(a).all():
+                raise ValueError(f"update from {cname}: tensor {t.name} holds non-finite values")
+            out.append(a)
+        return out
+
+    def _aggregate_guarded(self, cname: str) -> str:
+        """Aggregate; if the aggregator raises, evict the update that triggered it (and restore the optimiser state)
+        so that one bad client cannot wedge every later 'D' of the round on the same exception."""
+        strat = getattr(self.aggregator, "strategy", None)
+        snap = strat.state() if strat is not None and hasattr(strat, "state") else None
+        if snap and snap.get("m") is not None:
+            snap = {"m": np.array(snap["m"], copy=True), "v": np.array(snap["v"], copy=True)}
+        else:
+            snap = None
+        try:
+            return self._aggregate_locked()
+        except Exception:
+            if cname in self.round_reporters:
+                i = self.round_reporters.index(cname)
+                for lst in (self.round_reporters, self.round_updates, self.round_samples):
+                    del lst[i]
+                self.round_metrics = [m for m in self.round_metrics if m.get("cname") != cname]
+            if cname in self.ready_clients and len(self.ready_clients) > 1:
+                self.ready_clients.remove(cname)  # not waited for any more
+            if snap is not None:
+                strat.load_state(snap)
+            self.log(f"[server] aggregation failed on the update from {cname}: evicted")
+            raise
 
     def version_check(self, client_version: int, client_round: int):
         with self.lock:
@@ -284,6 +337,8 @@ class FLServer:
             if f == "duplicate":
                 self.manage_rounds(u.cname, u.current_round, weights)
             cfgd = {"model_version": self.model_version, "current_round": self.current_round, "state": state}
+            if state == FIN:
+                self._note_fin(u.cname)
             if state == RESP_ARY:
                 return self._weight_replies(lambda chunk, c: R(update_rep=pb.UpdateRep(
                     type="D", buffer_chunk=chunk, config=pb.to_config(c))), cfgd)
@@ -291,11 +346,28 @@ class FLServer:
         if req.version_req.type == "P":
             vc = pb.from_config(req.version_req.config)
             st, cfgd = self.version_check(int(vc.get("model_version", 0) or 0), int(vc.get("current_round", 0) or 0))
+            if st == pb.State.FIN:
+                self._note_fin(str(vc.get("cname", "") or ""))
             if st == pb.State.NOT_WAIT:
                 return self._weight_replies(lambda chunk, c: R(version_rep=pb.VersionRep(
                     state=st, buffer_chunk=chunk, config=pb.to_config(c))), cfgd)
             return [R(version_rep=pb.VersionRep(state=st, config=pb.to_config(cfgd)))]
         raise ValueError("unrecognised request")
+
+    def _note_fin(self, cname: str):
+        with self.lock:
+            self.fin_answered.add(cname or f"?{len(self.fin_answered)}")
+
+    def all_fin_delivered(self) -> bool:
+        """True once every reporter of the final round has been sent FIN (D reply or version poll).  Polls from clients
+        that do not name themselves (the reference's version request has no cname) are counted, not matched."""
+        with self.lock:
+            if not self.finished:
+                return False
+            named = {c for c in self.fin_answered if not c.startswith("?")}
+            anon = len(self.fin_answered) - len(named)
+            missing = [c for c in self.final_clients if c not in named]
+            return len(missing) <= anon
 
     def _fault(self, tag: str) -> str:
         return self.fault.on_request(tag, self.sleep) if self.fault else "ok"
@@ -383,10 +455,17 @@ def serve_forever(server: FLServer):
     gs, port = make_grpc_server(server)
     gs.start()
     server.log(f"[server] listening on {server.cfg.transport.bind} (port {port})")
+    # The reference server never stops (fl_server.py:222-226).  This one does, but only after every client of the last
+    # round has been told FIN: all but the last reporter learn it from a ``version P`` poll, which they send only every
+    # client.poll_interval_s (20 s by default), so stopping right after the aggregation would hand them a dead channel.
+    grace = server.cfg.server.fin_grace_s or (server.cfg.client.poll_interval_s + 5.0)
     try:
         while not server.finished:
-            time.sleep(0.5)
-        time.sleep(2.0)  # let the last FIN replies drain
+            time.sleep(0.2)
+        t_end = time.monotonic() + grace
+        while not server.all_fin_delivered() and time.monotonic() < t_end:
+            time.sleep(0.2)
+        time.sleep(1.0)  # let the last replies (and a final 'P' fetch of the aggregated model) drain
     except KeyboardInterrupt:
         pass
-    gs.stop(0)
+    gs.stop(2.0)

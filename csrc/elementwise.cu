@@ -1612,6 +1612,8 @@ constexpr int kMaxDevices = 64;
 float* g_noalloc_ptr[kMaxDevices] = {nullptr};
 
 // In host code `g_noalloc_bn_scratch` is only a handle for the device symbol, not an address a kernel can use.
+// The per-device cache below is a plain array: two host threads that make their first call on the same device at the
+// same moment may both do the look-up; they store the same value, so the only cost is the repeated look-up.
 int noalloc_scratch_for_current_device(float** out) {
   int dev = -1;
   cudaError_t e = cudaGetDevice(&dev);
@@ -1647,6 +1649,7 @@ int crackfl_bn_train_fwd_noalloc(const void* y, const float* gamma, const float*
                     "with C/8 dividing %d)\n", B, H, W, C, TPB);
     return (int)cudaErrorInvalidValue;
   }
+  CK_FITS32((long)B * H * W * C);  // bn_act_k indexes with 32-bit ints, as crackfl_bn_act does
   float* scratch = nullptr;
   int rc = noalloc_scratch_for_current_device(&scratch);
   if (rc) return rc;

@@ -109,3 +109,33 @@ def test_flatten_unflatten_and_checkpoint(tmp_path):
     np.testing.assert_array_equal(st["arenas"]["fedadam_m"][7], m[7])
     with pytest.raises(ValueError):
         wio.flatten(w[:-1], S)
+
+
+def test_checkpoint_commits_at_the_manifest(tmp_path, monkeypatch):
+    """Arena files carry a save id and the manifest rename is the single commit point: a crash after the new arenas are
+    written but before the manifest is replaced must leave the OLD round with the OLD weights."""
+    from crackfl.io import checkpoint as ck
+    from crackfl.models.spec import REFERENCE_SPEC as S
+    w1 = S.init_weights(1)
+    w2 = [w + 1 for w in w1]
+    d = str(tmp_path / "ck")
+    ck.save_checkpoint(d, S, w1, meta={"current_round": 2, "model_version": 2})
+    real = ck._atomic_write
+    def crash_on_manifest(path, data):
+        if path.endswith("manifest.json"):
+            raise OSError("power cut")
+        real(path, data)
+    monkeypatch.setattr(ck, "_atomic_write", crash_on_manifest)
+    with pytest.raises(OSError):
+        ck.save_checkpoint(d, S, w2, meta={"current_round": 3, "model_version": 3})
+    monkeypatch.setattr(ck, "_atomic_write", real)
+    st = ck.load_checkpoint(d, S)
+    assert st["meta"]["current_round"] == 2
+    np.testing.assert_array_equal(st["weights"][0], w1[0])
+    # a completed save replaces it and removes the previous arenas
+    ck.save_checkpoint(d, S, w2, meta={"current_round": 3, "model_version": 3})
+    st = ck.load_checkpoint(d, S)
+    assert st["meta"]["current_round"] == 3
+    np.testing.assert_array_equal(st["weights"][0], w2[0])
+    import os
+    assert sum(f.startswith("global.") for f in os.listdir(d)) <= 2  # the live one (+ the orphan of the crashed save)

@@ -231,3 +231,115 @@ def test_late_client_gets_ctw(tmp_path):
     clk.t += 100
     cl = C.FLClient(cfg, _StubTrainer(0.0), srv.transport, sleep=clk.sleep, log=lambda s: None)
     assert cl.run()["state"] == "CTW"
+
+
+def test_join_after_first_aggregation_does_not_reset_round(tmp_path):
+    """A fast first round can finish inside the admission window.  A client admitted after it must get the LIVE round
+    and model version (the reference would set the round back to 1, fl_server.py:61-63, and strand everybody)."""
+    srv, clk, cfg = _server(tmp_path, admission_window_s=10.0, ready_delay_s=0.0, max_rounds=2)
+    w0 = S.init_weights(0)
+    assert _ready(srv, "a")["current_round"] == 1
+    c, _ = _done(srv, "a", 1, [x + 1 for x in w0])
+    assert c["state"] == "RESP_ARY" and srv.current_round == 2 and srv.model_version == 2
+    clk.t = 3.0  # still inside the window
+    b = _ready(srv, "b")
+    assert b["state"] == "SW" and b["current_round"] == 2 and b["model_version"] == 2
+    assert srv.current_round == 2  # not reset
+    # both finish round 2: a is first (waits), b completes the round -> FIN for everybody
+    c, _ = _done(srv, "a", 2, [x + 1 for x in w0]); assert c["state"] == "RESP_ACY"
+    c, _ = _done(srv, "b", 2, [x + 3 for x in w0]); assert c["state"] == "FIN"
+    v = _one(srv, next(C.request_model_version(2, 2, "a"))).version_rep
+    assert v.state == pb.State.FIN and srv.all_fin_delivered()
+
+
+def test_malformed_update_is_rejected_and_does_not_wedge_the_round(tmp_path):
+    srv, clk, cfg = _server(tmp_path, max_rounds=1)
+    _ready(srv, "good"); _ready(srv, "bad")
+    w0 = S.init_weights(0)
+    # broadcastable shape: NumPy would silently accept it and corrupt the mean
+    wbad = [x.copy() for x in w0]; wbad[0] = np.zeros((1,), np.float32)
+    with pytest.raises(ValueError, match="shape"):
+        srv.manage_rounds("bad", 1, wbad)
+    wint = [x.copy() for x in w0]; wint[1] = wint[1].astype(np.int32)
+    with pytest.raises(ValueError, match="dtype"):
+        srv.manage_rounds("bad", 1, wint)
+    wnan = [x.copy() for x in w0]; wnan[2] = wnan[2] + np.nan
+    with pytest.raises(ValueError, match="non-finite"):
+        srv.manage_rounds("bad", 1, wnan)
+    assert srv.round_updates == [] and srv.round_reporters == []
+    # the round still completes once proper updates arrive
+    c, _ = _done(srv, "good", 1, [x + 1 for x in w0]); assert c["state"] == "RESP_ACY"
+    c, _ = _done(srv, "bad", 1, [x + 3 for x in w0]); assert c["state"] == "FIN"
+    np.testing.assert_allclose(srv.global_weights[0], w0[0] + 2, rtol=1e-6)
+
+
+def test_aggregator_failure_evicts_the_triggering_update(tmp_path):
+    srv, clk, cfg = _server(tmp_path, max_rounds=1)
+
+    class Flaky:
+        kind, calls = "host", 0
+        def aggregate(self, g, ups, ns=None):
+            Flaky.calls += 1
+            if Flaky.calls == 1:
+                raise RuntimeError("boom")
+            return [np.mean([u[i] for u in ups], axis=0) for i in range(len(g))]
+    srv.aggregator = Flaky()
+    _ready(srv, "a"); _ready(srv, "b")
+    w0 = S.init_weights(0)
+    _done(srv, "a", 1, [x + 1 for x in w0])
+    with pytest.raises(RuntimeError):
+        srv.manage_rounds("b", 1, [x + 3 for x in w0])
+    assert srv.round_reporters == ["a"] and "b" not in srv.ready_clients  # evicted, not queued
+    # nothing is wedged: a is the only client waited for; its (already queued) update aggregates on the next trigger
+    c, _ = _done(srv, "c-late", 1, [x + 5 for x in w0])
+    assert c["state"] == "FIN" and srv.finished
+
+
+def test_admission_capped_at_aggregator_slots(tmp_path):
+    srv, clk, cfg = _server(tmp_path)
+    srv.aggregator.max_clients = 2
+    assert _ready(srv, "a")["state"] == "SW" and _ready(srv, "b")["state"] == "SW"
+    assert _ready(srv, "c")["state"] == "CTW" and len(srv.ready_clients) == 2
+
+
+def test_serve_forever_keeps_serving_until_every_client_heard_fin(tmp_path, monkeypatch):
+    """serve_forever used to stop 2 s after the last aggregation; clients still inside their poll interval then hit a
+    dead server.  Here the poll interval (1.5 s) is longer than that old drain would be relative to the test's clock."""
+    import socket
+    import time as _t
+    from crackfl.protocol.server import serve_forever
+    monkeypatch.chdir(tmp_path)
+    s_ = socket.socket(); s_.bind(("127.0.0.1", 0)); port = s_.getsockname()[1]; s_.close()
+    cfg = fast_test_config()
+    cfg.server.max_rounds = 1
+    cfg.server.weights_dir = str(tmp_path / "sw")
+    cfg.transport.bind = f"127.0.0.1:{port}"
+    cfg.client.poll_interval_s = 1.5
+    cfg.server.fin_grace_s = 20.0
+    srv = FLServer(cfg, S.init_weights(0), S, log=lambda s: None)
+    st = threading.Thread(target=serve_forever, args=(srv,), daemon=True)
+    st.start()
+    _t.sleep(0.3)
+    results = {}
+    def run_client(i, delay):
+        ccfg = fast_test_config()
+        ccfg.client.name = f"c{i}"
+        ccfg.client.poll_interval_s = 1.5
+        ccfg.client.write_weights_file = False
+        call, ch = C.make_stub(ccfg, f"127.0.0.1:{port}")
+        tr = _StubTrainer(1.0)
+        orig = tr.fit
+        def slow_fit(w, cr):
+            _t.sleep(delay)
+            return orig(w, cr)
+        tr.fit = slow_fit
+        cl = C.FLClient(ccfg, tr, call, log=lambda s: None)
+        results[i] = (cl.run(), cl.final_weights is not None)
+        ch.close()
+    ts = [threading.Thread(target=run_client, args=(i, d)) for i, d in ((0, 0.0), (1, 0.4))]
+    [t.start() for t in ts]; [t.join(60) for t in ts]
+    st.join(30)
+    assert not st.is_alive()
+    assert results[0][0]["state"] == "FIN" and results[1][0]["state"] == "FIN"
+    assert results[0][1], "the first reporter must still be able to fetch the final model"
+    assert srv.all_fin_delivered()
