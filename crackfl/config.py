@@ -68,6 +68,8 @@ class TrainConfig:
     beta2: float = 0.999
     adam_eps: float = 1e-7
     loss: str = "bce"  # "bce" (client_fit_model.py:157) | "bce_dice" (extension)
+    bce_clip: bool = False  # False: cross-entropy from the logit, what Keras 2 fit() computes for a sigmoid output layer
+    #                         True: clipped probabilities [1e-7, 1-1e-7] (backend fall-back / Keras 3): no gradient outside
     dtype: str = "bf16"  # compute dtype of the B200 engine; the oracle back-end is fp32
     backend: str = "auto"  # auto | b200 | torch_ref
     shuffle_batches: bool = True  # Keras fit on a Sequence shuffles batch order each epoch

@@ -44,7 +44,7 @@ class UNetEngine:
     def __init__(self, spec: UNetSpec = REFERENCE_SPEC, batch: int = 16, height: int = 128, width: int = 128,
                  device: Optional[int] = None, lr: float = 1e-3, beta1: float = 0.9, beta2: float = 0.999,
                  eps: float = 1e-7, loss: str = "bce", conv_impl: Optional[str] = None, cuda_graph: bool = True,
-                 dice_smooth: float = 1.0):
+                 dice_smooth: float = 1.0, bce_clip: bool = False, arena: Optional[torch.Tensor] = None):
         if not torch.cuda.is_available():
             raise RuntimeError("UNetEngine needs a CUDA device (sm_100a)")
         spec.check_input(height, width)
@@ -54,6 +54,9 @@ class UNetEngine:
         self.lr, self.b1, self.b2, self.eps = lr, beta1, beta2, eps
         self.use_dice = 1 if loss == "bce_dice" else 0
         self.dice_smooth = dice_smooth
+        # 0: cross-entropy from the logit (what Keras 2 `fit` computes for a sigmoid output layer); 1: clipped probabilities
+        self.bce_clip = 1 if bce_clip else 0
+        self._ext_arena = arena
         self.conv_impl = conv_impl or default_conv_impl()
         self.cuda_graph = cuda_graph
         self.side_streams = os.environ.get("CRACKFL_SIDE_STREAM", "1") != "0"
@@ -484,7 +487,7 @@ class UNetEngine:
         dl = self.dec[-1]
         prog.append((lib.crackfl_head_fwd, (b(xprev), self.P(head.tensors[0]), self.P(head.tensors[1]),
                                             b("mask_u8") if with_mask else 0, self._acc_ptr() if with_mask else 0,
-                                            b("prob") if prob else 0, B, dl["r"], dl["rw"], dl["f"])))
+                                            b("prob") if prob else 0, B, dl["r"], dl["rw"], dl["f"], self.bce_clip)))
         return prog
 
     def _build_train(self):
@@ -502,11 +505,12 @@ class UNetEngine:
             self.n_fwd = len(prog)
             prog.append((lib.crackfl_head_fwd_bwd, (b(last + "s"), self.P(head.tensors[0]), self.P(head.tensors[1]), b("mask_u8"),
                                                     self._acc_ptr(), b(last + "ds"), self.G(head.tensors[0]),
-                                                    self.G(head.tensors[1]), B, dl["r"], dl["rw"], dl["f"], 1.0)))
+                                                    self.G(head.tensors[1]), B, dl["r"], dl["rw"], dl["f"], 1.0, self.bce_clip)))
         else:
             prog.append((lib.crackfl_head_bwd, (b(last + "s"), self.P(head.tensors[0]), self.P(head.tensors[1]), b("mask_u8"),
                                                 self._acc_ptr(), b(last + "ds"), self.G(head.tensors[0]), self.G(head.tensors[1]),
-                                                B, dl["r"], dl["rw"], dl["f"], self.use_dice, self.dice_smooth, 1.0)))
+                                                B, dl["r"], dl["rw"], dl["f"], self.use_dice, self.dice_smooth, 1.0,
+                                                self.bce_clip)))
         # ---- decoder backward
         for d, (ct1, bn1, ct2, bn2, res) in reversed(list(zip(self.dec, decs))):
             j, r, rw, cin, f = d["j"], d["r"], d["rw"], d["cin"], d["f"]
@@ -878,7 +882,8 @@ class B200Backend:
         t = cfg.train
         self.cfg, self.spec = cfg, spec
         self.engine = UNetEngine(spec, t.batch_size, t.image_size[0], t.image_size[1], device=device, lr=t.lr,
-                                 beta1=t.beta1, beta2=t.beta2, eps=t.adam_eps, loss=t.loss, cuda_graph=t.cuda_graph)
+                                 beta1=t.beta1, beta2=t.beta2, eps=t.adam_eps, loss=t.loss, cuda_graph=t.cuda_graph,
+                                 bce_clip=t.bce_clip)
         B, H, W = t.batch_size, t.image_size[0], t.image_size[1]
         self._hx = torch.empty((B, H, W, 3), dtype=torch.uint8).pin_memory()
         self._hy = torch.empty((B, H, W), dtype=torch.uint8).pin_memory()

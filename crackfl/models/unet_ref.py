@@ -9,7 +9,13 @@ that differ from PyTorch defaults made explicit (hard part H1):
 * ``Conv2DTranspose(f, 3, padding="same")`` stride 1, kernel stored ``(kh,kw,out,in)``;
 * BatchNormalization eps=1e-3, momentum=0.99; running variance gets the unbiased batch
   variance (TF fused batch norm behaviour), normalisation uses the biased one;
-* binary cross-entropy on probabilities clipped to [1e-7, 1-1e-7];
+* binary cross-entropy: Keras 2 ``fit`` on a model whose output layer carries ``activation="sigmoid"``
+  (``client_fit_model.py:145,157``) does NOT use the clipped-probability formula: ``backend.binary_crossentropy``
+  recovers the sigmoid's input (``_keras_logits`` / the op type ``Sigmoid``) and calls
+  ``tf.nn.sigmoid_cross_entropy_with_logits``, whose gradient ``sigmoid(z) - y`` never vanishes.  That is the default
+  here (``bce_logits_loss``).  The clipped form (``bce_loss``: probabilities in [1e-7, 1-1e-7], zero gradient outside,
+  the backend's fall-back and Keras 3's formula) is kept behind ``bce_clip=True``; with it a model whose logits all
+  pass -16.1 stops training for good (measured: ``scripts/fed_convergence.py``);
 * Keras Adam: ``theta -= lr_t * m / (sqrt(v) + eps)``, eps=1e-7 outside the bias correction.
 
 The weights argument is always the list of 112 tensors in ``UNetSpec`` order/layout.
@@ -137,6 +143,11 @@ def bce_loss(prob: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
     return -(y * torch.log(p) + (1.0 - y) * torch.log(1.0 - p)).mean()
 
 
+def bce_logits_loss(logits: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+    """``tf.nn.sigmoid_cross_entropy_with_logits`` averaged over every pixel: max(z,0) - z*y + log(1+exp(-|z|))."""
+    return (logits.clamp_min(0) - logits * y + torch.log1p(torch.exp(-logits.abs()))).mean()
+
+
 def dice_loss(prob: torch.Tensor, y: torch.Tensor, smooth: float = 1.0) -> torch.Tensor:
     """Soft Dice loss over the whole batch (north-star extension; not in the reference)."""
     inter = (prob * y).sum()
@@ -178,8 +189,9 @@ class RefTrainer:
     """
 
     def __init__(self, weights: Sequence, spec: UNetSpec = REFERENCE_SPEC, lr: float = 1e-3,
-                 loss: str = "bce", dtype=torch.float32, device="cpu"):
+                 loss: str = "bce", dtype=torch.float32, device="cpu", bce_clip: bool = False):
         self.spec = spec
+        self.bce_clip = bce_clip
         self.w = to_torch_weights(weights, dtype, device)
         self.trainable = [i for i, t in enumerate(spec.tensors) if t.trainable]
         for i in self.trainable:
@@ -188,18 +200,19 @@ class RefTrainer:
         self.loss_kind = loss
         self.bn_slots = [(l.tensors[2], l.tensors[3]) for l in spec.layers if l.op == "bn"]
 
-    def _loss(self, prob, y):
-        l = bce_loss(prob, y)
+    def _loss(self, logits, y):
+        prob = torch.sigmoid(logits)
+        l = bce_loss(prob, y) if self.bce_clip else bce_logits_loss(logits, y)
         if self.loss_kind == "bce_dice":
             l = l + dice_loss(prob, y)
-        return l
+        return l, prob
 
     def train_step(self, x: torch.Tensor, y: torch.Tensor) -> Tuple[float, float]:
         """x NCHW float in [0,1], y N1HW in {0,1}.  Returns (loss, accuracy)."""
         for i in self.trainable:
             self.w[i].grad = None
-        prob, stats = unet_forward(self.w, x, training=True, spec=self.spec)
-        loss = self._loss(prob, y)
+        logits, stats = unet_forward(self.w, x, training=True, spec=self.spec, return_logits=True)
+        loss, prob = self._loss(logits, y)
         loss.backward()
         self.opt.step([self.w[i].grad for i in self.trainable])
         with torch.no_grad():
@@ -211,8 +224,9 @@ class RefTrainer:
 
     @torch.no_grad()
     def eval_step(self, x, y) -> Tuple[float, float]:
-        prob, _ = unet_forward(self.w, x, training=False, spec=self.spec)
-        return float(self._loss(prob, y)), float(binary_accuracy(prob, y))
+        logits, _ = unet_forward(self.w, x, training=False, spec=self.spec, return_logits=True)
+        loss, prob = self._loss(logits, y)
+        return float(loss), float(binary_accuracy(prob, y))
 
     @torch.no_grad()
     def predict(self, x) -> torch.Tensor:

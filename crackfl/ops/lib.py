@@ -75,9 +75,9 @@ _SIGS = {
     "crackfl_down2sum": [vp, vp, vp, vp, i32, i32, i32, i32, vp],
     "crackfl_relu_bwd_add": [vp, vp, vp, vp, i64, vp],
     "crackfl_colsum": [vp, vp, i64, i32, vp],
-    "crackfl_head_fwd": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],
-    "crackfl_head_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, f32, vp],
-    "crackfl_head_fwd_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, vp],
+    "crackfl_head_fwd": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    "crackfl_head_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, f32, i32, vp],
+    "crackfl_head_fwd_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, i32, vp],
     "crackfl_conv_simt_fwd": [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
     "crackfl_wgrad_simt": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, vp],
     "crackfl_conv_tc_fwd": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],

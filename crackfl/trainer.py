@@ -45,7 +45,8 @@ class TorchRefBackend:
 
     def begin_round(self, weights: Sequence[np.ndarray]):
         from .models.unet_ref import RefTrainer
-        self.tr = RefTrainer(weights, self.spec, lr=self.cfg.train.lr, loss=self.cfg.train.loss)
+        self.tr = RefTrainer(weights, self.spec, lr=self.cfg.train.lr, loss=self.cfg.train.loss,
+                             bce_clip=self.cfg.train.bce_clip)
         self.reset_metrics()
 
     @staticmethod

@@ -27,7 +27,7 @@ def nhwc_to_nchw(t: torch.Tensor) -> torch.Tensor:
 
 
 def oracle_run(spec: UNetSpec, weights: List[np.ndarray], x_u8: np.ndarray, y_u8: np.ndarray, device, loss="bce",
-               dtype=torch.float32):
+               dtype=torch.float32, bce_clip: bool = False):
     """fp32 oracle forward+backward on `device`.  Returns (loss, acc, taps, grads list, new bn stats)."""
     w = R.to_torch_weights(weights, dtype, device)
     trainable = [i for i, t in enumerate(spec.tensors) if t.trainable]
@@ -36,8 +36,9 @@ def oracle_run(spec: UNetSpec, weights: List[np.ndarray], x_u8: np.ndarray, y_u8
     x = torch.from_numpy(x_u8).to(device).permute(0, 3, 1, 2).to(dtype) / 255.0
     y = torch.from_numpy(y_u8).to(device).permute(0, 3, 1, 2).to(dtype)
     taps: Dict[str, torch.Tensor] = {}
-    prob, stats = R.unet_forward(w, x, training=True, spec=spec, taps=taps)
-    l = R.bce_loss(prob, y)
+    logits, stats = R.unet_forward(w, x, training=True, spec=spec, taps=taps, return_logits=True)
+    prob = torch.sigmoid(logits)
+    l = R.bce_loss(prob, y) if bce_clip else R.bce_logits_loss(logits, y)
     if loss == "bce_dice":
         l = l + R.dice_loss(prob, y)
     l.backward()

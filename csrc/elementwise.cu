@@ -745,6 +745,18 @@ __global__ void __launch_bounds__(TPB) colsum_k(const __nv_bfloat16* __restrict_
 // acc = [bce_sum, correct, inter, psum, ysum, pixel_count]
 // Thread mapping: thread = (pixel, channel-vector); the c8 threads of one pixel are adjacent lanes of a
 // warp and reduce the 1x1-conv dot product with shuffles (c8 must divide 32).
+// Binary cross-entropy of one logit against y in {0,1}.
+//   clip == 0 (default): the form Keras 2 trains with.  `fit` on a model whose output layer is
+//     Conv2D(..., activation="sigmoid") (client_fit_model.py:145,157) does not see probabilities: the sigmoid caches its
+//     input (`output._keras_logits`; in graph mode the op type "Sigmoid" is traced back) and backend.binary_crossentropy
+//     switches to tf.nn.sigmoid_cross_entropy_with_logits: max(z,0) - z*y + log(1+exp(-|z|)), gradient sigmoid(z)-y for
+//     EVERY z.
+//   clip == 1: the fall-back of the same function (and Keras 3): probabilities clipped to [1e-7, 1-1e-7], and
+//     clip_by_value passes no gradient outside the clip - once |z| > 16.1 everywhere the step is dead for good.
+__device__ __forceinline__ float bce_logit(float z, float yv) {
+  return fmaxf(z, 0.f) - z * yv + __logf(1.f + __expf(-fabsf(z)));
+}
+
 __device__ __forceinline__ float head_logit(const float f[8], const float* sw, int cv, int c8) {
   float l = 0.f;
 #pragma unroll
@@ -756,7 +768,7 @@ __device__ __forceinline__ float head_logit(const float f[8], const float* sw, i
 __global__ void __launch_bounds__(TPB) head_fwd_k(const __nv_bfloat16* __restrict__ s, const float* __restrict__ w,
                                                   const float* __restrict__ bias, const uint8_t* __restrict__ mask,
                                                   float* __restrict__ acc, float* __restrict__ prob, int B, int Hl, int Wl,
-                                                  int C) {
+                                                  int C, int bce_clip) {
   ck::pdl_enter();
   extern __shared__ float sw[];
   for (int i = threadIdx.x; i < C; i += blockDim.x) sw[i] = w[i];
@@ -788,11 +800,12 @@ __global__ void __launch_bounds__(TPB) head_fwd_k(const __nv_bfloat16* __restric
     }
     if (mask) {
       const float pc = fminf(fmaxf(pr, 1e-7f), 1.f - 1e-7f);
-      const float lp = __logf(pc), lq = __logf(1.f - pc);
+      const float lp = bce_clip ? -__logf(pc) : bce_logit(logit, 1.f);
+      const float lq = bce_clip ? -__logf(1.f - pc) : bce_logit(logit, 0.f);
 #pragma unroll
       for (int d = 0; d < 4; ++d) {
         const float yv = mask[base + (d >> 1) * Wf + (d & 1)] ? 1.f : 0.f;
-        a[0] -= yv * lp + (1.f - yv) * lq;
+        a[0] += yv * lp + (1.f - yv) * lq;
         a[1] += ((pr > 0.5f) == (yv > 0.5f)) ? 1.f : 0.f;
         a[2] += pr * yv;
         a[3] += pr;
@@ -824,7 +837,7 @@ __global__ void __launch_bounds__(TPB) head_bwd_k(const __nv_bfloat16* __restric
                                                   const float* __restrict__ sums, __nv_bfloat16* __restrict__ ds,
                                                   float* __restrict__ dw, float* __restrict__ db, int B, int Hl, int Wl, int C,
                                                   int use_dice, float dice_smooth, float loss_scale,
-                                                  float* __restrict__ acc_out) {
+                                                  float* __restrict__ acc_out, int bce_clip) {
   ck::pdl_enter();
   extern __shared__ float sh[];  // w[C] | reduction scratch [TPB*8]
   float* sw = sh;
@@ -861,13 +874,14 @@ __global__ void __launch_bounds__(TPB) head_bwd_k(const __nv_bfloat16* __restric
     const int hl = (int)((p / Wl) % Hl);
     const long b = p / ((long)Wl * Hl);
     const long base = (b * Hf + 2 * hl) * Wf + 2 * wl;
-    const bool inside = (pr >= 1e-7f) && (pr <= 1.f - 1e-7f);  // clip_by_value passes no gradient outside
+    const bool inside = !bce_clip || ((pr >= 1e-7f) && (pr <= 1.f - 1e-7f));  // clip_by_value passes no gradient outside
     float dl = 0.f;
     const bool metrics = acc_out != nullptr && cv == 0;
     float lp = 0.f, lq = 0.f;
     if (metrics) {
       const float pc = fminf(fmaxf(pr, 1e-7f), 1.f - 1e-7f);
-      lp = __logf(pc); lq = __logf(1.f - pc);
+      lp = bce_clip ? -__logf(pc) : bce_logit(logit, 1.f);
+      lq = bce_clip ? -__logf(1.f - pc) : bce_logit(logit, 0.f);
     }
 #pragma unroll
     for (int d = 0; d < 4; ++d) {
@@ -875,7 +889,7 @@ __global__ void __launch_bounds__(TPB) head_bwd_k(const __nv_bfloat16* __restric
       if (inside) dl += (pr - yv) * invn;
       if (use_dice) dl += -(2.f * yv * dden - dnum) / (dden * dden) * pr * (1.f - pr);
       if (metrics) {
-        am[0] -= yv * lp + (1.f - yv) * lq;
+        am[0] += yv * lp + (1.f - yv) * lq;
         am[1] += ((pr > 0.5f) == (yv > 0.5f)) ? 1.f : 0.f;
         am[2] += pr * yv;
         am[3] += pr;
@@ -1450,21 +1464,21 @@ int crackfl_colsum(const void* g, float* out, long P, int C, cudaStream_t st) {
 }
 
 int crackfl_head_fwd(const void* s, const float* w, const float* bias, const void* mask_u8, float* acc, float* prob, int B,
-                     int Hl, int Wl, int C, cudaStream_t st) {
+                     int Hl, int Wl, int C, int bce_clip, cudaStream_t st) {
   const long P = (long)B * Hl * Wl;
   ck::launch(head_fwd_k, grid_for(P * (C / 8), 148 * 4), TPB, C * sizeof(float), st, (const __nv_bfloat16*)s, w, bias,
-                                                                   (const uint8_t*)mask_u8, acc, prob, B, Hl, Wl, C);
+                                                                   (const uint8_t*)mask_u8, acc, prob, B, Hl, Wl, C, bce_clip);
   CK_LAUNCH_CHECK();
   return 0;
 }
 
 int crackfl_head_bwd(const void* s, const float* w, const float* bias, const void* mask_u8, const float* sums, void* ds,
                      float* dw, float* db, int B, int Hl, int Wl, int C, int use_dice, float dice_smooth, float loss_scale,
-                     cudaStream_t st) {
+                     int bce_clip, cudaStream_t st) {
   const long P = (long)B * Hl * Wl;
   ck::launch(head_bwd_k, grid_for(P * (C / 8), 148 * 4), TPB, (C + TPB * 8) * sizeof(float), st, 
       (const __nv_bfloat16*)s, w, bias, (const uint8_t*)mask_u8, sums, (__nv_bfloat16*)ds, dw, db, B, Hl, Wl, C, use_dice,
-      dice_smooth, loss_scale, (float*)nullptr);
+      dice_smooth, loss_scale, (float*)nullptr, bce_clip);
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -1472,11 +1486,12 @@ int crackfl_head_bwd(const void* s, const float* w, const float* bias, const voi
 // plain-BCE training: forward metrics (loss / accuracy / dice sums into acc_out[6]) and the backward in ONE pass over s
 // (the BCE gradient needs nothing global but 1/N); with Dice the two-kernel sequence head_fwd -> head_bwd is required
 int crackfl_head_fwd_bwd(const void* s, const float* w, const float* bias, const void* mask_u8, float* acc_out, void* ds,
-                         float* dw, float* db, int B, int Hl, int Wl, int C, float loss_scale, cudaStream_t st) {
+                         float* dw, float* db, int B, int Hl, int Wl, int C, float loss_scale, int bce_clip,
+                         cudaStream_t st) {
   const long P = (long)B * Hl * Wl;
   ck::launch(head_bwd_k, grid_for(P * (C / 8), 148 * 4), TPB, (C + TPB * 8) * sizeof(float), st,
       (const __nv_bfloat16*)s, w, bias, (const uint8_t*)mask_u8, (const float*)nullptr, (__nv_bfloat16*)ds, dw, db, B, Hl, Wl, C,
-      0, 1.0f, loss_scale, acc_out);
+      0, 1.0f, loss_scale, acc_out, bce_clip);
   CK_LAUNCH_CHECK();
   return 0;
 }

@@ -125,15 +125,19 @@ int crackfl_relu_bwd_add(const void* g, const void* x, const void* add_or_null, 
 int crackfl_colsum(const void* g, float* out, long P, int C, cudaStream_t stream);
 
 /* ---- head: Conv2D(1,1x1,sigmoid) + binary_crossentropy (+Dice ext.) + accuracy (ref: :145,157) ---- */
-/* acc = [bce_sum, correct, intersection, prob_sum, mask_sum, pixel_count] (accumulated; caller zeroes) */
+/* acc = [bce_sum, correct, intersection, prob_sum, mask_sum, pixel_count] (accumulated; caller zeroes)
+   bce_clip = 0: cross-entropy from the logit, the form Keras 2 `fit` uses for a sigmoid output layer (the sigmoid's input is
+   recovered, tf.nn.sigmoid_cross_entropy_with_logits): gradient sigmoid(z)-y for every z.
+   bce_clip = 1: probabilities clipped to [1e-7, 1-1e-7] with no gradient outside the clip (backend fall-back / Keras 3). */
 int crackfl_head_fwd(const void* s, const float* w, const float* bias, const void* mask_u8_or_null, float* acc,
-                     float* prob_or_null, int B, int Hl, int Wl, int C, cudaStream_t stream);
+                     float* prob_or_null, int B, int Hl, int Wl, int C, int bce_clip, cudaStream_t stream);
 int crackfl_head_bwd(const void* s, const float* w, const float* bias, const void* mask_u8, const float* sums, void* ds,
                      float* dw, float* db, int B, int Hl, int Wl, int C, int use_dice, float dice_smooth, float loss_scale,
-                     cudaStream_t stream);
+                     int bce_clip, cudaStream_t stream);
 /* plain-BCE training step: forward metrics (acc_out[6], pre-zeroed) + backward in one pass over s */
 int crackfl_head_fwd_bwd(const void* s, const float* w, const float* bias, const void* mask_u8, float* acc_out, void* ds,
-                         float* dw, float* db, int B, int Hl, int Wl, int C, float loss_scale, cudaStream_t stream);
+                         float* dw, float* db, int B, int Hl, int Wl, int C, float loss_scale, int bce_clip,
+                         cudaStream_t stream);
 
 /* ---- GEMM-shaped convolutions ---------------------------------------------------------------- */
 /* CUDA-core implicit GEMM (cross-check + odd shapes).  Wk[N][taps*Cin] bf16, taps in {1,9}. */

@@ -471,7 +471,10 @@ def test_local_trainer_b200_backend_host_batches():
         assert np.isfinite(m["loss"]) and m["num_samples"] == 20
         outs.append((np.concatenate([x.ravel() for x in w]), m))
     (wh, mh), (wd, md), (wd2, md2) = outs
-    assert abs(mh["loss"] - md["loss"]) < 1e-3
+    # (the losses of two identical device-fed runs differ by several per cent after 15 Adam steps; before the loss was
+    # computed from the logit the step died early and the runs agreed trivially)
+    assert abs(mh["loss"] - md["loss"]) <= 3 * abs(md["loss"] - md2["loss"]) + 0.1 * md["loss"]
+    assert mh["loss"] < 1.0 and md["loss"] < 1.0  # started at ~1.4: training moves
     # runs are not bit-identical (order-dependent fp32 atomics + Adam's sign sensitivity near zero gradients): the host-fed
     # run must sit as close to a device-fed run as two device-fed runs sit to each other
     noise = float(np.linalg.norm(wd - wd2) / np.linalg.norm(wd))

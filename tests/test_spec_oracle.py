@@ -80,6 +80,22 @@ def test_bce_clip():
     assert abs(float(R.bce_loss(p, y)) - (-np.log(1e-7))) < 0.2
 
 
+def test_bce_from_logits_is_the_keras2_fit_form():
+    """sigmoid_cross_entropy_with_logits: same value as the probability form where that is finite, and a gradient
+    sigmoid(z)-y that does not vanish where the clipped form has none."""
+    z = torch.tensor([-30.0, -3.0, 0.5, 4.0, 30.0], requires_grad=True)
+    y = torch.tensor([1.0, 0.0, 1.0, 0.0, 0.0])
+    l = R.bce_logits_loss(z, y)
+    l.backward()
+    assert torch.allclose(z.grad, (torch.sigmoid(z.detach()) - y) / 5, atol=1e-7)
+    mid = slice(1, 4)
+    ref = F.binary_cross_entropy(torch.sigmoid(z.detach()[mid]), y[mid])
+    assert abs(float(R.bce_logits_loss(z.detach()[mid], y[mid])) - float(ref)) < 1e-6
+    zc = z.detach().clone().requires_grad_(True)
+    R.bce_loss(torch.sigmoid(zc), y).backward()
+    assert float(zc.grad[0]) == 0.0 and float(z.grad[0]) < -0.19  # the clipped form is dead at z = -30, y = 1
+
+
 def test_ref_trainer_loss_decreases_and_bn_updates():
     from crackfl.data.generator import synth_crack_batch
     s = REFERENCE_SPEC
