@@ -40,6 +40,8 @@ def parse():
     ap.add_argument("--conv-impl", default=None)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--width-mult", type=int, default=1)
+    ap.add_argument("--agg-sweep", default="8.233,64,256", help="model sizes (MB) of the aggregation-kernel summary "
+                    "emitted with N > 1 GPUs ('' = skip)")
     return ap.parse_args()
 
 
@@ -149,11 +151,14 @@ def main():
         label = "PyTorch eager/cuDNN stand-in (bf16 autocast, channels_last) - NOT the reference's Keras build"
     else:
         from crackfl.models.unet import UNetEngine
-        eng = UNetEngine(spec, B, S, S, device=local, conv_impl=a.conv_impl, cuda_graph=True)
+        # one client per GPU: the engine trains IN the federation's exported arena, so the round boundary is the fused
+        # kernel alone (peers pull the trained weights from it, the new global model is stored straight into it)
         fed = OnBoxFederation(spec, clients_per_gpu=1, strategy=a.strategy, payload=a.payload)
+        eng = UNetEngine(spec, B, S, S, device=local, conv_impl=a.conv_impl, cuda_graph=True, arena=fed.global_arena)
         init = torch.from_numpy(__import__("crackfl.io.weights", fromlist=["flatten"]).flatten(spec.init_weights(0), spec))
         fed.set_global(init)
-        eng.load_flat(fed.global_arena); eng.reset_optimizer()
+        eng.reset_optimizer()
+        fed.configure([B * a.steps], weighted=(a.strategy != "fedavg"))  # control plane, once, outside the timed region
 
         def step_dev(i):
             eng.x_u8.copy_(dx[i % NB], non_blocking=True)
@@ -183,12 +188,11 @@ def main():
             return pending[1]
 
         def round_end():
-            # FedAvg round boundary: publish the local fit, fused aggregate+broadcast kernel, reload, fresh Adam
-            fed.publish(0, eng.arena)
-            fed.aggregate([B * a.steps], weighted=(a.strategy != "fedavg"))
-            eng.load_flat(fed.global_arena)
+            # FedAvg round boundary: ONE launch of the fused aggregate+broadcast kernel over the live arenas (no host
+            # synchronisation, no collective call, no copy), then fresh Adam moments (4 fills) for the next round
+            fed.aggregate()
             eng.reset_optimizer()
-        launches = eng.launches_per_step * a.steps + 2
+        launches = eng.launches_per_step * a.steps + 1
         label = "crackfl sm_100a engine"
 
     # ---- device-timed, inputs resident on device
@@ -211,6 +215,7 @@ def main():
     agg_ms = torch.tensor([fed.last_agg_ms if a.impl == "ours" else 0.0], device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(agg_ms, op=dist.ReduceOp.MAX)
     ms = float(ms.item())
     clocks = sampler.stop() if rank == 0 else None
 
@@ -240,6 +245,16 @@ def main():
                "h2d_bytes_per_step": B * S * S * 3 + B * S * S, "d2h_bytes_per_step": 24 if a.impl == "ours" else 4,
                "wall_ms_rank0": wall_ms, "last_loss": last}
 
+    # ---- fused aggregation kernel alone, ranks aligned on the device first (BASELINE config 5, 3 points)
+    agg_sweep = None
+    if a.impl == "ours" and world > 1 and a.agg_sweep:
+        from crackfl.parallel.sweep import sweep_points
+        del eng
+        torch.cuda.empty_cache()
+        pts = sweep_points([float(x) for x in a.agg_sweep.split(",")], payload=a.payload, strategy=a.strategy)
+        agg_sweep = [{k: p[k] for k in ("mb", "ms_best", "ms_median", "roofline_ms_900", "roofline_frac_900",
+                                        "roofline_frac_770")} for p in pts]
+
     if rank == 0:
         out = {
             "metric": "FedAvg client-training U-Net seg images/sec (local fit steps + fused aggregation at the round "
@@ -256,6 +271,10 @@ def main():
                        "l2_note": "per-step activation working set (>1 GB at 256^2, B=16) exceeds the 126 MB L2; "
                                   f"inputs rotate over {NB} distinct batches"},
             "aggregate_ms": float(agg_ms.item()),
+            "aggregate_note": "device time of the round-boundary launch inside the timed region, max over ranks; it "
+                              "includes whatever skew the ranks reached it with.  agg_sweep = the same kernel with the "
+                              "ranks aligned on the device first, best of 8, fraction of (bytes per direction / 900 GB/s)",
+            "agg_sweep": agg_sweep,
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
         }
         print(json.dumps(out))

@@ -3,11 +3,10 @@
 
 Launch: python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 bench/agg_sweep.py [--sizes-mb 1,8,64,...]
 Every rank publishes K client updates with known values; after the fused kernel every rank's global arena must equal
-the NumPy weighted mean (fl_server.py:92-102 semantics), bit-identical on all ranks.  Timing: CUDA events around the
-launch(es), ranks released together by a barrier, max over ranks.  Roofline per GPU and direction: the G-1 shards of
-its partial that the other owners pull PLUS its updated shard pushed to G-1 peers = (partial_bytes + 4n)(G-1)/G,
-over the measured 770 GB/s per direction (B200_PROFILING.md; bench/p2p_probe.py measures 750-780 GB/s read and
-~710 GB/s write with this very kernel); for G=1 the bound is HBM traffic over the measured copy bandwidth.
+the NumPy weighted mean (fl_server.py:92-102 semantics), and the WHOLE arena is compared bit for bit across ranks.
+Timing and roofline: crackfl/parallel/sweep.py (ranks aligned on the device by a barrier-only launch, CUDA events, max
+over ranks; bytes per direction (partial_bytes + 4n)(G-1)/G over 900 GB/s, and over the measured 770 GB/s for context;
+for G=1 the bound is HBM traffic over the measured copy bandwidth).
 Works on CPU/Gloo too (host fallback path) so the logic is testable without GPUs.
 """
 import argparse
@@ -21,6 +20,19 @@ import torch
 import torch.distributed as dist
 
 from crackfl.parallel.runtime import OnBoxFederation, init_distributed
+from crackfl.parallel.sweep import roofline_ms, time_aggregate
+
+
+def same_on_all_ranks(t: torch.Tensor, chunk: int = 16 << 20) -> bool:
+    """Bit-for-bit comparison of the whole tensor against rank 0's, in chunks (int32 view: NaN-safe, -0 != +0)."""
+    ti = t.view(torch.int32)
+    ok = True
+    for o in range(0, ti.numel(), chunk):
+        mine = ti[o:o + chunk]
+        ref = mine.clone()
+        dist.broadcast(ref, 0)
+        ok = ok and bool(torch.equal(mine, ref))
+    return ok
 
 
 def main():
@@ -54,7 +66,7 @@ def main():
                     return glob + 0.01 * torch.cos(idx * (0.11 + 0.013 * cid))
                 for k in range(K):
                     fed.publish(k, update_of(rank * K + k))
-                ms = fed.aggregate(ns_all[rank], weighted=True)
+                fed.aggregate(ns_all[rank], weighted=True)
                 # oracle (same arithmetic as fl_server.py:92-102 with sample-count weights), evaluated on `dev`
                 flat_ns = np.array([x for row in ns_all for x in row], np.float64)
                 coef = (flat_ns / flat_ns.sum()).astype(np.float32)
@@ -73,40 +85,23 @@ def main():
                 ok = err < tol * (10 if strategy == "fedadam" else 1) + 1e-6
                 del avg, want
                 # all ranks bit-identical
-                if world > 1:
-                    chk = got[:4096].clone()
-                    ref = chk.clone()
-                    dist.broadcast(ref, 0)
-                    same = bool(torch.equal(chk, ref))
-                else:
-                    same = True
+                same = same_on_all_ranks(got) if world > 1 else True
                 flag = torch.tensor([1.0 if (ok and same) else 0.0], device=fed.global_arena.device)
                 if world > 1:
                     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
                 ok_all = ok_all and bool(flag.item() == 1.0)
                 # timing
-                times = []
-                for _ in range(a.iters):
-                    if cuda:
-                        torch.cuda.synchronize()
-                    if world > 1:
-                        dist.barrier()   # start every rank together: the max-over-ranks time is then the kernel, not rank skew
-                    times.append(fed.aggregate(ns_all[rank], weighted=True))
-                times.sort()
-                best, med = times[0], times[len(times) // 2]
-                pbytes = n * (2 if payload == "bf16_delta" else 4)
-                if world > 1:
-                    # bytes that must cross NVLink per GPU per direction for pull-reduce + push-broadcast:
-                    # outbound = my partial's shards served to the G-1 other owners + my updated shard pushed to G-1 peers
-                    # (inbound is the mirror image); NVLink is full duplex, so the bound is one direction's bytes.
-                    link_bytes = (pbytes + n * 4) * (world - 1) / world
-                    roof_ms = link_bytes / 770e9 * 1e3
+                if cuda:
+                    tm = time_aggregate(fed, a.iters)
                 else:
-                    hbm = K * n * 4 + pbytes + pbytes + n * 4 * 2
-                    roof_ms = hbm / 6454.6e9 * 1e3
+                    ts = sorted(fed.aggregate(ns_all[rank], weighted=True) for _ in range(a.iters))
+                    tm = {"ms_best": ts[0], "ms_median": ts[len(ts) // 2]}
+                roof = roofline_ms(n, world, payload, K)
                 rec = {"payload": payload, "strategy": strategy, "mb": mb, "numel": n, "world": world, "clients_per_gpu": K,
-                       "ms_best": best, "ms_median": med, "roofline_ms": roof_ms, "roofline_frac": roof_ms / best if best > 0 else None,
-                       "max_abs_err": err, "ok": bool(flag.item() == 1.0)}
+                       "nvls": bool(getattr(fed, "nvls", False)), **tm, **roof,
+                       "roofline_frac_900": roof["roofline_ms_900"] / tm["ms_best"] if tm["ms_best"] > 0 else None,
+                       "roofline_frac_770": roof["roofline_ms_770"] / tm["ms_best"] if tm["ms_best"] > 0 else None,
+                       "max_abs_err": err, "bit_identical_all_ranks_whole_arena": same, "ok": bool(flag.item() == 1.0)}
                 results.append(rec)
                 if rank == 0:
                     print(json.dumps(rec), flush=True)

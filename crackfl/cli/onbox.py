@@ -16,10 +16,12 @@ def main(argv=None) -> int:
     ap.add_argument("--clients-per-gpu", type=int, default=1)
     ap.add_argument("--strategy", default="fedavg", choices=["fedavg", "fedavg_weighted", "fedadam"])
     ap.add_argument("--payload", default="fp32", choices=["fp32", "bf16_delta"])
+    ap.add_argument("--eval-global", action="store_true", help="score every new global model on client 0's validation set")
     ap.add_argument("--save", default=None, help="write the final global model (Keras .h5) on rank 0")
     args, cfg = parse_with_config(ap, argv)
     init_distributed()
-    out = run_federated_onbox(cfg, args.rounds, args.clients_per_gpu, args.strategy, args.payload)
+    out = run_federated_onbox(cfg, args.rounds, args.clients_per_gpu, args.strategy, args.payload,
+                              eval_global=args.eval_global)
     if out["weights"] is not None:
         if args.save:
             from ..io.keras_h5 import save_keras_h5

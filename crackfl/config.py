@@ -94,6 +94,7 @@ class DataConfig:
     synthetic_train: int = 6213
     synthetic_val: int = 1024
     workers: int = 4
+    prefetch_batches: int = 4  # extension: batches decoded ahead of the training loop by a worker thread (0 = inline, as the reference)
 
 
 @dataclass

@@ -20,6 +20,8 @@ def synth_crack_batch_device(batch: int, h: int, w: int, seed: int, device=None)
 class DeviceSyntheticDataset:
     """Sequence-like dataset whose batches live on the device (for benchmarks and the on-box runtime)."""
 
+    device_resident = True  # nothing to decode or copy: the trainer indexes it inline, no prefetch thread
+
     def __init__(self, num_samples: int, batch_size: int, img_size, seed: int = 0, device=None):
         self.n, self.batch_size, self.img_size, self.seed, self.device = num_samples, batch_size, tuple(img_size), seed, device
         self._cache = {}

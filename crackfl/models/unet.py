@@ -99,7 +99,16 @@ class UNetEngine:
 
     def _alloc_params(self):
         n = self.spec.arena_numel
-        self.arena = self._new("arena", (n,), torch.float32)
+        if self._ext_arena is not None:
+            # parameters live in a buffer the caller owns (the on-box runtime's IPC-exported arena: peers read the
+            # trained weights out of it and write the next global model into it, runtime.py)
+            a = self._ext_arena
+            if a.dtype != torch.float32 or a.numel() != n or not a.is_contiguous() or a.device != self.dev:
+                raise ValueError("external arena must be a contiguous fp32 tensor of spec.arena_numel elements on the engine's device")
+            self.arena = a
+            self._bufs["arena"] = a
+        else:
+            self.arena = self._new("arena", (n,), torch.float32)
         self.grads = self._new("grads", (n,), torch.float32)
         self.m = self._new("adam_m", (n,), torch.float32)
         self.v = self._new("adam_v", (n,), torch.float32)
@@ -117,6 +126,9 @@ class UNetEngine:
         self.acc_off = zoff  # 6 floats of loss/metric accumulators for the current step
         self.bn_params = self._new("bn_params", (poff,), torch.float32)
         self.metrics_total = self._new("metrics_total", (8,), torch.float32)
+        # loss / metric sums of the most recent train step (the Adam launch saves them here before it clears the region)
+        self.last_acc = self._new("last_acc", (8,), torch.float32)
+        self._region_dirty = False  # set by anything but a complete train step; the next train step then clears it first
 
     def P(self, tensor_idx: int) -> int:
         """Device address of weight tensor ``tensor_idx`` inside the arena."""
@@ -623,7 +635,9 @@ class UNetEngine:
         prog.append((lib.crackfl_adam_step_tail, (self.arena.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(),
                                                   self.v.data_ptr(), self.step.data_ptr(), self.spec.arena_numel, self.lr,
                                                   self.b1, self.b2, self.eps, self._acc_ptr() + 4 * 8,
-                                                  self.metrics_total.data_ptr(), self._acc_ptr(), 6)))
+                                                  self.metrics_total.data_ptr(), self._acc_ptr(), 6,
+                                                  self.last_acc.data_ptr(), self.zero_region.data_ptr(),
+                                                  self.zero_region.numel())))
         return self._wgrad_resolve(prog)
 
     def enc_out_name(self) -> str:
@@ -686,7 +700,11 @@ class UNetEngine:
         join("aux")
 
     def _step_body(self, prog, accumulate: bool):
-        self.zero_region.zero_()
+        """The per-step scratch region (BN sums, loss accumulators, the Adam tail counter) must be zero when a step
+        starts.  A train step leaves it that way itself (last block of the Adam launch), so the hot path has no fill
+        kernel; eval / predict steps clear it before they run (``_exec`` clears it again before the next train step)."""
+        if prog is not self.train_prog:
+            self.zero_region.zero_()
         self._run(prog)
         if accumulate and prog is not self.train_prog:  # the train schedule accumulates inside its Adam launch
             st = torch.cuda.current_stream(self.dev).cuda_stream
@@ -694,6 +712,12 @@ class UNetEngine:
 
     def _exec(self, key: str, prog, accumulate: bool):
         with torch.cuda.device(self.dev):
+            if key == "train":
+                if self._region_dirty:
+                    self.zero_region.zero_()
+                    self._region_dirty = False
+            else:
+                self._region_dirty = True
             if not self.cuda_graph:
                 self._step_body(prog, accumulate)
                 return
@@ -732,6 +756,7 @@ class UNetEngine:
         names = [e[0].__name__ for e in self.train_prog if e[0] is not None]
         acc = [0.0] * len(names)
         st = torch.cuda.current_stream(self.dev)
+        self._region_dirty = True
         for rep in range(repeats + 1):
             self.zero_region.zero_()
             evs = [torch.cuda.Event(enable_timing=True) for _ in range(len(names) + 1)]
@@ -838,7 +863,7 @@ class UNetEngine:
 
     def step_loss(self) -> torch.Tensor:
         """Device scalar: mean BCE of the most recent step (for the end-to-end D2H read)."""
-        a = self.zero_region[self.acc_off:self.acc_off + 6]
+        a = self.last_acc[:6]
         return a[0] / a[5].clamp_min(1.0)
 
 
@@ -847,7 +872,7 @@ class UNetEngine:
         pinned memory + a stream synchronise (no device-side arithmetic kernels), the division is done on the host."""
         if getattr(self, "_acc_host", None) is None:
             self._acc_host = torch.empty(6, dtype=torch.float32, pin_memory=True)
-        self._acc_host.copy_(self.zero_region[self.acc_off:self.acc_off + 6], non_blocking=True)
+        self._acc_host.copy_(self.last_acc[:6], non_blocking=True)
         torch.cuda.current_stream(self.dev).synchronize()
         a = self._acc_host
         return float(a[0]) / max(float(a[5]), 1.0)
@@ -863,7 +888,7 @@ class UNetEngine:
             self._lr_i = 0
         i = self._lr_i
         self._lr_i ^= 1
-        self._lr_host[i].copy_(self.zero_region[self.acc_off:self.acc_off + 6], non_blocking=True)
+        self._lr_host[i].copy_(self.last_acc[:6], non_blocking=True)
         self._lr_ev[i].record(torch.cuda.current_stream(self.dev))
         return i
 
@@ -878,18 +903,19 @@ class B200Backend:
 
     name = "b200"
 
-    def __init__(self, cfg, spec: UNetSpec, device: Optional[int] = None):
+    def __init__(self, cfg, spec: UNetSpec, device: Optional[int] = None, arena: Optional[torch.Tensor] = None):
         t = cfg.train
         self.cfg, self.spec = cfg, spec
         self.engine = UNetEngine(spec, t.batch_size, t.image_size[0], t.image_size[1], device=device, lr=t.lr,
                                  beta1=t.beta1, beta2=t.beta2, eps=t.adam_eps, loss=t.loss, cuda_graph=t.cuda_graph,
-                                 bce_clip=t.bce_clip)
+                                 bce_clip=t.bce_clip, arena=arena)
         B, H, W = t.batch_size, t.image_size[0], t.image_size[1]
         self._hx = torch.empty((B, H, W, 3), dtype=torch.uint8).pin_memory()
         self._hy = torch.empty((B, H, W), dtype=torch.uint8).pin_memory()
 
     def begin_round(self, weights):
-        self.engine.load_weights(weights)
+        if weights is not None:  # None: the round's model is already in the arena (on-box broadcast)
+            self.engine.load_weights(weights)
         self.engine.reset_optimizer()
         self.engine.reset_metrics()
 
@@ -933,6 +959,9 @@ class B200Backend:
 
     def read_metrics(self):
         return self.engine.read_metrics()
+
+    def finish(self):
+        torch.cuda.current_stream(self.engine.dev).synchronize()
 
     def predict_batch(self, x_u8) -> np.ndarray:
         hx, _ = self._stage(x_u8, None)

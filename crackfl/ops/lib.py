@@ -41,7 +41,8 @@ class FedAggParams(C.Structure):
                 ("delta", i32), ("server_opt", i32), ("eta", f32), ("beta1", f32), ("beta2", f32), ("tau", f32),
                 ("master", vp), ("m", vp), ("v", vp), ("trainable", vp), ("mc_out", vp),
                 ("begin", i64), ("end", i64), ("pads", vp * MAX_RANKS), ("rank", i32), ("world", i32),
-                ("epoch", C.c_uint32), ("error_flag", vp), ("local_sync", vp), ("mc_in", vp), ("unroll", i32), ("load_mode", i32)]
+                ("epoch", C.c_uint32), ("error_flag", vp), ("local_sync", vp), ("mc_in", vp), ("unroll", i32), ("load_mode", i32),
+                ("timeout_cycles", C.c_longlong)]
 
 
 _SIGS = {
@@ -91,7 +92,7 @@ _SIGS = {
     "crackfl_weight_prep": [vp, vp, vp, i32, vp],
     "crackfl_adam_step": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, vp],
     "crackfl_f32_to_bf16": [vp, vp, i64, vp],
-    "crackfl_adam_step_tail": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, vp, vp, vp, i32, vp],
+    "crackfl_adam_step_tail": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, vp, vp, vp, i32, vp, vp, i32, vp],
     "crackfl_accum_small": [vp, vp, i32, vp],
     "crackfl_publish_delta": [vp, vp, vp, i64, vp],
     "crackfl_synth_cracks": [vp, vp, i32, i32, i32, C.c_uint, vp],

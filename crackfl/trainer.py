@@ -43,8 +43,10 @@ class TorchRefBackend:
         self.cfg, self.spec, self.tr = cfg, spec, None
         self._acc = [0.0, 0.0, 0]
 
-    def begin_round(self, weights: Sequence[np.ndarray]):
+    def begin_round(self, weights: Optional[Sequence[np.ndarray]]):
         from .models.unet_ref import RefTrainer
+        if weights is None:  # "the model is already where it is trained": carry on from the current weights
+            weights = self.tr.get_weights()
         self.tr = RefTrainer(weights, self.spec, lr=self.cfg.train.lr, loss=self.cfg.train.loss,
                              bce_clip=self.cfg.train.bce_clip)
         self.reset_metrics()
@@ -79,7 +81,7 @@ class TorchRefBackend:
         return self.tr.get_weights()
 
 
-def make_backend(cfg: Config, spec: UNetSpec, device: Optional[int] = None):
+def make_backend(cfg: Config, spec: UNetSpec, device: Optional[int] = None, arena=None):
     kind = cfg.train.backend
     if kind == "auto":
         import torch
@@ -88,8 +90,53 @@ def make_backend(cfg: Config, spec: UNetSpec, device: Optional[int] = None):
         return TorchRefBackend(cfg, spec)
     if kind == "b200":
         from .models.unet import B200Backend  # raises loudly if the CUDA library is missing
-        return B200Backend(cfg, spec, device=device)
+        return B200Backend(cfg, spec, device=device, arena=arena)
     raise ValueError(f"unknown backend {kind!r}")
+
+
+def _prefetched(ds, order, depth: int):
+    """Batches of ``ds`` in ``order``, fetched ``depth`` batches ahead by a worker thread.
+
+    The reference decodes the 32 JPEGs of a step inside ``fit``'s loop (``client_fit_model.py:30-43`` is called by Keras
+    with no ``workers``), so decode + resize sit on the critical path of every step.  Here ``ds[i]`` runs in a thread
+    (cv2 releases the GIL) and the training loop only ever waits on a queue.  Device-resident datasets and
+    ``depth <= 0`` fall through to plain indexing."""
+    if depth <= 0 or len(order) < 2 or getattr(ds, "device_resident", False):
+        for bi in order:
+            yield ds[bi]
+        return
+    import queue
+    import threading
+    q: "queue.Queue" = queue.Queue(maxsize=depth)
+    stop = threading.Event()
+
+    def work():
+        try:
+            for bi in order:
+                if stop.is_set():
+                    return
+                q.put(("ok", ds[bi]))
+            q.put(("end", None))
+        except BaseException as e:  # surfaced in the consumer
+            q.put(("err", e))
+
+    th = threading.Thread(target=work, daemon=True, name="crackfl-prefetch")
+    th.start()
+    try:
+        while True:
+            kind, item = q.get()
+            if kind == "end":
+                return
+            if kind == "err":
+                raise item
+            yield item
+    finally:
+        stop.set()
+        while th.is_alive():  # unblock a producer that is waiting on a full queue
+            try:
+                q.get_nowait()
+            except queue.Empty:
+                th.join(0.01)
 
 
 class LocalTrainer:
@@ -117,7 +164,11 @@ class LocalTrainer:
         w, _ = self.fit(wio.loads_auto(blob, allow_pickle=self.cfg.transport.allow_pickle), cr or 0)
         return w
 
-    def fit(self, weights: Sequence[np.ndarray], round_idx: int) -> Tuple[List[np.ndarray], Dict[str, float]]:
+    def fit(self, weights: Optional[Sequence[np.ndarray]], round_idx: int,
+            return_weights: bool = True) -> Tuple[Optional[List[np.ndarray]], Dict[str, float]]:
+        """``weights=None``: the round's global model is already resident in the back-end (the on-box runtime's
+        broadcast lands in the engine's arena), only the optimiser and the metrics are reset.  ``return_weights=False``
+        skips the device-to-host export for callers that read the arena in place."""
         t = self.cfg.train
         be = self.backend
         self.log(f"### Model Training - Round: {round_idx} ({be.name}) ###")
@@ -132,8 +183,7 @@ class LocalTrainer:
             if t.shuffle_batches:
                 self.rng.shuffle(order)  # Keras shuffles batch ORDER of a Sequence, not contents
             be.reset_metrics()
-            for bi in order:
-                x, y = self.train_ds[bi]
+            for x, y in _prefetched(self.train_ds, order, self.cfg.data.prefetch_batches):
                 be.train_batch(x, y)
             train_m = be.read_metrics()
             if t.validate and self.val_ds is not None and len(self.val_ds) > 0:
@@ -146,8 +196,10 @@ class LocalTrainer:
                 logger.epoch(epoch, train_m, val_m, be.get_weights() if t.histogram_freq else None)
             self.log(f"epoch {epoch + 1}/{t.local_epochs} - loss {train_m['loss']:.4f} - accuracy {train_m['accuracy']:.4f}"
                      + (f" - val_loss {val_m['loss']:.4f} - val_accuracy {val_m['accuracy']:.4f}" if val_m else ""))
+        if hasattr(be, "finish"):
+            be.finish()  # device back-end: the fit time below must cover the queued GPU work
         fit_s = time.perf_counter() - t0
-        out = be.get_weights()
+        out = be.get_weights() if return_weights else None
         if round_idx == t.predict_round and self.predict_ds is not None:
             from .postproc.measure import predict_and_measure
             self.last_measurements = predict_and_measure(be.predict_batch, self.predict_ds, self.cfg.measure)

@@ -67,7 +67,7 @@ def engine_vs_oracle(spec: UNetSpec = REFERENCE_SPEC, B=4, H=64, W=64, seed=0, c
     eng.load_weights(weights)
     eng.reset_optimizer(); eng.reset_metrics()
     eng.set_batch(x, y)
-    eng.zero_region.zero_()
+    eng.zero_region.zero_(); eng._region_dirty = True
     eng._run(eng.train_prog[:-1])  # everything but the optimiser
     torch.cuda.synchronize()
     acc = eng.zero_region[eng.acc_off:eng.acc_off + 6].cpu().numpy()
@@ -151,12 +151,12 @@ def directional_fd_check(spec: UNetSpec = REFERENCE_SPEC, B=8, H=64, W=64, seed=
 
     def loss_at(flat):
         eng.arena.copy_(flat)
-        eng.zero_region.zero_()
+        eng.zero_region.zero_(); eng._region_dirty = True
         eng._run(eng.fwd_prog)
         a = eng.zero_region[eng.acc_off:eng.acc_off + 6].cpu().numpy()
         return float(a[0]) / float(a[5])
 
-    eng.zero_region.zero_(); eng.grads.zero_()
+    eng.zero_region.zero_(); eng.grads.zero_(); eng._region_dirty = True
     eng._run(eng.train_prog[:-1])
     g = eng.grads.clone()
     _, _, _, ograds, _, _ = oracle_run(spec, weights, x, y, torch.device("cuda"))

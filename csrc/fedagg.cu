@@ -75,7 +75,14 @@ __device__ __forceinline__ uint2 multimem_ld_reduce_bf16x4(const void* mc) {
   return r;
 }
 
-constexpr long long SPIN_TIMEOUT_CYCLES = 4000000000LL;  // ~2 s at 1.9 GHz: a dead rank cannot hang the box
+// Spin limit when the caller passes timeout_cycles == 0: ~60 s at 1.9 GHz.  A dead rank still cannot hang the box,
+// and ranks that reach the round boundary seconds apart (uneven client data, K clients per GPU, a JPEG-bound
+// loader) no longer trip it; callers that rendezvous on the host first can pass something much shorter.
+constexpr long long DEFAULT_TIMEOUT_CYCLES = 120000000000LL;
+
+__device__ __forceinline__ long long spin_limit(const crackfl_fedagg_params& P) {
+  return P.timeout_cycles > 0 ? P.timeout_cycles : DEFAULT_TIMEOUT_CYCLES;
+}
 
 // Cross-GPU barrier over the signal pads.  pad layout per rank: [phase(2)][world] u32, monotonically
 // increasing epoch values (no reset race).  One thread per peer.
@@ -84,9 +91,9 @@ __device__ void pad_barrier(const crackfl_fedagg_params& P, int phase) {
   if (j < P.world) {
     st_release_sys(P.pads[j] + phase * CRACKFL_MAX_RANKS + P.rank, P.epoch);
     const uint32_t* mine = P.pads[P.rank] + phase * CRACKFL_MAX_RANKS + j;
-    const long long t0 = clock64();
+    const long long t0 = clock64(), lim = spin_limit(P);
     while (ld_acquire_sys(mine) < P.epoch) {
-      if (clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
+      if (clock64() - t0 > lim) {
         atomicExch(P.error_flag, 1 + phase);
         break;
       }
@@ -103,9 +110,9 @@ __global__ void __launch_bounds__(256) fedagg_k(const crackfl_fedagg_params P) {
       __syncthreads();
       if (threadIdx.x == 0) st_release_gpu(P.local_sync, P.epoch);
     } else if (threadIdx.x == 0) {
-      const long long t0 = clock64();
+      const long long t0 = clock64(), lim = 2 * spin_limit(P);
       while (ld_acquire_gpu(P.local_sync) < P.epoch) {
-        if (clock64() - t0 > 2 * SPIN_TIMEOUT_CYCLES) { atomicExch(P.error_flag, 3); break; }
+        if (clock64() - t0 > lim) { atomicExch(P.error_flag, 3); break; }
       }
     }
     __syncthreads();
@@ -213,9 +220,12 @@ __global__ void __launch_bounds__(256) fedagg_k(const crackfl_fedagg_params P) {
     __threadfence_system();
     __syncthreads();
     __shared__ int s_last;
+    // arrival counter of THIS launch: the last block resets it, so a round that timed out, or a different grid size
+    // on the next call, leaves nothing behind (every block gets here, also after a spin time-out)
     if (threadIdx.x == 0) {
       const unsigned prev = atomicAdd(P.local_sync + 1, 1u);
-      s_last = (prev + 1 == gridDim.x * P.epoch);
+      s_last = (prev + 1 == gridDim.x);
+      if (s_last) atomicExch(P.local_sync + 1, 0u);
     }
     __syncthreads();
     if (s_last) pad_barrier(P, 1);
@@ -236,7 +246,8 @@ int crackfl_fedagg(const crackfl_fedagg_params* p, int grid_blocks, cudaStream_t
   if (p->unroll == 8) blocks = (n4 + 256 * 8 - 1) / (256 * 8);
   if (blocks > grid_blocks) blocks = grid_blocks;
   if (blocks < 1) blocks = 1;
-  if (p->world > 1) blocks = grid_blocks;  // grid size is part of the exit-barrier arithmetic
+  // (every block of a multi-rank launch spins on block 0's release, so all of them must be resident at once:
+  //  grid_blocks is at most 8 blocks of 256 threads per SM; small shards simply use fewer blocks)
   const int g = (int)blocks;
   const bool u8 = p->unroll == 8;
   if (p->payload_bf16) {

@@ -17,10 +17,12 @@ __global__ void adam_tick_k(int* __restrict__ step) {
 __global__ void __launch_bounds__(256) adam_k(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
                                               float* __restrict__ v, int* __restrict__ step, long n4, float lr,
                                               float b1, float b2, float eps, unsigned* __restrict__ tail,
-                                              float* __restrict__ total, const float* __restrict__ acc, int nacc) {
+                                              float* __restrict__ total, const float* __restrict__ acc, int nacc,
+                                              float* __restrict__ last_acc, float* __restrict__ zbase, int zn) {
   ck::pdl_enter();
   __shared__ float s_lrt;
   __shared__ int s_t;
+  __shared__ int s_last;
   if (threadIdx.x == 0) {
     s_t = *step + (tail ? 1 : 0);
     const float t = (float)s_t;
@@ -49,7 +51,19 @@ __global__ void __launch_bounds__(256) adam_k(float* __restrict__ p, float* __re
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence();
-      if (atomicAdd(tail, 1u) == gridDim.x - 1) *step = s_t;  // every block has read the old count by now
+      s_last = (atomicAdd(tail, 1u) == gridDim.x - 1);
+      if (s_last) *step = s_t;  // every block has read the old count by now
+    }
+    if (zbase) {
+      // the last block to finish leaves the per-step scratch region (BN sums, loss accumulators, this counter) zeroed
+      // for the next step - no separate fill launch - after saving the step's loss/metric sums for the host to read
+      __syncthreads();
+      if (s_last) {
+        __threadfence();
+        if ((int)threadIdx.x < nacc) last_acc[threadIdx.x] = __ldcg(acc + threadIdx.x);
+        __syncthreads();
+        for (int i = threadIdx.x; i < zn; i += blockDim.x) zbase[i] = 0.f;
+      }
     }
   }
 }
@@ -144,20 +158,23 @@ int crackfl_adam_step(float* p, float* g, float* m, float* v, int* step, long n,
   long blocks = (n4 + 255) / 256;
   if (blocks > 148 * opt_cap()) blocks = 148 * opt_cap();
   ck::launch(adam_k, (int)blocks, 256, 0, st, p, g, m, v, step, n4, lr, b1, b2, eps, (unsigned*)nullptr, (float*)nullptr,
-             (const float*)nullptr, 0);
+             (const float*)nullptr, 0, (float*)nullptr, (float*)nullptr, 0);
   CK_LAUNCH_CHECK();
   return 0;
 }
 
 // Adam + step tick + metric accumulation in one launch; tail_counter must be zero on entry (it lives in the per-step
-// scratch region the caller zeroes anyway)
+// scratch region).  With zero_base != NULL the launch also ends the step: step_acc is saved to last_acc[nacc] and the
+// zero_n floats at zero_base (the whole per-step scratch region, counter included) are cleared for the next step.
 int crackfl_adam_step_tail(float* p, float* g, float* m, float* v, int* step, long n, float lr, float b1, float b2, float eps,
-                           unsigned* tail_counter, float* metrics_total, const float* step_acc, int nacc, cudaStream_t st) {
-  if (n % 4 || nacc > 32 || !tail_counter) return (int)cudaErrorInvalidValue;
+                           unsigned* tail_counter, float* metrics_total, const float* step_acc, int nacc, float* last_acc,
+                           float* zero_base, int zero_n, cudaStream_t st) {
+  if (n % 4 || nacc > 32 || !tail_counter || (zero_base && !last_acc)) return (int)cudaErrorInvalidValue;
   const long n4 = n / 4;
   long blocks = (n4 + 255) / 256;
   if (blocks > 148 * opt_cap()) blocks = 148 * opt_cap();
-  ck::launch(adam_k, (int)blocks, 256, 0, st, p, g, m, v, step, n4, lr, b1, b2, eps, tail_counter, metrics_total, step_acc, nacc);
+  ck::launch(adam_k, (int)blocks, 256, 0, st, p, g, m, v, step, n4, lr, b1, b2, eps, tail_counter, metrics_total, step_acc, nacc,
+             last_acc, zero_base, zero_n);
   CK_LAUNCH_CHECK();
   return 0;
 }

@@ -192,9 +192,12 @@ int crackfl_adam_step(float* p, float* g, float* m, float* v, int* step_dev, lon
                       cudaStream_t stream);
 int crackfl_f32_to_bf16(const float* in, void* out, long n, cudaStream_t stream);
 /* total[i] += step[i], i < n <= 32 (per-epoch metric accumulation of the per-step loss/accuracy sums) */
-/* Adam + step-count tick + metric accumulation (metrics_total[i] += step_acc[i]) in one launch; *tail_counter == 0 on entry */
+/* Adam + step-count tick + metric accumulation (metrics_total[i] += step_acc[i]) in one launch; *tail_counter == 0 on entry.
+   zero_base != NULL: the last block also saves step_acc to last_acc[nacc] and clears zero_n floats at zero_base (the
+   per-step scratch region), so the step needs no fill launch. */
 int crackfl_adam_step_tail(float* p, float* g, float* m, float* v, int* step_dev, long n, float lr, float b1, float b2, float eps,
-                           unsigned* tail_counter, float* metrics_total, const float* step_acc, int nacc, cudaStream_t stream);
+                           unsigned* tail_counter, float* metrics_total, const float* step_acc, int nacc, float* last_acc,
+                           float* zero_base, int zero_n, cudaStream_t stream);
 int crackfl_accum_small(float* total, const float* step, int n, cudaStream_t stream);
 /* staging of a client update as a bf16 delta against the global model (ref: fl_client.py:61-65 upload) */
 int crackfl_publish_delta(const float* local, const float* global, void* out_bf16, long n, cudaStream_t stream);
@@ -233,6 +236,7 @@ typedef struct {
   const void* mc_in;        /* NVLS multicast address of the (pre-scaled) partial arena: multimem.ld_reduce pull, or NULL */
   int unroll;               /* independent 16-byte loads per client per thread: 4 (default when 0) or 8 */
   int load_mode;            /* 0: ld.relaxed.sys (default), 1: ld.global.nc.L1::no_allocate (updates are immutable during the launch) */
+  long long timeout_cycles; /* spin limit of the cross-GPU barriers in SM clocks; 0 = default (~60 s) */
 } crackfl_fedagg_params;
 int crackfl_fedagg(const crackfl_fedagg_params* p, int grid_blocks, cudaStream_t stream);
 int crackfl_ipc_export(void* dev_ptr, void* handle_out64);

@@ -14,7 +14,7 @@ for tc in ("0", "1"):
     os.environ["CRACKFL_ENTRY_TC"] = tc
     eng = UNetEngine(S, B, H, H, cuda_graph=False)
     eng.load_weights(S.init_weights(0)); eng.reset_optimizer(); eng.set_batch(x, y)
-    eng.zero_region.zero_(); eng.grads.zero_()
+    eng.zero_region.zero_(); eng.grads.zero_(); eng._region_dirty = True
     eng._run(eng.train_prog[:-1])
     torch.cuda.synchronize()
     t = S.tensors[S.index("conv2d/kernel")]

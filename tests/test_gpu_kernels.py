@@ -430,11 +430,15 @@ def test_adam_step_tail_matches_adam_step():
         L.check(lib.crackfl_adam_step(pa.data_ptr(), ga.data_ptr(), ma.data_ptr(), va.data_ptr(), sa.data_ptr(), n, 1e-3, 0.9,
                                       0.999, 1e-7, _st()))
         L.check(lib.crackfl_accum_small(tot_a.data_ptr(), acc.data_ptr(), 6, _st()))
-        counter = torch.zeros(1, dtype=torch.int32, device="cuda")
+        # scratch region as the engine lays it out: [.. 40 floats of "BN sums" .. | acc 6 | pad 2 | counter]
+        region = torch.rand(49, device="cuda"); region[40:46] = acc; region[48] = 0
+        last = torch.zeros(6, device="cuda")
         L.check(lib.crackfl_adam_step_tail(pb.data_ptr(), gb.data_ptr(), mb.data_ptr(), vb.data_ptr(), sb.data_ptr(), n, 1e-3,
-                                           0.9, 0.999, 1e-7, counter.data_ptr(), tot_b.data_ptr(), acc.data_ptr(), 6, _st()))
+                                           0.9, 0.999, 1e-7, region.data_ptr() + 4 * 48, tot_b.data_ptr(),
+                                           region.data_ptr() + 4 * 40, 6, last.data_ptr(), region.data_ptr(), 49, _st()))
         torch.cuda.synchronize()
         assert float(gb.abs().max()) == 0.0
+        assert float(region.abs().max()) == 0.0 and torch.equal(last, acc)  # region cleared for the next step, sums saved
     assert torch.equal(pa, pb) and torch.equal(ma, mb) and torch.equal(va, vb)
     assert int(sa.item()) == int(sb.item()) == 3
     assert torch.allclose(tot_a, tot_b)

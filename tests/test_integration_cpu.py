@@ -159,3 +159,98 @@ dist.barrier(); dist.destroy_process_group()
     line = [l for l in r.stdout.splitlines() if l.startswith("RESULT")][0]
     res = json.loads(line.split(" ", 1)[1])
     assert res == {"rounds": 2, "n": 112, "finite": True}
+
+
+def test_gloo_mixed_round_onbox_plus_remote_update(tmp_path):
+    """SURVEY §5.8 item 6 on the host path: 2 Gloo ranks with one on-box client each + ONE off-box update staged on
+    rank 0 -> every rank's global model is the sample-weighted mean of the three (fl_server.py:92-102 arithmetic)."""
+    script = tmp_path / "mixed.py"
+    script.write_text(f"""
+import sys, json
+sys.path.insert(0, {ROOT!r})
+import numpy as np, torch, torch.distributed as dist
+from crackfl.parallel.runtime import OnBoxFederation, init_distributed
+init_distributed("gloo")
+r = dist.get_rank()
+n = 4096
+fed = OnBoxFederation(clients_per_gpu=1, strategy="fedavg_weighted", numel=n, remote_slots=2)
+g = torch.linspace(-1, 1, n)
+fed.set_global(g)
+ups = [g + 0.1 * (i + 1) * torch.cos(torch.arange(n) * 0.01 * (i + 1)) for i in range(3)]
+ns = [10.0, 30.0, 60.0]
+for rnd in range(2):   # second round: no remote update -> plain 2-client mean
+    fed.publish(0, ups[r])
+    if r == 0 and rnd == 0:
+        fed.stage_remote(ups[2].numpy(), ns[2])
+    fed.aggregate([ns[r]], weighted=True)
+    if rnd == 0:
+        want = (ns[0] * ups[0] + ns[1] * ups[1] + ns[2] * ups[2]) / 100.0
+    else:
+        want = (ns[0] * ups[0] + ns[1] * ups[1]) / 40.0
+    err = float((fed.global_arena - want).abs().max())
+    open({str(tmp_path)!r} + "/res_%d_%d.txt" % (r, rnd), "w").write(repr(err))
+dist.barrier(); dist.destroy_process_group()
+""")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29543", str(script)], capture_output=True,
+                       text=True, timeout=600, env=dict(os.environ, PYTHONPATH=ROOT))
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    errs = [float(open(tmp_path / f"res_{rk}_{rnd}.txt").read()) for rk in (0, 1) for rnd in (0, 1)]
+    assert all(e < 1e-6 for e in errs), errs
+
+
+def test_bridge_server_plus_onbox_round_cpu(tmp_path, monkeypatch):
+    """One process (world 1, oracle back-end): an FLServer whose aggregator is the OnBoxBridge serves ONE gRPC loopback
+    client while run_federated_onbox hosts 2 local clients; each round's global model is the uniform mean of the three
+    updates (fl_server.py:92-102) and the remote client receives it back."""
+    import threading
+    import numpy as np
+    import torch
+    from crackfl.config import fast_test_config
+    from crackfl.io import weights as wio
+    from crackfl.models.spec import REFERENCE_SPEC as S
+    from crackfl.parallel.bridge import OnBoxBridge
+    from crackfl.parallel.runtime import run_federated_onbox
+    from crackfl.protocol import client as C
+    from crackfl.protocol.server import FLServer, make_grpc_server
+    monkeypatch.chdir(tmp_path)
+    cfg = fast_test_config()
+    cfg.train.backend = "torch_ref"; cfg.train.image_size = (32, 32); cfg.train.batch_size = 4; cfg.train.local_epochs = 1
+    cfg.train.tensorboard = False; cfg.train.validate = False
+    cfg.data.synthetic_train = 4; cfg.data.synthetic_val = 0
+    cfg.client.log_root = str(tmp_path / "logs"); cfg.client.write_weights_file = False
+    cfg.server.max_rounds = 2; cfg.server.weights_dir = str(tmp_path / "sw")
+    bridge = OnBoxBridge(S, remote_slots=1, timeout_s=120)
+    srv = FLServer(cfg, S.init_weights(cfg.server.seed), S, aggregator=bridge, log=lambda s: None)
+    gs, port = make_grpc_server(srv, "127.0.0.1:0")
+    gs.start()
+    seen = {}
+
+    class Remote:
+        def fit(self, weights, cr):
+            seen[cr] = [w.copy() for w in weights]
+            return [w + 0.5 for w in weights], {"loss": 0.1, "accuracy": 0.9, "num_samples": 8}
+
+    def run_remote():
+        call, ch = C.make_stub(cfg, f"127.0.0.1:{port}")
+        cl = C.FLClient(cfg, Remote(), call, log=lambda s: None)
+        seen["result"] = cl.run()
+        seen["final"] = cl.final_weights
+        ch.close()
+    th = threading.Thread(target=run_remote)
+    th.start()
+    try:
+        out = run_federated_onbox(cfg, rounds=2, clients_per_gpu=2, strategy="fedavg", log=lambda s: None, bridge=bridge,
+                                  remote_slots=1)
+        th.join(120)
+    finally:
+        gs.stop(0)
+    assert not th.is_alive() and seen["result"]["rounds"] == 2 and bridge.rounds_bridged == 2
+    fed = out["federation"]
+    # last round: updates[0..1] are the two local fits, updates[2] the remote update; uniform mean of the three
+    want = fed.updates[:3].mean(0)
+    assert torch.allclose(fed.global_arena, want, rtol=1e-5, atol=1e-6)
+    # the remote client trained round 2 on the round-1 global model and got the final one back
+    np.testing.assert_allclose(wio.flatten(seen["final"], S), fed.global_arena.numpy(), rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(wio.flatten(srv.global_weights, S), fed.global_arena.numpy(), rtol=1e-6, atol=1e-6)
+    assert not np.allclose(wio.flatten(seen[2], S), wio.flatten(seen[1], S))
