@@ -57,26 +57,58 @@ class StandinUNet(nn.Module):
 
 
 class StandinTrainer:
-    def __init__(self, spec, device, lr=1e-3, autocast=True):
+    """mode: "eager" (Python-driven launches), "graph" (the whole step - zero_grad, forward, loss, backward, fused Adam -
+    captured once in a CUDA graph and replayed: no launch overhead, the fair comparison for a graph-replayed engine),
+    "compile" (torch.compile of the model, Inductor/Triton fusions, still Python-driven optimiser).
+    dtype: "bf16" (autocast) or "fp32" (what the reference trains in, client_fit_model.py:157; cuDNN may use TF32)."""
+
+    def __init__(self, spec, device, lr=1e-3, autocast=True, mode="eager", dtype="bf16", batch_shape=None):
         self.dev = device
+        self.mode = mode
         self.model = StandinUNet(spec).to(device).to(memory_format=torch.channels_last)
-        self.opt = torch.optim.Adam(self.model.parameters(), lr=lr, eps=1e-7, fused=True)
-        self.autocast = autocast
+        self.autocast = autocast and dtype == "bf16"
+        self.opt = torch.optim.Adam(self.model.parameters(), lr=lr, eps=1e-7, fused=True, capturable=(mode == "graph"))
+        self.fwd = torch.compile(self.model) if mode == "compile" else self.model
+        self._graph = None
+        self._sx = self._sy = self._sloss = None
 
     def _step(self, x_u8, y_u8):
         x = x_u8.permute(0, 3, 1, 2).float().div_(255.0).contiguous(memory_format=torch.channels_last)
         y = y_u8.unsqueeze(1).float()
         self.opt.zero_grad(set_to_none=True)
         with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.autocast):
-            logits = self.model(x)
+            logits = self.fwd(x)
         loss = F.binary_cross_entropy_with_logits(logits.float(), y)
         loss.backward()
         self.opt.step()
         return loss
 
+    def _capture(self, x_u8, y_u8):
+        self._sx, self._sy = x_u8.clone(), y_u8.clone()
+        s = torch.cuda.Stream(self.dev)
+        s.wait_stream(torch.cuda.current_stream(self.dev))
+        with torch.cuda.stream(s):
+            for _ in range(3):  # warm-up on a side stream (cuDNN autotune, lazy state) before capture
+                self._step(self._sx, self._sy)
+        torch.cuda.current_stream(self.dev).wait_stream(s)
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph):
+            self._sloss = self._step(self._sx, self._sy)
+
+    def _graph_step(self, x_u8, y_u8):
+        if self._graph is None:
+            self._capture(x_u8, y_u8)
+        self._sx.copy_(x_u8, non_blocking=True)
+        self._sy.copy_(y_u8, non_blocking=True)
+        self._graph.replay()
+        return self._sloss
+
     def train_step_device(self, x_u8_dev, y_u8_dev):
+        if self.mode == "graph":
+            return self._graph_step(x_u8_dev, y_u8_dev)
         return self._step(x_u8_dev, y_u8_dev)
 
     def train_step_host(self, x_u8_pinned, y_u8_pinned):
-        loss = self._step(x_u8_pinned.to(self.dev, non_blocking=True), y_u8_pinned.to(self.dev, non_blocking=True))
+        xd, yd = x_u8_pinned.to(self.dev, non_blocking=True), y_u8_pinned.to(self.dev, non_blocking=True)
+        loss = self._graph_step(xd, yd) if self.mode == "graph" else self._step(xd, yd)
         return float(loss.item())

@@ -40,6 +40,8 @@ def parse():
     ap.add_argument("--conv-impl", default=None)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--width-mult", type=int, default=1)
+    ap.add_argument("--standin-mode", default="eager", choices=["eager", "graph", "compile"])
+    ap.add_argument("--standin-dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--agg-sweep", default="8.233,64,256", help="model sizes (MB) of the aggregation-kernel summary "
                     "emitted with N > 1 GPUs ('' = skip)")
     return ap.parse_args()
@@ -143,12 +145,13 @@ def main():
     e2e_drain = None
     if a.impl == "standin":
         from baseline.torch_standin import StandinTrainer
-        tr = StandinTrainer(spec, dev)
+        tr = StandinTrainer(spec, dev, mode=a.standin_mode, dtype=a.standin_dtype)
         step_dev = lambda i: tr.train_step_device(dx[i % NB], dy[i % NB])
         step_e2e = lambda i: tr.train_step_host(hx[i % NB], hy[i % NB])
         round_end = lambda: None
         launches = None
-        label = "PyTorch eager/cuDNN stand-in (bf16 autocast, channels_last) - NOT the reference's Keras build"
+        label = (f"PyTorch/cuDNN stand-in ({a.standin_mode}, {a.standin_dtype}"
+                 f"{' autocast' if a.standin_dtype == 'bf16' else ''}, channels_last) - NOT the reference's Keras build")
     else:
         from crackfl.models.unet import UNetEngine
         # one client per GPU: the engine trains IN the federation's exported arena, so the round boundary is the fused
@@ -261,7 +264,7 @@ def main():
                       "boundary), max over ranks",
             "value": world * B * a.steps / (ms / 1e3), "unit": "images/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "bf16", "data": "synthetic crack images/masks, random-init weights",
+            "vs_baseline": None, "dtype": "bf16" if a.impl == "ours" else a.standin_dtype, "data": "synthetic crack images/masks, random-init weights",
             "impl": a.impl, "label": label,
             "config": {"model": "crack U-Net (Xception-style, 2.06M params)" if a.width_mult == 1 else
                        f"wide crack U-Net x{a.width_mult}", "global_batch": B * world, "per_gpu_batch": B,

@@ -18,6 +18,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 CSRC = os.path.join(ROOT, "csrc")
 LIBDIR = os.path.join(ROOT, "crackfl", "_lib")
 LIBPATH = os.path.join(LIBDIR, "libcrackfl.so")
+# The same optimiser / elementwise sources compiled WITHOUT --use_fast_math (IEEE division, sqrtf, logf, expf): not used
+# by the engine, only by tests/test_gpu_fastmath.py to bound what the fast-math build changes in Adam, BN finalize and BCE.
+IEEE_LIBPATH = os.path.join(LIBDIR, "libcrackfl_ieee.so")
+IEEE_SOURCES = ("optim.cu", "elementwise.cu")
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--use_fast_math", "-Xptxas", "-v",
               "-I", os.path.join(ROOT, "include")]
@@ -46,7 +50,8 @@ def _digest() -> str:
 
 def is_current() -> bool:
     stamp = os.path.join(LIBDIR, "build.stamp")
-    return os.path.exists(LIBPATH) and os.path.exists(stamp) and open(stamp).read().strip() == _digest()
+    return os.path.exists(LIBPATH) and os.path.exists(IEEE_LIBPATH) and os.path.exists(stamp) and \
+        open(stamp).read().strip() == _digest()
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -79,8 +84,19 @@ def _build_locked(verbose: bool) -> str:
             raise RuntimeError(f"nvcc failed on {src}:\n{r.stdout}\n{r.stderr}")
         return obj
 
+    def compile_ieee(_):
+        tmp = IEEE_LIBPATH + f".tmp.{os.getpid()}"
+        flags = [f for f in NVCC_FLAGS if f != "--use_fast_math"]
+        cmd = [nvcc, *ARCH_FLAGS, *flags, "-shared", "-o", tmp, *[os.path.join(CSRC, f) for f in IEEE_SOURCES], "-lcudart"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"nvcc failed on the IEEE variant:\n{r.stdout}\n{r.stderr}")
+        os.replace(tmp, IEEE_LIBPATH)
+
     with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 4)) as ex:
+        ieee_job = ex.submit(compile_ieee, None)
         objs = list(ex.map(compile_one, sources()))
+        ieee_job.result()
     with open(os.path.join(LIBDIR, "ptxas.log"), "w") as f:
         for s, l in logs.items():
             f.write(f"==== {os.path.basename(s)}\n{l}\n")

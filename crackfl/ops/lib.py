@@ -143,6 +143,20 @@ def get_lib(build_if_needed: bool = True) -> C.CDLL:
     return lib
 
 
+def get_ieee_lib() -> C.CDLL:
+    """The optimiser / elementwise kernels built without --use_fast_math (tests only, see build.IEEE_LIBPATH)."""
+    get_lib()
+    lib = C.CDLL(_build.IEEE_LIBPATH)
+    for name, sig in _SIGS.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError:
+            continue
+        fn.argtypes = sig
+        fn.restype = i32
+    return lib
+
+
 def check(code: int, what: str = ""):
     if code != 0:
         raise KernelError(f"{what or 'kernel launch'} failed with cudaError {code}")

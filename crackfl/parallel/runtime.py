@@ -344,8 +344,8 @@ class OnBoxFederation:
         L, lib = self.L, self.lib
         st = torch.cuda.current_stream(self.dev)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(st)
         K = self.K
+        p = None
         nrem = len(rcoef)
         # which buffer does each rank offer to its peers?  The live arena itself when that rank's single local update
         # needs no pass of its own (no remote updates, fp32 payload, no NVLS pre-scaling), else its pre-reduced partial.
@@ -375,7 +375,6 @@ class OnBoxFederation:
             p.rank, p.world, p.epoch = 0, 1, 1
             p.error_flag = p.local_sync = 0
             p.load_mode = 1
-            L.check(lib.crackfl_fedagg(C.byref(p), 148 * 8, st.cuda_stream), "fedagg pre-reduce")
         # (K11-K13) cross-GPU reduce + server update + broadcast, one launch
         q = L.FedAggParams()
         for r in range(self.world):
@@ -400,6 +399,11 @@ class OnBoxFederation:
         q.load_mode = int(os.environ.get("CRACKFL_AGG_LOAD_MODE", "0"))
         q.unroll = int(os.environ.get("CRACKFL_AGG_UNROLL", "4"))
         q.timeout_cycles = int(self.timeout_s * 1.9e9)
+        # (the parameter blocks are built before the first event so that, on an idle stream, the events bracket the
+        # launches and not the host-side set-up)
+        e0.record(st)
+        if p is not None:
+            L.check(lib.crackfl_fedagg(C.byref(p), 148 * 8, st.cuda_stream), "fedagg pre-reduce")
         L.check(lib.crackfl_fedagg(C.byref(q), self.grid_blocks, st.cuda_stream), "fedagg")
         e1.record(st)
         self._events = (e0, e1)
