@@ -94,7 +94,8 @@ class DataConfig:
     synthetic_train: int = 6213
     synthetic_val: int = 1024
     workers: int = 4
-    prefetch_batches: int = 4  # extension: batches decoded ahead of the training loop by a worker thread (0 = inline, as the reference)
+    prefetch_batches: int = 16  # extension: batches decoded ahead of the training loop (0 = inline, as the reference)
+    prefetch_threads: int = 8  # extension: threads that build those batches (whole batches in parallel)
 
 
 @dataclass

@@ -30,6 +30,8 @@ import numpy as np
 class Generator:
     """``Generator(keras.utils.Sequence)`` of ``client_fit_model.py:19-43``."""
 
+    _cv_threads_set = False
+
     def __init__(self, input_img_paths: Sequence[str], target_img_paths: Sequence[str], batch_size: int,
                  img_size: Tuple[int, int], as_float: bool = False, workers: int = 0):
         self.x, self.y = list(input_img_paths), list(target_img_paths)
@@ -45,6 +47,9 @@ class Generator:
 
     def _load_x(self, fn: str) -> np.ndarray:
         import cv2
+        if not Generator._cv_threads_set:  # batches are decoded in parallel by the caller's threads: no nested cv2 pool
+            cv2.setNumThreads(1)
+            Generator._cv_threads_set = True
         img = cv2.imread(fn, -1)
         if img is None:
             raise FileNotFoundError(fn)

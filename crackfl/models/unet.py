@@ -938,9 +938,9 @@ class B200Backend:
         if torch.is_tensor(x_u8) and x_u8.is_cuda:  # device-resident data (synthetic generator K15): no staging
             return x_u8, y_u8
         torch.cuda.current_stream(self.engine.dev).synchronize()  # previous H2D from the pinned buffers is done
-        self._hx.copy_(torch.as_tensor(np.ascontiguousarray(x_u8)))
+        np.copyto(self._hx.numpy(), np.asarray(x_u8).reshape(self._hx.shape), casting="unsafe")
         if y_u8 is not None:
-            self._hy.copy_(torch.as_tensor(np.ascontiguousarray(y_u8)).reshape(self._hy.shape))
+            np.copyto(self._hy.numpy(), np.asarray(y_u8).reshape(self._hy.shape), casting="unsafe")
         return self._hx, (self._hy if y_u8 is not None else None)
 
     def train_batch(self, x_u8, y_u8):
@@ -960,8 +960,11 @@ class B200Backend:
         if self._pin_ev[i] is not None:
             self._pin_ev[i].synchronize()  # the H2D copy that read this pinned buffer two batches ago is done
         hx, hy = self._pin[i]
-        hx.copy_(torch.as_tensor(np.ascontiguousarray(x_u8)).reshape(hx.shape))
-        hy.copy_(torch.as_tensor(np.ascontiguousarray(y_u8)).reshape(hy.shape))
+        # plain memcpy through NumPy views of the pinned buffers: torch's CPU copy_ splits a 3 MB copy over its OpenMP
+        # pool, and with decode threads busy on the same cores the slowest slice set the pace (measured: 9.5 ms per
+        # batch in train_batch against 0.2 ms for the memcpy)
+        np.copyto(hx.numpy(), np.asarray(x_u8).reshape(hx.shape), casting="unsafe")
+        np.copyto(hy.numpy(), np.asarray(y_u8).reshape(hy.shape), casting="unsafe")
         eng.prefetch(hx, hy)
         self._pin_ev[i] = eng._stage_ev[eng._stage_pending]
         eng.train_step_prefetched()

@@ -94,49 +94,60 @@ def make_backend(cfg: Config, spec: UNetSpec, device: Optional[int] = None, aren
     raise ValueError(f"unknown backend {kind!r}")
 
 
-def _prefetched(ds, order, depth: int):
-    """Batches of ``ds`` in ``order``, fetched ``depth`` batches ahead by a worker thread.
+def _prefetched(ds, order, depth: int, threads: int = 1):
+    """Batches of ``ds`` in ``order``, decoded up to ``depth`` batches ahead by ``threads`` worker threads.
 
     The reference decodes the 32 JPEGs of a step inside ``fit``'s loop (``client_fit_model.py:30-43`` is called by Keras
-    with no ``workers``), so decode + resize sit on the critical path of every step.  Here ``ds[i]`` runs in a thread
-    (cv2 releases the GIL) and the training loop only ever waits on a queue.  Device-resident datasets and
-    ``depth <= 0`` fall through to plain indexing."""
+    with no ``workers``), so decode + resize sit on the critical path of every step.  Here every worker takes the next
+    batch index, builds that whole batch (cv2 releases the GIL while it decodes) and parks it in an ordered buffer; the
+    training loop only ever waits for the next batch in order.  Parallelism is per BATCH, not per image: one Python call
+    per batch and no nested pools.  Device-resident datasets and ``depth <= 0`` fall through to plain indexing."""
     if depth <= 0 or len(order) < 2 or getattr(ds, "device_resident", False):
         for bi in order:
             yield ds[bi]
         return
-    import queue
     import threading
-    q: "queue.Queue" = queue.Queue(maxsize=depth)
-    stop = threading.Event()
+    cv = threading.Condition()
+    results, state = {}, {"next": 0, "consumed": 0, "stop": False}
+    n = len(order)
 
     def work():
-        try:
-            for bi in order:
-                if stop.is_set():
-                    return
-                q.put(("ok", ds[bi]))
-            q.put(("end", None))
-        except BaseException as e:  # surfaced in the consumer
-            q.put(("err", e))
-
-    th = threading.Thread(target=work, daemon=True, name="crackfl-prefetch")
-    th.start()
-    try:
         while True:
-            kind, item = q.get()
-            if kind == "end":
-                return
+            with cv:
+                while not state["stop"] and state["next"] < n and state["next"] - state["consumed"] >= depth:
+                    cv.wait()
+                if state["stop"] or state["next"] >= n:
+                    return
+                i = state["next"]
+                state["next"] += 1
+            try:
+                item = ("ok", ds[order[i]])
+            except BaseException as e:  # surfaced in the consumer, in order
+                item = ("err", e)
+            with cv:
+                results[i] = item
+                cv.notify_all()
+
+    ths = [threading.Thread(target=work, daemon=True, name=f"crackfl-prefetch-{k}") for k in range(max(1, threads))]
+    for t in ths:
+        t.start()
+    try:
+        for i in range(n):
+            with cv:
+                while i not in results:
+                    cv.wait()
+                kind, item = results.pop(i)
+                state["consumed"] = i + 1
+                cv.notify_all()
             if kind == "err":
                 raise item
             yield item
     finally:
-        stop.set()
-        while th.is_alive():  # unblock a producer that is waiting on a full queue
-            try:
-                q.get_nowait()
-            except queue.Empty:
-                th.join(0.01)
+        with cv:
+            state["stop"] = True
+            cv.notify_all()
+        for t in ths:
+            t.join(1.0)
 
 
 class LocalTrainer:
@@ -183,7 +194,7 @@ class LocalTrainer:
             if t.shuffle_batches:
                 self.rng.shuffle(order)  # Keras shuffles batch ORDER of a Sequence, not contents
             be.reset_metrics()
-            for x, y in _prefetched(self.train_ds, order, self.cfg.data.prefetch_batches):
+            for x, y in _prefetched(self.train_ds, order, self.cfg.data.prefetch_batches, self.cfg.data.prefetch_threads):
                 be.train_batch(x, y)
             train_m = be.read_metrics()
             if t.validate and self.val_ds is not None and len(self.val_ds) > 0:

@@ -805,6 +805,415 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
 }
 
 // ----------------------------------------------------------------------------------------------------------
+struct ConvArgsX {
+  const float* bias;
+  const __nv_bfloat16* add;
+  float* stats;
+  int B, H, W, Cin, N, taps;
+  int BN, kc, stages;
+  int sub_w;
+  int n_tiles_m, n_tiles_n;
+  uint32_t layout, sbo;
+  int base_off;              // set the descriptor's base_offset field from the start address
+  int dbg_noflush;
+  int astages;               // halo-tile ring depth (2..4)
+  int resident;              // all 9 * Cin/kc weight tiles stay in shared memory for the CTA's lifetime (stages == that count)
+  uint32_t a_stage, a_bytes; // halo stage pitch (1024-aligned) / payload bytes (180 rows of kc channels)
+  TileGeom g;
+  // transform stage
+  int xmode;                 // 1: relu(x), 2: relu(scale[c] * x + shift[c]) with zero outside the image
+  int diag;                  // depthwise: n-tile == channel chunk, block-diagonal weight tiles, one chunk per CTA
+  const float* bn;           // [scale C | shift C] (xmode 2, fin.stats == NULL)
+  crackfl_bn_fin fin;        // or: derive them from the statistics here and let block 0 publish them
+  __nv_bfloat16* side;       // optional: the transformed activation is also written out (B,H,W,Cin), by the n-tile-0 CTAs
+};
+
+// "xf" variant of the halo kernel: four extra warps TRANSFORM every halo tile in shared memory between the TMA load and
+// the MMAs - ReLU, or BatchNorm-apply + ReLU with the scale/shift derived from the statistics (K1: the
+// ReLU -> Conv2DTranspose -> BN chain of client_fit_model.py:128-134 without a separate BN-apply pass) - re-zeroing the
+// pixels that lie outside the image ("same" padding pads the ACTIVATION with zeros, and relu(shift) is not zero).
+// With `diag` the weight tiles are the 64x64 (32x32) block-diagonal expansion of a depthwise 3x3 kernel, so the depthwise
+// half of a SeparableConv2D (client_fit_model.py:109,113) runs on the tensor cores: 36 MMAs of 128x64x16 per 128-pixel
+// tile (~0.6 us) against ~0.9 us of HBM time for the tile, instead of an issue-bound CUDA-core stencil.
+// One CTA per SM (448 threads), everything else as in conv_tc_fwd_v3_k below.
+//
+// "resident" mode (small layers: 9 * Cin * N * 2 bytes <= ~80 KB, one n-tile): the weight tiles are loaded ONCE per CTA
+// onto a single barrier; per tile the producer only streams halo tiles and the issuing thread fires its 9 * kc/16 MMAs
+// back to back (no per-tap barrier round trip, no re-streaming of the weights from L2 for every 128-pixel tile, which
+// for N = 32 was more traffic than the activations).  kc = 32 (Cin = 32) uses the SWIZZLE_64B flavour of the same trick.
+__global__ void __launch_bounds__(64 + EPI_THREADS + 128, 1) conv_tc_xf_k(const __grid_constant__ CUtensorMap tmA,
+                                                        const __grid_constant__ CUtensorMap tmB,
+                                                        const __grid_constant__ CUtensorMap tmY, const ConvArgsX a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  // A ring: 2 halo tiles of (TH+2) x (TW+2) = 18 x 10 pixels x 64 channels (23040 B, padded to 23552);
+  // B ring: a.stages weight tiles [BN][64] (one per (chunk, tap)); then 2 output staging buffers.
+  constexpr uint32_t HALO_W = 10u;
+  const uint32_t A_STAGE = a.a_stage, A_BYTES = a.a_bytes, row_b = (uint32_t)a.kc * 2u;
+  const uint32_t b_bytes = (uint32_t)a.BN * row_b;
+  const uint32_t bring = base + (uint32_t)a.astages * A_STAGE;
+  const uint32_t out_bytes = 128u * (uint32_t)a.BN * 2u;
+  const uint32_t out0 = bring + a.stages * b_bytes;
+  const uint32_t bar_base = out0 + 2u * out_bytes;
+  const uint32_t fullA0 = bar_base, emptyA0 = bar_base + 32u, xfA0 = bar_base + 64u;
+  const uint32_t full0 = bar_base + 96u, empty0 = full0 + 8u * a.stages;
+  const uint32_t tfull0 = empty0 + 8u * a.stages, tempty0 = tfull0 + 16u;
+  const uint32_t tptr = tempty0 + 16u;
+  const uint32_t stat_smem = tptr + 16u;  // EPI_WARPS x 2 x 128 floats
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
+  const int kchunks = a.diag ? 1 : a.Cin / a.kc;
+  const int nch = a.Cin / a.kc;
+  // schedule: tile k of this CTA.  Plain: tile = blockIdx.x + k * gridDim.x over (m fastest, n).  diag: the CTA keeps ONE
+  // channel chunk (its weight tiles stay resident) and walks the m-tiles with stride gridDim.x / nch.
+  const int my_chunk = a.diag ? (int)(blockIdx.x % nch) : 0;
+  const int t_first = a.diag ? (int)(blockIdx.x / nch) : (int)blockIdx.x;
+  const int t_step = a.diag ? (int)(gridDim.x / nch) : (int)gridDim.x;
+  const int total_tiles = a.diag ? a.n_tiles_m : a.n_tiles_m * a.n_tiles_n;
+  const uint32_t ncols = (uint32_t)(2 * a.BN < 32 ? 32 : 2 * a.BN);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < a.stages; ++s) {
+      mbar_init(full0 + 8u * s, 1);
+      mbar_init(empty0 + 8u * s, 1);
+    }
+    for (int s = 0; s < a.astages; ++s) {
+      mbar_init(fullA0 + 8u * s, 1);
+      mbar_init(emptyA0 + 8u * s, 1);
+      mbar_init(xfA0 + 8u * s, 4);  // one arrival per transform warp
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull0 + 8u * s, 1);
+      mbar_init(tempty0 + 8u * s, EPI_WARPS);  // one arrival per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmY);
+  }
+  if (warp == 1) tmem_alloc(tptr, ncols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  ck::pdl_enter();  // set-up above overlapped the previous kernel's tail; global memory is touched only from here on
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tptr));
+  // BN scale / shift of the INPUT channels (xmode 2): from the published table, or straight from the statistics of the
+  // producing conv (finalize folded in, as in the *_fin elementwise kernels; block 0 publishes table + moving statistics)
+  float* xf_tab = reinterpret_cast<float*>(smem_raw + (stat_smem + 5120u - smem_u32(smem_raw)));  // [scale Cin | shift Cin]
+  if (a.xmode == 2) {
+    for (int c = threadIdx.x; c < a.Cin; c += blockDim.x) {
+      float scl, sft;
+      if (a.fin.stats) {
+        const float mean = a.fin.stats[c] / a.fin.count;
+        const float var = fmaxf(a.fin.stats[a.Cin + c] / a.fin.count - mean * mean, 0.f);
+        const float invstd = rsqrtf(var + a.fin.eps);
+        scl = a.fin.gamma[c] * invstd;
+        sft = a.fin.beta[c] - mean * scl;
+        if (blockIdx.x == 0) {
+          a.fin.bn_out[c] = scl; a.fin.bn_out[a.Cin + c] = sft; a.fin.bn_out[2 * a.Cin + c] = mean; a.fin.bn_out[3 * a.Cin + c] = invstd;
+          const float unb = a.fin.count > 1.f ? var * (a.fin.count / (a.fin.count - 1.f)) : var;
+          a.fin.run_mean[c] = a.fin.run_mean[c] * a.fin.momentum + mean * (1.f - a.fin.momentum);
+          a.fin.run_var[c] = a.fin.run_var[c] * a.fin.momentum + unb * (1.f - a.fin.momentum);
+        }
+      } else {
+        scl = a.bn[c]; sft = a.bn[a.Cin + c];
+      }
+      xf_tab[c] = scl; xf_tab[a.Cin + c] = sft;
+    }
+    __syncthreads();
+  }
+
+  if (warp == 0) {
+    // ---- producer: all lanes walk the schedule (uniform control flow), one elected lane issues
+    uint32_t ia = 0, ib = 0;  // ring positions: halo tiles / weight tiles
+    if (a.resident && t_first < total_tiles) {
+      if (elect_one()) {
+        mbar_expect_tx(full0, (uint32_t)a.stages * b_bytes);
+        for (int c = 0; c < kchunks; ++c)
+          for (int t = 0; t < 9; ++t)
+            tma_load_2d(bring + (uint32_t)(c * 9 + t) * b_bytes, &tmB, full0, a.diag ? 0 : t * a.Cin + c * a.kc,
+                        a.diag ? (my_chunk * 9 + t) * a.kc : 0);
+      }
+      __syncwarp();
+    }
+    for (int tile = t_first; tile < total_tiles; tile += t_step) {
+      int tm_ = tile % a.n_tiles_m;
+      const int n0 = a.diag ? my_chunk * a.kc : (tile / a.n_tiles_m) * a.BN;
+      const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
+      const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
+      const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
+      for (int c = 0; c < kchunks; ++c, ++ia) {
+        const uint32_t sa = ia % (uint32_t)a.astages, pha = (ia / (uint32_t)a.astages) & 1u;
+        mbar_wait(emptyA0 + 8u * sa, pha ^ 1u);
+        if (elect_one()) {
+          mbar_expect_tx(fullA0 + 8u * sa, A_BYTES);
+          tma_load_4d(base + sa * A_STAGE, &tmA, fullA0 + 8u * sa, (a.diag ? my_chunk : c) * a.kc, w0 - 1, h0 - 1, b0);  // halo: zero fill = padding
+        }
+        __syncwarp();
+        if (a.resident) continue;
+        for (int t = 0; t < 9; ++t, ++ib) {
+          const uint32_t s = ib % a.stages, ph = (ib / a.stages) & 1u;
+          mbar_wait(empty0 + 8u * s, ph ^ 1u);
+          if (elect_one()) {
+            mbar_expect_tx(full0 + 8u * s, b_bytes);
+            tma_load_2d(bring + s * b_bytes, &tmB, full0 + 8u * s, t * a.Cin + c * a.kc, n0);
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ---- MMA issue: uniform control flow, descriptors in {lo, hi} words, one elected lane fires the instructions
+    const uint32_t idesc = make_idesc(128, a.BN, 0, 0);
+    const uint32_t ahi = desc_hi(HALO_W * row_b, a.layout), bhi = desc_hi(a.sbo, a.layout);
+    const bool k64 = a.kc == 64;
+    uint32_t ia = 0, ib = 0, tcount = 0;
+    for (int tile = t_first; tile < total_tiles; tile += t_step, ++tcount) {
+      const uint32_t as = tcount & 1u, aph = (tcount >> 1) & 1u;
+      mbar_wait(tempty0 + 8u * as, aph ^ 1u);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + as * (uint32_t)a.BN;
+      if (a.resident && tcount == 0) {
+        mbar_wait(full0, 0u);  // the resident weight tiles have landed
+        tc_fence_after();
+      }
+      for (int c = 0; c < kchunks; ++c, ++ia) {
+        const uint32_t sa = ia % (uint32_t)a.astages, pha = (ia / (uint32_t)a.astages) & 1u;
+        mbar_wait(xfA0 + 8u * sa, pha);  // the transform warps have rewritten the tile
+        tc_fence_after();
+        const uint32_t halo = base + sa * A_STAGE;
+#pragma unroll
+        for (int t = 0; t < 9; ++t, ++ib) {
+          const uint32_t s = a.resident ? (uint32_t)(c * 9 + t) : ib % a.stages, ph = (ib / a.stages) & 1u;
+          if (!a.resident) {
+            mbar_wait(full0 + 8u * s, ph);
+            tc_fence_after();
+          }
+          // tap (kh,kw): output pixel (th,tw) reads halo pixel (th+kh, tw+kw).  One 8-row swizzle group = the 8
+          // pixels of one tile row, groups HALO_W * row_b bytes apart: the shifted window is still a canonical
+          // K-major swizzled operand, it just starts (kh*HALO_W + kw) rows into the halo tile.
+          const uint32_t alo = desc_lo(halo + (uint32_t)((t / 3) * HALO_W + (t % 3)) * row_b, 16);
+          const uint32_t blo = desc_lo(bring + s * b_bytes, 16);
+          const uint32_t first = (c > 0 || t > 0) ? 1u : 0u;
+          if (elect_one()) {
+            umma_f16_w(tacc, alo, ahi, blo, bhi, idesc, first);
+            umma_f16_w(tacc, alo + 2u, ahi, blo + 2u, bhi, idesc, 1u);
+            if (k64) {
+              umma_f16_w(tacc, alo + 4u, ahi, blo + 4u, bhi, idesc, 1u);
+              umma_f16_w(tacc, alo + 6u, ahi, blo + 6u, bhi, idesc, 1u);
+            }
+            if (!a.resident) umma_commit(empty0 + 8u * s);
+          }
+          __syncwarp();
+        }
+        if (elect_one()) umma_commit(emptyA0 + 8u * sa);
+        __syncwarp();
+      }
+      if (elect_one()) umma_commit(tfull0 + 8u * as);
+      __syncwarp();
+    }
+  } else if (warp >= 2 + EPI_WARPS) {
+    // ---- transform warps: halo tile in shared memory -> activation, in place, between TMA and MMA
+    const int xt = threadIdx.x - (64 + EPI_THREADS);  // 0..127
+    const int lane_ = threadIdx.x & 31;
+    const int cpr = a.kc >> 3;                        // 16-byte chunks per halo pixel (8 or 4)
+    const uint32_t swz_mask = a.kc == 64 ? 7u : 3u;   // SWIZZLE_128B / SWIZZLE_64B: chunk index ^= address bits [7..]
+    uint32_t ia = 0;
+    for (int tile = t_first; tile < total_tiles; tile += t_step) {
+      int tm_ = tile % a.n_tiles_m;
+      const int n0 = a.diag ? my_chunk * a.kc : (tile / a.n_tiles_m) * a.BN;
+      const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
+      const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
+      const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
+      const bool do_side = a.side != nullptr && (a.diag || n0 == 0);
+      for (int c = 0; c < kchunks; ++c, ++ia) {
+        const uint32_t sa = ia % (uint32_t)a.astages, pha = (ia / (uint32_t)a.astages) & 1u;
+        const int cbase = (a.diag ? my_chunk : c) * a.kc;
+        mbar_wait(fullA0 + 8u * sa, pha);
+        const uint32_t halo = base + sa * A_STAGE;
+        for (int idx = xt; idx < 180 * cpr; idx += 128) {
+          const int p = idx / cpr, j = idx - p * cpr;
+          const uint32_t addr = halo + (uint32_t)p * row_b + (uint32_t)j * 16u;
+          const int lch = (int)((uint32_t)j ^ ((addr >> 7) & swz_mask));  // logical chunk held at this physical slot
+          const int hr = p / (int)HALO_W, hc = p - hr * (int)HALO_W;
+          const int ih = h0 - 1 + hr, iw = w0 - 1 + hc;
+          const bool inside = ih >= 0 && ih < a.H && iw >= 0 && iw < a.W && b0 < a.B;
+          uint32_t v0, v1, v2, v3;
+          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v0), "=r"(v1), "=r"(v2), "=r"(v3) : "r"(addr));
+          if (a.xmode == 1) {
+            v0 = relu_bf2(v0); v1 = relu_bf2(v1); v2 = relu_bf2(v2); v3 = relu_bf2(v3);  // zero fill stays zero
+          } else if (inside) {
+            const float* sc = xf_tab + cbase + lch * 8;
+            const float* sh = sc + a.Cin;
+            const float4 s0 = *reinterpret_cast<const float4*>(sc), s1 = *reinterpret_cast<const float4*>(sc + 4);
+            const float4 h0_ = *reinterpret_cast<const float4*>(sh), h1_ = *reinterpret_cast<const float4*>(sh + 4);
+            v0 = f2_to_bf2_relu(ffma2(bf2_to_f2(v0), pk2(s0.x, s0.y), pk2(h0_.x, h0_.y)));
+            v1 = f2_to_bf2_relu(ffma2(bf2_to_f2(v1), pk2(s0.z, s0.w), pk2(h0_.z, h0_.w)));
+            v2 = f2_to_bf2_relu(ffma2(bf2_to_f2(v2), pk2(s1.x, s1.y), pk2(h1_.x, h1_.y)));
+            v3 = f2_to_bf2_relu(ffma2(bf2_to_f2(v3), pk2(s1.z, s1.w), pk2(h1_.z, h1_.w)));
+          } else {
+            v0 = v1 = v2 = v3 = 0u;  // "same" padding pads the activation: relu(shift) must not leak in
+          }
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v0), "r"(v1), "r"(v2), "r"(v3) : "memory");
+          if (do_side && inside && hr >= 1 && hr <= a.g.TH && hc >= 1 && hc <= a.g.TW) {
+            uint4 o; o.x = v0; o.y = v1; o.z = v2; o.w = v3;
+            ck::stg16(a.side + (((long)b0 * a.H + ih) * a.W + iw) * a.Cin + cbase + lch * 8, o);
+          }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the MMA's reads
+        __syncwarp();
+        if (lane_ == 0) mbar_arrive(xfA0 + 8u * sa);
+      }
+    }
+  } else {
+    const int q = warp & 3;          // TMEM lane quarter this warp may read
+    const int eg = (warp - 2) >> 2;  // column group: chunks eg, eg+2, ...
+    const int ew = eg * 4 + q;       // 0..7
+    const int r = q * 32 + lane;
+    const int tw = r % a.g.TW, th = (r / a.g.TW) % a.g.TH, tb = r / (a.g.TW * a.g.TH);
+    const int et = threadIdx.x - 64;  // 0..255 among the epilogue threads
+    const int nsub = a.BN / a.sub_w;
+    const uint32_t sub_bytes = 128u * (uint32_t)a.sub_w * 2u;
+    const uint32_t row_bytes = (uint32_t)a.sub_w * 2u;
+    // BN statistics are accumulated per CTA across all its tiles of one n-tile (registers: lane <-> column) and
+    // flushed with 2*BN atomics per CTA instead of 8*BN per tile: the per-tile version serialised thousands of
+    // same-address atomics in L2 and doubled the kernel time.
+    // Column sums come from the staged bf16 tile in shared memory (second version; the first transposed 2 x 32 registers
+    // through 62 warp shuffles per chunk and cost 8-11 us on the 128x128-pixel layers): thread = one bf16x2 word column x
+    // one group of rows, packed fp32 accumulators that live across all tiles of the CTA's current n-tile.
+    f2_t cs1 = 0ull, cs2 = 0ull;
+    const int wpr = a.BN >> 1;                 // bf16x2 words per tile row
+    const int s_wcol = et % wpr, s_rgrp = et / wpr, s_groups = EPI_THREADS / wpr, s_rows = 128 / s_groups;
+    int cur_n0 = -1;
+    auto flush_stats = [&](int n0f) {
+      // per-thread partials -> smem -> one atomic per column
+      float* red = reinterpret_cast<float*>(smem_raw + (stat_smem - smem_u32(smem_raw)));
+      epi_bar_sync();
+      float x0, x1, q0, q1;
+      upk2(cs1, x0, x1);
+      upk2(cs2, q0, q1);
+      red[(s_rgrp * 2 + 0) * a.BN + 2 * s_wcol] = x0; red[(s_rgrp * 2 + 0) * a.BN + 2 * s_wcol + 1] = x1;
+      red[(s_rgrp * 2 + 1) * a.BN + 2 * s_wcol] = q0; red[(s_rgrp * 2 + 1) * a.BN + 2 * s_wcol + 1] = q1;
+      cs1 = 0ull; cs2 = 0ull;
+      epi_bar_sync();
+      for (int i = et; i < 2 * a.BN; i += EPI_THREADS) {
+        const int which = i / a.BN, col = i % a.BN;
+        float v = 0.f;
+        for (int g = 0; g < s_groups; ++g) v += red[(g * 2 + which) * a.BN + col];
+        if (!a.dbg_noflush) atomicAdd(a.stats + which * a.N + n0f + col, v);
+      }
+    };
+    // bias vector into shared memory once (ordered by the first epi_bar_sync below): no global-memory latency between
+    // the accumulator becoming ready and the tile being stored
+    float* sbias = reinterpret_cast<float*>(smem_raw + (stat_smem + 4096u - smem_u32(smem_raw)));
+    if (a.bias)
+      for (int i = et; i < a.N; i += EPI_THREADS) sbias[i] = __ldg(a.bias + i);
+    uint32_t tcount = 0;
+    for (int tile = t_first; tile < total_tiles; tile += t_step, ++tcount) {
+      int tm_ = tile % a.n_tiles_m;
+      const int n0 = a.diag ? my_chunk * a.kc : (tile / a.n_tiles_m) * a.BN;
+      if (a.stats && n0 != cur_n0) {
+        if (cur_n0 >= 0) flush_stats(cur_n0);
+        cur_n0 = n0;
+      }
+      const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
+      const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
+      const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
+      const int pw = w0 + tw, ph_ = h0 + th, pb = b0 + tb;
+      const bool valid = pw < a.W && ph_ < a.H && pb < a.B;
+      const long pix = ((long)pb * a.H + ph_) * a.W + pw;
+      const uint32_t as = tcount & 1u, aph = (tcount >> 1) & 1u;
+      const uint32_t obuf = out0 + as * out_bytes;
+      // the TMA store that last read this staging buffer (two tiles ago) must have finished reading it
+      if (et == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+      epi_bar_sync();
+      mbar_wait(tfull0 + 8u * as, aph);
+      tc_fence_after();
+      for (int c0 = eg * 32; c0 < a.BN; c0 += 64) {
+        uint32_t raw[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * (uint32_t)a.BN + (uint32_t)c0, raw);
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
+        if (a.bias) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 bb = *reinterpret_cast<const float4*>(sbias + n0 + c0 + j);
+            v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
+          }
+        }
+        if (a.add && valid) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            float t8[8];
+            ck::unpack8(ck::ldg16(a.add + pix * a.N + n0 + c0 + j), t8);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[j + e] += t8[e];
+          }
+        }
+        if (a.stats && !valid) {  // out-of-image rows are clipped by the TMA store but must not enter the statistics
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0.f;
+        }
+        // bf16 pack + swizzled staging store (row r of sub-tile c0 / sub_w)
+        const int sub = c0 / a.sub_w, cin_sub = c0 % a.sub_w;
+        const uint32_t rowaddr = obuf + sub * sub_bytes + (uint32_t)r * row_bytes;
+        const uint32_t xorv = (a.sub_w == 64) ? (uint32_t)(r & 7) : (uint32_t)((r >> 1) & 3);
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+          const uint4 pk = ck::pack8(&v[j]);
+          const uint32_t chunk = (uint32_t)((cin_sub + j) >> 3);
+          const uint32_t dst = rowaddr + ((chunk ^ xorv) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(pk.x), "r"(pk.y), "r"(pk.z), "r"(pk.w)
+                       : "memory");
+        }
+      }
+      // accumulator stage fully read: hand it back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty0 + 8u * as);
+      // make the staging writes visible to the async proxy, then one thread stores the tile
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      epi_bar_sync();
+      if (et == 0) {
+        for (int sub = 0; sub < nsub; ++sub)
+          tma_store_4d(&tmY, obuf + sub * sub_bytes, n0 + sub * a.sub_w, w0, h0, b0);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+      if (a.stats) {
+        // the staged tile is complete (barrier above) and stays untouched until two tiles from now
+        const int col = 2 * s_wcol;
+        const int sub = col / a.sub_w, cin_sub = col % a.sub_w;
+        const uint32_t chunk = (uint32_t)(cin_sub >> 3), within = (uint32_t)(cin_sub & 7) * 2u;
+        const uint32_t colbase = obuf + sub * sub_bytes + within;
+        const int r0 = s_rgrp * s_rows;
+#pragma unroll 4
+        for (int rr = 0; rr < s_rows; ++rr) {
+          const int rw_ = r0 + rr;
+          const uint32_t xv = (a.sub_w == 64) ? (uint32_t)(rw_ & 7) : (uint32_t)((rw_ >> 1) & 3);
+          uint32_t w;
+          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(colbase + (uint32_t)rw_ * row_bytes + ((chunk ^ xv) << 4)));
+          const f2_t x = bf2_to_f2(w);
+          cs1 = fadd2(cs1, x);
+          cs2 = ffma2(x, x, cs2);
+        }
+      }
+    }
+    if (a.stats && cur_n0 >= 0) flush_stats(cur_n0);
+    // only the shared-memory reads of the last stores must finish before the CTA retires; the global writes are
+    // complete at grid end like any other store
+    if (et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, ncols);
+  }
+}
+
+
+// ----------------------------------------------------------------------------------------------------------
 struct WgradArgs {
   float* dW;
   long s_tap, s_ci, s_co;
