@@ -73,6 +73,16 @@ class UNetEngine:
         # tiles fall out of L2 before they are reduced - so the per-layer reduction right behind each GEMM stays the default
         self.wgrad_deferred = os.environ.get("CRACKFL_WGRAD_DEFERRED", "0") != "0"
         self.wgrad_split = os.environ.get("CRACKFL_WGRAD_SPLIT", "1") != "0"  # measured: -20 us per step
+        # K1: BN-apply + ReLU inside the second decoder conv of each block (no bn_act pass); depthwise forward on the tensor
+        # cores through block-diagonal weight tiles (csrc/conv_tc.cu conv_tc_xf_k)
+        # (measured, bench/xf_bench.py + full step: the fused prologue wins 2-4 us per layer for the 64..256-channel decoder
+        # convs and loses 10 us on the 32-channel one at 128^2, whose 64-byte halo rows are TMA-bound; the tensor-core
+        # depthwise kernel has a floor of ~2 us per 128-pixel tile per SM WITHOUT any transform work - the 180 x 128 B
+        # halo load and the 128 x 128 B store go through the one TMA unit of the SM - which is what the CUDA-core stencil
+        # already reaches, so it stays off: CRACKFL_XF_DEC=2 forces the prologue for every layer, CRACKFL_XF_DW=1 the
+        # depthwise path)
+        self.xf_dec = int(os.environ.get("CRACKFL_XF_DEC", "1"))
+        self.xf_dw = os.environ.get("CRACKFL_XF_DW", "0") != "0"
         # partial tiles added straight into the gradient arena with vector reductions: no workspace, no reduction launch
         # (22 launches fewer per step, 1.263 vs 1.287 ms/step; CRACKFL_WGRAD_ATOMIC=0 restores workspace + reduction)
         self.wgrad_atomic = os.environ.get("CRACKFL_WGRAD_ATOMIC", "1") != "0"
@@ -182,7 +192,23 @@ class UNetEngine:
                 oi = l.cout * l.cin
                 add(l.name + ".f", k.offset + 8 * oi, l.cout, 9, l.cin, l.cin, -oi, 1)
                 add(l.name + ".d", k.offset, l.cin, 9, l.cout, 1, oi, l.cin)
+        # depthwise kernels as block-diagonal bf16 tiles (only the diagonals are rewritten each step)
+        self.dw_ops: Dict[str, int] = {}
+        ddescs: List[L.DwDiagDesc] = []
+        if self.conv_impl == "tc" and self.xf_dw:
+            for l in self.spec.layers:
+                if l.op == "sepconv" and l.cin % 32 == 0:
+                    kc = 64 if l.cin % 64 == 0 else 32
+                    dwt = self.spec.tensors[l.tensors[0]]  # (3,3,cin,1)
+                    ddescs.append(L.DwDiagDesc(src_off=dwt.offset, dst_off=off, C=l.cin, kc=kc, flip=0, pad_=0))
+                    self.dw_ops[l.name] = off
+                    off += (l.cin // kc) * 9 * kc * kc
         self.ops_buf = self._new("ops", (off,), torch.bfloat16)
+        self.num_ddesc = len(ddescs)
+        if ddescs:
+            darr = (L.DwDiagDesc * len(ddescs))(*ddescs)
+            self.ddesc_dev = torch.frombuffer(bytearray(bytes(darr)), dtype=torch.uint8).clone().to(self.dev)
+            self._bufs["dw_diag_descs"] = self.ddesc_dev
         arr = (L.PrepDesc * len(descs))(*descs)
         raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).clone()
         self.desc_dev = raw.to(self.dev)
@@ -421,6 +447,9 @@ class UNetEngine:
         # bf16 GEMM operands of this step's weights: next to the im2col / entry kernels on the auxiliary stream
         prog.append((lib.crackfl_weight_prep, (self.arena.data_ptr(), self.ops_buf.data_ptr(), self.desc_dev.data_ptr(),
                                                self.num_desc), "aux"))
+        if self.num_ddesc:
+            prog.append((lib.crackfl_dw_diag_prep, (self.arena.data_ptr(), self.ops_buf.data_ptr(), self.ddesc_dev.data_ptr(),
+                                                    self.num_ddesc), "aux"))
         # entry
         r, rw, c0 = self.H // 2, self.W // 2, self.spec.entry
         if self.entry_tc:
@@ -446,7 +475,11 @@ class UNetEngine:
             # residual 1x1 stride-2 conv: a small GEMM that only depends on the block input; it runs on the auxiliary
             # stream next to the separable-conv chain and is joined before the block tail
             self._gemm(prog, b(xe), res.name + ".f", self.P(res.tensors[1]), 0, b(p + "rs"), B, r // 2, rw // 2, tag="aux")
-            if self.dw_tma:
+            dw_tc = self.conv_impl == "tc" and self.xf_dw and r >= 16 and rw >= 8
+            if dw_tc and sep1.name in self.dw_ops:
+                prog.append((lib.crackfl_conv_tc_xf, (b(xin), self.ops_buf.data_ptr() + 2 * self.dw_ops[sep1.name], 0, 0,
+                                                      b(p + "d1"), 0, B, r, rw, cin, cin, 1, 0, None, 0, 1)))
+            elif self.dw_tma:
                 prog.append((lib.crackfl_dw3x3_tma, (b(xin), self.P(sep1.tensors[0]), 0, None, b(p + "d1"), 0, 0, 0,
                                                      B, r, rw, cin, 0, 0, 0, 0)))
             else:
@@ -455,7 +488,11 @@ class UNetEngine:
                             self._zptr(bn1.name, "stats") if training else 0)
             fuse_dw = fuse and (rw % 4 == 0 or self.dw_tma)
             bn(bn1, b(p + "y1"), Pn, sd, consumer_finalizes=fuse_dw)
-            if self.dw_tma:
+            if dw_tc and sep2.name in self.dw_ops:
+                prog.append((lib.crackfl_conv_tc_xf, (b(p + "y1"), self.ops_buf.data_ptr() + 2 * self.dw_ops[sep2.name], 0, 0,
+                                                      b(p + "d2"), 0, B, r, rw, f, f, 2, self._bnptr(bn1.name),
+                                                      self._fin(bn1, Pn) if fuse_dw else None, 0, 1)))
+            elif self.dw_tma:
                 prog.append((lib.crackfl_dw3x3_tma, (b(p + "y1"), self.P(sep2.tensors[0]), self._bnptr(bn1.name),
                                                      self._fin(bn1, Pn) if fuse_dw else None, b(p + "d2"), 0, 0, 0,
                                                      B, r, rw, f, 1, 0, 0, 0)))
@@ -490,12 +527,23 @@ class UNetEngine:
             sd = self._gemm(prog, b(a0), ct1.name + ".f", self.P(ct1.tensors[1]), 0, b(p + "y1"), B, r, rw,
                             self._zptr(bn1.name, "stats") if training else 0)
             bn(bn1, b(p + "y1"), Pn, sd, consumer_finalizes=fuse)
-            if fuse:
-                prog.append((lib.crackfl_bn_act_fin, (b(p + "y1"), self._fin(bn1, Pn), b(p + "a1"), 0, B, r, rw, f, 1)))
+            if self.conv_impl == "tc" and self.xf_dec and (f >= 64 or self.xf_dec >= 2) and r >= 16 and rw >= 8 and \
+                    (fuse or not training) and self.gemm_stats:
+                # K1: the second conv applies BN1 + ReLU to its input tiles itself (and writes the activation out for its
+                # own weight gradient in training); no bn_act pass, no a1 read
+                stats2 = self._zptr(bn2.name, "stats") if training else 0
+                prog.append((lib.crackfl_conv_tc_xf, (b(p + "y1"), self.op_ptr(ct2.name + ".f"), self.P(ct2.tensors[1]), 0,
+                                                      b(p + "y2"), stats2, B, r, rw, f, f, 2, self._bnptr(bn1.name),
+                                                      self._fin(bn1, Pn) if training else None,
+                                                      b(p + "a1") if training else 0, 0)))
+                sd = training
             else:
-                prog.append((lib.crackfl_bn_act, (b(p + "y1"), self._bnptr(bn1.name), b(p + "a1"), 0, B, r, rw, f, 1)))
-            sd = self._gemm(prog, b(p + "a1"), ct2.name + ".f", self.P(ct2.tensors[1]), 0, b(p + "y2"), B, r, rw,
-                            self._zptr(bn2.name, "stats") if training else 0)
+                if fuse:
+                    prog.append((lib.crackfl_bn_act_fin, (b(p + "y1"), self._fin(bn1, Pn), b(p + "a1"), 0, B, r, rw, f, 1)))
+                else:
+                    prog.append((lib.crackfl_bn_act, (b(p + "y1"), self._bnptr(bn1.name), b(p + "a1"), 0, B, r, rw, f, 1)))
+                sd = self._gemm(prog, b(p + "a1"), ct2.name + ".f", self.P(ct2.tensors[1]), 0, b(p + "y2"), B, r, rw,
+                                self._zptr(bn2.name, "stats") if training else 0)
             bn(bn2, b(p + "y2"), Pn, sd, consumer_finalizes=fuse)
             prog.append((None, None, "join_aux"))
             last = j + 1 == len(self.dec)

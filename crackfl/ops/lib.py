@@ -29,6 +29,10 @@ class BnFin(C.Structure):
                 ("count", f32), ("eps", f32), ("momentum", f32)]
 
 
+class DwDiagDesc(C.Structure):
+    _fields_ = [("src_off", i64), ("dst_off", i64), ("C", i32), ("kc", i32), ("flip", i32), ("pad_", i32)]
+
+
 class WgradRedDesc(C.Structure):
     _fields_ = [("ws_off", i64), ("dw_off", i64), ("s_tap", i64), ("s_ci", i64), ("s_co", i64), ("need", i64),
                 ("groups", i32), ("ntn", i32), ("splits", i32), ("BN", i32), ("cw", i32), ("mblk", i32),
@@ -97,6 +101,8 @@ _SIGS = {
     "crackfl_publish_delta": [vp, vp, vp, i64, vp],
     "crackfl_synth_cracks": [vp, vp, i32, i32, i32, C.c_uint, vp],
     "crackfl_measure_masks": [vp, vp, i32, i32, i32, i32, vp],
+    "crackfl_conv_tc_xf": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, C.POINTER(BnFin), vp, i32, vp],
+    "crackfl_dw_diag_prep": [vp, vp, vp, i32, vp],
     "crackfl_fedagg": [C.POINTER(FedAggParams), i32, vp],
     "crackfl_ipc_export": [vp, vp],
     "crackfl_ipc_open": [vp, C.POINTER(vp)],

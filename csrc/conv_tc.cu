@@ -571,7 +571,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
 
   if (warp == 0) {
     // ---- producer: all lanes walk the schedule (uniform control flow), one elected lane issues
-    uint32_t ia = 0, ib = 0;  // ring positions: halo tiles / weight tiles
+    uint32_t ra_s = 0, ra_ph = 0, rb_s = 0, rb_ph = 0;  // ring positions and phases: halo tiles / weight tiles
     if (a.resident && (int)blockIdx.x < total_tiles) {
       if (elect_one()) {
         mbar_expect_tx(full0, (uint32_t)a.stages * b_bytes);
@@ -587,8 +587,9 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
       const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
       const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
       const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
-      for (int c = 0; c < kchunks; ++c, ++ia) {
-        const uint32_t sa = ia % (uint32_t)a.astages, pha = (ia / (uint32_t)a.astages) & 1u;
+      for (int c = 0; c < kchunks; ++c) {
+        const uint32_t sa = ra_s, pha = ra_ph;  // running ring position (no division on the issue path)
+        if (++ra_s == (uint32_t)a.astages) { ra_s = 0; ra_ph ^= 1u; }
         mbar_wait(emptyA0 + 8u * sa, pha ^ 1u);
         if (elect_one()) {
           mbar_expect_tx(fullA0 + 8u * sa, A_BYTES);
@@ -596,8 +597,9 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
         }
         __syncwarp();
         if (a.resident) continue;
-        for (int t = 0; t < 9; ++t, ++ib) {
-          const uint32_t s = ib % a.stages, ph = (ib / a.stages) & 1u;
+        for (int t = 0; t < 9; ++t) {
+          const uint32_t s = rb_s, ph = rb_ph;
+          if (++rb_s == (uint32_t)a.stages) { rb_s = 0; rb_ph ^= 1u; }
           mbar_wait(empty0 + 8u * s, ph ^ 1u);
           if (elect_one()) {
             mbar_expect_tx(full0 + 8u * s, b_bytes);
@@ -612,7 +614,13 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
     const uint32_t idesc = make_idesc(128, a.BN, 0, 0);
     const uint32_t ahi = desc_hi(HALO_W * row_b, a.layout), bhi = desc_hi(a.sbo, a.layout);
     const bool k64 = a.kc == 64;
-    uint32_t ia = 0, ib = 0, tcount = 0;
+    // Issue path without divisions: ring positions are running counters, the descriptor words of a tap are the words of
+    // the stage plus constants (the first version recomputed stage = counter % depth with two divide sequences per TAP:
+    // ~95 SASS instructions per four MMAs, which made the single issuing warp - not the tensor pipe, not TMA - the
+    // bottleneck of every halo-kernel launch; ncu source page of conv_tc_xf_k, profiles/ncu_xf_issue.md)
+    const uint32_t rb16 = row_b >> 4, bstep16 = b_bytes >> 4;
+    const uint32_t blo_res0 = desc_lo(bring, 16);
+    uint32_t ra_s = 0, ra_ph = 0, rb_s = 0, rb_ph = 0, tcount = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
       const uint32_t as = tcount & 1u, aph = (tcount >> 1) & 1u;
       mbar_wait(tempty0 + 8u * as, aph ^ 1u);
@@ -622,23 +630,28 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
         mbar_wait(full0, 0u);  // the resident weight tiles have landed
         tc_fence_after();
       }
-      for (int c = 0; c < kchunks; ++c, ++ia) {
-        const uint32_t sa = ia % (uint32_t)a.astages, pha = (ia / (uint32_t)a.astages) & 1u;
+      for (int c = 0; c < kchunks; ++c) {
+        const uint32_t sa = ra_s, pha = ra_ph;
+        if (++ra_s == (uint32_t)a.astages) { ra_s = 0; ra_ph ^= 1u; }
         mbar_wait(fullA0 + 8u * sa, pha);
         tc_fence_after();
-        const uint32_t halo = base + sa * A_STAGE;
+        const uint32_t alo_base = desc_lo(base + sa * A_STAGE, 16);
+        const uint32_t blo_c = blo_res0 + (uint32_t)(c * 9) * bstep16;
 #pragma unroll
-        for (int t = 0; t < 9; ++t, ++ib) {
-          const uint32_t s = a.resident ? (uint32_t)(c * 9 + t) : ib % a.stages, ph = (ib / a.stages) & 1u;
+        for (int t = 0; t < 9; ++t) {
+          uint32_t s = 0;
           if (!a.resident) {
+            s = rb_s;
+            const uint32_t ph = rb_ph;
+            if (++rb_s == (uint32_t)a.stages) { rb_s = 0; rb_ph ^= 1u; }
             mbar_wait(full0 + 8u * s, ph);
             tc_fence_after();
           }
           // tap (kh,kw): output pixel (th,tw) reads halo pixel (th+kh, tw+kw).  One 8-row swizzle group = the 8
           // pixels of one tile row, groups HALO_W * row_b bytes apart: the shifted window is still a canonical
           // K-major swizzled operand, it just starts (kh*HALO_W + kw) rows into the halo tile.
-          const uint32_t alo = desc_lo(halo + (uint32_t)((t / 3) * HALO_W + (t % 3)) * row_b, 16);
-          const uint32_t blo = desc_lo(bring + s * b_bytes, 16);
+          const uint32_t alo = alo_base + (uint32_t)((t / 3) * HALO_W + (t % 3)) * rb16;
+          const uint32_t blo = a.resident ? blo_c + (uint32_t)t * bstep16 : blo_res0 + s * bstep16;
           const uint32_t first = (c > 0 || t > 0) ? 1u : 0u;
           if (elect_one()) {
             umma_f16_w(tacc, alo, ahi, blo, bhi, idesc, first);
@@ -835,13 +848,15 @@ struct ConvArgsX {
 // With `diag` the weight tiles are the 64x64 (32x32) block-diagonal expansion of a depthwise 3x3 kernel, so the depthwise
 // half of a SeparableConv2D (client_fit_model.py:109,113) runs on the tensor cores: 36 MMAs of 128x64x16 per 128-pixel
 // tile (~0.6 us) against ~0.9 us of HBM time for the tile, instead of an issue-bound CUDA-core stencil.
-// One CTA per SM (448 threads), everything else as in conv_tc_fwd_v3_k below.
+// One CTA per SM (576 threads), everything else as in conv_tc_fwd_v3_k below.
 //
 // "resident" mode (small layers: 9 * Cin * N * 2 bytes <= ~80 KB, one n-tile): the weight tiles are loaded ONCE per CTA
 // onto a single barrier; per tile the producer only streams halo tiles and the issuing thread fires its 9 * kc/16 MMAs
 // back to back (no per-tap barrier round trip, no re-streaming of the weights from L2 for every 128-pixel tile, which
 // for N = 32 was more traffic than the activations).  kc = 32 (Cin = 32) uses the SWIZZLE_64B flavour of the same trick.
-__global__ void __launch_bounds__(64 + EPI_THREADS + 128, 1) conv_tc_xf_k(const __grid_constant__ CUtensorMap tmA,
+constexpr int XF_WARPS = 8;
+constexpr int XF_THREADS = XF_WARPS * 32;
+__global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k(const __grid_constant__ CUtensorMap tmA,
                                                         const __grid_constant__ CUtensorMap tmB,
                                                         const __grid_constant__ CUtensorMap tmY, const ConvArgsX a) {
   extern __shared__ uint8_t smem_raw[];
@@ -879,7 +894,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + 128, 1) conv_tc_xf_k(const 
     for (int s = 0; s < a.astages; ++s) {
       mbar_init(fullA0 + 8u * s, 1);
       mbar_init(emptyA0 + 8u * s, 1);
-      mbar_init(xfA0 + 8u * s, 4);  // one arrival per transform warp
+      mbar_init(xfA0 + 8u * s, XF_WARPS);  // one arrival per transform warp
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull0 + 8u * s, 1);
@@ -925,7 +940,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + 128, 1) conv_tc_xf_k(const 
 
   if (warp == 0) {
     // ---- producer: all lanes walk the schedule (uniform control flow), one elected lane issues
-    uint32_t ia = 0, ib = 0;  // ring positions: halo tiles / weight tiles
+    uint32_t ra_s = 0, ra_ph = 0, rb_s = 0, rb_ph = 0;  // ring positions and phases: halo tiles / weight tiles
     if (a.resident && t_first < total_tiles) {
       if (elect_one()) {
         mbar_expect_tx(full0, (uint32_t)a.stages * b_bytes);
@@ -942,8 +957,9 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + 128, 1) conv_tc_xf_k(const 
       const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
       const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
       const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
-      for (int c = 0; c < kchunks; ++c, ++ia) {
-        const uint32_t sa = ia % (uint32_t)a.astages, pha = (ia / (uint32_t)a.astages) & 1u;
+      for (int c = 0; c < kchunks; ++c) {
+        const uint32_t sa = ra_s, pha = ra_ph;  // running ring position (no division on the issue path)
+        if (++ra_s == (uint32_t)a.astages) { ra_s = 0; ra_ph ^= 1u; }
         mbar_wait(emptyA0 + 8u * sa, pha ^ 1u);
         if (elect_one()) {
           mbar_expect_tx(fullA0 + 8u * sa, A_BYTES);
@@ -951,8 +967,9 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + 128, 1) conv_tc_xf_k(const 
         }
         __syncwarp();
         if (a.resident) continue;
-        for (int t = 0; t < 9; ++t, ++ib) {
-          const uint32_t s = ib % a.stages, ph = (ib / a.stages) & 1u;
+        for (int t = 0; t < 9; ++t) {
+          const uint32_t s = rb_s, ph = rb_ph;
+          if (++rb_s == (uint32_t)a.stages) { rb_s = 0; rb_ph ^= 1u; }
           mbar_wait(empty0 + 8u * s, ph ^ 1u);
           if (elect_one()) {
             mbar_expect_tx(full0 + 8u * s, b_bytes);
@@ -967,7 +984,13 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + 128, 1) conv_tc_xf_k(const 
     const uint32_t idesc = make_idesc(128, a.BN, 0, 0);
     const uint32_t ahi = desc_hi(HALO_W * row_b, a.layout), bhi = desc_hi(a.sbo, a.layout);
     const bool k64 = a.kc == 64;
-    uint32_t ia = 0, ib = 0, tcount = 0;
+    // Issue path without divisions: ring positions are running counters, the descriptor words of a tap are the words of
+    // the stage plus constants (the first version recomputed stage = counter % depth with two divide sequences per TAP:
+    // ~95 SASS instructions per four MMAs, which made the single issuing warp - not the tensor pipe, not TMA - the
+    // bottleneck of every halo-kernel launch; ncu source page of conv_tc_xf_k, profiles/ncu_xf_issue.md)
+    const uint32_t rb16 = row_b >> 4, bstep16 = b_bytes >> 4;
+    const uint32_t blo_res0 = desc_lo(bring, 16);
+    uint32_t ra_s = 0, ra_ph = 0, rb_s = 0, rb_ph = 0, tcount = 0;
     for (int tile = t_first; tile < total_tiles; tile += t_step, ++tcount) {
       const uint32_t as = tcount & 1u, aph = (tcount >> 1) & 1u;
       mbar_wait(tempty0 + 8u * as, aph ^ 1u);
@@ -977,23 +1000,28 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + 128, 1) conv_tc_xf_k(const 
         mbar_wait(full0, 0u);  // the resident weight tiles have landed
         tc_fence_after();
       }
-      for (int c = 0; c < kchunks; ++c, ++ia) {
-        const uint32_t sa = ia % (uint32_t)a.astages, pha = (ia / (uint32_t)a.astages) & 1u;
+      for (int c = 0; c < kchunks; ++c) {
+        const uint32_t sa = ra_s, pha = ra_ph;
+        if (++ra_s == (uint32_t)a.astages) { ra_s = 0; ra_ph ^= 1u; }
         mbar_wait(xfA0 + 8u * sa, pha);  // the transform warps have rewritten the tile
         tc_fence_after();
-        const uint32_t halo = base + sa * A_STAGE;
+        const uint32_t alo_base = desc_lo(base + sa * A_STAGE, 16);
+        const uint32_t blo_c = blo_res0 + (uint32_t)(c * 9) * bstep16;
 #pragma unroll
-        for (int t = 0; t < 9; ++t, ++ib) {
-          const uint32_t s = a.resident ? (uint32_t)(c * 9 + t) : ib % a.stages, ph = (ib / a.stages) & 1u;
+        for (int t = 0; t < 9; ++t) {
+          uint32_t s = 0;
           if (!a.resident) {
+            s = rb_s;
+            const uint32_t ph = rb_ph;
+            if (++rb_s == (uint32_t)a.stages) { rb_s = 0; rb_ph ^= 1u; }
             mbar_wait(full0 + 8u * s, ph);
             tc_fence_after();
           }
           // tap (kh,kw): output pixel (th,tw) reads halo pixel (th+kh, tw+kw).  One 8-row swizzle group = the 8
           // pixels of one tile row, groups HALO_W * row_b bytes apart: the shifted window is still a canonical
           // K-major swizzled operand, it just starts (kh*HALO_W + kw) rows into the halo tile.
-          const uint32_t alo = desc_lo(halo + (uint32_t)((t / 3) * HALO_W + (t % 3)) * row_b, 16);
-          const uint32_t blo = desc_lo(bring + s * b_bytes, 16);
+          const uint32_t alo = alo_base + (uint32_t)((t / 3) * HALO_W + (t % 3)) * rb16;
+          const uint32_t blo = a.resident ? blo_c + (uint32_t)t * bstep16 : blo_res0 + s * bstep16;
           const uint32_t first = (c > 0 || t > 0) ? 1u : 0u;
           if (elect_one()) {
             umma_f16_w(tacc, alo, ahi, blo, bhi, idesc, first);
@@ -1013,51 +1041,93 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + 128, 1) conv_tc_xf_k(const 
       __syncwarp();
     }
   } else if (warp >= 2 + EPI_WARPS) {
-    // ---- transform warps: halo tile in shared memory -> activation, in place, between TMA and MMA
-    const int xt = threadIdx.x - (64 + EPI_THREADS);  // 0..127
+    // ---- transform warps: halo tile in shared memory -> activation, in place, between TMA and MMA.
+    // Thread = one 16-byte chunk COLUMN of the tile (j) and every (XF_THREADS / cpr)-th pixel row: the rows a thread
+    // visits are congruent modulo the swizzle period, so the logical channel group behind its physical chunk slot - and
+    // with it the 8 scale / shift values - is fixed for the whole kernel and lives in registers.  (First version: 128
+    // threads, chunk index and table look-up per element; one latency-bound warp per scheduler made the stage 4 us per
+    // tile and the kernel 1.6x slower than the CUDA-core stencil it replaces.)
+    const int xt = threadIdx.x - (64 + EPI_THREADS);  // 0..XF_THREADS-1
     const int lane_ = threadIdx.x & 31;
     const int cpr = a.kc >> 3;                        // 16-byte chunks per halo pixel (8 or 4)
-    const uint32_t swz_mask = a.kc == 64 ? 7u : 3u;   // SWIZZLE_128B / SWIZZLE_64B: chunk index ^= address bits [7..]
-    uint32_t ia = 0;
+    const int j = xt & (cpr - 1), prow = xt / cpr;    // chunk column, first row
+    const int rstep = XF_THREADS / cpr;               // 32 (kc 64) or 64 (kc 32) rows per pass
+    // SWIZZLE_128B: slot j of row p holds chunk j ^ (p & 7); SWIZZLE_64B (64-byte rows): j ^ ((p >> 1) & 3)
+    const int lch = a.kc == 64 ? (j ^ (prow & 7)) : (j ^ ((prow >> 1) & 3));
+    const uint32_t toff = (uint32_t)prow * row_b + (uint32_t)j * 16u;
+    // per-thread row table, fixed for the whole kernel: halo row / column of the k-th row this thread visits, whether it
+    // exists (p < 180) and whether it is an interior (= output) pixel; the tile loop only adds the tile origin
+    constexpr int XF_IT = 6;  // ceil(180 / 32); the 64-row passes of the 32-channel flavour need 3
+    int hrk[XF_IT], hck[XF_IT];
+    uint32_t live = 0, inter = 0;
+#pragma unroll
+    for (int k = 0; k < XF_IT; ++k) {
+      const int p = prow + k * rstep;
+      hrk[k] = p / (int)HALO_W; hck[k] = p - hrk[k] * (int)HALO_W;
+      if (p < 180) live |= 1u << k;
+      if (p < 180 && hrk[k] >= 1 && hrk[k] <= a.g.TH && hck[k] >= 1 && hck[k] <= a.g.TW) inter |= 1u << k;
+    }
+    const uint32_t kstride = (uint32_t)rstep * row_b;
+    const long pix_c = (long)a.Cin;
+    uint32_t ra_s = 0, ra_ph = 0;
     for (int tile = t_first; tile < total_tiles; tile += t_step) {
       int tm_ = tile % a.n_tiles_m;
       const int n0 = a.diag ? my_chunk * a.kc : (tile / a.n_tiles_m) * a.BN;
       const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
       const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
-      const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
+      const int w0 = tw_i * a.g.TW - 1, h0 = th_i * a.g.TH - 1, b0 = tm_ * a.g.TB;  // origin of the HALO tile
       const bool do_side = a.side != nullptr && (a.diag || n0 == 0);
-      for (int c = 0; c < kchunks; ++c, ++ia) {
-        const uint32_t sa = ia % (uint32_t)a.astages, pha = (ia / (uint32_t)a.astages) & 1u;
-        const int cbase = (a.diag ? my_chunk : c) * a.kc;
+      // a tile whose halo lies completely inside the image needs no per-pixel test (all but the border tiles)
+      const bool all_in = h0 >= 0 && h0 + 18 <= a.H && w0 >= 0 && w0 + 10 <= a.W;
+      for (int c = 0; c < kchunks; ++c) {
+        const uint32_t sa = ra_s, pha = ra_ph;
+        if (++ra_s == (uint32_t)a.astages) { ra_s = 0; ra_ph ^= 1u; }
+        const int cbase = (a.diag ? my_chunk : c) * a.kc + lch * 8;
+        f2_t sc2[4], sh2[4];
+        if (a.xmode == 2) {
+          const float4 s0 = *reinterpret_cast<const float4*>(xf_tab + cbase), s1 = *reinterpret_cast<const float4*>(xf_tab + cbase + 4);
+          const float4 t0 = *reinterpret_cast<const float4*>(xf_tab + a.Cin + cbase);
+          const float4 t1 = *reinterpret_cast<const float4*>(xf_tab + a.Cin + cbase + 4);
+          sc2[0] = pk2(s0.x, s0.y); sc2[1] = pk2(s0.z, s0.w); sc2[2] = pk2(s1.x, s1.y); sc2[3] = pk2(s1.z, s1.w);
+          sh2[0] = pk2(t0.x, t0.y); sh2[1] = pk2(t0.z, t0.w); sh2[2] = pk2(t1.x, t1.y); sh2[3] = pk2(t1.z, t1.w);
+        }
+        __nv_bfloat16* sbase = a.side + (((long)b0 * a.H + h0) * a.W + w0) * pix_c + cbase;  // halo pixel (0,0), this channel group
         mbar_wait(fullA0 + 8u * sa, pha);
-        const uint32_t halo = base + sa * A_STAGE;
-        for (int idx = xt; idx < 180 * cpr; idx += 128) {
-          const int p = idx / cpr, j = idx - p * cpr;
-          const uint32_t addr = halo + (uint32_t)p * row_b + (uint32_t)j * 16u;
-          const int lch = (int)((uint32_t)j ^ ((addr >> 7) & swz_mask));  // logical chunk held at this physical slot
-          const int hr = p / (int)HALO_W, hc = p - hr * (int)HALO_W;
-          const int ih = h0 - 1 + hr, iw = w0 - 1 + hc;
-          const bool inside = ih >= 0 && ih < a.H && iw >= 0 && iw < a.W && b0 < a.B;
-          uint32_t v0, v1, v2, v3;
-          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v0), "=r"(v1), "=r"(v2), "=r"(v3) : "r"(addr));
-          if (a.xmode == 1) {
-            v0 = relu_bf2(v0); v1 = relu_bf2(v1); v2 = relu_bf2(v2); v3 = relu_bf2(v3);  // zero fill stays zero
-          } else if (inside) {
-            const float* sc = xf_tab + cbase + lch * 8;
-            const float* sh = sc + a.Cin;
-            const float4 s0 = *reinterpret_cast<const float4*>(sc), s1 = *reinterpret_cast<const float4*>(sc + 4);
-            const float4 h0_ = *reinterpret_cast<const float4*>(sh), h1_ = *reinterpret_cast<const float4*>(sh + 4);
-            v0 = f2_to_bf2_relu(ffma2(bf2_to_f2(v0), pk2(s0.x, s0.y), pk2(h0_.x, h0_.y)));
-            v1 = f2_to_bf2_relu(ffma2(bf2_to_f2(v1), pk2(s0.z, s0.w), pk2(h0_.z, h0_.w)));
-            v2 = f2_to_bf2_relu(ffma2(bf2_to_f2(v2), pk2(s1.x, s1.y), pk2(h1_.x, h1_.y)));
-            v3 = f2_to_bf2_relu(ffma2(bf2_to_f2(v3), pk2(s1.z, s1.w), pk2(h1_.z, h1_.w)));
-          } else {
-            v0 = v1 = v2 = v3 = 0u;  // "same" padding pads the activation: relu(shift) must not leak in
+        if (a.xmode == 3) {
+          __syncwarp();
+          if (lane_ == 0) mbar_arrive(xfA0 + 8u * sa);
+          continue;
+        }
+        const uint32_t tbase = base + sa * A_STAGE + toff;
+        uint32_t v[XF_IT][4];
+#pragma unroll
+        for (int k = 0; k < XF_IT; ++k)
+          if (live >> k & 1u)
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[k][0]), "=r"(v[k][1]), "=r"(v[k][2]), "=r"(v[k][3])
+                         : "r"(tbase + (uint32_t)k * kstride));
+#pragma unroll
+        for (int k = 0; k < XF_IT; ++k) {
+          if (!(live >> k & 1u)) continue;
+          bool inside = true;
+          if (!all_in) {
+            const int ih = h0 + hrk[k], iw = w0 + hck[k];
+            inside = ih >= 0 && ih < a.H && iw >= 0 && iw < a.W;
           }
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v0), "r"(v1), "r"(v2), "r"(v3) : "memory");
-          if (do_side && inside && hr >= 1 && hr <= a.g.TH && hc >= 1 && hc <= a.g.TW) {
-            uint4 o; o.x = v0; o.y = v1; o.z = v2; o.w = v3;
-            ck::stg16(a.side + (((long)b0 * a.H + ih) * a.W + iw) * a.Cin + cbase + lch * 8, o);
+          if (a.xmode == 1) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) v[k][e] = relu_bf2(v[k][e]);  // zero fill stays zero
+          } else if (inside) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) v[k][e] = f2_to_bf2_relu(ffma2(bf2_to_f2(v[k][e]), sc2[e], sh2[e]));
+          } else {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) v[k][e] = 0u;  // "same" padding pads the activation: relu(shift) must not leak in
+          }
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(tbase + (uint32_t)k * kstride), "r"(v[k][0]), "r"(v[k][1]),
+                       "r"(v[k][2]), "r"(v[k][3]) : "memory");
+          if (do_side && inside && (inter >> k & 1u)) {
+            uint4 o; o.x = v[k][0]; o.y = v[k][1]; o.z = v[k][2]; o.w = v[k][3];
+            ck::stg16(sbase + ((long)hrk[k] * a.W + hck[k]) * pix_c, o);
           }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the MMA's reads
@@ -1851,6 +1921,104 @@ v2_path:
   int grid = 2 * g_num_sms;
   if (grid > total) grid = total;
   ck::launch(conv_tc_fwd_v2_k, grid, 64 + EPI_THREADS, smem, st, tmA, tmB, tmY, a);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+// 3x3 conv (or, with diag != 0, depthwise 3x3 through block-diagonal weight tiles) whose INPUT is activated on the fly
+// inside the kernel: xmode 1 = relu(X), xmode 2 = relu(scale * X + shift) with scale/shift from `bn` ([scale C | shift C])
+// or, when fin != NULL, derived from the BN statistics (block 0 then also publishes the table and the moving
+// statistics, like the *_fin elementwise launchers).  side != NULL: the activated input is also written out (the weight
+// gradient of this layer needs it).  diag: Wk is the [(C/kc)*9*kc][kc] matrix written by crackfl_dw_diag_prep, N == Cin.
+int crackfl_conv_tc_xf(const void* X, const void* Wk, const float* bias, const void* add, void* Y, float* stats, int B, int H,
+                       int W, int Cin, int N, int xmode, const float* bn, const crackfl_bn_fin* fin, void* side, int diag,
+                       cudaStream_t st) {
+  if (Cin % 32 || N % 32 || H < 16 || W < 8 || xmode < 1 || xmode > 3) return (int)cudaErrorInvalidValue;  // 3: profiling aid, tiles pass through untouched
+  if (xmode == 2 && !bn && !fin) return (int)cudaErrorInvalidValue;
+  if (diag && N != Cin) return (int)cudaErrorInvalidValue;
+  const int kc = (Cin % 64 == 0) ? 64 : 32;
+  if (Cin % kc) return (int)cudaErrorInvalidValue;
+  ConvArgsX a;
+  memset(&a, 0, sizeof(a));
+  a.bias = bias; a.add = (const __nv_bfloat16*)add; a.stats = stats;
+  a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.N = N; a.taps = 9;
+  a.BN = diag ? kc : (N > 128 ? 128 : N);
+  if (N % a.BN) return (int)cudaErrorInvalidValue;
+  a.kc = kc; a.layout = kc == 64 ? 2u : 4u; a.sbo = kc == 64 ? 1024u : 512u;
+  a.sub_w = (a.BN % 64 == 0) ? 64 : 32;
+  a.dbg_noflush = dbg_noflush();
+  a.xmode = xmode; a.diag = diag ? 1 : 0; a.bn = bn; a.side = (__nv_bfloat16*)side;
+  if (fin) a.fin = *fin;
+  a.a_bytes = 180u * (uint32_t)kc * 2u;
+  a.a_stage = (a.a_bytes + 1023u) & ~1023u;
+  a.g.TW = 8; a.g.TH = 16; a.g.TB = 1;
+  a.g.tiles_w = (W + 7) / 8; a.g.tiles_h = (H + 15) / 16; a.g.tiles_b = B;
+  a.n_tiles_m = a.g.tiles_w * a.g.tiles_h * a.g.tiles_b;
+  a.n_tiles_n = diag ? 1 : N / a.BN;
+  const uint32_t b_bytes = (uint32_t)a.BN * (uint32_t)kc * 2u;
+  const uint32_t out_bytes = 2u * 128u * (uint32_t)a.BN * 2u;
+  const uint32_t fixed = out_bytes + 12288u;  // staging + barriers + statistics scratch + bias + scale/shift table + slack
+  const uint32_t lim1 = 220u * 1024u;
+  const uint32_t wbytes = diag ? 9u * b_bytes : 9u * (uint32_t)Cin * (uint32_t)a.BN * 2u;
+  const bool resident = diag || (N == a.BN && wbytes + fixed + 2u * a.a_stage <= lim1);
+  a.resident = resident ? 1 : 0;
+  int stages;
+  if (resident) {
+    stages = diag ? 9 : 9 * (Cin / kc);
+    a.astages = (int)((lim1 - wbytes - fixed) / a.a_stage);
+    if (a.astages > 4) a.astages = 4;
+    {
+      static int dbg_ast = -1;  // tuning knob
+      if (dbg_ast < 0) { const char* e = getenv("CRACKFL_XF_ASTAGES"); dbg_ast = e ? atoi(e) : 0; }
+      if (dbg_ast >= 1 && dbg_ast <= a.astages) a.astages = dbg_ast;
+    }
+    if (a.astages < 1) return (int)cudaErrorInvalidValue;
+  } else {
+    if (kc != 64) return (int)cudaErrorInvalidValue;  // the streaming variant is only set up for 64-channel chunks
+    a.astages = 3;
+    stages = (int)((lim1 - fixed - 3u * a.a_stage) / b_bytes);
+    if (stages > 9) stages = 9;
+    if (stages < 2) return (int)cudaErrorInvalidValue;
+  }
+  a.stages = stages;
+  const size_t smem = (size_t)a.astages * a.a_stage + (size_t)stages * b_bytes + out_bytes + 1024 + 512 + 8192 + 2048;
+  CUtensorMap tmA, tmB, tmY;
+  const int dA[4] = {Cin, W, H, B}, bA[4] = {kc, 10, 18, 1};
+  int rc = get_map(X, 4, dA, bA, kc * 2, &tmA);
+  if (rc) return rc;
+  if (diag) {
+    const int dB[2] = {kc, (Cin / kc) * 9 * kc}, bB[2] = {kc, kc};
+    rc = get_map(Wk, 2, dB, bB, kc * 2, &tmB);
+  } else {
+    const int dB[2] = {9 * Cin, N}, bB[2] = {kc, a.BN};
+    rc = get_map(Wk, 2, dB, bB, kc * 2, &tmB);
+  }
+  if (rc) return rc;
+  const int dY[4] = {N, W, H, B}, bY[4] = {a.sub_w, 8, 16, 1};
+  rc = get_map(Y, 4, dY, bY, a.sub_w * 2, &tmY);
+  if (rc) return rc;
+  static bool attrx = false;
+  if (!attrx) {
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_xf_k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return (int)e;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+    attrx = true;
+  }
+  int grid = g_num_sms;
+  if (diag) {
+    const int nch = Cin / kc;
+    const int total = a.n_tiles_m * nch;
+    if (grid > total) grid = total;
+    grid = grid / nch * nch;  // every CTA keeps one channel chunk: the grid is a multiple of the chunk count
+    if (grid < nch) grid = nch;
+  } else {
+    const int total = a.n_tiles_m * a.n_tiles_n;
+    if (grid > total) grid = total;
+  }
+  ck::launch(conv_tc_xf_k, grid, 64 + EPI_THREADS + XF_THREADS, smem, st, tmA, tmB, tmY, a);
   CK_LAUNCH_CHECK();
   return 0;
 }

@@ -120,6 +120,22 @@ __global__ void __launch_bounds__(256) publish_delta_k(const float* __restrict__
     out[i] = __float2bfloat16_rn(local[i] - global[i]);
 }
 
+// Depthwise 3x3 kernels (Keras (3,3,C,1), fp32) -> block-diagonal bf16 weight tiles for the tensor-core depthwise path
+// (conv_tc_xf_k, diag): out[((chunk*9 + t)*kc + n)*kc + k] = (n == k) ? w[tp*C + chunk*kc + n] : 0, tp = flip ? 8-t : t.
+// Only the diagonal is written; the buffer is zeroed once when it is allocated.
+__global__ void __launch_bounds__(256) dw_diag_prep_k(const float* __restrict__ arena, __nv_bfloat16* __restrict__ ops,
+                                                      const crackfl_dw_diag_desc* __restrict__ descs) {
+  ck::pdl_enter();
+  const crackfl_dw_diag_desc d = descs[blockIdx.y];
+  const int total = 9 * d.C;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int t = i / d.C, c = i - t * d.C;
+    const int chunk = c / d.kc, n = c - chunk * d.kc;
+    const int tp = d.flip ? 8 - t : t;
+    ops[d.dst_off + ((long)(chunk * 9 + t) * d.kc + n) * d.kc + n] = __float2bfloat16_rn(arena[d.src_off + (long)tp * d.C + c]);
+  }
+}
+
 __global__ void accum_k(float* __restrict__ total, const float* __restrict__ step, int n) {
   ck::pdl_enter();
   if (threadIdx.x < n) total[threadIdx.x] += step[threadIdx.x];
@@ -184,6 +200,14 @@ int crackfl_weight_prep(const float* arena, void* ops, const crackfl_prep_desc* 
   if (gx < 0) { const char* e = getenv("CRACKFL_PREP_GRID_X"); gx = e ? atoi(e) : 48; if (gx < 1) gx = 48; }  // measured: 48: 1.279, 96: 1.282, 192: 1.286 ms/step (it overlaps the entry kernels on the auxiliary stream)
   dim3 grid(gx, num_desc);
   ck::launch(weight_prep_k, grid, 256, 0, st, arena, (__nv_bfloat16*)ops, descs_dev);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_dw_diag_prep(const float* arena, void* ops, const crackfl_dw_diag_desc* descs_dev, int num_desc, cudaStream_t st) {
+  if (num_desc <= 0) return 0;
+  dim3 grid(9, num_desc);
+  ck::launch(dw_diag_prep_k, grid, 256, 0, st, arena, (__nv_bfloat16*)ops, descs_dev);
   CK_LAUNCH_CHECK();
   return 0;
 }

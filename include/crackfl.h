@@ -140,6 +140,20 @@ int crackfl_head_fwd_bwd(const void* s, const float* w, const float* bias, const
                          cudaStream_t stream);
 
 /* ---- GEMM-shaped convolutions ---------------------------------------------------------------- */
+/* 3x3 conv whose input is activated inside the kernel (K1: ReLU -> Conv2DTranspose -> BN of client_fit_model.py:128-134
+ * without a BN-apply pass): xmode 1 = relu(X), 2 = relu(scale*X + shift) with scale/shift from bn[2*Cin] or derived from
+ * the statistics in *fin (block 0 publishes table + moving statistics).  side_or_null: the activated input is also
+ * written (B,H,W,Cin).  diag != 0: depthwise 3x3 on the tensor cores (client_fit_model.py:109,113), Wk = block-diagonal
+ * tiles from crackfl_dw_diag_prep, N == Cin.  H >= 16, W >= 8. */
+int crackfl_conv_tc_xf(const void* X, const void* Wk, const float* bias_or_null, const void* add_or_null, void* Y,
+                       float* stats_or_null, int B, int H, int W, int Cin, int N, int xmode, const float* bn_or_null,
+                       const crackfl_bn_fin* fin_or_null, void* side_or_null, int diag, cudaStream_t stream);
+typedef struct {
+  long src_off, dst_off; /* element offsets: depthwise kernel (3,3,C,1) in the fp32 arena / tiles in the bf16 operand buffer */
+  int C, kc, flip, pad_;  /* kc = 64 (C % 64 == 0) or 32; flip: taps reversed (input-gradient form) */
+} crackfl_dw_diag_desc;
+int crackfl_dw_diag_prep(const float* arena, void* ops, const crackfl_dw_diag_desc* descs_dev, int num_desc, cudaStream_t stream);
+
 /* CUDA-core implicit GEMM (cross-check + odd shapes).  Wk[N][taps*Cin] bf16, taps in {1,9}. */
 int crackfl_conv_simt_fwd(const void* X, const void* Wk, const float* bias_or_null, const void* add_or_null, void* Y, int B,
                           int H, int W, int Cin, int N, int taps, cudaStream_t stream);

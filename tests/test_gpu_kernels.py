@@ -502,3 +502,88 @@ def test_local_trainer_b200_backend_host_batches():
     noise = float(np.linalg.norm(wd - wd2) / np.linalg.norm(wd))
     diff = float(np.linalg.norm(wh - wd) / np.linalg.norm(wd))
     assert diff < 3 * noise + 1e-3, (diff, noise)
+
+
+@pytest.mark.parametrize("B,H,W,cin,N,xmode", [(2, 16, 16, 64, 64, 2), (2, 16, 16, 256, 256, 2), (2, 32, 24, 32, 32, 2),
+                                                (1, 20, 12, 128, 128, 2), (2, 16, 8, 64, 64, 1), (3, 48, 40, 64, 32, 2)])
+def test_conv_xf_bn_relu_prologue(B, H, W, cin, N, xmode):
+    """K1: 3x3 conv whose input is activated inside the kernel == conv(relu(scale*x+shift)) with ZERO padding of the
+    activation, and the side output == that activation (ref: client_fit_model.py:128-134)."""
+    L, lib = _lib()
+    torch.manual_seed(0)
+    x = torch.randn(B, H, W, cin, device="cuda").bfloat16()
+    wk = (torch.randn(N, 9 * cin, device="cuda") / np.sqrt(9 * cin)).bfloat16()
+    bias = torch.randn(N, device="cuda")
+    scale = torch.rand(cin, device="cuda") + 0.5; shift = torch.randn(cin, device="cuda") * 0.5 + 0.3
+    bn = torch.cat([scale, shift]).contiguous()
+    y = torch.zeros(B, H, W, N, device="cuda", dtype=torch.bfloat16)
+    side = torch.zeros(B, H, W, cin, device="cuda", dtype=torch.bfloat16)
+    stats = torch.zeros(2 * N, device="cuda")
+    L.check(lib.crackfl_conv_tc_xf(x.data_ptr(), wk.data_ptr(), bias.data_ptr(), 0, y.data_ptr(), stats.data_ptr(), B, H, W, cin,
+                                   N, xmode, bn.data_ptr(), None, side.data_ptr(), 0, _st()))
+    torch.cuda.synchronize()
+    act = torch.relu(x.float() * scale + shift) if xmode == 2 else torch.relu(x.float())
+    act = act.bfloat16().float()
+    assert float((side.float() - act).abs().max()) <= 2 ** -7 * float(act.abs().max())
+    ref = _conv_ref(act, wk.float(), bias, 9, cin)
+    err = float((y.float() - ref).norm() / ref.norm())
+    assert err < 1e-2, err
+    yf = y.float().reshape(-1, N)
+    assert torch.allclose(stats[:N], yf.sum(0), rtol=2e-2, atol=0.5)
+
+
+def test_conv_xf_finalize_from_statistics():
+    """The same prologue with scale/shift derived in the kernel from sum / sum-of-squares (finalize folded in): block 0
+    publishes the table and updates the moving statistics like crackfl_bn_finalize."""
+    L, lib = _lib()
+    torch.manual_seed(1)
+    B, H, W, cin, N = 2, 16, 16, 64, 64
+    x = torch.randn(B, H, W, cin, device="cuda").bfloat16()
+    wk = (torch.randn(N, 9 * cin, device="cuda") / np.sqrt(9 * cin)).bfloat16()
+    xf = x.float().reshape(-1, cin)
+    P = float(xf.shape[0])
+    st_in = torch.cat([xf.sum(0), (xf * xf).sum(0)]).contiguous()
+    gamma = torch.rand(cin, device="cuda") + 0.5; beta = torch.randn(cin, device="cuda") * 0.2
+    rm = torch.zeros(cin, device="cuda"); rv = torch.ones(cin, device="cuda"); bn_out = torch.zeros(4 * cin, device="cuda")
+    fin = L.BnFin(stats=st_in.data_ptr(), gamma=gamma.data_ptr(), beta=beta.data_ptr(), run_mean=rm.data_ptr(),
+                  run_var=rv.data_ptr(), bn_out=bn_out.data_ptr(), count=P, eps=1e-3, momentum=0.99)
+    y = torch.zeros(B, H, W, N, device="cuda", dtype=torch.bfloat16)
+    L.check(lib.crackfl_conv_tc_xf(x.data_ptr(), wk.data_ptr(), 0, 0, y.data_ptr(), 0, B, H, W, cin, N, 2, 0, C.byref(fin), 0,
+                                   0, _st()))
+    torch.cuda.synchronize()
+    mean = xf.mean(0); var = xf.var(0, unbiased=False)
+    scale = gamma * torch.rsqrt(var + 1e-3); shift = beta - mean * scale
+    assert torch.allclose(bn_out[:cin], scale, rtol=1e-4, atol=1e-5) and torch.allclose(bn_out[cin:2 * cin], shift, rtol=1e-4, atol=1e-5)
+    assert torch.allclose(rm, 0.01 * mean, rtol=1e-3, atol=1e-6)
+    act = torch.relu(x.float() * scale + shift).bfloat16().float()
+    ref = _conv_ref(act, wk.float(), None, 9, cin)
+    assert float((y.float() - ref).norm() / ref.norm()) < 1e-2
+
+
+@pytest.mark.parametrize("B,H,W,Cc,xmode,flip", [(2, 16, 16, 64, 1, 0), (2, 32, 24, 32, 1, 0), (1, 20, 12, 128, 2, 0),
+                                                  (2, 16, 16, 256, 2, 0), (2, 16, 16, 64, 1, 1)])
+def test_depthwise_on_tensor_cores(B, H, W, Cc, xmode, flip):
+    """Depthwise 3x3 (the first half of SeparableConv2D, client_fit_model.py:109,113) as the halo kernel with
+    block-diagonal weight tiles: == F.conv2d(groups=C) of the activated input (bf16 weights)."""
+    L, lib = _lib()
+    torch.manual_seed(2)
+    x = torch.randn(B, H, W, Cc, device="cuda").bfloat16()
+    w = torch.randn(9, Cc, device="cuda")          # Keras (3,3,C,1) flattened
+    kc = 64 if Cc % 64 == 0 else 32
+    ops = torch.zeros((Cc // kc) * 9 * kc * kc, device="cuda", dtype=torch.bfloat16)
+    d = L.DwDiagDesc(src_off=0, dst_off=0, C=Cc, kc=kc, flip=flip, pad_=0)
+    desc = torch.frombuffer(bytearray(bytes(d)), dtype=torch.uint8).clone().cuda()
+    L.check(lib.crackfl_dw_diag_prep(w.data_ptr(), ops.data_ptr(), desc.data_ptr(), 1, _st()))
+    scale = torch.rand(Cc, device="cuda") + 0.5; shift = torch.randn(Cc, device="cuda") * 0.5
+    bn = torch.cat([scale, shift]).contiguous()
+    y = torch.zeros(B, H, W, Cc, device="cuda", dtype=torch.bfloat16)
+    L.check(lib.crackfl_conv_tc_xf(x.data_ptr(), ops.data_ptr(), 0, 0, y.data_ptr(), 0, B, H, W, Cc, Cc, xmode, bn.data_ptr(),
+                                   None, 0, 1, _st()))
+    torch.cuda.synchronize()
+    act = (torch.relu(x.float() * scale + shift) if xmode == 2 else torch.relu(x.float())).bfloat16().float()
+    wq = w.bfloat16().float()
+    if flip:
+        wq = wq.flip(0)
+    ref = F.conv2d(act.permute(0, 3, 1, 2), wq.reshape(3, 3, Cc).permute(2, 0, 1)[:, None], padding=1, groups=Cc).permute(0, 2, 3, 1)
+    err = float((y.float() - ref).norm() / ref.norm())
+    assert err < 1e-2, err
