@@ -53,7 +53,24 @@ __host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, 
 struct TileGeom {
   int TW, TH, TB;           // pixel box, TW*TH*TB == 128
   int tiles_w, tiles_h, tiles_b;
+  // ceil(2^40 / d) for d = tiles_w, tiles_h, tiles per n-tile: x / d == (x * m) >> 40 for x * d < 2^40.  Every role of
+  // the persistent kernels decomposes its tile index once per tile; with runtime divisors that was three divide
+  // sequences (~25 instructions each) per thread per tile, ~10 % of all instructions of a pointwise GEMM launch
+  // (ncu source page, conv_tc_fwd_v2_k 64->64 @128^2: 11.7 M warp instructions, MUFU.RCP in every code region).
+  unsigned long long m_w, m_h, m_ntm;
 };
+
+__host__ __device__ __forceinline__ unsigned long long fd_magic(int d) { return ((1ull << 40) + (unsigned long long)d - 1) / (unsigned long long)d; }
+__device__ __forceinline__ int fd_div(int x, unsigned long long m) { return (int)(((unsigned long long)(unsigned)x * m) >> 40); }
+// tile -> (n-tile, w-tile, h-tile, b-tile) without divide sequences
+__device__ __forceinline__ void tile_coords(int tile, int n_tiles_m, const TileGeom& g, int& nt, int& tw_i, int& th_i, int& tb_i) {
+  nt = fd_div(tile, g.m_ntm);
+  int tm_ = tile - nt * n_tiles_m;
+  int q = fd_div(tm_, g.m_w);
+  tw_i = tm_ - q * g.tiles_w;
+  tb_i = fd_div(q, g.m_h);
+  th_i = q - tb_i * g.tiles_h;
+}
 
 struct ConvArgs {
   const float* bias;
@@ -294,10 +311,9 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
     uint32_t it_g = 0;  // global k-iteration counter across tiles (ring position)
     uint32_t s = 0, ph = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      int tm_ = tile % a.n_tiles_m;
-      const int n0 = (tile / a.n_tiles_m) * a.BN;
-      const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
-      const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
+      int nt_, tw_i, th_i, tm_;
+      tile_coords(tile, a.n_tiles_m, a.g, nt_, tw_i, th_i, tm_);
+      const int n0 = nt_ * a.BN;
       const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
       int t = 0, c = 0;
       for (int it = 0; it < iters; ++it, ++it_g) {
@@ -390,14 +406,13 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
       for (int i = et; i < a.N; i += EPI_THREADS) sbias[i] = __ldg(a.bias + i);
     uint32_t tcount = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
-      int tm_ = tile % a.n_tiles_m;
-      const int n0 = (tile / a.n_tiles_m) * a.BN;
+      int nt_, tw_i, th_i, tm_;
+      tile_coords(tile, a.n_tiles_m, a.g, nt_, tw_i, th_i, tm_);
+      const int n0 = nt_ * a.BN;
       if (a.stats && n0 != cur_n0) {
         if (cur_n0 >= 0) flush_stats(cur_n0);
         cur_n0 = n0;
       }
-      const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
-      const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
       const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
       const int pw = w0 + tw, ph_ = h0 + th, pb = b0 + tb;
       const bool valid = pw < a.W && ph_ < a.H && pb < a.B;
@@ -582,10 +597,9 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
       __syncwarp();
     }
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      int tm_ = tile % a.n_tiles_m;
-      const int n0 = (tile / a.n_tiles_m) * a.BN;
-      const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
-      const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
+      int nt_, tw_i, th_i, tm_;
+      tile_coords(tile, a.n_tiles_m, a.g, nt_, tw_i, th_i, tm_);
+      const int n0 = nt_ * a.BN;
       const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
       for (int c = 0; c < kchunks; ++c) {
         const uint32_t sa = ra_s, pha = ra_ph;  // running ring position (no division on the issue path)
@@ -715,14 +729,13 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
       for (int i = et; i < a.N; i += EPI_THREADS) sbias[i] = __ldg(a.bias + i);
     uint32_t tcount = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
-      int tm_ = tile % a.n_tiles_m;
-      const int n0 = (tile / a.n_tiles_m) * a.BN;
+      int nt_, tw_i, th_i, tm_;
+      tile_coords(tile, a.n_tiles_m, a.g, nt_, tw_i, th_i, tm_);
+      const int n0 = nt_ * a.BN;
       if (a.stats && n0 != cur_n0) {
         if (cur_n0 >= 0) flush_stats(cur_n0);
         cur_n0 = n0;
       }
-      const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
-      const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
       const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
       const int pw = w0 + tw, ph_ = h0 + th, pb = b0 + tb;
       const bool valid = pw < a.W && ph_ < a.H && pb < a.B;
@@ -952,10 +965,9 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k
       __syncwarp();
     }
     for (int tile = t_first; tile < total_tiles; tile += t_step) {
-      int tm_ = tile % a.n_tiles_m;
-      const int n0 = a.diag ? my_chunk * a.kc : (tile / a.n_tiles_m) * a.BN;
-      const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
-      const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
+      int nt_, tw_i, th_i, tm_;
+      tile_coords(tile, a.n_tiles_m, a.g, nt_, tw_i, th_i, tm_);
+      const int n0 = a.diag ? my_chunk * a.kc : nt_ * a.BN;
       const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
       for (int c = 0; c < kchunks; ++c) {
         const uint32_t sa = ra_s, pha = ra_ph;  // running ring position (no division on the issue path)
@@ -1071,10 +1083,9 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k
     const long pix_c = (long)a.Cin;
     uint32_t ra_s = 0, ra_ph = 0;
     for (int tile = t_first; tile < total_tiles; tile += t_step) {
-      int tm_ = tile % a.n_tiles_m;
-      const int n0 = a.diag ? my_chunk * a.kc : (tile / a.n_tiles_m) * a.BN;
-      const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
-      const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
+      int nt_, tw_i, th_i, tm_;
+      tile_coords(tile, a.n_tiles_m, a.g, nt_, tw_i, th_i, tm_);
+      const int n0 = a.diag ? my_chunk * a.kc : nt_ * a.BN;
       const int w0 = tw_i * a.g.TW - 1, h0 = th_i * a.g.TH - 1, b0 = tm_ * a.g.TB;  // origin of the HALO tile
       const bool do_side = a.side != nullptr && (a.diag || n0 == 0);
       // a tile whose halo lies completely inside the image needs no per-pixel test (all but the border tiles)
@@ -1180,14 +1191,13 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k
       for (int i = et; i < a.N; i += EPI_THREADS) sbias[i] = __ldg(a.bias + i);
     uint32_t tcount = 0;
     for (int tile = t_first; tile < total_tiles; tile += t_step, ++tcount) {
-      int tm_ = tile % a.n_tiles_m;
-      const int n0 = a.diag ? my_chunk * a.kc : (tile / a.n_tiles_m) * a.BN;
+      int nt_, tw_i, th_i, tm_;
+      tile_coords(tile, a.n_tiles_m, a.g, nt_, tw_i, th_i, tm_);
+      const int n0 = a.diag ? my_chunk * a.kc : nt_ * a.BN;
       if (a.stats && n0 != cur_n0) {
         if (cur_n0 >= 0) flush_stats(cur_n0);
         cur_n0 = n0;
       }
-      const int tw_i = tm_ % a.g.tiles_w; tm_ /= a.g.tiles_w;
-      const int th_i = tm_ % a.g.tiles_h; tm_ /= a.g.tiles_h;
       const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tm_ * a.g.TB;
       const int pw = w0 + tw, ph_ = h0 + th, pb = b0 + tb;
       const bool valid = pw < a.W && ph_ < a.H && pb < a.B;
@@ -1360,8 +1370,10 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
       for (int it = 0; it < iters; ++it) {
         mbar_wait(empty0 + 8u * s, ph ^ 1u);
         int tile = tile_begin + it;
-        const int tw_i = tile % a.g.tiles_w; tile /= a.g.tiles_w;
-        const int th_i = tile % a.g.tiles_h; tile /= a.g.tiles_h;
+        const int q_ = fd_div(tile, a.g.m_w);
+        const int tw_i = tile - q_ * a.g.tiles_w;
+        tile = fd_div(q_, a.g.m_h);
+        const int th_i = q_ - tile * a.g.tiles_h;
         const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tile * a.g.TB;
         const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
         if (elect_one()) {
@@ -1685,6 +1697,7 @@ TileGeom make_geom(int B, int H, int W) {
   g.tiles_w = (W + g.TW - 1) / g.TW;
   g.tiles_h = (H + g.TH - 1) / g.TH;
   g.tiles_b = (B + g.TB - 1) / g.TB;
+  g.m_w = fd_magic(g.tiles_w); g.m_h = fd_magic(g.tiles_h); g.m_ntm = fd_magic(g.tiles_w * g.tiles_h * g.tiles_b);
   return g;
 }
 
@@ -1800,6 +1813,8 @@ int crackfl_conv_tc_fwd(const void* X, const void* Wk, const float* bias, const 
     a.g.TW = 8; a.g.TH = 16; a.g.TB = 1;
     a.g.tiles_w = (W + 7) / 8; a.g.tiles_h = (H + 15) / 16; a.g.tiles_b = B;
     a.n_tiles_m = a.g.tiles_w * a.g.tiles_h * a.g.tiles_b;
+    a.g.m_w = fd_magic(a.g.tiles_w); a.g.m_h = fd_magic(a.g.tiles_h); a.g.m_ntm = fd_magic(a.n_tiles_m);
+  a.g.m_w = fd_magic(a.g.tiles_w); a.g.m_h = fd_magic(a.g.tiles_h); a.g.m_ntm = fd_magic(a.n_tiles_m);
     a.n_tiles_n = N / a.BN;
     const uint32_t b_bytes = (uint32_t)a.BN * (uint32_t)kc3 * 2u;
     const uint32_t out_bytes = 2u * 128u * (uint32_t)a.BN * 2u;
@@ -1887,6 +1902,7 @@ v2_path:
   a.sub_w = (a.BN % 64 == 0) ? 64 : 32;
   a.g = make_geom(B, H, W);
   a.n_tiles_m = a.g.tiles_w * a.g.tiles_h * a.g.tiles_b;
+  a.g.m_w = fd_magic(a.g.tiles_w); a.g.m_h = fd_magic(a.g.tiles_h); a.g.m_ntm = fd_magic(a.n_tiles_m);
   a.n_tiles_n = N / a.BN;
   const int iters = taps * (Cin / a.kc);
   const uint32_t stage_bytes = 128u * a.kc * 2u + (uint32_t)a.BN * a.kc * 2u;
@@ -1954,6 +1970,7 @@ int crackfl_conv_tc_xf(const void* X, const void* Wk, const float* bias, const v
   a.g.TW = 8; a.g.TH = 16; a.g.TB = 1;
   a.g.tiles_w = (W + 7) / 8; a.g.tiles_h = (H + 15) / 16; a.g.tiles_b = B;
   a.n_tiles_m = a.g.tiles_w * a.g.tiles_h * a.g.tiles_b;
+  a.g.m_w = fd_magic(a.g.tiles_w); a.g.m_h = fd_magic(a.g.tiles_h); a.g.m_ntm = fd_magic(a.n_tiles_m);
   a.n_tiles_n = diag ? 1 : N / a.BN;
   const uint32_t b_bytes = (uint32_t)a.BN * (uint32_t)kc * 2u;
   const uint32_t out_bytes = 2u * 128u * (uint32_t)a.BN * 2u;
