@@ -36,10 +36,14 @@ struct DwArgs {
   int flip;                     // use w[8 - t] (input gradient)
   int src_mode, resid;          // dgrad epilogue (see dw3x3_bwd_k in elementwise.cu)
   int tiles_x, tiles_y, total_tiles;
+  unsigned long long m_sp, m_tx, m_ty;  // ceil(2^40 / d) for d = tiles per channel block, tiles_x, tiles_y (tile -> coordinates without divide sequences)
   int nstage;                   // depth of the TMA ring (2..4)
   const float* rbn;             // dw_bwd_k: BN ([scale][shift][mean][invstd]) whose backward reductions ride along
   float* rsums;                 //           [sum dz C][sum dz*(y-mean) C], pre-zeroed (NULL: off)
 };
+
+__host__ __device__ __forceinline__ unsigned long long dw_magic(int d) { return ((1ull << 40) + (unsigned long long)d - 1) / (unsigned long long)d; }
+__device__ __forceinline__ int dw_fdiv(int x, unsigned long long m) { return (int)(((unsigned long long)(unsigned)x * m) >> 40); }
 
 __device__ __forceinline__ void load4(const uint8_t* smem_row, int off_bytes, float f[4]) {
   const uint2 v = *reinterpret_cast<const uint2*>(smem_row + off_bytes);
@@ -118,11 +122,12 @@ __global__ void __launch_bounds__(256, 2) dw_stencil_k(const __grid_constant__ C
   __syncthreads();
 
   auto issue = [&](int tile, int stage) {
-    const int cblk = tile / spatial;
-    int sp = tile % spatial;
-    const int tx_i = sp % a.tiles_x; sp /= a.tiles_x;
-    const int ty_i = sp % a.tiles_y;
-    const int b = sp / a.tiles_y;
+    const int cblk = dw_fdiv(tile, a.m_sp);
+    const int sp = tile - cblk * spatial;
+    const int q_ = dw_fdiv(sp, a.m_tx);
+    const int tx_i = sp - q_ * a.tiles_x;
+    const int b = dw_fdiv(q_, a.m_ty);
+    const int ty_i = q_ - b * a.tiles_y;
     mbar_expect_tx(bar0 + 8u * stage, stage_bytes);
     tma_load_4d(base + stage * stage_bytes, &tmX, bar0 + 8u * stage, cblk * CB, tx_i * TX - 1, ty_i * TY - 1, b);
     if (DGRAD) tma_load_4d(base + stage * stage_bytes + halo_bytes, &tmS, bar0 + 8u * stage, cblk * CB, tx_i * TX, ty_i * TY, b);
@@ -143,11 +148,12 @@ __global__ void __launch_bounds__(256, 2) dw_stencil_k(const __grid_constant__ C
       const int ns = stage == 0 ? NS - 1 : stage - 1;
       if (threadIdx.x == 0 && nxt < a.total_tiles) issue(nxt, ns);
     }
-    const int cblk = tile / spatial;
-    int sp = tile % spatial;
-    const int tx_i = sp % a.tiles_x; sp /= a.tiles_x;
-    const int ty_i = sp % a.tiles_y;
-    const int b = sp / a.tiles_y;
+    const int cblk = dw_fdiv(tile, a.m_sp);
+    const int sp = tile - cblk * spatial;
+    const int q_ = dw_fdiv(sp, a.m_tx);
+    const int tx_i = sp - q_ * a.tiles_x;
+    const int b = dw_fdiv(q_, a.m_ty);
+    const int ty_i = q_ - b * a.tiles_y;
     const int cg = cblk * CB + c4 * 4;  // first global channel of this thread
     if (cblk != cur_cblk) {             // uniform over the CTA
       cur_cblk = cblk;
@@ -318,11 +324,12 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
   pdl_enter();
 
   auto issue = [&](int tile, int stage) {
-    const int cblk = tile / spatial;
-    int sp = tile % spatial;
-    const int tx_i = sp % a.tiles_x; sp /= a.tiles_x;
-    const int ty_i = sp % a.tiles_y;
-    const int b = sp / a.tiles_y;
+    const int cblk = dw_fdiv(tile, a.m_sp);
+    const int sp = tile - cblk * spatial;
+    const int q_ = dw_fdiv(sp, a.m_tx);
+    const int tx_i = sp - q_ * a.tiles_x;
+    const int b = dw_fdiv(q_, a.m_ty);
+    const int ty_i = q_ - b * a.tiles_y;
     mbar_expect_tx(bar0 + 8u * stage, stage_bytes);
     tma_load_4d(base + stage * stage_bytes, &tmA, bar0 + 8u * stage, cblk * CB, tx_i * TX - 1, ty_i * TY - 1, b);
     tma_load_4d(base + stage * stage_bytes + a_bytes, &tmG, bar0 + 8u * stage, cblk * CB, tx_i * TX, ty_i * TY, b);
@@ -364,10 +371,11 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
       const int ns = stage == 0 ? NS - 1 : stage - 1;
       if (threadIdx.x == 0 && nxt < a.total_tiles) issue(nxt, ns);
     }
-    const int cblk = tile / spatial;
-    int sp = tile % spatial;
-    const int tx_i = sp % a.tiles_x; sp /= a.tiles_x;
-    const int ty_i = sp % a.tiles_y;
+    const int cblk = dw_fdiv(tile, a.m_sp);
+    const int sp = tile - cblk * spatial;
+    const int q_ = dw_fdiv(sp, a.m_tx);
+    const int tx_i = sp - q_ * a.tiles_x;
+    const int ty_i = q_ - dw_fdiv(q_, a.m_ty) * a.tiles_y;
     if (cblk != cur_cblk) {  // uniform over the CTA
       if (cur_cblk >= 0) flush(cur_cblk);
       cur_cblk = cblk;
@@ -492,11 +500,12 @@ __global__ void __launch_bounds__(512, 1) dw_bwd_k(const __grid_constant__ CUten
   __syncthreads();
 
   auto issue = [&](int tile, int stage) {
-    const int cblk = tile / spatial;
-    int sp = tile % spatial;
-    const int tx_i = sp % a.tiles_x; sp /= a.tiles_x;
-    const int ty_i = sp % a.tiles_y;
-    const int b = sp / a.tiles_y;
+    const int cblk = dw_fdiv(tile, a.m_sp);
+    const int sp = tile - cblk * spatial;
+    const int q_ = dw_fdiv(sp, a.m_tx);
+    const int tx_i = sp - q_ * a.tiles_x;
+    const int b = dw_fdiv(q_, a.m_ty);
+    const int ty_i = q_ - b * a.tiles_y;
     mbar_expect_tx(bar0 + 8u * stage, stage_bytes);
     tma_load_4d(base + stage * stage_bytes, &tmG, bar0 + 8u * stage, cblk * CB, tx_i * TX - 1, ty_i * TY - 1, b);
     tma_load_4d(base + stage * stage_bytes + halo_bytes, &tmS, bar0 + 8u * stage, cblk * CB, tx_i * TX - 1, ty_i * TY - 1, b);
@@ -564,11 +573,12 @@ __global__ void __launch_bounds__(512, 1) dw_bwd_k(const __grid_constant__ CUten
     const int stage = it & 1;
     const int nxt = tile + gridDim.x;
     if (threadIdx.x == 0 && nxt < a.total_tiles) issue(nxt, stage ^ 1);  // its last readers passed the barrier at the loop tail
-    const int cblk = tile / spatial;
-    int sp = tile % spatial;
-    const int tx_i = sp % a.tiles_x; sp /= a.tiles_x;
-    const int ty_i = sp % a.tiles_y;
-    const int b = sp / a.tiles_y;
+    const int cblk = dw_fdiv(tile, a.m_sp);
+    const int sp = tile - cblk * spatial;
+    const int q_ = dw_fdiv(sp, a.m_tx);
+    const int tx_i = sp - q_ * a.tiles_x;
+    const int b = dw_fdiv(q_, a.m_ty);
+    const int ty_i = q_ - b * a.tiles_y;
     const int cg = cblk * CB + c4 * 4;
     if (cblk != cur_cblk) {  // uniform over the CTA
       if (role == 1 && cur_cblk >= 0) flush(cur_cblk);
@@ -773,6 +783,7 @@ static int launch_stencil(const void* x, DwArgs& a, cudaStream_t st) {
   pick_ring(a, ((size_t)(TY + 2) * HW + (DGRAD ? (size_t)TY * TX : 0)) * 2, extra);
   a.tiles_x = (a.W + TX - 1) / TX; a.tiles_y = (a.H + TY - 1) / TY;
   a.total_tiles = a.tiles_x * a.tiles_y * a.B * (a.C / a.CB);
+  a.m_sp = dw_magic(a.tiles_x * a.tiles_y * a.B); a.m_tx = dw_magic(a.tiles_x); a.m_ty = dw_magic(a.tiles_y);
   CUtensorMap tm, tmS;
   const int d[4] = {a.C, a.W, a.H, a.B}, bx[4] = {a.CB, HW, TY + 2, 1}, bs[4] = {a.CB, TX, TY, 1};
   int rc = ck::get_tensor_map(x, 4, d, bx, 0, &tm);
@@ -831,6 +842,7 @@ int crackfl_dw3x3_wgrad_tma(const void* g, const void* src, const float* bn, flo
   pick_ring(a, ((size_t)(TY + 2) * HW + (size_t)TY * TX) * 2, extra);
   a.tiles_x = (W + TX - 1) / TX; a.tiles_y = (H + TY - 1) / TY;
   a.total_tiles = a.tiles_x * a.tiles_y * B * (C / a.CB);
+  a.m_sp = dw_magic(a.tiles_x * a.tiles_y * a.B); a.m_tx = dw_magic(a.tiles_x); a.m_ty = dw_magic(a.tiles_y);
   CUtensorMap tmA, tmG;
   const int d[4] = {C, W, H, B}, ba[4] = {a.CB, HW, TY + 2, 1}, bg[4] = {a.CB, TX, TY, 1};
   int rc = ck::get_tensor_map(src, 4, d, ba, 0, &tmA);
@@ -880,6 +892,7 @@ int crackfl_dw3x3_bwd_tma_bn(const void* g, const void* src, const float* w, con
   a.rbn = red_bn; a.rsums = red_bn ? red_sums : nullptr;
   a.tiles_x = (W + TX - 1) / TX; a.tiles_y = (H + TY - 1) / TY;
   a.total_tiles = a.tiles_x * a.tiles_y * B * (C / a.CB);
+  a.m_sp = dw_magic(a.tiles_x * a.tiles_y * a.B); a.m_tx = dw_magic(a.tiles_x); a.m_ty = dw_magic(a.tiles_y);
   CUtensorMap tmG, tmS;
   const int d[4] = {C, W, H, B}, bx[4] = {a.CB, HW, TY + 2, 1};
   int rc = ck::get_tensor_map(g, 4, d, bx, 0, &tmG);

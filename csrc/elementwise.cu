@@ -21,6 +21,35 @@ constexpr int TPB = 256;
 // removes one tiny launch (and its dependency bubble) per BN layer from the critical path of the step.
 typedef crackfl_bn_fin BnFin;
 
+// Flat vector index -> (pixel, w, h, b).  Channel-vector counts are powers of two and so are the spatial sizes of the
+// 128 / 256-pixel configurations: shifts and masks then replace three divide sequences (~25 instructions each, or ~100 for
+// the 64-bit ones the loss head used) per element; any other size takes the division path.
+struct IdxDec {
+  int lc, lw, lh;  // log2 of c8, W, H or -1
+};
+__device__ __forceinline__ int ck_log2_or_neg(int v) { return (v > 0 && (v & (v - 1)) == 0) ? (__ffs(v) - 1) : -1; }
+__device__ __forceinline__ IdxDec make_idxdec(int c8, int Wd, int Hd) {
+  IdxDec d;
+  d.lc = ck_log2_or_neg(c8); d.lw = ck_log2_or_neg(Wd); d.lh = ck_log2_or_neg(Hd);
+  if (d.lc < 0 || d.lw < 0 || d.lh < 0) d.lc = -1;
+  return d;
+}
+__device__ __forceinline__ void idx_dec(const IdxDec& d, int g, int c8, int Wd, int Hd, int& pix, int& w, int& h, int& b) {
+  if (d.lc >= 0) {
+    pix = g >> d.lc;
+    w = pix & (Wd - 1);
+    const int q = pix >> d.lw;
+    h = q & (Hd - 1);
+    b = q >> d.lh;
+  } else {
+    pix = g / c8;
+    w = pix % Wd;
+    const int q = pix / Wd;
+    h = q % Hd;
+    b = q / Hd;
+  }
+}
+
 __device__ __forceinline__ void bn_coeffs(const BnFin& f, const float* __restrict__ bn, int C, int cv, float sc[8],
                                           float sh[8]) {
   if (f.stats == nullptr) {
@@ -221,10 +250,8 @@ __global__ void __launch_bounds__(TPB, 4) bn_act_k(const __nv_bfloat16* __restri
       const uint4 v = pack8(f[u]);
       stg16(out + gi * 8, v);
       if (even) {
-        int p = gi / c8;
-        const int w = (int)(p % W); p /= W;
-        const int h = (int)(p % H);
-        const int b = (int)(p / H);
+        int p, w, h, b;
+        idx_dec(make_idxdec(c8, W, H), gi, c8, W, H, p, w, h, b);
         if (!(h & 1) && !(w & 1))
           stg16(even + ((((int)b * (H >> 1) + (h >> 1)) * (W >> 1) + (w >> 1)) * c8 + cv) * 8, v);
       }
@@ -363,11 +390,10 @@ __global__ void __launch_bounds__(TPB) pool_add_fwd_k(const __nv_bfloat16* __res
   float sc[8], sh[8];
   bn_coeffs(fin, bn, C, cv, sc, sh);
   bn_publish(fin, C);
+  const IdxDec dec = make_idxdec(c8, Wo, Ho);
   for (int g = g0; g < total; g += (int)gridDim.x * blockDim.x) {
-    int p = g / c8;
-    const int ow = (int)(p % Wo); p /= Wo;
-    const int oh = (int)(p % Ho);
-    const int b = (int)(p / Ho);
+    int p, ow, oh, b;
+    idx_dec(dec, g, c8, Wo, Ho, p, ow, oh, b);
     float best[8];
     int bi[8];
 #pragma unroll
@@ -424,11 +450,10 @@ __global__ void __launch_bounds__(TPB) dec_combine_fwd_k(const __nv_bfloat16* __
   float sc[8], sh[8];
   bn_coeffs(fin, bn, C, cv, sc, sh);
   bn_publish(fin, C);
+  const IdxDec dec = make_idxdec(c8, W, H);
   for (int g = g0; g < total; g += (int)gridDim.x * blockDim.x) {
-    int p = g / c8;
-    const int w = (int)(p % W); p /= W;
-    const int h = (int)(p % H);
-    const int b = (int)(p / H);
+    int p, w, h, b;
+    idx_dec(dec, g, c8, W, H, p, w, h, b);
     float f[8], r[8];
     unpack8(ldg16(y + g * 8), f);
     const int ri = rl_up ? ((((int)b * (H >> 1) + (h >> 1)) * (W >> 1) + (w >> 1)) * c8 + cv) : g;
@@ -457,12 +482,11 @@ __global__ void __launch_bounds__(TPB) down2sum_k(const __nv_bfloat16* __restric
   ck::pdl_enter();
   const int c8 = C >> 3;
   const int total = (int)B * Ho * Wo * c8;
+  const IdxDec dec = make_idxdec(c8, Wo, Ho);
   for (int g = (int)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (int)gridDim.x * blockDim.x) {
-    const int cv = (int)(g % c8);
-    int p = g / c8;
-    const int w = (int)(p % Wo); p /= Wo;
-    const int h = (int)(p % Ho);
-    const int b = (int)(p / Ho);
+    int p, w, h, b;
+    idx_dec(dec, g, c8, Wo, Ho, p, w, h, b);
+    const int cv = g - p * c8;
     const int W2 = 2 * Wo;
     const int base = (((int)b * 2 * Ho + 2 * h) * W2 + 2 * w) * c8 + cv;
     float a0[8], a1[8], a2[8], a3[8], o[8];
@@ -667,8 +691,10 @@ __global__ void __launch_bounds__(TPB, 2) pool_bwd_bn_k(const __nv_bfloat16* __r
   const int P2 = B * Ho * Wo;
   const int p0 = blockIdx.x * items_per_block;
   const int p1 = min(P2, p0 + items_per_block);
+  const IdxDec pdec = make_idxdec(1, Wo, Ho);
   for (int p = p0 + lane; p < p1; p += lanes) {
-    const int j = p % Wo, i = (p / Wo) % Ho, b = p / (Wo * Ho);
+    int pp_, j, i, b;
+    idx_dec(pdec, p, 1, Wo, Ho, pp_, j, i, b);
     float d[4][8];
 #pragma unroll
     for (int q = 0; q < 4; ++q)
@@ -780,20 +806,20 @@ __global__ void __launch_bounds__(TPB) head_fwd_k(const __nv_bfloat16* __restric
   const int Wf = 2 * Wl, Hf = 2 * Hl;
   float a[5] = {0, 0, 0, 0, 0};
   const long iters = (total + stride - 1) / stride;
+  const IdxDec hdec = make_idxdec(c8, Wl, Hl);  // (total fits 32 bits: checked by the launcher)
   for (long it = 0; it < iters; ++it) {
     const long g = it * stride + (long)blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = g < total;
     const long gg = valid ? g : 0;
-    const int cv = (int)(gg % c8);
-    const long p = gg / c8;
+    int p_, wl, hl, b_;
+    idx_dec(hdec, (int)gg, c8, Wl, Hl, p_, wl, hl, b_);
+    const int cv = (int)gg - p_ * c8;
+    const long p = p_, b = b_;
     float f[8];
     unpack8(ldg16(s + gg * 8), f);
     const float logit = head_logit(f, sw, cv, c8) + bias[0];
     if (!valid || cv != 0) continue;
     const float pr = 1.f / (1.f + __expf(-logit));
-    const int wl = (int)(p % Wl);
-    const int hl = (int)((p / Wl) % Hl);
-    const long b = p / ((long)Wl * Hl);
     const long base = (b * Hf + 2 * hl) * Wf + 2 * wl;
     if (prob) {
       prob[base] = pr; prob[base + 1] = pr; prob[base + Wf] = pr; prob[base + Wf + 1] = pr;
@@ -859,20 +885,20 @@ __global__ void __launch_bounds__(TPB) head_bwd_k(const __nv_bfloat16* __restric
   float dbl = 0.f;
   float am[5] = {0, 0, 0, 0, 0};  // acc_out != NULL (plain BCE): the forward's loss / metric sums, so head_fwd_k is not launched
   const long iters = (total + stride - 1) / stride;
+  const IdxDec hdec = make_idxdec(c8, Wl, Hl);  // (total fits 32 bits: checked by the launcher)
   for (long it = 0; it < iters; ++it) {
     const long g = it * stride + (long)blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = g < total;
     const long gg = valid ? g : 0;
-    const int cv = (int)(gg % c8);
-    const long p = gg / c8;
+    int p_, wl, hl, b_;
+    idx_dec(hdec, (int)gg, c8, Wl, Hl, p_, wl, hl, b_);
+    const int cv = (int)gg - p_ * c8;
+    const long p = p_, b = b_;
     float f[8], o[8];
     unpack8(ldg16(s + gg * 8), f);
     const float logit = head_logit(f, sw, cv, c8) + bias[0];
     if (!valid) continue;
     const float pr = 1.f / (1.f + __expf(-logit));
-    const int wl = (int)(p % Wl);
-    const int hl = (int)((p / Wl) % Hl);
-    const long b = p / ((long)Wl * Hl);
     const long base = (b * Hf + 2 * hl) * Wf + 2 * wl;
     const bool inside = !bce_clip || ((pr >= 1e-7f) && (pr <= 1.f - 1e-7f));  // clip_by_value passes no gradient outside
     float dl = 0.f;
@@ -1465,6 +1491,7 @@ int crackfl_colsum(const void* g, float* out, long P, int C, cudaStream_t st) {
 
 int crackfl_head_fwd(const void* s, const float* w, const float* bias, const void* mask_u8, float* acc, float* prob, int B,
                      int Hl, int Wl, int C, int bce_clip, cudaStream_t st) {
+  CK_FITS32((long)B * Hl * Wl * C);
   const long P = (long)B * Hl * Wl;
   ck::launch(head_fwd_k, grid_for(P * (C / 8), 148 * 4), TPB, C * sizeof(float), st, (const __nv_bfloat16*)s, w, bias,
                                                                    (const uint8_t*)mask_u8, acc, prob, B, Hl, Wl, C, bce_clip);
@@ -1475,6 +1502,7 @@ int crackfl_head_fwd(const void* s, const float* w, const float* bias, const voi
 int crackfl_head_bwd(const void* s, const float* w, const float* bias, const void* mask_u8, const float* sums, void* ds,
                      float* dw, float* db, int B, int Hl, int Wl, int C, int use_dice, float dice_smooth, float loss_scale,
                      int bce_clip, cudaStream_t st) {
+  CK_FITS32((long)B * Hl * Wl * C);
   const long P = (long)B * Hl * Wl;
   ck::launch(head_bwd_k, grid_for(P * (C / 8), 148 * 4), TPB, (C + TPB * 8) * sizeof(float), st, 
       (const __nv_bfloat16*)s, w, bias, (const uint8_t*)mask_u8, sums, (__nv_bfloat16*)ds, dw, db, B, Hl, Wl, C, use_dice,
@@ -1488,6 +1516,7 @@ int crackfl_head_bwd(const void* s, const float* w, const float* bias, const voi
 int crackfl_head_fwd_bwd(const void* s, const float* w, const float* bias, const void* mask_u8, float* acc_out, void* ds,
                          float* dw, float* db, int B, int Hl, int Wl, int C, float loss_scale, int bce_clip,
                          cudaStream_t st) {
+  CK_FITS32((long)B * Hl * Wl * C);
   const long P = (long)B * Hl * Wl;
   ck::launch(head_bwd_k, grid_for(P * (C / 8), 148 * 4), TPB, (C + TPB * 8) * sizeof(float), st,
       (const __nv_bfloat16*)s, w, bias, (const uint8_t*)mask_u8, (const float*)nullptr, (__nv_bfloat16*)ds, dw, db, B, Hl, Wl, C,
