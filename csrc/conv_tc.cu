@@ -1515,6 +1515,155 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
   }
 }
 
+// ----------------------------------------------------------------------------------------------------------
+// Halo weight gradient for the 3x3 layers.  wgrad_tc_k gives every (tap, channel-chunk) group its own CTAs, each of
+// which reloads the shifted activation box AND the dY tile: for a 64 -> 64 layer that is 9 x 3 tensor reads out of L2
+// (ncu: the MMA warp waits on TMA, tensor pipe 21 %, L2 the busiest unit).  Here a CTA owns one input-channel chunk x one
+// 64-column dY tile x a range of pixel tiles and, per 128-pixel tile, loads ONE (16+2) x (8+2) halo tile of X and one dY
+// tile; the nine taps are nine MN-major windows into the halo tile (start shifted by (kh*10 + kw) pixel rows, the 8-pixel
+// K groups 10 rows apart, consecutive kw taps as consecutive M blocks one row apart), accumulating into 6 (64-channel
+// chunks) or 3 (32-channel chunks) TMEM tiles of 128 x BN that live for the CTA's whole pixel range.  The last M block of
+// a group may be a non-existent tap kw = 3: its rows are computed and dropped.  Partial tiles are added to the Keras-layout
+// gradient arena with vector reductions.
+struct WgradHaloArgs {
+  float* dW;
+  long s_tap, s_ci, s_co;
+  int B, H, W, Cin, Cout;
+  int cw, BN;                 // channel chunk of X (64 / 32), dY columns per CTA (64 / 32)
+  int ntiles, tiles_per_split, stages, groups, khsplit;
+  uint32_t layoutA, layoutB, sboB;
+  uint32_t a_stage, a_bytes, b_bytes;
+  TileGeom g;
+};
+
+__global__ void __launch_bounds__(192) wgrad_halo_k(const __grid_constant__ CUtensorMap tmX,
+                                                    const __grid_constant__ CUtensorMap tmDY, const WgradHaloArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t stage_bytes = a.a_stage + a.b_bytes;  // both multiples of 1024
+  const uint32_t bar_base = base + a.stages * stage_bytes;
+  const uint32_t full0 = bar_base, empty0 = bar_base + 8u * a.stages, tfull = bar_base + 16u * a.stages;
+  const uint32_t tptr = tfull + 8u;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
+  // khsplit: one kernel row (kh) per CTA - a third of the accumulators and of the atomics per CTA, the halo tile is loaded
+  // by three CTAs instead of one
+  const int chunk = blockIdx.x;
+  const int n0 = (a.khsplit ? (int)blockIdx.y / 3 : (int)blockIdx.y) * a.BN;
+  const int kh_only = a.khsplit ? (int)blockIdx.y % 3 : -1;
+  const int my_groups = a.khsplit ? a.groups / 3 : a.groups;
+  const int tile_begin = blockIdx.z * a.tiles_per_split;
+  const int tile_end = min(a.ntiles, tile_begin + a.tiles_per_split);
+  const int iters = tile_end - tile_begin;
+  const uint32_t row_b = (uint32_t)a.cw * 2u;
+  uint32_t ncols = 32;
+  while (ncols < (uint32_t)(my_groups * a.BN)) ncols <<= 1;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < a.stages; ++s) {
+      mbar_init(full0 + 8u * s, 1);
+      mbar_init(empty0 + 8u * s, 1);
+    }
+    mbar_init(tfull, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    tma_prefetch_desc(&tmX);
+    tma_prefetch_desc(&tmDY);
+  }
+  if (warp == 1) tmem_alloc(tptr, ncols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  ck::pdl_enter();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tptr));
+
+  if (iters > 0) {
+    if (warp == 0) {
+      uint32_t s = 0, ph = 0;
+      for (int it = 0; it < iters; ++it) {
+        mbar_wait(empty0 + 8u * s, ph ^ 1u);
+        int tile = tile_begin + it;
+        const int q_ = fd_div(tile, a.g.m_w);
+        const int tw_i = tile - q_ * a.g.tiles_w;
+        tile = fd_div(q_, a.g.m_h);
+        const int th_i = q_ - tile * a.g.tiles_h;
+        const int w0 = tw_i * a.g.TW, h0 = th_i * a.g.TH, b0 = tile;
+        const uint32_t sa = base + s * stage_bytes;
+        if (elect_one()) {
+          mbar_expect_tx(full0 + 8u * s, a.a_bytes + a.b_bytes);
+          tma_load_4d(sa, &tmX, full0 + 8u * s, chunk * a.cw, w0 - 1, h0 - 1, b0);       // halo: zero fill = padding
+          tma_load_4d(sa + a.a_stage, &tmDY, full0 + 8u * s, n0, w0, h0, b0);
+        }
+        __syncwarp();
+        if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1u; }
+      }
+    } else if (warp == 1) {
+      const uint32_t idesc = make_idesc(128, a.BN, 1, 1);
+      // A: M blocks (consecutive kw taps) one pixel row apart, 8-pixel K groups one HALO row (10 pixels) apart
+      const uint32_t ahi = desc_hi(10u * row_b, a.layoutA), bhi = desc_hi(a.sboB, a.layoutB);
+      const uint32_t rb16 = row_b >> 4;
+      const uint32_t akstep = 20u * rb16;                                   // 16 pixels of K = 2 tile rows = 20 halo rows
+      const uint32_t bkstep = (16u * (uint32_t)a.BN * 2u) >> 4;            // 16 dY rows
+      const int gpk = a.groups / 3;                                         // groups per kh: 2 (cw 64) or 1 (cw 32)
+      uint32_t s = 0, ph = 0;
+      for (int it = 0; it < iters; ++it) {
+        mbar_wait(full0 + 8u * s, ph);
+        tc_fence_after();
+        const uint32_t sa = base + s * stage_bytes;
+        const uint32_t alo0 = desc_lo(sa, row_b), blo0 = desc_lo(sa + a.a_stage, 0);
+        if (elect_one()) {
+          for (int g = 0; g < my_groups; ++g) {
+            const int kh = kh_only >= 0 ? kh_only : g / gpk, kw0 = (kh_only >= 0 ? g : g - kh * gpk) * 2;
+            const uint32_t alo = alo0 + (uint32_t)(kh * 10 + kw0) * rb16;
+            const uint32_t tacc = tmem_base + (uint32_t)(g * a.BN);
+#pragma unroll
+            for (uint32_t k = 0; k < 8; ++k)
+              umma_f16_w(tacc, alo + k * akstep, ahi, blo0 + k * bkstep, bhi, idesc, (it > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(empty0 + 8u * s);
+        }
+        __syncwarp();
+        if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1u; }
+      }
+      if (elect_one()) umma_commit(tfull);
+      __syncwarp();
+    } else {
+      const int q = warp & 3;
+      const int r = q * 32 + lane;           // accumulator row = (M block, channel within the chunk)
+      const int blk = r / a.cw, ci = chunk * a.cw + (r - blk * a.cw);
+      const int gpk = a.groups / 3;
+      mbar_wait(tfull, 0);
+      tc_fence_after();
+      for (int g = 0; g < my_groups; ++g) {
+        const int kh = kh_only >= 0 ? kh_only : g / gpk, kw = (kh_only >= 0 ? g : g - kh * gpk) * 2 + blk;
+        const bool valid = kw < 3;           // the M block past the last tap is scratch
+        float* dst = a.dW + (long)(kh * 3 + kw) * a.s_tap + (long)ci * a.s_ci;
+        for (int c0 = 0; c0 < a.BN; c0 += 32) {
+          uint32_t raw[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(g * a.BN + c0), raw);
+          if (!valid) continue;
+          float* d = dst + (long)(n0 + c0) * a.s_co;
+          if (a.s_co == 1 && (reinterpret_cast<uintptr_t>(d) & 15) == 0) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d + j), "f"(__uint_as_float(raw[j])),
+                           "f"(__uint_as_float(raw[j + 1])), "f"(__uint_as_float(raw[j + 2])),
+                           "f"(__uint_as_float(raw[j + 3])) : "memory");
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) atomicAdd(d + (long)j * a.s_co, __uint_as_float(raw[j]));
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, ncols);
+  }
+}
+
 // Sum the per-CTA partial tiles of wgrad_tc_k over the pixel splits and add the result into the Keras-layout
 // gradient arena (one writer per element, no atomics).  A block is (256 / zl) float4 columns x zl split lanes: every
 // lane strides over the splits with four loads in flight, the lanes meet in shared memory, lane 0 writes.  (The first
@@ -2043,10 +2192,80 @@ int crackfl_conv_tc_xf(const void* X, const void* Wk, const float* bias, const v
 // cin_valid < Cin: the last Cin - cin_valid input channels are zero padding; their gradient rows are not written
 // (workspace path only)
 // mode 0: launch + per-layer reduction; 1: launch only, fill *desc for crackfl_wgrad_reduce_all; 2: plan only (no launch)
+static int wgrad_halo(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, long s_tap, long s_ci,
+                      long s_co, cudaStream_t st) {
+  WgradHaloArgs a;
+  memset(&a, 0, sizeof(a));
+  a.dW = dW; a.s_tap = s_tap; a.s_ci = s_ci; a.s_co = s_co;
+  a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.Cout = Cout;
+  a.cw = (Cin % 64 == 0) ? 64 : 32;
+  a.BN = (Cout % 64 == 0) ? 64 : 32;
+  a.groups = a.cw == 64 ? 6 : 3;
+  a.layoutA = a.cw == 64 ? 2u : 4u;
+  a.layoutB = a.BN == 64 ? 2u : 4u; a.sboB = a.BN == 64 ? 1024u : 512u;
+  a.a_bytes = 180u * (uint32_t)a.cw * 2u;
+  a.a_stage = (a.a_bytes + 1023u) & ~1023u;   // >= 4 spare pixel rows: the scratch tap kw = 3 may read past the tile
+  a.b_bytes = 128u * (uint32_t)a.BN * 2u;
+  a.g.TW = 8; a.g.TH = 16; a.g.TB = 1;
+  a.g.tiles_w = (W + 7) / 8; a.g.tiles_h = (H + 15) / 16; a.g.tiles_b = B;
+  a.ntiles = a.g.tiles_w * a.g.tiles_h * a.g.tiles_b;
+  a.g.m_w = fd_magic(a.g.tiles_w); a.g.m_h = fd_magic(a.g.tiles_h); a.g.m_ntm = fd_magic(a.ntiles);
+  const int chunks = Cin / a.cw, ntn = Cout / a.BN;
+  const uint32_t stage_bytes = a.a_stage + a.b_bytes;
+  static int khs = -1;
+  if (khs < 0) { const char* e = getenv("CRACKFL_WGRAD_HALO_KH"); khs = e ? atoi(e) : 1; }
+  a.khsplit = khs ? 1 : 0;
+  const int kmul = a.khsplit ? 3 : 1;
+  int per_sm = (2u * 2u * stage_bytes + 4096u <= 220u * 1024u && (a.groups / kmul) * a.BN <= 256) ? 2 : 1;
+  int stages = (int)(((per_sm == 2 ? 110u : 220u) * 1024u - 2048u) / stage_bytes);
+  if (stages > 5) stages = 5;
+  if (stages < 2) { per_sm = 1; stages = (int)((220u * 1024u - 2048u) / stage_bytes); }
+  static int fillh = -1;
+  if (fillh < 0) { const char* e = getenv("CRACKFL_WGRAD_HALO_FILL"); fillh = e ? atoi(e) : 50; if (fillh < 10 || fillh > 200) fillh = 50; }
+  int splits = (148 * per_sm * fillh / 100) / (chunks * ntn * kmul);
+  if (splits > a.ntiles) splits = a.ntiles;
+  if (splits < 1) splits = 1;
+  a.tiles_per_split = (a.ntiles + splits - 1) / splits;
+  splits = (a.ntiles + a.tiles_per_split - 1) / a.tiles_per_split;
+  if (stages > a.tiles_per_split) stages = a.tiles_per_split;
+  if (stages < 1) stages = 1;
+  a.stages = stages;
+  CUtensorMap tmX, tmDY;
+  const int dX[4] = {Cin, W, H, B}, bX[4] = {a.cw, 10, 18, 1};
+  int rc = get_map(X, 4, dX, bX, a.cw * 2, &tmX);
+  if (rc) return rc;
+  const int dD[4] = {Cout, W, H, B}, bD[4] = {a.BN, 8, 16, 1};
+  rc = get_map(dY, 4, dD, bD, a.BN * 2, &tmDY);
+  if (rc) return rc;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(wgrad_halo_k, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+    if (e != cudaSuccess) return (int)e;
+    attr = true;
+  }
+  const size_t smem = (size_t)stages * stage_bytes + 1024 + 256;
+  dim3 grid(chunks, ntn * kmul, splits);
+  ck::launch(wgrad_halo_k, grid, 192, smem, st, tmX, tmDY, a);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
 static int wgrad_impl(const void* X, const void* dY, float* dW, int B, int H, int W, int Cin, int Cout, int taps,
                       long s_tap, long s_ci, long s_co, float* workspace, long workspace_floats, int cin_valid,
                       int mode, crackfl_wgrad_red_desc* desc, cudaStream_t st) {
   if (Cin % 32 || Cout % 32 || (taps != 1 && taps != 9)) return (int)cudaErrorInvalidValue;
+  {
+    static int use_halo_w = -1;
+    if (use_halo_w < 0) { const char* e = getenv("CRACKFL_WGRAD_HALO"); use_halo_w = e ? atoi(e) : 1; }
+    // measured per layer (bench/wgrad_bench.py, us, per-(tap,chunk) kernel -> halo kernel with one kernel row per CTA and half
+    // the CTA slots): 16^2 x256: 17.8 -> 18.0, 32^2 x128: 17.1 -> 18.8, 64^2 x64: 20.4 -> 19.9, 128^2 x32: 32.1 -> 24.5,
+    // 128^2 32->64: 34.0 -> 26.3.  Both are bound by the split-K reduction (the halo kernel's CTAs each carry 3 taps), so the
+    // halo kernel is used where the pixel axis is long (>= 1024 tiles of 128 pixels); CRACKFL_WGRAD_HALO=2 forces it.
+    const long px_tiles = (long)B * ((H + 15) / 16) * ((W + 7) / 8);
+    if (use_halo_w && taps == 9 && mode == 0 && !workspace && H >= 16 && W >= 8 && (cin_valid <= 0 || cin_valid == Cin) &&
+        (px_tiles >= 1024 || use_halo_w >= 2))
+      return wgrad_halo(X, dY, dW, B, H, W, Cin, Cout, s_tap, s_ci, s_co, st);
+  }
   WgradArgs a;
   a.dW = dW; a.s_tap = s_tap; a.s_ci = s_ci; a.s_co = s_co;
   a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.Cout = Cout; a.taps = taps;

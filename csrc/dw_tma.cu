@@ -223,7 +223,7 @@ __global__ void __launch_bounds__(256, 2) dw_stencil_k(const __grid_constant__ C
           v.z = f2_to_bf2_relu(ffma2(bf2_to_f2(v.z), scp[2], shp[2]));
           v.w = f2_to_bf2_relu(ffma2(bf2_to_f2(v.w), scp[3], shp[3]));
           if (!interior) {
-            const int pi = idx / c8n;
+            const int pi = idx >> (c8n == 8 ? 3 : 2);  // c8n = CB / 8 is 8 or 4
             const int hr = pi / HW, hc = pi - hr * HW;
             const int gh = ty0 - 1 + hr, gx = w0 - 1 + hc;
             if (gh < 0 || gh >= a.H || gx < 0 || gx >= a.W) v = make_uint4(0u, 0u, 0u, 0u);
@@ -422,7 +422,7 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
           v.z = f2_to_bf2_relu(ffma2(bf2_to_f2(v.z), scp[2], shp[2]));
           v.w = f2_to_bf2_relu(ffma2(bf2_to_f2(v.w), scp[3], shp[3]));
           if (!interior) {
-            const int pi = idx / c8n;
+            const int pi = idx >> (c8n == 8 ? 3 : 2);  // c8n = CB / 8 is 8 or 4
             const int hr = pi / HW, hc = pi - hr * HW;
             const int gh = ty0 - 1 + hr, gx = w0 - 1 + hc;
             if (gh < 0 || gh >= a.H || gx < 0 || gx >= a.W) v = make_uint4(0u, 0u, 0u, 0u);
@@ -646,7 +646,7 @@ __global__ void __launch_bounds__(512, 1) dw_bwd_k(const __grid_constant__ CUten
           v.z = f2_to_bf2_relu(ffma2(bf2_to_f2(v.z), scp[2], shp[2]));
           v.w = f2_to_bf2_relu(ffma2(bf2_to_f2(v.w), scp[3], shp[3]));
           if (!interior) {
-            const int pi = idx / c8n;
+            const int pi = idx >> (c8n == 8 ? 3 : 2);  // c8n = CB / 8 is 8 or 4
             const int hr = pi / HW, hc = pi - hr * HW;
             const int gh = ty0 - 1 + hr, gx = w0 - 1 + hc;
             if (gh < 0 || gh >= a.H || gx < 0 || gx >= a.W) v = make_uint4(0u, 0u, 0u, 0u);

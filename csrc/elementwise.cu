@@ -544,9 +544,8 @@ __device__ __forceinline__ void load_dz(const __nv_bfloat16* __restrict__ g, con
       for (int j = 0; j < 8; ++j) dz[j] = fmaf(yv[j], sc[j], sh[j]) > 0.f ? dz[j] : 0.f;
     }
   } else {
-    const int w = (int)(p % W);
-    const int h = (int)((p / W) % H);
-    const int b = p / ((int)W * H);
+    int pp_, w, h, b;
+    idx_dec(make_idxdec(1, W, H), (int)p, 1, W, H, pp_, w, h, b);
     const int Ho = H >> 1, Wo = W >> 1;
 #pragma unroll
     for (int j = 0; j < 8; ++j) dz[j] = 0.f;
@@ -1250,12 +1249,11 @@ __global__ void __launch_bounds__(TPB) entry_im2col_k(const uint8_t* __restrict_
   ck::pdl_enter();
   const int Ho = H >> 1, Wo = W >> 1;
   const int total = (int)B * Ho * Wo * 4;
+  const IdxDec dec = make_idxdec(4, Wo, Ho);
   for (int i = (int)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int)gridDim.x * blockDim.x) {
     const int q = (int)(i & 3);
-    const int p = i >> 2;
-    const int ow = (int)(p % Wo);
-    const int oh = (int)((p / Wo) % Ho);
-    const int b = p / ((int)Wo * Ho);
+    int p, ow, oh, b;
+    idx_dec(dec, i, 4, Wo, Ho, p, ow, oh, b);
     float f[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {

@@ -587,3 +587,25 @@ def test_depthwise_on_tensor_cores(B, H, W, Cc, xmode, flip):
     ref = F.conv2d(act.permute(0, 3, 1, 2), wq.reshape(3, 3, Cc).permute(2, 0, 1)[:, None], padding=1, groups=Cc).permute(0, 2, 3, 1)
     err = float((y.float() - ref).norm() / ref.norm())
     assert err < 1e-2, err
+
+
+@pytest.mark.parametrize("B,H,W,cin,cout", [(2, 16, 16, 64, 64), (1, 16, 16, 256, 256), (2, 20, 12, 64, 128), (3, 48, 40, 32, 64),
+                                             (2, 32, 24, 128, 32)])
+def test_wgrad_halo_3x3(B, H, W, cin, cout):
+    """3x3 weight gradient from ONE halo tile per 128 pixels (nine MN-major windows, taps kw and kw+1 as consecutive M
+    blocks) == autograd of F.conv2d; two calls accumulate (the partial tiles are ADDED to the arena)."""
+    import os
+    os.environ["CRACKFL_WGRAD_HALO"] = "2"  # (read once per process: forces the halo kernel for every eligible shape)
+    L, lib = _lib()
+    torch.manual_seed(3)
+    x = torch.randn(B, H, W, cin, device="cuda").bfloat16()
+    dy = torch.randn(B, H, W, cout, device="cuda").bfloat16()
+    dw = torch.zeros(9, cin, cout, device="cuda")
+    for _ in range(2):
+        L.check(lib.crackfl_wgrad_tc(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), B, H, W, cin, cout, 9, cin * cout, cout, 1, _st()))
+    torch.cuda.synchronize()
+    w = torch.zeros(cout, cin, 3, 3, device="cuda", requires_grad=True)
+    F.conv2d(x.float().permute(0, 3, 1, 2), w, padding=1).backward(dy.float().permute(0, 3, 1, 2))
+    ref = w.grad.permute(2, 3, 1, 0).reshape(9, cin, cout)
+    err = float((dw / 2 - ref).norm() / ref.norm())
+    assert err < 1e-2, err
