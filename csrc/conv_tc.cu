@@ -481,16 +481,22 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
         const int sub = col / a.sub_w, cin_sub = col % a.sub_w;
         const uint32_t chunk = (uint32_t)(cin_sub >> 3), within = (uint32_t)(cin_sub & 7) * 2u;
         const uint32_t colbase = obuf + sub * sub_bytes + within;
-        const int r0 = s_rgrp * s_rows;
-#pragma unroll 4
-        for (int rr = 0; rr < s_rows; ++rr) {
-          const int rw_ = r0 + rr;
-          const uint32_t xv = (a.sub_w == 64) ? (uint32_t)(rw_ & 7) : (uint32_t)((rw_ >> 1) & 3);
-          uint32_t w;
-          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(colbase + (uint32_t)rw_ * row_bytes + ((chunk ^ xv) << 4)));
-          const f2_t x = bf2_to_f2(w);
-          cs1 = fadd2(cs1, x);
-          cs2 = ffma2(x, x, cs2);
+        // rows of a thread start at a multiple of 8 and s_rows (= BN / 4) is a multiple of 8: the swizzle term of row
+        // r0 + i only depends on i & 7, so the eight chunk offsets are tile-invariant and the loop body is load + unpack +
+        // two packed adds (the first version recomputed the swizzled address per row: ~13 instructions per row, as many
+        // instructions per tile as the rest of the epilogue - ncu source page of conv_tc_fwd_v2_k)
+        uint32_t raddr = colbase + (uint32_t)(s_rgrp * s_rows) * row_bytes;
+        for (int rr = 0; rr < s_rows; rr += 8) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const uint32_t xv = (a.sub_w == 64) ? (uint32_t)i : (uint32_t)(i >> 1);
+            uint32_t w;
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(raddr + (uint32_t)i * row_bytes + ((chunk ^ xv) << 4)));
+            const f2_t x = bf2_to_f2(w);
+            cs1 = fadd2(cs1, x);
+            cs2 = ffma2(x, x, cs2);
+          }
+          raddr += 8u * row_bytes;
         }
       }
     }
@@ -804,16 +810,22 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
         const int sub = col / a.sub_w, cin_sub = col % a.sub_w;
         const uint32_t chunk = (uint32_t)(cin_sub >> 3), within = (uint32_t)(cin_sub & 7) * 2u;
         const uint32_t colbase = obuf + sub * sub_bytes + within;
-        const int r0 = s_rgrp * s_rows;
-#pragma unroll 4
-        for (int rr = 0; rr < s_rows; ++rr) {
-          const int rw_ = r0 + rr;
-          const uint32_t xv = (a.sub_w == 64) ? (uint32_t)(rw_ & 7) : (uint32_t)((rw_ >> 1) & 3);
-          uint32_t w;
-          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(colbase + (uint32_t)rw_ * row_bytes + ((chunk ^ xv) << 4)));
-          const f2_t x = bf2_to_f2(w);
-          cs1 = fadd2(cs1, x);
-          cs2 = ffma2(x, x, cs2);
+        // rows of a thread start at a multiple of 8 and s_rows (= BN / 4) is a multiple of 8: the swizzle term of row
+        // r0 + i only depends on i & 7, so the eight chunk offsets are tile-invariant and the loop body is load + unpack +
+        // two packed adds (the first version recomputed the swizzled address per row: ~13 instructions per row, as many
+        // instructions per tile as the rest of the epilogue - ncu source page of conv_tc_fwd_v2_k)
+        uint32_t raddr = colbase + (uint32_t)(s_rgrp * s_rows) * row_bytes;
+        for (int rr = 0; rr < s_rows; rr += 8) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const uint32_t xv = (a.sub_w == 64) ? (uint32_t)i : (uint32_t)(i >> 1);
+            uint32_t w;
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(raddr + (uint32_t)i * row_bytes + ((chunk ^ xv) << 4)));
+            const f2_t x = bf2_to_f2(w);
+            cs1 = fadd2(cs1, x);
+            cs2 = ffma2(x, x, cs2);
+          }
+          raddr += 8u * row_bytes;
         }
       }
     }
@@ -1266,16 +1278,22 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k
         const int sub = col / a.sub_w, cin_sub = col % a.sub_w;
         const uint32_t chunk = (uint32_t)(cin_sub >> 3), within = (uint32_t)(cin_sub & 7) * 2u;
         const uint32_t colbase = obuf + sub * sub_bytes + within;
-        const int r0 = s_rgrp * s_rows;
-#pragma unroll 4
-        for (int rr = 0; rr < s_rows; ++rr) {
-          const int rw_ = r0 + rr;
-          const uint32_t xv = (a.sub_w == 64) ? (uint32_t)(rw_ & 7) : (uint32_t)((rw_ >> 1) & 3);
-          uint32_t w;
-          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(colbase + (uint32_t)rw_ * row_bytes + ((chunk ^ xv) << 4)));
-          const f2_t x = bf2_to_f2(w);
-          cs1 = fadd2(cs1, x);
-          cs2 = ffma2(x, x, cs2);
+        // rows of a thread start at a multiple of 8 and s_rows (= BN / 4) is a multiple of 8: the swizzle term of row
+        // r0 + i only depends on i & 7, so the eight chunk offsets are tile-invariant and the loop body is load + unpack +
+        // two packed adds (the first version recomputed the swizzled address per row: ~13 instructions per row, as many
+        // instructions per tile as the rest of the epilogue - ncu source page of conv_tc_fwd_v2_k)
+        uint32_t raddr = colbase + (uint32_t)(s_rgrp * s_rows) * row_bytes;
+        for (int rr = 0; rr < s_rows; rr += 8) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const uint32_t xv = (a.sub_w == 64) ? (uint32_t)i : (uint32_t)(i >> 1);
+            uint32_t w;
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(raddr + (uint32_t)i * row_bytes + ((chunk ^ xv) << 4)));
+            const f2_t x = bf2_to_f2(w);
+            cs1 = fadd2(cs1, x);
+            cs2 = ffma2(x, x, cs2);
+          }
+          raddr += 8u * row_bytes;
         }
       }
     }
