@@ -368,7 +368,8 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
     const int r = q * 32 + lane;
     const int tw = r % a.g.TW, th = (r / a.g.TW) % a.g.TH, tb = r / (a.g.TW * a.g.TH);
     const int et = threadIdx.x - 64;  // 0..255 among the epilogue threads
-    const int nsub = a.BN / a.sub_w;
+    const int sub_sh = a.sub_w == 64 ? 6 : 5;
+    const int nsub = a.BN >> sub_sh;
     const uint32_t sub_bytes = 128u * (uint32_t)a.sub_w * 2u;
     const uint32_t row_bytes = (uint32_t)a.sub_w * 2u;
     // BN statistics are accumulated per CTA across all its tiles of one n-tile (registers: lane <-> column) and
@@ -451,7 +452,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
           for (int j = 0; j < 32; ++j) v[j] = 0.f;
         }
         // bf16 pack + swizzled staging store (row r of sub-tile c0 / sub_w)
-        const int sub = c0 / a.sub_w, cin_sub = c0 % a.sub_w;
+        const int sub = c0 >> sub_sh, cin_sub = c0 & (a.sub_w - 1);  // sub_w is 64 or 32: no divide sequence per chunk
         const uint32_t rowaddr = obuf + sub * sub_bytes + (uint32_t)r * row_bytes;
         const uint32_t xorv = (a.sub_w == 64) ? (uint32_t)(r & 7) : (uint32_t)((r >> 1) & 3);
 #pragma unroll
@@ -478,7 +479,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v2_k(const __gri
       if (a.stats) {
         // the staged tile is complete (barrier above) and stays untouched until two tiles from now
         const int col = 2 * s_wcol;
-        const int sub = col / a.sub_w, cin_sub = col % a.sub_w;
+        const int sub = col >> sub_sh, cin_sub = col & (a.sub_w - 1);
         const uint32_t chunk = (uint32_t)(cin_sub >> 3), within = (uint32_t)(cin_sub & 7) * 2u;
         const uint32_t colbase = obuf + sub * sub_bytes + within;
         // rows of a thread start at a multiple of 8 and s_rows (= BN / 4) is a multiple of 8: the swizzle term of row
@@ -697,7 +698,8 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
     const int r = q * 32 + lane;
     const int tw = r % a.g.TW, th = (r / a.g.TW) % a.g.TH, tb = r / (a.g.TW * a.g.TH);
     const int et = threadIdx.x - 64;  // 0..255 among the epilogue threads
-    const int nsub = a.BN / a.sub_w;
+    const int sub_sh = a.sub_w == 64 ? 6 : 5;
+    const int nsub = a.BN >> sub_sh;
     const uint32_t sub_bytes = 128u * (uint32_t)a.sub_w * 2u;
     const uint32_t row_bytes = (uint32_t)a.sub_w * 2u;
     // BN statistics are accumulated per CTA across all its tiles of one n-tile (registers: lane <-> column) and
@@ -780,7 +782,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
           for (int j = 0; j < 32; ++j) v[j] = 0.f;
         }
         // bf16 pack + swizzled staging store (row r of sub-tile c0 / sub_w)
-        const int sub = c0 / a.sub_w, cin_sub = c0 % a.sub_w;
+        const int sub = c0 >> sub_sh, cin_sub = c0 & (a.sub_w - 1);  // sub_w is 64 or 32: no divide sequence per chunk
         const uint32_t rowaddr = obuf + sub * sub_bytes + (uint32_t)r * row_bytes;
         const uint32_t xorv = (a.sub_w == 64) ? (uint32_t)(r & 7) : (uint32_t)((r >> 1) & 3);
 #pragma unroll
@@ -807,7 +809,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS) conv_tc_fwd_v3_k(const __gri
       if (a.stats) {
         // the staged tile is complete (barrier above) and stays untouched until two tiles from now
         const int col = 2 * s_wcol;
-        const int sub = col / a.sub_w, cin_sub = col % a.sub_w;
+        const int sub = col >> sub_sh, cin_sub = col & (a.sub_w - 1);
         const uint32_t chunk = (uint32_t)(cin_sub >> 3), within = (uint32_t)(cin_sub & 7) * 2u;
         const uint32_t colbase = obuf + sub * sub_bytes + within;
         // rows of a thread start at a multiple of 8 and s_rows (= BN / 4) is a multiple of 8: the swizzle term of row
@@ -1165,7 +1167,8 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k
     const int r = q * 32 + lane;
     const int tw = r % a.g.TW, th = (r / a.g.TW) % a.g.TH, tb = r / (a.g.TW * a.g.TH);
     const int et = threadIdx.x - 64;  // 0..255 among the epilogue threads
-    const int nsub = a.BN / a.sub_w;
+    const int sub_sh = a.sub_w == 64 ? 6 : 5;
+    const int nsub = a.BN >> sub_sh;
     const uint32_t sub_bytes = 128u * (uint32_t)a.sub_w * 2u;
     const uint32_t row_bytes = (uint32_t)a.sub_w * 2u;
     // BN statistics are accumulated per CTA across all its tiles of one n-tile (registers: lane <-> column) and
@@ -1248,7 +1251,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k
           for (int j = 0; j < 32; ++j) v[j] = 0.f;
         }
         // bf16 pack + swizzled staging store (row r of sub-tile c0 / sub_w)
-        const int sub = c0 / a.sub_w, cin_sub = c0 % a.sub_w;
+        const int sub = c0 >> sub_sh, cin_sub = c0 & (a.sub_w - 1);  // sub_w is 64 or 32: no divide sequence per chunk
         const uint32_t rowaddr = obuf + sub * sub_bytes + (uint32_t)r * row_bytes;
         const uint32_t xorv = (a.sub_w == 64) ? (uint32_t)(r & 7) : (uint32_t)((r >> 1) & 3);
 #pragma unroll
@@ -1275,7 +1278,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k
       if (a.stats) {
         // the staged tile is complete (barrier above) and stays untouched until two tiles from now
         const int col = 2 * s_wcol;
-        const int sub = col / a.sub_w, cin_sub = col % a.sub_w;
+        const int sub = col >> sub_sh, cin_sub = col & (a.sub_w - 1);
         const uint32_t chunk = (uint32_t)(cin_sub >> 3), within = (uint32_t)(cin_sub & 7) * 2u;
         const uint32_t colbase = obuf + sub * sub_bytes + within;
         // rows of a thread start at a multiple of 8 and s_rows (= BN / 4) is a multiple of 8: the swizzle term of row
@@ -1385,6 +1388,16 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
     if (warp == 0) {
       // ---- producer: uniform control flow, one elected lane issues (see tc_common.cuh)
       uint32_t s = 0, ph = 0;
+      // (tap, chunk) of this CTA's M blocks: fixed for the whole pixel range, so the divisions are done once, not per stage
+      int m_c[4], m_dh[4], m_dw[4];
+#pragma unroll
+      for (int m = 0; m < 4; ++m) {
+        const int blk = min(group * a.mblk + m, a.total_blocks - 1);
+        const int t = blk / cchunks;
+        m_c[m] = (blk - t * cchunks) * a.cw;
+        m_dh[m] = a.taps == 9 ? t / 3 - 1 : 0;
+        m_dw[m] = a.taps == 9 ? t % 3 - 1 : 0;
+      }
       for (int it = 0; it < iters; ++it) {
         mbar_wait(empty0 + 8u * s, ph ^ 1u);
         int tile = tile_begin + it;
@@ -1396,12 +1409,9 @@ __global__ void __launch_bounds__(192) wgrad_tc_k(const __grid_constant__ CUtens
         const uint32_t sa = base + s * stage_bytes, sb = sa + a_bytes;
         if (elect_one()) {
           mbar_expect_tx(full0 + 8u * s, (uint32_t)nload * ablk_bytes + b_bytes);
-          for (int m = 0; m < nload; ++m) {
-            const int blk = min(group * a.mblk + m, a.total_blocks - 1);
-            const int t = blk / cchunks, c = blk % cchunks;
-            const int dh = a.taps == 9 ? t / 3 - 1 : 0, dw = a.taps == 9 ? t % 3 - 1 : 0;
-            tma_load_4d(sa + m * ablk_bytes, &tmX, full0 + 8u * s, c * a.cw, w0 + dw, h0 + dh, b0);
-          }
+#pragma unroll
+          for (int m = 0; m < 4; ++m)
+            if (m < nload) tma_load_4d(sa + m * ablk_bytes, &tmX, full0 + 8u * s, m_c[m], w0 + m_dw[m], h0 + m_dh[m], b0);
           for (int nb = 0; nb < a.nblk; ++nb)
             tma_load_4d(sb + nb * bblk_bytes, &tmDY, full0 + 8u * s, n0 + nb * a.nw, w0, h0, b0);
         }

@@ -646,8 +646,11 @@ __global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : 3) bn_bwd_apply_k(const _
     float yv[2][8], dz[2][8];
     unpack8(ldg16(y + gi * 8), yv[0]);
     if (has2) unpack8(ldg16(y + gj * 8), yv[1]);
-    load_dz<MODE>(g, arg, gi / c8, cv, c8, H, W, yv[0], sc, sh, dz[0]);
-    if (has2) load_dz<MODE>(g, arg, gj / c8, cv, c8, H, W, yv[1], sc, sh, dz[1]);
+    // (DIRECT / RELU sources only need the flat index back: the pixel index is computed with a shift, the division is
+    //  kept for the pooled source whose shapes need not be powers of two)
+    const int lc8 = ck_log2_or_neg(c8);
+    load_dz<MODE>(g, arg, lc8 >= 0 ? (gi >> lc8) : gi / c8, cv, c8, H, W, yv[0], sc, sh, dz[0]);
+    if (has2) load_dz<MODE>(g, arg, lc8 >= 0 ? (gj >> lc8) : gj / c8, cv, c8, H, W, yv[1], sc, sh, dz[1]);
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
       if (u == 1 && !has2) break;
