@@ -398,25 +398,32 @@ __global__ void __launch_bounds__(TPB) pool_add_fwd_k(const __nv_bfloat16* __res
     int bi[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; bi[j] = 0; }
+    // all nine window loads (and the residual) are issued before the first compare: the first version loaded, compared,
+    // loaded ... behind `continue`s, one dependent DRAM round trip per tap (ncu: long-scoreboard stall on every unpack).
+    // Taps that fall off the bottom / right edge re-read the window's first pixel and are skipped in the compare.
+    uint4 win[9];
+    const int ybase = (((int)b * H + 2 * oh) * W + 2 * ow) * c8 + cv;
 #pragma unroll
-    for (int kh = 0; kh < 3; ++kh) {
-      const int ih = 2 * oh + kh;
-      if (ih >= H) continue;
+    for (int t = 0; t < 9; ++t) {
+      const int kh = t / 3, kw = t - kh * 3;
+      const bool ok = 2 * oh + kh < H && 2 * ow + kw < W;
+      win[t] = ldg16(y + (ok ? ybase + (kh * W + kw) * c8 : ybase) * 8);
+    }
+    const uint4 rraw = ldg16(res + g * 8);
 #pragma unroll
-      for (int kw = 0; kw < 3; ++kw) {
-        const int iw = 2 * ow + kw;
-        if (iw >= W) continue;
-        float f[8];
-        unpack8(ldg16(y + ((((int)b * H + ih) * W + iw) * c8 + cv) * 8), f);
+    for (int t = 0; t < 9; ++t) {
+      const int kh = t / 3, kw = t - kh * 3;
+      if (2 * oh + kh >= H || 2 * ow + kw >= W) continue;
+      float f[8];
+      unpack8(win[t], f);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float z = fmaf(f[j], sc[j], sh[j]);
-          if (z > best[j]) { best[j] = z; bi[j] = kh * 3 + kw; }
-        }
+      for (int j = 0; j < 8; ++j) {
+        const float z = fmaf(f[j], sc[j], sh[j]);
+        if (z > best[j]) { best[j] = z; bi[j] = t; }
       }
     }
     float r[8];
-    unpack8(ldg16(res + g * 8), r);
+    unpack8(rraw, r);
 #pragma unroll
     for (int j = 0; j < 8; ++j) best[j] += r[j];
     const uint4 v = pack8(best);
@@ -703,15 +710,29 @@ __global__ void __launch_bounds__(TPB, 2) pool_bwd_bn_k(const __nv_bfloat16* __r
 #pragma unroll
       for (int e = 0; e < 8; ++e) d[q][e] = 0.f;
     // window (i + di, j + dj), di, dj in {0, -1}; pixel (r, c) of the 2x2 block sits at offset (r - 2di)*3 + (c - 2dj)
+    // the four windows' arg-max bytes and gradients, and the four y vectors of the 2x2 block, are all requested before
+    // the first use (the first version loaded and consumed them one by one behind `continue`s: one dependent DRAM round
+    // trip per window and per pixel - ncu: long-scoreboard on the first unpack after every load)
+    uint2 aw[4];
+    uint4 gw[4], yw[4];
+#pragma unroll
+    for (int wi = 0; wi < 4; ++wi) {
+      const int qi = max(i - (wi >> 1), 0), qj = max(j - (wi & 1), 0);  // clamped: an off-image window is skipped below
+      const int qv = ((b * Ho + qi) * Wo + qj) * c8 + cv;
+      aw[wi] = __ldg(reinterpret_cast<const uint2*>(arg + (size_t)qv * 8));
+      gw[wi] = ldg16(g + (size_t)qv * 8);
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      yw[q] = ldg16(y + (((size_t)(b * H + 2 * i + (q >> 1)) * W + 2 * j + (q & 1)) * c8 + cv) * 8);
 #pragma unroll
     for (int wi = 0; wi < 4; ++wi) {
       const int di = -(wi >> 1), dj = -(wi & 1);
       const int qi = i + di, qj = j + dj;
       if (qi < 0 || qj < 0) continue;
-      const int qv = ((b * Ho + qi) * Wo + qj) * c8 + cv;
-      const uint2 a = __ldg(reinterpret_cast<const uint2*>(arg + (size_t)qv * 8));
+      const uint2 a = aw[wi];
       float gq[8];
-      unpack8(ldg16(g + (size_t)qv * 8), gq);
+      unpack8(gw[wi], gq);
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const int r = q >> 1, c = q & 1;
@@ -730,7 +751,7 @@ __global__ void __launch_bounds__(TPB, 2) pool_bwd_bn_k(const __nv_bfloat16* __r
       const int h = 2 * i + (q >> 1), w = 2 * j + (q & 1);
       const size_t v = ((size_t)(b * H + h) * W + w) * c8 + cv;
       float yv[8];
-      unpack8(ldg16(y + v * 8), yv);
+      unpack8(yw[q], yv);
       // the reductions see the bf16-rounded dz, exactly what the apply pass will read back
       const uint4 pk = pack8(d[q]);
       float dr[8];
