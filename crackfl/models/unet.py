@@ -420,6 +420,22 @@ class UNetEngine:
         self._fins.append(f)
         return C.byref(f)
 
+    def _bn_eval_all(self, prog):
+        """Inference: scale/shift tables of all BN layers from the moving statistics, one launch."""
+        if getattr(self, "_bn_eval_descs", None) is None:
+            ts = self.spec.tensors
+            ds = []
+            for l in self.bn_layers:
+                g, bt, rm, rv = l.tensors
+                ds.append(L.BnEvalDesc(gamma_off=ts[g].offset, beta_off=ts[bt].offset, mean_off=ts[rm].offset,
+                                       var_off=ts[rv].offset, bn_off=self.bn_p[l.name], C=l.cout, pad_=0))
+            arr = (L.BnEvalDesc * len(ds))(*ds)
+            self._bn_eval_descs = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).clone().to(self.dev)
+            self._bufs["bn_eval_descs"] = self._bn_eval_descs
+        prog.append((self.lib.crackfl_bn_eval_prepare_all, (self.arena.data_ptr(), self.bn_params.data_ptr(),
+                                                            self._bn_eval_descs.data_ptr(), len(self.bn_layers),
+                                                            self.spec.bn_eps)))
+
     def _bn_eval(self, prog, bnl):
         g, bt, rm, rv = bnl.tensors
         prog.append((self.lib.crackfl_bn_eval_prepare, (self.P(g), self.P(bt), self.P(rm), self.P(rv), self._bnptr(bnl.name),
@@ -441,9 +457,10 @@ class UNetEngine:
                         prog.append((lib.crackfl_bn_stats, (y, self._zptr(bnl.name, "stats"), P, bnl.cout)))
                 else:
                     self._bn_train(prog, bnl, y, P, stats_done)
-            else:
-                self._bn_eval(prog, bnl)
+            # (eval: every layer's table was prepared by the single launch at the head of the schedule)
 
+        if not training:
+            self._bn_eval_all(prog)
         # bf16 GEMM operands of this step's weights: next to the im2col / entry kernels on the auxiliary stream
         prog.append((lib.crackfl_weight_prep, (self.arena.data_ptr(), self.ops_buf.data_ptr(), self.desc_dev.data_ptr(),
                                                self.num_desc), "aux"))

@@ -29,6 +29,11 @@ class BnFin(C.Structure):
                 ("count", f32), ("eps", f32), ("momentum", f32)]
 
 
+class BnEvalDesc(C.Structure):
+    _fields_ = [("gamma_off", i64), ("beta_off", i64), ("mean_off", i64), ("var_off", i64), ("bn_off", i64), ("C", i32),
+                ("pad_", i32)]
+
+
 class DwDiagDesc(C.Structure):
     _fields_ = [("src_off", i64), ("dst_off", i64), ("C", i32), ("kc", i32), ("flip", i32), ("pad_", i32)]
 
@@ -56,6 +61,7 @@ _SIGS = {
     "crackfl_bn_stats": [vp, vp, i64, i32, vp],
     "crackfl_bn_finalize": [vp, vp, vp, vp, vp, vp, i32, f32, f32, f32, vp],
     "crackfl_bn_eval_prepare": [vp, vp, vp, vp, vp, i32, f32, vp],
+    "crackfl_bn_eval_prepare_all": [vp, vp, vp, i32, f32, vp],
     "crackfl_bn_act": [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_bn_bwd_reduce": [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "crackfl_bn_bwd_apply": [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],

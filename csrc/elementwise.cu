@@ -219,6 +219,24 @@ __global__ void bn_eval_prepare_k(const float* __restrict__ gamma, const float* 
   bn[3 * C + c] = invstd;
 }
 
+// the same for every BN layer of the model in ONE launch (blockIdx.y = layer): the eval / predict forward used to spend 15
+// launches of ~4.5 us on these tables
+__global__ void bn_eval_prepare_all_k(const float* __restrict__ arena, float* __restrict__ bn_params,
+                                      const crackfl_bn_eval_desc* __restrict__ descs, float eps) {
+  ck::pdl_enter();
+  const crackfl_bn_eval_desc d = descs[blockIdx.y];
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < d.C; c += gridDim.x * blockDim.x) {
+    const float rm = arena[d.mean_off + c];
+    const float invstd = rsqrtf(arena[d.var_off + c] + eps);
+    const float sc = arena[d.gamma_off + c] * invstd;
+    float* bn = bn_params + d.bn_off;
+    bn[c] = sc;
+    bn[d.C + c] = arena[d.beta_off + c] - rm * sc;
+    bn[2 * d.C + c] = rm;
+    bn[3 * d.C + c] = invstd;
+  }
+}
+
 // out = [relu](y*scale+shift); optional compact copy of the even pixels (input of the 1x1 s2 residual conv)
 __global__ void __launch_bounds__(TPB, 4) bn_act_k(const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
                                                    __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ even,
@@ -1374,6 +1392,15 @@ int crackfl_bn_finalize(const float* stats, const float* gamma, const float* bet
 int crackfl_bn_eval_prepare(const float* gamma, const float* beta, const float* run_mean, const float* run_var, float* bn,
                             int C, float eps, cudaStream_t st) {
   ck::launch(bn_eval_prepare_k, (C + 127) / 128, 128, 0, st, gamma, beta, run_mean, run_var, bn, C, eps);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_bn_eval_prepare_all(const float* arena, float* bn_params, const crackfl_bn_eval_desc* descs_dev, int n, float eps,
+                                cudaStream_t st) {
+  if (n <= 0) return 0;
+  dim3 grid(2, n);
+  ck::launch(bn_eval_prepare_all_k, grid, 128, 0, st, arena, bn_params, descs_dev, eps);
   CK_LAUNCH_CHECK();
   return 0;
 }

@@ -47,6 +47,13 @@ int crackfl_bn_finalize(const float* stats, const float* gamma, const float* bet
                         float* bn, int C, float count, float eps, float momentum, cudaStream_t stream);
 int crackfl_bn_eval_prepare(const float* gamma, const float* beta, const float* run_mean, const float* run_var, float* bn,
                             int C, float eps, cudaStream_t stream);
+/* every BN layer's inference table in one launch: offsets are element offsets into the fp32 parameter arena / the bn table */
+typedef struct {
+  long gamma_off, beta_off, mean_off, var_off, bn_off;
+  int C, pad_;
+} crackfl_bn_eval_desc;
+int crackfl_bn_eval_prepare_all(const float* arena, float* bn_params, const crackfl_bn_eval_desc* descs_dev, int n, float eps,
+                                cudaStream_t stream);
 int crackfl_bn_act(const void* y, const float* bn, void* out, void* even_or_null, int B, int H, int W, int C, int relu,
                    cudaStream_t stream);
 /* mode: 0 dz=g, 1 dz=g*1[bn(y)>0], 2 dz=maxpool-backward gather of g through `arg` */
