@@ -81,7 +81,12 @@ class UNetEngine:
         # halo load and the 128 x 128 B store go through the one TMA unit of the SM - which is what the CUDA-core stencil
         # already reaches, so it stays off: CRACKFL_XF_DEC=2 forces the prologue for every layer, CRACKFL_XF_DW=1 the
         # depthwise path)
-        self.xf_dec = int(os.environ.get("CRACKFL_XF_DEC", "1"))
+        # K2: BN-backward apply inside the decoder convs' input-gradient kernels (no bn_bwd_apply pass; 1 = blocks with
+        # f >= 64, 2 = all).  Measured on the full step: 1.160 ms with it, 1.116 without (two halo tiles per stage through
+        # six transform warps cost more than the bn_bwd_apply pass they remove), so it is off unless asked for.
+        self.xf_bwd = int(os.environ.get("CRACKFL_XF_BWD", "0"))
+        # K1: BN-apply + ReLU as the prologue of the decoder's second conv.  1.122 ms with it, 1.115 without: off by default.
+        self.xf_dec = int(os.environ.get("CRACKFL_XF_DEC", "0"))
         self.xf_dw = os.environ.get("CRACKFL_XF_DW", "0") != "0"
         # partial tiles added straight into the gradient arena with vector reductions: no workspace, no reduction launch
         # (22 launches fewer per step, 1.263 vs 1.287 ms/step; CRACKFL_WGRAD_ATOMIC=0 restores workspace + reduction)
@@ -616,22 +621,35 @@ class UNetEngine:
             # BN2 (no ReLU after it)
             prog.append((lib.crackfl_bn_bwd_reduce, (b(p + "ds"), 0, b(p + "y2"), self._bnptr(bn2.name),
                                                      self._zptr(bn2.name, "sums"), B, r, rw, f, 0)))
-            prog.append((lib.crackfl_bn_bwd_apply, (b(p + "ds"), 0, b(p + "y2"), self._bnptr(bn2.name),
-                                                    self._zptr(bn2.name, "sums"), b(p + "dy2"), self.G(bn2.tensors[0]),
-                                                    self.G(bn2.tensors[1]), B, r, rw, f, 0)))
+            xf_b = self.conv_impl == "tc" and self.xf_bwd and (f >= 64 or self.xf_bwd >= 2) and r >= 16 and rw >= 8
+            if xf_b:
+                # K2: dy2 = BN-backward(ds, y2) is formed inside the input-gradient conv (and written out once for the
+                # weight gradient); the launch also writes dgamma / dbeta
+                prog.append((lib.crackfl_conv_tc_bnbwd, (b(p + "ds"), b(p + "y2"), self.op_ptr(ct2.name + ".d"), b(p + "da1"),
+                                                         B, r, rw, f, f, self._bnptr(bn2.name), self._zptr(bn2.name, "sums"), 0,
+                                                         b(p + "dy2"), self.G(bn2.tensors[0]), self.G(bn2.tensors[1]))))
+            else:
+                prog.append((lib.crackfl_bn_bwd_apply, (b(p + "ds"), 0, b(p + "y2"), self._bnptr(bn2.name),
+                                                        self._zptr(bn2.name, "sums"), b(p + "dy2"), self.G(bn2.tensors[0]),
+                                                        self.G(bn2.tensors[1]), B, r, rw, f, 0)))
+                self._gemm(prog, b(p + "dy2"), ct2.name + ".d", 0, 0, b(p + "da1"), B, r, rw)
             oi = ts[ct2.tensors[0]]
-            self._gemm(prog, b(p + "dy2"), ct2.name + ".d", 0, 0, b(p + "da1"), B, r, rw)
             # Keras (kh,kw,out,in) kernel: with the operands swapped (A = dY, B = X) the tile columns run along "in", the
             # contiguous axis of the arena, so the split reduction writes coalesced; the tap flip then cancels out
             self._wgrad(prog, b(p + "dy2"), b(p + "a1"), self.G(ct2.tensors[0]), B, r, rw, f, f, 9, f * f, f, 1)
             # BN1 + ReLU
             prog.append((lib.crackfl_bn_bwd_reduce, (b(p + "da1"), 0, b(p + "y1"), self._bnptr(bn1.name),
                                                      self._zptr(bn1.name, "sums"), B, r, rw, f, 1)))
-            prog.append((lib.crackfl_bn_bwd_apply, (b(p + "da1"), 0, b(p + "y1"), self._bnptr(bn1.name),
-                                                    self._zptr(bn1.name, "sums"), b(p + "dy1"), self.G(bn1.tensors[0]),
-                                                    self.G(bn1.tensors[1]), B, r, rw, f, 1)))
             a0 = "a0_0" if j == 0 else p + "a0"
-            self._gemm(prog, b(p + "dy1"), ct1.name + ".d", 0, 0, b(p + "da0"), B, r, rw)
+            if xf_b:
+                prog.append((lib.crackfl_conv_tc_bnbwd, (b(p + "da1"), b(p + "y1"), self.op_ptr(ct1.name + ".d"), b(p + "da0"),
+                                                         B, r, rw, f, cin, self._bnptr(bn1.name), self._zptr(bn1.name, "sums"), 1,
+                                                         b(p + "dy1"), self.G(bn1.tensors[0]), self.G(bn1.tensors[1]))))
+            else:
+                prog.append((lib.crackfl_bn_bwd_apply, (b(p + "da1"), 0, b(p + "y1"), self._bnptr(bn1.name),
+                                                        self._zptr(bn1.name, "sums"), b(p + "dy1"), self.G(bn1.tensors[0]),
+                                                        self.G(bn1.tensors[1]), B, r, rw, f, 1)))
+                self._gemm(prog, b(p + "dy1"), ct1.name + ".d", 0, 0, b(p + "da0"), B, r, rw)
             self._wgrad(prog, b(p + "dy1"), b(a0), self.G(ct1.tensors[0]), B, r, rw, f, cin, 9, f * cin, cin, 1)
             self._wgrad(prog, b(src_res), b(drl), self.G(res.tensors[0]), B, lr_, lrw, cin, f, 1, 0, f, 1)
             prog.append((lib.crackfl_colsum, (b(drl), self.G(res.tensors[1]), B * lr_ * lrw, f), os.environ.get("CRACKFL_COLSUM_STREAM", "side3")))

@@ -108,6 +108,7 @@ _SIGS = {
     "crackfl_synth_cracks": [vp, vp, i32, i32, i32, C.c_uint, vp],
     "crackfl_measure_masks": [vp, vp, i32, i32, i32, i32, vp],
     "crackfl_conv_tc_xf": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, C.POINTER(BnFin), vp, i32, vp],
+    "crackfl_conv_tc_bnbwd": [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, i32, vp, vp, vp, vp],
     "crackfl_dw_diag_prep": [vp, vp, vp, i32, vp],
     "crackfl_fedagg": [C.POINTER(FedAggParams), i32, vp],
     "crackfl_ipc_export": [vp, vp],

@@ -74,10 +74,20 @@ class DeviceAggregator:
         st = torch.cuda.current_stream(self.dev)
         with torch.cuda.device(self.dev):
             self.master.copy_(torch.from_numpy(wio.flatten(global_w, self.spec)))
-            for k, u in enumerate(updates):  # K16: H2D staging
-                self.host.copy_(torch.from_numpy(wio.flatten(u, self.spec)))
-                self.stage_f32[k].copy_(self.host, non_blocking=True)
-                st.synchronize()
+            # K16: H2D staging.  Two pinned buffers in turn: flattening update k+1 on the host overlaps the copy of
+            # update k, and only the copy that last read a buffer is waited for (the first version synchronised the
+            # stream once per client).
+            if not hasattr(self, "_pin"):
+                self._pin = [self.host, torch.empty_like(self.host).pin_memory()]
+                self._pin_ev = [None, None]
+            for k, u in enumerate(updates):
+                i = k & 1
+                if self._pin_ev[i] is not None:
+                    self._pin_ev[i].synchronize()
+                np.copyto(self._pin[i].numpy(), wio.flatten(u, self.spec))
+                self.stage_f32[k].copy_(self._pin[i], non_blocking=True)
+                self._pin_ev[i] = torch.cuda.Event()
+                self._pin_ev[i].record(st)
                 if self.payload == "bf16_delta":
                     L.check(self.lib.crackfl_publish_delta(self.stage_f32[k].data_ptr(), self.master.data_ptr(),
                                                            self.stage_bf16[k].data_ptr(), self.n, st.cuda_stream))

@@ -866,6 +866,13 @@ struct ConvArgsX {
   const float* bn;           // [scale C | shift C] (xmode 2, fin.stats == NULL)
   crackfl_bn_fin fin;        // or: derive them from the statistics here and let block 0 publish them
   __nv_bfloat16* side;       // optional: the transformed activation is also written out (B,H,W,Cin), by the n-tile-0 CTAs
+  // xmode 4 / 5 (K2): the input is BN-backward-applied on the fly, dy = A*dz + B*y + C per channel (5: dz masked by
+  // bn(y) > 0 first); dz comes through tmA, y through tmA2 into the second half of every halo stage
+  const float* sums;         // [sum dz C | sum dz*(y-mean) C] of the BN-backward reduce pass
+  float count;               // pixels per channel
+  float* dgamma;             // block 0 writes the BN parameter gradients, as bn_bwd_apply does
+  float* dbeta;
+  uint32_t a_pitch;          // bytes per halo ring slot: a_stage, or 2 * a_stage with two inputs
 };
 
 // "xf" variant of the halo kernel: four extra warps TRANSFORM every halo tile in shared memory between the TMA load and
@@ -881,17 +888,22 @@ struct ConvArgsX {
 // onto a single barrier; per tile the producer only streams halo tiles and the issuing thread fires its 9 * kc/16 MMAs
 // back to back (no per-tap barrier round trip, no re-streaming of the weights from L2 for every 128-pixel tile, which
 // for N = 32 was more traffic than the activations).  kc = 32 (Cin = 32) uses the SWIZZLE_64B flavour of the same trick.
-constexpr int XF_WARPS = 8;
-constexpr int XF_THREADS = XF_WARPS * 32;
-__global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k(const __grid_constant__ CUtensorMap tmA,
+// Two instantiations: one input (ReLU / BN-apply prologue: 8 transform warps, 576 threads) and two inputs (BN-backward
+// prologue: 6 transform warps, 512 threads and 128 registers each - with 8 warps the coefficient registers spilled).
+template <bool TWO_IN>
+__global__ void __launch_bounds__(64 + EPI_THREADS + (TWO_IN ? 6 : 8) * 32, 1) conv_tc_xf_k(const __grid_constant__ CUtensorMap tmA,
                                                         const __grid_constant__ CUtensorMap tmB,
-                                                        const __grid_constant__ CUtensorMap tmY, const ConvArgsX a) {
+                                                        const __grid_constant__ CUtensorMap tmY,
+                                                        const __grid_constant__ CUtensorMap tmA2, const ConvArgsX a) {
+  constexpr int XF_WARPS = TWO_IN ? 6 : 8;
+  constexpr int XF_THREADS = XF_WARPS * 32;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   // A ring: 2 halo tiles of (TH+2) x (TW+2) = 18 x 10 pixels x 64 channels (23040 B, padded to 23552);
   // B ring: a.stages weight tiles [BN][64] (one per (chunk, tap)); then 2 output staging buffers.
   constexpr uint32_t HALO_W = 10u;
-  const uint32_t A_STAGE = a.a_stage, A_BYTES = a.a_bytes, row_b = (uint32_t)a.kc * 2u;
+  const uint32_t A_STAGE = a.a_pitch, A_BYTES = a.a_bytes, row_b = (uint32_t)a.kc * 2u;
+  constexpr bool two_in = TWO_IN;
   const uint32_t b_bytes = (uint32_t)a.BN * row_b;
   const uint32_t bring = base + (uint32_t)a.astages * A_STAGE;
   const uint32_t out_bytes = 128u * (uint32_t)a.BN * 2u;
@@ -921,7 +933,7 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k
     for (int s = 0; s < a.astages; ++s) {
       mbar_init(fullA0 + 8u * s, 1);
       mbar_init(emptyA0 + 8u * s, 1);
-      mbar_init(xfA0 + 8u * s, XF_WARPS);  // one arrival per transform warp
+      mbar_init(xfA0 + 8u * s, TWO_IN ? 6 : 8);  // one arrival per transform warp
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull0 + 8u * s, 1);
@@ -942,6 +954,21 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k
   // BN scale / shift of the INPUT channels (xmode 2): from the published table, or straight from the statistics of the
   // producing conv (finalize folded in, as in the *_fin elementwise kernels; block 0 publishes table + moving statistics)
   float* xf_tab = reinterpret_cast<float*>(smem_raw + (stat_smem + 5120u - smem_u32(smem_raw)));  // [scale Cin | shift Cin]
+  if (a.xmode >= 4) {
+    // BN backward: dy = sc*is... per channel:  m1 = mean(dz), m2 = is * mean(dz * (y - mu));  dy = sc * (dz - m1 - xhat * m2)
+    //            = A * dz + B * y + C  with A = sc, B = -sc * is * m2, C = -sc * m1 - B * mu       (bn = [sc | sh | mu | is])
+    const float invn = 1.0f / a.count;
+    for (int c = threadIdx.x; c < a.Cin; c += blockDim.x) {
+      const float sc = a.bn[c], sh = a.bn[a.Cin + c], mu = a.bn[2 * a.Cin + c], is = a.bn[3 * a.Cin + c];
+      const float s1 = a.sums[c], s2 = a.sums[a.Cin + c];
+      const float m1 = s1 * invn, m2 = is * s2 * invn;
+      const float Bc = -sc * is * m2;
+      xf_tab[c] = sc; xf_tab[a.Cin + c] = Bc; xf_tab[2 * a.Cin + c] = -sc * m1 - Bc * mu;
+      xf_tab[3 * a.Cin + c] = sc; xf_tab[4 * a.Cin + c] = sh;  // forward BN (mask of xmode 5)
+      if (blockIdx.x == 0 && a.dgamma) { a.dbeta[c] = s1; a.dgamma[c] = is * s2; }
+    }
+    __syncthreads();
+  }
   if (a.xmode == 2) {
     for (int c = threadIdx.x; c < a.Cin; c += blockDim.x) {
       float scl, sft;
@@ -988,8 +1015,9 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k
         if (++ra_s == (uint32_t)a.astages) { ra_s = 0; ra_ph ^= 1u; }
         mbar_wait(emptyA0 + 8u * sa, pha ^ 1u);
         if (elect_one()) {
-          mbar_expect_tx(fullA0 + 8u * sa, A_BYTES);
+          mbar_expect_tx(fullA0 + 8u * sa, two_in ? 2u * A_BYTES : A_BYTES);
           tma_load_4d(base + sa * A_STAGE, &tmA, fullA0 + 8u * sa, (a.diag ? my_chunk : c) * a.kc, w0 - 1, h0 - 1, b0);  // halo: zero fill = padding
+          if (two_in) tma_load_4d(base + sa * A_STAGE + a.a_stage, &tmA2, fullA0 + 8u * sa, c * a.kc, w0 - 1, h0 - 1, b0);
         }
         __syncwarp();
         if (a.resident) continue;
@@ -1077,21 +1105,20 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k
     const int lane_ = threadIdx.x & 31;
     const int cpr = a.kc >> 3;                        // 16-byte chunks per halo pixel (8 or 4)
     const int j = xt & (cpr - 1), prow = xt / cpr;    // chunk column, first row
-    const int rstep = XF_THREADS / cpr;               // 32 (kc 64) or 64 (kc 32) rows per pass
+    const int rstep = XF_THREADS / cpr;               // 24 / 32 (kc 64) or 48 / 64 (kc 32) rows per pass: multiples of the swizzle period
     // SWIZZLE_128B: slot j of row p holds chunk j ^ (p & 7); SWIZZLE_64B (64-byte rows): j ^ ((p >> 1) & 3)
     const int lch = a.kc == 64 ? (j ^ (prow & 7)) : (j ^ ((prow >> 1) & 3));
     const uint32_t toff = (uint32_t)prow * row_b + (uint32_t)j * 16u;
     // per-thread row table, fixed for the whole kernel: halo row / column of the k-th row this thread visits, whether it
     // exists (p < 180) and whether it is an interior (= output) pixel; the tile loop only adds the tile origin
-    constexpr int XF_IT = 6;  // ceil(180 / 32); the 64-row passes of the 32-channel flavour need 3
-    int hrk[XF_IT], hck[XF_IT];
+    constexpr int XF_IT = TWO_IN ? 8 : 6;  // ceil(180 / rows per pass): 24 rows with 192 threads, 32 with 256 (kc 64)
     uint32_t live = 0, inter = 0;
 #pragma unroll
     for (int k = 0; k < XF_IT; ++k) {
       const int p = prow + k * rstep;
-      hrk[k] = p / (int)HALO_W; hck[k] = p - hrk[k] * (int)HALO_W;
+      const int hr = (p * 205) >> 11, hc = p - hr * 10;  // p / 10, exact for p < 1024 (kept out of registers: recomputed below)
       if (p < 180) live |= 1u << k;
-      if (p < 180 && hrk[k] >= 1 && hrk[k] <= a.g.TH && hck[k] >= 1 && hck[k] <= a.g.TW) inter |= 1u << k;
+      if (p < 180 && hr >= 1 && hr <= a.g.TH && hc >= 1 && hc <= a.g.TW) inter |= 1u << k;
     }
     const uint32_t kstride = (uint32_t)rstep * row_b;
     const long pix_c = (long)a.Cin;
@@ -1108,7 +1135,18 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k
         const uint32_t sa = ra_s, pha = ra_ph;
         if (++ra_s == (uint32_t)a.astages) { ra_s = 0; ra_ph ^= 1u; }
         const int cbase = (a.diag ? my_chunk : c) * a.kc + lch * 8;
-        f2_t sc2[4], sh2[4];
+        f2_t sc2[4], sh2[4], cb2[4], cc2[4];
+        if constexpr (TWO_IN) {
+          const float* tA = xf_tab + cbase;
+          const int Cn = a.Cin;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            sc2[e] = pk2(tA[2 * e], tA[2 * e + 1]);                         // A
+            cb2[e] = pk2(tA[Cn + 2 * e], tA[Cn + 2 * e + 1]);               // B
+            cc2[e] = pk2(tA[2 * Cn + 2 * e], tA[2 * Cn + 2 * e + 1]);       // C
+            sh2[e] = 0ull;
+          }
+        }
         if (a.xmode == 2) {
           const float4 s0 = *reinterpret_cast<const float4*>(xf_tab + cbase), s1 = *reinterpret_cast<const float4*>(xf_tab + cbase + 4);
           const float4 t0 = *reinterpret_cast<const float4*>(xf_tab + a.Cin + cbase);
@@ -1124,21 +1162,50 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k
           continue;
         }
         const uint32_t tbase = base + sa * A_STAGE + toff;
+        // four rows at a time: their loads are issued together, then transformed and stored (all eight at once spilled)
+#pragma unroll
+        constexpr int XF_B = TWO_IN ? 4 : XF_IT;
+#pragma unroll
+        for (int kb = 0; kb < XF_IT; kb += XF_B) {
         uint32_t v[XF_IT][4];
 #pragma unroll
-        for (int k = 0; k < XF_IT; ++k)
+        for (int k = kb; k < kb + XF_B; ++k)
           if (live >> k & 1u)
             asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[k][0]), "=r"(v[k][1]), "=r"(v[k][2]), "=r"(v[k][3])
                          : "r"(tbase + (uint32_t)k * kstride));
 #pragma unroll
-        for (int k = 0; k < XF_IT; ++k) {
+        for (int k = kb; k < kb + XF_B; ++k) {
           if (!(live >> k & 1u)) continue;
+          const int p_ = prow + k * rstep;
+          const int hr_ = (p_ * 205) >> 11, hc_ = p_ - hr_ * 10;
           bool inside = true;
           if (!all_in) {
-            const int ih = h0 + hrk[k], iw = w0 + hck[k];
+            const int ih = h0 + hr_, iw = w0 + hc_;
             inside = ih >= 0 && ih < a.H && iw >= 0 && iw < a.W;
           }
-          if (a.xmode == 1) {
+          if constexpr (TWO_IN) {
+            uint32_t y4[4];
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(y4[0]), "=r"(y4[1]), "=r"(y4[2]), "=r"(y4[3])
+                         : "r"(tbase + a.a_stage + (uint32_t)k * kstride));
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const f2_t yv = bf2_to_f2(y4[e]);
+              f2_t dzv = bf2_to_f2(v[k][e]);
+              if (a.xmode == 5) {  // dz passes only where the forward activation was positive
+                float z0, z1, d0, d1;
+                // (forward scale / shift stay in shared memory: keeping them in registers too made the kernel spill)
+                const f2_t ms = *reinterpret_cast<const f2_t*>(xf_tab + 3 * a.Cin + cbase + 2 * e);
+                const f2_t mt = *reinterpret_cast<const f2_t*>(xf_tab + 4 * a.Cin + cbase + 2 * e);
+                upk2(ffma2(yv, ms, mt), z0, z1);
+                upk2(dzv, d0, d1);
+                dzv = pk2(z0 > 0.f ? d0 : 0.f, z1 > 0.f ? d1 : 0.f);
+              }
+              const f2_t o = ffma2(sc2[e], dzv, ffma2(cb2[e], yv, cc2[e]));
+              float o0, o1;
+              upk2(o, o0, o1);
+              v[k][e] = inside ? ck::pack2(o0, o1) : 0u;  // zero outside the image: the padding of dy, not C
+            }
+          } else if (a.xmode == 1) {
 #pragma unroll
             for (int e = 0; e < 4; ++e) v[k][e] = relu_bf2(v[k][e]);  // zero fill stays zero
           } else if (inside) {
@@ -1152,8 +1219,9 @@ __global__ void __launch_bounds__(64 + EPI_THREADS + XF_THREADS, 1) conv_tc_xf_k
                        "r"(v[k][2]), "r"(v[k][3]) : "memory");
           if (do_side && inside && (inter >> k & 1u)) {
             uint4 o; o.x = v[k][0]; o.y = v[k][1]; o.z = v[k][2]; o.w = v[k][3];
-            ck::stg16(sbase + ((long)hrk[k] * a.W + hck[k]) * pix_c, o);
+            ck::stg16(sbase + ((long)hr_ * a.W + hc_) * pix_c, o);
           }
+        }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the MMA's reads
         __syncwarp();
@@ -2123,11 +2191,13 @@ v2_path:
 // or, when fin != NULL, derived from the BN statistics (block 0 then also publishes the table and the moving
 // statistics, like the *_fin elementwise launchers).  side != NULL: the activated input is also written out (the weight
 // gradient of this layer needs it).  diag: Wk is the [(C/kc)*9*kc][kc] matrix written by crackfl_dw_diag_prep, N == Cin.
-int crackfl_conv_tc_xf(const void* X, const void* Wk, const float* bias, const void* add, void* Y, float* stats, int B, int H,
-                       int W, int Cin, int N, int xmode, const float* bn, const crackfl_bn_fin* fin, void* side, int diag,
-                       cudaStream_t st) {
-  if (Cin % 32 || N % 32 || H < 16 || W < 8 || xmode < 1 || xmode > 3) return (int)cudaErrorInvalidValue;  // 3: profiling aid, tiles pass through untouched
+static int conv_tc_xf_impl(const void* X, const void* X2, const void* Wk, const float* bias, const void* add, void* Y,
+                           float* stats, int B, int H, int W, int Cin, int N, int xmode, const float* bn,
+                           const crackfl_bn_fin* fin, void* side, int diag, const float* sums, float count, float* dgamma,
+                           float* dbeta, cudaStream_t st) {
+  if (Cin % 32 || N % 32 || H < 16 || W < 8 || xmode < 1 || xmode > 5) return (int)cudaErrorInvalidValue;  // 3: profiling aid, tiles pass through untouched
   if (xmode == 2 && !bn && !fin) return (int)cudaErrorInvalidValue;
+  if (xmode >= 4 && (!X2 || !bn || !sums || diag || count <= 0.f)) return (int)cudaErrorInvalidValue;
   if (diag && N != Cin) return (int)cudaErrorInvalidValue;
   const int kc = (Cin % 64 == 0) ? 64 : 32;
   if (Cin % kc) return (int)cudaErrorInvalidValue;
@@ -2144,6 +2214,8 @@ int crackfl_conv_tc_xf(const void* X, const void* Wk, const float* bias, const v
   if (fin) a.fin = *fin;
   a.a_bytes = 180u * (uint32_t)kc * 2u;
   a.a_stage = (a.a_bytes + 1023u) & ~1023u;
+  a.a_pitch = xmode >= 4 ? 2u * a.a_stage : a.a_stage;
+  a.sums = sums; a.count = count; a.dgamma = dgamma; a.dbeta = dbeta;
   a.g.TW = 8; a.g.TH = 16; a.g.TB = 1;
   a.g.tiles_w = (W + 7) / 8; a.g.tiles_h = (H + 15) / 16; a.g.tiles_b = B;
   a.n_tiles_m = a.g.tiles_w * a.g.tiles_h * a.g.tiles_b;
@@ -2151,15 +2223,15 @@ int crackfl_conv_tc_xf(const void* X, const void* Wk, const float* bias, const v
   a.n_tiles_n = diag ? 1 : N / a.BN;
   const uint32_t b_bytes = (uint32_t)a.BN * (uint32_t)kc * 2u;
   const uint32_t out_bytes = 2u * 128u * (uint32_t)a.BN * 2u;
-  const uint32_t fixed = out_bytes + 12288u;  // staging + barriers + statistics scratch + bias + scale/shift table + slack
+  const uint32_t fixed = out_bytes + 16384u;  // staging + barriers + statistics scratch + bias + coefficient tables + slack
   const uint32_t lim1 = 220u * 1024u;
   const uint32_t wbytes = diag ? 9u * b_bytes : 9u * (uint32_t)Cin * (uint32_t)a.BN * 2u;
-  const bool resident = diag || (N == a.BN && wbytes + fixed + 2u * a.a_stage <= lim1);
+  const bool resident = diag || (N == a.BN && wbytes + fixed + 2u * a.a_pitch <= lim1);
   a.resident = resident ? 1 : 0;
   int stages;
   if (resident) {
     stages = diag ? 9 : 9 * (Cin / kc);
-    a.astages = (int)((lim1 - wbytes - fixed) / a.a_stage);
+    a.astages = (int)((lim1 - wbytes - fixed) / a.a_pitch);
     if (a.astages > 4) a.astages = 4;
     {
       static int dbg_ast = -1;  // tuning knob
@@ -2169,16 +2241,18 @@ int crackfl_conv_tc_xf(const void* X, const void* Wk, const float* bias, const v
     if (a.astages < 1) return (int)cudaErrorInvalidValue;
   } else {
     if (kc != 64) return (int)cudaErrorInvalidValue;  // the streaming variant is only set up for 64-channel chunks
-    a.astages = 3;
-    stages = (int)((lim1 - fixed - 3u * a.a_stage) / b_bytes);
+    a.astages = xmode >= 4 ? 2 : 3;
+    stages = (int)((lim1 - fixed - (uint32_t)a.astages * a.a_pitch) / b_bytes);
     if (stages > 9) stages = 9;
     if (stages < 2) return (int)cudaErrorInvalidValue;
   }
   a.stages = stages;
-  const size_t smem = (size_t)a.astages * a.a_stage + (size_t)stages * b_bytes + out_bytes + 1024 + 512 + 8192 + 2048;
-  CUtensorMap tmA, tmB, tmY;
+  const size_t smem = (size_t)a.astages * a.a_pitch + (size_t)stages * b_bytes + out_bytes + 1024 + 512 + 8192 + 2048 + 4096;
+  CUtensorMap tmA, tmB, tmY, tmA2;
   const int dA[4] = {Cin, W, H, B}, bA[4] = {kc, 10, 18, 1};
   int rc = get_map(X, 4, dA, bA, kc * 2, &tmA);
+  if (rc) return rc;
+  rc = get_map(X2 ? X2 : X, 4, dA, bA, kc * 2, &tmA2);
   if (rc) return rc;
   if (diag) {
     const int dB[2] = {kc, (Cin / kc) * 9 * kc}, bB[2] = {kc, kc};
@@ -2193,7 +2267,8 @@ int crackfl_conv_tc_xf(const void* X, const void* Wk, const float* bias, const v
   if (rc) return rc;
   static bool attrx = false;
   if (!attrx) {
-    cudaError_t e = cudaFuncSetAttribute(conv_tc_xf_k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_xf_k<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_xf_k<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return (int)e;
     int dev = 0;
     cudaGetDevice(&dev);
@@ -2212,9 +2287,30 @@ int crackfl_conv_tc_xf(const void* X, const void* Wk, const float* bias, const v
     const int total = a.n_tiles_m * a.n_tiles_n;
     if (grid > total) grid = total;
   }
-  ck::launch(conv_tc_xf_k, grid, 64 + EPI_THREADS + XF_THREADS, smem, st, tmA, tmB, tmY, a);
+  if (xmode >= 4) ck::launch(conv_tc_xf_k<true>, grid, 64 + EPI_THREADS + 6 * 32, smem, st, tmA, tmB, tmY, tmA2, a);
+  else ck::launch(conv_tc_xf_k<false>, grid, 64 + EPI_THREADS + 8 * 32, smem, st, tmA, tmB, tmY, tmA2, a);
   CK_LAUNCH_CHECK();
   return 0;
+}
+
+int crackfl_conv_tc_xf(const void* X, const void* Wk, const float* bias, const void* add, void* Y, float* stats, int B, int H,
+                       int W, int Cin, int N, int xmode, const float* bn, const crackfl_bn_fin* fin, void* side, int diag,
+                       cudaStream_t st) {
+  if (xmode > 3) return (int)cudaErrorInvalidValue;
+  return conv_tc_xf_impl(X, nullptr, Wk, bias, add, Y, stats, B, H, W, Cin, N, xmode, bn, fin, side, diag, nullptr, 0.f, nullptr,
+                         nullptr, st);
+}
+
+// K2: 3x3 conv (the input gradient of a decoder conv) whose input dy is formed inside the kernel from the gradient dz w.r.t.
+// the BN output and the BN input y:  dy = BN-backward(dz, y) per channel from `bn` ([scale|shift|mean|invstd]) and the
+// reduce pass's `sums` ([sum dz | sum dz*(y-mean)]); relu_mask != 0 masks dz by bn(y) > 0 first (the BN + ReLU pair).
+// dy is written to dy_out (the layer's weight gradient reads it) and block 0 writes dgamma / dbeta: the launch replaces
+// crackfl_bn_bwd_apply + crackfl_conv_tc_fwd.
+int crackfl_conv_tc_bnbwd(const void* dz, const void* y, const void* Wk, void* Y, int B, int H, int W, int Cin, int N,
+                          const float* bn, const float* sums, int relu_mask, void* dy_out, float* dgamma, float* dbeta,
+                          cudaStream_t st) {
+  return conv_tc_xf_impl(dz, y, Wk, nullptr, nullptr, Y, nullptr, B, H, W, Cin, N, relu_mask ? 5 : 4, bn, nullptr, dy_out, 0, sums,
+                         (float)((long)B * H * W), dgamma, dbeta, st);
 }
 
 // cin_valid < Cin: the last Cin - cin_valid input channels are zero padding; their gradient rows are not written

@@ -155,6 +155,13 @@ int crackfl_head_fwd_bwd(const void* s, const float* w, const float* bias, const
 int crackfl_conv_tc_xf(const void* X, const void* Wk, const float* bias_or_null, const void* add_or_null, void* Y,
                        float* stats_or_null, int B, int H, int W, int Cin, int N, int xmode, const float* bn_or_null,
                        const crackfl_bn_fin* fin_or_null, void* side_or_null, int diag, cudaStream_t stream);
+/* K2: input gradient of a 3x3 conv with the BatchNorm backward of its input folded in (ref: the backward of
+ * BatchNormalization -> [ReLU] in front of a Conv2DTranspose, client_fit_model.py:128-134): dy = BN-backward(dz, y) is formed
+ * inside the kernel from bn = [scale|shift|mean|invstd] and sums = [sum dz | sum dz*(y-mean)] (crackfl_bn_bwd_reduce), written to
+ * dy_out for the weight gradient, and dgamma / dbeta are written too.  Replaces crackfl_bn_bwd_apply + crackfl_conv_tc_fwd. */
+int crackfl_conv_tc_bnbwd(const void* dz, const void* y, const void* Wk, void* Y, int B, int H, int W, int Cin, int N,
+                          const float* bn, const float* sums, int relu_mask, void* dy_out, float* dgamma, float* dbeta,
+                          cudaStream_t stream);
 typedef struct {
   long src_off, dst_off; /* element offsets: depthwise kernel (3,3,C,1) in the fp32 arena / tiles in the bf16 operand buffer */
   int C, kc, flip, pad_;  /* kc = 64 (C % 64 == 0) or 32; flip: taps reversed (input-gradient form) */

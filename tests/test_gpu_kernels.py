@@ -205,6 +205,23 @@ def test_engine_gradients_are_as_close_to_fp32_as_a_bf16_pytorch_run():
     assert min(v[1] for v in rep["grad"].values() if not isinstance(v[0], str)) > floor - 0.05
 
 
+@pytest.mark.parametrize("knobs", [{"CRACKFL_XF_DEC": "2"}, {"CRACKFL_XF_BWD": "2"}, {"CRACKFL_XF_DEC": "2", "CRACKFL_XF_BWD": "2"}])
+def test_engine_with_fused_prologue_paths_vs_oracle(knobs, monkeypatch):
+    """The opt-in schedules (BN-apply+ReLU / BN-backward apply as the prologue of the decoder convs) against the same oracle
+    and the same bounds as the default schedule."""
+    from crackfl.utils.check import engine_vs_oracle, format_report, worst
+    for k, v in knobs.items():
+        monkeypatch.setenv(k, v)
+    rep = engine_vs_oracle(B=8, H=128, W=128, conv_impl="tc", randomize_bn=False)
+    wf, wc = worst(rep)
+    txt = format_report(rep)
+    assert abs(rep["loss"][0] - rep["loss"][1]) < 2e-2 * max(1.0, rep["loss"][1]), txt
+    assert wf < 6e-2 and wc > 0.90, txt
+    decoder_tail = [v[1] for k, v in rep["grad"].items() if not isinstance(v[0], str) and
+                    k.split("/")[0] in ("conv2d_transpose_6", "conv2d_transpose_7", "conv2d_7", "conv2d_8")]
+    assert min(decoder_tail) > 0.995, txt
+
+
 def test_engine_randomised_bn_params_vs_oracle():
     from crackfl.utils.check import engine_vs_oracle, format_report, worst
     rep = engine_vs_oracle(B=4, H=64, W=64, conv_impl="tc", randomize_bn=True)
@@ -608,4 +625,41 @@ def test_wgrad_halo_3x3(B, H, W, cin, cout):
     F.conv2d(x.float().permute(0, 3, 1, 2), w, padding=1).backward(dy.float().permute(0, 3, 1, 2))
     ref = w.grad.permute(2, 3, 1, 0).reshape(9, cin, cout)
     err = float((dw / 2 - ref).norm() / ref.norm())
+    assert err < 1e-2, err
+
+
+@pytest.mark.parametrize("B,H,W,cin,N,relu_mask", [(2, 16, 16, 64, 64, 0), (2, 16, 16, 64, 128, 1), (1, 20, 12, 128, 256, 1),
+                                                    (2, 32, 24, 256, 256, 0)])
+def test_conv_bn_backward_prologue(B, H, W, cin, N, relu_mask):
+    """K2: the input gradient of a decoder conv with the BatchNorm backward of its input formed inside the kernel ==
+    crackfl_bn_bwd_reduce -> crackfl_bn_bwd_apply -> crackfl_conv_tc_fwd (and the same dy, dgamma, dbeta)."""
+    L, lib = _lib()
+    torch.manual_seed(4)
+    dz = torch.randn(B, H, W, cin, device="cuda").bfloat16()
+    y = torch.randn(B, H, W, cin, device="cuda").bfloat16()
+    wk = (torch.randn(N, 9 * cin, device="cuda") / np.sqrt(9 * cin)).bfloat16()
+    yf = y.float().reshape(-1, cin)
+    mean, var = yf.mean(0), yf.var(0, unbiased=False)
+    invstd = torch.rsqrt(var + 1e-3)
+    gamma = torch.rand(cin, device="cuda") + 0.5; beta = torch.randn(cin, device="cuda") * 0.3
+    scale = gamma * invstd; shift = beta - mean * scale
+    bn = torch.cat([scale, shift, mean, invstd]).contiguous()
+    mode = 1 if relu_mask else 0
+    sums = torch.zeros(2 * cin, device="cuda")
+    L.check(lib.crackfl_bn_bwd_reduce(dz.data_ptr(), 0, y.data_ptr(), bn.data_ptr(), sums.data_ptr(), B, H, W, cin, mode, _st()))
+    # reference path
+    dy_ref = torch.zeros_like(dz); dg_ref = torch.zeros(cin, device="cuda"); db_ref = torch.zeros(cin, device="cuda")
+    L.check(lib.crackfl_bn_bwd_apply(dz.data_ptr(), 0, y.data_ptr(), bn.data_ptr(), sums.data_ptr(), dy_ref.data_ptr(),
+                                     dg_ref.data_ptr(), db_ref.data_ptr(), B, H, W, cin, mode, _st()))
+    out_ref = torch.zeros(B, H, W, N, device="cuda", dtype=torch.bfloat16)
+    L.check(lib.crackfl_conv_tc_fwd(dy_ref.data_ptr(), wk.data_ptr(), 0, 0, out_ref.data_ptr(), 0, B, H, W, cin, N, 9, _st()))
+    # fused path
+    dy = torch.zeros_like(dz); dg = torch.zeros(cin, device="cuda"); db = torch.zeros(cin, device="cuda")
+    out = torch.zeros(B, H, W, N, device="cuda", dtype=torch.bfloat16)
+    L.check(lib.crackfl_conv_tc_bnbwd(dz.data_ptr(), y.data_ptr(), wk.data_ptr(), out.data_ptr(), B, H, W, cin, N, bn.data_ptr(),
+                                      sums.data_ptr(), relu_mask, dy.data_ptr(), dg.data_ptr(), db.data_ptr(), _st()))
+    torch.cuda.synchronize()
+    assert torch.allclose(dg, dg_ref, rtol=1e-5, atol=1e-5) and torch.allclose(db, db_ref, rtol=1e-5, atol=1e-5)
+    assert float((dy.float() - dy_ref.float()).abs().max()) <= 2 ** -7 * float(dy_ref.float().abs().max()) + 1e-6
+    err = float((out.float() - out_ref.float()).norm() / out_ref.float().norm())
     assert err < 1e-2, err
