@@ -6,7 +6,7 @@ import argparse
 import json
 import sys
 
-from ..parallel.runtime import init_distributed, run_federated_onbox
+from ..parallel.runtime import init_distributed, run_federated_onbox, shutdown_distributed
 from .common import parse_with_config
 
 
@@ -28,6 +28,7 @@ def main(argv=None) -> int:
             from ..trainer import spec_from_config
             save_keras_h5(args.save, spec_from_config(cfg), out["weights"])
         print(json.dumps({"rounds": out["rounds"]}))
+    shutdown_distributed()
     return 0
 
 

@@ -461,6 +461,15 @@ def init_distributed(backend: Optional[str] = None):
     dist.init_process_group(backend=backend)
 
 
+def shutdown_distributed():
+    """Counterpart of init_distributed for CLI exits: ranks leave together and the process group is torn down."""
+    if dist.is_available() and dist.is_initialized():
+        try:
+            dist.barrier()
+        finally:
+            dist.destroy_process_group()
+
+
 def run_federated_onbox(cfg, rounds: int, clients_per_gpu: int = 1, strategy: str = "fedavg", payload: str = "fp32",
                         spec: Optional[UNetSpec] = None, steps_per_round: Optional[int] = None, log=print,
                         eval_global: bool = False, bridge=None, remote_slots: int = 0) -> dict:
