@@ -741,6 +741,248 @@ __global__ void __launch_bounds__(512, 1) dw_bwd_k(const __grid_constant__ CUten
   if (role == 0 && cur_cblk >= 0 && a.rsums) flush_bn(cur_cblk);
 }
 
+// Fourth generation of the one-pass depthwise backward.  ncu on dw_bwd_k (profiles/ncu_step_all_kernels_part2.md): issue
+// slots 35 % busy with `barrier` the top stall - the input-gradient warps execute twice the instructions of the
+// weight-gradient warps, so half the CTA waits at the end-of-tile barrier - then `no_instruction` (two different unrolled
+// bodies share the instruction cache).  And with tiles dealt out round-robin a CTA changed channel block, and paid the
+// 18-barrier weight-gradient flush, after almost every tile of the 32x32 / 64x64 layers.  Here
+//   * every thread does BOTH jobs for (2 channels, one column, TY/RG rows): the g window it slides for the input
+//     gradient holds the centre value the weight gradient needs and the activation window holds the mask / BN-sum value
+//     the input gradient needs, so all 16 warps run one body of equal length (halved per-thread register arrays keep it
+//     under 128 registers);
+//   * a CTA owns a CONTIGUOUS range of tiles (channel-block-major order), so it flushes once or twice per launch, through
+//     a [slot][11][CB] staging area summed by a column of threads instead of tap-by-tap barriers.
+template <int TY, int RG>
+__global__ void __launch_bounds__(512, 1) dw_bwd2_k(const __grid_constant__ CUtensorMap tmG,
+                                                    const __grid_constant__ CUtensorMap tmS, const DwArgs a) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 127u) & ~127u;
+  uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
+  const int CB = a.CB, rowb = CB * 2;
+  const uint32_t halo_bytes = (uint32_t)((TY + 2) * HW * rowb);
+  const uint32_t stage_bytes = 2u * halo_bytes;  // [g halo][src halo]
+  const uint32_t bar0 = base + 2u * stage_bytes;
+  float* coef = reinterpret_cast<float*>(gbase + 2u * stage_bytes + 64);  // [scale CB][shift CB]
+  float* red = coef + 2 * 64;                                             // [512 / nc2 slots][11][CB]
+  const int nc2 = CB >> 1;
+  constexpr int rows = TY / RG;
+  const int tl = threadIdx.x;
+  const int c2 = tl % nc2, col = (tl / nc2) % TX, rg = tl / (nc2 * TX), slot = tl / nc2;
+  const int nslot = 512 / nc2;
+  const int spatial = a.tiles_x * a.tiles_y * a.B;
+  const int t_lo = (int)(((long)blockIdx.x * a.total_tiles) / gridDim.x);
+  const int t_hi = (int)(((long)(blockIdx.x + 1) * a.total_tiles) / gridDim.x);
+
+  if (threadIdx.x == 0) {
+    mbar_init(bar0, 1);
+    mbar_init(bar0 + 8u, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    tma_prefetch_desc(&tmG);
+    tma_prefetch_desc(&tmS);
+  }
+  pdl_enter();
+  __syncthreads();
+
+  auto issue = [&](int tile, int stage) {
+    const int cblk = dw_fdiv(tile, a.m_sp);
+    const int sp = tile - cblk * spatial;
+    const int q_ = dw_fdiv(sp, a.m_tx);
+    const int tx_i = sp - q_ * a.tiles_x;
+    const int b = dw_fdiv(q_, a.m_ty);
+    const int ty_i = q_ - b * a.tiles_y;
+    mbar_expect_tx(bar0 + 8u * stage, stage_bytes);
+    tma_load_4d(base + stage * stage_bytes, &tmG, bar0 + 8u * stage, cblk * CB, tx_i * TX - 1, ty_i * TY - 1, b);
+    tma_load_4d(base + stage * stage_bytes + halo_bytes, &tmS, bar0 + 8u * stage, cblk * CB, tx_i * TX - 1, ty_i * TY - 1, b);
+  };
+  if (threadIdx.x == 0 && t_lo < t_hi) issue(t_lo, 0);
+
+  f2_t wk[9], wacc[9];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) { wk[t] = 0ull; wacc[t] = 0ull; }
+  f2_t bs1 = 0ull, bs2 = 0ull;  // BN-backward reductions of the layer below: sum dz and sum dz * a (see dw_bwd_k)
+  int cur_cblk = -1;
+
+  auto flush = [&](int cblk) {  // all 512 threads
+    float* mine = red + slot * 11 * CB + c2 * 2;
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      float lo, hi;
+      upk2(wacc[t], lo, hi);
+      *reinterpret_cast<float2*>(mine + t * CB) = make_float2(lo, hi);
+      wacc[t] = 0ull;
+    }
+    {
+      float lo, hi;
+      upk2(bs1, lo, hi);
+      *reinterpret_cast<float2*>(mine + 9 * CB) = make_float2(lo, hi);
+      upk2(bs2, lo, hi);
+      *reinterpret_cast<float2*>(mine + 10 * CB) = make_float2(lo, hi);
+      bs1 = bs2 = 0ull;
+    }
+    __syncthreads();
+    for (int i = tl; i < 11 * CB; i += 512) {
+      float v = 0.f;
+      for (int q = 0; q < nslot; ++q) v += red[q * 11 * CB + i];
+      red[i] = v;  // slot 0, element i: read and written by this thread only
+    }
+    __syncthreads();
+    for (int i = tl; i < 9 * CB; i += 512) {
+      const int t = i / CB, c = i - t * CB;
+      atomicAdd(a.dwk + (long)t * a.C + cblk * CB + c, red[i]);
+    }
+    if (a.rsums && tl < CB) {
+      const int c = cblk * CB + tl;
+      const float S1 = red[9 * CB + tl], S2 = red[10 * CB + tl];
+      const float sc = a.rbn[c], sh = a.rbn[a.C + c], mu = a.rbn[2 * a.C + c];
+      const float beta = sh + mu * sc;
+      atomicAdd(a.rsums + c, S1);
+      atomicAdd(a.rsums + a.C + c, sc != 0.f ? (S2 - beta * S1) / sc : 0.f);
+    }
+    __syncthreads();
+  };
+
+  int it = 0;
+  for (int tile = t_lo; tile < t_hi; ++tile, ++it) {
+    const int stage = it & 1;
+    if (threadIdx.x == 0 && tile + 1 < t_hi) issue(tile + 1, stage ^ 1);  // its last readers passed the barrier at the loop tail
+    const int cblk = dw_fdiv(tile, a.m_sp);
+    const int sp = tile - cblk * spatial;
+    const int q_ = dw_fdiv(sp, a.m_tx);
+    const int tx_i = sp - q_ * a.tiles_x;
+    const int b = dw_fdiv(q_, a.m_ty);
+    const int ty_i = q_ - b * a.tiles_y;
+    const int cg = cblk * CB + c2 * 2;
+    if (cblk != cur_cblk) {  // uniform over the CTA
+      if (cur_cblk >= 0) flush(cur_cblk);
+      cur_cblk = cblk;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        const float2 v = __ldg(reinterpret_cast<const float2*>(a.w + (8 - t) * a.C + cg));
+        wk[t] = pk2(v.x, v.y);
+      }
+      if (a.src_mode == 1) {
+        __syncthreads();  // the previous tile's pre-pass readers of coef are done
+        if (threadIdx.x < (CB >> 2)) {
+          const float4 s4 = __ldg(reinterpret_cast<const float4*>(a.src_bn + cblk * CB + threadIdx.x * 4));
+          const float4 h4 = __ldg(reinterpret_cast<const float4*>(a.src_bn + a.C + cblk * CB + threadIdx.x * 4));
+          *reinterpret_cast<float4*>(coef + threadIdx.x * 4) = s4;
+          *reinterpret_cast<float4*>(coef + CB + threadIdx.x * 4) = h4;
+        }
+        __syncthreads();
+      }
+    }
+    const int w0 = tx_i * TX, ty0 = ty_i * TY, h0 = ty0 + rg * rows;
+    const int gw = w0 + col;
+    uint32_t rres[(rows + 1) / 2];
+#pragma unroll
+    for (int i = 0; i < (rows + 1) / 2; ++i) {
+      rres[i] = 0u;
+      const int oh = h0 + 2 * i;  // h0 is even
+      if (a.resid && !(col & 1) && oh < a.H && gw < a.W)
+        rres[i] = __ldg(reinterpret_cast<const uint32_t*>(
+            a.resid_t + (((long)b * (a.H >> 1) + (oh >> 1)) * (a.W >> 1) + (gw >> 1)) * a.C + cg));
+    }
+    mbar_wait(bar0 + 8u * stage, (uint32_t)(it >> 1) & 1u);
+    uint8_t* tile_g = gbase + stage * stage_bytes;
+    uint8_t* tile_a = tile_g + halo_bytes;
+
+    {  // activation pre-pass on the src halo, in place; out-of-image pixels stay zero
+      const int c8n = CB >> 3;
+      const int nchunk = (TY + 2) * HW * c8n;
+      if (a.src_mode == 0) {
+        for (int idx = threadIdx.x; idx < nchunk; idx += 512) {
+          uint4* q = reinterpret_cast<uint4*>(tile_a) + idx;
+          uint4 v = *q;
+          v.x = relu_bf2(v.x); v.y = relu_bf2(v.y); v.z = relu_bf2(v.z); v.w = relu_bf2(v.w);
+          *q = v;
+        }
+      } else {
+        const bool interior = w0 >= 1 && w0 + TX < a.W && ty0 >= 1 && ty0 + TY < a.H;
+        const int c8 = threadIdx.x % c8n;
+        f2_t scp[4], shp[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          scp[j] = *reinterpret_cast<const f2_t*>(coef + c8 * 8 + 2 * j);
+          shp[j] = *reinterpret_cast<const f2_t*>(coef + CB + c8 * 8 + 2 * j);
+        }
+        for (int idx = threadIdx.x; idx < nchunk; idx += 512) {
+          uint4* q = reinterpret_cast<uint4*>(tile_a) + idx;
+          uint4 v = *q;
+          v.x = f2_to_bf2_relu(ffma2(bf2_to_f2(v.x), scp[0], shp[0]));
+          v.y = f2_to_bf2_relu(ffma2(bf2_to_f2(v.y), scp[1], shp[1]));
+          v.z = f2_to_bf2_relu(ffma2(bf2_to_f2(v.z), scp[2], shp[2]));
+          v.w = f2_to_bf2_relu(ffma2(bf2_to_f2(v.w), scp[3], shp[3]));
+          if (!interior) {
+            const int pi = idx >> (c8n == 8 ? 3 : 2);  // c8n = CB / 8 is 8 or 4
+            const int hr = pi / HW, hc = pi - hr * HW;
+            const int gh = ty0 - 1 + hr, gx = w0 - 1 + hc;
+            if (gh < 0 || gh >= a.H || gx < 0 || gx >= a.W) v = make_uint4(0u, 0u, 0u, 0u);
+          }
+          *q = v;
+        }
+      }
+      __syncthreads();
+    }
+
+    f2_t wg[3][3], wa[3][3];
+    const size_t toff = (size_t)(((rg * rows) * HW + col) * rowb + c2 * 4);
+    const long out_rs = (long)a.W * a.C;
+    __nv_bfloat16* const out_p = a.out + (((long)b * a.H + h0) * a.W + gw) * a.C + cg;
+    const uint8_t* const g_row0 = tile_g + toff;
+    const uint8_t* const a_row0 = tile_a + toff;
+#pragma unroll
+    for (int r = 0; r < rows + 2; ++r) {
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        wg[r % 3][kx] = bf2_to_f2(*reinterpret_cast<const uint32_t*>(g_row0 + (r * HW + kx) * rowb));
+        wa[r % 3][kx] = bf2_to_f2(*reinterpret_cast<const uint32_t*>(a_row0 + (r * HW + kx) * rowb));
+      }
+      if (r >= 2) {
+        const int oh = h0 + r - 2;
+        // input gradient: three independent partial sums (one per window row) instead of one 9-deep chain
+        f2_t p[3];
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
+          p[ky] = fmul2(wg[(r - 2 + ky) % 3][0], wk[ky * 3]);
+          p[ky] = ffma2(wg[(r - 2 + ky) % 3][1], wk[ky * 3 + 1], p[ky]);
+          p[ky] = ffma2(wg[(r - 2 + ky) % 3][2], wk[ky * 3 + 2], p[ky]);
+        }
+        const f2_t acc = fadd2(fadd2(p[0], p[1]), p[2]);
+        // weight gradient: the centre of the g window is g at this output pixel (out-of-image g = TMA zero fill)
+        const f2_t gc = wg[(r - 1) % 3][1];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) wacc[t] = ffma2(wa[(r - 2 + t / 3) % 3][t % 3], gc, wacc[t]);
+        const f2_t ac = wa[(r - 1) % 3][1];  // activated forward input at this pixel: > 0 <=> the relu passed it
+        float o0, o1, a0, a1;
+        upk2(acc, o0, o1);
+        upk2(ac, a0, a1);
+        float r0 = 0.f, r1 = 0.f;
+        if (((r - 2) & 1) == 0) {
+          const uint32_t rv = rres[(r - 2) / 2];
+          r0 = __uint_as_float(rv << 16); r1 = __uint_as_float(rv & 0xffff0000u);
+        }
+        if (a.resid == 2) {
+          o0 = a0 > 0.f ? o0 + r0 : 0.f;
+          o1 = a1 > 0.f ? o1 + r1 : 0.f;
+        } else {
+          o0 = (a0 > 0.f ? o0 : 0.f) + r0;
+          o1 = (a1 > 0.f ? o1 : 0.f) + r1;
+        }
+        const uint32_t pk = pack2(o0, o1);
+        if (a.rsums) {  // sums over the bf16-rounded dz, exactly what the apply pass reads back
+          const f2_t d = bf2_to_f2(pk);
+          bs1 = fadd2(bs1, d);
+          bs2 = ffma2(d, ac, bs2);
+        }
+        if (oh < a.H && gw < a.W) *reinterpret_cast<uint32_t*>(out_p + (r - 2) * out_rs) = pk;
+      }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();  // every thread is done with this stage before it is refilled
+  }
+  if (cur_cblk >= 0) flush(cur_cblk);
+}
+
 int g_sms = 0;
 int num_sms() {
   if (g_sms <= 0) {
@@ -910,8 +1152,24 @@ int crackfl_dw3x3_bwd_tma_bn(const void* g, const void* src, const float* w, con
   }
   int grid = num_sms();
   if (grid > a.total_tiles) grid = a.total_tiles;
-  if (a.CB == 64) ck::launch(dw_bwd_k<TY, 1>, grid, 512, smem, st, tmG, tmS, a);
-  else ck::launch(dw_bwd_k<TY, 2>, grid, 512, smem, st, tmG, tmS, a);
+  static int gen = -1;  // CRACKFL_DW_BWD=3: the role-split kernel; default: every thread does both gradients (dw_bwd2_k)
+  if (gen < 0) { const char* e = getenv("CRACKFL_DW_BWD"); gen = e ? atoi(e) : 4; }
+  if (gen == 3) {
+    if (a.CB == 64) ck::launch(dw_bwd_k<TY, 1>, grid, 512, smem, st, tmG, tmS, a);
+    else ck::launch(dw_bwd_k<TY, 2>, grid, 512, smem, st, tmG, tmS, a);
+  } else {
+    const size_t smem2 = 2 * 2 * (size_t)(TY + 2) * HW * a.CB * 2 + 64 + 2 * 64 * sizeof(float) +
+                         (size_t)(512 / (a.CB / 2)) * 11 * a.CB * sizeof(float) + 128;
+    static bool attr2 = false;
+    if (!attr2) {
+      cudaError_t e = cudaFuncSetAttribute(dw_bwd2_k<TY, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_bwd2_k<TY, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024);
+      if (e != cudaSuccess) return (int)e;
+      attr2 = true;
+    }
+    if (a.CB == 64) ck::launch(dw_bwd2_k<TY, 1>, grid, 512, smem2, st, tmG, tmS, a);
+    else ck::launch(dw_bwd2_k<TY, 2>, grid, 512, smem2, st, tmG, tmS, a);
+  }
   CK_LAUNCH_CHECK();
   return 0;
 }

@@ -6,6 +6,8 @@
 #include <cstdio>
 #include <cstdlib>
 
+#include <mutex>
+#include <unordered_map>
 #include "common.cuh"
 #include "../include/crackfl.h"
 
@@ -632,7 +634,7 @@ __global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : 3) bn_bwd_reduce_k(const 
 // dy = scale * (dz - mean(dz) - xhat * mean(dz*xhat)), folded into dy = A*dz + Bc*y + Cc per channel;
 // block 0 also emits dgamma = sum dz*xhat and dbeta = sum dz.
 template <int MODE>
-__global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : 3) bn_bwd_apply_k(const __nv_bfloat16* __restrict__ g, const uint8_t* __restrict__ arg,
+__global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : (MODE == 0 ? 4 : 3)) bn_bwd_apply_k(const __nv_bfloat16* __restrict__ g, const uint8_t* __restrict__ arg,
                                                       const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
                                                       const float* __restrict__ sums, __nv_bfloat16* __restrict__ dy,
                                                       float* __restrict__ dgamma, float* __restrict__ dbeta, long P, int H,
@@ -1310,6 +1312,25 @@ __global__ void __launch_bounds__(TPB) entry_im2col_k(const uint8_t* __restrict_
   }
 }
 
+// Grid of a grid-stride streaming kernel capped at what is RESIDENT at once: a kernel that fits three blocks per SM and is
+// launched with 4 x 148 runs a second wave of 148 lone blocks over the last quarter of the tensor (8 warps per SM).
+// CRACKFL_EW_OCC=0 restores the fixed 4 x 148.
+inline int blocks_per_sm_of(const void* kernel, int want) {
+  static int mode = -1;
+  if (mode < 0) { const char* e = getenv("CRACKFL_EW_OCC"); mode = e ? atoi(e) : 1; }
+  if (!mode) return want;
+  static std::mutex mu;
+  static std::unordered_map<const void*, int> cache;
+  std::lock_guard<std::mutex> lk(mu);
+  auto it = cache.find(kernel);
+  if (it == cache.end()) {
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, TPB, 0) != cudaSuccess || occ < 1) occ = want;
+    it = cache.emplace(kernel, occ).first;
+  }
+  return it->second < want ? it->second : want;
+}
+
 inline int grid_for(long total, int cap = 0) {
   // blocks per SM of the grid-stride streaming kernels.  Measured on the full step (ms): 2: 1.354, 3: 1.325, 4: 1.311,
   // 6: 1.315, 8: 1.315, 12: 1.336, 16: 1.347, 24: 1.375, 48: 1.404 - about one resident wave is best (no tail of
@@ -1460,7 +1481,7 @@ int crackfl_pool_add_fwd(const void* y, const float* bn, const void* res, void* 
                          int B, int H, int W, int C, cudaStream_t st) {
   CK_FITS32((long)B * H * W * C);
   const long total = (long)B * (H / 2) * (W / 2) * (C / 8);
-  ck::launch(pool_add_fwd_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)y, bn, (const __nv_bfloat16*)res,
+  ck::launch(pool_add_fwd_k, grid_for(total, 148 * blocks_per_sm_of((const void*)pool_add_fwd_k, 4)), TPB, 0, st, (const __nv_bfloat16*)y, bn, (const __nv_bfloat16*)res,
                                                   (__nv_bfloat16*)out, (__nv_bfloat16*)even, (__nv_bfloat16*)relu_out,
                                                   (uint8_t*)arg, B, H, W, C, BnFin{});
   CK_LAUNCH_CHECK();
@@ -1517,7 +1538,8 @@ int crackfl_bn_bwd_apply(const void* g, const void* arg, const void* y, const fl
                          float* dgamma, float* dbeta, int B, int H, int W, int C, int mode, cudaStream_t st) {
   CK_FITS32((long)B * H * W * C);
   const long P = (long)B * H * W;
-  const int grid = grid_for(P * (C / 8));
+  const void* kfn = mode == 0 ? (const void*)bn_bwd_apply_k<0> : mode == 1 ? (const void*)bn_bwd_apply_k<1> : (const void*)bn_bwd_apply_k<2>;
+  const int grid = grid_for(P * (C / 8), 148 * blocks_per_sm_of(kfn, 4));
   const __nv_bfloat16* gp = (const __nv_bfloat16*)g;
   const __nv_bfloat16* yp = (const __nv_bfloat16*)y;
   const uint8_t* ap = (const uint8_t*)arg;
@@ -1632,7 +1654,7 @@ int crackfl_pool_add_fwd_fin(const void* y, const crackfl_bn_fin* fin, const voi
                              void* arg, int B, int H, int W, int C, cudaStream_t st) {
   CK_FITS32((long)B * H * W * C);
   const long total = (long)B * (H / 2) * (W / 2) * (C / 8);
-  ck::launch(pool_add_fwd_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)y, nullptr, (const __nv_bfloat16*)res,
+  ck::launch(pool_add_fwd_k, grid_for(total, 148 * blocks_per_sm_of((const void*)pool_add_fwd_k, 4)), TPB, 0, st, (const __nv_bfloat16*)y, nullptr, (const __nv_bfloat16*)res,
                                                   (__nv_bfloat16*)out, (__nv_bfloat16*)even, (__nv_bfloat16*)relu_out,
                                                   (uint8_t*)arg, B, H, W, C, *fin);
   CK_LAUNCH_CHECK();

@@ -316,7 +316,8 @@ def test_server_with_device_aggregator(tmp_path):
     assert srv.history[0]["aggregator"] == "device"
 
 
-@pytest.mark.parametrize("B,H,W,Cc,mode", [(2, 32, 32, 64, 0), (2, 20, 24, 32, 1), (1, 16, 16, 128, 1), (2, 14, 14, 64, 0)])
+@pytest.mark.parametrize("B,H,W,Cc,mode", [(2, 32, 32, 64, 0), (2, 20, 24, 32, 1), (1, 16, 16, 128, 1), (2, 14, 14, 64, 0),
+                                           (16, 32, 32, 256, 1), (9, 40, 48, 32, 0)])  # last two: CTAs that span channel blocks / many tiles
 def test_dw3x3_tma_fwd_dgrad_wgrad(B, H, W, Cc, mode):
     """TMA-staged depthwise kernels vs autograd of relu[(bn)] -> depthwise conv."""
     L, lib = _lib()
