@@ -87,6 +87,7 @@ class UNetEngine:
         self.xf_bwd = int(os.environ.get("CRACKFL_XF_BWD", "0"))
         # K1: BN-apply + ReLU as the prologue of the decoder's second conv.  1.122 ms with it, 1.115 without: off by default.
         self.xf_dec = int(os.environ.get("CRACKFL_XF_DEC", "0"))
+        self.prep_flat = os.environ.get("CRACKFL_PREP_FLAT", "1") != "0"  # one 32x32 tile per block (0: 48 blocks per operand)
         self.xf_dw = os.environ.get("CRACKFL_XF_DW", "0") != "0"
         # partial tiles added straight into the gradient arena with vector reductions: no workspace, no reduction launch
         # (22 launches fewer per step, 1.263 vs 1.287 ms/step; CRACKFL_WGRAD_ATOMIC=0 restores workspace + reduction)
@@ -219,6 +220,12 @@ class UNetEngine:
         self.desc_dev = raw.to(self.dev)
         self._bufs["prep_descs"] = self.desc_dev
         self.num_desc = len(descs)
+        pref = [0]
+        for d in descs:
+            pref.append(pref[-1] + ((d.N + 31) // 32) * ((d.K + 31) // 32) * d.T)
+        self.prep_tiles = pref[-1]
+        self.prep_prefix = torch.tensor(pref, dtype=torch.int32).to(self.dev)
+        self._bufs["prep_prefix"] = self.prep_prefix
 
     def op_ptr(self, name: str) -> int:
         return self.ops_buf.data_ptr() + 2 * self.ops[name][0]
@@ -467,8 +474,12 @@ class UNetEngine:
         if not training:
             self._bn_eval_all(prog)
         # bf16 GEMM operands of this step's weights: next to the im2col / entry kernels on the auxiliary stream
-        prog.append((lib.crackfl_weight_prep, (self.arena.data_ptr(), self.ops_buf.data_ptr(), self.desc_dev.data_ptr(),
-                                               self.num_desc), "aux"))
+        if self.prep_flat and self.num_desc <= 128:
+            prog.append((lib.crackfl_weight_prep_flat, (self.arena.data_ptr(), self.ops_buf.data_ptr(), self.desc_dev.data_ptr(),
+                                                        self.prep_prefix.data_ptr(), self.num_desc, self.prep_tiles), "aux"))
+        else:
+            prog.append((lib.crackfl_weight_prep, (self.arena.data_ptr(), self.ops_buf.data_ptr(), self.desc_dev.data_ptr(),
+                                                   self.num_desc), "aux"))
         if self.num_ddesc:
             prog.append((lib.crackfl_dw_diag_prep, (self.arena.data_ptr(), self.ops_buf.data_ptr(), self.ddesc_dev.data_ptr(),
                                                     self.num_ddesc), "aux"))
@@ -764,11 +775,12 @@ class UNetEngine:
             tag = entry[2] if len(entry) > 2 else None
             if isinstance(tag, tuple):  # ("rec" | "wait", stream, key): explicit event edges between the extra streams
                 if self.side_streams:
+                    s_ = main if tag[1] == "main" else streams[tag[1]]
                     if tag[0] == "rec":
                         events[tag[2]] = torch.cuda.Event()
-                        events[tag[2]].record(streams[tag[1]])
+                        events[tag[2]].record(s_)
                     else:
-                        streams[tag[1]].wait_event(events[tag[2]])
+                        s_.wait_event(events[tag[2]])
                 continue
             if tag == "join":
                 join("side")

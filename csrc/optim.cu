@@ -106,6 +106,61 @@ __global__ void __launch_bounds__(256) weight_prep_k(const float* __restrict__ a
   }
 }
 
+// One 32x32 tile per block over ALL operands (tile_prefix[i] = first flat tile of operand i, tile_prefix[num] = total):
+// weight_prep_k walks up to 12 tiles per block with two barriers each for the 256x9x256 decoder kernels while most of its
+// 48 x 43 blocks find nothing to do; here every tile of the step is in flight at once.
+__global__ void __launch_bounds__(256) weight_prep_flat_k(const float* __restrict__ arena, __nv_bfloat16* __restrict__ ops,
+                                                          const crackfl_prep_desc* __restrict__ descs,
+                                                          const int* __restrict__ tile_prefix, int num_desc) {
+  ck::pdl_enter();
+  __shared__ float tile[32][33];
+  __shared__ int pref[129];
+  for (int i = threadIdx.x; i <= num_desc; i += 256) pref[i] = tile_prefix[i];
+  __syncthreads();
+  int lo = 0, hi = num_desc - 1;  // last operand whose first tile is <= blockIdx.x
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (pref[mid] <= (int)blockIdx.x) lo = mid; else hi = mid - 1;
+  }
+  const crackfl_prep_desc d = descs[lo];
+  const int tl = (int)blockIdx.x - pref[lo];
+  const int tn = (d.N + 31) / 32, tk = (d.K + 31) / 32;
+  const int Kd = d.pad_ ? d.pad_ : d.K;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  const int kt = tl % tk, nt = (tl / tk) % tn, t = tl / (tk * tn);
+  const int n0 = nt * 32, k0 = kt * 32;
+  const float* src = arena + d.src_off + (long)t * d.s_t;
+  __nv_bfloat16* dst = ops + d.dst_off + (long)t * Kd;
+  if (d.s_n == 1 && d.s_k != 1) {  // read with n fastest, write with k fastest
+    float v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int n = n0 + tx, k = k0 + ty + 8 * i;
+      v[i] = (n < d.N && k < d.K) ? src[n + (long)k * d.s_k] : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) tile[ty + 8 * i][tx] = v[i];
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int n = n0 + ty + 8 * i, k = k0 + tx;
+      if (n < d.N && k < d.K) dst[(long)n * d.T * Kd + k] = __float2bfloat16_rn(tile[tx][ty + 8 * i]);
+    }
+  } else {
+    float v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int n = n0 + ty + 8 * i, k = k0 + tx;
+      v[i] = (n < d.N && k < d.K) ? src[(long)n * d.s_n + (long)k * d.s_k] : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int n = n0 + ty + 8 * i, k = k0 + tx;
+      if (n < d.N && k < d.K) dst[(long)n * d.T * Kd + k] = __float2bfloat16_rn(v[i]);
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) f32_to_bf16_k(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long n) {
   ck::pdl_enter();
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
@@ -200,6 +255,14 @@ int crackfl_weight_prep(const float* arena, void* ops, const crackfl_prep_desc* 
   if (gx < 0) { const char* e = getenv("CRACKFL_PREP_GRID_X"); gx = e ? atoi(e) : 48; if (gx < 1) gx = 48; }  // measured: 48: 1.279, 96: 1.282, 192: 1.286 ms/step (it overlaps the entry kernels on the auxiliary stream)
   dim3 grid(gx, num_desc);
   ck::launch(weight_prep_k, grid, 256, 0, st, arena, (__nv_bfloat16*)ops, descs_dev);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_weight_prep_flat(const float* arena, void* ops, const crackfl_prep_desc* descs_dev, const int* tile_prefix_dev,
+                             int num_desc, int total_tiles, cudaStream_t st) {
+  if (num_desc < 1 || num_desc > 128 || total_tiles < 1) return (int)cudaErrorInvalidValue;
+  ck::launch(weight_prep_flat_k, total_tiles, 256, 0, st, arena, (__nv_bfloat16*)ops, descs_dev, tile_prefix_dev, num_desc);
   CK_LAUNCH_CHECK();
   return 0;
 }

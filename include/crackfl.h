@@ -215,6 +215,10 @@ typedef struct {
 } crackfl_prep_desc;
 int crackfl_weight_prep(const float* arena, void* ops_bf16, const crackfl_prep_desc* descs_dev, int num_desc,
                         cudaStream_t stream);
+/* same result, one 32x32 tile per block: tile_prefix_dev[i] = number of 32x32 tiles (ceil(N/32) * ceil(K/32) * T) of the
+   operands before i, tile_prefix_dev[num_desc] = total_tiles; num_desc <= 128 */
+int crackfl_weight_prep_flat(const float* arena, void* ops_bf16, const crackfl_prep_desc* descs_dev, const int* tile_prefix_dev,
+                             int num_desc, int total_tiles, cudaStream_t stream);
 /* ref: client_fit_model.py:157 optimizer="Adam" (Keras form, eps 1e-7); also zeroes g */
 int crackfl_adam_step(float* p, float* g, float* m, float* v, int* step_dev, long n, float lr, float b1, float b2, float eps,
                       cudaStream_t stream);
