@@ -87,6 +87,7 @@ class UNetEngine:
         self.xf_bwd = int(os.environ.get("CRACKFL_XF_BWD", "0"))
         # K1: BN-apply + ReLU as the prologue of the decoder's second conv.  1.122 ms with it, 1.115 without: off by default.
         self.xf_dec = int(os.environ.get("CRACKFL_XF_DEC", "0"))
+        self.adam_early = os.environ.get("CRACKFL_ADAM_EARLY", "1") != "0"
         self.prep_flat = os.environ.get("CRACKFL_PREP_FLAT", "1") != "0"  # one 32x32 tile per block (0: 48 blocks per operand)
         self.xf_dw = os.environ.get("CRACKFL_XF_DW", "0") != "0"
         # partial tiles added straight into the gradient arena with vector reductions: no workspace, no reduction launch
@@ -115,6 +116,9 @@ class UNetEngine:
         self._side2_stream = torch.cuda.Stream(self.dev, priority=lo)
         self._side3_stream = torch.cuda.Stream(self.dev, priority=lo)  # bias-gradient column sums
         self.launches_per_step = sum(1 for e in self.train_prog if e[0] is not None)
+        # forward + backward without the optimiser launches (gradient checks): the gradient arena is left as computed
+        self.grad_prog = [e for e in self.train_prog if e[0] is None or
+                          getattr(e[0], "__name__", "") not in ("crackfl_adam_part", "crackfl_adam_step_tail", "crackfl_adam_step")]
 
     # ------------------------------------------------------------------ allocation
     def _new(self, name: str, shape, dtype=torch.bfloat16) -> torch.Tensor:
@@ -672,6 +676,22 @@ class UNetEngine:
             else:
                 prog.append((lib.crackfl_relu_bwd_add, (b(p + "da0"), b(src_res), b(p + "T"), b("dx_bott"),
                                                         B * r * rw * cin)))
+        # ---- the decoder's and the head's gradients are complete once the side streams drain: their Adam update runs
+        # now, next to the encoder's backward pass, and the launch at the end of the step only has the encoder's parameters
+        # left (the bf16 operand copies, not the arena, feed the rest of this step's GEMMs; the depthwise kernels and the
+        # BN tables the encoder's backward reads are outside this range)
+        adam_split = 0
+        if self.adam_early and decs:
+            first = min(ts[t].offset for t in decs[0][0].tensors)
+            adam_split = (first + 3) // 4 * 4
+            cs = os.environ.get("CRACKFL_COLSUM_STREAM", "side3")
+            if cs in ("side2", "side3"):
+                prog.append((None, None, ("rec", cs, "dec_colsum")))
+                prog.append((None, None, ("wait", "side", "dec_colsum")))
+            n_early = self.spec.arena_numel - adam_split
+            prog.append((lib.crackfl_adam_part, (self.arena.data_ptr() + 4 * adam_split, self.grads.data_ptr() + 4 * adam_split,
+                                                 self.m.data_ptr() + 4 * adam_split, self.v.data_ptr() + 4 * adam_split,
+                                                 self.step.data_ptr(), n_early, self.lr, self.b1, self.b2, self.eps), "side"))
         # ---- encoder backward
         dx_next = "dx_bott"
         for e, (sep1, bn1, sep2, bn2, res) in reversed(list(zip(self.enc, encs))):
@@ -739,7 +759,8 @@ class UNetEngine:
         # ---- optimiser (also zeroes the gradient arena)
         # Adam, its step tick and the metric accumulation in one launch (counter slot acc_off + 8 of the zeroed region)
         prog.append((lib.crackfl_adam_step_tail, (self.arena.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(),
-                                                  self.v.data_ptr(), self.step.data_ptr(), self.spec.arena_numel, self.lr,
+                                                  self.v.data_ptr(), self.step.data_ptr(),
+                                                  adam_split if adam_split else self.spec.arena_numel, self.lr,
                                                   self.b1, self.b2, self.eps, self._acc_ptr() + 4 * 8,
                                                   self.metrics_total.data_ptr(), self._acc_ptr(), 6,
                                                   self.last_acc.data_ptr(), self.zero_region.data_ptr(),

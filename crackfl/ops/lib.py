@@ -102,6 +102,7 @@ _SIGS = {
     "crackfl_weight_prep": [vp, vp, vp, i32, vp],
     "crackfl_weight_prep_flat": [vp, vp, vp, vp, i32, i32, vp],
     "crackfl_adam_step": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, vp],
+    "crackfl_adam_part": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, vp],
     "crackfl_f32_to_bf16": [vp, vp, i64, vp],
     "crackfl_adam_step_tail": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, vp, vp, vp, i32, vp, vp, i32, vp],
     "crackfl_accum_small": [vp, vp, i32, vp],

@@ -68,7 +68,7 @@ def engine_vs_oracle(spec: UNetSpec = REFERENCE_SPEC, B=4, H=64, W=64, seed=0, c
     eng.reset_optimizer(); eng.reset_metrics()
     eng.set_batch(x, y)
     eng.zero_region.zero_(); eng._region_dirty = True
-    eng._run(eng.train_prog[:-1])  # everything but the optimiser
+    eng._run(eng.grad_prog)  # everything but the optimiser
     torch.cuda.synchronize()
     acc = eng.zero_region[eng.acc_off:eng.acc_off + 6].cpu().numpy()
     eloss, eacc = float(acc[0] / acc[5]), float(acc[1] / acc[5])
@@ -157,7 +157,7 @@ def directional_fd_check(spec: UNetSpec = REFERENCE_SPEC, B=8, H=64, W=64, seed=
         return float(a[0]) / float(a[5])
 
     eng.zero_region.zero_(); eng.grads.zero_(); eng._region_dirty = True
-    eng._run(eng.train_prog[:-1])
+    eng._run(eng.grad_prog)
     g = eng.grads.clone()
     _, _, _, ograds, _, _ = oracle_run(spec, weights, x, y, torch.device("cuda"))
     out = {}

@@ -751,24 +751,27 @@ __global__ void __launch_bounds__(512, 1) dw_bwd_k(const __grid_constant__ CUten
 //     the input gradient needs, so all 16 warps run one body of equal length (halved per-thread register arrays keep it
 //     under 128 registers);
 //   * a CTA owns a CONTIGUOUS range of tiles (channel-block-major order), so it flushes once or twice per launch, through
-//     a [slot][11][CB] staging area summed by a column of threads instead of tap-by-tap barriers.
-template <int TY, int RG>
+//     a [slot][11][CB] staging area summed by a column of threads instead of tap-by-tap barriers;
+//   * (ncu on the first version of this kernel: the in-place activation pre-pass over the src halo was 25 % of all
+//     instructions and 28 % of the stall samples, ~80 instructions per 16-byte chunk with its barrier) the activation is
+//     applied to the three window values a thread loads per row instead - relu on the packed word, or FFMA2 + max for
+//     relu(bn) with the shift masked off where the halo pixel is outside the image (TMA zero fill * scale + 0 = 0) - and
+//     the channel block is a compile-time constant (CB = 64 / RG), so every shared-memory offset is an immediate.
+template <int TY, int RG, int SMODE>
 __global__ void __launch_bounds__(512, 1) dw_bwd2_k(const __grid_constant__ CUtensorMap tmG,
                                                     const __grid_constant__ CUtensorMap tmS, const DwArgs a) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 127u) & ~127u;
   uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
-  const int CB = a.CB, rowb = CB * 2;
-  const uint32_t halo_bytes = (uint32_t)((TY + 2) * HW * rowb);
-  const uint32_t stage_bytes = 2u * halo_bytes;  // [g halo][src halo]
+  constexpr int CB = 64 / RG, rowb = CB * 2, nc2 = CB >> 1;
+  constexpr uint32_t halo_bytes = (uint32_t)((TY + 2) * HW * rowb);
+  constexpr uint32_t stage_bytes = 2u * halo_bytes;  // [g halo][src halo]
   const uint32_t bar0 = base + 2u * stage_bytes;
-  float* coef = reinterpret_cast<float*>(gbase + 2u * stage_bytes + 64);  // [scale CB][shift CB]
-  float* red = coef + 2 * 64;                                             // [512 / nc2 slots][11][CB]
-  const int nc2 = CB >> 1;
+  float* red = reinterpret_cast<float*>(gbase + 2u * stage_bytes + 64);  // [512 / nc2 slots][11][CB]
   constexpr int rows = TY / RG;
+  constexpr int nslot = 512 / nc2;
   const int tl = threadIdx.x;
   const int c2 = tl % nc2, col = (tl / nc2) % TX, rg = tl / (nc2 * TX), slot = tl / nc2;
-  const int nslot = 512 / nc2;
   const int spatial = a.tiles_x * a.tiles_y * a.B;
   const int t_lo = (int)(((long)blockIdx.x * a.total_tiles) / gridDim.x);
   const int t_hi = (int)(((long)(blockIdx.x + 1) * a.total_tiles) / gridDim.x);
@@ -800,6 +803,7 @@ __global__ void __launch_bounds__(512, 1) dw_bwd2_k(const __grid_constant__ CUte
 #pragma unroll
   for (int t = 0; t < 9; ++t) { wk[t] = 0ull; wacc[t] = 0ull; }
   f2_t bs1 = 0ull, bs2 = 0ull;  // BN-backward reductions of the layer below: sum dz and sum dz * a (see dw_bwd_k)
+  f2_t sc2 = 0ull, sh2 = 0ull;  // relu(bn) source: scale / shift of this thread's two channels
   int cur_cblk = -1;
 
   auto flush = [&](int cblk) {  // all 512 threads
@@ -822,6 +826,7 @@ __global__ void __launch_bounds__(512, 1) dw_bwd2_k(const __grid_constant__ CUte
     __syncthreads();
     for (int i = tl; i < 11 * CB; i += 512) {
       float v = 0.f;
+#pragma unroll 8
       for (int q = 0; q < nslot; ++q) v += red[q * 11 * CB + i];
       red[i] = v;  // slot 0, element i: read and written by this thread only
     }
@@ -860,15 +865,10 @@ __global__ void __launch_bounds__(512, 1) dw_bwd2_k(const __grid_constant__ CUte
         const float2 v = __ldg(reinterpret_cast<const float2*>(a.w + (8 - t) * a.C + cg));
         wk[t] = pk2(v.x, v.y);
       }
-      if (a.src_mode == 1) {
-        __syncthreads();  // the previous tile's pre-pass readers of coef are done
-        if (threadIdx.x < (CB >> 2)) {
-          const float4 s4 = __ldg(reinterpret_cast<const float4*>(a.src_bn + cblk * CB + threadIdx.x * 4));
-          const float4 h4 = __ldg(reinterpret_cast<const float4*>(a.src_bn + a.C + cblk * CB + threadIdx.x * 4));
-          *reinterpret_cast<float4*>(coef + threadIdx.x * 4) = s4;
-          *reinterpret_cast<float4*>(coef + CB + threadIdx.x * 4) = h4;
-        }
-        __syncthreads();
+      if (SMODE == 1) {
+        const float2 s_ = __ldg(reinterpret_cast<const float2*>(a.src_bn + cg));
+        const float2 h_ = __ldg(reinterpret_cast<const float2*>(a.src_bn + a.C + cg));
+        sc2 = pk2(s_.x, s_.y); sh2 = pk2(h_.x, h_.y);
       }
     }
     const int w0 = tx_i * TX, ty0 = ty_i * TY, h0 = ty0 + rg * rows;
@@ -882,60 +882,44 @@ __global__ void __launch_bounds__(512, 1) dw_bwd2_k(const __grid_constant__ CUte
         rres[i] = __ldg(reinterpret_cast<const uint32_t*>(
             a.resid_t + (((long)b * (a.H >> 1) + (oh >> 1)) * (a.W >> 1) + (gw >> 1)) * a.C + cg));
     }
-    mbar_wait(bar0 + 8u * stage, (uint32_t)(it >> 1) & 1u);
-    uint8_t* tile_g = gbase + stage * stage_bytes;
-    uint8_t* tile_a = tile_g + halo_bytes;
-
-    {  // activation pre-pass on the src halo, in place; out-of-image pixels stay zero
-      const int c8n = CB >> 3;
-      const int nchunk = (TY + 2) * HW * c8n;
-      if (a.src_mode == 0) {
-        for (int idx = threadIdx.x; idx < nchunk; idx += 512) {
-          uint4* q = reinterpret_cast<uint4*>(tile_a) + idx;
-          uint4 v = *q;
-          v.x = relu_bf2(v.x); v.y = relu_bf2(v.y); v.z = relu_bf2(v.z); v.w = relu_bf2(v.w);
-          *q = v;
-        }
-      } else {
-        const bool interior = w0 >= 1 && w0 + TX < a.W && ty0 >= 1 && ty0 + TY < a.H;
-        const int c8 = threadIdx.x % c8n;
-        f2_t scp[4], shp[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          scp[j] = *reinterpret_cast<const f2_t*>(coef + c8 * 8 + 2 * j);
-          shp[j] = *reinterpret_cast<const f2_t*>(coef + CB + c8 * 8 + 2 * j);
-        }
-        for (int idx = threadIdx.x; idx < nchunk; idx += 512) {
-          uint4* q = reinterpret_cast<uint4*>(tile_a) + idx;
-          uint4 v = *q;
-          v.x = f2_to_bf2_relu(ffma2(bf2_to_f2(v.x), scp[0], shp[0]));
-          v.y = f2_to_bf2_relu(ffma2(bf2_to_f2(v.y), scp[1], shp[1]));
-          v.z = f2_to_bf2_relu(ffma2(bf2_to_f2(v.z), scp[2], shp[2]));
-          v.w = f2_to_bf2_relu(ffma2(bf2_to_f2(v.w), scp[3], shp[3]));
-          if (!interior) {
-            const int pi = idx >> (c8n == 8 ? 3 : 2);  // c8n = CB / 8 is 8 or 4
-            const int hr = pi / HW, hc = pi - hr * HW;
-            const int gh = ty0 - 1 + hr, gx = w0 - 1 + hc;
-            if (gh < 0 || gh >= a.H || gx < 0 || gx >= a.W) v = make_uint4(0u, 0u, 0u, 0u);
-          }
-          *q = v;
-        }
-      }
-      __syncthreads();
+    // relu(bn): a halo pixel outside the image must read as 0, not relu(shift) - its shift is masked off (column masks per
+    // tile here, the row mask per window row below); only tiles on the image border take that path
+    const bool border = SMODE == 1 && !(w0 >= 1 && w0 + TX < a.W && ty0 >= 1 && ty0 + TY < a.H);
+    f2_t shk0 = sh2, shk2 = sh2, shk1 = sh2;
+    if (border) {
+      if (gw - 1 < 0 || gw - 1 >= a.W) shk0 = 0ull;
+      if (gw >= a.W) shk1 = 0ull;
+      if (gw + 1 >= a.W) shk2 = 0ull;
     }
+    mbar_wait(bar0 + 8u * stage, (uint32_t)(it >> 1) & 1u);
+    const uint8_t* tile_g = gbase + stage * stage_bytes;
+    const uint8_t* tile_a = tile_g + halo_bytes;
 
     f2_t wg[3][3], wa[3][3];
-    const size_t toff = (size_t)(((rg * rows) * HW + col) * rowb + c2 * 4);
+    const uint32_t toff = (uint32_t)(((rg * rows) * HW + col) * rowb + c2 * 4);
     const long out_rs = (long)a.W * a.C;
     __nv_bfloat16* const out_p = a.out + (((long)b * a.H + h0) * a.W + gw) * a.C + cg;
     const uint8_t* const g_row0 = tile_g + toff;
     const uint8_t* const a_row0 = tile_a + toff;
 #pragma unroll
     for (int r = 0; r < rows + 2; ++r) {
+      f2_t s0 = shk0, s1 = shk1, s2 = shk2;
+      if (border) {
+        const int gh = h0 - 1 + r;
+        if (gh < 0 || gh >= a.H) { s0 = 0ull; s1 = 0ull; s2 = 0ull; }
+      }
 #pragma unroll
       for (int kx = 0; kx < 3; ++kx) {
         wg[r % 3][kx] = bf2_to_f2(*reinterpret_cast<const uint32_t*>(g_row0 + (r * HW + kx) * rowb));
-        wa[r % 3][kx] = bf2_to_f2(*reinterpret_cast<const uint32_t*>(a_row0 + (r * HW + kx) * rowb));
+        const uint32_t av = *reinterpret_cast<const uint32_t*>(a_row0 + (r * HW + kx) * rowb);
+        if (SMODE == 0) {
+          wa[r % 3][kx] = bf2_to_f2(relu_bf2(av));
+        } else {
+          const f2_t y_ = ffma2(bf2_to_f2(av), sc2, kx == 0 ? s0 : (kx == 1 ? s1 : s2));
+          float lo, hi;
+          upk2(y_, lo, hi);
+          wa[r % 3][kx] = pk2(fmaxf(lo, 0.f), fmaxf(hi, 0.f));
+        }
       }
       if (r >= 2) {
         const int oh = h0 + r - 2;
@@ -956,29 +940,31 @@ __global__ void __launch_bounds__(512, 1) dw_bwd2_k(const __grid_constant__ CUte
         float o0, o1, a0, a1;
         upk2(acc, o0, o1);
         upk2(ac, a0, a1);
-        float r0 = 0.f, r1 = 0.f;
-        if (((r - 2) & 1) == 0) {
+        if (((r - 2) & 1) == 0) {  // (compile time: the residual-path gradient lives on even rows)
           const uint32_t rv = rres[(r - 2) / 2];
-          r0 = __uint_as_float(rv << 16); r1 = __uint_as_float(rv & 0xffff0000u);
-        }
-        if (a.resid == 2) {
-          o0 = a0 > 0.f ? o0 + r0 : 0.f;
-          o1 = a1 > 0.f ? o1 + r1 : 0.f;
+          const float r0 = __uint_as_float(rv << 16), r1 = __uint_as_float(rv & 0xffff0000u);
+          if (a.resid == 2) {
+            o0 = a0 > 0.f ? o0 + r0 : 0.f;
+            o1 = a1 > 0.f ? o1 + r1 : 0.f;
+          } else {
+            o0 = (a0 > 0.f ? o0 : 0.f) + r0;
+            o1 = (a1 > 0.f ? o1 : 0.f) + r1;
+          }
         } else {
-          o0 = (a0 > 0.f ? o0 : 0.f) + r0;
-          o1 = (a1 > 0.f ? o1 : 0.f) + r1;
+          o0 = a0 > 0.f ? o0 : 0.f;
+          o1 = a1 > 0.f ? o1 : 0.f;
         }
-        const uint32_t pk = pack2(o0, o1);
+        const bool inimg = oh < a.H && gw < a.W;
+        const uint32_t pk = inimg ? pack2(o0, o1) : 0u;
         if (a.rsums) {  // sums over the bf16-rounded dz, exactly what the apply pass reads back
           const f2_t d = bf2_to_f2(pk);
           bs1 = fadd2(bs1, d);
           bs2 = ffma2(d, ac, bs2);
         }
-        if (oh < a.H && gw < a.W) *reinterpret_cast<uint32_t*>(out_p + (r - 2) * out_rs) = pk;
+        if (inimg) *reinterpret_cast<uint32_t*>(out_p + (r - 2) * out_rs) = pk;
       }
     }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    __syncthreads();  // every thread is done with this stage before it is refilled
+    __syncthreads();  // every thread is done reading this stage before it is refilled
   }
   if (cur_cblk >= 0) flush(cur_cblk);
 }
@@ -1158,17 +1144,24 @@ int crackfl_dw3x3_bwd_tma_bn(const void* g, const void* src, const float* w, con
     if (a.CB == 64) ck::launch(dw_bwd_k<TY, 1>, grid, 512, smem, st, tmG, tmS, a);
     else ck::launch(dw_bwd_k<TY, 2>, grid, 512, smem, st, tmG, tmS, a);
   } else {
-    const size_t smem2 = 2 * 2 * (size_t)(TY + 2) * HW * a.CB * 2 + 64 + 2 * 64 * sizeof(float) +
+    const size_t smem2 = 2 * 2 * (size_t)(TY + 2) * HW * a.CB * 2 + 64 +
                          (size_t)(512 / (a.CB / 2)) * 11 * a.CB * sizeof(float) + 128;
     static bool attr2 = false;
     if (!attr2) {
-      cudaError_t e = cudaFuncSetAttribute(dw_bwd2_k<TY, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_bwd2_k<TY, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024);
+      cudaError_t e = cudaFuncSetAttribute(dw_bwd2_k<TY, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_bwd2_k<TY, 1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_bwd2_k<TY, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_bwd2_k<TY, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024);
       if (e != cudaSuccess) return (int)e;
       attr2 = true;
     }
-    if (a.CB == 64) ck::launch(dw_bwd2_k<TY, 1>, grid, 512, smem2, st, tmG, tmS, a);
-    else ck::launch(dw_bwd2_k<TY, 2>, grid, 512, smem2, st, tmG, tmS, a);
+    if (a.CB == 64) {
+      if (src_mode == 1) ck::launch(dw_bwd2_k<TY, 1, 1>, grid, 512, smem2, st, tmG, tmS, a);
+      else ck::launch(dw_bwd2_k<TY, 1, 0>, grid, 512, smem2, st, tmG, tmS, a);
+    } else {
+      if (src_mode == 1) ck::launch(dw_bwd2_k<TY, 2, 1>, grid, 512, smem2, st, tmG, tmS, a);
+      else ck::launch(dw_bwd2_k<TY, 2, 0>, grid, 512, smem2, st, tmG, tmS, a);
+    }
   }
   CK_LAUNCH_CHECK();
   return 0;

@@ -596,7 +596,7 @@ __device__ __forceinline__ void load_dz(const __nv_bfloat16* __restrict__ g, con
 
 // sums = [sum dz  C][sum dz*(y-mean)  C]   (centred moment: no cancellation; apply multiplies by invstd)
 template <int MODE>
-__global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : 3) bn_bwd_reduce_k(const __nv_bfloat16* __restrict__ g, const uint8_t* __restrict__ arg,
+__global__ void __launch_bounds__(TPB, MODE == 2 ? 2 : (MODE == 0 ? 4 : 3)) bn_bwd_reduce_k(const __nv_bfloat16* __restrict__ g, const uint8_t* __restrict__ arg,
                                                        const __nv_bfloat16* __restrict__ y, const float* __restrict__ bn,
                                                        float* __restrict__ sums, long P, int H, int W, int C,
                                                        int pix_per_block) {

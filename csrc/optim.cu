@@ -18,13 +18,13 @@ __global__ void __launch_bounds__(256) adam_k(float* __restrict__ p, float* __re
                                               float* __restrict__ v, int* __restrict__ step, long n4, float lr,
                                               float b1, float b2, float eps, unsigned* __restrict__ tail,
                                               float* __restrict__ total, const float* __restrict__ acc, int nacc,
-                                              float* __restrict__ last_acc, float* __restrict__ zbase, int zn) {
+                                              float* __restrict__ last_acc, float* __restrict__ zbase, int zn, int tplus) {
   ck::pdl_enter();
   __shared__ float s_lrt;
   __shared__ int s_t;
   __shared__ int s_last;
   if (threadIdx.x == 0) {
-    s_t = *step + (tail ? 1 : 0);
+    s_t = *step + ((tail || tplus) ? 1 : 0);
     const float t = (float)s_t;
     s_lrt = lr * sqrtf(1.f - powf(b2, t)) / (1.f - powf(b1, t));
   }
@@ -229,7 +229,22 @@ int crackfl_adam_step(float* p, float* g, float* m, float* v, int* step, long n,
   long blocks = (n4 + 255) / 256;
   if (blocks > 148 * opt_cap()) blocks = 148 * opt_cap();
   ck::launch(adam_k, (int)blocks, 256, 0, st, p, g, m, v, step, n4, lr, b1, b2, eps, (unsigned*)nullptr, (float*)nullptr,
-             (const float*)nullptr, 0, (float*)nullptr, (float*)nullptr, 0);
+             (const float*)nullptr, 0, (float*)nullptr, (float*)nullptr, 0, 0);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+// Adam over a sub-range of the arena BEFORE the step's crackfl_adam_step_tail launch (which covers the rest and publishes
+// the new step count): uses t = *step + 1 and leaves the counter alone.  The engine updates the decoder's parameters
+// this way as soon as the decoder's gradients are complete, next to the encoder's backward pass.
+int crackfl_adam_part(float* p, float* g, float* m, float* v, const int* step, long n, float lr, float b1, float b2, float eps,
+                      cudaStream_t st) {
+  if (n % 4 || n <= 0) return (int)cudaErrorInvalidValue;
+  const long n4 = n / 4;
+  long blocks = (n4 + 255) / 256;
+  if (blocks > 148 * opt_cap()) blocks = 148 * opt_cap();
+  ck::launch(adam_k, (int)blocks, 256, 0, st, p, g, m, v, const_cast<int*>(step), n4, lr, b1, b2, eps, (unsigned*)nullptr,
+             (float*)nullptr, (const float*)nullptr, 0, (float*)nullptr, (float*)nullptr, 0, 1);
   CK_LAUNCH_CHECK();
   return 0;
 }
@@ -245,7 +260,7 @@ int crackfl_adam_step_tail(float* p, float* g, float* m, float* v, int* step, lo
   long blocks = (n4 + 255) / 256;
   if (blocks > 148 * opt_cap()) blocks = 148 * opt_cap();
   ck::launch(adam_k, (int)blocks, 256, 0, st, p, g, m, v, step, n4, lr, b1, b2, eps, tail_counter, metrics_total, step_acc, nacc,
-             last_acc, zero_base, zero_n);
+             last_acc, zero_base, zero_n, 1);
   CK_LAUNCH_CHECK();
   return 0;
 }

@@ -222,6 +222,10 @@ int crackfl_weight_prep_flat(const float* arena, void* ops_bf16, const crackfl_p
 /* ref: client_fit_model.py:157 optimizer="Adam" (Keras form, eps 1e-7); also zeroes g */
 int crackfl_adam_step(float* p, float* g, float* m, float* v, int* step_dev, long n, float lr, float b1, float b2, float eps,
                       cudaStream_t stream);
+/* Adam over a sub-range, launched before the step's crackfl_adam_step_tail (which covers the rest and ticks the counter):
+   t = *step + 1, the counter is not written.  n % 4 == 0, pointers 16-byte aligned. */
+int crackfl_adam_part(float* p, float* g, float* m, float* v, const int* step_dev, long n, float lr, float b1, float b2, float eps,
+                      cudaStream_t stream);
 int crackfl_f32_to_bf16(const float* in, void* out, long n, cudaStream_t stream);
 /* total[i] += step[i], i < n <= 32 (per-epoch metric accumulation of the per-step loss/accuracy sums) */
 /* Adam + step-count tick + metric accumulation (metrics_total[i] += step_acc[i]) in one launch; *tail_counter == 0 on entry.

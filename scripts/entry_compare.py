@@ -15,7 +15,7 @@ for tc in ("0", "1"):
     eng = UNetEngine(S, B, H, H, cuda_graph=False)
     eng.load_weights(S.init_weights(0)); eng.reset_optimizer(); eng.set_batch(x, y)
     eng.zero_region.zero_(); eng.grads.zero_(); eng._region_dirty = True
-    eng._run(eng.train_prog[:-1])
+    eng._run(eng.grad_prog)
     torch.cuda.synchronize()
     t = S.tensors[S.index("conv2d/kernel")]
     res[tc] = (eng._bufs["y0"].float().clone(), eng.grads[t.offset:t.offset + t.numel].clone(),

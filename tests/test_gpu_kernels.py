@@ -266,6 +266,40 @@ def test_engine_training_reduces_loss_with_graph():
     assert p.shape == (8, 64, 64) and float(p.min()) >= 0 and float(p.max()) <= 1
 
 
+def test_early_decoder_adam_is_one_keras_adam_step():
+    """The step's Adam update runs as two launches (decoder + head parameters as soon as their gradients are complete, the
+    rest at the end of the step).  Two engine runs of one step differ by more than any useful tolerance (atomic summation
+    order -> bf16 roundings -> ReLU decisions), so the check is internal to one run: after every step, over the WHOLE
+    arena, v and the parameter change must be what Keras Adam makes of the gradient that m implies, with the same t."""
+    from crackfl.models.unet import UNetEngine
+    from crackfl.models.spec import REFERENCE_SPEC as S
+    from crackfl.data.generator import synth_crack_batch
+    x, y = synth_crack_batch(8, 64, 64, 3)
+    eng = UNetEngine(S, 8, 64, 64, cuda_graph=True)
+    assert eng.adam_early and any(e[0] is not None and e[0].__name__ == "crackfl_adam_part" for e in eng.train_prog)
+    eng.load_weights(S.init_weights(0)); eng.reset_optimizer()
+    b1, b2, lr, eps = eng.b1, eng.b2, eng.lr, eng.eps
+    m_prev = torch.zeros_like(eng.m); v_prev = torch.zeros_like(eng.v); p_prev = eng.arena.clone()
+    tr = torch.zeros(S.arena_numel, device="cuda")  # BN moving statistics live in the arena too and move in the forward pass
+    for tn in S.tensors:
+        if tn.trainable:
+            tr[tn.offset:tn.offset + tn.numel] = 1.0
+    for t in (1, 2, 3):
+        eng.train_step(x, y)
+        torch.cuda.synchronize()
+        assert int(eng.step.item()) == t
+        assert float(eng.grads.abs().max()) == 0.0  # both launches clear their part of the gradient arena
+        g = (eng.m - b1 * m_prev) / (1 - b1)
+        v_want = b2 * v_prev + (1 - b2) * g * g
+        assert float((eng.v - v_want).norm() / v_want.norm()) < 1e-3, t
+        lrt = lr * np.sqrt(1 - b2 ** t) / (1 - b1 ** t)
+        dp_want = -lrt * eng.m / (eng.v.sqrt() + eps)
+        dp = (eng.arena - p_prev) * tr
+        assert float((dp - dp_want).norm() / dp_want.norm()) < 1e-3, t
+        assert float(g[S.arena_numel // 2:].abs().max()) > 0 and float(g[:1024].abs().max()) > 0
+        m_prev, v_prev, p_prev = eng.m.clone(), eng.v.clone(), eng.arena.clone()
+
+
 def test_device_synth_and_measure():
     from crackfl.data.synthetic_device import synth_crack_batch_device
     from crackfl.postproc.device_measure import measure_masks_device, measure_masks_reference
