@@ -1881,12 +1881,16 @@ std::mutex g_maps_mu;
 // bf16 tensor with `rank` dims (innermost first) tightly packed; box per dim; swizzle 128B or 64B.
 }  // namespace
 
+// swz_bytes | CK_MAP_OOB_NAN: out-of-bounds elements are delivered as NaN instead of zero (for consumers that apply
+// relu(scale * x + shift) on load: max(NaN, 0) = 0, where a zero would have become relu(shift))
 int ck::get_tensor_map(const void* ptr, int rank, const int* dims, const int* box, int swz_bytes, CUtensorMap* out) {
+  const bool oob_nan = (swz_bytes & CK_MAP_OOB_NAN) != 0;
+  swz_bytes &= ~CK_MAP_OOB_NAN;
   MapKey k;
   memset(&k, 0, sizeof(k));
   k.ptr = ptr;
   for (int i = 0; i < rank; ++i) { k.d[i] = dims[i]; k.box[i] = box[i]; }
-  k.swz = swz_bytes * 8 + rank;
+  k.swz = swz_bytes * 8 + rank + (oob_nan ? (1 << 20) : 0);
   std::lock_guard<std::mutex> lk(g_maps_mu);
   auto it = g_maps.find(k);
   if (it != g_maps.end()) { *out = it->second; return 0; }
@@ -1906,7 +1910,8 @@ int ck::get_tensor_map(const void* ptr, int rank, const int* dims, const int* bo
   CUresult r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), gdim, gstr, bx, es,
                    CU_TENSOR_MAP_INTERLEAVE_NONE,
                    swz_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : (swz_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE),
-                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   oob_nan ? CU_TENSOR_MAP_FLOAT_OOB_FILL_NAN_REQUEST_ZERO_FMA : CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return 10000 + (int)r;
   g_maps[k] = tm;
   *out = tm;

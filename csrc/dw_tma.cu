@@ -463,6 +463,139 @@ __global__ void __launch_bounds__(256, 2) dw_wgrad_k(const __grid_constant__ CUt
   if (cur_cblk >= 0) flush(cur_cblk);
 }
 
+// Third generation of the forward stencil.  ncu on dw_stencil_k (64 channels, 128x128): the in-place activation pre-pass
+// is 28 % of the instructions and 41 % of the stall samples (its barrier, dependent LDS -> STS round trips, the
+// coefficient hand-off through shared memory).  Here the activation is applied to the three words a thread loads per
+// window row; the halo comes through a tensor map that delivers out-of-image pixels as NaN, so relu(scale * x + shift)
+// is exactly 0 there (max(NaN, 0) = 0) with no border masks; the channel block is a compile-time constant; every thread
+// computes the BN coefficients of its own four channels; a CTA owns a contiguous range of tiles.
+template <int TY, int RG, int AMODE>
+__global__ void __launch_bounds__(256, 2) dw_fwd2_k(const __grid_constant__ CUtensorMap tmX, const DwArgs a) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 127u) & ~127u;
+  uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
+  constexpr int CB = 64 / RG, rowb = CB * 2, nc4 = CB >> 2;
+  constexpr uint32_t stage_bytes = (uint32_t)((TY + 2) * HW * rowb);
+  const int NS = a.nstage;
+  const uint32_t bar0 = base + (uint32_t)NS * stage_bytes;
+  constexpr int rows = TY / RG;
+  const int c4 = threadIdx.x % nc4, col = (threadIdx.x / nc4) % TX, rg = threadIdx.x / (nc4 * TX);
+  const int spatial = a.tiles_x * a.tiles_y * a.B;
+  const int t_lo = (int)(((long)blockIdx.x * a.total_tiles) / gridDim.x);
+  const int t_hi = (int)(((long)(blockIdx.x + 1) * a.total_tiles) / gridDim.x);
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < NS; ++i) mbar_init(bar0 + 8u * i, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    tma_prefetch_desc(&tmX);
+  }
+  pdl_enter();
+  fin_publish(a.fin, a.C);
+  __syncthreads();
+
+  auto issue = [&](int tile, int stage) {
+    const int cblk = dw_fdiv(tile, a.m_sp);
+    const int sp = tile - cblk * spatial;
+    const int q_ = dw_fdiv(sp, a.m_tx);
+    const int tx_i = sp - q_ * a.tiles_x;
+    const int b = dw_fdiv(q_, a.m_ty);
+    const int ty_i = q_ - b * a.tiles_y;
+    mbar_expect_tx(bar0 + 8u * stage, stage_bytes);
+    tma_load_4d(base + stage * stage_bytes, &tmX, bar0 + 8u * stage, cblk * CB, tx_i * TX - 1, ty_i * TY - 1, b);
+  };
+  if (threadIdx.x == 0)
+    for (int i = 0; i < NS - 1; ++i)
+      if (t_lo + i < t_hi) issue(t_lo + i, i);
+
+  int cur_cblk = -1;
+  f2_t wk[9][2], sc[2] = {0ull, 0ull}, sh[2] = {0ull, 0ull};
+  int stage = 0;
+  uint32_t par = 0;
+  for (int tile = t_lo; tile < t_hi; ++tile) {
+    {
+      // refill the stage consumed in the previous iteration (its last readers passed the barrier at the loop tail)
+      const int nxt = tile + (NS - 1);
+      const int ns = stage == 0 ? NS - 1 : stage - 1;
+      if (threadIdx.x == 0 && nxt < t_hi) issue(nxt, ns);
+    }
+    const int cblk = dw_fdiv(tile, a.m_sp);
+    const int sp = tile - cblk * spatial;
+    const int q_ = dw_fdiv(sp, a.m_tx);
+    const int tx_i = sp - q_ * a.tiles_x;
+    const int b = dw_fdiv(q_, a.m_ty);
+    const int ty_i = q_ - b * a.tiles_y;
+    const int cg = cblk * CB + c4 * 4;  // first global channel of this thread
+    if (cblk != cur_cblk) {             // uniform over the CTA
+      cur_cblk = cblk;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(a.w + (a.flip ? 8 - t : t) * a.C + cg));
+        wk[t][0] = pk2(v.x, v.y); wk[t][1] = pk2(v.z, v.w);
+      }
+      if (AMODE == 1) {
+        float s_[4], h_[4];
+        coeffs4(a.fin, a.bn, a.C, cg, s_, h_);
+        sc[0] = pk2(s_[0], s_[1]); sc[1] = pk2(s_[2], s_[3]);
+        sh[0] = pk2(h_[0], h_[1]); sh[1] = pk2(h_[2], h_[3]);
+      }
+    }
+    const int w0 = tx_i * TX, ty0 = ty_i * TY, h0 = ty0 + rg * rows;
+    const int gw = w0 + col;
+    mbar_wait(bar0 + 8u * stage, par);
+    const uint8_t* tile_s = gbase + stage * stage_bytes;
+
+    f2_t win[3][3][2];
+    const long out_rs = (long)a.W * a.C;  // elements per image row
+    __nv_bfloat16* const out_p = a.out + (((long)b * a.H + h0) * a.W + gw) * a.C + cg;
+    const uint8_t* const row0 = tile_s + (uint32_t)(((rg * rows) * HW + col) * rowb + c4 * 8);
+#pragma unroll
+    for (int r = 0; r < rows + 2; ++r) {
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        uint2 v = *reinterpret_cast<const uint2*>(row0 + (r * HW + kx) * rowb);
+        if (AMODE == 0) {
+          win[r % 3][kx][0] = bf2_to_f2(relu_bf2(v.x));
+          win[r % 3][kx][1] = bf2_to_f2(relu_bf2(v.y));
+        } else if (AMODE == 1) {
+          float l0, h0_, l1, h1;
+          upk2(ffma2(bf2_to_f2(v.x), sc[0], sh[0]), l0, h0_);
+          upk2(ffma2(bf2_to_f2(v.y), sc[1], sh[1]), l1, h1);
+          win[r % 3][kx][0] = pk2(fmaxf(l0, 0.f), fmaxf(h0_, 0.f));
+          win[r % 3][kx][1] = pk2(fmaxf(l1, 0.f), fmaxf(h1, 0.f));
+        } else {
+          win[r % 3][kx][0] = bf2_to_f2(v.x);
+          win[r % 3][kx][1] = bf2_to_f2(v.y);
+        }
+      }
+      if (r >= 2) {
+        const int oh = h0 + r - 2;
+        f2_t p0[3], p1[3];  // one partial sum per window row: three independent chains per channel pair
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
+          p0[ky] = fmul2(win[(r - 2 + ky) % 3][0][0], wk[ky * 3][0]);
+          p1[ky] = fmul2(win[(r - 2 + ky) % 3][0][1], wk[ky * 3][1]);
+#pragma unroll
+          for (int kx = 1; kx < 3; ++kx) {
+            p0[ky] = ffma2(win[(r - 2 + ky) % 3][kx][0], wk[ky * 3 + kx][0], p0[ky]);
+            p1[ky] = ffma2(win[(r - 2 + ky) % 3][kx][1], wk[ky * 3 + kx][1], p1[ky]);
+          }
+        }
+        float o4[4];
+        upk2(fadd2(fadd2(p0[0], p0[1]), p0[2]), o4[0], o4[1]);
+        upk2(fadd2(fadd2(p1[0], p1[1]), p1[2]), o4[2], o4[3]);
+        if (oh < a.H && gw < a.W) {
+          uint2 pk;
+          pk.x = pack2(o4[0], o4[1]);
+          pk.y = pack2(o4[2], o4[3]);
+          *reinterpret_cast<uint2*>(out_p + (r - 2) * out_rs) = pk;
+        }
+      }
+    }
+    __syncthreads();  // every thread is done reading this stage before it is refilled
+    if (++stage == NS) { stage = 0; par ^= 1u; }
+  }
+}
+
 // Depthwise backward in ONE pass (third generation): the gradient tile g (with halo) and the forward-input tile src (with
 // halo) are staged once; after an in-place activation pre-pass on src (a = relu(src) or relu(bn(src)))
 //   warps 0-7   compute the input gradient  dz = (3x3^T g) * [a > 0] (+ residual-path gradient) and,
@@ -1054,7 +1187,38 @@ int crackfl_dw3x3_tma(const void* x, const float* w, const float* bn, const crac
     if (act_mode != 2) return (int)cudaErrorInvalidValue;  // the gradient variant takes g as is
     return launch_stencil<8, true>(x, a, st);
   }
-  return launch_stencil<16, false>(x, a, st);
+  static int gen = -1;  // CRACKFL_DW_FWD=2: the pre-pass kernel (dw_stencil_k); default: activation on load (dw_fwd2_k)
+  if (gen < 0) { const char* e = getenv("CRACKFL_DW_FWD"); gen = e ? atoi(e) : 3; }
+  if (gen == 2) return launch_stencil<16, false>(x, a, st);
+  constexpr int TY = 16;
+  const size_t extra = 64 + 128;
+  pick_ring(a, (size_t)(TY + 2) * HW * 2, extra);
+  a.tiles_x = (a.W + TX - 1) / TX; a.tiles_y = (a.H + TY - 1) / TY;
+  a.total_tiles = a.tiles_x * a.tiles_y * a.B * (a.C / a.CB);
+  a.m_sp = dw_magic(a.tiles_x * a.tiles_y * a.B); a.m_tx = dw_magic(a.tiles_x); a.m_ty = dw_magic(a.tiles_y);
+  CUtensorMap tm;
+  const int d[4] = {a.C, a.W, a.H, a.B}, bx[4] = {a.CB, HW, TY + 2, 1};
+  // relu / relu(bn) sources: out-of-image pixels arrive as NaN and leave the activation as exact zeros
+  int rc = ck::get_tensor_map(x, 4, d, bx, act_mode == 2 ? 0 : ck::CK_MAP_OOB_NAN, &tm);
+  if (rc) return rc;
+  const size_t smem = (size_t)a.nstage * (TY + 2) * HW * a.CB * 2 + extra;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaSuccess;
+#define CK_DWF_ATTR(RG_, AM_) if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_fwd2_k<TY, RG_, AM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+    CK_DWF_ATTR(1, 0) CK_DWF_ATTR(1, 1) CK_DWF_ATTR(1, 2) CK_DWF_ATTR(2, 0) CK_DWF_ATTR(2, 1) CK_DWF_ATTR(2, 2)
+#undef CK_DWF_ATTR
+    if (e != cudaSuccess) return (int)e;
+    attr = true;
+  }
+  int grid = dw_per_sm() * num_sms();
+  if (grid > a.total_tiles) grid = a.total_tiles;
+#define CK_DWF_GO(RG_, AM_) ck::launch(dw_fwd2_k<TY, RG_, AM_>, grid, 256, smem, st, tm, a)
+  if (a.CB == 64) { if (act_mode == 0) CK_DWF_GO(1, 0); else if (act_mode == 1) CK_DWF_GO(1, 1); else CK_DWF_GO(1, 2); }
+  else { if (act_mode == 0) CK_DWF_GO(2, 0); else if (act_mode == 1) CK_DWF_GO(2, 1); else CK_DWF_GO(2, 2); }
+#undef CK_DWF_GO
+  CK_LAUNCH_CHECK();
+  return 0;
 }
 
 int crackfl_dw3x3_wgrad_tma(const void* g, const void* src, const float* bn, float* dwk, int B, int H, int W, int C, int mode,

@@ -6,6 +6,7 @@
 
 namespace ck {
 // host: cached cuTensorMapEncodeTiled for a tightly packed bf16 tensor (dims innermost first); swizzle 128 / 64 / 0 bytes
+constexpr int CK_MAP_OOB_NAN = 0x1000;  // flag or-ed into swz_bytes
 int get_tensor_map(const void* ptr, int rank, const int* dims, const int* box, int swz_bytes, CUtensorMap* out);
 }  // namespace ck
 
