@@ -797,6 +797,10 @@ class UNetEngine:
             if isinstance(tag, tuple):  # ("rec" | "wait", stream, key): explicit event edges between the extra streams
                 if self.side_streams:
                     s_ = main if tag[1] == "main" else streams[tag[1]]
+                    if tag[0] == "rec" and s_ is not main and not forked.get(tag[1], False):
+                        continue  # nothing was launched on that stream since the last join: there is nothing to wait for
+                    if tag[0] == "wait" and tag[2] not in events:
+                        continue
                     if tag[0] == "rec":
                         events[tag[2]] = torch.cuda.Event()
                         events[tag[2]].record(s_)

@@ -6,8 +6,9 @@ lines = open(path).read().splitlines()
 i = next(k for k, l in enumerate(lines) if l.startswith('"ID"'))
 rows = list(csv.DictReader(io.StringIO("\n".join(lines[i:]))))
 names = [re.sub(r'^(void )?<unnamed>::', '', r['Kernel Name']).split('(')[0] for r in rows]
-ad = [k for k, n in enumerate(names) if n.startswith('adam_k')]
-s, e = ad[-2] + 1, ad[-1] + 1
+# a step runs from one weight re-layout launch (first entry of the schedule) to the next; the step has two adam_k launches
+ad = [k for k, n in enumerate(names) if n.startswith('weight_prep')]
+s, e = ad[-2], ad[-1]
 tot = 0
 agg = collections.defaultdict(lambda: [0, 0.0])
 out = []
