@@ -2427,10 +2427,11 @@ static int wgrad_impl(const void* X, const void* dY, float* dW, int B, int H, in
   if (stages > 6) stages = 6;
   static int fill = -1;  // tuning knob: percentage of the 148 * per_sm CTA slots the split count may fill
   if (fill < 0) { const char* e = getenv("CRACKFL_WGRAD_FILL"); fill = e ? atoi(e) : 0; if (fill < 10 || fill > 100) fill = 0; }
-  // default: every slot when the partial tiles go to a workspace (one reduction launch sums them), three quarters of
-  // them when they are added to the arena with vector atomics (fewer, longer CTAs = fewer contended reductions per
-  // element; measured on the full step: 1.287 / 1.274 / 1.263 / 1.281 ms at 100 / 60 / 75 / 50 %)
-  const int fill_eff = fill ? fill : ((!workspace && mode == 0) ? 75 : 100);
+  // default: every slot when the partial tiles go to a workspace (one reduction launch sums them), half of them when they
+  // are added to the arena with vector atomics (fewer, longer CTAs = fewer contended reductions per element and more room
+  // for the main chain; measured on the full step at the 1.03 ms build: 1.029 / 1.025 / 1.028 / 1.027 / 1.031 / 1.068 ms
+  // at 40 / 50 / 60 / 67 / 75 / 90 %)
+  const int fill_eff = fill ? fill : ((!workspace && mode == 0) ? 50 : 100);
   int splits = (148 * per_sm * fill_eff / 100) / (groups * ntn);
   if (splits > a.ntiles) splits = a.ntiles;
   if (splits < 1) splits = 1;

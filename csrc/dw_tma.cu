@@ -888,8 +888,9 @@ __global__ void __launch_bounds__(512, 1) dw_bwd_k(const __grid_constant__ CUten
 //   * (ncu on the first version of this kernel: the in-place activation pre-pass over the src halo was 25 % of all
 //     instructions and 28 % of the stall samples, ~80 instructions per 16-byte chunk with its barrier) the activation is
 //     applied to the three window values a thread loads per row instead - relu on the packed word, or FFMA2 + max for
-//     relu(bn) with the shift masked off where the halo pixel is outside the image (TMA zero fill * scale + 0 = 0) - and
-//     the channel block is a compile-time constant (CB = 64 / RG), so every shared-memory offset is an immediate.
+//     relu(bn); the src halo comes through a tensor map that delivers out-of-image pixels as NaN, so both give an exact
+//     zero there (max(NaN, 0) = 0) with no border masks - and the channel block is a compile-time constant
+//     (CB = 64 / RG), so every shared-memory offset is an immediate.
 template <int TY, int RG, int SMODE>
 __global__ void __launch_bounds__(512, 1) dw_bwd2_k(const __grid_constant__ CUtensorMap tmG,
                                                     const __grid_constant__ CUtensorMap tmS, const DwArgs a) {
@@ -1015,15 +1016,6 @@ __global__ void __launch_bounds__(512, 1) dw_bwd2_k(const __grid_constant__ CUte
         rres[i] = __ldg(reinterpret_cast<const uint32_t*>(
             a.resid_t + (((long)b * (a.H >> 1) + (oh >> 1)) * (a.W >> 1) + (gw >> 1)) * a.C + cg));
     }
-    // relu(bn): a halo pixel outside the image must read as 0, not relu(shift) - its shift is masked off (column masks per
-    // tile here, the row mask per window row below); only tiles on the image border take that path
-    const bool border = SMODE == 1 && !(w0 >= 1 && w0 + TX < a.W && ty0 >= 1 && ty0 + TY < a.H);
-    f2_t shk0 = sh2, shk2 = sh2, shk1 = sh2;
-    if (border) {
-      if (gw - 1 < 0 || gw - 1 >= a.W) shk0 = 0ull;
-      if (gw >= a.W) shk1 = 0ull;
-      if (gw + 1 >= a.W) shk2 = 0ull;
-    }
     mbar_wait(bar0 + 8u * stage, (uint32_t)(it >> 1) & 1u);
     const uint8_t* tile_g = gbase + stage * stage_bytes;
     const uint8_t* tile_a = tile_g + halo_bytes;
@@ -1036,11 +1028,6 @@ __global__ void __launch_bounds__(512, 1) dw_bwd2_k(const __grid_constant__ CUte
     const uint8_t* const a_row0 = tile_a + toff;
 #pragma unroll
     for (int r = 0; r < rows + 2; ++r) {
-      f2_t s0 = shk0, s1 = shk1, s2 = shk2;
-      if (border) {
-        const int gh = h0 - 1 + r;
-        if (gh < 0 || gh >= a.H) { s0 = 0ull; s1 = 0ull; s2 = 0ull; }
-      }
 #pragma unroll
       for (int kx = 0; kx < 3; ++kx) {
         wg[r % 3][kx] = bf2_to_f2(*reinterpret_cast<const uint32_t*>(g_row0 + (r * HW + kx) * rowb));
@@ -1048,7 +1035,7 @@ __global__ void __launch_bounds__(512, 1) dw_bwd2_k(const __grid_constant__ CUte
         if (SMODE == 0) {
           wa[r % 3][kx] = bf2_to_f2(relu_bf2(av));
         } else {
-          const f2_t y_ = ffma2(bf2_to_f2(av), sc2, kx == 0 ? s0 : (kx == 1 ? s1 : s2));
+          const f2_t y_ = ffma2(bf2_to_f2(av), sc2, sh2);  // out-of-image pixels arrive as NaN: max(NaN, 0) = 0
           float lo, hi;
           upk2(y_, lo, hi);
           wa[r % 3][kx] = pk2(fmaxf(lo, 0.f), fmaxf(hi, 0.f));
@@ -1257,6 +1244,47 @@ int crackfl_dw3x3_wgrad_tma(const void* g, const void* src, const float* bn, flo
   return 0;
 }
 
+}  // extern "C"
+
+namespace {
+// dw_bwd2_k with TY tile rows (a: everything but the tile geometry filled in)
+template <int TY>
+int launch_bwd2(const void* g, const void* src, DwArgs& a, cudaStream_t st) {
+  a.tiles_x = (a.W + TX - 1) / TX; a.tiles_y = (a.H + TY - 1) / TY;
+  a.total_tiles = a.tiles_x * a.tiles_y * a.B * (a.C / a.CB);
+  a.m_sp = dw_magic(a.tiles_x * a.tiles_y * a.B); a.m_tx = dw_magic(a.tiles_x); a.m_ty = dw_magic(a.tiles_y);
+  CUtensorMap tmG, tmS;
+  const int d[4] = {a.C, a.W, a.H, a.B}, bx[4] = {a.CB, HW, TY + 2, 1};
+  int rc = ck::get_tensor_map(g, 4, d, bx, 0, &tmG);
+  if (rc) return rc;
+  rc = ck::get_tensor_map(src, 4, d, bx, ck::CK_MAP_OOB_NAN, &tmS);
+  if (rc) return rc;
+  const size_t smem = 2 * 2 * (size_t)(TY + 2) * HW * a.CB * 2 + 64 + (size_t)(512 / (a.CB / 2)) * 11 * a.CB * sizeof(float) + 128;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(dw_bwd2_k<TY, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_bwd2_k<TY, 1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_bwd2_k<TY, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_bwd2_k<TY, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    if (e != cudaSuccess) return (int)e;
+    attr = true;
+  }
+  int grid = num_sms();
+  if (grid > a.total_tiles) grid = a.total_tiles;
+  if (a.CB == 64) {
+    if (a.src_mode == 1) ck::launch(dw_bwd2_k<TY, 1, 1>, grid, 512, smem, st, tmG, tmS, a);
+    else ck::launch(dw_bwd2_k<TY, 1, 0>, grid, 512, smem, st, tmG, tmS, a);
+  } else {
+    if (a.src_mode == 1) ck::launch(dw_bwd2_k<TY, 2, 1>, grid, 512, smem, st, tmG, tmS, a);
+    else ck::launch(dw_bwd2_k<TY, 2, 0>, grid, 512, smem, st, tmG, tmS, a);
+  }
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
 // dz (input gradient) and dW (weight gradient) of the depthwise 3x3 in one pass; arguments as crackfl_dw3x3_tma (gradient
 // variant) + crackfl_dw3x3_wgrad_tma
 int crackfl_dw3x3_bwd_tma_bn(const void* g, const void* src, const float* w, const float* src_bn, const void* resid_t, void* dz,
@@ -1304,29 +1332,16 @@ int crackfl_dw3x3_bwd_tma_bn(const void* g, const void* src, const float* w, con
   if (grid > a.total_tiles) grid = a.total_tiles;
   static int gen = -1;  // CRACKFL_DW_BWD=3: the role-split kernel; default: every thread does both gradients (dw_bwd2_k)
   if (gen < 0) { const char* e = getenv("CRACKFL_DW_BWD"); gen = e ? atoi(e) : 4; }
-  if (gen == 3) {
-    if (a.CB == 64) ck::launch(dw_bwd_k<TY, 1>, grid, 512, smem, st, tmG, tmS, a);
-    else ck::launch(dw_bwd_k<TY, 2>, grid, 512, smem, st, tmG, tmS, a);
-  } else {
-    const size_t smem2 = 2 * 2 * (size_t)(TY + 2) * HW * a.CB * 2 + 64 +
-                         (size_t)(512 / (a.CB / 2)) * 11 * a.CB * sizeof(float) + 128;
-    static bool attr2 = false;
-    if (!attr2) {
-      cudaError_t e = cudaFuncSetAttribute(dw_bwd2_k<TY, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_bwd2_k<TY, 1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_bwd2_k<TY, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(dw_bwd2_k<TY, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024);
-      if (e != cudaSuccess) return (int)e;
-      attr2 = true;
-    }
-    if (a.CB == 64) {
-      if (src_mode == 1) ck::launch(dw_bwd2_k<TY, 1, 1>, grid, 512, smem2, st, tmG, tmS, a);
-      else ck::launch(dw_bwd2_k<TY, 1, 0>, grid, 512, smem2, st, tmG, tmS, a);
-    } else {
-      if (src_mode == 1) ck::launch(dw_bwd2_k<TY, 2, 1>, grid, 512, smem2, st, tmG, tmS, a);
-      else ck::launch(dw_bwd2_k<TY, 2, 0>, grid, 512, smem2, st, tmG, tmS, a);
-    }
+  if (gen != 3) {
+    // tile rows per channel block width (CRACKFL_DW_BWD_TY64 / _TY32 = 8 | 16): 16 halves the halo rows per output row
+    static int ty64 = -1, ty32 = -1;
+    if (ty64 < 0) { const char* e = getenv("CRACKFL_DW_BWD_TY64"); ty64 = e ? atoi(e) : 16; }
+    if (ty32 < 0) { const char* e = getenv("CRACKFL_DW_BWD_TY32"); ty32 = e ? atoi(e) : 16; }
+    const int ty = a.CB == 64 ? ty64 : ty32;
+    return (ty == 16 && H >= 16) ? launch_bwd2<16>(g, src, a, st) : launch_bwd2<8>(g, src, a, st);
   }
+  if (a.CB == 64) ck::launch(dw_bwd_k<TY, 1>, grid, 512, smem, st, tmG, tmS, a);
+  else ck::launch(dw_bwd_k<TY, 2>, grid, 512, smem, st, tmG, tmS, a);
   CK_LAUNCH_CHECK();
   return 0;
 }
