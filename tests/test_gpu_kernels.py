@@ -266,6 +266,24 @@ def test_engine_training_reduces_loss_with_graph():
     assert p.shape == (8, 64, 64) and float(p.min()) >= 0 and float(p.max()) <= 1
 
 
+def test_weight_prep_flat_matches_per_operand_grid():
+    """One 32x32 tile per block over all 43 operands (weight_prep_flat_k) writes exactly what the per-operand grid
+    (weight_prep_k) writes: every bf16 GEMM operand of the model, forward and transposed, padded entry kernel included."""
+    from crackfl.models.unet import UNetEngine
+    from crackfl.models.spec import REFERENCE_SPEC as S, wide_spec
+    L, lib = _lib()
+    for spec in (S, wide_spec(2)):
+        eng = UNetEngine(spec, 2, 32, 32, cuda_graph=False)
+        eng.load_weights(spec.init_weights(3))
+        a = torch.zeros_like(eng.ops_buf); b = torch.zeros_like(eng.ops_buf)
+        L.check(lib.crackfl_weight_prep(eng.arena.data_ptr(), a.data_ptr(), eng.desc_dev.data_ptr(), eng.num_desc, _st()))
+        L.check(lib.crackfl_weight_prep_flat(eng.arena.data_ptr(), b.data_ptr(), eng.desc_dev.data_ptr(),
+                                             eng.prep_prefix.data_ptr(), eng.num_desc, eng.prep_tiles, _st()))
+        torch.cuda.synchronize()
+        assert float(a.float().abs().sum()) > 0
+        assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+
+
 def test_early_decoder_adam_is_one_keras_adam_step():
     """The step's Adam update runs as two launches (decoder + head parameters as soon as their gradients are complete, the
     rest at the end of the step).  Two engine runs of one step differ by more than any useful tolerance (atomic summation
