@@ -6,7 +6,7 @@ from __future__ import annotations
 import argparse
 import sys
 
-from ..protocol.server import FLServer, HostAggregator, serve_forever
+from ..protocol.server import FLServer, serve_forever
 from ..trainer import spec_from_config
 from .common import parse_with_config
 

@@ -1,7 +1,6 @@
 """``client_fit_model`` - ``learning_fit(mt, ec, bs, pr, cr)`` with the reference's call surface
 (client_fit_model.py:46-52,225-240; used at fl_client.py:102,109,154,165)."""
 import os
-import pickle
 
 from ..config import Config
 from ..data.generator import Generator  # noqa: F401  (the reference module also exports it)

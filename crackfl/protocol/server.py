@@ -39,7 +39,7 @@ import numpy as np
 from ..config import Config
 from ..io import checkpoint as ckpt
 from ..io import weights as wio
-from ..parallel.fedavg import FedAdam, FedAvg, make_strategy
+from ..parallel.fedavg import make_strategy
 from . import messages as pb
 
 SW, CTW = "SW", "CTW"
