@@ -489,6 +489,19 @@ __global__ void __launch_bounds__(256, 2) dw_fwd2_k(const __grid_constant__ CUte
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     tma_prefetch_desc(&tmX);
   }
+  // the stencil weights are parameters (last written by the previous step's Adam, long complete): the first channel
+  // block's nine float4 loads go out BEFORE the wait on the previous kernel (ncu: ~8 % of the samples of the whole kernel
+  // sat on that first dependent load)
+  f2_t wk[9][2], sc[2] = {0ull, 0ull}, sh[2] = {0ull, 0ull};
+  int w_cblk = -1;
+  if (t_lo < t_hi) {
+    w_cblk = dw_fdiv(t_lo, a.m_sp);
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      const float4 v = __ldg(reinterpret_cast<const float4*>(a.w + (a.flip ? 8 - t : t) * a.C + w_cblk * CB + c4 * 4));
+      wk[t][0] = pk2(v.x, v.y); wk[t][1] = pk2(v.z, v.w);
+    }
+  }
   pdl_enter();
   fin_publish(a.fin, a.C);
   __syncthreads();
@@ -508,7 +521,6 @@ __global__ void __launch_bounds__(256, 2) dw_fwd2_k(const __grid_constant__ CUte
       if (t_lo + i < t_hi) issue(t_lo + i, i);
 
   int cur_cblk = -1;
-  f2_t wk[9][2], sc[2] = {0ull, 0ull}, sh[2] = {0ull, 0ull};
   int stage = 0;
   uint32_t par = 0;
   for (int tile = t_lo; tile < t_hi; ++tile) {
@@ -527,10 +539,13 @@ __global__ void __launch_bounds__(256, 2) dw_fwd2_k(const __grid_constant__ CUte
     const int cg = cblk * CB + c4 * 4;  // first global channel of this thread
     if (cblk != cur_cblk) {             // uniform over the CTA
       cur_cblk = cblk;
+      if (cblk != w_cblk) {
+        w_cblk = cblk;
 #pragma unroll
-      for (int t = 0; t < 9; ++t) {
-        const float4 v = __ldg(reinterpret_cast<const float4*>(a.w + (a.flip ? 8 - t : t) * a.C + cg));
-        wk[t][0] = pk2(v.x, v.y); wk[t][1] = pk2(v.z, v.w);
+        for (int t = 0; t < 9; ++t) {
+          const float4 v = __ldg(reinterpret_cast<const float4*>(a.w + (a.flip ? 8 - t : t) * a.C + cg));
+          wk[t][0] = pk2(v.x, v.y); wk[t][1] = pk2(v.z, v.w);
+        }
       }
       if (AMODE == 1) {
         float s_[4], h_[4];
@@ -917,6 +932,20 @@ __global__ void __launch_bounds__(512, 1) dw_bwd2_k(const __grid_constant__ CUte
     tma_prefetch_desc(&tmG);
     tma_prefetch_desc(&tmS);
   }
+  // the (flipped) stencil weights of the first channel block are fetched BEFORE the wait on the previous kernel: they are
+  // parameters, last written by the previous step's Adam (ncu: 8 % of the kernel's samples sat on that first load)
+  f2_t wk[9], wacc[9];
+  int w_cblk = -1;
+#pragma unroll
+  for (int t = 0; t < 9; ++t) { wk[t] = 0ull; wacc[t] = 0ull; }
+  if (t_lo < t_hi) {
+    w_cblk = dw_fdiv(t_lo, a.m_sp);
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      const float2 v = __ldg(reinterpret_cast<const float2*>(a.w + (8 - t) * a.C + w_cblk * CB + c2 * 2));
+      wk[t] = pk2(v.x, v.y);
+    }
+  }
   pdl_enter();
   __syncthreads();
 
@@ -933,9 +962,6 @@ __global__ void __launch_bounds__(512, 1) dw_bwd2_k(const __grid_constant__ CUte
   };
   if (threadIdx.x == 0 && t_lo < t_hi) issue(t_lo, 0);
 
-  f2_t wk[9], wacc[9];
-#pragma unroll
-  for (int t = 0; t < 9; ++t) { wk[t] = 0ull; wacc[t] = 0ull; }
   f2_t bs1 = 0ull, bs2 = 0ull;  // BN-backward reductions of the layer below: sum dz and sum dz * a (see dw_bwd_k)
   f2_t sc2 = 0ull, sh2 = 0ull;  // relu(bn) source: scale / shift of this thread's two channels
   int cur_cblk = -1;
@@ -994,10 +1020,13 @@ __global__ void __launch_bounds__(512, 1) dw_bwd2_k(const __grid_constant__ CUte
     if (cblk != cur_cblk) {  // uniform over the CTA
       if (cur_cblk >= 0) flush(cur_cblk);
       cur_cblk = cblk;
+      if (cblk != w_cblk) {
+        w_cblk = cblk;
 #pragma unroll
-      for (int t = 0; t < 9; ++t) {
-        const float2 v = __ldg(reinterpret_cast<const float2*>(a.w + (8 - t) * a.C + cg));
-        wk[t] = pk2(v.x, v.y);
+        for (int t = 0; t < 9; ++t) {
+          const float2 v = __ldg(reinterpret_cast<const float2*>(a.w + (8 - t) * a.C + cg));
+          wk[t] = pk2(v.x, v.y);
+        }
       }
       if (SMODE == 1) {
         const float2 s_ = __ldg(reinterpret_cast<const float2*>(a.src_bn + cg));
