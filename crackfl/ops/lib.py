@@ -84,6 +84,7 @@ _SIGS = {
     "crackfl_pool_bwd": [vp, vp, vp, i32, i32, i32, i32, vp],
     "crackfl_pool_bwd_bn": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],
     "crackfl_down2sum": [vp, vp, vp, vp, i32, i32, i32, i32, vp],
+    "crackfl_down2sum_bn": [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],
     "crackfl_relu_bwd_add": [vp, vp, vp, vp, i64, vp],
     "crackfl_colsum": [vp, vp, i64, i32, vp],
     "crackfl_head_fwd": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],

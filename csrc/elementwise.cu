@@ -539,6 +539,79 @@ __global__ void __launch_bounds__(TPB) down2sum_k(const __nv_bfloat16* __restric
   }
 }
 
+// down2sum_k for a 2x2 block of output pixels per thread, plus what the next two launches of the decoder's backward pass
+// would do with that output: the BN-backward reductions of the layer whose output gradient it is (sum out and
+// sum out * (y - mean), as bn_bwd_reduce_k<0>) and, optionally, the next down2sum of it (lowres = 2x2 sum of out).
+// Everything downstream sees the bf16-rounded out values, exactly as the separate launches would.
+__global__ void __launch_bounds__(TPB, 3) down2sum_bn_k(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict__ mask,
+                                                        const __nv_bfloat16* __restrict__ add, __nv_bfloat16* __restrict__ out,
+                                                        __nv_bfloat16* __restrict__ lowres, const __nv_bfloat16* __restrict__ y,
+                                                        const float* __restrict__ bn, float* __restrict__ sums, int B, int Ho,
+                                                        int Wo, int C, int items_per_block) {
+  ck::pdl_enter();
+  __shared__ float sm[TPB * 8];
+  const int c8 = C >> 3, Hq = Ho >> 1, Wq = Wo >> 1, lanes = TPB / c8;
+  const int cv = threadIdx.x % c8, lane = threadIdx.x / c8;
+  float mu[8], s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  load8f(bn + 2 * C + cv * 8, mu);
+  const int P2 = B * Hq * Wq;
+  const int p0 = blockIdx.x * items_per_block;
+  const int p1 = min(P2, p0 + items_per_block);
+  const IdxDec pdec = make_idxdec(1, Wq, Hq);
+  const int W2 = 2 * Wo;
+  for (int p = p0 + lane; p < p1; p += lanes) {
+    int pp_, j, i, b;
+    idx_dec(pdec, p, 1, Wq, Hq, pp_, j, i, b);
+    float part[2][8];  // (q0 + q1) and (q2 + q3) of the rounded outputs: down2sum_k's summation order
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int h = 2 * i + (q >> 1), w = 2 * j + (q & 1);
+      const int g = ((b * Ho + h) * Wo + w) * c8 + cv;
+      const int base = ((b * 2 * Ho + 2 * h) * W2 + 2 * w) * c8 + cv;
+      const uint4 v0 = ldg16(in + (size_t)base * 8), v1 = ldg16(in + (size_t)(base + c8) * 8);
+      const uint4 v2 = ldg16(in + (size_t)(base + W2 * c8) * 8), v3 = ldg16(in + (size_t)(base + W2 * c8 + c8) * 8);
+      const uint4 yv4 = ldg16(y + (size_t)g * 8);
+      uint4 m4 = make_uint4(0u, 0u, 0u, 0u), t4 = make_uint4(0u, 0u, 0u, 0u);
+      if (mask) m4 = ldg16(mask + (size_t)g * 8);
+      if (add) t4 = ldg16(add + (size_t)g * 8);
+      float a0[8], a1[8], a2[8], a3[8], o[8], yv[8];
+      unpack8(v0, a0); unpack8(v1, a1); unpack8(v2, a2); unpack8(v3, a3); unpack8(yv4, yv);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[e] = (a0[e] + a1[e]) + (a2[e] + a3[e]);
+      if (mask) {
+        float m[8];
+        unpack8(m4, m);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = m[e] > 0.f ? o[e] : 0.f;
+      }
+      if (add) {
+        float t[8];
+        unpack8(t4, t);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] += t[e];
+      }
+      const uint4 pk = pack8(o);
+      float dr[8];
+      unpack8(pk, dr);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        s1[e] += dr[e];
+        s2[e] = fmaf(dr[e], yv[e] - mu[e], s2[e]);
+        part[q >> 1][e] = (q & 1) ? part[q >> 1][e] + dr[e] : dr[e];
+      }
+      stg16(out + (size_t)g * 8, pk);
+    }
+    if (lowres) {
+      float lo[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) lo[e] = part[0][e] + part[1][e];
+      stg16(lowres + (size_t)(((b * Hq + i) * Wq + j) * c8 + cv) * 8, pack8(lo));
+    }
+  }
+  block_channel_atomic(s1, c8, sm, sums);
+  block_channel_atomic(s2, c8, sm, sums + C);
+}
+
 // out = 1[x > 0] * g + add      (first decoder block: gradient into the bottleneck tensor)
 __global__ void __launch_bounds__(TPB) relu_bwd_add_k(const __nv_bfloat16* __restrict__ g, const __nv_bfloat16* __restrict__ x,
                                                       const __nv_bfloat16* __restrict__ add, __nv_bfloat16* __restrict__ out,
@@ -1504,6 +1577,22 @@ int crackfl_down2sum(const void* in, const void* mask, const void* add, void* ou
   const long total = (long)B * Ho * Wo * (C / 8);
   ck::launch(down2sum_k, grid_for(total), TPB, 0, st, (const __nv_bfloat16*)in, (const __nv_bfloat16*)mask,
                                               (const __nv_bfloat16*)add, (__nv_bfloat16*)out, B, Ho, Wo, C);
+  CK_LAUNCH_CHECK();
+  return 0;
+}
+
+int crackfl_down2sum_bn(const void* in, const void* mask, const void* add, void* out, void* lowres, const void* y, const float* bn,
+                        float* sums, int B, int Ho, int Wo, int C, cudaStream_t st) {
+  CK_FITS32((long)B * Ho * Wo * C * 4);
+  if ((Ho | Wo) & 1 || C % 8 || TPB % (C >> 3) || !y || !bn || !sums) return (int)cudaErrorInvalidValue;
+  const int P2 = B * (Ho / 2) * (Wo / 2), lanes = TPB / (C >> 3);
+  static int per_sm = -1;  // tuning knob
+  if (per_sm < 0) { const char* e = getenv("CRACKFL_D2S_BLOCKS_PER_SM"); per_sm = e ? atoi(e) : 3; if (per_sm < 1) per_sm = 3; }
+  int ipb = (P2 + 148 * per_sm - 1) / (148 * per_sm);
+  ipb = (ipb + lanes - 1) / lanes * lanes;
+  ck::launch(down2sum_bn_k, (P2 + ipb - 1) / ipb, TPB, 0, st, (const __nv_bfloat16*)in, (const __nv_bfloat16*)mask,
+             (const __nv_bfloat16*)add, (__nv_bfloat16*)out, (__nv_bfloat16*)lowres, (const __nv_bfloat16*)y, bn, sums, B, Ho, Wo,
+             C, ipb);
   CK_LAUNCH_CHECK();
   return 0;
 }

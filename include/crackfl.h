@@ -128,6 +128,11 @@ int crackfl_pool_bwd_bn(const void* g, const void* argmax_u8, const void* y, con
                         int H, int W, int C, cudaStream_t stream);
 int crackfl_down2sum(const void* in, const void* mask_or_null, const void* add_or_null, void* out, int B, int Ho, int Wo,
                      int C, cudaStream_t stream);
+/* crackfl_down2sum + the two launches that follow it in the decoder's backward pass: sums[c] += sum out, sums[C + c] +=
+   sum out * (y - mean[c]) (= crackfl_bn_bwd_reduce(out, y, bn, mode 0); sums pre-zeroed) and, when lowres != NULL,
+   lowres = 2x2 sum of out (= crackfl_down2sum(out)).  Ho, Wo even. */
+int crackfl_down2sum_bn(const void* in, const void* mask_or_null, const void* add_or_null, void* out, void* lowres_or_null,
+                        const void* y, const float* bn, float* sums, int B, int Ho, int Wo, int C, cudaStream_t stream);
 int crackfl_relu_bwd_add(const void* g, const void* x, const void* add_or_null, void* out, long numel, cudaStream_t stream);
 int crackfl_colsum(const void* g, float* out, long P, int C, cudaStream_t stream);
 

@@ -266,6 +266,36 @@ def test_engine_training_reduces_loss_with_graph():
     assert p.shape == (8, 64, 64) and float(p.min()) >= 0 and float(p.max()) <= 1
 
 
+@pytest.mark.parametrize("B,Ho,Wo,Cc,with_low", [(2, 16, 16, 64, True), (3, 8, 12, 256, False), (16, 32, 32, 128, True), (1, 6, 10, 32, True)])
+def test_down2sum_bn_equals_the_three_launches(B, Ho, Wo, Cc, with_low):
+    """One launch (2x2 sum of the upstream gradient with ReLU mask and residual add, the BN-backward reductions over the
+    result, and the result's own 2x2 sum) against crackfl_down2sum, crackfl_bn_bwd_reduce and crackfl_down2sum again."""
+    L, lib = _lib()
+    torch.manual_seed(1)
+    x = torch.randn(B, 2 * Ho, 2 * Wo, Cc, device="cuda").bfloat16()
+    mask = torch.randn(B, Ho, Wo, Cc, device="cuda").bfloat16()
+    add = torch.randn(B, Ho, Wo, Cc, device="cuda").bfloat16()
+    y = torch.randn(B, Ho, Wo, Cc, device="cuda").bfloat16()
+    bn = torch.cat([torch.rand(Cc, device="cuda") + 0.5, torch.randn(Cc, device="cuda") * 0.2,
+                    torch.randn(Cc, device="cuda") * 0.1, torch.rand(Cc, device="cuda") + 0.5]).contiguous()
+    out_r = torch.zeros(B, Ho, Wo, Cc, device="cuda", dtype=torch.bfloat16); low_r = torch.zeros(B, Ho // 2, Wo // 2, Cc, device="cuda", dtype=torch.bfloat16)
+    sums_r = torch.zeros(2 * Cc, device="cuda")
+    L.check(lib.crackfl_down2sum(x.data_ptr(), mask.data_ptr(), add.data_ptr(), out_r.data_ptr(), B, Ho, Wo, Cc, _st()))
+    L.check(lib.crackfl_bn_bwd_reduce(out_r.data_ptr(), 0, y.data_ptr(), bn.data_ptr(), sums_r.data_ptr(), B, Ho, Wo, Cc, 0, _st()))
+    L.check(lib.crackfl_down2sum(out_r.data_ptr(), 0, 0, low_r.data_ptr(), B, Ho // 2, Wo // 2, Cc, _st()))
+    out = torch.zeros_like(out_r); low = torch.full_like(low_r, 7.0); sums = torch.zeros_like(sums_r)
+    L.check(lib.crackfl_down2sum_bn(x.data_ptr(), mask.data_ptr(), add.data_ptr(), out.data_ptr(),
+                                    low.data_ptr() if with_low else 0, y.data_ptr(), bn.data_ptr(), sums.data_ptr(), B, Ho, Wo, Cc,
+                                    _st()))
+    torch.cuda.synchronize()
+    assert torch.equal(out.view(torch.int16), out_r.view(torch.int16))
+    if with_low:
+        assert torch.equal(low.view(torch.int16), low_r.view(torch.int16))
+    else:
+        assert float((low.float() - 7.0).abs().max()) == 0.0  # untouched
+    assert float((sums - sums_r).abs().max() / sums_r.abs().max()) < 1e-4
+
+
 def test_weight_prep_flat_matches_per_operand_grid():
     """One 32x32 tile per block over all 43 operands (weight_prep_flat_k) writes exactly what the per-operand grid
     (weight_prep_k) writes: every bf16 GEMM operand of the model, forward and transposed, padded entry kernel included."""
