@@ -66,7 +66,9 @@ def dumps_raw(weights: Sequence[np.ndarray]) -> bytes:
     hdr = [RAW_MAGIC, struct.pack("<I", len(weights))]
     body = []
     for w in weights:
-        a = np.ascontiguousarray(w)
+        a = np.asarray(w)
+        if not a.flags.c_contiguous:  # (np.ascontiguousarray would also turn a 0-d array into shape (1,))
+            a = np.ascontiguousarray(a)
         if a.dtype.byteorder == ">":
             a = a.astype(a.dtype.newbyteorder("<"))
         code = _DTYPE_CODES.get(a.dtype.str)

@@ -1,0 +1,66 @@
+"""Property tests (hypothesis) of the pieces every round passes through: aggregation coefficients, the weighted mean and the
+raw tensor framing.  Small random tensor lists instead of the 112-tensor model, so hundreds of cases run in seconds."""
+import numpy as np
+import pytest
+from hypothesis import given, settings, strategies as st
+
+from crackfl.io import weights as wio
+from crackfl.parallel import fedavg as fa
+
+shapes = st.lists(st.lists(st.integers(1, 5), min_size=0, max_size=3).map(tuple), min_size=1, max_size=5)
+
+
+def _updates(shape_list, k, seed):
+    rng = np.random.default_rng(seed)
+    return [[rng.standard_normal(s).astype(np.float32) for s in shape_list] for _ in range(k)]
+
+
+@settings(max_examples=60, deadline=None)
+@given(shapes, st.integers(1, 6), st.integers(0, 2 ** 16))
+def test_uniform_mean_is_the_reference_sum_over_count(shape_list, k, seed):
+    """fl_server.py:92-102: sum the clients' lists element-wise, divide by the number of clients."""
+    ups = _updates(shape_list, k, seed)
+    got = fa.fedavg_mean(ups)
+    for i, s in enumerate(shape_list):
+        want = sum(u[i].astype(np.float64) for u in ups) / k
+        assert got[i].shape == tuple(s) and got[i].dtype == np.float32
+        np.testing.assert_allclose(got[i], want, rtol=1e-5, atol=1e-6)
+
+
+@settings(max_examples=60, deadline=None)
+@given(shapes, st.lists(st.integers(1, 10 ** 6), min_size=1, max_size=6), st.integers(0, 2 ** 16))
+def test_weighted_mean_properties(shape_list, ns, seed):
+    k = len(ns)
+    ups = _updates(shape_list, k, seed)
+    c = fa.normalise_coefficients(k, ns)
+    assert abs(float(c.sum()) - 1.0) < 1e-6 and (c > 0).all()
+    got = fa.fedavg_weighted(ups, ns)
+    for i in range(len(shape_list)):
+        want = sum(ci * u[i].astype(np.float64) for ci, u in zip(c, ups))
+        np.testing.assert_allclose(got[i], want, rtol=1e-4, atol=1e-5)
+        # a convex combination stays inside the clients' range
+        lo = np.min([u[i] for u in ups], axis=0); hi = np.max([u[i] for u in ups], axis=0)
+        assert (got[i] >= lo - 1e-5).all() and (got[i] <= hi + 1e-5).all()
+    # scaling every sample count by the same factor changes nothing
+    again = fa.fedavg_weighted(ups, [7 * n for n in ns])
+    for a, b in zip(got, again):
+        np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-6)
+    # identical clients: the mean is that client, whatever the counts
+    same = fa.fedavg_weighted([ups[0]] * k, ns)
+    for a, b in zip(same, ups[0]):
+        np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-6)
+
+
+@settings(max_examples=60, deadline=None)
+@given(shapes, st.integers(0, 2 ** 16))
+def test_raw_framing_roundtrip_and_rejects_truncation(shape_list, seed):
+    w = _updates(shape_list, 1, seed)[0]
+    buf = wio.dumps_raw(w)
+    back = wio.loads_raw(buf)
+    assert len(back) == len(w)
+    for a, b in zip(w, back):
+        assert a.shape == b.shape and a.dtype == b.dtype and np.array_equal(a, b)
+    assert wio.loads_auto(buf) is not None
+    if len(buf) > 1:
+        with pytest.raises(Exception):
+            wio.loads_raw(buf[:-1])
