@@ -156,7 +156,9 @@ class _Writer:
         return addr
 
     def write_dataset(self, ds: H5Dataset) -> int:
-        a = np.ascontiguousarray(ds.data)
+        a = np.asarray(ds.data)
+        if not a.flags.c_contiguous:  # (np.ascontiguousarray would turn a scalar dataset - Keras' `iterations` - into shape (1,))
+            a = np.ascontiguousarray(a)
         if a.dtype.byteorder == ">":
             a = a.astype(a.dtype.newbyteorder("<"))
         raw = a.tobytes()
@@ -479,14 +481,20 @@ class _Reader:
                 if addr == UNDEF:
                     return np.zeros(shape, dtype=dt if not isinstance(dt, tuple) else object)
                 raw = bytes(self.b[self.base + addr:self.base + addr + size])
-                out = self._decode(dt, shape, raw)
-                return np.asarray(out)
+                return self._as_data(self._decode(dt, shape, raw), dt)
             if cls == 0:
                 size = struct.unpack_from("<H", layout, 2)[0]
-                return np.asarray(self._decode(dt, shape, layout[4:4 + size]))
+                return self._as_data(self._decode(dt, shape, layout[4:4 + size]), dt)
             if cls == 2:
                 return self._chunked(layout, dt, shape, filters)
         raise H5FormatError(f"unsupported data layout (version {ver})")
+
+    @staticmethod
+    def _as_data(out, dt) -> np.ndarray:
+        """_decode hands scalars back as Python values (what attribute readers want); a scalar DATASET keeps its dtype."""
+        if isinstance(out, np.ndarray) or isinstance(dt, tuple):
+            return np.asarray(out)
+        return np.asarray(out, dtype=dt)
 
     def _chunked(self, layout: bytes, dt, shape, filters) -> np.ndarray:
         rank1 = layout[2]

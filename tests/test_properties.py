@@ -64,3 +64,49 @@ def test_raw_framing_roundtrip_and_rejects_truncation(shape_list, seed):
     if len(buf) > 1:
         with pytest.raises(Exception):
             wio.loads_raw(buf[:-1])
+
+
+# ---- pure-Python HDF5 subset: random trees survive a write -> read round trip
+from crackfl.io import hdf5 as h5  # noqa: E402
+
+_names = st.text(alphabet="abcdefghijklmnopqrstuvwxyzABCXYZ0123456789_:.", min_size=1, max_size=24)
+_dtypes = st.sampled_from([np.float32, np.float64, np.int32, np.int64, np.uint8])
+_arrays = st.tuples(_dtypes, st.lists(st.integers(0, 4), min_size=0, max_size=4), st.integers(0, 2 ** 16))
+
+
+def _mk(dt, shape, seed):
+    rng = np.random.default_rng(seed)
+    return (rng.standard_normal(shape) * 50).astype(dt)
+
+
+@settings(max_examples=60, deadline=None)
+@given(st.dictionaries(_names, st.dictionaries(_names, _arrays, min_size=0, max_size=12), min_size=0, max_size=4),
+       st.dictionaries(_names, _arrays, min_size=0, max_size=3))
+def test_hdf5_random_tree_roundtrip(groups, top):
+    root = h5.H5Group()
+    root.attrs["n_groups"] = np.array([len(groups)], np.int64)
+    for gname, dsets in groups.items():
+        g = root.require_group(gname)
+        g.attrs["label"] = gname.encode()
+        for dname, (dt, shape, seed) in dsets.items():
+            g.children[dname] = h5.H5Dataset(_mk(dt, shape, seed), {"seed": np.array([seed], np.int32)})
+    for dname, (dt, shape, seed) in top.items():
+        if dname not in root.children:
+            root.children[dname] = h5.H5Dataset(_mk(dt, shape, seed))
+    w = h5._Writer()
+    back = h5.read_h5_bytes(w.finish(root))
+    assert int(back.attrs["n_groups"][0]) == len(groups)
+    for gname, dsets in groups.items():
+        g = back[gname]
+        assert bytes(g.attrs["label"]) == gname.encode()
+        assert set(g.children) >= set(dsets)
+        for dname, (dt, shape, seed) in dsets.items():
+            want = _mk(dt, shape, seed)
+            got = g.children[dname].data
+            assert got.dtype == want.dtype and got.shape == want.shape and np.array_equal(got, want)
+            assert int(g.children[dname].attrs["seed"][0]) == seed
+    for dname, (dt, shape, seed) in top.items():
+        if isinstance(back.children.get(dname), h5.H5Dataset):
+            want = _mk(dt, shape, seed)
+            got = back.children[dname].data
+            assert got.dtype == want.dtype and got.shape == want.shape and np.array_equal(got, want)
