@@ -110,3 +110,82 @@ def test_hdf5_random_tree_roundtrip(groups, top):
             want = _mk(dt, shape, seed)
             got = back.children[dname].data
             assert got.dtype == want.dtype and got.shape == want.shape and np.array_equal(got, want)
+
+
+# ---- server round state machine under random interleavings (fl_server.py:107-150 semantics + the documented fixes)
+from crackfl.config import fast_test_config  # noqa: E402
+from crackfl.models.spec import REFERENCE_SPEC as S  # noqa: E402
+from crackfl.protocol import client as C  # noqa: E402
+from crackfl.protocol import messages as pb  # noqa: E402
+from crackfl.protocol.server import FLServer  # noqa: E402
+
+_W0 = S.init_weights(0)
+
+
+class _Clock:
+    def __init__(self):
+        self.t = 0.0
+
+    def __call__(self):
+        return self.t
+
+    def sleep(self, s):
+        self.t += s
+
+
+@settings(max_examples=12, deadline=None)
+@given(st.integers(1, 4), st.integers(1, 3), st.randoms(use_true_random=False))
+def test_round_state_machine_under_random_interleavings(tmp_path_factory, k, rounds, rnd):
+    tmp = tmp_path_factory.mktemp("sm")
+    cfg = fast_test_config()
+    cfg.server.weights_dir = str(tmp / "w"); cfg.server.log_dir = str(tmp / "l"); cfg.server.max_rounds = rounds
+    clk = _Clock()
+    srv = FLServer(cfg, [w.copy() for w in _W0], S, clock=clk, sleep=clk.sleep, log=lambda s: None)
+
+    def one(req):
+        out = srv.handle(req)
+        assert len(out) == 1
+        return out[0]
+
+    names = []
+    for i in range(k):
+        c = pb.from_config(one(next(C.request_ready(f"c{i}"))).ready_rep.config)
+        assert c["state"] == "SW"
+        names.append(c["cname"])
+    finished = set()
+    for r in range(1, rounds + 1):
+        order = names[:]
+        rnd.shuffle(order)
+        offs = {n: float(rnd.randint(-3, 3)) for n in names}
+        want0 = _W0[0] + np.float32(sum(offs.values()) / k)
+        for pos, n in enumerate(order):
+            if r > 1 and rnd.random() < 0.3:  # a stale upload from the previous round changes nothing
+                reqs = list(C.request_traindone(n, r - 1, wio.dumps_raw(_W0), {}, 1 << 30))
+                assert pb.from_config(one(reqs[0]).update_rep.config)["state"] == "RESP_ACY"
+            if rnd.random() < 0.5:  # a version poll in the middle of the round: told to wait
+                v = one(next(C.request_model_version(r, r))).version_rep
+                assert v.state == pb.State.WAIT
+            w = [x + np.float32(offs[n]) if i == 0 else x for i, x in enumerate(_W0)]
+            reqs = list(C.request_traindone(n, r, wio.dumps_raw(w), {}, 1 << 30))
+            rep = one(reqs[0]).update_rep
+            state = pb.from_config(rep.config)["state"]
+            last = pos == k - 1
+            if not last:
+                assert state == "RESP_ACY" and rep.buffer_chunk == b""
+            elif r < rounds:
+                assert state == "RESP_ARY"
+                np.testing.assert_allclose(wio.loads_auto(rep.buffer_chunk)[0], want0, rtol=1e-5, atol=1e-5)
+            else:
+                assert state == "FIN"
+                finished.add(n)
+        np.testing.assert_allclose(srv.global_weights[0], want0, rtol=1e-5, atol=1e-5)
+        assert srv.model_version == cfg.server.initial_model_version + r and len(srv.history) == r
+        for n in order[:-1]:  # the clients that were told to wait learn the outcome from the poll
+            v = one(next(C.request_model_version(r, r))).version_rep
+            if r < rounds:
+                assert v.state == pb.State.NOT_WAIT and pb.from_config(v.config)["current_round"] == r + 1
+                np.testing.assert_allclose(wio.loads_auto(v.buffer_chunk)[0], want0, rtol=1e-5, atol=1e-5)
+            else:
+                assert v.state == pb.State.FIN
+                finished.add(n)
+    assert finished == set(names) and srv.finished
