@@ -114,7 +114,7 @@ class FLServer:
         self.finished = False
         self.history: List[dict] = []
         self._payload_cache = {}
-        self._chunks: Dict[str, Dict[int, bytes]] = {}
+        self._chunks: Dict[str, tuple] = {}  # cname -> (chunk_count, {index: bytes})
         self._next_id = 0
         self.final_clients: List[str] = []  # reporters of the last round: each must be told FIN before the server stops
         self.fin_answered: set = set()
@@ -380,17 +380,31 @@ class FLServer:
         n = (len(blob) + cap - 1) // cap
         return [make(blob[i * cap:(i + 1) * cap], {**cfgd, "chunk_index": i, "chunk_count": n}) for i in range(n)]
 
+    MAX_CHUNKS = 4096
+
     def _assemble_chunks(self, cname: str, chunk: bytes, ucfg: dict) -> Optional[bytes]:
+        """Chunked 'D' payloads (extension; the reference sends one message, fl_client.py:61-65).  Returns the whole payload
+        once every index 0..n-1 has arrived (any order, a repeated index overwrites), None before that.  A malformed
+        header is a ValueError for that client only; a different chunk_count, or an unchunked payload, from the same
+        client supersedes what it had half-sent."""
         n = int(ucfg.get("chunk_count", 0) or 0)
         if n <= 1:
+            with self.lock:
+                self._chunks.pop(cname, None)
             return chunk
+        i = int(ucfg.get("chunk_index", 0) or 0)
+        if n > self.MAX_CHUNKS or not 0 <= i < n:
+            raise ValueError(f"update from {cname}: chunk {i} of {n} is not acceptable")
         with self.lock:
-            parts = self._chunks.setdefault(cname, {})
-            parts[int(ucfg.get("chunk_index", 0) or 0)] = chunk
-            if len(parts) < n:
+            ent = self._chunks.get(cname)
+            if ent is None or ent[0] != n:
+                ent = (n, {})
+                self._chunks[cname] = ent
+            ent[1][i] = chunk
+            if len(ent[1]) < n:
                 return None
             del self._chunks[cname]
-        return b"".join(parts[i] for i in range(n))
+        return b"".join(ent[1][k] for k in range(n))
 
     # gRPC servicer entry point (``TransportService.transport`` fl_server.py:209-212)
     def transport(self, request_iterator, context=None):

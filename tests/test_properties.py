@@ -189,3 +189,41 @@ def test_round_state_machine_under_random_interleavings(tmp_path_factory, k, rou
                 assert v.state == pb.State.FIN
                 finished.add(n)
     assert finished == set(names) and srv.finished
+
+
+@settings(max_examples=80, deadline=None)
+@given(st.binary(min_size=0, max_size=4000), st.integers(1, 700), st.randoms(use_true_random=False))
+def test_chunked_upload_reassembles_in_any_order(tmp_path_factory, payload, cap, rnd):
+    tmp = tmp_path_factory.mktemp("ch")
+    cfg = fast_test_config()
+    cfg.server.weights_dir = str(tmp / "w"); cfg.server.log_dir = str(tmp / "l")
+    srv = FLServer(cfg, [w.copy() for w in _W0], S, log=lambda s: None)
+    reqs = list(C.request_traindone("c0", 1, payload, {"num_samples": 3}, cap))
+    assert b"".join(r.update_req.buffer_chunk for r in reqs) == payload
+    order = list(range(len(reqs)))
+    rnd.shuffle(order)
+    if len(order) > 1 and rnd.random() < 0.5:
+        order.insert(rnd.randrange(len(order)), order[0])  # one chunk arrives twice
+    out = None
+    for pos, i in enumerate(order):
+        u = reqs[i].update_req
+        out = srv._assemble_chunks(u.cname, u.buffer_chunk, pb.from_config(u.config))
+        if pos < len(order) - 1 and len(reqs) > 1:
+            assert out is None or pos >= len(set(order[:pos + 1])) - 1
+    assert out == payload
+    assert "c0" not in srv._chunks  # nothing is left behind
+
+
+def test_chunk_headers_that_cannot_be_right_are_refused(tmp_path):
+    cfg = fast_test_config()
+    cfg.server.weights_dir = str(tmp_path / "w"); cfg.server.log_dir = str(tmp_path / "l")
+    srv = FLServer(cfg, [w.copy() for w in _W0], S, log=lambda s: None)
+    for hdr in ({"chunk_index": 3, "chunk_count": 3}, {"chunk_index": -1, "chunk_count": 2}, {"chunk_index": 0, "chunk_count": 10 ** 6}):
+        with pytest.raises(ValueError):
+            srv._assemble_chunks("c0", b"x", hdr)
+    # a half-sent upload is superseded by a fresh one with another chunk count, and by an unchunked payload
+    assert srv._assemble_chunks("c0", b"a", {"chunk_index": 0, "chunk_count": 3}) is None
+    assert srv._assemble_chunks("c0", b"b", {"chunk_index": 0, "chunk_count": 2}) is None
+    assert srv._assemble_chunks("c0", b"c", {"chunk_index": 1, "chunk_count": 2}) == b"bc"
+    assert srv._assemble_chunks("c0", b"a", {"chunk_index": 0, "chunk_count": 3}) is None
+    assert srv._assemble_chunks("c0", b"whole", {}) == b"whole" and "c0" not in srv._chunks
