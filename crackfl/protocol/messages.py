@@ -131,11 +131,15 @@ __all__ = ["Scalar", "ReadyReq", "UpdateReq", "VersionReq", "ReadyRep", "UpdateR
 
 
 def scalar(v) -> "Scalar":
-    """Python value -> Scalar (bool/int -> scint32, float -> scfloat, str -> scstring)."""
-    if isinstance(v, bool) or isinstance(v, int):
-        return Scalar(scint32=int(v))
-    if isinstance(v, float):
-        return Scalar(scfloat=v)
+    """Python / NumPy value -> Scalar (bool/int -> scint32, float -> scfloat, anything else -> scstring).  An integer that
+    does not fit int32 travels as its decimal string (receivers convert with int()/float()), never as an exception."""
+    import numbers
+    import numpy as np
+    if isinstance(v, (bool, numbers.Integral, np.bool_)):
+        i = int(v)
+        return Scalar(scint32=i) if -(1 << 31) <= i < (1 << 31) else Scalar(scstring=str(i))
+    if isinstance(v, numbers.Real):
+        return Scalar(scfloat=float(v))
     return Scalar(scstring=str(v))
 
 

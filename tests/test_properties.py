@@ -227,3 +227,25 @@ def test_chunk_headers_that_cannot_be_right_are_refused(tmp_path):
     assert srv._assemble_chunks("c0", b"c", {"chunk_index": 1, "chunk_count": 2}) == b"bc"
     assert srv._assemble_chunks("c0", b"a", {"chunk_index": 0, "chunk_count": 3}) is None
     assert srv._assemble_chunks("c0", b"whole", {}) == b"whole" and "c0" not in srv._chunks
+
+
+@settings(max_examples=200, deadline=None)
+@given(st.dictionaries(st.text(min_size=1, max_size=12),
+                       st.one_of(st.booleans(), st.integers(-2 ** 40, 2 ** 40), st.floats(allow_nan=False, width=32),
+                                 st.text(max_size=20),
+                                 st.integers(-1000, 1000).map(np.int64), st.integers(0, 255).map(np.uint8),
+                                 st.floats(-1e3, 1e3).map(np.float32), st.booleans().map(np.bool_)), max_size=8))
+def test_config_map_codec_never_raises_and_keeps_values(d):
+    """The Scalar map of every message (fl_server.py:61-73): whatever a trainer puts into its metrics must get across."""
+    back = pb.from_config(pb.to_config(d))
+    assert set(back) == set(d)
+    for k, v in d.items():
+        b = back[k]
+        if isinstance(v, (bool, np.bool_)):
+            assert b == int(v)
+        elif isinstance(v, (int, np.integer)):
+            assert int(b) == int(v)  # out-of-int32 values travel as their decimal string
+        elif isinstance(v, (float, np.floating)):
+            assert isinstance(b, float) and (b == np.float32(v) or abs(b - float(v)) <= 1e-6 * abs(float(v)))
+        else:
+            assert b == v
