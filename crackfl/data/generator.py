@@ -90,6 +90,10 @@ def list_jpgs(d: str) -> List[str]:
 def split_paths(images: List[str], masks: List[str], count: int = 6213, seed: int = 1337, mode: str = "client"):
     """Returns (train_x, train_y, val_x, val_y).  See module docstring for the two modes."""
     images, masks = list(images), list(masks)
+    if len(images) != len(masks):
+        # the two same-seed shuffles only keep pairs aligned for lists of equal length (the reference would train on
+        # mismatched pairs without a word)
+        raise ValueError(f"{len(images)} images but {len(masks)} masks")
     random.Random(seed).shuffle(images)
     random.Random(seed).shuffle(masks)
     if mode == "client":  # client_fit_model.py:78-81

@@ -249,3 +249,58 @@ def test_config_map_codec_never_raises_and_keeps_values(d):
             assert isinstance(b, float) and (b == np.float32(v) or abs(b - float(v)) <= 1e-6 * abs(float(v)))
         else:
             assert b == v
+
+
+def test_config_json_round_trip_and_override_types(tmp_path):
+    """Every knob survives to_dict -> JSON -> load, and a --section.key=value override keeps the field's type."""
+    import dataclasses
+    import json as _json
+    from crackfl.config import Config
+    base = Config()
+    base.train.image_size = (96, 160); base.server.round_timeout_s = 12.5; base.train.validate = False
+    p = tmp_path / "c.json"
+    p.write_text(_json.dumps(base.to_dict()))
+    back = Config.load(str(p), env=False)
+    assert back.to_dict() == base.to_dict() and back.train.image_size == (96, 160)
+    for sec_f in dataclasses.fields(base):
+        sec = getattr(base, sec_f.name)
+        for f in dataclasses.fields(sec):
+            cur = getattr(sec, f.name)
+            if isinstance(cur, bool):
+                txt, want = ("false" if cur else "true"), (not cur)
+            elif isinstance(cur, int):
+                txt, want = str(cur + 3), cur + 3
+            elif isinstance(cur, float):
+                txt, want = repr(cur + 0.25), cur + 0.25
+            elif isinstance(cur, tuple):
+                txt, want = "48x80", (48, 80)
+            else:
+                txt, want = "some/value", "some/value"
+            c = Config.load(None, overrides=[f"--{sec_f.name}.{f.name}={txt}"], env=False)
+            got = getattr(getattr(c, sec_f.name), f.name)
+            assert got == want and type(got) is type(want), (sec_f.name, f.name, got)
+    with pytest.raises(KeyError):
+        Config.load(None, overrides=["--train.no_such_knob=1"], env=False)
+    with pytest.raises(KeyError):
+        Config.load(None, overrides=["--nosection.x=1"], env=False)
+
+
+@settings(max_examples=80, deadline=None)
+@given(st.integers(0, 60), st.integers(0, 70), st.integers(0, 2 ** 16), st.sampled_from(["client", "script"]))
+def test_split_keeps_pairs_together_and_partitions_the_set(n, count, seed, mode):
+    """client_fit_model.py:76-82 / test/Segmentation.py:84-90: two same-seed shuffles, then a cut."""
+    from crackfl.data.generator import split_paths
+    imgs = [f"img/{i:04d}.jpg" for i in range(n)]
+    msks = [f"msk/{i:04d}.jpg" for i in range(n)]
+    tx, ty, vx, vy = split_paths(imgs, msks, count, seed, mode)
+    assert len(tx) == len(ty) and len(vx) == len(vy)
+    for a, b in zip(tx + vx, ty + vy):
+        assert a[4:] == b[4:]  # image i stays with mask i
+    if count > 0 or mode == "client":
+        assert sorted(tx + vx) == imgs and not set(tx) & set(vx)
+    if mode == "client":
+        assert len(tx) == min(count, n)
+    elif count > 0:
+        assert len(vx) == min(count, n)
+    with pytest.raises(ValueError):
+        split_paths(imgs + ["img/extra.jpg"], msks, count, seed, mode)
