@@ -262,7 +262,9 @@ class FLServer:
         strat = getattr(self.aggregator, "strategy", None)
         snap = strat.state() if strat is not None and hasattr(strat, "state") else None
         if snap and snap.get("m") is not None:
-            snap = {"m": np.array(snap["m"], copy=True), "v": np.array(snap["v"], copy=True)}
+            # deep copy: the moments are LISTS of per-tensor arrays (different shapes) that aggregate() re-binds in place
+            snap = {k: ([np.array(a, copy=True) for a in v] if isinstance(v, (list, tuple)) else np.array(v, copy=True))
+                    for k, v in snap.items() if v is not None}
         else:
             snap = None
         try:

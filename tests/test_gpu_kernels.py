@@ -398,6 +398,33 @@ def test_server_with_device_aggregator(tmp_path):
     assert srv.history[0]["aggregator"] == "device"
 
 
+def test_server_with_device_aggregator_fedadam_two_rounds(tmp_path):
+    """FedAdam through the server on the device aggregator for more than one round: the guarded aggregation snapshots the
+    optimiser moments (per-tensor lists) before every round; the result follows the host FedAdam."""
+    from crackfl.config import fast_test_config
+    from crackfl.io import weights as wio
+    from crackfl.models.spec import REFERENCE_SPEC as S
+    from crackfl.parallel import fedavg as fa
+    from crackfl.parallel.device_agg import DeviceAggregator
+    from crackfl.protocol import client as Cl, messages as pb
+    from crackfl.protocol.server import FLServer
+    cfg = fast_test_config()
+    cfg.server.weights_dir = str(tmp_path / "sw"); cfg.server.strategy = "fedadam"; cfg.server.max_rounds = 3
+    srv = FLServer(cfg, S.init_weights(0), S, aggregator=DeviceAggregator(S, "fedadam", max_clients=4), log=lambda s: None)
+    srv.handle(next(Cl.request_ready("a")))
+    w0 = S.init_weights(0)
+    ref = fa.FedAdam(eta=cfg.server.fedadam_eta, beta1=cfg.server.fedadam_beta1, beta2=cfg.server.fedadam_beta2,
+                     tau=cfg.server.fedadam_tau, trainable_mask=[t.trainable for t in S.tensors])
+    g = [w.copy() for w in w0]
+    for r in (1, 2):
+        up = [x + np.float32(0.01 * r) for x in w0]
+        rep = srv.handle(list(Cl.request_traindone("a", r, wio.dumps_raw(up), {"num_samples": 2}, 1 << 30))[0])[0]
+        assert pb.from_config(rep.update_rep.config)["state"] == "RESP_ARY"
+        g = ref.aggregate(g, [up], [2])
+        np.testing.assert_allclose(srv.global_weights[0], g[0], rtol=1e-4, atol=1e-5)
+    assert srv.history[-1]["aggregator"] == "device"
+
+
 @pytest.mark.parametrize("B,H,W,Cc,mode", [(2, 32, 32, 64, 0), (2, 20, 24, 32, 1), (1, 16, 16, 128, 1), (2, 14, 14, 64, 0),
                                            (16, 32, 32, 256, 1), (9, 40, 48, 32, 0)])  # last two: CTAs that span channel blocks / many tiles
 def test_dw3x3_tma_fwd_dgrad_wgrad(B, H, W, Cc, mode):

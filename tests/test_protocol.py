@@ -343,3 +343,39 @@ def test_serve_forever_keeps_serving_until_every_client_heard_fin(tmp_path, monk
     assert results[0][0]["state"] == "FIN" and results[1][0]["state"] == "FIN"
     assert results[0][1], "the first reporter must still be able to fetch the final model"
     assert srv.all_fin_delivered()
+
+
+def test_fedadam_on_the_host_aggregator_runs_past_round_one_and_survives_a_failed_aggregation(tmp_path):
+    """The guarded aggregation snapshots the server optimiser's moments before every round: per-tensor lists of different
+    shapes (a ragged np.array() of them raised from round 2 on), restored when the aggregation fails."""
+    from crackfl.parallel import fedavg as fa
+    srv, _, cfg = _server(tmp_path, strategy="fedadam", max_rounds=4, aggregator="host")
+    _ready(srv, "a")
+    w0 = S.init_weights(0)
+    ref = fa.FedAdam(eta=cfg.server.fedadam_eta, beta1=cfg.server.fedadam_beta1, beta2=cfg.server.fedadam_beta2,
+                     tau=cfg.server.fedadam_tau, trainable_mask=[t.trainable for t in S.tensors])
+    g = [w.copy() for w in w0]
+    for r in (1, 2):
+        up = [x + np.float32(0.01 * r) for x in w0]
+        c, _ = _done(srv, "a", r, up, {"num_samples": 4})
+        assert c["state"] == "RESP_ARY" and c["current_round"] == r + 1
+        g = ref.aggregate(g, [up], [4])
+        np.testing.assert_allclose(srv.global_weights[0], g[0], rtol=1e-5, atol=1e-6)
+    # round 3: the aggregator fails once; the moments must be what they were before the attempt
+    strat = srv.aggregator.strategy
+    m_before = [a.copy() for a in strat.m]
+    real = srv.aggregator.aggregate
+
+    def boom(*a, **k):
+        strat.m[0] = strat.m[0] + 123.0  # a half-done update
+        raise RuntimeError("aggregator down")
+    srv.aggregator.aggregate = boom
+    with pytest.raises(RuntimeError):
+        _done(srv, "a", 3, [x + np.float32(0.03) for x in w0], {"num_samples": 4})
+    np.testing.assert_array_equal(strat.m[0], m_before[0])
+    srv.aggregator.aggregate = real
+    up = [x + np.float32(0.03) for x in w0]
+    c, _ = _done(srv, "a", 3, up, {"num_samples": 4})
+    assert c["state"] == "RESP_ARY"
+    g = ref.aggregate(g, [up], [4])
+    np.testing.assert_allclose(srv.global_weights[0], g[0], rtol=1e-5, atol=1e-6)
