@@ -379,3 +379,28 @@ def test_fedadam_on_the_host_aggregator_runs_past_round_one_and_survives_a_faile
     assert c["state"] == "RESP_ARY"
     g = ref.aggregate(g, [up], [4])
     np.testing.assert_allclose(srv.global_weights[0], g[0], rtol=1e-5, atol=1e-6)
+
+
+def test_fedadam_server_resumes_with_its_moments(tmp_path):
+    """A resumed FedAdam federation continues exactly like an uninterrupted one: the optimiser moments are part of the
+    checkpoint (extension; the reference has neither a server optimiser nor a resume)."""
+    w0 = S.init_weights(0)
+    ups = {r: [x + np.float32(0.02 * r) for x in w0] for r in (1, 2, 3)}
+    # uninterrupted
+    a, _, _ = _server(tmp_path / "u", strategy="fedadam", max_rounds=5, aggregator="host")
+    _ready(a, "c")
+    for r in (1, 2, 3):
+        _done(a, "c", r, ups[r], {"num_samples": 3})
+    # interrupted after round 2
+    b, _, cfg = _server(tmp_path / "i", strategy="fedadam", max_rounds=5, aggregator="host")
+    _ready(b, "c")
+    for r in (1, 2):
+        _done(b, "c", r, ups[r], {"num_samples": 3})
+    cfg.server.resume = True
+    b2 = FLServer(cfg, S.init_weights(9), S, log=lambda s: None)
+    assert b2.current_round == 3 and b2.model_version == 3 and b2.ready_clients == ["c"]
+    assert b2.aggregator.strategy.m is not None
+    c, _ = _done(b2, "c", 3, ups[3], {"num_samples": 3})
+    assert c["state"] == "RESP_ARY"
+    for x, y in zip(b2.global_weights, a.global_weights):
+        np.testing.assert_allclose(x, y, rtol=1e-6, atol=1e-7)
